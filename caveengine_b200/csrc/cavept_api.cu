@@ -1,0 +1,704 @@
+// C ABI of libcavept (include/cavept.h): context, scene upload, BVH build, render,
+// read-back.  Host logic mirrors cave/engine/renderer/path_tracer/path_tracer.cpp;
+// all geometry/tracing work is done by the kernels in kernels.cu.  No CPU path.
+#include <cuda_runtime.h>
+
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../../include/cavept.h"
+#include "kernels.h"
+#include "tlas_host.h"
+
+using namespace cavept;
+
+namespace {
+
+template<class T>
+struct DevBuf {
+    T* ptr = nullptr;
+    size_t cap = 0;  // elements
+    cudaError_t reserve(size_t n) {
+        if (n <= cap) return cudaSuccess;
+        if (ptr) cudaFree(ptr);
+        ptr = nullptr;
+        cap = 0;
+        const size_t want = n + n / 8 + 16;
+        cudaError_t e = cudaMalloc(&ptr, want * sizeof(T));
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() {
+        if (ptr) cudaFree(ptr);
+        ptr = nullptr;
+        cap = 0;
+    }
+};
+
+struct MeshRecord {
+    int built = -1;  // order of first appearance among instances, or -1 if unreferenced
+    int vertex_count = 0, tri_count = 0;
+    int vert_off = 0, tri_off = 0, node_off = 0;
+    int first_material = 0;  // material of the first instance using this mesh (path_tracer.cpp:227-231)
+};
+
+}  // namespace
+
+struct cavept_ctx {
+    cavept_config cfg{};
+    int device = 0;
+    int mode = CAVEPT_MODE_NONE;
+    bool scene_resident = false;
+    bool dirty = true;
+    bool count_visits = false;
+    std::string last_error;
+    CudaExec ex;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr;
+
+    // scene bookkeeping
+    std::vector<MeshRecord> meshes;
+    std::vector<int> built_order;  // built index -> input mesh id
+    std::vector<cavept_instance> instances;
+    std::vector<cavept_material> materials;
+    std::vector<GpuPtMesh> gpu_meshes;
+    std::vector<GpuPtMaterial> gpu_materials;
+    int n_verts = 0, n_tris = 0, n_nodes = 0, n_pairs = 0, n_fast_nodes = 0, tlas_root = 0, tlas_depth = 0;
+
+    // reference-layout arrays
+    DevBuf<GpuPtVertex> d_vertices;
+    DevBuf<GpuPtIndex> d_indices;
+    DevBuf<GpuPtBvh> d_nodes;
+    DevBuf<GpuPtMesh> d_meshes;
+    DevBuf<GpuPtMaterial> d_materials;
+    // production layout
+    DevBuf<FastNode> d_fnodes;
+    DevBuf<FastTri> d_ftris;
+    DevBuf<int> d_inst_root;
+    // upload staging
+    DevBuf<float> d_raw_pos, d_raw_nrm;
+    DevBuf<uint32_t> d_raw_idx;
+    DevBuf<int> d_tri_off, d_vert_off;
+    // build scratch
+    DevBuf<F4> d_tri_bmin, d_tri_bmax, d_tri_centroid;
+    DevBuf<int> d_order, d_order_next, d_node_of, d_node_of_next, d_scan, d_scan_tmp, d_counters;
+    DevBuf<unsigned char> d_flags;
+    DevBuf<BuildItem> d_items, d_items_next;
+    DevBuf<ItemAccum> d_accum_items;
+    DevBuf<ItemBins> d_bins;
+    DevBuf<int> d_node_parent, d_node_count, d_is_pair, d_pair_rank, d_leaf_tris, d_tri_base;
+    // image
+    DevBuf<F4> d_accum, d_tone;
+    DevBuf<unsigned char> d_tone8;
+    DevBuf<unsigned long long> d_stats;
+
+    float cam_pos[3] = { 0, 0, 0 }, cam_right[3] = { 1, 0, 0 }, cam_up[3] = { 0, 1, 0 }, cam_fwd[3] = { 0, 0, 1 };
+    float cam_fov = 50.0f;
+
+    cavept_stats stats{};
+    int build_levels = 0;
+};
+
+namespace {
+
+int fail(cavept_ctx* ctx, int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    if (ctx) ctx->last_error = buf;
+    return code;
+}
+
+#define CU(ctx, call)                                                                                   \
+    do {                                                                                                \
+        cudaError_t e_ = (call);                                                                        \
+        if (e_ != cudaSuccess) return fail(ctx, CAVEPT_ERR_CUDA, "%s: %s", #call, cudaGetErrorString(e_)); \
+    } while (0)
+
+int check_exec(cavept_ctx* ctx, const char* where) {
+    if (ctx->ex.first_error != cudaSuccess) {
+        const cudaError_t e = ctx->ex.first_error;
+        ctx->ex.first_error = cudaSuccess;
+        return fail(ctx, CAVEPT_ERR_CUDA, "%s: %s", where, cudaGetErrorString(e));
+    }
+    return CAVEPT_OK;
+}
+
+int select_device(cavept_ctx* ctx) {
+    CU(ctx, cudaSetDevice(ctx->device));
+    return CAVEPT_OK;
+}
+
+// GpuPtMaterial from MaterialComponent, path_tracer.cpp:140-145
+GpuPtMaterial make_gpu_material(const cavept_material& m) {
+    GpuPtMaterial g;
+    for (int k = 0; k < 3; ++k) {
+        g.baseColor[k] = m.base_color[k];
+        g.emissive[k] = g.baseColor[k] * m.emissive;
+    }
+    g.roughness = m.roughness;
+    g.metallic = m.metallic;
+    return g;
+}
+
+// UpdateAccelStructure (path_tracer.cpp:120-201): materials de-duplicated in mesh-key
+// order, instance array with world matrix + glm::inverse.
+int rebuild_instance_arrays(cavept_ctx* ctx) {
+    std::map<int, int> lookup;  // material id -> GpuPtMaterial slot
+    ctx->gpu_materials.clear();
+    for (size_t mesh_id = 0; mesh_id < ctx->meshes.size(); ++mesh_id) {  // std::map<Guid, MeshData> iteration == ascending key
+        const MeshRecord& rec = ctx->meshes[mesh_id];
+        if (rec.built < 0) continue;
+        if (lookup.count(rec.first_material)) continue;
+        lookup[rec.first_material] = (int)ctx->gpu_materials.size();
+        ctx->gpu_materials.push_back(make_gpu_material(ctx->materials[rec.first_material]));
+    }
+    ctx->gpu_meshes.resize(ctx->instances.size());
+    std::vector<int> inst_root(ctx->instances.size());
+    for (size_t i = 0; i < ctx->instances.size(); ++i) {
+        const cavept_instance& in = ctx->instances[i];
+        const MeshRecord& rec = ctx->meshes[in.mesh];
+        GpuPtMesh& g = ctx->gpu_meshes[i];
+        std::memset(&g, 0, sizeof(g));
+        std::memcpy(g.transform, in.transform, sizeof(g.transform));
+        mat4_inverse(g.transform, g.transformInv);
+        g.rootBvhId = rec.node_off;
+        g.materialId = lookup[rec.first_material];
+        inst_root[i] = 2 * ctx->n_pairs + rec.built;
+    }
+    CU(ctx, ctx->d_meshes.reserve(ctx->gpu_meshes.size()));
+    CU(ctx, ctx->d_materials.reserve(ctx->gpu_materials.size()));
+    CU(ctx, ctx->d_inst_root.reserve(inst_root.size()));
+    ctx->ex.upload(ctx->d_meshes.ptr, ctx->gpu_meshes.data(), ctx->gpu_meshes.size() * sizeof(GpuPtMesh));
+    ctx->ex.upload(ctx->d_materials.ptr, ctx->gpu_materials.data(), ctx->gpu_materials.size() * sizeof(GpuPtMaterial));
+    ctx->ex.upload(ctx->d_inst_root.ptr, inst_root.data(), inst_root.size() * sizeof(int));
+    CU(ctx, cudaStreamSynchronize(ctx->ex.stream));
+    return check_exec(ctx, "instance upload");
+}
+
+// TLAS over the instances' world boxes; appended after the BLAS nodes.
+int rebuild_tlas(cavept_ctx* ctx) {
+    const int n_built = (int)ctx->built_order.size();
+    // mesh root boxes: the first node of each mesh in the reference-layout array
+    std::vector<GpuPtBvh> roots(n_built);
+    for (int k = 0; k < n_built; ++k) {
+        const MeshRecord& rec = ctx->meshes[ctx->built_order[k]];
+        CU(ctx, cudaMemcpyAsync(&roots[k], ctx->d_nodes.ptr + rec.node_off, sizeof(GpuPtBvh), cudaMemcpyDeviceToHost, ctx->ex.stream));
+    }
+    CU(ctx, cudaStreamSynchronize(ctx->ex.stream));
+    std::vector<WorldBox> boxes(ctx->instances.size());
+    for (size_t i = 0; i < ctx->instances.size(); ++i) {
+        const MeshRecord& rec = ctx->meshes[ctx->instances[i].mesh];
+        boxes[i] = transform_box(ctx->instances[i].transform, roots[rec.built].min, roots[rec.built].max);
+    }
+    const int base = 2 * ctx->n_pairs + n_built;
+    std::vector<FastNode> tlas;
+    ctx->tlas_depth = build_tlas(boxes, base, tlas);
+    ctx->tlas_root = base;
+    ctx->n_fast_nodes = base + (int)tlas.size();
+    if ((size_t)ctx->n_fast_nodes > ctx->d_fnodes.cap) return fail(ctx, CAVEPT_ERR_CAPACITY, "fast node buffer too small");
+    ctx->ex.upload(ctx->d_fnodes.ptr + base, tlas.data(), tlas.size() * sizeof(FastNode));
+    CU(ctx, cudaStreamSynchronize(ctx->ex.stream));
+    if (ctx->build_levels + ctx->tlas_depth + 2 > kStackSize) {
+        return fail(ctx, CAVEPT_ERR_CAPACITY, "BVH depth %d + TLAS depth %d exceeds the traversal stack (%d)", ctx->build_levels, ctx->tlas_depth, kStackSize);
+    }
+    return check_exec(ctx, "tlas upload");
+}
+
+int build_all(cavept_ctx* ctx) {
+    const int n_built = (int)ctx->built_order.size();
+    const int T = ctx->n_tris;
+    const int n_nodes = ctx->n_nodes;
+    std::vector<int> tri_off(n_built + 1), vert_off(n_built + 1);
+    for (int k = 0; k < n_built; ++k) {
+        const MeshRecord& rec = ctx->meshes[ctx->built_order[k]];
+        tri_off[k] = rec.tri_off;
+        vert_off[k] = rec.vert_off;
+    }
+    tri_off[n_built] = T;
+    vert_off[n_built] = ctx->n_verts;
+    CU(ctx, ctx->d_tri_off.reserve(n_built + 1));
+    CU(ctx, ctx->d_vert_off.reserve(n_built + 1));
+    ctx->ex.upload(ctx->d_tri_off.ptr, tri_off.data(), tri_off.size() * sizeof(int));
+    ctx->ex.upload(ctx->d_vert_off.ptr, vert_off.data(), vert_off.size() * sizeof(int));
+
+    const size_t items_cap = (size_t)std::max(T, n_built) + 2;
+    const size_t bins_cap = (size_t)T / 5 + (size_t)n_built + 2;
+    CU(ctx, ctx->d_tri_bmin.reserve(T));
+    CU(ctx, ctx->d_tri_bmax.reserve(T));
+    CU(ctx, ctx->d_tri_centroid.reserve(T));
+    CU(ctx, ctx->d_order.reserve(T));
+    CU(ctx, ctx->d_order_next.reserve(T));
+    CU(ctx, ctx->d_node_of.reserve(T));
+    CU(ctx, ctx->d_node_of_next.reserve(T));
+    CU(ctx, ctx->d_flags.reserve(T));
+    CU(ctx, ctx->d_scan.reserve((size_t)std::max(T, n_nodes) + 1));
+    CU(ctx, ctx->d_scan_tmp.reserve((size_t)std::max(T, n_nodes) / kScanTile + 4));
+    CU(ctx, ctx->d_counters.reserve(4));
+    CU(ctx, ctx->d_items.reserve(items_cap));
+    CU(ctx, ctx->d_items_next.reserve(items_cap));
+    CU(ctx, ctx->d_accum_items.reserve(items_cap));
+    CU(ctx, ctx->d_bins.reserve(bins_cap));
+    CU(ctx, ctx->d_nodes.reserve(n_nodes));
+    CU(ctx, ctx->d_node_parent.reserve(n_nodes));
+    CU(ctx, ctx->d_node_count.reserve(n_nodes));
+    ctx->ex.scan_tmp = ctx->d_scan_tmp.ptr;
+
+    // raw -> reference layouts
+    launch_assemble_vertices(ctx->ex, ctx->d_raw_pos.ptr, ctx->d_raw_nrm.ptr, ctx->d_vertices.ptr, ctx->n_verts);
+    launch_assemble_indices(ctx->ex, ctx->d_raw_idx.ptr, ctx->d_tri_off.ptr, ctx->d_vert_off.ptr, n_built, ctx->d_indices.ptr, T);
+
+    BuildArrays a{};
+    a.vertices = ctx->d_vertices.ptr;
+    a.indices = ctx->d_indices.ptr;
+    a.n_tris = T;
+    a.tri_bmin = ctx->d_tri_bmin.ptr;
+    a.tri_bmax = ctx->d_tri_bmax.ptr;
+    a.tri_centroid = ctx->d_tri_centroid.ptr;
+    a.order = ctx->d_order.ptr;
+    a.order_next = ctx->d_order_next.ptr;
+    a.node_of = ctx->d_node_of.ptr;
+    a.node_of_next = ctx->d_node_of_next.ptr;
+    a.flags = ctx->d_flags.ptr;
+    a.scan = ctx->d_scan.ptr;
+    a.items = ctx->d_items.ptr;
+    a.items_next = ctx->d_items_next.ptr;
+    a.accum = ctx->d_accum_items.ptr;
+    a.bins = ctx->d_bins.ptr;
+    a.counters = ctx->d_counters.ptr;
+    a.bins_capacity = (int)bins_cap;
+    a.nodes = ctx->d_nodes.ptr;
+    a.node_parent = ctx->d_node_parent.ptr;
+    a.node_count = ctx->d_node_count.ptr;
+
+    const unsigned long long launches_before = ctx->ex.launches;
+    CU(ctx, cudaEventRecord(ctx->ev0, ctx->ex.stream));
+    std::vector<BuildItem> scratch(n_built);
+    BuildReport report{};
+    const int rc = run_build_bvh_parity(ctx->ex, a, tri_off.data(), ctx->d_tri_off.ptr, n_built, scratch.data(), &report);
+    CU(ctx, cudaEventRecord(ctx->ev1, ctx->ex.stream));
+    ctx->build_levels = report.levels;
+    if (int e = check_exec(ctx, "bvh build")) return e;
+    if (rc != 0) {
+        return fail(ctx, CAVEPT_ERR_DEGENERATE_GEOMETRY, "BVH build failed (bits %d:%s%s%s%s) -- the reference traps on this input (bvh_accel.cpp:117-120,138-141)",
+                    report.error_bits, (report.error_bits & BUILD_ERR_DEPTH) ? " depth>64" : "", (report.error_bits & BUILD_ERR_EMPTY_SIDE) ? " empty-split-side" : "",
+                    (report.error_bits & BUILD_ERR_BAD_AREA) ? " zero-area" : "", (report.error_bits & BUILD_ERR_BINS) ? " bins" : "");
+    }
+
+    // production layout
+    CU(ctx, ctx->d_is_pair.reserve(n_nodes));
+    CU(ctx, ctx->d_pair_rank.reserve((size_t)n_nodes + 1));
+    CU(ctx, ctx->d_leaf_tris.reserve(n_nodes));
+    CU(ctx, ctx->d_tri_base.reserve((size_t)n_nodes + 1));
+    CU(ctx, ctx->d_ftris.reserve(T));
+    // pairs <= T/2 .. generous bound: every kept node is a reference node; + roots + TLAS (2*instances)
+    CU(ctx, ctx->d_fnodes.reserve((size_t)n_nodes + n_built + 2 * ctx->instances.size() + 8));
+    CompactArrays c{};
+    c.nodes = ctx->d_nodes.ptr;
+    c.node_parent = ctx->d_node_parent.ptr;
+    c.node_count = ctx->d_node_count.ptr;
+    c.n_nodes = n_nodes;
+    c.vertices = ctx->d_vertices.ptr;
+    c.indices = ctx->d_indices.ptr;
+    c.is_pair = ctx->d_is_pair.ptr;
+    c.pair_rank = ctx->d_pair_rank.ptr;
+    c.leaf_tris = ctx->d_leaf_tris.ptr;
+    c.tri_base = ctx->d_tri_base.ptr;
+    c.fnodes = ctx->d_fnodes.ptr;
+    c.ftris = ctx->d_ftris.ptr;
+    ctx->n_pairs = run_compact_layout(ctx->ex, c);
+    CU(ctx, cudaEventRecord(ctx->ev2, ctx->ex.stream));
+    CU(ctx, cudaStreamSynchronize(ctx->ex.stream));
+    if (int e = check_exec(ctx, "compact layout")) return e;
+    float ms_build = 0.0f, ms_compact = 0.0f;
+    CU(ctx, cudaEventElapsedTime(&ms_build, ctx->ev0, ctx->ev1));
+    CU(ctx, cudaEventElapsedTime(&ms_compact, ctx->ev1, ctx->ev2));
+    ctx->stats.last_build_ms = ms_build;
+    ctx->stats.last_compact_ms = ms_compact;
+    ctx->stats.build_levels = report.levels;
+    ctx->stats.build_launches = (int)(ctx->ex.launches - launches_before);
+    return CAVEPT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+CAVEPT_API int cavept_create(const cavept_config* config, cavept_ctx** out_ctx) {
+    if (!config || !out_ctx) return CAVEPT_ERR_INVALID_ARG;
+    *out_ctx = nullptr;
+    if (config->width <= 0 || config->height <= 0 || config->max_bounce <= 0) return CAVEPT_ERR_INVALID_ARG;
+    int n_dev = 0;
+    if (cudaGetDeviceCount(&n_dev) != cudaSuccess || n_dev == 0) return CAVEPT_ERR_CUDA;
+    cavept_ctx* ctx = new cavept_ctx();
+    ctx->cfg = *config;
+    if (config->device >= 0) {
+        ctx->device = config->device;
+    } else if (cudaGetDevice(&ctx->device) != cudaSuccess) {
+        delete ctx;
+        return CAVEPT_ERR_CUDA;
+    }
+    bool ok = cudaSetDevice(ctx->device) == cudaSuccess;
+    ok = ok && cudaStreamCreateWithFlags(&ctx->ex.stream, cudaStreamNonBlocking) == cudaSuccess;
+    ok = ok && cudaEventCreate(&ctx->ev0) == cudaSuccess && cudaEventCreate(&ctx->ev1) == cudaSuccess && cudaEventCreate(&ctx->ev2) == cudaSuccess;
+    const size_t n_pixels = (size_t)config->width * config->height;
+    ok = ok && ctx->d_accum.reserve(n_pixels) == cudaSuccess && ctx->d_stats.reserve(4) == cudaSuccess;
+    ok = ok && cudaMemsetAsync(ctx->d_accum.ptr, 0, n_pixels * sizeof(F4), ctx->ex.stream) == cudaSuccess;
+    ok = ok && cudaMemsetAsync(ctx->d_stats.ptr, 0, 4 * sizeof(unsigned long long), ctx->ex.stream) == cudaSuccess;
+    ok = ok && cudaStreamSynchronize(ctx->ex.stream) == cudaSuccess;
+    if (!ok) {
+        cavept_destroy(ctx);
+        return CAVEPT_ERR_CUDA;
+    }
+    *out_ctx = ctx;
+    return CAVEPT_OK;
+}
+
+CAVEPT_API void cavept_destroy(cavept_ctx* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    if (ctx->ex.stream) cudaStreamSynchronize(ctx->ex.stream);
+    ctx->d_vertices.release(); ctx->d_indices.release(); ctx->d_nodes.release(); ctx->d_meshes.release(); ctx->d_materials.release();
+    ctx->d_fnodes.release(); ctx->d_ftris.release(); ctx->d_inst_root.release();
+    ctx->d_raw_pos.release(); ctx->d_raw_nrm.release(); ctx->d_raw_idx.release(); ctx->d_tri_off.release(); ctx->d_vert_off.release();
+    ctx->d_tri_bmin.release(); ctx->d_tri_bmax.release(); ctx->d_tri_centroid.release();
+    ctx->d_order.release(); ctx->d_order_next.release(); ctx->d_node_of.release(); ctx->d_node_of_next.release();
+    ctx->d_scan.release(); ctx->d_scan_tmp.release(); ctx->d_counters.release(); ctx->d_flags.release();
+    ctx->d_items.release(); ctx->d_items_next.release(); ctx->d_accum_items.release(); ctx->d_bins.release();
+    ctx->d_node_parent.release(); ctx->d_node_count.release(); ctx->d_is_pair.release(); ctx->d_pair_rank.release();
+    ctx->d_leaf_tris.release(); ctx->d_tri_base.release();
+    ctx->d_accum.release(); ctx->d_tone.release(); ctx->d_tone8.release(); ctx->d_stats.release();
+    if (ctx->ev0) cudaEventDestroy(ctx->ev0);
+    if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+    if (ctx->ev2) cudaEventDestroy(ctx->ev2);
+    if (ctx->ex.stream) cudaStreamDestroy(ctx->ex.stream);
+    delete ctx;
+}
+
+CAVEPT_API const char* cavept_last_error(const cavept_ctx* ctx) { return ctx ? ctx->last_error.c_str() : "null context"; }
+
+CAVEPT_API int cavept_set_mode(cavept_ctx* ctx, int mode) {
+    if (!ctx) return CAVEPT_ERR_INVALID_ARG;
+    if (mode != CAVEPT_MODE_NONE && mode != CAVEPT_MODE_INTERACTIVE && mode != CAVEPT_MODE_TILED) {
+        return fail(ctx, CAVEPT_ERR_INVALID_ARG, "invalid mode %d", mode);  // reference: CRASH_NOW_MSG("Invalid mode"), path_tracer.cpp:59-61
+    }
+    ctx->mode = mode;
+    return CAVEPT_OK;
+}
+
+CAVEPT_API int cavept_is_active(const cavept_ctx* ctx) {
+    // PathTracer::IsActive, path_tracer.cpp:312-322
+    return (ctx && ctx->mode == CAVEPT_MODE_INTERACTIVE && ctx->scene_resident) ? 1 : 0;
+}
+
+CAVEPT_API int cavept_upload_scene(cavept_ctx* ctx, const cavept_mesh* meshes, int mesh_count, const cavept_instance* instances, int instance_count,
+                                   const cavept_material* materials, int material_count) {
+    if (!ctx) return CAVEPT_ERR_INVALID_ARG;
+    if (!meshes || !instances || !materials || mesh_count <= 0 || instance_count <= 0 || material_count <= 0) {
+        return fail(ctx, CAVEPT_ERR_INVALID_ARG, "upload_scene: null or empty input");
+    }
+    if (int e = select_device(ctx)) return e;
+    ctx->scene_resident = false;
+    ctx->meshes.assign(mesh_count, MeshRecord());
+    ctx->built_order.clear();
+    long long n_verts = 0, n_tris = 0;
+    for (int i = 0; i < instance_count; ++i) {  // CreateAccelStructure: each unique mesh once, first appearance order
+        const cavept_instance& in = instances[i];
+        if (in.mesh < 0 || in.mesh >= mesh_count || in.material < 0 || in.material >= material_count) {
+            return fail(ctx, CAVEPT_ERR_INVALID_ARG, "instance %d references mesh %d / material %d out of range", i, in.mesh, in.material);
+        }
+        MeshRecord& rec = ctx->meshes[in.mesh];
+        if (rec.built >= 0) continue;
+        const cavept_mesh& m = meshes[in.mesh];
+        if (!m.positions || !m.normals || !m.indices || m.vertex_count <= 0 || m.index_count <= 0 || m.index_count % 3 != 0) {
+            return fail(ctx, CAVEPT_ERR_INVALID_ARG, "mesh %d: bad arrays (index_count %% 3 != 0 is a DEV_ASSERT in the reference, bvh_accel.cpp:269)", in.mesh);
+        }
+        for (int k = 0; k < m.index_count; ++k) {
+            if (m.indices[k] >= (uint32_t)m.vertex_count) return fail(ctx, CAVEPT_ERR_INVALID_ARG, "mesh %d: index %d out of range", in.mesh, k);
+        }
+        rec.built = (int)ctx->built_order.size();
+        rec.vertex_count = m.vertex_count;
+        rec.tri_count = m.index_count / 3;
+        rec.vert_off = (int)n_verts;
+        rec.tri_off = (int)n_tris;
+        rec.node_off = (int)(2 * n_tris - rec.built);  // sum of (2 n_i - 1) over the meshes before
+        rec.first_material = in.material;
+        ctx->built_order.push_back(in.mesh);
+        n_verts += m.vertex_count;
+        n_tris += rec.tri_count;
+        if (n_tris > (1ll << 28) || n_verts > (1ll << 29)) return fail(ctx, CAVEPT_ERR_CAPACITY, "scene too large");
+    }
+    const int n_built = (int)ctx->built_order.size();
+    ctx->n_verts = (int)n_verts;
+    ctx->n_tris = (int)n_tris;
+    ctx->n_nodes = (int)(2 * n_tris - n_built);
+    ctx->instances.assign(instances, instances + instance_count);
+    ctx->materials.assign(materials, materials + material_count);
+
+    CU(ctx, ctx->d_raw_pos.reserve((size_t)n_verts * 3));
+    CU(ctx, ctx->d_raw_nrm.reserve((size_t)n_verts * 3));
+    CU(ctx, ctx->d_raw_idx.reserve((size_t)n_tris * 3));
+    CU(ctx, ctx->d_vertices.reserve(n_verts));
+    CU(ctx, ctx->d_indices.reserve(n_tris));
+    for (int k = 0; k < n_built; ++k) {
+        const MeshRecord& rec = ctx->meshes[ctx->built_order[k]];
+        const cavept_mesh& m = meshes[ctx->built_order[k]];
+        ctx->ex.upload(ctx->d_raw_pos.ptr + (size_t)rec.vert_off * 3, m.positions, (size_t)m.vertex_count * 3 * sizeof(float));
+        ctx->ex.upload(ctx->d_raw_nrm.ptr + (size_t)rec.vert_off * 3, m.normals, (size_t)m.vertex_count * 3 * sizeof(float));
+        ctx->ex.upload(ctx->d_raw_idx.ptr + (size_t)rec.tri_off * 3, m.indices, (size_t)m.index_count * sizeof(uint32_t));
+    }
+    CU(ctx, cudaStreamSynchronize(ctx->ex.stream));  // caller's buffers are free to go after this point
+    if (int e = check_exec(ctx, "scene upload")) return e;
+    if (int e = build_all(ctx)) return e;
+    if (int e = rebuild_instance_arrays(ctx)) return e;
+    if (int e = rebuild_tlas(ctx)) return e;
+    ctx->scene_resident = true;
+    ctx->dirty = true;
+    ctx->stats.triangle_count = ctx->n_tris;
+    ctx->stats.node_count = ctx->n_nodes;
+    ctx->stats.fast_node_count = ctx->n_fast_nodes;
+    ctx->stats.instance_count = instance_count;
+    return CAVEPT_OK;
+}
+
+CAVEPT_API int cavept_update_instances(cavept_ctx* ctx, const cavept_instance* instances, int instance_count) {
+    if (!ctx || !instances) return CAVEPT_ERR_INVALID_ARG;
+    if (!ctx->scene_resident) return fail(ctx, CAVEPT_ERR_NOT_READY, "no scene resident");
+    if (instance_count != (int)ctx->instances.size()) return fail(ctx, CAVEPT_ERR_INVALID_ARG, "instance count changed (%d != %zu): re-upload the scene", instance_count, ctx->instances.size());
+    for (int i = 0; i < instance_count; ++i) {
+        if (instances[i].mesh != ctx->instances[i].mesh) return fail(ctx, CAVEPT_ERR_INVALID_ARG, "instance %d changed mesh: re-upload the scene", i);
+    }
+    if (int e = select_device(ctx)) return e;
+    for (int i = 0; i < instance_count; ++i) std::memcpy(ctx->instances[i].transform, instances[i].transform, sizeof(float) * 16);
+    if (int e = rebuild_instance_arrays(ctx)) return e;
+    if (int e = rebuild_tlas(ctx)) return e;
+    ctx->dirty = true;  // SCENE_DIRTY_WORLD
+    return CAVEPT_OK;
+}
+
+CAVEPT_API int cavept_update_materials(cavept_ctx* ctx, const cavept_material* materials, int material_count) {
+    if (!ctx || !materials) return CAVEPT_ERR_INVALID_ARG;
+    if (!ctx->scene_resident) return fail(ctx, CAVEPT_ERR_NOT_READY, "no scene resident");
+    if (material_count != (int)ctx->materials.size()) return fail(ctx, CAVEPT_ERR_INVALID_ARG, "material count changed");
+    if (int e = select_device(ctx)) return e;
+    ctx->materials.assign(materials, materials + material_count);
+    if (int e = rebuild_instance_arrays(ctx)) return e;
+    ctx->dirty = true;
+    return CAVEPT_OK;
+}
+
+CAVEPT_API int cavept_rebuild_mesh(cavept_ctx* ctx, int mesh, const float* positions, const float* normals) {
+    if (!ctx || !positions) return CAVEPT_ERR_INVALID_ARG;
+    if (!ctx->scene_resident) return fail(ctx, CAVEPT_ERR_NOT_READY, "no scene resident");
+    if (mesh < 0 || mesh >= (int)ctx->meshes.size() || ctx->meshes[mesh].built < 0) return fail(ctx, CAVEPT_ERR_INVALID_ARG, "mesh %d is not resident", mesh);
+    if (int e = select_device(ctx)) return e;
+    const MeshRecord& rec = ctx->meshes[mesh];
+    ctx->ex.upload(ctx->d_raw_pos.ptr + (size_t)rec.vert_off * 3, positions, (size_t)rec.vertex_count * 3 * sizeof(float));
+    if (normals) ctx->ex.upload(ctx->d_raw_nrm.ptr + (size_t)rec.vert_off * 3, normals, (size_t)rec.vertex_count * 3 * sizeof(float));
+    CU(ctx, cudaStreamSynchronize(ctx->ex.stream));
+    ctx->scene_resident = false;
+    if (int e = build_all(ctx)) return e;  // all meshes share one level-synchronous pass
+    if (int e = rebuild_instance_arrays(ctx)) return e;
+    if (int e = rebuild_tlas(ctx)) return e;
+    ctx->scene_resident = true;
+    ctx->dirty = true;
+    return CAVEPT_OK;
+}
+
+CAVEPT_API int cavept_get_mesh_bvh(cavept_ctx* ctx, int mesh, void* out, int capacity_nodes) {
+    if (!ctx || !out) return -CAVEPT_ERR_INVALID_ARG;
+    if (!ctx->scene_resident || mesh < 0 || mesh >= (int)ctx->meshes.size() || ctx->meshes[mesh].built < 0) return -fail(ctx, CAVEPT_ERR_NOT_READY, "mesh %d is not resident", mesh);
+    if (select_device(ctx)) return -CAVEPT_ERR_CUDA;
+    const MeshRecord& rec = ctx->meshes[mesh];
+    const int n = 2 * rec.tri_count - 1;
+    if (capacity_nodes < n) return -fail(ctx, CAVEPT_ERR_CAPACITY, "need %d nodes", n);
+    GpuPtBvh* o = static_cast<GpuPtBvh*>(out);
+    if (cudaMemcpyAsync(o, ctx->d_nodes.ptr + rec.node_off, (size_t)n * sizeof(GpuPtBvh), cudaMemcpyDeviceToHost, ctx->ex.stream) != cudaSuccess ||
+        cudaStreamSynchronize(ctx->ex.stream) != cudaSuccess) {
+        return -fail(ctx, CAVEPT_ERR_CUDA, "bvh read-back failed");
+    }
+    for (int i = 0; i < n; ++i) {  // undo AppendBvhs (path_tracer.cpp:90-118): back to what FillGpuBvhAccel emits
+        if (o[i].hitIdx >= 0) o[i].hitIdx -= rec.node_off;
+        if (o[i].missIdx >= 0) o[i].missIdx -= rec.node_off;
+        if (o[i].triangleIndex >= 0) o[i].triangleIndex -= rec.tri_off;
+    }
+    return n;
+}
+
+CAVEPT_API int cavept_get_scene_counts(cavept_ctx* ctx, int* vertices, int* triangles, int* nodes, int* instances, int* materials) {
+    if (!ctx) return CAVEPT_ERR_INVALID_ARG;
+    if (!ctx->scene_resident) return fail(ctx, CAVEPT_ERR_NOT_READY, "no scene resident");
+    if (vertices) *vertices = ctx->n_verts;
+    if (triangles) *triangles = ctx->n_tris;
+    if (nodes) *nodes = ctx->n_nodes;
+    if (instances) *instances = (int)ctx->gpu_meshes.size();
+    if (materials) *materials = (int)ctx->gpu_materials.size();
+    return CAVEPT_OK;
+}
+
+CAVEPT_API int cavept_get_scene_arrays(cavept_ctx* ctx, void* v, void* i, void* b, void* m, void* mat) {
+    if (!ctx) return CAVEPT_ERR_INVALID_ARG;
+    if (!ctx->scene_resident) return fail(ctx, CAVEPT_ERR_NOT_READY, "no scene resident");
+    if (int e = select_device(ctx)) return e;
+    if (v) ctx->ex.download(v, ctx->d_vertices.ptr, (size_t)ctx->n_verts * sizeof(GpuPtVertex));
+    if (i) ctx->ex.download(i, ctx->d_indices.ptr, (size_t)ctx->n_tris * sizeof(GpuPtIndex));
+    if (b) ctx->ex.download(b, ctx->d_nodes.ptr, (size_t)ctx->n_nodes * sizeof(GpuPtBvh));
+    if (m) ctx->ex.download(m, ctx->d_meshes.ptr, ctx->gpu_meshes.size() * sizeof(GpuPtMesh));
+    if (mat) ctx->ex.download(mat, ctx->d_materials.ptr, ctx->gpu_materials.size() * sizeof(GpuPtMaterial));
+    return check_exec(ctx, "scene read-back");
+}
+
+CAVEPT_API int cavept_set_camera(cavept_ctx* ctx, const float position[3], const float right[3], const float up[3], const float forward[3], float fov_degree) {
+    if (!ctx || !position || !right || !up || !forward) return CAVEPT_ERR_INVALID_ARG;
+    std::memcpy(ctx->cam_pos, position, 12);
+    std::memcpy(ctx->cam_right, right, 12);
+    std::memcpy(ctx->cam_up, up, 12);
+    std::memcpy(ctx->cam_fwd, forward, 12);
+    ctx->cam_fov = fov_degree;
+    ctx->dirty = true;  // SCENE_DIRTY_CAMERA
+    return CAVEPT_OK;
+}
+
+CAVEPT_API int cavept_reset(cavept_ctx* ctx) {
+    if (!ctx) return CAVEPT_ERR_INVALID_ARG;
+    ctx->dirty = true;
+    return CAVEPT_OK;
+}
+
+CAVEPT_API int cavept_render(cavept_ctx* ctx, int first_frame_index, int n_frames) {
+    if (!ctx) return CAVEPT_ERR_INVALID_ARG;
+    if (n_frames <= 0) return fail(ctx, CAVEPT_ERR_INVALID_ARG, "n_frames must be positive");
+    if (!cavept_is_active(ctx)) return fail(ctx, CAVEPT_ERR_NOT_READY, "path tracer not active (mode INTERACTIVE and a resident scene are required)");
+    if (int e = select_device(ctx)) return e;
+    TraceParams p{};
+    p.vertices = ctx->d_vertices.ptr;
+    p.indices = ctx->d_indices.ptr;
+    p.bvhs = ctx->d_nodes.ptr;
+    p.meshes = ctx->d_meshes.ptr;
+    p.materials = ctx->d_materials.ptr;
+    p.mesh_count = (int)ctx->gpu_meshes.size();
+    p.fnodes = ctx->d_fnodes.ptr;
+    p.ftris = ctx->d_ftris.ptr;
+    p.inst_fast_root = ctx->d_inst_root.ptr;
+    p.tlas_root = ctx->tlas_root;
+    std::memcpy(p.cam_pos, ctx->cam_pos, 12);
+    std::memcpy(p.cam_right, ctx->cam_right, 12);
+    std::memcpy(p.cam_up, ctx->cam_up, 12);
+    std::memcpy(p.cam_fwd, ctx->cam_fwd, 12);
+    p.cam_distance = std::tan(ctx->cam_fov * 3.141592653589793f / 180.0f);  // path_tracer.cs.glsl:31-32 (the full angle, as the shader has it)
+    p.width = ctx->cfg.width;
+    p.height = ctx->cfg.height;
+    p.max_bounce = ctx->cfg.max_bounce;
+    p.first_frame = first_frame_index;
+    p.n_frames = n_frames;
+    p.reset_first = ctx->dirty ? 1 : 0;
+    p.accum = ctx->d_accum.ptr;
+    p.counters = ctx->d_stats.ptr;
+    CU(ctx, cudaEventRecord(ctx->ev0, ctx->ex.stream));
+    launch_trace(ctx->ex, p, ctx->cfg.trace_mode == CAVEPT_TRACE_FAST, ctx->count_visits);
+    CU(ctx, cudaEventRecord(ctx->ev1, ctx->ex.stream));
+    ctx->dirty = false;
+    return check_exec(ctx, "render launch");
+}
+
+CAVEPT_API int cavept_sync(cavept_ctx* ctx) {
+    if (!ctx) return CAVEPT_ERR_INVALID_ARG;
+    if (int e = select_device(ctx)) return e;
+    CU(ctx, cudaStreamSynchronize(ctx->ex.stream));
+    return CAVEPT_OK;
+}
+
+CAVEPT_API int cavept_read_accum(cavept_ctx* ctx, float* out, size_t bytes) {
+    if (!ctx || !out) return CAVEPT_ERR_INVALID_ARG;
+    const size_t need = (size_t)ctx->cfg.width * ctx->cfg.height * sizeof(F4);
+    if (bytes < need) return fail(ctx, CAVEPT_ERR_CAPACITY, "need %zu bytes", need);
+    if (int e = select_device(ctx)) return e;
+    ctx->ex.download(out, ctx->d_accum.ptr, need);
+    return check_exec(ctx, "accumulator read-back");
+}
+
+CAVEPT_API int cavept_write_accum(cavept_ctx* ctx, const float* in, size_t bytes) {
+    if (!ctx || !in) return CAVEPT_ERR_INVALID_ARG;
+    const size_t need = (size_t)ctx->cfg.width * ctx->cfg.height * sizeof(F4);
+    if (bytes < need) return fail(ctx, CAVEPT_ERR_CAPACITY, "need %zu bytes", need);
+    if (int e = select_device(ctx)) return e;
+    ctx->ex.upload(ctx->d_accum.ptr, in, need);
+    CU(ctx, cudaStreamSynchronize(ctx->ex.stream));
+    ctx->dirty = false;
+    return check_exec(ctx, "accumulator upload");
+}
+
+CAVEPT_API int cavept_read_tonemapped_rgba8(cavept_ctx* ctx, uint8_t* out, size_t bytes) {
+    if (!ctx || !out) return CAVEPT_ERR_INVALID_ARG;
+    const size_t n = (size_t)ctx->cfg.width * ctx->cfg.height;
+    if (bytes < n * 4) return fail(ctx, CAVEPT_ERR_CAPACITY, "need %zu bytes", n * 4);
+    if (int e = select_device(ctx)) return e;
+    CU(ctx, ctx->d_tone8.reserve(n * 4));
+    launch_tonemap_rgba8(ctx->ex, ctx->d_accum.ptr, ctx->d_tone8.ptr, (int)n);
+    ctx->ex.download(out, ctx->d_tone8.ptr, n * 4);
+    return check_exec(ctx, "tone pass");
+}
+
+CAVEPT_API int cavept_read_tonemapped_rgba32f(cavept_ctx* ctx, float* out, size_t bytes) {
+    if (!ctx || !out) return CAVEPT_ERR_INVALID_ARG;
+    const size_t n = (size_t)ctx->cfg.width * ctx->cfg.height;
+    if (bytes < n * sizeof(F4)) return fail(ctx, CAVEPT_ERR_CAPACITY, "need %zu bytes", n * sizeof(F4));
+    if (int e = select_device(ctx)) return e;
+    CU(ctx, ctx->d_tone.reserve(n));
+    launch_tonemap_f32(ctx->ex, ctx->d_accum.ptr, ctx->d_tone.ptr, (int)n);
+    ctx->ex.download(out, ctx->d_tone.ptr, n * sizeof(F4));
+    return check_exec(ctx, "tone pass");
+}
+
+CAVEPT_API int cavept_get_stats(cavept_ctx* ctx, cavept_stats* out) {
+    if (!ctx || !out) return CAVEPT_ERR_INVALID_ARG;
+    if (int e = select_device(ctx)) return e;
+    unsigned long long c[4] = { 0, 0, 0, 0 };
+    ctx->ex.download(c, ctx->d_stats.ptr, sizeof(c));
+    if (int e = check_exec(ctx, "stats read-back")) return e;
+    ctx->stats.segments = c[0];
+    ctx->stats.node_visits = c[1];
+    ctx->stats.triangle_tests = c[2];
+    ctx->stats.kernel_launches = ctx->ex.launches;
+    float ms = 0.0f;
+    if (cudaEventQuery(ctx->ev1) == cudaSuccess && cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1) == cudaSuccess) ctx->stats.last_render_ms = ms;
+    *out = ctx->stats;
+    return CAVEPT_OK;
+}
+
+CAVEPT_API int cavept_reset_stats(cavept_ctx* ctx) {
+    if (!ctx) return CAVEPT_ERR_INVALID_ARG;
+    if (int e = select_device(ctx)) return e;
+    ctx->ex.fill(ctx->d_stats.ptr, 0, 4 * sizeof(unsigned long long));
+    return check_exec(ctx, "stats reset");
+}
+
+CAVEPT_API int cavept_set_count_visits(cavept_ctx* ctx, int enable) {
+    if (!ctx) return CAVEPT_ERR_INVALID_ARG;
+    ctx->count_visits = enable != 0;
+    return CAVEPT_OK;
+}
+
+CAVEPT_API void* cavept_stream(cavept_ctx* ctx) { return ctx ? (void*)ctx->ex.stream : nullptr; }
+CAVEPT_API void* cavept_accum_device_ptr(cavept_ctx* ctx) { return ctx ? (void*)ctx->d_accum.ptr : nullptr; }
+
+CAVEPT_API int cavept_accum_to_sums(cavept_ctx* ctx) {
+    if (!ctx) return CAVEPT_ERR_INVALID_ARG;
+    if (int e = select_device(ctx)) return e;
+    launch_accum_scale(ctx->ex, ctx->d_accum.ptr, ctx->cfg.width * ctx->cfg.height, true);
+    return check_exec(ctx, "accum_to_sums");
+}
+CAVEPT_API int cavept_accum_from_sums(cavept_ctx* ctx) {
+    if (!ctx) return CAVEPT_ERR_INVALID_ARG;
+    if (int e = select_device(ctx)) return e;
+    launch_accum_scale(ctx->ex, ctx->d_accum.ptr, ctx->cfg.width * ctx->cfg.height, false);
+    return check_exec(ctx, "accum_from_sums");
+}
+
+}  // extern "C"

@@ -1,0 +1,207 @@
+// Shared definitions for the cavept kernels.
+//
+// Kernel bodies are written as `CV_HD` functions of a global thread index so that
+// the exact same source can be (a) wrapped by __global__ kernels in kernels.cu and
+// (b) stepped serially by the g++-built emulator under tests/emu/, which lets the
+// algorithms be checked against the oracle in a container without a GPU.  The
+// emulator is test code; the product has no CPU path.
+//
+// Float semantics: device code is compiled with -fmad=false and host emulation with
+// -ffp-contract=off, so every `a * b + c` below is two rounded operations, exactly
+// as the reference's C++ builder (x86-64, no FMA) and its fp32 shader evaluate it.
+// Where the fast kernel wants a fused multiply-add it calls cv_fma() explicitly.
+#pragma once
+
+#include <stdint.h>
+
+#if defined(__CUDACC__)
+#define CV_HD __host__ __device__ __forceinline__
+#define CV_D __device__ __forceinline__
+#else
+#define CV_HD inline
+#define CV_D inline
+#include <cmath>
+#include <cstring>
+#endif
+
+namespace cavept {
+
+// ---- reference GPU layouts: cave/shader/structured_buffer.hlsl.h:24-61 -------------
+struct GpuPtBvh {  // 48 B
+    float min[3];
+    int missIdx;
+    float max[3];
+    int hitIdx;
+    float pad[2];
+    int leaf;
+    int triangleIndex;
+};
+struct GpuPtVertex {  // 32 B
+    float position[3];
+    int pad1;
+    float normal[3];
+    int pad2;
+};
+struct GpuPtIndex {  // 16 B
+    int tri[3];
+    int pad1;
+};
+struct GpuPtMesh {  // 144 B
+    float transform[16];
+    float transformInv[16];
+    float pad[2];
+    int rootBvhId;
+    int materialId;
+};
+struct GpuPtMaterial {  // 32 B
+    float baseColor[3];
+    float roughness;
+    float emissive[3];
+    float metallic;
+};
+static_assert(sizeof(GpuPtBvh) == 48 && sizeof(GpuPtVertex) == 32 && sizeof(GpuPtIndex) == 16, "layout");
+static_assert(sizeof(GpuPtMesh) == 144 && sizeof(GpuPtMaterial) == 32, "layout");
+
+struct F3 {
+    float x, y, z;
+};
+struct alignas(16) F4 {
+    float x, y, z, w;
+};
+
+CV_HD F3 f3(float x, float y, float z) {
+    F3 r;
+    r.x = x;
+    r.y = y;
+    r.z = z;
+    return r;
+}
+CV_HD F3 operator+(F3 a, F3 b) { return f3(a.x + b.x, a.y + b.y, a.z + b.z); }
+CV_HD F3 operator-(F3 a, F3 b) { return f3(a.x - b.x, a.y - b.y, a.z - b.z); }
+CV_HD F3 operator*(F3 a, F3 b) { return f3(a.x * b.x, a.y * b.y, a.z * b.z); }
+CV_HD F3 operator*(float s, F3 a) { return f3(s * a.x, s * a.y, s * a.z); }
+CV_HD F3 operator*(F3 a, float s) { return f3(a.x * s, a.y * s, a.z * s); }
+CV_HD float comp(F3 a, int i) { return i == 0 ? a.x : (i == 1 ? a.y : a.z); }
+
+// cave/engine/math/detail/common.h:50-58 -- (a < b ? a : b), (a > b ? a : b)
+CV_HD float min_ref(float a, float b) { return a < b ? a : b; }
+CV_HD float max_ref(float a, float b) { return a > b ? a : b; }
+
+// cave/engine/math/detail/vector_math.h:513-545
+CV_HD float dot3(F3 a, F3 b) {
+    float r = a.x * b.x + a.y * b.y;
+    r += a.z * b.z;
+    return r;
+}
+CV_HD F3 cross3(F3 a, F3 b) { return f3(a.y * b.z - b.y * a.z, a.z * b.x - b.z * a.x, a.x * b.y - b.x * a.y); }
+
+CV_HD float cv_sqrt(float x) {
+#if defined(__CUDA_ARCH__)
+    return __fsqrt_rn(x);
+#else
+    return sqrtf(x);
+#endif
+}
+CV_HD float cv_div(float a, float b) {
+#if defined(__CUDA_ARCH__)
+    return __fdiv_rn(a, b);
+#else
+    return a / b;
+#endif
+}
+CV_HD float cv_fma(float a, float b, float c) {
+#if defined(__CUDA_ARCH__)
+    return __fmaf_rn(a, b, c);
+#else
+    return fmaf(a, b, c);
+#endif
+}
+CV_HD F3 normalize3(F3 a) {  // vector_math.h:527-536
+    const float inv = cv_div(1.0f, cv_sqrt(dot3(a, a)));
+    return a * inv;
+}
+CV_HD F3 lerp3(F3 x, F3 y, float s) { return (1.0f - s) * x + s * y; }  // vector_math.h:507-510
+
+CV_HD uint32_t f2u(float f) {
+#if defined(__CUDA_ARCH__)
+    return __float_as_uint(f);
+#else
+    uint32_t u;
+    memcpy(&u, &f, 4);
+    return u;
+#endif
+}
+CV_HD float u2f(uint32_t u) {
+#if defined(__CUDA_ARCH__)
+    return __uint_as_float(u);
+#else
+    float f;
+    memcpy(&f, &u, 4);
+    return f;
+#endif
+}
+
+#define CV_INF (u2f(0x7f800000u))
+
+// Order-preserving float -> uint32 map with -0 and +0 sharing one key.
+CV_HD uint32_t ordered_key(float v) {
+    uint32_t b = f2u(v);
+    if ((b << 1) == 0u) b = 0u;
+    return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+CV_HD float ordered_value(uint32_t k) { return u2f((k & 0x80000000u) ? (k & 0x7fffffffu) : ~k); }
+
+// ---- atomics: real ones on the device, plain serial updates in the emulator --------
+CV_D void cv_atomic_min_u64(unsigned long long* p, unsigned long long v) {
+#if defined(__CUDA_ARCH__)
+    atomicMin(p, v);
+#else
+    if (v < *p) *p = v;
+#endif
+}
+CV_D void cv_atomic_max_u64(unsigned long long* p, unsigned long long v) {
+#if defined(__CUDA_ARCH__)
+    atomicMax(p, v);
+#else
+    if (v > *p) *p = v;
+#endif
+}
+CV_D void cv_atomic_min_u32(uint32_t* p, uint32_t v) {
+#if defined(__CUDA_ARCH__)
+    atomicMin(p, v);
+#else
+    if (v < *p) *p = v;
+#endif
+}
+CV_D void cv_atomic_max_u32(uint32_t* p, uint32_t v) {
+#if defined(__CUDA_ARCH__)
+    atomicMax(p, v);
+#else
+    if (v > *p) *p = v;
+#endif
+}
+CV_D int cv_atomic_add_i32(int* p, int v) {
+#if defined(__CUDA_ARCH__)
+    return atomicAdd(p, v);
+#else
+    int o = *p;
+    *p = o + v;
+    return o;
+#endif
+}
+CV_D void cv_atomic_or_i32(int* p, int v) {
+#if defined(__CUDA_ARCH__)
+    atomicOr(p, v);
+#else
+    *p |= v;
+#endif
+}
+CV_D void cv_atomic_add_u64(unsigned long long* p, unsigned long long v) {
+#if defined(__CUDA_ARCH__)
+    atomicAdd(p, v);
+#else
+    *p += v;
+#endif
+}
+
+}  // namespace cavept

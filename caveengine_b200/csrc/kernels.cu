@@ -1,0 +1,281 @@
+// __global__ wrappers for the kernel bodies, the scan primitive, and launchers.
+// Compiled for sm_100a only, with -fmad=false (see cv_common.h on float semantics).
+#include "kernels.h"
+
+namespace cavept {
+
+// ---- generic element-wise launch -------------------------------------------------------
+template<class F>
+__global__ void __launch_bounds__(256) k_for_each(F f, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) f(i);
+}
+
+template<class F>
+void CudaExec::launch(int n, F f) {
+    if (n <= 0) return;
+    k_for_each<F><<<(n + 255) / 256, 256, 0, stream>>>(f, n);
+    note(cudaGetLastError());
+    ++launches;
+}
+
+void CudaExec::upload(void* dst, const void* src, size_t bytes) {
+    if (bytes) note(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, stream));
+    // pageable sources are staged before the call returns; pinned sources must stay live
+    // until the stream reaches the copy -- callers that reuse pinned buffers synchronise.
+}
+void CudaExec::download(void* dst, const void* src, size_t bytes) {
+    if (bytes) note(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, stream));
+    note(cudaStreamSynchronize(stream));
+}
+void CudaExec::fill(void* dst, int byte, size_t bytes) {
+    if (bytes) note(cudaMemsetAsync(dst, byte, bytes, stream));
+}
+
+// ---- exclusive scan (reduce, scan of block sums, apply) ---------------------------------
+// Tiles of kScanTile = 256 threads x 8 consecutive elements.  out has n + 1 entries.
+constexpr int kScanThreads = 256;
+constexpr int kScanPerThread = kScanTile / kScanThreads;
+
+__device__ __forceinline__ int block_exclusive_scan(int v, int* total) {
+    // exclusive scan of one int per thread over a 256-thread block
+    __shared__ int warp_sums[kScanThreads / 32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int incl = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const int t = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += t;
+    }
+    if (lane == 31) warp_sums[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+        int s = lane < kScanThreads / 32 ? warp_sums[lane] : 0;
+#pragma unroll
+        for (int d = 1; d < kScanThreads / 32; d <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, s, d);
+            if (lane >= d) s += t;
+        }
+        if (lane < kScanThreads / 32) warp_sums[lane] = s;  // inclusive over warps
+    }
+    __syncthreads();
+    const int warp_offset = warp == 0 ? 0 : warp_sums[warp - 1];
+    *total = warp_sums[kScanThreads / 32 - 1];
+    const int result = warp_offset + incl - v;
+    __syncthreads();  // warp_sums is reused by the next call
+    return result;
+}
+
+template<class T>
+__global__ void __launch_bounds__(kScanThreads) k_scan_tile_sums(const T* __restrict__ in, int* __restrict__ sums, int n) {
+    const int base = blockIdx.x * kScanTile + threadIdx.x * kScanPerThread;
+    int s = 0;
+#pragma unroll
+    for (int k = 0; k < kScanPerThread; ++k) {
+        const int i = base + k;
+        if (i < n) s += (int)in[i];
+    }
+    int total;
+    block_exclusive_scan(s, &total);
+    if (threadIdx.x == 0) sums[blockIdx.x] = total;
+}
+
+// single block: sums[0..nb) -> exclusive scan in place, sums[nb] = grand total
+__global__ void __launch_bounds__(kScanThreads) k_scan_sums(int* sums, int nb) {
+    __shared__ int carry_s;
+    if (threadIdx.x == 0) carry_s = 0;
+    __syncthreads();
+    for (int base = 0; base < nb; base += kScanThreads) {
+        const int i = base + threadIdx.x;
+        const int v = i < nb ? sums[i] : 0;
+        int total;
+        const int ex = block_exclusive_scan(v, &total);
+        const int carry = carry_s;
+        if (i < nb) sums[i] = carry + ex;
+        __syncthreads();
+        if (threadIdx.x == 0) carry_s = carry + total;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) sums[nb] = carry_s;
+}
+
+template<class T>
+__global__ void __launch_bounds__(kScanThreads) k_scan_apply(const T* __restrict__ in, const int* __restrict__ sums, int* __restrict__ out, int n, int nb) {
+    const int base = blockIdx.x * kScanTile + threadIdx.x * kScanPerThread;
+    int v[kScanPerThread];
+    int s = 0;
+#pragma unroll
+    for (int k = 0; k < kScanPerThread; ++k) {
+        const int i = base + k;
+        v[k] = i < n ? (int)in[i] : 0;
+        s += v[k];
+    }
+    int total;
+    int run = block_exclusive_scan(s, &total) + sums[blockIdx.x];
+#pragma unroll
+    for (int k = 0; k < kScanPerThread; ++k) {
+        const int i = base + k;
+        if (i < n) out[i] = run;
+        run += v[k];
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) out[n] = sums[nb];
+}
+
+template<class T>
+static void scan_impl(CudaExec& ex, const T* in, int* out, int n) {
+    if (n <= 0) return;
+    const int nb = (n + kScanTile - 1) / kScanTile;
+    k_scan_tile_sums<T><<<nb, kScanThreads, 0, ex.stream>>>(in, ex.scan_tmp, n);
+    k_scan_sums<<<1, kScanThreads, 0, ex.stream>>>(ex.scan_tmp, nb);
+    k_scan_apply<T><<<nb, kScanThreads, 0, ex.stream>>>(in, ex.scan_tmp, out, n, nb);
+    ex.note(cudaGetLastError());
+    ex.launches += 3;
+}
+void CudaExec::scan_u8(const unsigned char* in, int* out, int n) { scan_impl<unsigned char>(*this, in, out, n); }
+void CudaExec::scan_i32(const int* in, int* out, int n) { scan_impl<int>(*this, in, out, n); }
+
+// ---- scene assembly -------------------------------------------------------------------
+struct FnAssembleVertices {
+    const float* positions;
+    const float* normals;
+    GpuPtVertex* out;
+    __device__ void operator()(int i) const {
+        GpuPtVertex v;
+        v.position[0] = positions[3 * i];
+        v.position[1] = positions[3 * i + 1];
+        v.position[2] = positions[3 * i + 2];
+        v.pad1 = 0;
+        v.normal[0] = normals[3 * i];
+        v.normal[1] = normals[3 * i + 1];
+        v.normal[2] = normals[3 * i + 2];
+        v.pad2 = 0;
+        out[i] = v;
+    }
+};
+struct FnAssembleIndices {
+    const uint32_t* raw;
+    const int* tri_off;
+    const int* vert_off;
+    int n_meshes;
+    GpuPtIndex* out;
+    __device__ void operator()(int i) const {
+        int lo = 0, hi = n_meshes;
+        while (hi - lo > 1) {
+            const int mid = (lo + hi) >> 1;
+            if (tri_off[mid] <= i) lo = mid; else hi = mid;
+        }
+        const int off = vert_off[lo];  // AppendIndices: dest.tri = source.tri + p_vertex_count
+        GpuPtIndex o;
+        o.tri[0] = (int)raw[3 * i] + off;
+        o.tri[1] = (int)raw[3 * i + 1] + off;
+        o.tri[2] = (int)raw[3 * i + 2] + off;
+        o.pad1 = 0;
+        out[i] = o;
+    }
+};
+void launch_assemble_vertices(CudaExec& ex, const float* positions, const float* normals, GpuPtVertex* out, int n_vertices) {
+    ex.launch(n_vertices, FnAssembleVertices{ positions, normals, out });
+}
+void launch_assemble_indices(CudaExec& ex, const uint32_t* raw_indices, const int* tri_off, const int* vert_off, int n_meshes, GpuPtIndex* out, int n_tris) {
+    ex.launch(n_tris, FnAssembleIndices{ raw_indices, tri_off, vert_off, n_meshes, out });
+}
+
+int run_build_bvh_parity(CudaExec& ex, BuildArrays a, const int* tri_off_host, const int* d_tri_off, int n_meshes, BuildItem* host_scratch, BuildReport* report) {
+    return build_bvh_parity(ex, a, tri_off_host, d_tri_off, n_meshes, host_scratch, report);
+}
+int run_compact_layout(CudaExec& ex, CompactArrays c) { return run_compact(ex, c); }
+
+// ---- path-trace pass ------------------------------------------------------------------
+// Block = 128 threads = a 16 x 8 pixel tile; each warp covers an 8 x 4 sub-tile so the
+// primary rays of a warp are coherent.  Replaces Dispatch(ceil(W/16), ceil(H/16), 1) of a
+// 16x16 work group (cave/engine/render_graph/common_passes.cpp:990-997).
+template<bool kFast, bool kCount>
+__global__ void __launch_bounds__(128) k_trace(const TraceParams p) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int x = blockIdx.x * 16 + (warp & 1) * 8 + (lane & 7);
+    const int y = blockIdx.y * 8 + (warp >> 1) * 4 + (lane >> 3);
+    unsigned long long cnt[3] = { 0ull, 0ull, 0ull };
+    unsigned int segs = body_trace_pixel<kFast, kCount>(p, x, y, cnt);
+    segs = __reduce_add_sync(0xffffffffu, segs);
+    if (lane == 0 && segs) atomicAdd(&p.counters[0], (unsigned long long)segs);
+    if (kCount) {
+#pragma unroll
+        for (int k = 1; k < 3; ++k) {
+            unsigned long long v = cnt[k];
+#pragma unroll
+            for (int d = 16; d > 0; d >>= 1) v += __shfl_down_sync(0xffffffffu, v, d);
+            if (lane == 0 && v) atomicAdd(&p.counters[k], v);
+        }
+    }
+}
+
+void launch_trace(CudaExec& ex, const TraceParams& p, bool fast, bool count_visits) {
+    const dim3 grid((p.width + 15) / 16, (p.height + 7) / 8, 1), block(128, 1, 1);
+    if (fast) {
+        if (count_visits) k_trace<true, true><<<grid, block, 0, ex.stream>>>(p);
+        else k_trace<true, false><<<grid, block, 0, ex.stream>>>(p);
+    } else {
+        if (count_visits) k_trace<false, true><<<grid, block, 0, ex.stream>>>(p);
+        else k_trace<false, false><<<grid, block, 0, ex.stream>>>(p);
+    }
+    ex.note(cudaGetLastError());
+    ++ex.launches;
+}
+
+// ---- tone pass: c/(c+1), pow(c, 1/2.2) (cave/shader/glsl/post_process.ps.glsl:72-76) ----
+__device__ __forceinline__ float tone(float c) {
+    c = __fdiv_rn(c, c + 1.0f);
+    return powf(c, 1.0f / 2.2f);
+}
+struct FnToneRgba8 {
+    const F4* accum;
+    uchar4* out;
+    __device__ void operator()(int i) const {
+        const F4 a = accum[i];
+        uchar4 o;
+        o.x = (unsigned char)(fminf(fmaxf(tone(a.x), 0.0f), 1.0f) * 255.0f + 0.5f);
+        o.y = (unsigned char)(fminf(fmaxf(tone(a.y), 0.0f), 1.0f) * 255.0f + 0.5f);
+        o.z = (unsigned char)(fminf(fmaxf(tone(a.z), 0.0f), 1.0f) * 255.0f + 0.5f);
+        o.w = 255;
+        out[i] = o;
+    }
+};
+struct FnToneF32 {
+    const F4* accum;
+    F4* out;
+    __device__ void operator()(int i) const {
+        const F4 a = accum[i];
+        F4 o;
+        o.x = tone(a.x);
+        o.y = tone(a.y);
+        o.z = tone(a.z);
+        o.w = 1.0f;
+        out[i] = o;
+    }
+};
+void launch_tonemap_rgba8(CudaExec& ex, const F4* accum, unsigned char* out, int n_pixels) {
+    ex.launch(n_pixels, FnToneRgba8{ accum, reinterpret_cast<uchar4*>(out) });
+}
+void launch_tonemap_f32(CudaExec& ex, const F4* accum, F4* out, int n_pixels) { ex.launch(n_pixels, FnToneF32{ accum, out }); }
+
+// (mean, n) <-> (sum, n) for the multi-GPU sum-reduce
+struct FnAccumScale {
+    F4* accum;
+    bool to_sums;
+    __device__ void operator()(int i) const {
+        F4 a = accum[i];
+        if (to_sums) {
+            a.x *= a.w;
+            a.y *= a.w;
+            a.z *= a.w;
+        } else if (a.w > 0.0f) {
+            a.x = __fdiv_rn(a.x, a.w);
+            a.y = __fdiv_rn(a.y, a.w);
+            a.z = __fdiv_rn(a.z, a.w);
+        }
+        accum[i] = a;
+    }
+};
+void launch_accum_scale(CudaExec& ex, F4* accum, int n_pixels, bool to_sums) { ex.launch(n_pixels, FnAccumScale{ accum, to_sums }); }
+
+}  // namespace cavept

@@ -1,0 +1,187 @@
+/* cavept -- C ABI of the B200-native drop-in for CaveEngine's progressive path
+ * tracer pass.  Plain pointers and sizes only; no C++/torch/CUDA types.  Every
+ * entry point cites the reference interface it replaces (paths relative to the
+ * CaveEngine repository root).
+ *
+ * The library is CUDA-only: there is no CPU code path.  Every call that needs the
+ * device returns CAVEPT_ERR_CUDA when no usable sm_100 device is present.
+ *
+ * Threading: a context is externally synchronised (the reference runs the whole
+ * path on the main thread, cave/engine/runtime/application.cpp:269-272).  Distinct
+ * contexts (one per GPU / per process) are independent.
+ *
+ * Ownership: the caller owns every host pointer; the library copies during the call
+ * and never retains host pointers.  The context owns all device memory.
+ */
+#ifndef CAVEPT_H_
+#define CAVEPT_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define CAVEPT_API __attribute__((visibility("default")))
+#else
+#define CAVEPT_API
+#endif
+
+typedef struct cavept_ctx cavept_ctx;
+
+/* Return codes.  The reference traps (DEV_ASSERT / CRASH_NOW_MSG,
+ * cave/engine/core/error/error_macros.h:88-125) where this ABI returns an error. */
+enum {
+    CAVEPT_OK = 0,
+    CAVEPT_ERR_INVALID_ARG = 1,
+    CAVEPT_ERR_DEGENERATE_GEOMETRY = 2, /* bvh_accel.cpp:117-120 (depth > 64), :138-141 (empty split side) */
+    CAVEPT_ERR_CUDA = 3,
+    CAVEPT_ERR_NOT_READY = 4, /* render/read before a scene is resident */
+    CAVEPT_ERR_CAPACITY = 5
+};
+
+/* enum class PathTracerMode, cave/engine/renderer/path_tracer_render_system.h:10-14 */
+enum { CAVEPT_MODE_NONE = 0, CAVEPT_MODE_INTERACTIVE = 1, CAVEPT_MODE_TILED = 2 };
+
+/* Which traversal the render launch uses.
+ * REFERENCE_WALK reproduces HitScene (cave/shader/shared_path_tracer.h:152-189)
+ * literally on the device: every mesh, stackless hit/miss-link walk over the 48-byte
+ * GpuPtBvh array.  FAST is the production kernel: TLAS over instances, ordered
+ * traversal with a short stack over 32-byte nodes, pre-gathered triangles.  Both
+ * return the same closest hit (up to exact-tie order, SURVEY.md section 8a note ii). */
+enum { CAVEPT_TRACE_FAST = 0, CAVEPT_TRACE_REFERENCE_WALK = 1 };
+
+/* BVH builder.  PARITY reproduces BvhBuilder::ConstructHelper
+ * (cave/engine/renderer/path_tracer/bvh_accel.cpp:115-219) bit-exactly.
+ * LBVH is the Morton/radix-sort builder for per-frame rebuilds (beyond the reference,
+ * which never rebuilds: path_tracer.cpp:69). */
+enum { CAVEPT_BVH_PARITY = 0, CAVEPT_BVH_LBVH = 1 };
+
+typedef struct cavept_config {
+    int device;     /* CUDA ordinal; -1 = current device */
+    int width;      /* accumulator size; reference default 1920x1080 (renderer/graphics_dvars.h:3) */
+    int height;
+    int max_bounce; /* MAX_BOUNCE, a #define 5 in the reference (shared_path_tracer.h:25); run-time here */
+    int trace_mode; /* CAVEPT_TRACE_* */
+    int bvh_mode;   /* CAVEPT_BVH_* */
+} cavept_config;
+
+/* MeshAsset fields the uploader reads (cave/engine/assets/mesh_asset.h:44-46). */
+typedef struct cavept_mesh {
+    const float* positions;  /* vertex_count * 3, tightly packed */
+    const float* normals;    /* vertex_count * 3 */
+    const uint32_t* indices; /* index_count, 3 per triangle */
+    int vertex_count;
+    int index_count;
+} cavept_mesh;
+
+/* One MeshRendererComponent + TransformComponent
+ * (cave/engine/scene/mesh_renderer_component.h:21-44, transform_component.h:26,41).
+ * As in the reference (path_tracer.cpp:227-231) the material of the FIRST instance
+ * that references a mesh is used by every instance of that mesh. */
+typedef struct cavept_instance {
+    int mesh;
+    int material;
+    float transform[16]; /* world matrix, column-major (glm::mat4) */
+} cavept_instance;
+
+/* MaterialComponent fields (cave/engine/scene/material_component.h:12-21); the device
+ * copy is GpuPtMaterial with emissive = base_color * emissive (path_tracer.cpp:140-145). */
+typedef struct cavept_material {
+    float base_color[3];
+    float roughness;
+    float metallic;
+    float emissive;
+} cavept_material;
+
+typedef struct cavept_stats {
+    uint64_t segments;        /* path segments (HitScene calls) traced since the last reset of stats */
+    uint64_t node_visits;     /* filled only when CAVEPT_STATS_COUNT_VISITS was requested */
+    uint64_t triangle_tests;
+    uint64_t kernel_launches; /* our __global__ launches since context creation */
+    float last_build_ms;      /* device time of the last BVH build (all meshes), CUDA events */
+    float last_compact_ms;    /* device time of deriving the production layout from it */
+    float last_render_ms;     /* device time of the last cavept_render, CUDA events */
+    int triangle_count;
+    int node_count;           /* GpuPtBvh nodes in the reference layout */
+    int fast_node_count;      /* 32-byte nodes of the production layout */
+    int instance_count;
+    int build_levels;
+    int build_launches;
+} cavept_stats;
+
+/* ---- lifetime; replaces the file-static PathTracer in
+ *      cave/engine/renderer/path_tracer_render_system.cpp:8-10 ------------------- */
+CAVEPT_API int cavept_create(const cavept_config* config, cavept_ctx** out_ctx);
+CAVEPT_API void cavept_destroy(cavept_ctx* ctx);
+CAVEPT_API const char* cavept_last_error(const cavept_ctx* ctx);
+
+/* ---- SetPathTracerMode / IsPathTracerActive,
+ *      path_tracer_render_system.h:17-18, path_tracer.cpp:312-322 ---------------- */
+CAVEPT_API int cavept_set_mode(cavept_ctx* ctx, int mode);
+CAVEPT_API int cavept_is_active(const cavept_ctx* ctx); /* 1 iff mode == INTERACTIVE and a BVH is resident */
+
+/* ---- RequestPathTracerUpdate -> PathTracer::Update -> CreateAccelStructure
+ *      (path_tracer.cpp:49-70, :203-310): builds every referenced mesh's BVH on the
+ *      device, concatenates the scene-global arrays (:72-118) and uploads instances
+ *      and materials (:120-201).  Resets the accumulator. --------------------------- */
+CAVEPT_API int cavept_upload_scene(cavept_ctx* ctx, const cavept_mesh* meshes, int mesh_count,
+                                   const cavept_instance* instances, int instance_count,
+                                   const cavept_material* materials, int material_count);
+/* The two dirty-driven re-uploads of UpdateAccelStructure (path_tracer.cpp:156-158, :197-199).
+ * Instance count/mesh ids must match the uploaded scene; both mark the scene dirty. */
+CAVEPT_API int cavept_update_instances(cavept_ctx* ctx, const cavept_instance* instances, int instance_count);
+CAVEPT_API int cavept_update_materials(cavept_ctx* ctx, const cavept_material* materials, int material_count);
+/* New vertex positions (and normals, may be NULL) for one mesh + BVH rebuild on the
+ * device (BASELINE config 5; beyond the reference, path_tracer.cpp:69 "@TODO"). */
+CAVEPT_API int cavept_rebuild_mesh(cavept_ctx* ctx, int mesh, const float* positions, const float* normals);
+
+/* ---- parity read-backs of what BindPathTracerData binds (path_tracer.cpp:324-331):
+ *      the reference-layout arrays, structured_buffer.hlsl.h:24-61 ------------------ */
+CAVEPT_API int cavept_get_mesh_bvh(cavept_ctx* ctx, int mesh, void* out_gpu_pt_bvh, int capacity_nodes); /* mesh-local indices, as FillGpuBvhAccel emits; returns count or <0 */
+CAVEPT_API int cavept_get_scene_counts(cavept_ctx* ctx, int* vertices, int* triangles, int* nodes, int* instances, int* materials);
+CAVEPT_API int cavept_get_scene_arrays(cavept_ctx* ctx, void* gpu_pt_vertices, void* gpu_pt_indices, void* gpu_pt_bvhs, void* gpu_pt_meshes, void* gpu_pt_materials); /* any may be NULL */
+
+/* ---- per-frame constants, PerFrameConstantBuffer c_camera* (cave/shader/cbuffer.hlsl.h:193-207),
+ *      filled at cave/engine/runtime/render_system.cpp:89-93.  Marks the scene dirty
+ *      (SCENE_DIRTY_CAMERA, cave/engine/scene/scene.cpp:60-63). -------------------- */
+CAVEPT_API int cavept_set_camera(cavept_ctx* ctx, const float position[3], const float right[3], const float up[3],
+                                 const float forward[3], float fov_degree);
+/* c_sceneDirty = 1 for the next rendered frame (render_system.cpp:125): the next frame
+ * overwrites the accumulator instead of averaging into it (path_tracer.cs.glsl:46-57). */
+CAVEPT_API int cavept_reset(cavept_ctx* ctx);
+
+/* ---- PathTracerPassFunc (cave/engine/render_graph/common_passes.cpp:977-999): one
+ *      Dispatch per frame in the reference; here n_frames consecutive c_frameIndex
+ *      values [first_frame_index, +n_frames) in one launch, accumulated with the
+ *      reference's running mean.  Asynchronous on the context's stream. ------------- */
+CAVEPT_API int cavept_render(cavept_ctx* ctx, int first_frame_index, int n_frames);
+CAVEPT_API int cavept_sync(cavept_ctx* ctx);
+
+/* ---- read-back.  The reference leaves RG_RES_PATHTRACER (RGBA32F, rgb = running
+ *      mean, a = sample count; common_passes.cpp:1001-1009) on the GPU; this is the
+ *      headless equivalent.  Pixel (x, y) at index y*width + x, as imageStore writes. */
+CAVEPT_API int cavept_read_accum(cavept_ctx* ctx, float* out_rgba32f, size_t bytes);
+/* Tone pass: c/(c+1) then pow(c, 1/2.2) (cave/shader/glsl/post_process.ps.glsl:72-76). */
+CAVEPT_API int cavept_read_tonemapped_rgba8(cavept_ctx* ctx, uint8_t* out_rgba8, size_t bytes);
+CAVEPT_API int cavept_read_tonemapped_rgba32f(cavept_ctx* ctx, float* out_rgba32f, size_t bytes);
+/* Restore a saved accumulator (checkpoint/resume; the accumulator is the only state). */
+CAVEPT_API int cavept_write_accum(cavept_ctx* ctx, const float* rgba32f, size_t bytes);
+
+/* ---- measurement and multi-GPU plumbing ------------------------------------------ */
+CAVEPT_API int cavept_get_stats(cavept_ctx* ctx, cavept_stats* out);
+CAVEPT_API int cavept_reset_stats(cavept_ctx* ctx);
+CAVEPT_API int cavept_set_count_visits(cavept_ctx* ctx, int enable); /* instrumented kernels: node visits / triangle tests */
+CAVEPT_API void* cavept_stream(cavept_ctx* ctx);            /* cudaStream_t the context launches on */
+CAVEPT_API void* cavept_accum_device_ptr(cavept_ctx* ctx);  /* float4[width*height] */
+/* Compositor support: converts the accumulator in place between
+ * (mean, n) and (sum, n) so ranks can be combined with one sum-reduce of float4. */
+CAVEPT_API int cavept_accum_to_sums(cavept_ctx* ctx);
+CAVEPT_API int cavept_accum_from_sums(cavept_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CAVEPT_H_ */

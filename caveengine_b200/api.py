@@ -1,0 +1,323 @@
+"""ctypes binding of include/cavept.h and a Python mirror of the reference facade.
+
+Reference surface mirrored (cave/engine/renderer/path_tracer_render_system.h:10-21):
+    enum class PathTracerMode { NONE, INTERACTIVE, TILED }
+    SetPathTracerMode(mode)            -> PathTracer.set_mode
+    IsPathTracerActive()               -> PathTracer.is_active
+    RequestPathTracerUpdate(cam,scene) -> PathTracer.request_update(scene)
+    Bind/UnbindPathTracerData + PathTracerPassFunc's Dispatch
+        (cave/engine/render_graph/common_passes.cpp:977-999) -> PathTracer.render
+"""
+from __future__ import annotations
+
+import ctypes as C
+import enum
+import os
+from typing import Optional
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(_HERE, "libcavept.so")
+_lib: Optional[C.CDLL] = None
+
+
+class CaveptError(RuntimeError):
+    def __init__(self, code: int, message: str):
+        super().__init__(f"cavept error {code}: {message}")
+        self.code = code
+
+
+class PathTracerMode(enum.IntEnum):  # path_tracer_render_system.h:10-14
+    NONE = 0
+    INTERACTIVE = 1
+    TILED = 2
+
+
+class TraceMode(enum.IntEnum):
+    FAST = 0
+    REFERENCE_WALK = 1
+
+
+ERR_INVALID_ARG, ERR_DEGENERATE_GEOMETRY, ERR_CUDA, ERR_NOT_READY, ERR_CAPACITY = 1, 2, 3, 4, 5
+
+
+class _Config(C.Structure):
+    _fields_ = [("device", C.c_int), ("width", C.c_int), ("height", C.c_int), ("max_bounce", C.c_int), ("trace_mode", C.c_int), ("bvh_mode", C.c_int)]
+
+
+class _Mesh(C.Structure):
+    _fields_ = [("positions", C.c_void_p), ("normals", C.c_void_p), ("indices", C.c_void_p), ("vertex_count", C.c_int), ("index_count", C.c_int)]
+
+
+class _Instance(C.Structure):
+    _fields_ = [("mesh", C.c_int), ("material", C.c_int), ("transform", C.c_float * 16)]
+
+
+class _Material(C.Structure):
+    _fields_ = [("base_color", C.c_float * 3), ("roughness", C.c_float), ("metallic", C.c_float), ("emissive", C.c_float)]
+
+
+class Stats(C.Structure):
+    _fields_ = [
+        ("segments", C.c_uint64), ("node_visits", C.c_uint64), ("triangle_tests", C.c_uint64), ("kernel_launches", C.c_uint64),
+        ("last_build_ms", C.c_float), ("last_compact_ms", C.c_float), ("last_render_ms", C.c_float),
+        ("triangle_count", C.c_int), ("node_count", C.c_int), ("fast_node_count", C.c_int), ("instance_count", C.c_int),
+        ("build_levels", C.c_int), ("build_launches", C.c_int),
+    ]
+
+    def as_dict(self):
+        return {k: getattr(self, k) for k, _ in self._fields_}
+
+
+# every symbol include/cavept.h declares: (name, restype, argtypes)
+_P = C.c_void_p
+ABI = [
+    ("cavept_create", C.c_int, [C.POINTER(_Config), C.POINTER(_P)]),
+    ("cavept_destroy", None, [_P]),
+    ("cavept_last_error", C.c_char_p, [_P]),
+    ("cavept_set_mode", C.c_int, [_P, C.c_int]),
+    ("cavept_is_active", C.c_int, [_P]),
+    ("cavept_upload_scene", C.c_int, [_P, C.POINTER(_Mesh), C.c_int, C.POINTER(_Instance), C.c_int, C.POINTER(_Material), C.c_int]),
+    ("cavept_update_instances", C.c_int, [_P, C.POINTER(_Instance), C.c_int]),
+    ("cavept_update_materials", C.c_int, [_P, C.POINTER(_Material), C.c_int]),
+    ("cavept_rebuild_mesh", C.c_int, [_P, C.c_int, _P, _P]),
+    ("cavept_get_mesh_bvh", C.c_int, [_P, C.c_int, _P, C.c_int]),
+    ("cavept_get_scene_counts", C.c_int, [_P] + [C.POINTER(C.c_int)] * 5),
+    ("cavept_get_scene_arrays", C.c_int, [_P] * 6),
+    ("cavept_set_camera", C.c_int, [_P, C.POINTER(C.c_float), C.POINTER(C.c_float), C.POINTER(C.c_float), C.POINTER(C.c_float), C.c_float]),
+    ("cavept_reset", C.c_int, [_P]),
+    ("cavept_render", C.c_int, [_P, C.c_int, C.c_int]),
+    ("cavept_sync", C.c_int, [_P]),
+    ("cavept_read_accum", C.c_int, [_P, _P, C.c_size_t]),
+    ("cavept_read_tonemapped_rgba8", C.c_int, [_P, _P, C.c_size_t]),
+    ("cavept_read_tonemapped_rgba32f", C.c_int, [_P, _P, C.c_size_t]),
+    ("cavept_write_accum", C.c_int, [_P, _P, C.c_size_t]),
+    ("cavept_get_stats", C.c_int, [_P, C.POINTER(Stats)]),
+    ("cavept_reset_stats", C.c_int, [_P]),
+    ("cavept_set_count_visits", C.c_int, [_P, C.c_int]),
+    ("cavept_stream", _P, [_P]),
+    ("cavept_accum_device_ptr", _P, [_P]),
+    ("cavept_accum_to_sums", C.c_int, [_P]),
+    ("cavept_accum_from_sums", C.c_int, [_P]),
+]
+
+
+def library_path() -> str:
+    return _LIB_PATH
+
+
+def load_library() -> C.CDLL:
+    """Loads libcavept.so and binds every ABI symbol.  Fails loudly if it is missing:
+    there is no fallback implementation."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(_LIB_PATH):
+        raise FileNotFoundError(f"{_LIB_PATH} is missing -- build it with `python -m caveengine_b200.build` (needs nvcc); cavept has no CPU fallback")
+    lib = C.CDLL(_LIB_PATH)
+    for name, restype, argtypes in ABI:
+        fn = getattr(lib, name)  # AttributeError if the library does not export it
+        fn.restype = restype
+        fn.argtypes = argtypes
+    _lib = lib
+    return lib
+
+
+# numpy dtypes of the reference GPU layouts (cave/shader/structured_buffer.hlsl.h:24-61)
+BVH_DT = np.dtype([("min", "<f4", 3), ("miss", "<i4"), ("max", "<f4", 3), ("hit", "<i4"), ("pad", "<f4", 2), ("leaf", "<i4"), ("tri", "<i4")])
+VERTEX_DT = np.dtype([("position", "<f4", 3), ("pad1", "<i4"), ("normal", "<f4", 3), ("pad2", "<i4")])
+INDEX_DT = np.dtype([("tri", "<i4", 3), ("pad1", "<i4")])
+MESH_DT = np.dtype([("transform", "<f4", 16), ("transform_inv", "<f4", 16), ("pad", "<f4", 2), ("root", "<i4"), ("material", "<i4")])
+MATERIAL_DT = np.dtype([("base_color", "<f4", 3), ("roughness", "<f4"), ("emissive", "<f4", 3), ("metallic", "<f4")])
+
+
+def _f3(v):
+    return (C.c_float * 3)(*[float(x) for x in v])
+
+
+class PathTracer:
+    """One context == the reference's file-static PathTracer
+    (cave/engine/renderer/path_tracer_render_system.cpp:8-10), on one GPU."""
+
+    def __init__(self, width: int = 1920, height: int = 1080, max_bounce: int = 5, trace_mode: TraceMode = TraceMode.FAST, device: int = -1):
+        self._lib = load_library()
+        self._ctx = _P()
+        self.width, self.height, self.max_bounce = width, height, max_bounce
+        cfg = _Config(device, width, height, max_bounce, int(trace_mode), 0)
+        rc = self._lib.cavept_create(C.byref(cfg), C.byref(self._ctx))
+        if rc != 0:
+            self._ctx = _P()
+            raise CaveptError(rc, "cavept_create failed (is a CUDA device visible? cavept has no CPU path)")
+        self._keep = None
+        self._resident = False
+
+    # -- lifetime ---------------------------------------------------------------------
+    def close(self):
+        if getattr(self, "_ctx", None):
+            self._lib.cavept_destroy(self._ctx)
+            self._ctx = _P()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def _check(self, rc: int):
+        if rc != 0:
+            raise CaveptError(rc, self._lib.cavept_last_error(self._ctx).decode(errors="replace"))
+
+    # -- SetPathTracerMode / IsPathTracerActive -----------------------------------------
+    def set_mode(self, mode: PathTracerMode):
+        self._check(self._lib.cavept_set_mode(self._ctx, int(mode)))
+
+    def is_active(self) -> bool:
+        return bool(self._lib.cavept_is_active(self._ctx))
+
+    # -- RequestPathTracerUpdate ---------------------------------------------------------
+    def request_update(self, scene):
+        """PathTracer::Update (path_tracer.cpp:49-70): no-op unless the mode is
+        INTERACTIVE/TILED; first call uploads the scene and builds the BVHs."""
+        if not self._resident:
+            self.upload_scene(scene)
+            self._resident = True
+        self.set_camera(scene.camera)
+
+    def upload_scene(self, scene):
+        meshes = (_Mesh * len(scene.meshes))()
+        keep = []
+        for k, m in enumerate(scene.meshes):
+            pos = np.ascontiguousarray(m.positions, dtype=np.float32)
+            nrm = np.ascontiguousarray(m.normals, dtype=np.float32)
+            idx = np.ascontiguousarray(m.indices, dtype=np.uint32)
+            keep += [pos, nrm, idx]
+            meshes[k] = _Mesh(pos.ctypes.data, nrm.ctypes.data, idx.ctypes.data, pos.shape[0], idx.size)
+        inst = self._instances(scene.instances)
+        mats = self._materials(scene.materials)
+        self._check(self._lib.cavept_upload_scene(self._ctx, meshes, len(scene.meshes), inst, len(scene.instances), mats, len(scene.materials)))
+
+    @staticmethod
+    def _instances(instances):
+        arr = (_Instance * len(instances))()
+        for k, i in enumerate(instances):
+            arr[k] = _Instance(i.mesh, i.material, (C.c_float * 16)(*[float(x) for x in np.asarray(i.transform, dtype=np.float32)]))
+        return arr
+
+    @staticmethod
+    def _materials(materials):
+        arr = (_Material * len(materials))()
+        for k, m in enumerate(materials):
+            arr[k] = _Material(_f3(m.base_color), m.roughness, m.metallic, m.emissive)
+        return arr
+
+    def update_instances(self, instances):
+        self._check(self._lib.cavept_update_instances(self._ctx, self._instances(instances), len(instances)))
+
+    def update_materials(self, materials):
+        self._check(self._lib.cavept_update_materials(self._ctx, self._materials(materials), len(materials)))
+
+    def rebuild_mesh(self, mesh: int, positions: np.ndarray, normals: Optional[np.ndarray] = None):
+        pos = np.ascontiguousarray(positions, dtype=np.float32)
+        nrm = None if normals is None else np.ascontiguousarray(normals, dtype=np.float32)
+        self._check(self._lib.cavept_rebuild_mesh(self._ctx, mesh, pos.ctypes.data, None if nrm is None else nrm.ctypes.data))
+
+    # -- parity read-backs ----------------------------------------------------------------
+    def get_mesh_bvh(self, mesh: int, n_tris: int) -> np.ndarray:
+        out = np.zeros(max(2 * n_tris - 1, 1), dtype=BVH_DT)
+        rc = self._lib.cavept_get_mesh_bvh(self._ctx, mesh, out.ctypes.data, out.shape[0])
+        if rc < 0:
+            self._check(-rc)
+        return out[:rc]
+
+    def get_scene_arrays(self):
+        n = [C.c_int() for _ in range(5)]
+        self._check(self._lib.cavept_get_scene_counts(self._ctx, *[C.byref(x) for x in n]))
+        nv, nt, nb, ni, nm = [x.value for x in n]
+        v, i, b = np.zeros(nv, dtype=VERTEX_DT), np.zeros(nt, dtype=INDEX_DT), np.zeros(nb, dtype=BVH_DT)
+        m, mat = np.zeros(ni, dtype=MESH_DT), np.zeros(nm, dtype=MATERIAL_DT)
+        self._check(self._lib.cavept_get_scene_arrays(self._ctx, v.ctypes.data, i.ctypes.data, b.ctypes.data, m.ctypes.data, mat.ctypes.data))
+        return {"vertices": v, "indices": i, "bvhs": b, "meshes": m, "materials": mat}
+
+    # -- per-frame constants ---------------------------------------------------------------
+    def set_camera(self, cam):
+        self._check(self._lib.cavept_set_camera(self._ctx, _f3(cam.position), _f3(cam.right), _f3(cam.up), _f3(cam.forward), float(cam.fov_degree)))
+
+    def reset(self):
+        self._check(self._lib.cavept_reset(self._ctx))
+
+    # -- the pass ----------------------------------------------------------------------------
+    def render(self, first_frame_index: int, n_frames: int = 1, sync: bool = False):
+        self._check(self._lib.cavept_render(self._ctx, first_frame_index, n_frames))
+        if sync:
+            self.sync()
+
+    def sync(self):
+        self._check(self._lib.cavept_sync(self._ctx))
+
+    # -- read-back ---------------------------------------------------------------------------
+    def read_accum(self, out: Optional[np.ndarray] = None) -> np.ndarray:
+        if out is None:
+            out = np.empty((self.height, self.width, 4), dtype=np.float32)
+        self._check(self._lib.cavept_read_accum(self._ctx, out.ctypes.data, out.nbytes))
+        return out
+
+    def write_accum(self, accum: np.ndarray):
+        a = np.ascontiguousarray(accum, dtype=np.float32)
+        self._check(self._lib.cavept_write_accum(self._ctx, a.ctypes.data, a.nbytes))
+
+    def read_tonemapped_rgba8(self) -> np.ndarray:
+        out = np.empty((self.height, self.width, 4), dtype=np.uint8)
+        self._check(self._lib.cavept_read_tonemapped_rgba8(self._ctx, out.ctypes.data, out.nbytes))
+        return out
+
+    def read_tonemapped(self) -> np.ndarray:
+        out = np.empty((self.height, self.width, 4), dtype=np.float32)
+        self._check(self._lib.cavept_read_tonemapped_rgba32f(self._ctx, out.ctypes.data, out.nbytes))
+        return out
+
+    # -- measurement / multi-GPU plumbing ---------------------------------------------------
+    def stats(self) -> dict:
+        s = Stats()
+        self._check(self._lib.cavept_get_stats(self._ctx, C.byref(s)))
+        return s.as_dict()
+
+    def reset_stats(self):
+        self._check(self._lib.cavept_reset_stats(self._ctx))
+
+    def set_count_visits(self, enable: bool):
+        self._check(self._lib.cavept_set_count_visits(self._ctx, 1 if enable else 0))
+
+    @property
+    def stream_handle(self) -> int:
+        return int(self._lib.cavept_stream(self._ctx) or 0)
+
+    @property
+    def accum_device_ptr(self) -> int:
+        return int(self._lib.cavept_accum_device_ptr(self._ctx) or 0)
+
+    def accum_to_sums(self):
+        self._check(self._lib.cavept_accum_to_sums(self._ctx))
+
+    def accum_from_sums(self):
+        self._check(self._lib.cavept_accum_from_sums(self._ctx))
+
+    def accum_as_torch(self):
+        """Zero-copy torch view of the device accumulator (H, W, 4) float32, for
+        torch.distributed collectives.  torch is plumbing only."""
+        import torch
+
+        class _Holder:
+            pass
+
+        h = _Holder()
+        h.__cuda_array_interface__ = {"shape": (self.height, self.width, 4), "typestr": "<f4", "data": (self.accum_device_ptr, False), "version": 3, "strides": None}
+        t = torch.as_tensor(h, device="cuda")
+        self._keep = h
+        return t

@@ -1,0 +1,271 @@
+"""GPU parity tests (run on the B200 box: pytest -m gpu).  Everything goes through the C ABI
+(libcavept.so via caveengine_b200.api); the oracle is only the checker.
+
+Tolerances (stated here, used below):
+  * BVH nodes and scene arrays: bit-exact (memcmp of all bytes).
+  * Images, device vs CPU oracle: the RNG streams are identical, arithmetic is fp32 in the
+    same operation order; the only differences are device sincosf vs libm sinf/cosf (<= 2 ulp)
+    and, for the reference's own code, its double promotions.  A pixel "matches" when every
+    channel is within 1e-4 * (|ref| + 1e-3); at most 1 % of pixels may differ (a 1-ulp
+    direction change can flip a discrete hit after several bounces), and the image RMSE must
+    be below 2 % of the mean radiance.
+  * FAST traversal vs REFERENCE_WALK on the device (same arithmetic, same sincosf): identical
+    closest hits except exact-tie / box-grazing rays: <= 0.1 % of pixels may differ at all.
+"""
+import numpy as np
+import pytest
+
+import helpers as H
+from caveengine_b200 import scenes
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def api():
+    import torch
+
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    import caveengine_b200 as cb
+
+    cb.load_library()  # raises if libcavept.so is missing: no fallback
+    return cb
+
+
+def _tracer(api, scene, w, h, mb, mode):
+    pt = api.PathTracer(w, h, mb, trace_mode=mode, device=0)
+    pt.set_mode(api.PathTracerMode.INTERACTIVE)
+    pt.upload_scene(scene)
+    pt.set_camera(scene.camera)
+    return pt
+
+
+def _pixel_tol(img, ref, max_bad=0.01, rel=1e-4):
+    bad = H.image_mismatch(img, ref, rel=rel)
+    assert bad <= max_bad, f"{bad:.4%} of pixels differ"
+    mean = float(np.mean(np.asarray(ref)[..., :3]))
+    assert H.rmse(img, ref) <= 0.02 * mean + 1e-6
+
+
+# ---- BVH: bit-exact -------------------------------------------------------------------------
+@pytest.mark.parametrize("name", ["tiny", "cornell", "heightfield", "sponza"])
+def test_bvh_bit_exact_vs_oracle(api, best_oracle, scene_cache, name):
+    sc = scene_cache(name)
+    with _tracer(api, sc, 64, 36, 5, api.TraceMode.FAST) as pt:
+        used = sorted({i.mesh for i in sc.instances})
+        for m in used:
+            mesh = sc.meshes[m]
+            want = best_oracle.bvh_build(mesh.indices, mesh.positions)
+            got = pt.get_mesh_bvh(m, mesh.n_tris)
+            assert got.shape == want.shape
+            assert got.tobytes() == want.tobytes(), f"{name} mesh {m}: GPU BVH differs from the {best_oracle.kind} builder"
+        st = pt.stats()
+        assert st["triangle_count"] == sc.n_tris if name != "tiny" else True
+        assert st["build_launches"] > 0
+
+
+def test_bvh_bit_exact_vs_reference_golden(api):
+    g = H.load_golden("bvh_golden.npz")
+    for name in H.golden_cases(g):
+        mesh = scenes.Mesh(g[f"{name}/positions"], np.zeros_like(g[f"{name}/positions"]), g[f"{name}/indices"])
+        sc = scenes.Scene(name, [mesh], [scenes.Instance(0, 0, scenes.mat_identity())], [scenes.Material((0.5, 0.5, 0.5), 0.5, 0.0, 0.0)], scenes.look_at((0, 1, -3), (0, 0, 0)))
+        with _tracer(api, sc, 32, 18, 5, api.TraceMode.FAST) as pt:
+            got = pt.get_mesh_bvh(0, mesh.n_tris)
+            assert got.tobytes() == g[f"{name}/nodes"].tobytes(), name
+
+
+@pytest.mark.parametrize("name", ["tiny", "cornell"])
+def test_scene_arrays_match_reference_assembly(api, best_oracle, scene_cache, name):
+    sc = scene_cache(name)
+    asm = best_oracle.assemble(sc)
+    with _tracer(api, sc, 32, 18, 5, api.TraceMode.FAST) as pt:
+        got = pt.get_scene_arrays()
+    for k in ("vertices", "indices", "bvhs", "meshes", "materials"):
+        assert got[k].tobytes() == getattr(asm, k).tobytes(), k
+
+
+def test_degenerate_geometry_is_an_error_not_a_trap(api):
+    mesh = H.coincident_centroid_mesh(6)
+    sc = scenes.Scene("degenerate", [mesh], [scenes.Instance(0, 0, scenes.mat_identity())], [scenes.Material((0.5, 0.5, 0.5), 0.5, 0.0, 0.0)], scenes.look_at((0, 1, -3), (0, 0, 0)))
+    pt = api.PathTracer(32, 18, 5, device=0)
+    with pytest.raises(api.CaveptError) as e:
+        pt.upload_scene(sc)
+    assert e.value.code == 2
+    assert not pt.is_active()
+    pt.close()
+
+
+# ---- images ------------------------------------------------------------------------------------
+@pytest.mark.parametrize("name,mb,frames", [("tiny", 5, (0, 4)), ("cornell", 5, (7, 3)), ("heightfield", 5, (0, 2)), ("sponza", 8, (0, 2))])
+@pytest.mark.parametrize("mode", ["REFERENCE_WALK", "FAST"])
+def test_image_vs_cpu_oracle(api, port_oracle, scene_cache, name, mb, frames, mode):
+    sc = scene_cache(name)
+    w, h = (96, 54) if name != "sponza" else (64, 36)
+    asm = port_oracle.assemble(sc)
+    want, st = port_oracle.render(asm, sc.camera, w, h, frames[0], frames[1], mb)
+    with _tracer(api, sc, w, h, mb, getattr(api.TraceMode, mode)) as pt:
+        pt.reset_stats()
+        pt.render(frames[0], frames[1], sync=True)
+        img = pt.read_accum()
+        segs = pt.stats()["segments"]
+    assert abs(segs - st["segments"]) <= max(4, st["segments"] // 500)
+    _pixel_tol(img, want)
+
+
+@pytest.mark.parametrize("name", ["tiny_mb5", "cornell_mb5"])
+def test_reference_walk_vs_reference_golden_image(api, name):
+    """Golden image made by the reference's own shader code; the device input is rebuilt from raw
+    meshes, so this also pins the whole upload path."""
+    g = H.load_golden("image_golden.npz")
+    _, cam, p, want = H.golden_scene(g, name)
+    sc = scenes.tiny_scene() if name.startswith("tiny") else scenes.cornell_scene()
+    with _tracer(api, sc, p["width"], p["height"], p["max_bounce"], api.TraceMode.REFERENCE_WALK) as pt:
+        got = pt.get_scene_arrays()
+        if got["bvhs"].tobytes() != g[f"{name}/bvhs"].tobytes() or got["vertices"].tobytes() != g[f"{name}/vertices"].tobytes():
+            pytest.skip("this host generates a different procedural scene than the golden's")
+        pt.render(p["first_frame"], p["n_frames"], sync=True)
+        img = pt.read_accum()
+    _pixel_tol(img, want)
+
+
+def test_fast_equals_reference_walk_full_size(api, scene_cache):
+    """1080p, 8 bounces, 262k triangles: production traversal vs the literal walk, both on the device."""
+    sc = scene_cache("sponza")
+    out = {}
+    for mode in ("REFERENCE_WALK", "FAST"):
+        with _tracer(api, sc, 1920, 1080, 8, getattr(api.TraceMode, mode)) as pt:
+            pt.reset_stats()
+            pt.render(0, 1, sync=True)
+            out[mode] = (pt.read_accum(), pt.stats()["segments"])
+    a, sa = out["REFERENCE_WALK"]
+    b, sb = out["FAST"]
+    assert abs(sa - sb) <= sa // 2000
+    differ = float((np.abs(a - b)[..., :3].max(axis=-1) > 0).mean())
+    assert differ <= 0.001, f"{differ:.4%} of pixels differ"
+    # size-independent properties: sample count, nominal segment bounds, finite radiance
+    assert np.all(b[..., 3] == 1.0)
+    assert 1920 * 1080 <= sb <= 1920 * 1080 * 8
+    assert np.isfinite(b).all() and (b[..., :3] >= 0).all()
+
+
+def test_progressive_accumulation_and_reset(api, scene_cache):
+    sc = scene_cache("tiny")
+    with _tracer(api, sc, 64, 36, 5, api.TraceMode.FAST) as pt:
+        pt.render(0, 6, sync=True)
+        one = pt.read_accum()
+        pt.reset()
+        pt.render(0, 2)
+        pt.render(2, 4, sync=True)
+        two = pt.read_accum()
+        assert one.tobytes() == two.tobytes()  # launches of several frames == the reference's frame-by-frame running mean
+        assert np.all(one[..., 3] == 6.0)
+        pt.set_camera(sc.camera)  # SCENE_DIRTY_CAMERA -> next frame overwrites (path_tracer.cs.glsl:46-57)
+        pt.render(0, 1, sync=True)
+        assert np.all(pt.read_accum()[..., 3] == 1.0)
+        # checkpoint / resume through the accumulator
+        pt.write_accum(one)
+        pt.render(6, 1, sync=True)
+        resumed = pt.read_accum()
+        pt.reset()
+        pt.render(0, 7, sync=True)
+        assert resumed.tobytes() == pt.read_accum().tobytes()
+
+
+def test_mode_gating_mirrors_reference(api, scene_cache):
+    sc = scene_cache("tiny")
+    pt = api.PathTracer(32, 18, 5, device=0)
+    assert not pt.is_active()
+    with pytest.raises(api.CaveptError) as e:
+        pt.render(0, 1)
+    assert e.value.code == 4
+    pt.upload_scene(sc)
+    assert not pt.is_active()  # mode is still NONE (path_tracer.cpp:312-322)
+    pt.set_mode(api.PathTracerMode.INTERACTIVE)
+    assert pt.is_active()
+    pt.set_camera(sc.camera)
+    pt.render(0, 1, sync=True)
+    pt.set_mode(api.PathTracerMode.NONE)
+    assert not pt.is_active()
+    with pytest.raises(api.CaveptError):
+        pt.set_mode(7)
+    pt.close()
+
+
+def test_update_instances_equals_fresh_upload(api, scene_cache):
+    import copy
+
+    sc = scene_cache("tiny")
+    moved = copy.deepcopy(sc)
+    moved.instances[1].transform = scenes.mat_trs((0.4, 1.5, 1.2), yaw_deg=12.0)
+    moved.instances[3].transform = scenes.mat_trs((3.2, 0.55, 1.4), yaw_deg=-40.0, s=1.2)
+    with _tracer(api, sc, 64, 36, 5, api.TraceMode.FAST) as pt:
+        pt.render(0, 2, sync=True)
+        pt.update_instances(moved.instances)
+        pt.render(0, 2, sync=True)
+        a = pt.read_accum()
+    with _tracer(api, moved, 64, 36, 5, api.TraceMode.FAST) as pt:
+        pt.render(0, 2, sync=True)
+        b = pt.read_accum()
+    assert a.tobytes() == b.tobytes()
+
+
+def test_update_materials(api, port_oracle, scene_cache):
+    import copy
+
+    sc = copy.deepcopy(scene_cache("cornell"))
+    with _tracer(api, sc, 64, 36, 5, api.TraceMode.FAST) as pt:
+        sc.materials[1] = scenes.Material((0.1, 0.2, 0.9), 0.5, 0.0, 0.0)
+        pt.update_materials(sc.materials)
+        pt.render(0, 2, sync=True)
+        img = pt.read_accum()
+    want, _ = port_oracle.render(port_oracle.assemble(sc), sc.camera, 64, 36, 0, 2, 5)
+    _pixel_tol(img, want)
+
+
+def test_tonemap_matches_post_process(api, port_oracle, scene_cache):
+    sc = scene_cache("cornell")
+    with _tracer(api, sc, 64, 36, 5, api.TraceMode.FAST) as pt:
+        pt.render(0, 4, sync=True)
+        acc = pt.read_accum()
+        tone = pt.read_tonemapped()
+        tone8 = pt.read_tonemapped_rgba8()
+    want = port_oracle.tonemap(acc)
+    assert np.max(np.abs(tone - want)) <= 2e-6
+    assert np.max(np.abs(tone8[..., :3].astype(np.int32) - np.rint(np.clip(want[..., :3], 0, 1) * 255).astype(np.int32))) <= 1
+    assert np.all(tone8[..., 3] == 255)
+
+
+def test_sum_reduce_round_trip(api, scene_cache):
+    sc = scene_cache("tiny")
+    with _tracer(api, sc, 64, 36, 5, api.TraceMode.FAST) as pt:
+        pt.render(0, 5, sync=True)
+        mean = pt.read_accum()
+        pt.accum_to_sums()
+        sums = pt.read_accum()
+        assert np.allclose(sums[..., :3], mean[..., :3] * 5.0, rtol=1e-6)
+        pt.accum_from_sums()
+        back = pt.read_accum()
+        assert np.allclose(back[..., :3], mean[..., :3], rtol=1e-6, atol=1e-7)
+        import torch
+
+        t = pt.accum_as_torch()
+        assert t.shape == (36, 64, 4) and t.is_cuda
+        torch.cuda.synchronize()
+        assert np.array_equal(t.cpu().numpy(), back)
+
+
+def test_visit_counters(api, scene_cache):
+    sc = scene_cache("heightfield")
+    with _tracer(api, sc, 96, 54, 5, api.TraceMode.REFERENCE_WALK) as pt:
+        pt.set_count_visits(True)
+        pt.reset_stats()
+        pt.render(0, 1, sync=True)
+        walk = pt.stats()
+    with _tracer(api, sc, 96, 54, 5, api.TraceMode.FAST) as pt:
+        pt.set_count_visits(True)
+        pt.reset_stats()
+        pt.render(0, 1, sync=True)
+        fast = pt.stats()
+    assert walk["segments"] == fast["segments"] or abs(walk["segments"] - fast["segments"]) <= 2
+    assert 0 < fast["node_visits"] < walk["node_visits"]  # ordered traversal visits fewer nodes than the fixed-order walk

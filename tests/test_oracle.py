@@ -1,0 +1,101 @@
+"""CPU tests: the oracle port (oracle/cave_oracle.cpp) against the golden vectors that the
+reference's own code produced (tests/golden/make_golden.py), and -- where oracle/_ref was
+built -- against the reference's code run live."""
+import numpy as np
+import pytest
+
+import helpers as H
+
+
+def test_port_bvh_matches_reference_golden(port_oracle):
+    g = H.load_golden("bvh_golden.npz")
+    cases = H.golden_cases(g)
+    assert len(cases) >= 9
+    for name in cases:
+        nodes = port_oracle.bvh_build(g[f"{name}/indices"], g[f"{name}/positions"])
+        want = g[f"{name}/nodes"]
+        assert nodes.shape[0] == want.shape[0] == 2 * (g[f"{name}/indices"].size // 3) - 1, name
+        assert nodes.tobytes() == want.tobytes(), f"{name}: BVH bytes differ from the reference builder's"
+
+
+def test_port_bvh_large_digests(port_oracle):
+    from caveengine_b200 import scenes
+
+    g = H.load_golden("bvh_digests.npz")
+    meshes = {"heightfield_10000": scenes.heightfield_mesh(), "sponza_mesh0_floor": scenes.sponza_scene().meshes[0], "sponza_mesh22_blob": scenes.sponza_scene().meshes[22]}
+    checked = 0
+    for name, mesh in meshes.items():
+        if H.sha(mesh.positions, mesh.indices) != g[f"{name}/input_sha256"].tobytes():
+            continue  # this host generated a different procedural mesh; the live comparisons still cover it
+        nodes = port_oracle.bvh_build(mesh.indices, mesh.positions)
+        assert nodes.shape[0] == int(g[f"{name}/n_nodes"][0])
+        assert H.sha(nodes) == g[f"{name}/nodes_sha256"].tobytes(), name
+        checked += 1
+    assert checked >= 1
+
+
+def test_port_inverse_matches_glm(port_oracle):
+    g = H.load_golden("inverse_golden.npz")
+    for m, want in zip(g["mats"], g["inverses"]):
+        assert port_oracle.mat4_inverse(m).tobytes() == want.tobytes()
+
+
+@pytest.mark.parametrize("name", ["tiny_mb5", "cornell_mb5", "tiny_mb8", "tiny_mb1"])
+def test_port_image_matches_reference_golden(port_oracle, name):
+    g = H.load_golden("image_golden.npz")
+    asm, cam, p, want = H.golden_scene(g, name)
+    img, st = port_oracle.render(asm, cam, p["width"], p["height"], p["first_frame"], p["n_frames"], p["max_bounce"], threads=2)
+    # fp32-pure arithmetic vs the header-as-C++ double promotions can flip a rare path
+    assert abs(st["segments"] - p["segments"]) <= max(2, p["segments"] // 1000)
+    # the header compiled as C++ promotes a few expressions to double; the fp32-pure
+    # port may differ by an ulp there: tolerance 1e-5 relative, at most 0.2 % of pixels beyond it
+    assert H.image_mismatch(img, want, rel=1e-5) <= 0.002
+    assert H.rmse(img, want) < 5e-3
+
+
+def test_port_degenerate_geometry_is_an_error(port_oracle):
+    mesh = H.coincident_centroid_mesh(6)
+    with pytest.raises(ValueError):
+        port_oracle.bvh_build(mesh.indices, mesh.positions)
+
+
+def test_port_counts_are_consistent(port_oracle, scene_cache):
+    sc = scene_cache("tiny")
+    asm = port_oracle.assemble(sc)
+    _, st = port_oracle.render(asm, sc.camera, 32, 18, 0, 2, 5, threads=1)
+    n_samples = 32 * 18 * 2
+    assert n_samples <= st["segments"] <= n_samples * 5
+    assert st["mesh_iters"] == st["segments"] * len(sc.instances)
+    assert st["node_visits"] >= st["mesh_iters"]
+
+
+def test_progressive_accumulation_equals_one_shot(port_oracle, scene_cache):
+    sc = scene_cache("tiny")
+    asm = port_oracle.assemble(sc)
+    one, _ = port_oracle.render(asm, sc.camera, 24, 14, 0, 6, 5)
+    acc, _ = port_oracle.render(asm, sc.camera, 24, 14, 0, 2, 5)
+    acc, _ = port_oracle.render(asm, sc.camera, 24, 14, 2, 4, 5, accum=acc, reset_first=False)
+    assert one.tobytes() == acc.tobytes()
+    assert np.all(one[..., 3] == 6.0)
+
+
+# ---- live against the reference's own code (only where oracle/_ref exists) ---------------
+def test_ref_live_bvh_all_scene_meshes(port_oracle, ref_oracle, scene_cache):
+    for name in ("tiny", "cornell", "heightfield", "sponza"):
+        for mesh in scene_cache(name).meshes:
+            assert port_oracle.bvh_build(mesh.indices, mesh.positions).tobytes() == ref_oracle.bvh_build(mesh.indices, mesh.positions).tobytes()
+
+
+def test_ref_live_trap_on_degenerate(ref_oracle):
+    mesh = H.coincident_centroid_mesh(6)
+    with pytest.raises(ValueError):
+        ref_oracle.bvh_build(mesh.indices, mesh.positions)
+
+
+def test_ref_live_image_sponza(port_oracle, ref_oracle, scene_cache):
+    sc = scene_cache("sponza")
+    asm = ref_oracle.assemble(sc)
+    a, sa = port_oracle.render(asm, sc.camera, 64, 36, 5, 2, 8)
+    b, sb = ref_oracle.render(asm, sc.camera, 64, 36, 5, 2, 8)
+    assert abs(sa["segments"] - sb["segments"]) <= 16
+    assert H.image_mismatch(a, b, rel=1e-5) <= 0.005

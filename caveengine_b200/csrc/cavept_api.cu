@@ -77,7 +77,9 @@ struct cavept_ctx {
     DevBuf<GpuPtMaterial> d_materials;
     // production layout
     DevBuf<FastNode> d_fnodes;
-    DevBuf<FastTri> d_ftris;
+    DevBuf<FastTri> d_ftris, d_fnormals;
+    DevBuf<int> d_mesh_root_ref;
+    std::vector<int> mesh_root_ref;
     DevBuf<int> d_inst_root;
     // upload staging
     DevBuf<float> d_raw_pos, d_raw_nrm;
@@ -170,7 +172,7 @@ int rebuild_instance_arrays(cavept_ctx* ctx) {
         mat4_inverse(g.transform, g.transformInv);
         g.rootBvhId = rec.node_off;
         g.materialId = lookup[rec.first_material];
-        inst_root[i] = 2 * ctx->n_pairs + rec.built;
+        inst_root[i] = ctx->mesh_root_ref[rec.built];
     }
     CU(ctx, ctx->d_meshes.reserve(ctx->gpu_meshes.size()));
     CU(ctx, ctx->d_materials.reserve(ctx->gpu_materials.size()));
@@ -197,10 +199,9 @@ int rebuild_tlas(cavept_ctx* ctx) {
         const MeshRecord& rec = ctx->meshes[ctx->instances[i].mesh];
         boxes[i] = transform_box(ctx->instances[i].transform, roots[rec.built].min, roots[rec.built].max);
     }
-    const int base = 2 * ctx->n_pairs + n_built;
+    const int base = 2 * ctx->n_pairs;
     std::vector<FastNode> tlas;
-    ctx->tlas_depth = build_tlas(boxes, base, tlas);
-    ctx->tlas_root = base;
+    ctx->tlas_depth = build_tlas(boxes, base, tlas, &ctx->tlas_root);
     ctx->n_fast_nodes = base + (int)tlas.size();
     if ((size_t)ctx->n_fast_nodes > ctx->d_fnodes.cap) return fail(ctx, CAVEPT_ERR_CAPACITY, "fast node buffer too small");
     ctx->ex.upload(ctx->d_fnodes.ptr + base, tlas.data(), tlas.size() * sizeof(FastNode));
@@ -297,6 +298,8 @@ int build_all(cavept_ctx* ctx) {
     CU(ctx, ctx->d_leaf_tris.reserve(n_nodes));
     CU(ctx, ctx->d_tri_base.reserve((size_t)n_nodes + 1));
     CU(ctx, ctx->d_ftris.reserve(T));
+    CU(ctx, ctx->d_fnormals.reserve(T));
+    CU(ctx, ctx->d_mesh_root_ref.reserve(n_built));
     // pairs <= T/2 .. generous bound: every kept node is a reference node; + roots + TLAS (2*instances)
     CU(ctx, ctx->d_fnodes.reserve((size_t)n_nodes + n_built + 2 * ctx->instances.size() + 8));
     CompactArrays c{};
@@ -312,7 +315,11 @@ int build_all(cavept_ctx* ctx) {
     c.tri_base = ctx->d_tri_base.ptr;
     c.fnodes = ctx->d_fnodes.ptr;
     c.ftris = ctx->d_ftris.ptr;
+    c.fnormals = ctx->d_fnormals.ptr;
+    c.mesh_root_ref = ctx->d_mesh_root_ref.ptr;
     ctx->n_pairs = run_compact_layout(ctx->ex, c);
+    ctx->mesh_root_ref.resize(n_built);
+    ctx->ex.download(ctx->mesh_root_ref.data(), ctx->d_mesh_root_ref.ptr, sizeof(int) * (size_t)n_built);
     CU(ctx, cudaEventRecord(ctx->ev2, ctx->ex.stream));
     CU(ctx, cudaStreamSynchronize(ctx->ex.stream));
     if (int e = check_exec(ctx, "compact layout")) return e;
@@ -365,7 +372,7 @@ CAVEPT_API void cavept_destroy(cavept_ctx* ctx) {
     cudaSetDevice(ctx->device);
     if (ctx->ex.stream) cudaStreamSynchronize(ctx->ex.stream);
     ctx->d_vertices.release(); ctx->d_indices.release(); ctx->d_nodes.release(); ctx->d_meshes.release(); ctx->d_materials.release();
-    ctx->d_fnodes.release(); ctx->d_ftris.release(); ctx->d_inst_root.release();
+    ctx->d_fnodes.release(); ctx->d_ftris.release(); ctx->d_fnormals.release(); ctx->d_mesh_root_ref.release(); ctx->d_inst_root.release();
     ctx->d_raw_pos.release(); ctx->d_raw_nrm.release(); ctx->d_raw_idx.release(); ctx->d_tri_off.release(); ctx->d_vert_off.release();
     ctx->d_tri_bmin.release(); ctx->d_tri_bmax.release(); ctx->d_tri_centroid.release();
     ctx->d_order.release(); ctx->d_order_next.release(); ctx->d_node_of.release(); ctx->d_node_of_next.release();
@@ -585,6 +592,7 @@ CAVEPT_API int cavept_render(cavept_ctx* ctx, int first_frame_index, int n_frame
     p.mesh_count = (int)ctx->gpu_meshes.size();
     p.fnodes = ctx->d_fnodes.ptr;
     p.ftris = ctx->d_ftris.ptr;
+    p.fnormals = ctx->d_fnormals.ptr;
     p.inst_fast_root = ctx->d_inst_root.ptr;
     p.tlas_root = ctx->tlas_root;
     std::memcpy(p.cam_pos, ctx->cam_pos, 12);

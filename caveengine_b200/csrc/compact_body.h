@@ -9,7 +9,9 @@
 //     three dependent 32 B vertex gathers (112 B).
 // Node j of the reference array is "kept" iff it is a root or its parent holds more
 // than kFastLeafMax triangles.  Positions: the children of the r-th kept interior node
-// (r = exclusive scan in pre-order) sit at 2r and 2r+1; mesh roots follow the pairs.
+// (r = exclusive scan in pre-order) sit at 2r and 2r+1.  A mesh root has no record of its
+// own (its box is never tested: the TLAS holds a padded superset); only its node
+// reference is kept, in mesh_root_ref[m].
 #pragma once
 #include "cv_common.h"
 #include "trace_body.h"
@@ -29,6 +31,8 @@ struct CompactArrays {
     int* tri_base;    // exclusive scan of leaf_tris (n_nodes + 1)
     FastNode* fnodes;
     FastTri* ftris;
+    FastTri* fnormals;    // per FastTri slot: the triangle's three vertex normals
+    int* mesh_root_ref;   // per built mesh: node reference of its root
     int n_pairs;          // filled by the driver after the scan
 };
 
@@ -49,23 +53,12 @@ CV_D void body_compact_emit(const CompactArrays& c, int j) {
     if (j >= c.n_nodes) return;
     if (!compact_kept(c, j)) return;
     const int parent = c.node_parent[j];
-    int pos;
-    if (parent < 0) {
-        pos = 2 * c.n_pairs + (-1 - parent);
-    } else {
-        pos = 2 * c.pair_rank[parent] + (j == parent + 1 ? 0 : 1);
-    }
-    const GpuPtBvh src = c.nodes[j];
-    FastNode out;
-    out.mn[0] = src.min[0]; out.mn[1] = src.min[1]; out.mn[2] = src.min[2];
-    out.mx[0] = src.max[0]; out.mx[1] = src.max[1]; out.mx[2] = src.max[2];
     const int count = c.node_count[j];
+    int ref;
     if (count > kFastLeafMax) {
-        out.a = 2 * c.pair_rank[j];
-        out.b = 0;
+        ref = 2 * c.pair_rank[j];
     } else {
-        out.a = c.tri_base[j];
-        out.b = count;
+        ref = make_leaf_ref(c.tri_base[j], count);
         // the subtree of j occupies slots [j, j + 2*count - 1) in pre-order
         int k = 0;
         for (int s = j; s < j + 2 * count - 1; ++s) {
@@ -78,10 +71,24 @@ CV_D void body_compact_emit(const CompactArrays& c, int j) {
             t.v1.x = vb.position[0]; t.v1.y = vb.position[1]; t.v1.z = vb.position[2]; t.v1.w = 0.0f;
             t.v2.x = vc.position[0]; t.v2.y = vc.position[1]; t.v2.z = vc.position[2]; t.v2.w = 0.0f;
             c.ftris[c.tri_base[j] + k] = t;
+            t.v0.x = va.normal[0]; t.v0.y = va.normal[1]; t.v0.z = va.normal[2];
+            t.v1.x = vb.normal[0]; t.v1.y = vb.normal[1]; t.v1.z = vb.normal[2];
+            t.v2.x = vc.normal[0]; t.v2.y = vc.normal[1]; t.v2.z = vc.normal[2];
+            c.fnormals[c.tri_base[j] + k] = t;
             ++k;
         }
     }
-    c.fnodes[pos] = out;
+    if (parent < 0) {
+        c.mesh_root_ref[-1 - parent] = ref;
+        return;
+    }
+    const GpuPtBvh src = c.nodes[j];
+    FastNode out;
+    out.mn[0] = src.min[0]; out.mn[1] = src.min[1]; out.mn[2] = src.min[2];
+    out.mx[0] = src.max[0]; out.mx[1] = src.max[1]; out.mx[2] = src.max[2];
+    out.a = ref;
+    out.b = count;
+    c.fnodes[2 * c.pair_rank[parent] + (j == parent + 1 ? 0 : 1)] = out;
 }
 
 struct FnCompactClassify {
@@ -93,7 +100,7 @@ struct FnCompactEmit {
     CV_D void operator()(int j) const { body_compact_emit(c, j); }
 };
 
-// Runs the compaction; returns the number of sibling pairs (2*pairs + n_meshes nodes written).
+// Runs the compaction; returns the number of sibling pairs (2*pairs nodes written).
 template<class Exec>
 int run_compact(Exec& ex, CompactArrays c) {
     ex.launch(c.n_nodes, FnCompactClassify{ c });

@@ -65,8 +65,8 @@ inline void tlas_fill(const std::vector<WorldBox>& boxes, std::vector<int>& ids,
     }
     max_depth = std::max(max_depth, depth);
     if (hi - lo == 1) {
-        n.a = ids[lo];
-        n.b = -1;
+        n.a = make_instance_ref(ids[lo]);
+        n.b = 1;
         out[slot] = n;
         return;
     }
@@ -79,22 +79,27 @@ inline void tlas_fill(const std::vector<WorldBox>& boxes, std::vector<int>& ids,
     });
     const int pair = (int)out.size();
     out.resize(out.size() + 2);
-    n.a = base + pair;
-    n.b = 0;
+    n.a = base + pair;  // interior reference = index of the child pair
+    n.b = hi - lo;
     out[slot] = n;
     tlas_fill(boxes, ids, lo, mid, pair, base, out, depth + 1, max_depth);
     tlas_fill(boxes, ids, mid, hi, pair + 1, base, out, depth + 1, max_depth);
 }
 }  // namespace detail
 
-// out[0] is the root; child indices are absolute (base + position in out).  Returns depth.
-inline int build_tlas(const std::vector<WorldBox>& boxes, int base, std::vector<FastNode>& out) {
+// Child pairs are written to out[0..]; references are absolute (base + position in out), so
+// `base` must be even-aligned with the FastNode array position out[0] will be copied to.
+// The root has no record: its node reference is returned in *root_ref.  Returns depth.
+inline int build_tlas(const std::vector<WorldBox>& boxes, int base, std::vector<FastNode>& out, int* root_ref) {
     out.clear();
-    out.resize(1);
+    out.resize(1);  // scratch slot 0 receives the root record; callers skip it
     std::vector<int> ids(boxes.size());
     for (size_t i = 0; i < ids.size(); ++i) ids[i] = (int)i;
     int max_depth = 0;
-    detail::tlas_fill(boxes, ids, 0, (int)boxes.size(), 0, base, out, 0, max_depth);
+    // out[0] is a scratch root record; pairs start at out[1], hence base - 1 below
+    detail::tlas_fill(boxes, ids, 0, (int)boxes.size(), 0, base - 1, out, 0, max_depth);
+    *root_ref = out[0].a;
+    out.erase(out.begin());
     return max_depth;
 }
 

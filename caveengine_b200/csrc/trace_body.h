@@ -21,10 +21,9 @@ constexpr float kRayTMax = 999999999.0f;   // RAY_T_MAX, :27
 constexpr int kFastLeafMax = 4;            // subtrees of <= 4 triangles are median-split in the reference (:138); they become leaves here
 constexpr int kStackSize = 64;
 
-// 32-byte node of the production layout.  Siblings are adjacent (pair at a, a+1).
-//   interior: a = index of the left child, b = 0
-//   leaf:     a = first FastTri slot,      b = triangle count (1..4)
-//   TLAS leaf: a = instance index,          b = -1
+// 32-byte node of the production layout.  Siblings are adjacent (a pair is 64 bytes).
+//   a = the node's own reference (see make_leaf_ref / make_instance_ref below)
+//   b = subtree triangle count (informational)
 struct alignas(16) FastNode {
     float mn[3];
     int a;
@@ -50,8 +49,9 @@ struct TraceParams {
     // production layout
     const FastNode* fnodes;
     const FastTri* ftris;
-    const int* inst_fast_root;  // per instance: FastNode index of its mesh's root
-    int tlas_root;
+    const FastTri* fnormals;    // per FastTri slot: the three vertex normals (shading)
+    const int* inst_fast_root;  // per instance: node reference of its mesh's root
+    int tlas_root;              // node reference of the TLAS root
     // PerFrameConstantBuffer (cbuffer.hlsl.h:193-207)
     float cam_pos[3], cam_right[3], cam_up[3], cam_fwd[3];
     float cam_distance;  // tan(c_cameraFovDegree * PI / 180), path_tracer.cs.glsl:31-32
@@ -185,103 +185,147 @@ CV_D Hit hit_scene_reference(const TraceParams& p, Ray& ray, unsigned long long*
     return res;
 }
 
-// Slab test of the production traversal: same interval logic as HitBvh plus the
-// (result-neutral) rejection of boxes entirely behind the origin; returns entry t.
-CV_HD bool slab_fast(F3 o, F3 inv, float ray_t, const float* mn, const float* mx, float& t_entry) {
-    const float ax = (mn[0] - o.x) * inv.x, bx = (mx[0] - o.x) * inv.x;
-    const float ay = (mn[1] - o.y) * inv.y, by = (mx[1] - o.y) * inv.y;
-    const float az = (mn[2] - o.z) * inv.z, bz = (mx[2] - o.z) * inv.z;
+// ---- production traversal ---------------------------------------------------------------
+// Node references (one int): interior = index of the child pair (children at ref, ref+1);
+// leaf = sign bit | (count-1) << 29 | first FastTri slot inside a BLAS, sign bit | instance
+// index inside the TLAS.  A node's own reference is stored in its record, so one 64-byte
+// fetch of a sibling pair yields both boxes and both references.
+constexpr int kRefSentinel = 0x7fffffff;  // bottom of the stack
+constexpr int kRefDeferredPop = 0x7ffffffe;
+CV_HD bool ref_is_interior(int r) { return (uint32_t)r < (uint32_t)kRefDeferredPop; }
+CV_HD int make_leaf_ref(int first_slot, int count) { return (int)(0x80000000u | ((uint32_t)(count - 1) << 29) | (uint32_t)first_slot); }
+CV_HD int make_instance_ref(int instance) { return (int)(0x80000000u | (uint32_t)instance); }
+
+#if defined(__CUDA_ARCH__)
+#define CV_WARP_ANY(pred) __any_sync(0xffffffffu, (pred))
+#define CV_WARP_COUNT(pred) __popc(__ballot_sync(0xffffffffu, (pred)))
+#else  // the emulator steps one lane at a time: a warp of one
+#define CV_WARP_ANY(pred) (pred)
+#define CV_WARP_COUNT(pred) ((pred) ? 1 : 0)
+#endif
+
+// Slab test of the production traversal.  Same interval logic as HitBvh (:133-149) with
+// two result-neutral changes: boxes entirely behind the origin are rejected, and the exit
+// distance is widened by 2 ulp so that rounding differences to the reference's
+// (min - o) * inv form can only ever add candidate triangles, never lose one.
+CV_HD bool slab_fast(F3 inv, F3 oinv, float ray_t, const FastNode& n, float& t_entry) {
+    const float ax = cv_fma(n.mn[0], inv.x, oinv.x), bx = cv_fma(n.mx[0], inv.x, oinv.x);
+    const float ay = cv_fma(n.mn[1], inv.y, oinv.y), by = cv_fma(n.mx[1], inv.y, oinv.y);
+    const float az = cv_fma(n.mn[2], inv.z, oinv.z), bz = cv_fma(n.mx[2], inv.z, oinv.z);
     const float tmin = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fminf(az, bz));
-    const float tmax = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fmaxf(az, bz));
+    const float tmax = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fmaxf(az, bz)) * 1.0000003f;
     t_entry = tmin;
     return (tmin <= tmax) && (ray_t > tmin) && (tmax >= 0.0f);
 }
 
-// ---- production traversal ---------------------------------------------------------------
-template<bool kCount>
-CV_D Hit hit_scene_fast(const TraceParams& p, Ray& ray, unsigned long long* cnt) {
-    Hit res;
-    res.mesh = -1;
-    res.tri = -1;
-    res.u = 0.0f;
-    res.v = 0.0f;
+// Per-lane traversal state of the production kernel.
+struct Walk {
     int stack[kStackSize];
-    int sp = 0;
-    // active ray = world ray while in the TLAS, mesh-local ray while inside an instance
-    F3 o = ray.origin, d = ray.direction, inv = ray.inv_dir;
-    int cur_instance = -1;
-    int node = p.tlas_root;  // TLAS nodes live at indices >= tlas_base == tlas_root (root is the first TLAS node)
-    const int tlas_base = p.tlas_root;
-    for (;;) {
-        if (node >= tlas_base && cur_instance >= 0) {  // popped back into the TLAS
-            o = ray.origin;
-            d = ray.direction;
-            inv = ray.inv_dir;
-            cur_instance = -1;
+    int sp;         // stack[0] holds the sentinel
+    int ref;        // current node reference
+    int leaf;       // postponed BLAS leaf (0 = none)
+    int instance;   // -1 while in the TLAS
+    int blas_sp;    // stack depth at instance entry (0 = not inside an instance)
+    F3 o, d, inv, oinv;  // active ray: world ray in the TLAS, mesh-local ray inside an instance
+    int hit_instance, hit_slot;
+    float hit_u, hit_v;
+};
+
+CV_D void walk_set_ray(Walk& w, F3 o, F3 d) {
+    w.o = o;
+    w.d = d;
+    w.inv = recip3(d);
+    w.oinv = f3(-(o.x * w.inv.x), -(o.y * w.inv.y), -(o.z * w.inv.z));
+}
+
+CV_D void walk_begin(const TraceParams& p, Walk& w, const Ray& ray) {
+    w.stack[0] = kRefSentinel;
+    w.sp = 1;
+    w.ref = p.tlas_root;
+    w.leaf = 0;
+    w.instance = -1;
+    w.blas_sp = 0;
+    w.hit_instance = -1;
+    w.hit_slot = -1;
+    w.hit_u = 0.0f;
+    w.hit_v = 0.0f;
+    walk_set_ray(w, ray.origin, ray.direction);
+}
+
+// Pop the next reference.  Leaving an instance restores the world ray; that is postponed
+// (kRefDeferredPop) while a leaf of this instance is still waiting to be intersected.
+CV_D void walk_pop(Walk& w, const Ray& ray) {
+    if (w.sp == w.blas_sp) {
+        if (w.leaf < 0) {
+            w.ref = kRefDeferredPop;
+            return;
         }
-        const FastNode nd = p.fnodes[node];
-        bool descend = false;
-        if (nd.b == 0) {  // interior: test both children, go near first
-            const FastNode c0 = p.fnodes[nd.a];
-            const FastNode c1 = p.fnodes[nd.a + 1];
-            if (kCount) cnt[1] += 2;
-            float t0, t1;
-            const bool h0 = slab_fast(o, inv, ray.t, c0.mn, c0.mx, t0);
-            const bool h1 = slab_fast(o, inv, ray.t, c1.mn, c1.mx, t1);
-            if (h0 && h1) {
-                const bool swap = t1 < t0;
-                node = swap ? nd.a + 1 : nd.a;
-                if (sp < kStackSize) stack[sp++] = swap ? nd.a : nd.a + 1;
-                descend = true;
-            } else if (h0 || h1) {
-                node = h0 ? nd.a : nd.a + 1;
-                descend = true;
-            }
-        } else if (nd.b > 0) {  // BLAS leaf
-            for (int k = 0; k < nd.b; ++k) {
-                const FastTri tr = p.ftris[nd.a + k];
-                if (kCount) ++cnt[2];
-                float u, v;
-                if (hit_triangle(f3(tr.v0.x, tr.v0.y, tr.v0.z), f3(tr.v1.x, tr.v1.y, tr.v1.z), f3(tr.v2.x, tr.v2.y, tr.v2.z), o, d, ray.t, u, v)) {
-                    res.tri = (int)f2u(tr.v0.w);
-                    res.mesh = cur_instance;
-                    res.u = u;
-                    res.v = v;
-                }
-            }
-        } else {  // TLAS leaf: enter the instance (HitScene :160-166)
-            cur_instance = nd.a;
-            const GpuPtMesh& mesh = p.meshes[cur_instance];
-            o = mat_mul(mesh.transformInv, ray.origin, 1.0f);
-            d = mat_mul(mesh.transformInv, ray.direction, 0.0f);
-            inv = recip3(d);
-            node = p.inst_fast_root[cur_instance];
-            // the mesh root's own box was already accepted through the TLAS (a padded superset)
-            descend = true;
-        }
-        if (!descend) {
-            if (sp == 0) break;
-            node = stack[--sp];
+        walk_set_ray(w, ray.origin, ray.direction);
+        w.instance = -1;
+        w.blas_sp = 0;
+    }
+    w.ref = w.stack[--w.sp];
+}
+
+template<bool kCount>
+CV_D void walk_intersect_leaf(const TraceParams& p, Walk& w, int leaf_ref, Ray& ray, unsigned long long* cnt) {
+    const int first = leaf_ref & 0x1fffffff;
+    const int count = ((leaf_ref >> 29) & 3) + 1;
+    for (int k = 0; k < count; ++k) {
+        const FastTri tr = p.ftris[first + k];
+        if (kCount) ++cnt[2];
+        float u, v;
+        if (hit_triangle(f3(tr.v0.x, tr.v0.y, tr.v0.z), f3(tr.v1.x, tr.v1.y, tr.v1.z), f3(tr.v2.x, tr.v2.y, tr.v2.z), w.o, w.d, ray.t, u, v)) {
+            w.hit_slot = first + k;
+            w.hit_instance = w.instance;
+            w.hit_u = u;
+            w.hit_v = v;
         }
     }
-    return res;
+}
+
+// One interior step (or instance entry) for a lane whose reference is actionable.
+template<bool kCount>
+CV_D void walk_step(const TraceParams& p, Walk& w, const Ray& ray, unsigned long long* cnt) {
+    if (w.ref < 0) {  // TLAS leaf: enter the instance (HitScene :160-166)
+        w.instance = w.ref & 0x7fffffff;
+        const GpuPtMesh& mesh = p.meshes[w.instance];
+        walk_set_ray(w, mat_mul(mesh.transformInv, ray.origin, 1.0f), mat_mul(mesh.transformInv, ray.direction, 0.0f));
+        w.blas_sp = w.sp;
+        w.ref = p.inst_fast_root[w.instance];
+    } else {
+        const FastNode c0 = p.fnodes[w.ref];
+        const FastNode c1 = p.fnodes[w.ref + 1];
+        if (kCount) cnt[1] += 2;
+        float t0, t1;
+        const bool h0 = slab_fast(w.inv, w.oinv, ray.t, c0, t0);
+        const bool h1 = slab_fast(w.inv, w.oinv, ray.t, c1, t1);
+        if (h0 && h1) {
+            const bool swap = t1 < t0;
+            w.ref = swap ? c1.a : c0.a;
+            w.stack[w.sp++] = swap ? c0.a : c1.a;
+        } else if (h0 || h1) {
+            w.ref = h0 ? c0.a : c1.a;
+        } else {
+            walk_pop(w, ray);
+        }
+    }
+    // postpone the first BLAS leaf and keep descending while other lanes still search
+    if (w.ref < 0 && w.instance >= 0 && w.leaf == 0 && w.sp > w.blas_sp) {
+        w.leaf = w.ref;
+        w.ref = w.stack[--w.sp];
+    }
 }
 
 // ---- one RayColor iteration after the scene query (:198-235).  Returns true when the
 //      path ends (miss, or MAX_BOUNCE segments traced). ---------------------------------
-CV_D bool shade_segment(const TraceParams& p, const Hit& hit, Ray& ray, uint32_t& state, F3& radiance, F3& throughput, int& bounce) {
-    if (hit.mesh >= 0 && hit.tri >= 0) {
+CV_D bool shade_hit(const TraceParams& p, bool is_hit, int mesh_id, F3 n1, F3 n2, F3 n3, float u, float v, Ray& ray, uint32_t& state, F3& radiance,
+                    F3& throughput, int& bounce) {
+    if (is_hit) {
         ray.origin = ray.origin + ray.t * ray.direction;
         ray.t = kRayTMax;
-        const GpuPtMesh& mesh = p.meshes[hit.mesh];
-        const int* idx = p.indices[hit.tri].tri;
-        const GpuPtVertex& va = p.vertices[idx[0]];
-        const GpuPtVertex& vb = p.vertices[idx[1]];
-        const GpuPtVertex& vc = p.vertices[idx[2]];
-        const F3 n1 = f3(va.normal[0], va.normal[1], va.normal[2]);
-        const F3 n2 = f3(vb.normal[0], vb.normal[1], vb.normal[2]);
-        const F3 n3 = f3(vc.normal[0], vc.normal[1], vc.normal[2]);
-        F3 n = n1 + hit.u * (n2 - n1) + hit.v * (n3 - n1);
+        const GpuPtMesh& mesh = p.meshes[mesh_id];
+        F3 n = n1 + u * (n2 - n1) + v * (n3 - n1);
         n = normalize3(mat_mul(mesh.transform, n, 0.0f));
         const GpuPtMaterial& mat = p.materials[mesh.materialId];
         const float reflect_chance = rnd(state) > mat.metallic ? 0.0f : 1.0f;
@@ -297,6 +341,21 @@ CV_D bool shade_segment(const TraceParams& p, const Hit& hit, Ray& ray, uint32_t
     }
     radiance = radiance + f3(0.3f, 0.3f, 0.3f) * throughput;
     return true;
+}
+
+CV_D bool shade_segment(const TraceParams& p, const Hit& hit, Ray& ray, uint32_t& state, F3& radiance, F3& throughput, int& bounce) {
+    const bool is_hit = hit.mesh >= 0 && hit.tri >= 0;
+    F3 n1 = f3(0, 0, 0), n2 = n1, n3 = n1;
+    if (is_hit) {
+        const int* idx = p.indices[hit.tri].tri;
+        const GpuPtVertex& va = p.vertices[idx[0]];
+        const GpuPtVertex& vb = p.vertices[idx[1]];
+        const GpuPtVertex& vc = p.vertices[idx[2]];
+        n1 = f3(va.normal[0], va.normal[1], va.normal[2]);
+        n2 = f3(vb.normal[0], vb.normal[1], vb.normal[2]);
+        n3 = f3(vc.normal[0], vc.normal[1], vc.normal[2]);
+    }
+    return shade_hit(p, is_hit, hit.mesh, n1, n2, n3, hit.u, hit.v, ray, state, radiance, throughput, bounce);
 }
 
 // ---- main(), path_tracer.cs.glsl:11-44: seed, jitter, camera ray -----------------------
@@ -336,12 +395,11 @@ CV_HD void accumulate(F4& acc, F3 radiance, bool dirty) {
     }
 }
 
-// One pixel, frames [first_frame, first_frame + n_frames).  The segment loop is flat: a
-// lane whose path ends starts its next sample at once, so the lanes of a warp stay in
-// the traversal code together whatever bounce each of them is on.
+// One pixel, frames [first_frame, first_frame + n_frames), REFERENCE_WALK traversal.  The
+// segment loop is flat: a lane whose path ends starts its next sample at once.
 // Returns the number of segments traced; visit counters go to cnt[1..2] when kCount.
-template<bool kFast, bool kCount>
-CV_D unsigned int body_trace_pixel(const TraceParams& p, int x, int y, unsigned long long* cnt) {
+template<bool kCount>
+CV_D unsigned int body_trace_pixel_reference(const TraceParams& p, int x, int y, unsigned long long* cnt) {
     if (x >= p.width || y >= p.height || p.n_frames <= 0) return 0u;
     const size_t pix = (size_t)y * (size_t)p.width + (size_t)x;
     F4 acc = p.accum[pix];
@@ -353,7 +411,7 @@ CV_D unsigned int body_trace_pixel(const TraceParams& p, int x, int y, unsigned 
     F3 radiance = f3(0.0f, 0.0f, 0.0f), throughput = f3(1.0f, 1.0f, 1.0f);
     start_path(p, x, y, p.first_frame, ray, seed);
     for (;;) {
-        const Hit hit = kFast ? hit_scene_fast<kCount>(p, ray, cnt) : hit_scene_reference<kCount>(p, ray, cnt);
+        const Hit hit = hit_scene_reference<kCount>(p, ray, cnt);
         ++segments;
         if (shade_segment(p, hit, ray, seed, radiance, throughput, bounce)) {
             accumulate(acc, radiance, f == 0 && p.reset_first != 0);
@@ -365,6 +423,88 @@ CV_D unsigned int body_trace_pixel(const TraceParams& p, int x, int y, unsigned 
         }
     }
     p.accum[pix] = acc;
+    return segments;
+}
+
+// Production kernel body: ONE loop per warp in which every lane is either descending the
+// BVH, intersecting a leaf, or shading -- whatever sample and bounce it is on.
+//   phase A  interior steps; a lane that reaches a leaf postpones it and keeps descending
+//            while any other lane is still searching (speculative while-while traversal);
+//   phase B  every lane intersects its postponed / current leaf;
+//   phase C  lanes whose traversal finished shade and start their next segment -- done in
+//            batches (>= kShadeBatch lanes, or nobody left traversing) so the shading code
+//            is not replayed for one lane at a time.
+// Lanes of a warp never wait for the slowest ray of a segment, only for a shading batch.
+constexpr int kShadeBatch = 8;
+
+template<bool kCount>
+CV_D unsigned int body_trace_pixel_fast(const TraceParams& p, int x, int y, unsigned long long* cnt) {
+    const bool valid = x < p.width && y < p.height && p.n_frames > 0;
+    const size_t pix = valid ? (size_t)y * (size_t)p.width + (size_t)x : 0;
+    Ray ray;
+    uint32_t seed = 1u;
+    int f = 0;
+    int bounce = 0;
+    unsigned int segments = 0;
+    F3 radiance = f3(0.0f, 0.0f, 0.0f), throughput = f3(1.0f, 1.0f, 1.0f);
+    bool done = !valid;
+    Walk w;
+    ray.origin = f3(0, 0, 0);
+    ray.direction = f3(0, 0, 1);
+    ray.inv_dir = f3(0, 0, 1);
+    ray.t = kRayTMax;
+    if (valid) start_path(p, x, y, p.first_frame, ray, seed);
+    walk_begin(p, w, ray);
+    if (!valid) w.ref = kRefSentinel;
+    for (;;) {
+        // ---- phase A -------------------------------------------------------------------
+        for (;;) {
+            const bool can_step = ref_is_interior(w.ref) || (w.ref < 0 && w.instance < 0);
+            if (!CV_WARP_ANY(can_step && w.leaf == 0)) break;  // nobody is searching any more
+            if (can_step) walk_step<kCount>(p, w, ray, cnt);
+        }
+        // ---- phase B -------------------------------------------------------------------
+        if (w.leaf < 0) {
+            walk_intersect_leaf<kCount>(p, w, w.leaf, ray, cnt);
+            w.leaf = 0;
+        }
+        if (w.ref < 0 && w.instance >= 0) {
+            walk_intersect_leaf<kCount>(p, w, w.ref, ray, cnt);
+            walk_pop(w, ray);
+        } else if (w.ref == kRefDeferredPop) {
+            walk_pop(w, ray);
+        }
+        // ---- phase C -------------------------------------------------------------------
+        const bool need_shade = !done && w.ref == kRefSentinel && w.leaf == 0;
+        const int n_need = CV_WARP_COUNT(need_shade);
+        const int n_walking = CV_WARP_COUNT(!done && !need_shade);
+        if (need_shade && (n_need >= kShadeBatch || n_walking == 0)) {
+            ++segments;
+            const bool is_hit = w.hit_slot >= 0;
+            F3 n1 = f3(0, 0, 0), n2 = n1, n3 = n1;
+            if (is_hit) {
+                const FastTri nr = p.fnormals[w.hit_slot];
+                n1 = f3(nr.v0.x, nr.v0.y, nr.v0.z);
+                n2 = f3(nr.v1.x, nr.v1.y, nr.v1.z);
+                n3 = f3(nr.v2.x, nr.v2.y, nr.v2.z);
+            }
+            if (shade_hit(p, is_hit, w.hit_instance, n1, n2, n3, w.hit_u, w.hit_v, ray, seed, radiance, throughput, bounce)) {
+                F4 acc = p.accum[pix];
+                accumulate(acc, radiance, f == 0 && p.reset_first != 0);
+                p.accum[pix] = acc;
+                if (++f == p.n_frames) {
+                    done = true;
+                } else {
+                    radiance = f3(0.0f, 0.0f, 0.0f);
+                    throughput = f3(1.0f, 1.0f, 1.0f);
+                    bounce = 0;
+                    start_path(p, x, y, p.first_frame + f, ray, seed);
+                }
+            }
+            if (!done) walk_begin(p, w, ray);
+        }
+        if (!CV_WARP_ANY(!done)) break;
+    }
     return segments;
 }
 

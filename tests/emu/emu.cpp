@@ -87,7 +87,7 @@ EMU_API int emu_bvh_build(const GpuPtVertex* vertices, const GpuPtIndex* indices
 // Production layout from the arrays emu_bvh_build returned.  fnodes needs
 // n_nodes + n_meshes + 2*n_instances + 8 entries, ftris n_tris.  Returns pair count.
 EMU_API int emu_compact(const GpuPtBvh* nodes, const int* parent, const int* count, int n_nodes, const GpuPtVertex* vertices, const GpuPtIndex* indices,
-                        FastNode* fnodes, FastTri* ftris) {
+                        FastNode* fnodes, FastTri* ftris, FastTri* fnormals, int* mesh_root_ref) {
     std::vector<int> is_pair(n_nodes), pair_rank(n_nodes + 1), leaf_tris(n_nodes), tri_base(n_nodes + 1);
     CompactArrays c{};
     c.nodes = nodes;
@@ -102,22 +102,24 @@ EMU_API int emu_compact(const GpuPtBvh* nodes, const int* parent, const int* cou
     c.tri_base = tri_base.data();
     c.fnodes = fnodes;
     c.ftris = ftris;
+    c.fnormals = fnormals;
+    c.mesh_root_ref = mesh_root_ref;
     EmuExec ex;
     return run_compact(ex, c);
 }
 
 // TLAS exactly as cavept_api.cu builds it: root boxes = first node of each built mesh.
 // mesh_of_instance[i] = built-mesh index; mesh_root_node[k] = GpuPtBvh slot of mesh k's root.
-// Writes TLAS nodes at fnodes[base..]; returns number of TLAS nodes.
+// Writes TLAS nodes at fnodes[base..]; returns number of TLAS nodes, root reference in *root_ref.
 EMU_API int emu_tlas(const GpuPtBvh* nodes, const GpuPtMesh* meshes, int n_instances, const int* mesh_of_instance, const int* mesh_root_node, int base,
-                     FastNode* fnodes) {
+                     FastNode* fnodes, int* root_ref) {
     std::vector<WorldBox> boxes(n_instances);
     for (int i = 0; i < n_instances; ++i) {
         const GpuPtBvh& r = nodes[mesh_root_node[mesh_of_instance[i]]];
         boxes[i] = transform_box(meshes[i].transform, r.min, r.max);
     }
     std::vector<FastNode> tlas;
-    build_tlas(boxes, base, tlas);
+    build_tlas(boxes, base, tlas, root_ref);
     std::memcpy(fnodes + base, tlas.data(), tlas.size() * sizeof(FastNode));
     return (int)tlas.size();
 }
@@ -133,7 +135,7 @@ struct EmuCamera {
 };
 
 EMU_API long long emu_render(const GpuPtVertex* vertices, const GpuPtIndex* indices, const GpuPtBvh* bvhs, const GpuPtMesh* meshes, int mesh_count,
-                             const GpuPtMaterial* materials, const FastNode* fnodes, const FastTri* ftris, const int* inst_fast_root, int tlas_root,
+                             const GpuPtMaterial* materials, const FastNode* fnodes, const FastTri* ftris, const FastTri* fnormals, const int* inst_fast_root, int tlas_root,
                              const EmuCamera* cam, int max_bounce, int width, int height, int first_frame, int n_frames, int reset_first, float* accum,
                              int fast, unsigned long long* counters) {
     TraceParams p{};
@@ -145,6 +147,7 @@ EMU_API long long emu_render(const GpuPtVertex* vertices, const GpuPtIndex* indi
     p.mesh_count = mesh_count;
     p.fnodes = fnodes;
     p.ftris = ftris;
+    p.fnormals = fnormals;
     p.inst_fast_root = inst_fast_root;
     p.tlas_root = tlas_root;
     std::memcpy(p.cam_pos, cam->position, 12);
@@ -164,7 +167,7 @@ EMU_API long long emu_render(const GpuPtVertex* vertices, const GpuPtIndex* indi
     long long segs = 0;
     for (int y = 0; y < height; ++y) {
         for (int x = 0; x < width; ++x) {
-            segs += fast ? body_trace_pixel<true, true>(p, x, y, cnt) : body_trace_pixel<false, true>(p, x, y, cnt);
+            segs += fast ? body_trace_pixel_fast<true>(p, x, y, cnt) : body_trace_pixel_reference<true>(p, x, y, cnt);
         }
     }
     if (counters) {

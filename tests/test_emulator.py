@@ -104,15 +104,20 @@ def test_compact_layout_invariants(port_oracle, scene_cache):
     sc = scene_cache("heightfield")
     asm = port_oracle.assemble(sc)
     emu = E.EmuScene(asm, sc)
-    fn = emu.fnodes[: emu.tlas_root + emu.n_tlas]
-    blas = fn[: emu.tlas_root]
-    leaves = blas[blas["b"] > 0]
-    assert int(leaves["b"].sum()) == sc.n_tris  # every triangle in exactly one leaf
-    assert leaves["b"].max() <= 4
+    blas = emu.fnodes[: emu.tlas_base]
+    refs = blas["a"]
+    leaf = refs < 0
+    counts = ((refs[leaf] >> 29) & 3) + 1
+    assert int(counts.sum()) == sc.n_tris  # every triangle in exactly one leaf
+    assert np.array_equal(counts, blas["b"][leaf])
     ids = emu.ftris["v0"][:, 3].view(np.int32)
     assert sorted(ids.tolist()) == list(range(sc.n_tris))
-    interior = blas[blas["b"] == 0]
-    assert np.all(interior["a"] % 2 == 0) and np.all(interior["a"] + 1 < emu.tlas_root)
+    interior = refs[~leaf]
+    assert np.all(interior % 2 == 0) and np.all(interior + 1 < emu.tlas_base)
+    assert sorted(interior.tolist() + [int(emu.mesh_root_ref[0])]) == list(range(0, emu.tlas_base, 2))  # every pair referenced once
+    # pre-gathered normals follow the triangles
+    tri = asm.indices["tri"][ids]
+    assert np.array_equal(emu.fnormals["v1"][:, :3], asm.vertices["normal"][tri[:, 1]])
 
 
 def test_inverse_matches_glm_golden():

@@ -195,7 +195,8 @@ __global__ void __launch_bounds__(128) k_trace(const TraceParams p) {
     const int x = blockIdx.x * 16 + (warp & 1) * 8 + (lane & 7);
     const int y = blockIdx.y * 8 + (warp >> 1) * 4 + (lane >> 3);
     unsigned long long cnt[3] = { 0ull, 0ull, 0ull };
-    unsigned int segs = kFast ? body_trace_pixel_fast<kCount>(p, x, y, cnt) : body_trace_pixel_reference<kCount>(p, x, y, cnt);
+    __shared__ int s_stack[kFast ? kStackSize * 128 : 1];  // [depth][thread]: conflict-free whatever each lane's depth
+    unsigned int segs = kFast ? body_trace_pixel_fast<kCount>(p, x, y, s_stack + threadIdx.x, 128, cnt) : body_trace_pixel_reference<kCount>(p, x, y, cnt);
     segs = __reduce_add_sync(0xffffffffu, segs);
     if (lane == 0 && segs) atomicAdd(&p.counters[0], (unsigned long long)segs);
     if (kCount) {

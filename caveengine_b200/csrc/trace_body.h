@@ -19,7 +19,7 @@ namespace cavept {
 constexpr float kEpsilon = 1.1920929e-7f;  // EPSILON, shared_path_tracer.h:24
 constexpr float kRayTMax = 999999999.0f;   // RAY_T_MAX, :27
 constexpr int kFastLeafMax = 4;            // subtrees of <= 4 triangles are median-split in the reference (:138); they become leaves here
-constexpr int kStackSize = 64;
+constexpr int kStackSize = 32;  // per-lane entries in shared memory (16 KB per 128-thread block)
 
 // 32-byte node of the production layout.  Siblings are adjacent (a pair is 64 bytes).
 //   a = the node's own reference (see make_leaf_ref / make_instance_ref below)
@@ -220,8 +220,9 @@ CV_HD bool slab_fast(F3 inv, F3 oinv, float ray_t, const FastNode& n, float& t_e
 
 // Per-lane traversal state of the production kernel.
 struct Walk {
-    int stack[kStackSize];
-    int sp;         // stack[0] holds the sentinel
+    int* stack;     // lane-strided: entry k of this lane is stack[k * stride]
+    int stride;
+    int sp;         // entry 0 holds the sentinel
     int ref;        // current node reference
     int leaf;       // postponed BLAS leaf (0 = none)
     int instance;   // -1 while in the TLAS
@@ -264,7 +265,7 @@ CV_D void walk_pop(Walk& w, const Ray& ray) {
         w.instance = -1;
         w.blas_sp = 0;
     }
-    w.ref = w.stack[--w.sp];
+    w.ref = w.stack[(--w.sp) * w.stride];
 }
 
 template<bool kCount>
@@ -303,7 +304,7 @@ CV_D void walk_step(const TraceParams& p, Walk& w, const Ray& ray, unsigned long
         if (h0 && h1) {
             const bool swap = t1 < t0;
             w.ref = swap ? c1.a : c0.a;
-            w.stack[w.sp++] = swap ? c0.a : c1.a;
+            w.stack[(w.sp++) * w.stride] = swap ? c0.a : c1.a;
         } else if (h0 || h1) {
             w.ref = h0 ? c0.a : c1.a;
         } else {
@@ -313,7 +314,7 @@ CV_D void walk_step(const TraceParams& p, Walk& w, const Ray& ray, unsigned long
     // postpone the first BLAS leaf and keep descending while other lanes still search
     if (w.ref < 0 && w.instance >= 0 && w.leaf == 0 && w.sp > w.blas_sp) {
         w.leaf = w.ref;
-        w.ref = w.stack[--w.sp];
+        w.ref = w.stack[(--w.sp) * w.stride];
     }
 }
 
@@ -438,7 +439,7 @@ CV_D unsigned int body_trace_pixel_reference(const TraceParams& p, int x, int y,
 constexpr int kShadeBatch = 8;
 
 template<bool kCount>
-CV_D unsigned int body_trace_pixel_fast(const TraceParams& p, int x, int y, unsigned long long* cnt) {
+CV_D unsigned int body_trace_pixel_fast(const TraceParams& p, int x, int y, int* stack, int stride, unsigned long long* cnt) {
     const bool valid = x < p.width && y < p.height && p.n_frames > 0;
     const size_t pix = valid ? (size_t)y * (size_t)p.width + (size_t)x : 0;
     Ray ray;
@@ -449,6 +450,8 @@ CV_D unsigned int body_trace_pixel_fast(const TraceParams& p, int x, int y, unsi
     F3 radiance = f3(0.0f, 0.0f, 0.0f), throughput = f3(1.0f, 1.0f, 1.0f);
     bool done = !valid;
     Walk w;
+    w.stack = stack;
+    w.stride = stride;
     ray.origin = f3(0, 0, 0);
     ray.direction = f3(0, 0, 1);
     ray.inv_dir = f3(0, 0, 1);

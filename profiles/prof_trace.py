@@ -1,0 +1,23 @@
+#!/usr/bin/env python3
+"""Tiny driver for ncu captures: uploads the bench scene and renders `spp` frames once
+(after one warm launch).  Usage: python profiles/prof_trace.py [spp] [scene]"""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import caveengine_b200 as cb
+from caveengine_b200 import scenes
+
+spp = int(sys.argv[1]) if len(sys.argv) > 1 else 2
+name = sys.argv[2] if len(sys.argv) > 2 else "sponza"
+scene = {"sponza": scenes.sponza_scene, "cornell": scenes.cornell_scene}[name]()
+pt = cb.PathTracer(1920, 1080, 8 if name == "sponza" else 5)
+pt.set_mode(cb.PathTracerMode.INTERACTIVE)
+pt.upload_scene(scene)
+pt.set_camera(scene.camera)
+pt.render(0, 1, sync=True)
+pt.reset_stats()
+pt.render(1, spp, sync=True)
+st = pt.stats()
+print("segments", st["segments"], "ms", st["last_render_ms"], "Mseg/s", st["segments"] / st["last_render_ms"] / 1e3, "build_ms", st["last_build_ms"])
+pt.close()

@@ -165,9 +165,10 @@ EMU_API long long emu_render(const GpuPtVertex* vertices, const GpuPtIndex* indi
     unsigned long long cnt[3] = { 0, 0, 0 };
     p.counters = cnt;
     long long segs = 0;
+    int stack[kStackSize];
     for (int y = 0; y < height; ++y) {
         for (int x = 0; x < width; ++x) {
-            segs += fast ? body_trace_pixel_fast<true>(p, x, y, cnt) : body_trace_pixel_reference<true>(p, x, y, cnt);
+            segs += fast ? body_trace_pixel_fast<true>(p, x, y, stack, 1, cnt) : body_trace_pixel_reference<true>(p, x, y, cnt);
         }
     }
     if (counters) {

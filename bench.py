@@ -280,7 +280,7 @@ def main():
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": workload, "trace_mode": args.trace_mode, "l2": "flushed between steps (256 MiB memset on the launch stream); scene working set ~35 MB is L2-resident in steady state",
                        "parallelism": f"frames split over {world} GPU(s), one NCCL sum-reduce of the float4 accumulator"},
-            "bvh_build_ms": build["last_build_ms"], "bvh_compact_ms": build["last_compact_ms"], "bvh_levels": build["build_levels"], "bvh_launches": build["build_launches"],
+            "bvh_build_ms": build["last_build_ms"], "bvh_fast_build_ms": build["last_fast_build_ms"], "bvh_fast_levels": build["fast_build_levels"], "bvh_fast_launches": build["fast_build_launches"], "bvh_levels": build["build_levels"], "bvh_launches": build["build_launches"],
             "scene_upload_and_build_wall_ms_cold": upload_ms,
             "segments_per_step": seg_per_launch, "last_kernel_ms": kernel_ms_last,
             "gpu_launches": int(launches),

@@ -10,6 +10,7 @@ There is no CPU implementation here: importing works anywhere, but creating a
 `PathTracer` raises unless the CUDA library is present and a GPU is visible.
 """
 from .api import (  # noqa: F401
+    BvhMode,
     CaveptError,
     PathTracer,
     PathTracerMode,

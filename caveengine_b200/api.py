@@ -39,6 +39,11 @@ class TraceMode(enum.IntEnum):
     REFERENCE_WALK = 1
 
 
+class BvhMode(enum.IntEnum):
+    PARITY = 0  # reference-layout per-mesh BVHs (bit-exact) + the production tree
+    FAST = 1  # production tree only
+
+
 ERR_INVALID_ARG, ERR_DEGENERATE_GEOMETRY, ERR_CUDA, ERR_NOT_READY, ERR_CAPACITY = 1, 2, 3, 4, 5
 
 
@@ -61,9 +66,9 @@ class _Material(C.Structure):
 class Stats(C.Structure):
     _fields_ = [
         ("segments", C.c_uint64), ("node_visits", C.c_uint64), ("triangle_tests", C.c_uint64), ("kernel_launches", C.c_uint64),
-        ("last_build_ms", C.c_float), ("last_compact_ms", C.c_float), ("last_render_ms", C.c_float),
+        ("last_build_ms", C.c_float), ("last_fast_build_ms", C.c_float), ("last_render_ms", C.c_float),
         ("triangle_count", C.c_int), ("node_count", C.c_int), ("fast_node_count", C.c_int), ("instance_count", C.c_int),
-        ("build_levels", C.c_int), ("build_launches", C.c_int),
+        ("build_levels", C.c_int), ("build_launches", C.c_int), ("fast_build_levels", C.c_int), ("fast_build_launches", C.c_int),
     ]
 
     def as_dict(self):
@@ -140,11 +145,12 @@ class PathTracer:
     """One context == the reference's file-static PathTracer
     (cave/engine/renderer/path_tracer_render_system.cpp:8-10), on one GPU."""
 
-    def __init__(self, width: int = 1920, height: int = 1080, max_bounce: int = 5, trace_mode: TraceMode = TraceMode.FAST, device: int = -1):
+    def __init__(self, width: int = 1920, height: int = 1080, max_bounce: int = 5, trace_mode: TraceMode = TraceMode.FAST, device: int = -1,
+                 bvh_mode: BvhMode = BvhMode.PARITY):
         self._lib = load_library()
         self._ctx = _P()
         self.width, self.height, self.max_bounce = width, height, max_bounce
-        cfg = _Config(device, width, height, max_bounce, int(trace_mode), 0)
+        cfg = _Config(device, width, height, max_bounce, int(trace_mode), int(bvh_mode))
         rc = self._lib.cavept_create(C.byref(cfg), C.byref(self._ctx))
         if rc != 0:
             self._ctx = _P()

@@ -9,7 +9,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libcavept.so")
 SOURCES = ["kernels.cu", "cavept_api.cu"]
-HEADERS = ["cv_common.h", "bvh_parity_body.h", "bvh_parity_driver.h", "compact_body.h", "trace_body.h", "tlas_host.h", "kernels.h", "../../include/cavept.h"]
+HEADERS = ["cv_common.h", "bvh_parity_body.h", "bvh_parity_driver.h", "wbvh_body.h", "trace_body.h", "host_math.h", "kernels.h", "../../include/cavept.h"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

@@ -13,7 +13,7 @@
 
 #include "../../include/cavept.h"
 #include "kernels.h"
-#include "tlas_host.h"
+#include "host_math.h"
 
 using namespace cavept;
 
@@ -67,7 +67,8 @@ struct cavept_ctx {
     std::vector<cavept_material> materials;
     std::vector<GpuPtMesh> gpu_meshes;
     std::vector<GpuPtMaterial> gpu_materials;
-    int n_verts = 0, n_tris = 0, n_nodes = 0, n_pairs = 0, n_fast_nodes = 0, tlas_root = 0, tlas_depth = 0;
+    int n_verts = 0, n_tris = 0, n_nodes = 0, n_prims = 0, n_pairs = 0, root_ref = 0, fast_levels = 0;
+    bool nodes_resident = false;  // reference-layout GpuPtBvh array built (CAVEPT_BVH_PARITY)
 
     // reference-layout arrays
     DevBuf<GpuPtVertex> d_vertices;
@@ -78,9 +79,13 @@ struct cavept_ctx {
     // production layout
     DevBuf<FastNode> d_fnodes;
     DevBuf<FastTri> d_ftris, d_fnormals;
-    DevBuf<int> d_mesh_root_ref;
-    std::vector<int> mesh_root_ref;
-    DevBuf<int> d_inst_root;
+    DevBuf<int> d_inst_prim_off, d_inst_tri_off;
+    DevBuf<F4> d_prim_bmin, d_prim_bmax;
+    DevBuf<int> d_w_order, d_w_order_next, d_w_node_of, d_w_node_of_next, d_w_scan, d_w_counters;
+    DevBuf<unsigned char> d_w_flags;
+    DevBuf<WItem> d_w_items, d_w_items_next;
+    DevBuf<WBins> d_w_bins;
+    DevBuf<uint32_t> d_w_root_acc;
     // upload staging
     DevBuf<float> d_raw_pos, d_raw_nrm;
     DevBuf<uint32_t> d_raw_idx;
@@ -92,7 +97,7 @@ struct cavept_ctx {
     DevBuf<BuildItem> d_items, d_items_next;
     DevBuf<ItemAccum> d_accum_items;
     DevBuf<ItemBins> d_bins;
-    DevBuf<int> d_node_parent, d_node_count, d_is_pair, d_pair_rank, d_leaf_tris, d_tri_base;
+    DevBuf<int> d_node_parent, d_node_count;
     // image
     DevBuf<F4> d_accum, d_tone;
     DevBuf<unsigned char> d_tone8;
@@ -162,7 +167,6 @@ int rebuild_instance_arrays(cavept_ctx* ctx) {
         ctx->gpu_materials.push_back(make_gpu_material(ctx->materials[rec.first_material]));
     }
     ctx->gpu_meshes.resize(ctx->instances.size());
-    std::vector<int> inst_root(ctx->instances.size());
     for (size_t i = 0; i < ctx->instances.size(); ++i) {
         const cavept_instance& in = ctx->instances[i];
         const MeshRecord& rec = ctx->meshes[in.mesh];
@@ -172,44 +176,106 @@ int rebuild_instance_arrays(cavept_ctx* ctx) {
         mat4_inverse(g.transform, g.transformInv);
         g.rootBvhId = rec.node_off;
         g.materialId = lookup[rec.first_material];
-        inst_root[i] = ctx->mesh_root_ref[rec.built];
     }
     CU(ctx, ctx->d_meshes.reserve(ctx->gpu_meshes.size()));
     CU(ctx, ctx->d_materials.reserve(ctx->gpu_materials.size()));
-    CU(ctx, ctx->d_inst_root.reserve(inst_root.size()));
     ctx->ex.upload(ctx->d_meshes.ptr, ctx->gpu_meshes.data(), ctx->gpu_meshes.size() * sizeof(GpuPtMesh));
     ctx->ex.upload(ctx->d_materials.ptr, ctx->gpu_materials.data(), ctx->gpu_materials.size() * sizeof(GpuPtMaterial));
-    ctx->ex.upload(ctx->d_inst_root.ptr, inst_root.data(), inst_root.size() * sizeof(int));
     CU(ctx, cudaStreamSynchronize(ctx->ex.stream));
     return check_exec(ctx, "instance upload");
 }
 
-// TLAS over the instances' world boxes; appended after the BLAS nodes.
-int rebuild_tlas(cavept_ctx* ctx) {
-    const int n_built = (int)ctx->built_order.size();
-    // mesh root boxes: the first node of each mesh in the reference-layout array
-    std::vector<GpuPtBvh> roots(n_built);
-    for (int k = 0; k < n_built; ++k) {
-        const MeshRecord& rec = ctx->meshes[ctx->built_order[k]];
-        CU(ctx, cudaMemcpyAsync(&roots[k], ctx->d_nodes.ptr + rec.node_off, sizeof(GpuPtBvh), cudaMemcpyDeviceToHost, ctx->ex.stream));
-    }
-    CU(ctx, cudaStreamSynchronize(ctx->ex.stream));
-    std::vector<WorldBox> boxes(ctx->instances.size());
-    for (size_t i = 0; i < ctx->instances.size(); ++i) {
+// Production BVH: one world-space tree over every (instance, triangle) pair (wbvh_body.h).
+// Needs d_vertices / d_indices / d_meshes; rerun whenever geometry or a transform changes.
+int build_world(cavept_ctx* ctx) {
+    const int n_inst = (int)ctx->instances.size();
+    std::vector<int> prim_off(n_inst + 1), tri_off(n_inst);
+    long long total = 0;
+    for (int i = 0; i < n_inst; ++i) {
         const MeshRecord& rec = ctx->meshes[ctx->instances[i].mesh];
-        boxes[i] = transform_box(ctx->instances[i].transform, roots[rec.built].min, roots[rec.built].max);
+        prim_off[i] = (int)total;
+        tri_off[i] = rec.tri_off;
+        total += rec.tri_count;
+        if (total > (1ll << 28)) return fail(ctx, CAVEPT_ERR_CAPACITY, "more than 2^28 instanced triangles");
     }
-    const int base = 2 * ctx->n_pairs;
-    std::vector<FastNode> tlas;
-    ctx->tlas_depth = build_tlas(boxes, base, tlas, &ctx->tlas_root);
-    ctx->n_fast_nodes = base + (int)tlas.size();
-    if ((size_t)ctx->n_fast_nodes > ctx->d_fnodes.cap) return fail(ctx, CAVEPT_ERR_CAPACITY, "fast node buffer too small");
-    ctx->ex.upload(ctx->d_fnodes.ptr + base, tlas.data(), tlas.size() * sizeof(FastNode));
+    prim_off[n_inst] = (int)total;
+    const int P = (int)total;
+    ctx->n_prims = P;
+    const size_t items_cap = (size_t)P / 2 + 8, pairs_cap = (size_t)P + 8;
+    CU(ctx, ctx->d_inst_prim_off.reserve(n_inst + 1));
+    CU(ctx, ctx->d_inst_tri_off.reserve(n_inst));
+    CU(ctx, ctx->d_prim_bmin.reserve(P));
+    CU(ctx, ctx->d_prim_bmax.reserve(P));
+    CU(ctx, ctx->d_w_order.reserve(P));
+    CU(ctx, ctx->d_w_order_next.reserve(P));
+    CU(ctx, ctx->d_w_node_of.reserve(P));
+    CU(ctx, ctx->d_w_node_of_next.reserve(P));
+    CU(ctx, ctx->d_w_flags.reserve(P));
+    CU(ctx, ctx->d_w_scan.reserve((size_t)P + 1));
+    CU(ctx, ctx->d_scan_tmp.reserve((size_t)P / kScanTile + 4));
+    CU(ctx, ctx->d_w_items.reserve(items_cap));
+    CU(ctx, ctx->d_w_items_next.reserve(items_cap));
+    CU(ctx, ctx->d_w_bins.reserve(items_cap));
+    CU(ctx, ctx->d_w_counters.reserve(4));
+    CU(ctx, ctx->d_w_root_acc.reserve(12));
+    CU(ctx, ctx->d_fnodes.reserve(2 * pairs_cap));
+    CU(ctx, ctx->d_ftris.reserve(P));
+    CU(ctx, ctx->d_fnormals.reserve(P));
+    ctx->ex.scan_tmp = ctx->d_scan_tmp.ptr;
+    ctx->ex.upload(ctx->d_inst_prim_off.ptr, prim_off.data(), prim_off.size() * sizeof(int));
+    ctx->ex.upload(ctx->d_inst_tri_off.ptr, tri_off.data(), tri_off.size() * sizeof(int));
     CU(ctx, cudaStreamSynchronize(ctx->ex.stream));
-    if (ctx->build_levels + ctx->tlas_depth + 2 > kStackSize) {
-        return fail(ctx, CAVEPT_ERR_CAPACITY, "BVH depth %d + TLAS depth %d exceeds the traversal stack (%d)", ctx->build_levels, ctx->tlas_depth, kStackSize);
+
+    WBuild b{};
+    b.vertices = ctx->d_vertices.ptr;
+    b.indices = ctx->d_indices.ptr;
+    b.instances = ctx->d_meshes.ptr;
+    b.inst_prim_off = ctx->d_inst_prim_off.ptr;
+    b.inst_tri_off = ctx->d_inst_tri_off.ptr;
+    b.n_inst = n_inst;
+    b.n_prims = P;
+    b.bmin = ctx->d_prim_bmin.ptr;
+    b.bmax = ctx->d_prim_bmax.ptr;
+    b.order = ctx->d_w_order.ptr;
+    b.order_next = ctx->d_w_order_next.ptr;
+    b.node_of = ctx->d_w_node_of.ptr;
+    b.node_of_next = ctx->d_w_node_of_next.ptr;
+    b.flags = ctx->d_w_flags.ptr;
+    b.scan = ctx->d_w_scan.ptr;
+    b.items = ctx->d_w_items.ptr;
+    b.items_next = ctx->d_w_items_next.ptr;
+    b.bins = ctx->d_w_bins.ptr;
+    b.items_capacity = (int)items_cap;
+    b.pairs_capacity = (int)pairs_cap;
+    b.counters = ctx->d_w_counters.ptr;
+    b.root_acc = ctx->d_w_root_acc.ptr;
+    b.fnodes = ctx->d_fnodes.ptr;
+    b.ftris = ctx->d_ftris.ptr;
+    b.fnormals = ctx->d_fnormals.ptr;
+
+    const unsigned long long launches_before = ctx->ex.launches;
+    CU(ctx, cudaEventRecord(ctx->ev0, ctx->ex.stream));
+    WReport rep{};
+    int rc = run_build_wbvh(ctx->ex, b, &rep);
+    if (rc == 0 && rep.levels + 2 > kStackSize) {  // deeper than the traversal stack: rebuild balanced (median splits)
+        b.force_median = 1;
+        rc = run_build_wbvh(ctx->ex, b, &rep);
     }
-    return check_exec(ctx, "tlas upload");
+    CU(ctx, cudaEventRecord(ctx->ev1, ctx->ex.stream));
+    CU(ctx, cudaStreamSynchronize(ctx->ex.stream));
+    if (int e = check_exec(ctx, "world bvh build")) return e;
+    if (rc != 0) return fail(ctx, CAVEPT_ERR_CAPACITY, "world BVH build failed (bits %d)", rep.error_bits);
+    if (rep.levels + 2 > kStackSize) return fail(ctx, CAVEPT_ERR_CAPACITY, "world BVH depth %d exceeds the traversal stack (%d)", rep.levels, kStackSize);
+    float ms = 0.0f;
+    CU(ctx, cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1));
+    ctx->stats.last_fast_build_ms = ms;
+    ctx->stats.fast_build_levels = rep.levels;
+    ctx->stats.fast_build_launches = (int)(ctx->ex.launches - launches_before);
+    ctx->n_pairs = rep.n_pairs;
+    ctx->root_ref = rep.root_ref;
+    ctx->fast_levels = rep.levels;
+    ctx->stats.fast_node_count = 2 * rep.n_pairs;
+    return CAVEPT_OK;
 }
 
 int build_all(cavept_ctx* ctx) {
@@ -228,6 +294,18 @@ int build_all(cavept_ctx* ctx) {
     CU(ctx, ctx->d_vert_off.reserve(n_built + 1));
     ctx->ex.upload(ctx->d_tri_off.ptr, tri_off.data(), tri_off.size() * sizeof(int));
     ctx->ex.upload(ctx->d_vert_off.ptr, vert_off.data(), vert_off.size() * sizeof(int));
+
+    // raw -> reference layouts
+    launch_assemble_vertices(ctx->ex, ctx->d_raw_pos.ptr, ctx->d_raw_nrm.ptr, ctx->d_vertices.ptr, ctx->n_verts);
+    launch_assemble_indices(ctx->ex, ctx->d_raw_idx.ptr, ctx->d_tri_off.ptr, ctx->d_vert_off.ptr, n_built, ctx->d_indices.ptr, T);
+    ctx->nodes_resident = false;
+    ctx->stats.last_build_ms = 0.0f;
+    ctx->stats.build_levels = 0;
+    ctx->stats.build_launches = 0;
+    if (ctx->cfg.bvh_mode != CAVEPT_BVH_PARITY) {  // production tree only: no reference-layout GpuPtBvh array
+        CU(ctx, cudaStreamSynchronize(ctx->ex.stream));
+        return check_exec(ctx, "scene assembly");
+    }
 
     const size_t items_cap = (size_t)std::max(T, n_built) + 2;
     const size_t bins_cap = (size_t)T / 5 + (size_t)n_built + 2;
@@ -250,10 +328,6 @@ int build_all(cavept_ctx* ctx) {
     CU(ctx, ctx->d_node_parent.reserve(n_nodes));
     CU(ctx, ctx->d_node_count.reserve(n_nodes));
     ctx->ex.scan_tmp = ctx->d_scan_tmp.ptr;
-
-    // raw -> reference layouts
-    launch_assemble_vertices(ctx->ex, ctx->d_raw_pos.ptr, ctx->d_raw_nrm.ptr, ctx->d_vertices.ptr, ctx->n_verts);
-    launch_assemble_indices(ctx->ex, ctx->d_raw_idx.ptr, ctx->d_tri_off.ptr, ctx->d_vert_off.ptr, n_built, ctx->d_indices.ptr, T);
 
     BuildArrays a{};
     a.vertices = ctx->d_vertices.ptr;
@@ -292,44 +366,13 @@ int build_all(cavept_ctx* ctx) {
                     (report.error_bits & BUILD_ERR_BAD_AREA) ? " zero-area" : "", (report.error_bits & BUILD_ERR_BINS) ? " bins" : "");
     }
 
-    // production layout
-    CU(ctx, ctx->d_is_pair.reserve(n_nodes));
-    CU(ctx, ctx->d_pair_rank.reserve((size_t)n_nodes + 1));
-    CU(ctx, ctx->d_leaf_tris.reserve(n_nodes));
-    CU(ctx, ctx->d_tri_base.reserve((size_t)n_nodes + 1));
-    CU(ctx, ctx->d_ftris.reserve(T));
-    CU(ctx, ctx->d_fnormals.reserve(T));
-    CU(ctx, ctx->d_mesh_root_ref.reserve(n_built));
-    // pairs <= T/2 .. generous bound: every kept node is a reference node; + roots + TLAS (2*instances)
-    CU(ctx, ctx->d_fnodes.reserve((size_t)n_nodes + n_built + 2 * ctx->instances.size() + 8));
-    CompactArrays c{};
-    c.nodes = ctx->d_nodes.ptr;
-    c.node_parent = ctx->d_node_parent.ptr;
-    c.node_count = ctx->d_node_count.ptr;
-    c.n_nodes = n_nodes;
-    c.vertices = ctx->d_vertices.ptr;
-    c.indices = ctx->d_indices.ptr;
-    c.is_pair = ctx->d_is_pair.ptr;
-    c.pair_rank = ctx->d_pair_rank.ptr;
-    c.leaf_tris = ctx->d_leaf_tris.ptr;
-    c.tri_base = ctx->d_tri_base.ptr;
-    c.fnodes = ctx->d_fnodes.ptr;
-    c.ftris = ctx->d_ftris.ptr;
-    c.fnormals = ctx->d_fnormals.ptr;
-    c.mesh_root_ref = ctx->d_mesh_root_ref.ptr;
-    ctx->n_pairs = run_compact_layout(ctx->ex, c);
-    ctx->mesh_root_ref.resize(n_built);
-    ctx->ex.download(ctx->mesh_root_ref.data(), ctx->d_mesh_root_ref.ptr, sizeof(int) * (size_t)n_built);
-    CU(ctx, cudaEventRecord(ctx->ev2, ctx->ex.stream));
     CU(ctx, cudaStreamSynchronize(ctx->ex.stream));
-    if (int e = check_exec(ctx, "compact layout")) return e;
-    float ms_build = 0.0f, ms_compact = 0.0f;
+    float ms_build = 0.0f;
     CU(ctx, cudaEventElapsedTime(&ms_build, ctx->ev0, ctx->ev1));
-    CU(ctx, cudaEventElapsedTime(&ms_compact, ctx->ev1, ctx->ev2));
     ctx->stats.last_build_ms = ms_build;
-    ctx->stats.last_compact_ms = ms_compact;
     ctx->stats.build_levels = report.levels;
     ctx->stats.build_launches = (int)(ctx->ex.launches - launches_before);
+    ctx->nodes_resident = true;
     return CAVEPT_OK;
 }
 
@@ -372,14 +415,16 @@ CAVEPT_API void cavept_destroy(cavept_ctx* ctx) {
     cudaSetDevice(ctx->device);
     if (ctx->ex.stream) cudaStreamSynchronize(ctx->ex.stream);
     ctx->d_vertices.release(); ctx->d_indices.release(); ctx->d_nodes.release(); ctx->d_meshes.release(); ctx->d_materials.release();
-    ctx->d_fnodes.release(); ctx->d_ftris.release(); ctx->d_fnormals.release(); ctx->d_mesh_root_ref.release(); ctx->d_inst_root.release();
+    ctx->d_fnodes.release(); ctx->d_ftris.release(); ctx->d_fnormals.release(); ctx->d_inst_prim_off.release(); ctx->d_inst_tri_off.release();
+    ctx->d_prim_bmin.release(); ctx->d_prim_bmax.release(); ctx->d_w_order.release(); ctx->d_w_order_next.release(); ctx->d_w_node_of.release();
+    ctx->d_w_node_of_next.release(); ctx->d_w_scan.release(); ctx->d_w_counters.release(); ctx->d_w_flags.release(); ctx->d_w_items.release();
+    ctx->d_w_items_next.release(); ctx->d_w_bins.release(); ctx->d_w_root_acc.release();
     ctx->d_raw_pos.release(); ctx->d_raw_nrm.release(); ctx->d_raw_idx.release(); ctx->d_tri_off.release(); ctx->d_vert_off.release();
     ctx->d_tri_bmin.release(); ctx->d_tri_bmax.release(); ctx->d_tri_centroid.release();
     ctx->d_order.release(); ctx->d_order_next.release(); ctx->d_node_of.release(); ctx->d_node_of_next.release();
     ctx->d_scan.release(); ctx->d_scan_tmp.release(); ctx->d_counters.release(); ctx->d_flags.release();
     ctx->d_items.release(); ctx->d_items_next.release(); ctx->d_accum_items.release(); ctx->d_bins.release();
-    ctx->d_node_parent.release(); ctx->d_node_count.release(); ctx->d_is_pair.release(); ctx->d_pair_rank.release();
-    ctx->d_leaf_tris.release(); ctx->d_tri_base.release();
+    ctx->d_node_parent.release(); ctx->d_node_count.release();
     ctx->d_accum.release(); ctx->d_tone.release(); ctx->d_tone8.release(); ctx->d_stats.release();
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
@@ -464,12 +509,11 @@ CAVEPT_API int cavept_upload_scene(cavept_ctx* ctx, const cavept_mesh* meshes, i
     if (int e = check_exec(ctx, "scene upload")) return e;
     if (int e = build_all(ctx)) return e;
     if (int e = rebuild_instance_arrays(ctx)) return e;
-    if (int e = rebuild_tlas(ctx)) return e;
+    if (int e = build_world(ctx)) return e;
     ctx->scene_resident = true;
     ctx->dirty = true;
     ctx->stats.triangle_count = ctx->n_tris;
     ctx->stats.node_count = ctx->n_nodes;
-    ctx->stats.fast_node_count = ctx->n_fast_nodes;
     ctx->stats.instance_count = instance_count;
     return CAVEPT_OK;
 }
@@ -484,7 +528,7 @@ CAVEPT_API int cavept_update_instances(cavept_ctx* ctx, const cavept_instance* i
     if (int e = select_device(ctx)) return e;
     for (int i = 0; i < instance_count; ++i) std::memcpy(ctx->instances[i].transform, instances[i].transform, sizeof(float) * 16);
     if (int e = rebuild_instance_arrays(ctx)) return e;
-    if (int e = rebuild_tlas(ctx)) return e;
+    if (int e = build_world(ctx)) return e;
     ctx->dirty = true;  // SCENE_DIRTY_WORLD
     return CAVEPT_OK;
 }
@@ -512,7 +556,7 @@ CAVEPT_API int cavept_rebuild_mesh(cavept_ctx* ctx, int mesh, const float* posit
     ctx->scene_resident = false;
     if (int e = build_all(ctx)) return e;  // all meshes share one level-synchronous pass
     if (int e = rebuild_instance_arrays(ctx)) return e;
-    if (int e = rebuild_tlas(ctx)) return e;
+    if (int e = build_world(ctx)) return e;
     ctx->scene_resident = true;
     ctx->dirty = true;
     return CAVEPT_OK;
@@ -521,6 +565,7 @@ CAVEPT_API int cavept_rebuild_mesh(cavept_ctx* ctx, int mesh, const float* posit
 CAVEPT_API int cavept_get_mesh_bvh(cavept_ctx* ctx, int mesh, void* out, int capacity_nodes) {
     if (!ctx || !out) return -CAVEPT_ERR_INVALID_ARG;
     if (!ctx->scene_resident || mesh < 0 || mesh >= (int)ctx->meshes.size() || ctx->meshes[mesh].built < 0) return -fail(ctx, CAVEPT_ERR_NOT_READY, "mesh %d is not resident", mesh);
+    if (!ctx->nodes_resident) return -fail(ctx, CAVEPT_ERR_NOT_READY, "the reference-layout BVH is only built in CAVEPT_BVH_PARITY mode");
     if (select_device(ctx)) return -CAVEPT_ERR_CUDA;
     const MeshRecord& rec = ctx->meshes[mesh];
     const int n = 2 * rec.tri_count - 1;
@@ -555,7 +600,10 @@ CAVEPT_API int cavept_get_scene_arrays(cavept_ctx* ctx, void* v, void* i, void* 
     if (int e = select_device(ctx)) return e;
     if (v) ctx->ex.download(v, ctx->d_vertices.ptr, (size_t)ctx->n_verts * sizeof(GpuPtVertex));
     if (i) ctx->ex.download(i, ctx->d_indices.ptr, (size_t)ctx->n_tris * sizeof(GpuPtIndex));
-    if (b) ctx->ex.download(b, ctx->d_nodes.ptr, (size_t)ctx->n_nodes * sizeof(GpuPtBvh));
+    if (b) {
+        if (!ctx->nodes_resident) return fail(ctx, CAVEPT_ERR_NOT_READY, "the reference-layout BVH is only built in CAVEPT_BVH_PARITY mode");
+        ctx->ex.download(b, ctx->d_nodes.ptr, (size_t)ctx->n_nodes * sizeof(GpuPtBvh));
+    }
     if (m) ctx->ex.download(m, ctx->d_meshes.ptr, ctx->gpu_meshes.size() * sizeof(GpuPtMesh));
     if (mat) ctx->ex.download(mat, ctx->d_materials.ptr, ctx->gpu_materials.size() * sizeof(GpuPtMaterial));
     return check_exec(ctx, "scene read-back");
@@ -582,6 +630,7 @@ CAVEPT_API int cavept_render(cavept_ctx* ctx, int first_frame_index, int n_frame
     if (!ctx) return CAVEPT_ERR_INVALID_ARG;
     if (n_frames <= 0) return fail(ctx, CAVEPT_ERR_INVALID_ARG, "n_frames must be positive");
     if (!cavept_is_active(ctx)) return fail(ctx, CAVEPT_ERR_NOT_READY, "path tracer not active (mode INTERACTIVE and a resident scene are required)");
+    if (ctx->cfg.trace_mode == CAVEPT_TRACE_REFERENCE_WALK && !ctx->nodes_resident) return fail(ctx, CAVEPT_ERR_NOT_READY, "CAVEPT_TRACE_REFERENCE_WALK needs the reference-layout BVH (CAVEPT_BVH_PARITY)");
     if (int e = select_device(ctx)) return e;
     TraceParams p{};
     p.vertices = ctx->d_vertices.ptr;
@@ -593,8 +642,7 @@ CAVEPT_API int cavept_render(cavept_ctx* ctx, int first_frame_index, int n_frame
     p.fnodes = ctx->d_fnodes.ptr;
     p.ftris = ctx->d_ftris.ptr;
     p.fnormals = ctx->d_fnormals.ptr;
-    p.inst_fast_root = ctx->d_inst_root.ptr;
-    p.tlas_root = ctx->tlas_root;
+    p.root_ref = ctx->root_ref;
     std::memcpy(p.cam_pos, ctx->cam_pos, 12);
     std::memcpy(p.cam_right, ctx->cam_right, 12);
     std::memcpy(p.cam_up, ctx->cam_up, 12);

@@ -204,4 +204,49 @@ CV_D void cv_atomic_add_u64(unsigned long long* p, unsigned long long v) {
 #endif
 }
 
+// ---- warp-aggregated atomics ------------------------------------------------------------
+// Lanes of a warp that pass the same key combine their operands with one redux.sync and a
+// single lane issues the atomic: up to 32x fewer atomics on the hot addresses of the
+// builders' top levels.  The emulator runs a warp of one.
+struct CvGroup {
+    unsigned mask;
+    bool leader;
+};
+CV_D CvGroup cv_group_by(int key) {
+    CvGroup g;
+#if defined(__CUDA_ARCH__)
+    g.mask = __match_any_sync(__activemask(), key);
+    g.leader = (__ffs(g.mask) - 1) == (int)(threadIdx.x & 31u);
+#else
+    (void)key;
+    g.mask = 1u;
+    g.leader = true;
+#endif
+    return g;
+}
+CV_D void cv_group_min_u32(const CvGroup& g, uint32_t* p, uint32_t v) {
+#if defined(__CUDA_ARCH__)
+    v = __reduce_min_sync(g.mask, v);
+    if (g.leader) atomicMin(p, v);
+#else
+    if (v < *p) *p = v;
+#endif
+}
+CV_D void cv_group_max_u32(const CvGroup& g, uint32_t* p, uint32_t v) {
+#if defined(__CUDA_ARCH__)
+    v = __reduce_max_sync(g.mask, v);
+    if (g.leader) atomicMax(p, v);
+#else
+    if (v > *p) *p = v;
+#endif
+}
+CV_D void cv_group_add_i32(const CvGroup& g, int* p, int v) {
+#if defined(__CUDA_ARCH__)
+    v = __reduce_add_sync(g.mask, v);
+    if (g.leader) atomicAdd(p, v);
+#else
+    *p += v;
+#endif
+}
+
 }  // namespace cavept

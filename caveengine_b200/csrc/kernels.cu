@@ -183,7 +183,7 @@ void launch_assemble_indices(CudaExec& ex, const uint32_t* raw_indices, const in
 int run_build_bvh_parity(CudaExec& ex, BuildArrays a, const int* tri_off_host, const int* d_tri_off, int n_meshes, BuildItem* host_scratch, BuildReport* report) {
     return build_bvh_parity(ex, a, tri_off_host, d_tri_off, n_meshes, host_scratch, report);
 }
-int run_compact_layout(CudaExec& ex, CompactArrays c) { return run_compact(ex, c); }
+int run_build_wbvh(CudaExec& ex, WBuild b, WReport* report) { return build_wbvh(ex, b, report); }
 
 // ---- path-trace pass ------------------------------------------------------------------
 // Block = 128 threads = a 16 x 8 pixel tile; each warp covers an 8 x 4 sub-tile so the

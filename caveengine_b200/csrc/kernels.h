@@ -4,8 +4,8 @@
 #include <cuda_runtime.h>
 
 #include "bvh_parity_driver.h"
-#include "compact_body.h"
 #include "trace_body.h"
+#include "wbvh_body.h"
 
 namespace cavept {
 
@@ -35,7 +35,7 @@ void launch_assemble_vertices(CudaExec& ex, const float* positions, const float*
 void launch_assemble_indices(CudaExec& ex, const uint32_t* raw_indices, const int* tri_off, const int* vert_off, int n_meshes, GpuPtIndex* out, int n_tris);
 
 int run_build_bvh_parity(CudaExec& ex, BuildArrays a, const int* tri_off_host, const int* d_tri_off, int n_meshes, BuildItem* host_scratch, BuildReport* report);
-int run_compact_layout(CudaExec& ex, CompactArrays c);
+int run_build_wbvh(CudaExec& ex, WBuild b, WReport* report);
 
 void launch_trace(CudaExec& ex, const TraceParams& p, bool fast, bool count_visits);
 void launch_tonemap_rgba8(CudaExec& ex, const F4* accum, unsigned char* out, int n_pixels);

@@ -32,7 +32,7 @@ struct alignas(16) FastNode {
 };
 static_assert(sizeof(FastNode) == 32, "FastNode");
 
-// Pre-gathered triangle: 3 x float4; w lanes carry the scene-global triangle id and padding.
+// Pre-gathered triangle: 3 x float4 world-space vertices; v0.w = instance, v1.w = scene-global triangle id.
 struct alignas(16) FastTri {
     F4 v0, v1, v2;
 };
@@ -49,9 +49,8 @@ struct TraceParams {
     // production layout
     const FastNode* fnodes;
     const FastTri* ftris;
-    const FastTri* fnormals;    // per FastTri slot: the three vertex normals (shading)
-    const int* inst_fast_root;  // per instance: node reference of its mesh's root
-    int tlas_root;              // node reference of the TLAS root
+    const FastTri* fnormals;  // per FastTri slot: the three vertex normals (mesh space), v0.w = instance
+    int root_ref;             // node reference of the root
     // PerFrameConstantBuffer (cbuffer.hlsl.h:193-207)
     float cam_pos[3], cam_right[3], cam_up[3], cam_fwd[3];
     float cam_distance;  // tan(c_cameraFovDegree * PI / 180), path_tracer.cs.glsl:31-32
@@ -186,15 +185,13 @@ CV_D Hit hit_scene_reference(const TraceParams& p, Ray& ray, unsigned long long*
 }
 
 // ---- production traversal ---------------------------------------------------------------
-// Node references (one int): interior = index of the child pair (children at ref, ref+1);
-// leaf = sign bit | (count-1) << 29 | first FastTri slot inside a BLAS, sign bit | instance
-// index inside the TLAS.  A node's own reference is stored in its record, so one 64-byte
-// fetch of a sibling pair yields both boxes and both references.
-constexpr int kRefSentinel = 0x7fffffff;  // bottom of the stack
-constexpr int kRefDeferredPop = 0x7ffffffe;
-CV_HD bool ref_is_interior(int r) { return (uint32_t)r < (uint32_t)kRefDeferredPop; }
+// One world-space tree over every (instance, triangle) pair (wbvh_body.h).  Node references
+// (one int): interior = index of the child pair's first record (children at ref, ref + 1);
+// leaf = sign bit | (count - 1) << 29 | first FastTri slot.  A node's own reference is stored
+// in its record, so one 64-byte fetch of a sibling pair yields both boxes and both references.
+constexpr int kRefSentinel = 0x7fffffff;  // bottom of the stack: nothing left to traverse
+CV_HD bool ref_is_interior(int r) { return (uint32_t)r < (uint32_t)kRefSentinel; }
 CV_HD int make_leaf_ref(int first_slot, int count) { return (int)(0x80000000u | ((uint32_t)(count - 1) << 29) | (uint32_t)first_slot); }
-CV_HD int make_instance_ref(int instance) { return (int)(0x80000000u | (uint32_t)instance); }
 
 #if defined(__CUDA_ARCH__)
 #define CV_WARP_ANY(pred) __any_sync(0xffffffffu, (pred))
@@ -204,117 +201,105 @@ CV_HD int make_instance_ref(int instance) { return (int)(0x80000000u | (uint32_t
 #define CV_WARP_COUNT(pred) ((pred) ? 1 : 0)
 #endif
 
-// Slab test of the production traversal.  Same interval logic as HitBvh (:133-149) with
-// two result-neutral changes: boxes entirely behind the origin are rejected, and the exit
-// distance is widened by 2 ulp so that rounding differences to the reference's
-// (min - o) * inv form can only ever add candidate triangles, never lose one.
-CV_HD bool slab_fast(F3 inv, F3 oinv, float ray_t, const FastNode& n, float& t_entry) {
-    const float ax = cv_fma(n.mn[0], inv.x, oinv.x), bx = cv_fma(n.mx[0], inv.x, oinv.x);
-    const float ay = cv_fma(n.mn[1], inv.y, oinv.y), by = cv_fma(n.mx[1], inv.y, oinv.y);
-    const float az = cv_fma(n.mn[2], inv.z, oinv.z), bz = cv_fma(n.mx[2], inv.z, oinv.z);
-    const float tmin = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fminf(az, bz));
-    const float tmax = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fmaxf(az, bz)) * 1.0000003f;
-    t_entry = tmin;
-    return (tmin <= tmax) && (ray_t > tmin) && (tmax >= 0.0f);
-}
-
-// Per-lane traversal state of the production kernel.
+// Per-lane traversal state of the production kernel.  The stack lives in shared memory,
+// lane-strided ([depth][thread]), so any mix of depths is bank-conflict free.
 struct Walk {
-    int* stack;     // lane-strided: entry k of this lane is stack[k * stride]
+    int* stack;
     int stride;
-    int sp;         // entry 0 holds the sentinel
-    int ref;        // current node reference
-    int leaf;       // postponed BLAS leaf (0 = none)
-    int instance;   // -1 while in the TLAS
-    int blas_sp;    // stack depth at instance entry (0 = not inside an instance)
-    F3 o, d, inv, oinv;  // active ray: world ray in the TLAS, mesh-local ray inside an instance
-    int hit_instance, hit_slot;
+    int sp;          // entry 0 holds the sentinel
+    int ref;         // node reference being processed (interior, leaf, or the sentinel)
+    int q0, q1;      // postponed leaves (0 = empty); q0 is the older
+    F3 inv, oinv;    // 1/d and -o/d of the segment's ray
+    int hit_slot;
     float hit_u, hit_v;
 };
 
-CV_D void walk_set_ray(Walk& w, F3 o, F3 d) {
-    w.o = o;
-    w.d = d;
-    w.inv = recip3(d);
-    w.oinv = f3(-(o.x * w.inv.x), -(o.y * w.inv.y), -(o.z * w.inv.z));
+// 1/d for the slab test.  Not IEEE-critical: boxes are padded (wbvh_body.h) and a zero
+// component is replaced by a huge finite slope so that 0 * inf never makes a NaN.
+CV_HD float slab_recip(float d) {
+    const float a = fabsf(d) > 1e-30f ? d : (f2u(d) >> 31 ? -1e-30f : 1e-30f);
+#if defined(__CUDA_ARCH__)
+    return __frcp_rn(a);
+#else
+    return 1.0f / a;
+#endif
 }
 
 CV_D void walk_begin(const TraceParams& p, Walk& w, const Ray& ray) {
     w.stack[0] = kRefSentinel;
     w.sp = 1;
-    w.ref = p.tlas_root;
-    w.leaf = 0;
-    w.instance = -1;
-    w.blas_sp = 0;
-    w.hit_instance = -1;
+    w.ref = p.root_ref;
+    w.q0 = 0;
+    w.q1 = 0;
     w.hit_slot = -1;
     w.hit_u = 0.0f;
     w.hit_v = 0.0f;
-    walk_set_ray(w, ray.origin, ray.direction);
+    w.inv = f3(slab_recip(ray.direction.x), slab_recip(ray.direction.y), slab_recip(ray.direction.z));
+    w.oinv = f3(-(ray.origin.x * w.inv.x), -(ray.origin.y * w.inv.y), -(ray.origin.z * w.inv.z));
 }
 
-// Pop the next reference.  Leaving an instance restores the world ray; that is postponed
-// (kRefDeferredPop) while a leaf of this instance is still waiting to be intersected.
-CV_D void walk_pop(Walk& w, const Ray& ray) {
-    if (w.sp == w.blas_sp) {
-        if (w.leaf < 0) {
-            w.ref = kRefDeferredPop;
-            return;
-        }
-        walk_set_ray(w, ray.origin, ray.direction);
-        w.instance = -1;
-        w.blas_sp = 0;
-    }
-    w.ref = w.stack[(--w.sp) * w.stride];
-}
-
-template<bool kCount>
-CV_D void walk_intersect_leaf(const TraceParams& p, Walk& w, int leaf_ref, Ray& ray, unsigned long long* cnt) {
-    const int first = leaf_ref & 0x1fffffff;
-    const int count = ((leaf_ref >> 29) & 3) + 1;
-    for (int k = 0; k < count; ++k) {
-        const FastTri tr = p.ftris[first + k];
-        if (kCount) ++cnt[2];
-        float u, v;
-        if (hit_triangle(f3(tr.v0.x, tr.v0.y, tr.v0.z), f3(tr.v1.x, tr.v1.y, tr.v1.z), f3(tr.v2.x, tr.v2.y, tr.v2.z), w.o, w.d, ray.t, u, v)) {
-            w.hit_slot = first + k;
-            w.hit_instance = w.instance;
-            w.hit_u = u;
-            w.hit_v = v;
-        }
-    }
-}
-
-// One interior step (or instance entry) for a lane whose reference is actionable.
-template<bool kCount>
-CV_D void walk_step(const TraceParams& p, Walk& w, const Ray& ray, unsigned long long* cnt) {
-    if (w.ref < 0) {  // TLAS leaf: enter the instance (HitScene :160-166)
-        w.instance = w.ref & 0x7fffffff;
-        const GpuPtMesh& mesh = p.meshes[w.instance];
-        walk_set_ray(w, mat_mul(mesh.transformInv, ray.origin, 1.0f), mat_mul(mesh.transformInv, ray.direction, 0.0f));
-        w.blas_sp = w.sp;
-        w.ref = p.inst_fast_root[w.instance];
-    } else {
-        const FastNode c0 = p.fnodes[w.ref];
-        const FastNode c1 = p.fnodes[w.ref + 1];
-        if (kCount) cnt[1] += 2;
-        float t0, t1;
-        const bool h0 = slab_fast(w.inv, w.oinv, ray.t, c0, t0);
-        const bool h1 = slab_fast(w.inv, w.oinv, ray.t, c1, t1);
-        if (h0 && h1) {
-            const bool swap = t1 < t0;
-            w.ref = swap ? c1.a : c0.a;
-            w.stack[(w.sp++) * w.stride] = swap ? c0.a : c1.a;
-        } else if (h0 || h1) {
-            w.ref = h0 ? c0.a : c1.a;
-        } else {
-            walk_pop(w, ray);
-        }
-    }
-    // postpone the first BLAS leaf and keep descending while other lanes still search
-    if (w.ref < 0 && w.instance >= 0 && w.leaf == 0 && w.sp > w.blas_sp) {
-        w.leaf = w.ref;
+// A leaf held in `ref` moves to the queue when there is room; the lane pops its next node.
+CV_D void walk_park_leaf(Walk& w) {
+    if (w.ref < 0 && w.q1 == 0) {
+        if (w.q0 == 0) w.q0 = w.ref; else w.q1 = w.ref;
         w.ref = w.stack[(--w.sp) * w.stride];
+    }
+}
+
+// One interior step: fetch the sibling pair, slab-test both boxes against [0, ray.t], descend
+// into the nearer hit child and push the other.  Same interval logic as HitBvh (:133-149);
+// boxes entirely behind the origin or beyond the current hit are rejected.
+template<bool kCount>
+CV_D void walk_step(const TraceParams& p, Walk& w, float ray_t, unsigned long long* cnt) {
+    const F4* q = reinterpret_cast<const F4*>(p.fnodes + w.ref);
+    const F4 a0 = q[0], a1 = q[1], b0 = q[2], b1 = q[3];
+    if (kCount) cnt[1] += 2;
+    const float ax = cv_fma(a0.x, w.inv.x, w.oinv.x), bx = cv_fma(a1.x, w.inv.x, w.oinv.x);
+    const float ay = cv_fma(a0.y, w.inv.y, w.oinv.y), by = cv_fma(a1.y, w.inv.y, w.oinv.y);
+    const float az = cv_fma(a0.z, w.inv.z, w.oinv.z), bz = cv_fma(a1.z, w.inv.z, w.oinv.z);
+    const float cx = cv_fma(b0.x, w.inv.x, w.oinv.x), dx = cv_fma(b1.x, w.inv.x, w.oinv.x);
+    const float cy = cv_fma(b0.y, w.inv.y, w.oinv.y), dy = cv_fma(b1.y, w.inv.y, w.oinv.y);
+    const float cz = cv_fma(b0.z, w.inv.z, w.oinv.z), dz = cv_fma(b1.z, w.inv.z, w.oinv.z);
+    const float n0 = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), 0.0f));
+    const float f0 = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), ray_t));
+    const float n1 = fmaxf(fmaxf(fminf(cx, dx), fminf(cy, dy)), fmaxf(fminf(cz, dz), 0.0f));
+    const float f1 = fminf(fminf(fmaxf(cx, dx), fmaxf(cy, dy)), fminf(fmaxf(cz, dz), ray_t));
+    const bool h0 = n0 <= f0, h1 = n1 <= f1;
+    const int r0 = (int)f2u(a0.w), r1 = (int)f2u(b0.w);
+    const bool second_first = h1 && (!h0 || n1 < n0);
+    if (h0 && h1) {
+        w.stack[w.sp * w.stride] = second_first ? r0 : r1;
+        ++w.sp;
+    }
+    if (h0 || h1) {
+        w.ref = second_first ? r1 : r0;
+    } else {
+        w.ref = w.stack[(--w.sp) * w.stride];
+    }
+}
+
+// One triangle of the oldest postponed leaf.  World-space vertices: for an identity
+// instance this is HitScene's arithmetic bit for bit; for a transformed instance the
+// reference intersects in mesh space with the inverse-transformed ray (:160-166), which is
+// the same (t, u, v) up to fp32 rounding of the transform.
+template<bool kCount>
+CV_D void walk_test_triangle(const TraceParams& p, Walk& w, const Ray& ray, float& ray_t, unsigned long long* cnt) {
+    const int leaf = w.q0;
+    const int slot = leaf & 0x1fffffff;
+    const int more = (leaf >> 29) & 3;
+    const FastTri tr = p.ftris[slot];
+    if (kCount) ++cnt[2];
+    float u, v;
+    if (hit_triangle(f3(tr.v0.x, tr.v0.y, tr.v0.z), f3(tr.v1.x, tr.v1.y, tr.v1.z), f3(tr.v2.x, tr.v2.y, tr.v2.z), ray.origin, ray.direction, ray_t, u, v)) {
+        w.hit_slot = slot;
+        w.hit_u = u;
+        w.hit_v = v;
+    }
+    if (more > 0) {
+        w.q0 = make_leaf_ref(slot + 1, more);
+    } else {
+        w.q0 = w.q1;
+        w.q1 = 0;
     }
 }
 
@@ -427,15 +412,18 @@ CV_D unsigned int body_trace_pixel_reference(const TraceParams& p, int x, int y,
     return segments;
 }
 
-// Production kernel body: ONE loop per warp in which every lane is either descending the
-// BVH, intersecting a leaf, or shading -- whatever sample and bounce it is on.
-//   phase A  interior steps; a lane that reaches a leaf postpones it and keeps descending
-//            while any other lane is still searching (speculative while-while traversal);
-//   phase B  every lane intersects its postponed / current leaf;
-//   phase C  lanes whose traversal finished shade and start their next segment -- done in
-//            batches (>= kShadeBatch lanes, or nobody left traversing) so the shading code
-//            is not replayed for one lane at a time.
-// Lanes of a warp never wait for the slowest ray of a segment, only for a shading batch.
+// Production kernel body: ONE loop per warp in which every lane is descending the tree,
+// has triangles waiting, or has finished its segment -- whatever sample and bounce it is on.
+// Each trip of the loop the warp votes and runs the unit of work most lanes can take part in:
+//   A  one interior step.  A lane that reaches a leaf parks it (two-entry queue) and keeps
+//      descending -- speculative traversal: the pending triangles can only shorten ray.t, so
+//      the extra nodes visited never change the closest hit;
+//   B  one triangle of the oldest parked leaf, when too few lanes can still step;
+//   C  shade + next segment (or next sample) for lanes whose traversal is complete, in batches
+//      of >= kShadeBatch lanes so the long shading sequence is not replayed per lane.
+// The order in which ONE lane visits its nodes and triangles does not depend on its
+// neighbours, so images are deterministic.
+constexpr int kStepQuorum = 20;  // of 32: run A while at least this share of the live lanes can step
 constexpr int kShadeBatch = 8;
 
 template<bool kCount>
@@ -460,38 +448,32 @@ CV_D unsigned int body_trace_pixel_fast(const TraceParams& p, int x, int y, int*
     walk_begin(p, w, ray);
     if (!valid) w.ref = kRefSentinel;
     for (;;) {
-        // ---- phase A -------------------------------------------------------------------
-        for (;;) {
-            const bool can_step = ref_is_interior(w.ref) || (w.ref < 0 && w.instance < 0);
-            if (!CV_WARP_ANY(can_step && w.leaf == 0)) break;  // nobody is searching any more
-            if (can_step) walk_step<kCount>(p, w, ray, cnt);
-        }
-        // ---- phase B -------------------------------------------------------------------
-        if (w.leaf < 0) {
-            walk_intersect_leaf<kCount>(p, w, w.leaf, ray, cnt);
-            w.leaf = 0;
-        }
-        if (w.ref < 0 && w.instance >= 0) {
-            walk_intersect_leaf<kCount>(p, w, w.ref, ray, cnt);
-            walk_pop(w, ray);
-        } else if (w.ref == kRefDeferredPop) {
-            walk_pop(w, ray);
-        }
-        // ---- phase C -------------------------------------------------------------------
-        const bool need_shade = !done && w.ref == kRefSentinel && w.leaf == 0;
-        const int n_need = CV_WARP_COUNT(need_shade);
-        const int n_walking = CV_WARP_COUNT(!done && !need_shade);
-        if (need_shade && (n_need >= kShadeBatch || n_walking == 0)) {
+        walk_park_leaf(w);
+        const bool can_step = ref_is_interior(w.ref);
+        const bool has_tri = w.q0 != 0;
+        const bool need_shade = !done && !can_step && !has_tri && w.ref == kRefSentinel;
+        const int n_live = CV_WARP_COUNT(!done);
+        if (n_live == 0) break;
+        const int n_step = CV_WARP_COUNT(can_step);
+        const int n_tri = CV_WARP_COUNT(has_tri);
+        const int n_shade = CV_WARP_COUNT(need_shade);
+        if (n_step * 32 >= n_live * kStepQuorum || (n_step > 0 && n_tri == 0 && n_shade < kShadeBatch)) {
+            if (can_step) walk_step<kCount>(p, w, ray.t, cnt);
+        } else if (n_tri > 0) {
+            if (has_tri) walk_test_triangle<kCount>(p, w, ray, ray.t, cnt);
+        } else if (need_shade) {
             ++segments;
             const bool is_hit = w.hit_slot >= 0;
             F3 n1 = f3(0, 0, 0), n2 = n1, n3 = n1;
+            int instance = 0;
             if (is_hit) {
                 const FastTri nr = p.fnormals[w.hit_slot];
                 n1 = f3(nr.v0.x, nr.v0.y, nr.v0.z);
                 n2 = f3(nr.v1.x, nr.v1.y, nr.v1.z);
                 n3 = f3(nr.v2.x, nr.v2.y, nr.v2.z);
+                instance = (int)f2u(nr.v0.w);
             }
-            if (shade_hit(p, is_hit, w.hit_instance, n1, n2, n3, w.hit_u, w.hit_v, ray, seed, radiance, throughput, bounce)) {
+            if (shade_hit(p, is_hit, instance, n1, n2, n3, w.hit_u, w.hit_v, ray, seed, radiance, throughput, bounce)) {
                 F4 acc = p.accum[pix];
                 accumulate(acc, radiance, f == 0 && p.reset_first != 0);
                 p.accum[pix] = acc;
@@ -506,7 +488,6 @@ CV_D unsigned int body_trace_pixel_fast(const TraceParams& p, int x, int y, int*
             }
             if (!done) walk_begin(p, w, ray);
         }
-        if (!CV_WARP_ANY(!done)) break;
     }
     return segments;
 }

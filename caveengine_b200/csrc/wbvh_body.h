@@ -1,0 +1,496 @@
+// Production BVH builder: one world-space tree over every (instance, triangle) pair.
+//
+// The reference has no such structure: HitScene (cave/shader/shared_path_tracer.h:152-189)
+// loops over every mesh and walks each mesh's own tree.  The closest hit of that loop is
+// the closest hit over all (instance, triangle) pairs, so ONE tree over all pairs returns
+// the same hit while visiting far fewer nodes.  Triangles are
+// stored in world space: for an identity instance that is HitScene's arithmetic bit for bit;
+// for a transformed instance the reference intersects in mesh space with the
+// inverse-transformed ray (:160-166) -- the same (t, u, v) up to fp32 rounding of the transform.
+//
+// Construction is top-down binned SAH, level-synchronous (all nodes of a level in the same
+// launches), 16 bins on the axis of largest centroid extent:
+//   prim pass   world AABB of every pair, scene bounds + centroid bounds (atomics)
+//   per level   clear bins | bin (count, AABB, centroid bounds per bin) | split (SAH sweep,
+//               child boxes straight from the bins = the bottom-up AABB reduction is folded
+//               into the binning) | flag | exclusive scan | stable scatter
+//   emit        leaves are contiguous ranges of the final order: pre-gather 3 x float4
+//               positions and normals per slot
+// Nodes are the 32-byte FastNode records of trace_body.h, siblings adjacent.
+//
+// Boxes are padded by pad = 2^-20 * (largest |coordinate| in the scene) so that the
+// fused-multiply-add slab test of the tracer (walk_step, trace_body.h) is conservative.
+#pragma once
+#include "cv_common.h"
+#include "trace_body.h"
+
+namespace cavept {
+
+constexpr int kWBins = 16;
+constexpr int kWMedianDepth = 48;  // safety net: positional median splits below this depth
+
+struct WBin {
+    int count;
+    uint32_t mn[3], mx[3];    // ordered keys of the AABB
+    uint32_t cmn[3], cmx[3];  // ordered keys of the centroid bounds
+};
+struct WBins {
+    WBin b[kWBins];
+};
+
+struct WItem {
+    int start, count;  // segment of `order`
+    int pair;          // children go to fnodes[2*pair], fnodes[2*pair + 1]
+    int depth;
+    int axis;          // binning axis; -1: positional median split
+    float cmin, cscale;
+    int split;         // left child = bins [0, split]
+    int n_left;
+    int child_item[2];  // index of each child in the next level, -1 if it is a leaf
+    float box_mn[3], box_mx[3];
+    float cb_mn[3], cb_mx[3];
+};
+
+enum { WB_ERR_CAPACITY = 1 };
+
+struct WBuild {
+    // inputs: the reference-layout scene arrays
+    const GpuPtVertex* vertices;
+    const GpuPtIndex* indices;
+    const GpuPtMesh* instances;
+    const int* inst_prim_off;  // n_inst + 1
+    const int* inst_tri_off;   // per instance: scene-global index of its mesh's first triangle
+    int n_inst;
+    int n_prims;
+    float pad;
+    int force_median;
+    // per prim
+    F4* bmin;  // xyz world AABB min, w = bits of the scene-global triangle id
+    F4* bmax;  // xyz world AABB max, w = bits of the instance id
+    int* order;
+    int* order_next;
+    int* node_of;
+    int* node_of_next;
+    unsigned char* flags;
+    int* scan;
+    WItem* items;
+    WItem* items_next;
+    WBins* bins;
+    int items_capacity;
+    int pairs_capacity;
+    int* counters;       // [0] items emitted for the next level, [1] pairs allocated, [2] error bits
+    uint32_t* root_acc;  // [0..2] scene min keys, [3..5] max keys, [6..8] centroid min keys, [9..11] centroid max keys
+    // outputs
+    FastNode* fnodes;
+    FastTri* ftris;
+    FastTri* fnormals;
+};
+
+CV_HD int wb_find_instance(const int* off, int n, int p) {
+    int lo = 0, hi = n;
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (off[mid] <= p) lo = mid; else hi = mid;
+    }
+    return lo;
+}
+
+// world-space position of a mesh-space vertex (glm column-major world matrix)
+CV_HD F3 wb_world(const float* m, const float* v) {
+    return f3(m[0] * v[0] + m[4] * v[1] + m[8] * v[2] + m[12], m[1] * v[0] + m[5] * v[1] + m[9] * v[2] + m[13], m[2] * v[0] + m[6] * v[1] + m[10] * v[2] + m[14]);
+}
+
+// ---- prim pass ---------------------------------------------------------------------------
+CV_D void wb_body_prim(const WBuild& b, int p) {
+    if (p >= b.n_prims) return;
+    const int inst = wb_find_instance(b.inst_prim_off, b.n_inst, p);
+    const int tri = b.inst_tri_off[inst] + (p - b.inst_prim_off[inst]);
+    const float* m = b.instances[inst].transform;
+    const int* t = b.indices[tri].tri;
+    F3 mn = f3(CV_INF, CV_INF, CV_INF), mx = f3(-CV_INF, -CV_INF, -CV_INF);
+    for (int k = 0; k < 3; ++k) {
+        const F3 w = wb_world(m, b.vertices[t[k]].position);
+        mn = f3(fminf(mn.x, w.x), fminf(mn.y, w.y), fminf(mn.z, w.z));
+        mx = f3(fmaxf(mx.x, w.x), fmaxf(mx.y, w.y), fmaxf(mx.z, w.z));
+    }
+    F4 o;
+    o.x = mn.x; o.y = mn.y; o.z = mn.z; o.w = u2f((uint32_t)tri);
+    b.bmin[p] = o;
+    o.x = mx.x; o.y = mx.y; o.z = mx.z; o.w = u2f((uint32_t)inst);
+    b.bmax[p] = o;
+    const F3 c = 0.5f * (mn + mx);
+    const CvGroup g = cv_group_by(0);
+    cv_group_min_u32(g, &b.root_acc[0], ordered_key(mn.x));
+    cv_group_min_u32(g, &b.root_acc[1], ordered_key(mn.y));
+    cv_group_min_u32(g, &b.root_acc[2], ordered_key(mn.z));
+    cv_group_max_u32(g, &b.root_acc[3], ordered_key(mx.x));
+    cv_group_max_u32(g, &b.root_acc[4], ordered_key(mx.y));
+    cv_group_max_u32(g, &b.root_acc[5], ordered_key(mx.z));
+    cv_group_min_u32(g, &b.root_acc[6], ordered_key(c.x));
+    cv_group_min_u32(g, &b.root_acc[7], ordered_key(c.y));
+    cv_group_min_u32(g, &b.root_acc[8], ordered_key(c.z));
+    cv_group_max_u32(g, &b.root_acc[9], ordered_key(c.x));
+    cv_group_max_u32(g, &b.root_acc[10], ordered_key(c.y));
+    cv_group_max_u32(g, &b.root_acc[11], ordered_key(c.z));
+}
+
+// pad the boxes (b.pad is known once the scene bounds are), identity order, everything in item 0
+CV_D void wb_body_init(const WBuild& b, int p) {
+    if (p >= b.n_prims) return;
+    F4 mn = b.bmin[p], mx = b.bmax[p];
+    mn.x -= b.pad; mn.y -= b.pad; mn.z -= b.pad;
+    mx.x += b.pad; mx.y += b.pad; mx.z += b.pad;
+    b.bmin[p] = mn;
+    b.bmax[p] = mx;
+    b.order[p] = p;
+    b.node_of[p] = 0;
+}
+
+// ---- per level ----------------------------------------------------------------------------
+// thread j: bin j % 16 of item j / 16 is cleared; the first thread of an item also picks its axis
+CV_D void wb_body_prep(const WBuild& b, int j, int n_items) {
+    const int w = j / kWBins, k = j % kWBins;
+    if (w >= n_items) return;
+    WBin& bin = b.bins[w].b[k];
+    bin.count = 0;
+    for (int c = 0; c < 3; ++c) {
+        bin.mn[c] = 0xffffffffu;
+        bin.mx[c] = 0u;
+        bin.cmn[c] = 0xffffffffu;
+        bin.cmx[c] = 0u;
+    }
+    if (k != 0) return;
+    WItem& it = b.items[w];
+    const F3 ext = f3(it.cb_mx[0] - it.cb_mn[0], it.cb_mx[1] - it.cb_mn[1], it.cb_mx[2] - it.cb_mn[2]);
+    int axis = 0;
+    if (ext.y > comp(ext, axis)) axis = 1;
+    if (ext.z > comp(ext, axis)) axis = 2;
+    const float e = comp(ext, axis);
+    if (!(e > 0.0f) || b.force_median || it.depth >= kWMedianDepth) {
+        it.axis = -1;  // all centroids coincide (or the safety net): split the list in the middle
+        it.cmin = 0.0f;
+        it.cscale = 0.0f;
+    } else {
+        it.axis = axis;
+        it.cmin = it.cb_mn[axis];
+        it.cscale = cv_div((float)kWBins, e);
+    }
+}
+
+CV_HD int wb_bin_of(const WItem& it, F4 mn, F4 mx) {
+    const float c = it.axis == 0 ? 0.5f * (mn.x + mx.x) : (it.axis == 1 ? 0.5f * (mn.y + mx.y) : 0.5f * (mn.z + mx.z));
+    const int k = (int)((c - it.cmin) * it.cscale);
+    return k < 0 ? 0 : (k > kWBins - 1 ? kWBins - 1 : k);
+}
+
+CV_D void wb_body_bin(const WBuild& b, int i) {
+    if (i >= b.n_prims) return;
+    const int w = b.node_of[i];
+    if (w < 0) return;
+    const WItem& it = b.items[w];
+    if (it.axis < 0) return;
+    const int p = b.order[i];
+    const F4 mn = b.bmin[p], mx = b.bmax[p];
+    const int k = wb_bin_of(it, mn, mx);
+    WBin& bin = b.bins[w].b[k];
+    const F3 c = f3(0.5f * (mn.x + mx.x), 0.5f * (mn.y + mx.y), 0.5f * (mn.z + mx.z));
+    const CvGroup g = cv_group_by(w * kWBins + k);
+    cv_group_add_i32(g, &bin.count, 1);
+    cv_group_min_u32(g, &bin.mn[0], ordered_key(mn.x));
+    cv_group_min_u32(g, &bin.mn[1], ordered_key(mn.y));
+    cv_group_min_u32(g, &bin.mn[2], ordered_key(mn.z));
+    cv_group_max_u32(g, &bin.mx[0], ordered_key(mx.x));
+    cv_group_max_u32(g, &bin.mx[1], ordered_key(mx.y));
+    cv_group_max_u32(g, &bin.mx[2], ordered_key(mx.z));
+    cv_group_min_u32(g, &bin.cmn[0], ordered_key(c.x));
+    cv_group_min_u32(g, &bin.cmn[1], ordered_key(c.y));
+    cv_group_min_u32(g, &bin.cmn[2], ordered_key(c.z));
+    cv_group_max_u32(g, &bin.cmx[0], ordered_key(c.x));
+    cv_group_max_u32(g, &bin.cmx[1], ordered_key(c.y));
+    cv_group_max_u32(g, &bin.cmx[2], ordered_key(c.z));
+}
+
+struct WBox {
+    F3 mn, mx;
+};
+CV_HD WBox wb_empty() {
+    WBox r;
+    r.mn = f3(CV_INF, CV_INF, CV_INF);
+    r.mx = f3(-CV_INF, -CV_INF, -CV_INF);
+    return r;
+}
+CV_HD void wb_grow(WBox& a, F3 mn, F3 mx) {
+    a.mn = f3(fminf(a.mn.x, mn.x), fminf(a.mn.y, mn.y), fminf(a.mn.z, mn.z));
+    a.mx = f3(fmaxf(a.mx.x, mx.x), fmaxf(a.mx.y, mx.y), fmaxf(a.mx.z, mx.z));
+}
+CV_HD float wb_half_area(const WBox& a) {
+    const F3 e = a.mx - a.mn;
+    return e.x * e.y + e.y * e.z + e.z * e.x;
+}
+
+// one thread per item: SAH sweep over the 15 planes, children boxes from the bins, child
+// records written into this item's pair, interior children queued for the next level
+CV_D void wb_body_split(const WBuild& b, int w, int n_items) {
+    if (w >= n_items) return;
+    WItem& it = b.items[w];
+    WBox box[2], cb[2];
+    int cnt[2];
+    if (it.axis >= 0) {
+        const WBins& bins = b.bins[w];
+        WBox bb[kWBins];
+        int bc[kWBins];
+        for (int k = 0; k < kWBins; ++k) {
+            const WBin& s = bins.b[k];
+            bc[k] = s.count;
+            bb[k].mn = f3(ordered_value(s.mn[0]), ordered_value(s.mn[1]), ordered_value(s.mn[2]));
+            bb[k].mx = f3(ordered_value(s.mx[0]), ordered_value(s.mx[1]), ordered_value(s.mx[2]));
+        }
+        // suffix areas, then a prefix sweep
+        float right_area[kWBins];
+        int right_cnt[kWBins];
+        WBox acc = wb_empty();
+        int n = 0;
+        for (int k = kWBins - 1; k >= 1; --k) {
+            if (bc[k] > 0) wb_grow(acc, bb[k].mn, bb[k].mx);
+            n += bc[k];
+            right_area[k] = n > 0 ? wb_half_area(acc) : 0.0f;
+            right_cnt[k] = n;
+        }
+        acc = wb_empty();
+        n = 0;
+        int best = -1;
+        float best_cost = CV_INF;
+        for (int k = 0; k < kWBins - 1; ++k) {
+            if (bc[k] > 0) wb_grow(acc, bb[k].mn, bb[k].mx);
+            n += bc[k];
+            if (n == 0 || right_cnt[k + 1] == 0) continue;
+            const float cost = (float)n * wb_half_area(acc) + (float)right_cnt[k + 1] * right_area[k + 1];
+            if (cost < best_cost) {
+                best_cost = cost;
+                best = k;
+            }
+        }
+        if (best < 0) {
+            it.axis = -1;  // everything in one bin (cannot happen with a positive extent; kept as a guard)
+        } else {
+            it.split = best;
+            box[0] = box[1] = cb[0] = cb[1] = wb_empty();
+            cnt[0] = cnt[1] = 0;
+            for (int k = 0; k < kWBins; ++k) {
+                if (bc[k] == 0) continue;
+                const int s = k <= best ? 0 : 1;
+                const WBin& src = bins.b[k];
+                wb_grow(box[s], bb[k].mn, bb[k].mx);
+                wb_grow(cb[s], f3(ordered_value(src.cmn[0]), ordered_value(src.cmn[1]), ordered_value(src.cmn[2])),
+                        f3(ordered_value(src.cmx[0]), ordered_value(src.cmx[1]), ordered_value(src.cmx[2])));
+                cnt[s] += bc[k];
+            }
+        }
+    }
+    if (it.axis < 0) {
+        cnt[0] = it.count / 2;
+        cnt[1] = it.count - cnt[0];
+        for (int s = 0; s < 2; ++s) {
+            box[s].mn = f3(it.box_mn[0], it.box_mn[1], it.box_mn[2]);
+            box[s].mx = f3(it.box_mx[0], it.box_mx[1], it.box_mx[2]);
+            cb[s].mn = f3(it.cb_mn[0], it.cb_mn[1], it.cb_mn[2]);
+            cb[s].mx = f3(it.cb_mx[0], it.cb_mx[1], it.cb_mx[2]);
+        }
+    }
+    it.n_left = cnt[0];
+    for (int s = 0; s < 2; ++s) {
+        const int start = s == 0 ? it.start : it.start + cnt[0];
+        int ref;
+        it.child_item[s] = -1;
+        if (cnt[s] <= kFastLeafMax) {
+            ref = make_leaf_ref(start, cnt[s]);
+        } else {
+            const int pair = cv_atomic_add_i32(&b.counters[1], 1);
+            const int slot = cv_atomic_add_i32(&b.counters[0], 1);
+            if (pair >= b.pairs_capacity || slot >= b.items_capacity) {
+                cv_atomic_or_i32(&b.counters[2], WB_ERR_CAPACITY);
+                ref = make_leaf_ref(start, 1);
+            } else {
+                ref = 2 * pair;
+                it.child_item[s] = slot;
+                WItem c;
+                c.start = start;
+                c.count = cnt[s];
+                c.pair = pair;
+                c.depth = it.depth + 1;
+                c.axis = -1;
+                c.cmin = c.cscale = 0.0f;
+                c.split = c.n_left = 0;
+                c.child_item[0] = c.child_item[1] = -1;
+                c.box_mn[0] = box[s].mn.x; c.box_mn[1] = box[s].mn.y; c.box_mn[2] = box[s].mn.z;
+                c.box_mx[0] = box[s].mx.x; c.box_mx[1] = box[s].mx.y; c.box_mx[2] = box[s].mx.z;
+                c.cb_mn[0] = cb[s].mn.x; c.cb_mn[1] = cb[s].mn.y; c.cb_mn[2] = cb[s].mn.z;
+                c.cb_mx[0] = cb[s].mx.x; c.cb_mx[1] = cb[s].mx.y; c.cb_mx[2] = cb[s].mx.z;
+                b.items_next[slot] = c;
+            }
+        }
+        FastNode o;
+        o.mn[0] = box[s].mn.x; o.mn[1] = box[s].mn.y; o.mn[2] = box[s].mn.z;
+        o.mx[0] = box[s].mx.x; o.mx[1] = box[s].mx.y; o.mx[2] = box[s].mx.z;
+        o.a = ref;
+        o.b = cnt[s];
+        b.fnodes[2 * it.pair + s] = o;
+    }
+}
+
+CV_D void wb_body_flag(const WBuild& b, int i) {
+    if (i >= b.n_prims) return;
+    const int w = b.node_of[i];
+    unsigned char f = 0;
+    if (w >= 0) {
+        const WItem& it = b.items[w];
+        if (it.axis >= 0) {
+            const int p = b.order[i];
+            f = wb_bin_of(it, b.bmin[p], b.bmax[p]) <= it.split ? 1 : 0;
+        } else {
+            f = (i - it.start) < it.n_left ? 1 : 0;
+        }
+    }
+    b.flags[i] = f;
+}
+
+CV_D void wb_body_scatter(const WBuild& b, int i) {
+    if (i >= b.n_prims) return;
+    const int w = b.node_of[i];
+    if (w < 0) {
+        b.order_next[i] = b.order[i];
+        b.node_of_next[i] = -1;
+        return;
+    }
+    const WItem& it = b.items[w];
+    const int lefts_before = b.scan[i] - b.scan[it.start];
+    int dst, side;
+    if (b.flags[i]) {
+        dst = it.start + lefts_before;
+        side = 0;
+    } else {
+        dst = it.start + it.n_left + ((i - it.start) - lefts_before);
+        side = 1;
+    }
+    b.order_next[dst] = b.order[i];
+    b.node_of_next[dst] = it.child_item[side];
+}
+
+// ---- emit: slot s of the final order holds prim order[s] --------------------------------------
+// World-space vertices (the same wb_world() values the boxes were built from) and mesh-space
+// normals.  A mirroring instance (det < 0) flips the winding the reference's mesh-space
+// back-face test sees (shared_path_tracer.h:106), so its triangles are stored as (A, C, B).
+CV_D void wb_body_emit(const WBuild& b, int s) {
+    if (s >= b.n_prims) return;
+    const int p = b.order[s];
+    const uint32_t tri = f2u(b.bmin[p].w), inst = f2u(b.bmax[p].w);
+    const float* m = b.instances[inst].transform;
+    const float det = m[0] * (m[5] * m[10] - m[9] * m[6]) - m[4] * (m[1] * m[10] - m[9] * m[2]) + m[8] * (m[1] * m[6] - m[5] * m[2]);
+    const int* idx = b.indices[tri].tri;
+    const int i1 = det < 0.0f ? idx[2] : idx[1], i2 = det < 0.0f ? idx[1] : idx[2];
+    const GpuPtVertex va = b.vertices[idx[0]], vb = b.vertices[i1], vc = b.vertices[i2];
+    const F3 wa = wb_world(m, va.position), wb = wb_world(m, vb.position), wc = wb_world(m, vc.position);
+    FastTri t;
+    t.v0.x = wa.x; t.v0.y = wa.y; t.v0.z = wa.z; t.v0.w = u2f(inst);
+    t.v1.x = wb.x; t.v1.y = wb.y; t.v1.z = wb.z; t.v1.w = u2f(tri);
+    t.v2.x = wc.x; t.v2.y = wc.y; t.v2.z = wc.z; t.v2.w = 0.0f;
+    b.ftris[s] = t;
+    t.v0.x = va.normal[0]; t.v0.y = va.normal[1]; t.v0.z = va.normal[2];
+    t.v1.x = vb.normal[0]; t.v1.y = vb.normal[1]; t.v1.z = vb.normal[2];
+    t.v2.x = vc.normal[0]; t.v2.y = vc.normal[1]; t.v2.z = vc.normal[2];
+    b.fnormals[s] = t;
+}
+
+struct FnWbPrim { WBuild b; CV_D void operator()(int i) const { wb_body_prim(b, i); } };
+struct FnWbInit { WBuild b; CV_D void operator()(int i) const { wb_body_init(b, i); } };
+struct FnWbPrep { WBuild b; int n; CV_D void operator()(int i) const { wb_body_prep(b, i, n); } };
+struct FnWbBin { WBuild b; CV_D void operator()(int i) const { wb_body_bin(b, i); } };
+struct FnWbSplit { WBuild b; int n; CV_D void operator()(int i) const { wb_body_split(b, i, n); } };
+struct FnWbFlag { WBuild b; CV_D void operator()(int i) const { wb_body_flag(b, i); } };
+struct FnWbScatter { WBuild b; CV_D void operator()(int i) const { wb_body_scatter(b, i); } };
+struct FnWbEmit { WBuild b; CV_D void operator()(int i) const { wb_body_emit(b, i); } };
+
+struct WReport {
+    int levels;
+    int n_pairs;
+    int root_ref;
+    int error_bits;
+    float scene_mn[3], scene_mx[3];
+    float pad;
+};
+
+// Host-side level loop (Exec = CudaExec on the device, EmuExec in the test emulator).
+template<class Exec>
+int build_wbvh(Exec& ex, WBuild b, WReport* rep) {
+    rep->levels = 0;
+    rep->n_pairs = 0;
+    rep->error_bits = 0;
+    rep->root_ref = kRefSentinel;
+    if (b.n_prims <= 0) return 0;
+    uint32_t acc[12];
+    for (int k = 0; k < 12; ++k) acc[k] = ((k / 3) % 2 == 0) ? 0xffffffffu : 0u;
+    ex.upload(b.root_acc, acc, sizeof(acc));
+    ex.launch(b.n_prims, FnWbPrim{ b });
+    ex.download(acc, b.root_acc, sizeof(acc));
+    float scale = 0.0f;
+    for (int k = 0; k < 3; ++k) {
+        rep->scene_mn[k] = ordered_value(acc[k]);
+        rep->scene_mx[k] = ordered_value(acc[3 + k]);
+        const float a0 = rep->scene_mn[k] < 0 ? -rep->scene_mn[k] : rep->scene_mn[k], a1 = rep->scene_mx[k] < 0 ? -rep->scene_mx[k] : rep->scene_mx[k];
+        scale = scale > a0 ? scale : a0;
+        scale = scale > a1 ? scale : a1;
+    }
+    b.pad = scale * (1.0f / 1048576.0f) + 1e-30f;
+    rep->pad = b.pad;
+    ex.launch(b.n_prims, FnWbInit{ b });
+    if (b.n_prims <= kFastLeafMax) {
+        rep->root_ref = make_leaf_ref(0, b.n_prims);
+        ex.launch(b.n_prims, FnWbEmit{ b });
+        return 0;
+    }
+    WItem root;
+    root.start = 0;
+    root.count = b.n_prims;
+    root.pair = 0;
+    root.depth = 0;
+    root.axis = -1;
+    root.cmin = root.cscale = 0.0f;
+    root.split = root.n_left = 0;
+    root.child_item[0] = root.child_item[1] = -1;
+    for (int k = 0; k < 3; ++k) {
+        root.box_mn[k] = rep->scene_mn[k] - b.pad;
+        root.box_mx[k] = rep->scene_mx[k] + b.pad;
+        root.cb_mn[k] = ordered_value(acc[6 + k]);
+        root.cb_mx[k] = ordered_value(acc[9 + k]);
+    }
+    ex.upload(b.items, &root, sizeof(root));
+    int counters[3] = { 0, 1, 0 };
+    ex.upload(b.counters, counters, sizeof(counters));
+    int n_items = 1;
+    rep->root_ref = 0;
+    while (n_items > 0) {
+        ex.launch(n_items * kWBins, FnWbPrep{ b, n_items });
+        ex.launch(b.n_prims, FnWbBin{ b });
+        ex.launch(n_items, FnWbSplit{ b, n_items });
+        ex.launch(b.n_prims, FnWbFlag{ b });
+        ex.scan_u8(b.flags, b.scan, b.n_prims);
+        ex.launch(b.n_prims, FnWbScatter{ b });
+        ex.download(counters, b.counters, sizeof(counters));
+        ++rep->levels;
+        if (counters[2] != 0) {
+            rep->error_bits = counters[2];
+            return -1;
+        }
+        n_items = counters[0];
+        rep->n_pairs = counters[1];
+        counters[0] = 0;
+        ex.upload(b.counters, counters, sizeof(counters));
+        WItem* ti = b.items; b.items = b.items_next; b.items_next = ti;
+        int* to = b.order; b.order = b.order_next; b.order_next = to;
+        int* tn = b.node_of; b.node_of = b.node_of_next; b.node_of_next = tn;
+    }
+    ex.launch(b.n_prims, FnWbEmit{ b });
+    return 0;
+}
+
+}  // namespace cavept

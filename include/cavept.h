@@ -48,16 +48,20 @@ enum { CAVEPT_MODE_NONE = 0, CAVEPT_MODE_INTERACTIVE = 1, CAVEPT_MODE_TILED = 2 
 /* Which traversal the render launch uses.
  * REFERENCE_WALK reproduces HitScene (cave/shader/shared_path_tracer.h:152-189)
  * literally on the device: every mesh, stackless hit/miss-link walk over the 48-byte
- * GpuPtBvh array.  FAST is the production kernel: TLAS over instances, ordered
- * traversal with a short stack over 32-byte nodes, pre-gathered triangles.  Both
- * return the same closest hit (up to exact-tie order, SURVEY.md section 8a note ii). */
+ * GpuPtBvh array (needs CAVEPT_BVH_PARITY).  FAST is the production kernel: one
+ * world-space tree over every (instance, triangle) pair, near-first ordered traversal
+ * with a shared-memory stack over 32-byte nodes, pre-gathered world-space triangles.
+ * Both return the same closest hit (up to exact-tie order, SURVEY.md section 8a note ii,
+ * and fp32 rounding of the instance transform for non-identity instances). */
 enum { CAVEPT_TRACE_FAST = 0, CAVEPT_TRACE_REFERENCE_WALK = 1 };
 
-/* BVH builder.  PARITY reproduces BvhBuilder::ConstructHelper
- * (cave/engine/renderer/path_tracer/bvh_accel.cpp:115-219) bit-exactly.
- * LBVH is the Morton/radix-sort builder for per-frame rebuilds (beyond the reference,
- * which never rebuilds: path_tracer.cpp:69). */
-enum { CAVEPT_BVH_PARITY = 0, CAVEPT_BVH_LBVH = 1 };
+/* Which acceleration structures a scene upload builds (always on the device).
+ * PARITY: the reference-layout per-mesh BVHs, bit-exact with BvhBuilder::ConstructHelper
+ * (cave/engine/renderer/path_tracer/bvh_accel.cpp:115-219) -- what cavept_get_mesh_bvh /
+ * cavept_get_scene_arrays read back and REFERENCE_WALK traverses -- AND the production tree.
+ * FAST: the production tree only (binned-SAH world-space builder), for renders and
+ * per-frame rebuilds (the reference never rebuilds: path_tracer.cpp:69). */
+enum { CAVEPT_BVH_PARITY = 0, CAVEPT_BVH_FAST = 1 };
 
 typedef struct cavept_config {
     int device;     /* CUDA ordinal; -1 = current device */
@@ -101,8 +105,8 @@ typedef struct cavept_stats {
     uint64_t node_visits;     /* filled only when CAVEPT_STATS_COUNT_VISITS was requested */
     uint64_t triangle_tests;
     uint64_t kernel_launches; /* our __global__ launches since context creation */
-    float last_build_ms;      /* device time of the last BVH build (all meshes), CUDA events */
-    float last_compact_ms;    /* device time of deriving the production layout from it */
+    float last_build_ms;      /* device time of the last reference-layout BVH build (all meshes), CUDA events; 0 in CAVEPT_BVH_FAST */
+    float last_fast_build_ms; /* device time of the last production (world-space) BVH build */
     float last_render_ms;     /* device time of the last cavept_render, CUDA events */
     int triangle_count;
     int node_count;           /* GpuPtBvh nodes in the reference layout */
@@ -110,6 +114,8 @@ typedef struct cavept_stats {
     int instance_count;
     int build_levels;
     int build_launches;
+    int fast_build_levels;
+    int fast_build_launches;
 } cavept_stats;
 
 /* ---- lifetime; replaces the file-static PathTracer in

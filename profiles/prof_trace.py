@@ -19,5 +19,5 @@ pt.render(0, 1, sync=True)
 pt.reset_stats()
 pt.render(1, spp, sync=True)
 st = pt.stats()
-print("segments", st["segments"], "ms", st["last_render_ms"], "Mseg/s", st["segments"] / st["last_render_ms"] / 1e3, "build_ms", st["last_build_ms"])
+print("segments", st["segments"], "ms", st["last_render_ms"], "Mseg/s", st["segments"] / st["last_render_ms"] / 1e3, "build_ms", st["last_build_ms"], "fast_build_ms", st["last_fast_build_ms"], "levels", st["fast_build_levels"], "launches", st["fast_build_launches"], "fast_nodes", st["fast_node_count"])
 pt.close()

@@ -9,9 +9,9 @@
 #include <vector>
 
 #include "bvh_parity_driver.h"
-#include "compact_body.h"
-#include "tlas_host.h"
+#include "host_math.h"
 #include "trace_body.h"
+#include "wbvh_body.h"
 
 using namespace cavept;
 
@@ -84,44 +84,55 @@ EMU_API int emu_bvh_build(const GpuPtVertex* vertices, const GpuPtIndex* indices
     return rc;
 }
 
-// Production layout from the arrays emu_bvh_build returned.  fnodes needs
-// n_nodes + n_meshes + 2*n_instances + 8 entries, ftris n_tris.  Returns pair count.
-EMU_API int emu_compact(const GpuPtBvh* nodes, const int* parent, const int* count, int n_nodes, const GpuPtVertex* vertices, const GpuPtIndex* indices,
-                        FastNode* fnodes, FastTri* ftris, FastTri* fnormals, int* mesh_root_ref) {
-    std::vector<int> is_pair(n_nodes), pair_rank(n_nodes + 1), leaf_tris(n_nodes), tri_base(n_nodes + 1);
-    CompactArrays c{};
-    c.nodes = nodes;
-    c.node_parent = parent;
-    c.node_count = count;
-    c.n_nodes = n_nodes;
-    c.vertices = vertices;
-    c.indices = indices;
-    c.is_pair = is_pair.data();
-    c.pair_rank = pair_rank.data();
-    c.leaf_tris = leaf_tris.data();
-    c.tri_base = tri_base.data();
-    c.fnodes = fnodes;
-    c.ftris = ftris;
-    c.fnormals = fnormals;
-    c.mesh_root_ref = mesh_root_ref;
+// Production (world-space) BVH exactly as cavept_api.cu builds it.  inst_prim_off has
+// n_inst + 1 entries, inst_tri_off n_inst.  fnodes needs 2 * (n_prims + 8) entries, ftris /
+// fnormals n_prims.  Returns 0 ok; report = {levels, n_pairs, root_ref, error_bits}.
+EMU_API int emu_wbvh_build(const GpuPtVertex* vertices, const GpuPtIndex* indices, const GpuPtMesh* instances, int n_inst, const int* inst_prim_off,
+                           const int* inst_tri_off, int force_median, FastNode* fnodes, FastTri* ftris, FastTri* fnormals, int* report, float* out_pad) {
+    const int P = inst_prim_off[n_inst];
+    const size_t items_cap = (size_t)P / 2 + 8, pairs_cap = (size_t)P + 8;
+    std::vector<F4> bmin(P), bmax(P);
+    std::vector<int> order(P), order_next(P), node_of(P), node_of_next(P), scan(P + 1), counters(4);
+    std::vector<unsigned char> flags(P);
+    std::vector<WItem> items(items_cap), items_next(items_cap);
+    std::vector<WBins> bins(items_cap);
+    std::vector<uint32_t> root_acc(12);
+    WBuild b{};
+    b.vertices = vertices;
+    b.indices = indices;
+    b.instances = instances;
+    b.inst_prim_off = inst_prim_off;
+    b.inst_tri_off = inst_tri_off;
+    b.n_inst = n_inst;
+    b.n_prims = P;
+    b.force_median = force_median;
+    b.bmin = bmin.data();
+    b.bmax = bmax.data();
+    b.order = order.data();
+    b.order_next = order_next.data();
+    b.node_of = node_of.data();
+    b.node_of_next = node_of_next.data();
+    b.flags = flags.data();
+    b.scan = scan.data();
+    b.items = items.data();
+    b.items_next = items_next.data();
+    b.bins = bins.data();
+    b.items_capacity = (int)items_cap;
+    b.pairs_capacity = (int)pairs_cap;
+    b.counters = counters.data();
+    b.root_acc = root_acc.data();
+    b.fnodes = fnodes;
+    b.ftris = ftris;
+    b.fnormals = fnormals;
     EmuExec ex;
-    return run_compact(ex, c);
-}
-
-// TLAS exactly as cavept_api.cu builds it: root boxes = first node of each built mesh.
-// mesh_of_instance[i] = built-mesh index; mesh_root_node[k] = GpuPtBvh slot of mesh k's root.
-// Writes TLAS nodes at fnodes[base..]; returns number of TLAS nodes, root reference in *root_ref.
-EMU_API int emu_tlas(const GpuPtBvh* nodes, const GpuPtMesh* meshes, int n_instances, const int* mesh_of_instance, const int* mesh_root_node, int base,
-                     FastNode* fnodes, int* root_ref) {
-    std::vector<WorldBox> boxes(n_instances);
-    for (int i = 0; i < n_instances; ++i) {
-        const GpuPtBvh& r = nodes[mesh_root_node[mesh_of_instance[i]]];
-        boxes[i] = transform_box(meshes[i].transform, r.min, r.max);
-    }
-    std::vector<FastNode> tlas;
-    build_tlas(boxes, base, tlas, root_ref);
-    std::memcpy(fnodes + base, tlas.data(), tlas.size() * sizeof(FastNode));
-    return (int)tlas.size();
+    WReport rep{};
+    const int rc = build_wbvh(ex, b, &rep);
+    report[0] = rep.levels;
+    report[1] = rep.n_pairs;
+    report[2] = rep.root_ref;
+    report[3] = rep.error_bits;
+    if (out_pad) *out_pad = rep.pad;
+    return rc;
 }
 
 EMU_API void emu_mat4_inverse(const float* m, float* out) { mat4_inverse(m, out); }
@@ -135,7 +146,7 @@ struct EmuCamera {
 };
 
 EMU_API long long emu_render(const GpuPtVertex* vertices, const GpuPtIndex* indices, const GpuPtBvh* bvhs, const GpuPtMesh* meshes, int mesh_count,
-                             const GpuPtMaterial* materials, const FastNode* fnodes, const FastTri* ftris, const FastTri* fnormals, const int* inst_fast_root, int tlas_root,
+                             const GpuPtMaterial* materials, const FastNode* fnodes, const FastTri* ftris, const FastTri* fnormals, int root_ref,
                              const EmuCamera* cam, int max_bounce, int width, int height, int first_frame, int n_frames, int reset_first, float* accum,
                              int fast, unsigned long long* counters) {
     TraceParams p{};
@@ -148,8 +159,7 @@ EMU_API long long emu_render(const GpuPtVertex* vertices, const GpuPtIndex* indi
     p.fnodes = fnodes;
     p.ftris = ftris;
     p.fnormals = fnormals;
-    p.inst_fast_root = inst_fast_root;
-    p.tlas_root = tlas_root;
+    p.root_ref = root_ref;
     std::memcpy(p.cam_pos, cam->position, 12);
     std::memcpy(p.cam_right, cam->right, 12);
     std::memcpy(p.cam_up, cam->up, 12);

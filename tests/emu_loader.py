@@ -39,7 +39,7 @@ def _p(a):
 
 
 class EmuScene:
-    """Runs the product's build pipeline (parity BVH -> compact layout -> TLAS) in emulation
+    """Runs the product's build pipeline (parity BVH + production world-space BVH) in emulation
     on the scene-global arrays of an oracle-assembled scene."""
 
     def __init__(self, asm, scene):
@@ -65,21 +65,25 @@ class EmuScene:
         self.levels, self.error_bits = levels.value, err.value
         if self.rc != 0:
             return
+        self.build_world(asm, scene, built)
+
+    def build_world(self, asm, scene, built, force_median=False):
+        """Production (world-space) BVH, as cavept_api.cu's build_world() drives it."""
         n_inst = len(scene.instances)
-        self.fnodes = np.zeros(self.n_nodes + n_meshes + 2 * n_inst + 8, dtype=FASTNODE_DT)
-        self.ftris = np.zeros(n_tris, dtype=FASTTRI_DT)
-        self.fnormals = np.zeros(n_tris, dtype=FASTTRI_DT)
-        self.mesh_root_ref = np.zeros(n_meshes, dtype=np.int32)
-        self.n_pairs = self.lib.emu_compact(_p(self.nodes), _p(self.parent), _p(self.count), C.c_int(self.n_nodes), _p(asm.vertices), _p(asm.indices),
-                                            _p(self.fnodes), _p(self.ftris), _p(self.fnormals), _p(self.mesh_root_ref))
-        mesh_of_inst = np.array([built.index(i.mesh) for i in scene.instances], dtype=np.int32)
-        root_node = (2 * self.tri_off[:-1] - np.arange(n_meshes)).astype(np.int32)
-        self.tlas_base = 2 * self.n_pairs
-        root_ref = C.c_int()
-        self.n_tlas = self.lib.emu_tlas(_p(self.nodes), _p(asm.meshes), C.c_int(n_inst), _p(mesh_of_inst), _p(root_node), C.c_int(self.tlas_base), _p(self.fnodes),
-                                        C.byref(root_ref))
-        self.tlas_root = root_ref.value
-        self.inst_fast_root = self.mesh_root_ref[mesh_of_inst].astype(np.int32)
+        tri_counts = [scene.meshes[i.mesh].n_tris for i in scene.instances]
+        self.inst_prim_off = np.concatenate([[0], np.cumsum(tri_counts)]).astype(np.int32)
+        self.inst_tri_off = np.array([int(self.tri_off[built.index(i.mesh)]) for i in scene.instances], dtype=np.int32)
+        P = int(self.inst_prim_off[-1])
+        self.n_prims = P
+        self.fnodes = np.zeros(2 * (P + 8), dtype=FASTNODE_DT)
+        self.ftris = np.zeros(P, dtype=FASTTRI_DT)
+        self.fnormals = np.zeros(P, dtype=FASTTRI_DT)
+        report = np.zeros(4, dtype=np.int32)
+        pad = C.c_float()
+        self.wrc = self.lib.emu_wbvh_build(_p(asm.vertices), _p(asm.indices), _p(asm.meshes), C.c_int(n_inst), _p(self.inst_prim_off), _p(self.inst_tri_off),
+                                           C.c_int(1 if force_median else 0), _p(self.fnodes), _p(self.ftris), _p(self.fnormals), _p(report), C.byref(pad))
+        self.fast_levels, self.n_pairs, self.root_ref, self.wb_error_bits = [int(v) for v in report]
+        self.pad = pad.value
 
     def render(self, camera, width, height, first_frame, n_frames, max_bounce, fast, accum=None, reset_first=True):
         from oracle.oracle import _cam
@@ -90,7 +94,7 @@ class EmuScene:
         counters = (C.c_ulonglong * 3)()
         a = self.asm
         segs = self.lib.emu_render(_p(a.vertices), _p(a.indices), _p(self.nodes), _p(a.meshes), C.c_int(a.meshes.shape[0]), _p(a.materials), _p(self.fnodes),
-                                   _p(self.ftris), _p(self.fnormals), _p(self.inst_fast_root), C.c_int(self.tlas_root), C.byref(cam), C.c_int(max_bounce), C.c_int(width),
+                                   _p(self.ftris), _p(self.fnormals), C.c_int(self.root_ref), C.byref(cam), C.c_int(max_bounce), C.c_int(width),
                                    C.c_int(height), C.c_int(first_frame), C.c_int(n_frames), C.c_int(1 if reset_first else 0), _p(accum), C.c_int(1 if fast else 0),
                                    counters)
         return accum, {"segments": int(segs), "node_visits": int(counters[1]), "tri_tests": int(counters[2])}

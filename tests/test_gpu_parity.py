@@ -7,10 +7,15 @@ Tolerances (stated here, used below):
     same operation order; the only differences are device sincosf vs libm sinf/cosf (<= 2 ulp)
     and, for the reference's own code, its double promotions.  A pixel "matches" when every
     channel is within 1e-4 * (|ref| + 1e-3); at most 1 % of pixels may differ (a 1-ulp
-    direction change can flip a discrete hit after several bounces), and the image RMSE must
-    be below 2 % of the mean radiance.
-  * FAST traversal vs REFERENCE_WALK on the device (same arithmetic, same sincosf): identical
-    closest hits except exact-tie / box-grazing rays: <= 0.1 % of pixels may differ at all.
+    direction change can flip a discrete hit after several bounces; at the 2-4 spp of these
+    tests one flipped path onto a light is an O(1) change of that pixel), and the image RMSE
+    must be below 4 % of the mean radiance.
+  * FAST traversal vs REFERENCE_WALK on the device (same sincosf).  Identity instances: the
+    world-space triangles ARE the mesh-space triangles, so (t, u, v) are bit-identical and
+    <= 0.1 % of pixels may differ at all (exact-tie / box-grazing rays).  Transformed instances:
+    the reference intersects in mesh space with the inverse-transformed ray, the production tree
+    in world space -- equal up to fp32 rounding of the transform: per-pixel 1e-4 relative,
+    <= 1 % of pixels beyond it.
 """
 import numpy as np
 import pytest
@@ -45,7 +50,7 @@ def _pixel_tol(img, ref, max_bad=0.01, rel=1e-4):
     bad = H.image_mismatch(img, ref, rel=rel)
     assert bad <= max_bad, f"{bad:.4%} of pixels differ"
     mean = float(np.mean(np.asarray(ref)[..., :3]))
-    assert H.rmse(img, ref) <= 0.02 * mean + 1e-6
+    assert H.rmse(img, ref) <= 0.04 * mean + 1e-6
 
 
 # ---- BVH: bit-exact -------------------------------------------------------------------------
@@ -141,12 +146,59 @@ def test_fast_equals_reference_walk_full_size(api, scene_cache):
     a, sa = out["REFERENCE_WALK"]
     b, sb = out["FAST"]
     assert abs(sa - sb) <= sa // 2000
-    differ = float((np.abs(a - b)[..., :3].max(axis=-1) > 0).mean())
-    assert differ <= 0.001, f"{differ:.4%} of pixels differ"
+    # 17 of the 25 instances carry a transform.  At 1 spp a flipped path onto a lamp (emissive 20)
+    # is an O(10) change of that pixel, so the bound is on how many pixels move, not on the RMSE.
+    bad = H.image_mismatch(b, a, rel=1e-4)
+    assert bad <= 0.005, f"{bad:.4%} of pixels differ"
+    assert abs(float(b[..., :3].mean()) - float(a[..., :3].mean())) <= 0.005 * float(a[..., :3].mean())
     # size-independent properties: sample count, nominal segment bounds, finite radiance
     assert np.all(b[..., 3] == 1.0)
     assert 1920 * 1080 <= sb <= 1920 * 1080 * 8
     assert np.isfinite(b).all() and (b[..., :3] >= 0).all()
+
+
+def test_fast_equals_reference_walk_bitwise_for_identity_instances(api, scene_cache):
+    sc = scene_cache("heightfield")
+    out = {}
+    for mode in ("REFERENCE_WALK", "FAST"):
+        with _tracer(api, sc, 960, 540, 5, getattr(api.TraceMode, mode)) as pt:
+            pt.reset_stats()
+            pt.render(0, 2, sync=True)
+            out[mode] = (pt.read_accum(), pt.stats()["segments"])
+    a, sa = out["REFERENCE_WALK"]
+    b, sb = out["FAST"]
+    assert abs(sa - sb) <= max(2, sa // 5000)
+    differ = float((np.abs(a - b)[..., :3].max(axis=-1) > 0).mean())
+    assert differ <= 0.001, f"{differ:.4%} of pixels differ"
+
+
+def test_fast_only_bvh_mode(api, scene_cache):
+    """CAVEPT_BVH_FAST builds the production tree only: same image, no reference-layout read-back."""
+    sc = scene_cache("tiny")
+    with _tracer(api, sc, 64, 36, 5, api.TraceMode.FAST) as pt:
+        pt.render(0, 3, sync=True)
+        want = pt.read_accum()
+        st_parity = pt.stats()
+    pt = api.PathTracer(64, 36, 5, trace_mode=api.TraceMode.FAST, device=0, bvh_mode=api.BvhMode.FAST)
+    pt.set_mode(api.PathTracerMode.INTERACTIVE)
+    pt.upload_scene(sc)
+    pt.set_camera(sc.camera)
+    pt.render(0, 3, sync=True)
+    assert pt.read_accum().tobytes() == want.tobytes()
+    st = pt.stats()
+    assert st["build_launches"] == 0 and st["fast_build_launches"] > 0 and st["fast_build_levels"] == st_parity["fast_build_levels"]
+    assert st["fast_node_count"] == st_parity["fast_node_count"] > 0
+    with pytest.raises(api.CaveptError) as e:
+        pt.get_mesh_bvh(0, sc.meshes[0].n_tris)
+    assert e.value.code == 4
+    pt.close()
+    ref = api.PathTracer(64, 36, 5, trace_mode=api.TraceMode.REFERENCE_WALK, device=0, bvh_mode=api.BvhMode.FAST)
+    ref.set_mode(api.PathTracerMode.INTERACTIVE)
+    ref.upload_scene(sc)
+    with pytest.raises(api.CaveptError) as e:
+        ref.render(0, 1)
+    assert e.value.code == 4
+    ref.close()
 
 
 def test_progressive_accumulation_and_reset(api, scene_cache):

@@ -143,6 +143,33 @@ CV_HD float u2f(uint32_t u) {
 
 #define CV_INF (u2f(0x7f800000u))
 
+// 32-byte record fetched with ONE 256-bit load (LDG.E.256, new with sm_100): half the L1
+// wavefronts of two 128-bit loads when every lane reads a different cache line.
+struct alignas(32) F8 {
+    float a, b, c, d, e, f, g, h;
+};
+CV_HD F8 ld256(const void* p) {
+    F8 r;
+#if defined(__CUDA_ARCH__)
+    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(r.a), "=f"(r.b), "=f"(r.c), "=f"(r.d), "=f"(r.e), "=f"(r.f), "=f"(r.g), "=f"(r.h)
+                 : "l"(p));
+#else
+    memcpy(&r, p, 32);
+#endif
+    return r;
+}
+// 1/x to ~1 ulp (MUFU.RCP): for slopes whose error the padded boxes absorb, never for results.
+CV_HD float rcp_approx(float x) {
+#if defined(__CUDA_ARCH__)
+    float r;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+#else
+    return 1.0f / x;
+#endif
+}
+
 // Order-preserving float -> uint32 map with -0 and +0 sharing one key.
 CV_HD uint32_t ordered_key(float v) {
     uint32_t b = f2u(v);

@@ -2,6 +2,8 @@
 // Compiled for sm_100a only, with -fmad=false (see cv_common.h on float semantics).
 #include "kernels.h"
 
+#include <cstdlib>
+
 namespace cavept {
 
 // ---- generic element-wise launch -------------------------------------------------------
@@ -189,14 +191,14 @@ int run_build_wbvh(CudaExec& ex, WBuild b, WReport* report) { return build_wbvh(
 // Block = 128 threads = a 16 x 8 pixel tile; each warp covers an 8 x 4 sub-tile so the
 // primary rays of a warp are coherent.  Replaces Dispatch(ceil(W/16), ceil(H/16), 1) of a
 // 16x16 work group (cave/engine/render_graph/common_passes.cpp:990-997).
-template<bool kFast, bool kCount>
+template<bool kFast, bool kCount, int kQuorum = kStepQuorum, int kBatch = kShadeBatch>
 __global__ void __launch_bounds__(128) k_trace(const TraceParams p) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int x = blockIdx.x * 16 + (warp & 1) * 8 + (lane & 7);
     const int y = blockIdx.y * 8 + (warp >> 1) * 4 + (lane >> 3);
     unsigned long long cnt[3] = { 0ull, 0ull, 0ull };
     __shared__ int s_stack[kFast ? kStackSize * 128 : 1];  // [depth][thread]: conflict-free whatever each lane's depth
-    unsigned int segs = kFast ? body_trace_pixel_fast<kCount>(p, x, y, s_stack + threadIdx.x, 128, cnt) : body_trace_pixel_reference<kCount>(p, x, y, cnt);
+    unsigned int segs = kFast ? body_trace_pixel_fast<kCount, kQuorum, kBatch>(p, x, y, s_stack + threadIdx.x, 128, cnt) : body_trace_pixel_reference<kCount>(p, x, y, cnt);
     segs = __reduce_add_sync(0xffffffffu, segs);
     if (lane == 0 && segs) atomicAdd(&p.counters[0], (unsigned long long)segs);
     if (kCount) {
@@ -212,8 +214,14 @@ __global__ void __launch_bounds__(128) k_trace(const TraceParams p) {
 
 void launch_trace(CudaExec& ex, const TraceParams& p, bool fast, bool count_visits) {
     const dim3 grid((p.width + 15) / 16, (p.height + 7) / 8, 1), block(128, 1, 1);
+    static const int variant = getenv("CAVEPT_VARIANT") ? atoi(getenv("CAVEPT_VARIANT")) : 0;  // tuning experiments only
     if (fast) {
         if (count_visits) k_trace<true, true><<<grid, block, 0, ex.stream>>>(p);
+        else if (variant == 1) k_trace<true, false, 16, 8><<<grid, block, 0, ex.stream>>>(p);
+        else if (variant == 2) k_trace<true, false, 24, 8><<<grid, block, 0, ex.stream>>>(p);
+        else if (variant == 3) k_trace<true, false, 20, 12><<<grid, block, 0, ex.stream>>>(p);
+        else if (variant == 4) k_trace<true, false, 20, 4><<<grid, block, 0, ex.stream>>>(p);
+        else if (variant == 5) k_trace<true, false, 12, 8><<<grid, block, 0, ex.stream>>>(p);
         else k_trace<true, false><<<grid, block, 0, ex.stream>>>(p);
     } else {
         if (count_visits) k_trace<false, true><<<grid, block, 0, ex.stream>>>(p);

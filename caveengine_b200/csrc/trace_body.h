@@ -32,11 +32,15 @@ struct alignas(16) FastNode {
 };
 static_assert(sizeof(FastNode) == 32, "FastNode");
 
-// Pre-gathered triangle: 3 x float4 world-space vertices; v0.w = instance, v1.w = scene-global triangle id.
-struct alignas(16) FastTri {
-    F4 v0, v1, v2;
+// Pre-gathered triangle, 3 x float4.  In `ftris`: v0 = world-space A, v1 = AB = B - A,
+// v2 = AC = C - A (the two subtractions HitTriangle starts with, :94-95, done once at build
+// time -- same fp32 operations, same bits); v0.w = instance, v1.w = scene-global triangle id.
+// In `fnormals`: the three mesh-space vertex normals, v0.w = instance.  Records are padded
+// to 64 bytes so one triangle is two 256-bit loads from a single cache line.
+struct alignas(64) FastTri {
+    F4 v0, v1, v2, pad;
 };
-static_assert(sizeof(FastTri) == 48, "FastTri");
+static_assert(sizeof(FastTri) == 64, "FastTri");
 
 struct TraceParams {
     // reference-layout arrays (what BindPathTracerData binds, path_tracer.cpp:324-331)
@@ -107,9 +111,11 @@ CV_HD F3 mat_mul(const float* m, F3 v, float w) {
 CV_HD F3 recip3(F3 d) { return f3(cv_div(1.0f, d.x), cv_div(1.0f, d.y), cv_div(1.0f, d.z)); }
 
 // ---- HitTriangle, :88-130 ------------------------------------------------------------
+CV_HD bool hit_triangle_edges(F3 A, F3 AB, F3 AC, F3 origin, F3 direction, float& ray_t, float& out_u, float& out_v);
 CV_HD bool hit_triangle(F3 A, F3 B, F3 C, F3 origin, F3 direction, float& ray_t, float& out_u, float& out_v) {
-    const F3 AB = B - A;
-    const F3 AC = C - A;
+    return hit_triangle_edges(A, B - A, C - A, origin, direction, ray_t, out_u, out_v);
+}
+CV_HD bool hit_triangle_edges(F3 A, F3 AB, F3 AC, F3 origin, F3 direction, float& ray_t, float& out_u, float& out_v) {
     const F3 P = cross3(direction, AC);
     const float det = dot3(AB, P);
     if (det < kEpsilon) return false;  // back faces culled
@@ -218,11 +224,7 @@ struct Walk {
 // component is replaced by a huge finite slope so that 0 * inf never makes a NaN.
 CV_HD float slab_recip(float d) {
     const float a = fabsf(d) > 1e-30f ? d : (f2u(d) >> 31 ? -1e-30f : 1e-30f);
-#if defined(__CUDA_ARCH__)
-    return __frcp_rn(a);
-#else
-    return 1.0f / a;
-#endif
+    return rcp_approx(a);
 }
 
 CV_D void walk_begin(const TraceParams& p, Walk& w, const Ray& ray) {
@@ -251,21 +253,21 @@ CV_D void walk_park_leaf(Walk& w) {
 // boxes entirely behind the origin or beyond the current hit are rejected.
 template<bool kCount>
 CV_D void walk_step(const TraceParams& p, Walk& w, float ray_t, unsigned long long* cnt) {
-    const F4* q = reinterpret_cast<const F4*>(p.fnodes + w.ref);
-    const F4 a0 = q[0], a1 = q[1], b0 = q[2], b1 = q[3];
+    const F8 c0 = ld256(p.fnodes + w.ref);      // mn.xyz, ref, mx.xyz, count
+    const F8 c1 = ld256(p.fnodes + w.ref + 1);  // same cache line
     if (kCount) cnt[1] += 2;
-    const float ax = cv_fma(a0.x, w.inv.x, w.oinv.x), bx = cv_fma(a1.x, w.inv.x, w.oinv.x);
-    const float ay = cv_fma(a0.y, w.inv.y, w.oinv.y), by = cv_fma(a1.y, w.inv.y, w.oinv.y);
-    const float az = cv_fma(a0.z, w.inv.z, w.oinv.z), bz = cv_fma(a1.z, w.inv.z, w.oinv.z);
-    const float cx = cv_fma(b0.x, w.inv.x, w.oinv.x), dx = cv_fma(b1.x, w.inv.x, w.oinv.x);
-    const float cy = cv_fma(b0.y, w.inv.y, w.oinv.y), dy = cv_fma(b1.y, w.inv.y, w.oinv.y);
-    const float cz = cv_fma(b0.z, w.inv.z, w.oinv.z), dz = cv_fma(b1.z, w.inv.z, w.oinv.z);
+    const float ax = cv_fma(c0.a, w.inv.x, w.oinv.x), bx = cv_fma(c0.e, w.inv.x, w.oinv.x);
+    const float ay = cv_fma(c0.b, w.inv.y, w.oinv.y), by = cv_fma(c0.f, w.inv.y, w.oinv.y);
+    const float az = cv_fma(c0.c, w.inv.z, w.oinv.z), bz = cv_fma(c0.g, w.inv.z, w.oinv.z);
+    const float cx = cv_fma(c1.a, w.inv.x, w.oinv.x), dx = cv_fma(c1.e, w.inv.x, w.oinv.x);
+    const float cy = cv_fma(c1.b, w.inv.y, w.oinv.y), dy = cv_fma(c1.f, w.inv.y, w.oinv.y);
+    const float cz = cv_fma(c1.c, w.inv.z, w.oinv.z), dz = cv_fma(c1.g, w.inv.z, w.oinv.z);
     const float n0 = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), 0.0f));
     const float f0 = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), ray_t));
     const float n1 = fmaxf(fmaxf(fminf(cx, dx), fminf(cy, dy)), fmaxf(fminf(cz, dz), 0.0f));
     const float f1 = fminf(fminf(fmaxf(cx, dx), fmaxf(cy, dy)), fminf(fmaxf(cz, dz), ray_t));
     const bool h0 = n0 <= f0, h1 = n1 <= f1;
-    const int r0 = (int)f2u(a0.w), r1 = (int)f2u(b0.w);
+    const int r0 = (int)f2u(c0.d), r1 = (int)f2u(c1.d);
     const bool second_first = h1 && (!h0 || n1 < n0);
     if (h0 && h1) {
         w.stack[w.sp * w.stride] = second_first ? r0 : r1;
@@ -287,10 +289,11 @@ CV_D void walk_test_triangle(const TraceParams& p, Walk& w, const Ray& ray, floa
     const int leaf = w.q0;
     const int slot = leaf & 0x1fffffff;
     const int more = (leaf >> 29) & 3;
-    const FastTri tr = p.ftris[slot];
+    const F8 t0 = ld256(&p.ftris[slot]);             // A.xyz, instance, AB.xyz, triangle id
+    const F8 t1 = ld256(&p.ftris[slot].v2);          // AC.xyz (same cache line)
     if (kCount) ++cnt[2];
     float u, v;
-    if (hit_triangle(f3(tr.v0.x, tr.v0.y, tr.v0.z), f3(tr.v1.x, tr.v1.y, tr.v1.z), f3(tr.v2.x, tr.v2.y, tr.v2.z), ray.origin, ray.direction, ray_t, u, v)) {
+    if (hit_triangle_edges(f3(t0.a, t0.b, t0.c), f3(t0.e, t0.f, t0.g), f3(t1.a, t1.b, t1.c), ray.origin, ray.direction, ray_t, u, v)) {
         w.hit_slot = slot;
         w.hit_u = u;
         w.hit_v = v;
@@ -418,15 +421,16 @@ CV_D unsigned int body_trace_pixel_reference(const TraceParams& p, int x, int y,
 //   A  one interior step.  A lane that reaches a leaf parks it (two-entry queue) and keeps
 //      descending -- speculative traversal: the pending triangles can only shorten ray.t, so
 //      the extra nodes visited never change the closest hit;
-//   B  one triangle of the oldest parked leaf, when too few lanes can still step;
+//   B  one triangle of the oldest parked leaf, once at least as many lanes wait on triangles
+//      as can still step;
 //   C  shade + next segment (or next sample) for lanes whose traversal is complete, in batches
 //      of >= kShadeBatch lanes so the long shading sequence is not replayed per lane.
 // The order in which ONE lane visits its nodes and triangles does not depend on its
 // neighbours, so images are deterministic.
-constexpr int kStepQuorum = 20;  // of 32: run A while at least this share of the live lanes can step
+constexpr int kStepQuorum = 20;  // of 32 lanes: keep stepping while at least this many can
 constexpr int kShadeBatch = 8;
 
-template<bool kCount>
+template<bool kCount, int kQuorum = kStepQuorum, int kBatch = kShadeBatch>
 CV_D unsigned int body_trace_pixel_fast(const TraceParams& p, int x, int y, int* stack, int stride, unsigned long long* cnt) {
     const bool valid = x < p.width && y < p.height && p.n_frames > 0;
     const size_t pix = valid ? (size_t)y * (size_t)p.width + (size_t)x : 0;
@@ -448,45 +452,54 @@ CV_D unsigned int body_trace_pixel_fast(const TraceParams& p, int x, int y, int*
     walk_begin(p, w, ray);
     if (!valid) w.ref = kRefSentinel;
     for (;;) {
-        walk_park_leaf(w);
+        // ---- A, the tight loop: one ballot per step while a quorum can step -----------------
+        for (;;) {
+            walk_park_leaf(w);
+            const bool can_step = ref_is_interior(w.ref);
+            if (CV_WARP_COUNT(can_step) < kQuorum) break;
+            if (can_step) walk_step<kCount>(p, w, ray.t, cnt);
+        }
+        // ---- the vote ------------------------------------------------------------------------
         const bool can_step = ref_is_interior(w.ref);
         const bool has_tri = w.q0 != 0;
-        const bool need_shade = !done && !can_step && !has_tri && w.ref == kRefSentinel;
-        const int n_live = CV_WARP_COUNT(!done);
-        if (n_live == 0) break;
+        const bool need_shade = !done && !can_step && !has_tri;  // ref is the sentinel: a parked-full lane has_tri
         const int n_step = CV_WARP_COUNT(can_step);
         const int n_tri = CV_WARP_COUNT(has_tri);
         const int n_shade = CV_WARP_COUNT(need_shade);
-        if (n_step * 32 >= n_live * kStepQuorum || (n_step > 0 && n_tri == 0 && n_shade < kShadeBatch)) {
-            if (can_step) walk_step<kCount>(p, w, ray.t, cnt);
-        } else if (n_tri > 0) {
+        if (n_step + n_tri + n_shade == 0) break;  // every lane has rendered all its frames
+        if (n_tri > 0 && n_tri >= n_step) {
             if (has_tri) walk_test_triangle<kCount>(p, w, ray, ray.t, cnt);
-        } else if (need_shade) {
-            ++segments;
-            const bool is_hit = w.hit_slot >= 0;
-            F3 n1 = f3(0, 0, 0), n2 = n1, n3 = n1;
-            int instance = 0;
-            if (is_hit) {
-                const FastTri nr = p.fnormals[w.hit_slot];
-                n1 = f3(nr.v0.x, nr.v0.y, nr.v0.z);
-                n2 = f3(nr.v1.x, nr.v1.y, nr.v1.z);
-                n3 = f3(nr.v2.x, nr.v2.y, nr.v2.z);
-                instance = (int)f2u(nr.v0.w);
-            }
-            if (shade_hit(p, is_hit, instance, n1, n2, n3, w.hit_u, w.hit_v, ray, seed, radiance, throughput, bounce)) {
-                F4 acc = p.accum[pix];
-                accumulate(acc, radiance, f == 0 && p.reset_first != 0);
-                p.accum[pix] = acc;
-                if (++f == p.n_frames) {
-                    done = true;
-                } else {
-                    radiance = f3(0.0f, 0.0f, 0.0f);
-                    throughput = f3(1.0f, 1.0f, 1.0f);
-                    bounce = 0;
-                    start_path(p, x, y, p.first_frame + f, ray, seed);
+        } else if (n_shade >= kBatch || n_step == 0) {
+            if (need_shade) {
+                ++segments;
+                const bool is_hit = w.hit_slot >= 0;
+                F3 n1 = f3(0, 0, 0), n2 = n1, n3 = n1;
+                int instance = 0;
+                if (is_hit) {
+                    const FastTri nr = p.fnormals[w.hit_slot];
+                    n1 = f3(nr.v0.x, nr.v0.y, nr.v0.z);
+                    n2 = f3(nr.v1.x, nr.v1.y, nr.v1.z);
+                    n3 = f3(nr.v2.x, nr.v2.y, nr.v2.z);
+                    instance = (int)f2u(nr.v0.w);
                 }
+                if (shade_hit(p, is_hit, instance, n1, n2, n3, w.hit_u, w.hit_v, ray, seed, radiance, throughput, bounce)) {
+                    F4 acc = p.accum[pix];
+                    accumulate(acc, radiance, f == 0 && p.reset_first != 0);
+                    p.accum[pix] = acc;
+                    if (++f == p.n_frames) {
+                        done = true;
+                    } else {
+                        radiance = f3(0.0f, 0.0f, 0.0f);
+                        throughput = f3(1.0f, 1.0f, 1.0f);
+                        bounce = 0;
+                        start_path(p, x, y, p.first_frame + f, ray, seed);
+                    }
+                }
+                walk_begin(p, w, ray);
+                if (done) w.ref = kRefSentinel;
             }
-            if (!done) walk_begin(p, w, ray);
+        } else {
+            if (can_step) walk_step<kCount>(p, w, ray.t, cnt);
         }
     }
     return segments;

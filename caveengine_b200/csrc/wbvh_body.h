@@ -390,10 +390,12 @@ CV_D void wb_body_emit(const WBuild& b, int s) {
     const int i1 = det < 0.0f ? idx[2] : idx[1], i2 = det < 0.0f ? idx[1] : idx[2];
     const GpuPtVertex va = b.vertices[idx[0]], vb = b.vertices[i1], vc = b.vertices[i2];
     const F3 wa = wb_world(m, va.position), wb = wb_world(m, vb.position), wc = wb_world(m, vc.position);
+    const F3 ab = wb - wa, ac = wc - wa;  // HitTriangle's first two lines (shared_path_tracer.h:94-95)
     FastTri t;
     t.v0.x = wa.x; t.v0.y = wa.y; t.v0.z = wa.z; t.v0.w = u2f(inst);
-    t.v1.x = wb.x; t.v1.y = wb.y; t.v1.z = wb.z; t.v1.w = u2f(tri);
-    t.v2.x = wc.x; t.v2.y = wc.y; t.v2.z = wc.z; t.v2.w = 0.0f;
+    t.v1.x = ab.x; t.v1.y = ab.y; t.v1.z = ab.z; t.v1.w = u2f(tri);
+    t.v2.x = ac.x; t.v2.y = ac.y; t.v2.z = ac.z; t.v2.w = 0.0f;
+    t.pad.x = t.pad.y = t.pad.z = t.pad.w = 0.0f;
     b.ftris[s] = t;
     t.v0.x = va.normal[0]; t.v0.y = va.normal[1]; t.v0.z = va.normal[2];
     t.v1.x = vb.normal[0]; t.v1.y = vb.normal[1]; t.v1.z = vb.normal[2];

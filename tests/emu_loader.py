@@ -15,7 +15,7 @@ LIB = os.path.join(HERE, "emu", "libcavept_emu.so")
 SRC = os.path.join(HERE, "emu", "emu.cpp")
 
 FASTNODE_DT = np.dtype([("mn", "<f4", 3), ("a", "<i4"), ("mx", "<f4", 3), ("b", "<i4")])
-FASTTRI_DT = np.dtype([("v0", "<f4", 4), ("v1", "<f4", 4), ("v2", "<f4", 4)])
+FASTTRI_DT = np.dtype([("v0", "<f4", 4), ("v1", "<f4", 4), ("v2", "<f4", 4), ("pad", "<f4", 4)])
 
 
 def _stale() -> bool:

@@ -127,7 +127,8 @@ def _world_tree_check(emu, asm, sc):
     fn = emu.fnodes
     seen_slots = np.zeros(P, dtype=np.int32)
     seen_pairs = np.zeros(max(emu.n_pairs, 1), dtype=np.int32)
-    verts = np.stack([emu.ftris["v0"][:, :3], emu.ftris["v1"][:, :3], emu.ftris["v2"][:, :3]], axis=1)  # (P, 3, 3) world space
+    a0 = emu.ftris["v0"][:, :3]  # records hold A, AB = B - A, AC = C - A (world space)
+    verts = np.stack([a0, a0 + emu.ftris["v1"][:, :3], a0 + emu.ftris["v2"][:, :3]], axis=1)  # (P, 3, 3)
     max_depth = 0
 
     def visit(ref, depth, box):
@@ -138,7 +139,8 @@ def _world_tree_check(emu, asm, sc):
             seen_slots[first:first + count] += 1
             if box is not None:
                 v = verts[first:first + count].reshape(-1, 3)
-                assert np.all(v >= box[0]) and np.all(v <= box[1])
+                slack = 0.5 * emu.pad  # A + AB re-rounds B by <= 1 ulp; the boxes are padded by emu.pad
+                assert np.all(v >= box[0] - slack) and np.all(v <= box[1] + slack)
             return count
         assert ref % 2 == 0
         seen_pairs[ref // 2] += 1

@@ -85,6 +85,41 @@ class ClockSampler:
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def ncu_digest():
+    """Newest committed digest of an `ncu --set full` capture of k_trace (profiles/summarize.py json)."""
+    import glob
+
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "*_k_trace_ncu.json")))
+    return (json.load(open(files[-1])), os.path.basename(files[-1])) if files else (None, None)
+
+
+def roofline(achieved, peaks, peak_kind, bytes_per_segment, vn, vt, seg_per_launch, launch_ms, clocks, spp):
+    """The contract's object quotes ALGORITHMIC gather bytes against the HBM peak.  That ratio is
+    NOT a speed-of-light claim for this kernel: the 262k-triangle working set (~35 MB) lives in the
+    126 MB L2, DRAM moves ~1 byte per segment (`traffic`), and what the kernel saturates is the
+    L1TEX data pipe -- one wavefront per (lane, 32-byte gather) -- so `binding` carries that roof:
+    wavefronts per segment from the committed ncu capture x the live segment rate, against
+    1 wavefront / clock / SM at the sampled SM clock."""
+    r = {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"], "traffic": None,
+         "peak_kind": peak_kind, "kernel": "k_trace<fast>", "bytes_per_segment": bytes_per_segment, "node_visits_per_segment": vn,
+         "triangle_tests_per_segment": vt,
+         "note": "nominal: algorithmic bytes (own traversal policy) / HBM peak; the working set is L2-resident, HBM is not the binding roof -- see `binding`"}
+    d, name = ncu_digest()
+    if d and d.get("segments_of_launch"):
+        scale = seg_per_launch / d["segments_of_launch"]
+        r["traffic"] = d["dram_bytes"] * scale
+        r["traffic_source"] = f"profiles/{name}: dram__bytes_read+write of a {d['spp_of_launch']}-spp launch ({d['segments_of_launch']} segments)" + ("" if d["spp_of_launch"] == spp else f", scaled by segments to this {spp}-spp launch")
+        wf_per_seg = d["l1_lsu_wavefronts"] / d["segments_of_launch"]
+        mhz = (clocks or {}).get("sm_mhz") or peaks.get("sm_max_mhz") or 1965.0
+        peak_wf = 148 * mhz * 1e6
+        ach_wf = wf_per_seg * seg_per_launch / (launch_ms * 1e-3)
+        r["binding"] = {"unit": "l1tex data-pipe LSU wavefronts/s", "wavefronts_per_segment": wf_per_seg, "achieved": ach_wf, "peak": peak_wf, "frac": ach_wf / peak_wf,
+                        "ncu_pct_of_peak_in_capture": d["l1_lsu_wavefronts_pct_of_peak"], "l2_hit_pct": d["l2_hit_pct"], "l2_throughput_pct": d["l2_throughput_pct"],
+                        "l2_bytes_per_segment": d["l2_bytes"] / d["segments_of_launch"], "dram_bytes_per_segment": d["dram_bytes"] / d["segments_of_launch"],
+                        "fma_pipe_pct": d["fma_pipe_pct"], "issue_active_pct": d["issue_active_pct"]}
+    return r
+
+
 def cpu_sample_rows(cores: int):
     """Bounded CPU sample of the same workload: a band of full-width rows of the 1080p image
     at 1 spp (frame 0), about 20 s of single-thread work per 8 cores."""
@@ -287,9 +322,7 @@ def main():
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 13 * 4, "d2h_bytes_per_step": int(host.nbytes),
                     "note": "per step: cavept_set_camera (host constants) + cavept_render + cavept_read_accum into host memory; scene resident as in the reference"},
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"], "traffic": None,
-                         "peak_kind": peak_kind, "kernel": "k_trace<fast>", "bytes_per_segment": bytes_per_segment, "node_visits_per_segment": vn,
-                         "triangle_tests_per_segment": vt, "note": "algorithmic bytes under our own traversal policy; working set is L2-resident so HBM is the nominal, not the binding, roof"},
+            "roofline": roofline(achieved, peaks, peak_kind, bytes_per_segment, vn, vt, seg_per_launch, launch_ms, clocks, S),
         }
         if world == 1 and not args.no_cpu_baseline:
             threads = os.cpu_count() or 1

@@ -2,8 +2,6 @@
 // Compiled for sm_100a only, with -fmad=false (see cv_common.h on float semantics).
 #include "kernels.h"
 
-#include <cstdlib>
-
 namespace cavept {
 
 // ---- generic element-wise launch -------------------------------------------------------
@@ -214,14 +212,8 @@ __global__ void __launch_bounds__(128) k_trace(const TraceParams p) {
 
 void launch_trace(CudaExec& ex, const TraceParams& p, bool fast, bool count_visits) {
     const dim3 grid((p.width + 15) / 16, (p.height + 7) / 8, 1), block(128, 1, 1);
-    static const int variant = getenv("CAVEPT_VARIANT") ? atoi(getenv("CAVEPT_VARIANT")) : 0;  // tuning experiments only
     if (fast) {
         if (count_visits) k_trace<true, true><<<grid, block, 0, ex.stream>>>(p);
-        else if (variant == 1) k_trace<true, false, 16, 8><<<grid, block, 0, ex.stream>>>(p);
-        else if (variant == 2) k_trace<true, false, 24, 8><<<grid, block, 0, ex.stream>>>(p);
-        else if (variant == 3) k_trace<true, false, 20, 12><<<grid, block, 0, ex.stream>>>(p);
-        else if (variant == 4) k_trace<true, false, 20, 4><<<grid, block, 0, ex.stream>>>(p);
-        else if (variant == 5) k_trace<true, false, 12, 8><<<grid, block, 0, ex.stream>>>(p);
         else k_trace<true, false><<<grid, block, 0, ex.stream>>>(p);
     } else {
         if (count_visits) k_trace<false, true><<<grid, block, 0, ex.stream>>>(p);

@@ -25,6 +25,8 @@ KEYS = [
     "smsp__average_warps_issue_stalled_math_pipe_throttle_per_issue_active.ratio", "smsp__average_warps_issue_stalled_no_instruction_per_issue_active.ratio",
     "smsp__average_warps_issue_stalled_dispatch_stall_per_issue_active.ratio", "smsp__average_warps_issue_stalled_lg_throttle_per_issue_active.ratio",
     "smsp__average_warps_issue_stalled_mio_throttle_per_issue_active.ratio", "smsp__average_warps_issue_stalled_barrier_per_issue_active.ratio",
+    "l1tex__data_pipe_lsu_wavefronts.sum", "l1tex__data_pipe_lsu_wavefronts.avg.pct_of_peak_sustained_elapsed", "l1tex__data_pipe_lsu_wavefronts_mem_shared.sum",
+    "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum", "lts__t_sectors.sum", "l1tex__lsu_writeback_active.avg.pct_of_peak_sustained_elapsed",
 ]
 
 
@@ -64,5 +66,43 @@ def full(src, dst):
     print(open(dst).read())
 
 
+def as_json(src, dst, spp="0", segments="0"):
+    """Machine-readable digest of one `ncu --set full` capture of k_trace; bench.py reads the
+    newest profiles/*_k_trace_ncu.json for roofline.traffic (DRAM bytes of that launch)."""
+    import json
+
+    out = subprocess.run(["ncu", "-i", src, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(out.splitlines()))
+    hdr, units, r = rows[0], rows[1], rows[2]
+
+    def val(k):
+        if k not in hdr:
+            return None
+        i = hdr.index(k)
+        v = float(r[i].replace(",", ""))
+        scale = {"Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12, "us": 1e-3, "ns": 1e-6, "s": 1e3}.get(units[i], 1.0)
+        return v * scale
+
+    d = {
+        "source": src, "kernel": r[hdr.index("Kernel Name")], "spp_of_launch": int(spp), "segments_of_launch": int(segments),
+        "duration_ms_under_ncu": val("gpu__time_duration.sum"),
+        "dram_bytes": (val("dram__bytes_read.sum") or 0) + (val("dram__bytes_write.sum") or 0),
+        "l2_bytes": (val("lts__t_sectors.sum") or 0) * 32.0,
+        "l1_global_load_bytes": (val("l1tex__t_sectors_pipe_lsu_mem_global_op_ld.sum") or 0) * 32.0,
+        "l1_lsu_wavefronts": val("l1tex__data_pipe_lsu_wavefronts.sum") or (val("SM_A.TriageCompute.l1tex__data_pipe_lsu_wavefronts.avg") or 0) * 148.0,
+        "l1_lsu_wavefronts_pct_of_peak": val("l1tex__data_pipe_lsu_wavefronts.avg.pct_of_peak_sustained_elapsed"),
+        "l1_hit_pct": val("l1tex__t_sector_hit_rate.pct"), "l2_hit_pct": val("lts__t_sector_hit_rate.pct"),
+        "l2_throughput_pct": val("lts__throughput.avg.pct_of_peak_sustained_elapsed"),
+        "dram_throughput_pct": val("gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed"),
+        "issue_active_pct": val("smsp__issue_active.avg.pct_of_peak_sustained_active"),
+        "fma_pipe_pct": val("sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active"),
+        "threads_per_instruction": val("smsp__thread_inst_executed_per_inst_executed.ratio"),
+        "registers_per_thread": val("launch__registers_per_thread"),
+        "warps_active_pct": val("sm__warps_active.avg.pct_of_peak_sustained_active"),
+    }
+    json.dump(d, open(dst, "w"), indent=1)
+    print(json.dumps(d, indent=1))
+
+
 if __name__ == "__main__":
-    {"launches": launches, "full": full}[sys.argv[1]](sys.argv[2], sys.argv[3])
+    {"launches": launches, "full": full, "json": as_json}[sys.argv[1]](*sys.argv[2:])

@@ -96,10 +96,10 @@ def ncu_digest():
 def roofline(achieved, peaks, peak_kind, bytes_per_segment, vn, vt, seg_per_launch, launch_ms, clocks, spp):
     """The contract's object quotes ALGORITHMIC gather bytes against the HBM peak.  That ratio is
     NOT a speed-of-light claim for this kernel: the 262k-triangle working set (~35 MB) lives in the
-    126 MB L2, DRAM moves ~1 byte per segment (`traffic`), and what the kernel saturates is the
-    L1TEX data pipe -- one wavefront per (lane, 32-byte gather) -- so `binding` carries that roof:
-    wavefronts per segment from the committed ncu capture x the live segment rate, against
-    1 wavefront / clock / SM at the sampled SM clock."""
+    126 MB L2 and DRAM moves < 1 byte per segment (`traffic`).  `binding` carries what ncu says the
+    kernel is actually limited by: unit utilisations from the committed capture, plus the L1TEX
+    gather rate (one wavefront per lane per 32-byte gather; wavefronts per segment from the capture
+    x the live segment rate, against 1 wavefront / clock / SM at the sampled SM clock)."""
     r = {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"], "traffic": None,
          "peak_kind": peak_kind, "kernel": "k_trace<fast>", "bytes_per_segment": bytes_per_segment, "node_visits_per_segment": vn,
          "triangle_tests_per_segment": vt,
@@ -113,10 +113,14 @@ def roofline(achieved, peaks, peak_kind, bytes_per_segment, vn, vt, seg_per_laun
         mhz = (clocks or {}).get("sm_mhz") or peaks.get("sm_max_mhz") or 1965.0
         peak_wf = 148 * mhz * 1e6
         ach_wf = wf_per_seg * seg_per_launch / (launch_ms * 1e-3)
-        r["binding"] = {"unit": "l1tex data-pipe LSU wavefronts/s", "wavefronts_per_segment": wf_per_seg, "achieved": ach_wf, "peak": peak_wf, "frac": ach_wf / peak_wf,
-                        "ncu_pct_of_peak_in_capture": d["l1_lsu_wavefronts_pct_of_peak"], "l2_hit_pct": d["l2_hit_pct"], "l2_throughput_pct": d["l2_throughput_pct"],
-                        "l2_bytes_per_segment": d["l2_bytes"] / d["segments_of_launch"], "dram_bytes_per_segment": d["dram_bytes"] / d["segments_of_launch"],
-                        "fma_pipe_pct": d["fma_pipe_pct"], "issue_active_pct": d["issue_active_pct"]}
+        units = {"instruction issue slots": d["issue_active_pct"], "l1tex data-pipe LSU wavefronts": d["l1_lsu_wavefronts_pct_of_peak"],
+                 "l2 throughput": d["l2_throughput_pct"], "fma pipe": d["fma_pipe_pct"], "dram throughput": d["dram_throughput_pct"]}
+        top = max(units, key=lambda k: units[k] or 0.0)
+        r["binding"] = {"most_utilised_unit": top, "pct_of_peak_in_capture": units, "active_threads_per_warp_instruction": d["threads_per_instruction"],
+                        "warps_active_pct": d["warps_active_pct"], "registers_per_thread": d["registers_per_thread"],
+                        "l1_wavefronts_per_segment": wf_per_seg, "l1_wavefronts_per_s_live": ach_wf, "l1_wavefronts_per_s_peak": peak_wf, "l1_wavefront_frac_live": ach_wf / peak_wf,
+                        "l2_hit_pct": d["l2_hit_pct"], "l2_bytes_per_segment": d["l2_bytes"] / d["segments_of_launch"], "dram_bytes_per_segment": d["dram_bytes"] / d["segments_of_launch"],
+                        "note": "a divergent gather kernel: no single unit saturates; issue slots (with ~18 of 32 lanes active per instruction) and the L1 gather pipe share the bound"}
     return r
 
 
@@ -303,12 +307,13 @@ def main():
         peaks, peak_kind = measured_peaks()
         seg_per_launch = segments / max(args.steps, 1)
         launch_ms = elapsed_ms / max(args.steps, 1)  # flush + launch; the flush is < 0.1 ms
-        # algorithmic bytes per segment, own traversal policy: 32 B per node visited,
-        # 48 B per triangle tested, 112 B shading gather (16 B indices + 3 x 32 B vertices) per hit
-        # segment (upper bound: every segment), + 32 B per pixel per launch of accumulator traffic
+        # algorithmic bytes per segment, own traversal policy: 16 B per node record
+        # visited (a sibling pair is one 32-byte QPair), 64 B per triangle tested (one FastTri
+        # record), 96 B shading gather (64 B normals record + 32 B material) per hit segment
+        # (upper bound: every segment), + 32 B per pixel per sample of accumulator traffic
         pixels = WIDTH * HEIGHT
-        bytes_per_segment = vn * 32.0 + vt * 48.0 + 112.0
-        algo_bytes = seg_per_launch * bytes_per_segment + 32.0 * pixels
+        bytes_per_segment = vn * 16.0 + vt * 64.0 + 96.0
+        algo_bytes = seg_per_launch * bytes_per_segment + 32.0 * pixels * S
         achieved = algo_bytes / (launch_ms * 1e-3) / 1e9
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": max_ms / max(args.steps, 1),

@@ -78,6 +78,8 @@ struct cavept_ctx {
     DevBuf<GpuPtMaterial> d_materials;
     // production layout
     DevBuf<FastNode> d_fnodes;
+    DevBuf<QPair> d_qpairs;
+    float grid_origin[3] = { 0, 0, 0 }, grid_scale[3] = { 1, 1, 1 };
     DevBuf<FastTri> d_ftris, d_fnormals;
     DevBuf<int> d_inst_prim_off, d_inst_tri_off;
     DevBuf<F4> d_prim_bmin, d_prim_bmax;
@@ -219,6 +221,7 @@ int build_world(cavept_ctx* ctx) {
     CU(ctx, ctx->d_w_counters.reserve(4));
     CU(ctx, ctx->d_w_root_acc.reserve(12));
     CU(ctx, ctx->d_fnodes.reserve(2 * pairs_cap));
+    CU(ctx, ctx->d_qpairs.reserve(pairs_cap));
     CU(ctx, ctx->d_ftris.reserve(P));
     CU(ctx, ctx->d_fnormals.reserve(P));
     ctx->ex.scan_tmp = ctx->d_scan_tmp.ptr;
@@ -250,6 +253,7 @@ int build_world(cavept_ctx* ctx) {
     b.counters = ctx->d_w_counters.ptr;
     b.root_acc = ctx->d_w_root_acc.ptr;
     b.fnodes = ctx->d_fnodes.ptr;
+    b.qpairs = ctx->d_qpairs.ptr;
     b.ftris = ctx->d_ftris.ptr;
     b.fnormals = ctx->d_fnormals.ptr;
 
@@ -272,7 +276,11 @@ int build_world(cavept_ctx* ctx) {
     ctx->stats.fast_build_levels = rep.levels;
     ctx->stats.fast_build_launches = (int)(ctx->ex.launches - launches_before);
     ctx->n_pairs = rep.n_pairs;
-    ctx->root_ref = rep.root_ref;
+    ctx->root_ref = wb_quantised_ref(rep.root_ref);
+    for (int k = 0; k < 3; ++k) {
+        ctx->grid_origin[k] = rep.grid_origin[k];
+        ctx->grid_scale[k] = rep.grid_scale[k];
+    }
     ctx->fast_levels = rep.levels;
     ctx->stats.fast_node_count = 2 * rep.n_pairs;
     return CAVEPT_OK;
@@ -415,7 +423,7 @@ CAVEPT_API void cavept_destroy(cavept_ctx* ctx) {
     cudaSetDevice(ctx->device);
     if (ctx->ex.stream) cudaStreamSynchronize(ctx->ex.stream);
     ctx->d_vertices.release(); ctx->d_indices.release(); ctx->d_nodes.release(); ctx->d_meshes.release(); ctx->d_materials.release();
-    ctx->d_fnodes.release(); ctx->d_ftris.release(); ctx->d_fnormals.release(); ctx->d_inst_prim_off.release(); ctx->d_inst_tri_off.release();
+    ctx->d_fnodes.release(); ctx->d_qpairs.release(); ctx->d_ftris.release(); ctx->d_fnormals.release(); ctx->d_inst_prim_off.release(); ctx->d_inst_tri_off.release();
     ctx->d_prim_bmin.release(); ctx->d_prim_bmax.release(); ctx->d_w_order.release(); ctx->d_w_order_next.release(); ctx->d_w_node_of.release();
     ctx->d_w_node_of_next.release(); ctx->d_w_scan.release(); ctx->d_w_counters.release(); ctx->d_w_flags.release(); ctx->d_w_items.release();
     ctx->d_w_items_next.release(); ctx->d_w_bins.release(); ctx->d_w_root_acc.release();
@@ -640,6 +648,11 @@ CAVEPT_API int cavept_render(cavept_ctx* ctx, int first_frame_index, int n_frame
     p.materials = ctx->d_materials.ptr;
     p.mesh_count = (int)ctx->gpu_meshes.size();
     p.fnodes = ctx->d_fnodes.ptr;
+    p.qpairs = ctx->d_qpairs.ptr;
+    for (int k = 0; k < 3; ++k) {
+        p.grid_origin[k] = ctx->grid_origin[k];
+        p.grid_scale[k] = ctx->grid_scale[k];
+    }
     p.ftris = ctx->d_ftris.ptr;
     p.fnormals = ctx->d_fnormals.ptr;
     p.root_ref = ctx->root_ref;

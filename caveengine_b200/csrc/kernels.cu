@@ -190,7 +190,7 @@ int run_build_wbvh(CudaExec& ex, WBuild b, WReport* report) { return build_wbvh(
 // primary rays of a warp are coherent.  Replaces Dispatch(ceil(W/16), ceil(H/16), 1) of a
 // 16x16 work group (cave/engine/render_graph/common_passes.cpp:990-997).
 template<bool kFast, bool kCount, int kQuorum = kStepQuorum, int kBatch = kShadeBatch>
-__global__ void __launch_bounds__(128) k_trace(const TraceParams p) {
+__global__ void __launch_bounds__(128, 8) k_trace(const TraceParams p) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int x = blockIdx.x * 16 + (warp & 1) * 8 + (lane & 7);
     const int y = blockIdx.y * 8 + (warp >> 1) * 4 + (lane >> 3);

@@ -18,7 +18,7 @@ namespace cavept {
 
 constexpr float kEpsilon = 1.1920929e-7f;  // EPSILON, shared_path_tracer.h:24
 constexpr float kRayTMax = 999999999.0f;   // RAY_T_MAX, :27
-constexpr int kFastLeafMax = 4;            // subtrees of <= 4 triangles are median-split in the reference (:138); they become leaves here
+constexpr int kFastLeafMax = 2;            // leaves of the production tree hold at most this many triangles (measured on B200: 2 beats 4 and 1)
 constexpr int kStackSize = 32;  // per-lane entries in shared memory (16 KB per 128-thread block)
 
 // 32-byte node of the production layout.  Siblings are adjacent (a pair is 64 bytes).
@@ -32,10 +32,32 @@ struct alignas(16) FastNode {
 };
 static_assert(sizeof(FastNode) == 32, "FastNode");
 
+// What the tracer actually fetches: a sibling PAIR in 32 bytes = ONE 256-bit load (one L1
+// wavefront per lane instead of two).  The twelve box planes are 15-bit coordinates on a
+// per-axis grid over the scene box (cell = extent / 32767, rounded outward at build time), two
+// per word; r0/r1 are the children's references (interior = index of the child's own QPair).
+//   q[0] = c0.min.x | c0.max.x << 16   q[1] = c0.min.y | c0.max.y << 16   q[2] = c0.min.z | c0.max.z << 16
+//   q[3..5] the same for child 1
+// A coordinate g decodes with one PRMT to the float 0.5 + g / 65536 (bits 0x3F000000 | g << 8),
+// and the slab planes are t = v * I + O with I = 65536 / d_grid, O = -(32768 + o_grid) / d_grid.
+// Min and max of an axis share a word, so the PRMT selector itself picks the plane the ray
+// enters through (near) or leaves through (far) from the sign of the direction: no min/max
+// per axis in the slab test.
+struct alignas(32) QPair {
+    uint32_t q[6];
+    int r0, r1;
+};
+static_assert(sizeof(QPair) == 32, "QPair");
+constexpr float kGridCells = 32767.0f;
+constexpr uint32_t kSelLo = 0x7104u, kSelHi = 0x7324u, kSelFlip = 0x0220u;  // __byte_perm selectors: low / high half -> bytes 1..2
+
 // Pre-gathered triangle, 3 x float4.  In `ftris`: v0 = world-space A, v1 = AB = B - A,
 // v2 = AC = C - A (the two subtractions HitTriangle starts with, :94-95, done once at build
 // time -- same fp32 operations, same bits); v0.w = instance, v1.w = scene-global triangle id.
-// In `fnormals`: the three mesh-space vertex normals, v0.w = instance.  Records are padded
+// In `fnormals`: the three vertex normals times the instance's world matrix (w = 0, not
+// normalised: the shader interpolates first, transforms, then normalises, :206-210 -- the
+// transform is linear, so transforming the corners first is the same up to fp32 rounding and
+// bit-identical for an identity instance); v0.w = instance, v1.w = material id.  Records are padded
 // to 64 bytes so one triangle is two 256-bit loads from a single cache line.
 struct alignas(64) FastTri {
     F4 v0, v1, v2, pad;
@@ -51,9 +73,11 @@ struct TraceParams {
     const GpuPtMaterial* materials;
     int mesh_count;  // c_ptObjectCount
     // production layout
-    const FastNode* fnodes;
+    const FastNode* fnodes;  // fp32 boxes as built (read-back / tests); the tracer reads qpairs
+    const QPair* qpairs;
+    float grid_origin[3], grid_scale[3];  // grid coordinate = (world - origin) * scale, in [0, 32767]
     const FastTri* ftris;
-    const FastTri* fnormals;  // per FastTri slot: the three vertex normals (mesh space), v0.w = instance
+    const FastTri* fnormals;  // per FastTri slot: the three world-transformed vertex normals, v0.w = instance, v1.w = material
     int root_ref;             // node reference of the root
     // PerFrameConstantBuffer (cbuffer.hlsl.h:193-207)
     float cam_pos[3], cam_right[3], cam_up[3], cam_fwd[3];
@@ -192,9 +216,9 @@ CV_D Hit hit_scene_reference(const TraceParams& p, Ray& ray, unsigned long long*
 
 // ---- production traversal ---------------------------------------------------------------
 // One world-space tree over every (instance, triangle) pair (wbvh_body.h).  Node references
-// (one int): interior = index of the child pair's first record (children at ref, ref + 1);
-// leaf = sign bit | (count - 1) << 29 | first FastTri slot.  A node's own reference is stored
-// in its record, so one 64-byte fetch of a sibling pair yields both boxes and both references.
+// (one int): interior = index of the QPair holding the node's two children;
+// leaf = sign bit | (count - 1) << 29 | first FastTri slot.  (In the fp32 FastNode array the
+// builder emits, an interior reference is the index of the child pair's first record = 2 * QPair index.)
 constexpr int kRefSentinel = 0x7fffffff;  // bottom of the stack: nothing left to traverse
 CV_HD bool ref_is_interior(int r) { return (uint32_t)r < (uint32_t)kRefSentinel; }
 CV_HD int make_leaf_ref(int first_slot, int count) { return (int)(0x80000000u | ((uint32_t)(count - 1) << 29) | (uint32_t)first_slot); }
@@ -212,10 +236,12 @@ CV_HD int make_leaf_ref(int first_slot, int count) { return (int)(0x80000000u | 
 struct Walk {
     int* stack;
     int stride;
-    int sp;          // entry 0 holds the sentinel
+    int sp;          // entries in shared memory; entry 0 holds the sentinel
+    int top;         // the top of the stack lives in a register: a pop never waits for shared memory
     int ref;         // node reference being processed (interior, leaf, or the sentinel)
     int q0, q1;      // postponed leaves (0 = empty); q0 is the older
-    F3 inv, oinv;    // 1/d and -o/d of the segment's ray
+    F3 inv, oinv;    // slab planes: t = v * inv + oinv for a decoded grid coordinate v (see QPair)
+    uint32_t near_x, near_y, near_z;  // PRMT selectors of the entry plane per axis (exit = ^ kSelFlip)
     int hit_slot;
     float hit_u, hit_v;
 };
@@ -230,53 +256,77 @@ CV_HD float slab_recip(float d) {
 CV_D void walk_begin(const TraceParams& p, Walk& w, const Ray& ray) {
     w.stack[0] = kRefSentinel;
     w.sp = 1;
+    w.top = kRefSentinel;
     w.ref = p.root_ref;
     w.q0 = 0;
     w.q1 = 0;
     w.hit_slot = -1;
     w.hit_u = 0.0f;
     w.hit_v = 0.0f;
-    w.inv = f3(slab_recip(ray.direction.x), slab_recip(ray.direction.y), slab_recip(ray.direction.z));
-    w.oinv = f3(-(ray.origin.x * w.inv.x), -(ray.origin.y * w.inv.y), -(ray.origin.z * w.inv.z));
+    // the ray in grid coordinates; t is unchanged because origin and direction scale together
+    const F3 og = f3((ray.origin.x - p.grid_origin[0]) * p.grid_scale[0], (ray.origin.y - p.grid_origin[1]) * p.grid_scale[1], (ray.origin.z - p.grid_origin[2]) * p.grid_scale[2]);
+    const F3 ig = f3(slab_recip(ray.direction.x * p.grid_scale[0]), slab_recip(ray.direction.y * p.grid_scale[1]), slab_recip(ray.direction.z * p.grid_scale[2]));
+    w.inv = 65536.0f * ig;
+    w.oinv = f3(-((32768.0f + og.x) * ig.x), -((32768.0f + og.y) * ig.y), -((32768.0f + og.z) * ig.z));
+    w.near_x = (f2u(ig.x) >> 31) ? kSelHi : kSelLo;
+    w.near_y = (f2u(ig.y) >> 31) ? kSelHi : kSelLo;
+    w.near_z = (f2u(ig.z) >> 31) ? kSelHi : kSelLo;
+}
+
+CV_D void walk_push(Walk& w, int r) {
+    w.stack[w.sp * w.stride] = w.top;
+    ++w.sp;
+    w.top = r;
+}
+CV_D int walk_pop(Walk& w) {
+    const int r = w.top;
+    w.top = w.stack[(--w.sp) * w.stride];  // consumed by the NEXT pop or push: the latency is hidden
+    return r;
+}
+
+// 15-bit grid coordinate (low or high half of `w`, picked by the selector) -> the float
+// 0.5 + g / 65536: one PRMT
+CV_HD float q_sel(uint32_t w, uint32_t sel) {
+#if defined(__CUDA_ARCH__)
+    return __uint_as_float(__byte_perm(w, 0x3F000000u, sel));
+#else
+    return u2f(0x3F000000u | ((sel == kSelLo ? (w & 0xffffu) : (w >> 16)) << 8));
+#endif
 }
 
 // A leaf held in `ref` moves to the queue when there is room; the lane pops its next node.
 CV_D void walk_park_leaf(Walk& w) {
     if (w.ref < 0 && w.q1 == 0) {
         if (w.q0 == 0) w.q0 = w.ref; else w.q1 = w.ref;
-        w.ref = w.stack[(--w.sp) * w.stride];
+        w.ref = walk_pop(w);
     }
 }
 
-// One interior step: fetch the sibling pair, slab-test both boxes against [0, ray.t], descend
+// One interior step: fetch the sibling pair (QPair), slab-test both boxes against [0, ray.t], descend
 // into the nearer hit child and push the other.  Same interval logic as HitBvh (:133-149);
 // boxes entirely behind the origin or beyond the current hit are rejected.
 template<bool kCount>
 CV_D void walk_step(const TraceParams& p, Walk& w, float ray_t, unsigned long long* cnt) {
-    const F8 c0 = ld256(p.fnodes + w.ref);      // mn.xyz, ref, mx.xyz, count
-    const F8 c1 = ld256(p.fnodes + w.ref + 1);  // same cache line
+    const F8 c = ld256(p.qpairs + w.ref);  // the whole pair: one 256-bit load
     if (kCount) cnt[1] += 2;
-    const float ax = cv_fma(c0.a, w.inv.x, w.oinv.x), bx = cv_fma(c0.e, w.inv.x, w.oinv.x);
-    const float ay = cv_fma(c0.b, w.inv.y, w.oinv.y), by = cv_fma(c0.f, w.inv.y, w.oinv.y);
-    const float az = cv_fma(c0.c, w.inv.z, w.oinv.z), bz = cv_fma(c0.g, w.inv.z, w.oinv.z);
-    const float cx = cv_fma(c1.a, w.inv.x, w.oinv.x), dx = cv_fma(c1.e, w.inv.x, w.oinv.x);
-    const float cy = cv_fma(c1.b, w.inv.y, w.oinv.y), dy = cv_fma(c1.f, w.inv.y, w.oinv.y);
-    const float cz = cv_fma(c1.c, w.inv.z, w.oinv.z), dz = cv_fma(c1.g, w.inv.z, w.oinv.z);
-    const float n0 = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fmaxf(fminf(az, bz), 0.0f));
-    const float f0 = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fminf(fmaxf(az, bz), ray_t));
-    const float n1 = fmaxf(fmaxf(fminf(cx, dx), fminf(cy, dy)), fmaxf(fminf(cz, dz), 0.0f));
-    const float f1 = fminf(fminf(fmaxf(cx, dx), fmaxf(cy, dy)), fminf(fmaxf(cz, dz), ray_t));
+    const uint32_t far_x = w.near_x ^ kSelFlip, far_y = w.near_y ^ kSelFlip, far_z = w.near_z ^ kSelFlip;
+    const uint32_t q0 = f2u(c.a), q1 = f2u(c.b), q2 = f2u(c.c), q3 = f2u(c.d), q4 = f2u(c.e), q5 = f2u(c.f);
+    const float ax = cv_fma(q_sel(q0, w.near_x), w.inv.x, w.oinv.x), bx = cv_fma(q_sel(q0, far_x), w.inv.x, w.oinv.x);
+    const float ay = cv_fma(q_sel(q1, w.near_y), w.inv.y, w.oinv.y), by = cv_fma(q_sel(q1, far_y), w.inv.y, w.oinv.y);
+    const float az = cv_fma(q_sel(q2, w.near_z), w.inv.z, w.oinv.z), bz = cv_fma(q_sel(q2, far_z), w.inv.z, w.oinv.z);
+    const float cx = cv_fma(q_sel(q3, w.near_x), w.inv.x, w.oinv.x), dx = cv_fma(q_sel(q3, far_x), w.inv.x, w.oinv.x);
+    const float cy = cv_fma(q_sel(q4, w.near_y), w.inv.y, w.oinv.y), dy = cv_fma(q_sel(q4, far_y), w.inv.y, w.oinv.y);
+    const float cz = cv_fma(q_sel(q5, w.near_z), w.inv.z, w.oinv.z), dz = cv_fma(q_sel(q5, far_z), w.inv.z, w.oinv.z);
+    const float n0 = fmaxf(fmaxf(ax, ay), fmaxf(az, 0.0f)), f0 = fminf(fminf(bx, by), fminf(bz, ray_t));
+    const float n1 = fmaxf(fmaxf(cx, cy), fmaxf(cz, 0.0f)), f1 = fminf(fminf(dx, dy), fminf(dz, ray_t));
     const bool h0 = n0 <= f0, h1 = n1 <= f1;
-    const int r0 = (int)f2u(c0.d), r1 = (int)f2u(c1.d);
+    const int r0 = (int)f2u(c.g), r1 = (int)f2u(c.h);
     const bool second_first = h1 && (!h0 || n1 < n0);
-    if (h0 && h1) {
-        w.stack[w.sp * w.stride] = second_first ? r0 : r1;
-        ++w.sp;
-    }
+    if (h0 && h1) walk_push(w, second_first ? r0 : r1);
     if (h0 || h1) {
         w.ref = second_first ? r1 : r0;
     } else {
-        w.ref = w.stack[(--w.sp) * w.stride];
+        w.ref = walk_pop(w);
     }
 }
 
@@ -308,15 +358,13 @@ CV_D void walk_test_triangle(const TraceParams& p, Walk& w, const Ray& ray, floa
 
 // ---- one RayColor iteration after the scene query (:198-235).  Returns true when the
 //      path ends (miss, or MAX_BOUNCE segments traced). ---------------------------------
-CV_D bool shade_hit(const TraceParams& p, bool is_hit, int mesh_id, F3 n1, F3 n2, F3 n3, float u, float v, Ray& ray, uint32_t& state, F3& radiance,
-                    F3& throughput, int& bounce) {
+// `n` is the interpolated normal already multiplied by the instance's world matrix (:206-210,
+// before the normalize); `mat` the instance's material.
+CV_D bool shade_hit(const TraceParams& p, bool is_hit, F3 n, const GpuPtMaterial& mat, Ray& ray, uint32_t& state, F3& radiance, F3& throughput, int& bounce) {
     if (is_hit) {
         ray.origin = ray.origin + ray.t * ray.direction;
         ray.t = kRayTMax;
-        const GpuPtMesh& mesh = p.meshes[mesh_id];
-        F3 n = n1 + u * (n2 - n1) + v * (n3 - n1);
-        n = normalize3(mat_mul(mesh.transform, n, 0.0f));
-        const GpuPtMaterial& mat = p.materials[mesh.materialId];
+        n = normalize3(n);
         const float reflect_chance = rnd(state) > mat.metallic ? 0.0f : 1.0f;
         const F3 diffuse_dir = normalize3(n + random_unit_vector(state));
         F3 reflect_dir = ray.direction - 2.0f * dot3(n, ray.direction) * n;
@@ -334,17 +382,21 @@ CV_D bool shade_hit(const TraceParams& p, bool is_hit, int mesh_id, F3 n1, F3 n2
 
 CV_D bool shade_segment(const TraceParams& p, const Hit& hit, Ray& ray, uint32_t& state, F3& radiance, F3& throughput, int& bounce) {
     const bool is_hit = hit.mesh >= 0 && hit.tri >= 0;
-    F3 n1 = f3(0, 0, 0), n2 = n1, n3 = n1;
+    F3 n = f3(0, 0, 0);
+    GpuPtMaterial mat = {};
     if (is_hit) {
         const int* idx = p.indices[hit.tri].tri;
         const GpuPtVertex& va = p.vertices[idx[0]];
         const GpuPtVertex& vb = p.vertices[idx[1]];
         const GpuPtVertex& vc = p.vertices[idx[2]];
-        n1 = f3(va.normal[0], va.normal[1], va.normal[2]);
-        n2 = f3(vb.normal[0], vb.normal[1], vb.normal[2]);
-        n3 = f3(vc.normal[0], vc.normal[1], vc.normal[2]);
+        const F3 n1 = f3(va.normal[0], va.normal[1], va.normal[2]);
+        const F3 n2 = f3(vb.normal[0], vb.normal[1], vb.normal[2]);
+        const F3 n3 = f3(vc.normal[0], vc.normal[1], vc.normal[2]);
+        const GpuPtMesh& mesh = p.meshes[hit.mesh];
+        n = mat_mul(mesh.transform, n1 + hit.u * (n2 - n1) + hit.v * (n3 - n1), 0.0f);
+        mat = p.materials[mesh.materialId];
     }
-    return shade_hit(p, is_hit, hit.mesh, n1, n2, n3, hit.u, hit.v, ray, state, radiance, throughput, bounce);
+    return shade_hit(p, is_hit, n, mat, ray, state, radiance, throughput, bounce);
 }
 
 // ---- main(), path_tracer.cs.glsl:11-44: seed, jitter, camera ray -----------------------
@@ -473,16 +525,19 @@ CV_D unsigned int body_trace_pixel_fast(const TraceParams& p, int x, int y, int*
             if (need_shade) {
                 ++segments;
                 const bool is_hit = w.hit_slot >= 0;
-                F3 n1 = f3(0, 0, 0), n2 = n1, n3 = n1;
-                int instance = 0;
+                F3 n = f3(0, 0, 0);
+                GpuPtMaterial mat = {};
                 if (is_hit) {
-                    const FastTri nr = p.fnormals[w.hit_slot];
-                    n1 = f3(nr.v0.x, nr.v0.y, nr.v0.z);
-                    n2 = f3(nr.v1.x, nr.v1.y, nr.v1.z);
-                    n3 = f3(nr.v2.x, nr.v2.y, nr.v2.z);
-                    instance = (int)f2u(nr.v0.w);
+                    // world-space vertex normals and the material id, pre-gathered at build time
+                    const F8 a = ld256(&p.fnormals[w.hit_slot]);     // n1.xyz, instance, n2.xyz, material
+                    const F8 b = ld256(&p.fnormals[w.hit_slot].v2);  // n3.xyz
+                    const F3 n1 = f3(a.a, a.b, a.c), n2 = f3(a.e, a.f, a.g), n3 = f3(b.a, b.b, b.c);
+                    n = n1 + w.hit_u * (n2 - n1) + w.hit_v * (n3 - n1);
+                    const F8 m = ld256(&p.materials[(int)f2u(a.h)]);
+                    mat.baseColor[0] = m.a; mat.baseColor[1] = m.b; mat.baseColor[2] = m.c; mat.roughness = m.d;
+                    mat.emissive[0] = m.e; mat.emissive[1] = m.f; mat.emissive[2] = m.g; mat.metallic = m.h;
                 }
-                if (shade_hit(p, is_hit, instance, n1, n2, n3, w.hit_u, w.hit_v, ray, seed, radiance, throughput, bounce)) {
+                if (shade_hit(p, is_hit, n, mat, ray, seed, radiance, throughput, bounce)) {
                     F4 acc = p.accum[pix];
                     accumulate(acc, radiance, f == 0 && p.reset_first != 0);
                     p.accum[pix] = acc;

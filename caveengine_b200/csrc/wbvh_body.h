@@ -82,6 +82,8 @@ struct WBuild {
     uint32_t* root_acc;  // [0..2] scene min keys, [3..5] max keys, [6..8] centroid min keys, [9..11] centroid max keys
     // outputs
     FastNode* fnodes;
+    QPair* qpairs;  // quantised copy of fnodes, what the tracer fetches
+    float grid_origin[3], grid_scale[3];
     FastTri* ftris;
     FastTri* fnormals;
 };
@@ -377,8 +379,8 @@ CV_D void wb_body_scatter(const WBuild& b, int i) {
 }
 
 // ---- emit: slot s of the final order holds prim order[s] --------------------------------------
-// World-space vertices (the same wb_world() values the boxes were built from) and mesh-space
-// normals.  A mirroring instance (det < 0) flips the winding the reference's mesh-space
+// World-space vertices (the same wb_world() values the boxes were built from) and the vertex
+// normals times the world matrix.  A mirroring instance (det < 0) flips the winding the reference's mesh-space
 // back-face test sees (shared_path_tracer.h:106), so its triangles are stored as (A, C, B).
 CV_D void wb_body_emit(const WBuild& b, int s) {
     if (s >= b.n_prims) return;
@@ -397,10 +399,45 @@ CV_D void wb_body_emit(const WBuild& b, int s) {
     t.v2.x = ac.x; t.v2.y = ac.y; t.v2.z = ac.z; t.v2.w = 0.0f;
     t.pad.x = t.pad.y = t.pad.z = t.pad.w = 0.0f;
     b.ftris[s] = t;
-    t.v0.x = va.normal[0]; t.v0.y = va.normal[1]; t.v0.z = va.normal[2];
-    t.v1.x = vb.normal[0]; t.v1.y = vb.normal[1]; t.v1.z = vb.normal[2];
-    t.v2.x = vc.normal[0]; t.v2.y = vc.normal[1]; t.v2.z = vc.normal[2];
+    const F3 na = mat_mul(m, f3(va.normal[0], va.normal[1], va.normal[2]), 0.0f);  // the shader's own transform (:210)
+    const F3 nb = mat_mul(m, f3(vb.normal[0], vb.normal[1], vb.normal[2]), 0.0f);
+    const F3 nc = mat_mul(m, f3(vc.normal[0], vc.normal[1], vc.normal[2]), 0.0f);
+    t.v0.x = na.x; t.v0.y = na.y; t.v0.z = na.z;
+    t.v1.x = nb.x; t.v1.y = nb.y; t.v1.z = nb.z; t.v1.w = u2f((uint32_t)b.instances[inst].materialId);
+    t.v2.x = nc.x; t.v2.y = nc.y; t.v2.z = nc.z;
     b.fnormals[s] = t;
+}
+
+// ---- quantise: FastNode pair k -> QPair k --------------------------------------------------
+// Grid coordinates are rounded OUTWARD (floor for min planes, ceil for max planes) with a 1/64
+// cell margin that covers the fp32 rounding of this conversion and of the tracer's grid-space
+// ray set-up (each below 2^-8 cell), so a quantised box always contains the fp32 box.
+CV_HD uint32_t wb_grid_lo(float v, float origin, float scale) {
+    float g = floorf((v - origin) * scale - 0.015625f);
+    g = g < 0.0f ? 0.0f : (g > kGridCells ? kGridCells : g);
+    return (uint32_t)(int)g;
+}
+CV_HD uint32_t wb_grid_hi(float v, float origin, float scale) {
+    float g = ceilf((v - origin) * scale + 0.015625f);
+    g = g < 0.0f ? 0.0f : (g > kGridCells ? kGridCells : g);
+    return (uint32_t)(int)g;
+}
+CV_HD int wb_quantised_ref(int r) { return ref_is_interior(r) ? (r >> 1) : r; }
+
+CV_D void wb_body_quantise(const WBuild& b, int k, int n_pairs) {
+    if (k >= n_pairs) return;
+    QPair o;
+    for (int s = 0; s < 2; ++s) {
+        const FastNode n = b.fnodes[2 * k + s];
+        uint32_t lo[3], hi[3];
+        for (int c = 0; c < 3; ++c) {
+            lo[c] = wb_grid_lo(n.mn[c], b.grid_origin[c], b.grid_scale[c]);
+            hi[c] = wb_grid_hi(n.mx[c], b.grid_origin[c], b.grid_scale[c]);
+        }
+        for (int c = 0; c < 3; ++c) o.q[3 * s + c] = lo[c] | (hi[c] << 16);
+        if (s == 0) o.r0 = wb_quantised_ref(n.a); else o.r1 = wb_quantised_ref(n.a);
+    }
+    b.qpairs[k] = o;
 }
 
 struct FnWbPrim { WBuild b; CV_D void operator()(int i) const { wb_body_prim(b, i); } };
@@ -411,6 +448,7 @@ struct FnWbSplit { WBuild b; int n; CV_D void operator()(int i) const { wb_body_
 struct FnWbFlag { WBuild b; CV_D void operator()(int i) const { wb_body_flag(b, i); } };
 struct FnWbScatter { WBuild b; CV_D void operator()(int i) const { wb_body_scatter(b, i); } };
 struct FnWbEmit { WBuild b; CV_D void operator()(int i) const { wb_body_emit(b, i); } };
+struct FnWbQuantise { WBuild b; int n; CV_D void operator()(int i) const { wb_body_quantise(b, i, n); } };
 
 struct WReport {
     int levels;
@@ -419,6 +457,7 @@ struct WReport {
     int error_bits;
     float scene_mn[3], scene_mx[3];
     float pad;
+    float grid_origin[3], grid_scale[3];
 };
 
 // Host-side level loop (Exec = CudaExec on the device, EmuExec in the test emulator).
@@ -444,6 +483,13 @@ int build_wbvh(Exec& ex, WBuild b, WReport* rep) {
     }
     b.pad = scale * (1.0f / 1048576.0f) + 1e-30f;
     rep->pad = b.pad;
+    for (int k = 0; k < 3; ++k) {  // the quantisation grid spans the padded scene box plus two spare cells on each side,
+        // so outward rounding never meets the clamp at 0 / 32767
+        const float lo = rep->scene_mn[k] - b.pad, hi = rep->scene_mx[k] + b.pad;
+        const float scale = (kGridCells - 4.0f) / (hi - lo);
+        b.grid_scale[k] = rep->grid_scale[k] = scale;
+        b.grid_origin[k] = rep->grid_origin[k] = lo - 2.0f / scale;
+    }
     ex.launch(b.n_prims, FnWbInit{ b });
     if (b.n_prims <= kFastLeafMax) {
         rep->root_ref = make_leaf_ref(0, b.n_prims);
@@ -492,6 +538,7 @@ int build_wbvh(Exec& ex, WBuild b, WReport* rep) {
         int* tn = b.node_of; b.node_of = b.node_of_next; b.node_of_next = tn;
     }
     ex.launch(b.n_prims, FnWbEmit{ b });
+    ex.launch(rep->n_pairs, FnWbQuantise{ b, rep->n_pairs });
     return 0;
 }
 

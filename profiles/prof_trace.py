@@ -20,4 +20,9 @@ pt.reset_stats()
 pt.render(1, spp, sync=True)
 st = pt.stats()
 print("segments", st["segments"], "ms", st["last_render_ms"], "Mseg/s", st["segments"] / st["last_render_ms"] / 1e3, "build_ms", st["last_build_ms"], "fast_build_ms", st["last_fast_build_ms"], "levels", st["fast_build_levels"], "launches", st["fast_build_launches"], "fast_nodes", st["fast_node_count"])
+pt.set_count_visits(True)
+pt.reset_stats()
+pt.render(1 << 20, 1, sync=True)
+c = pt.stats()
+print("per segment: node records", c["node_visits"] / c["segments"], "triangle tests", c["triangle_tests"] / c["segments"])
 pt.close()

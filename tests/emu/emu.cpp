@@ -85,10 +85,11 @@ EMU_API int emu_bvh_build(const GpuPtVertex* vertices, const GpuPtIndex* indices
 }
 
 // Production (world-space) BVH exactly as cavept_api.cu builds it.  inst_prim_off has
-// n_inst + 1 entries, inst_tri_off n_inst.  fnodes needs 2 * (n_prims + 8) entries, ftris /
+// n_inst + 1 entries, inst_tri_off n_inst.  fnodes needs 2 * (n_prims + 8) entries, qpairs n_prims + 8, ftris /
 // fnormals n_prims.  Returns 0 ok; report = {levels, n_pairs, root_ref, error_bits}.
 EMU_API int emu_wbvh_build(const GpuPtVertex* vertices, const GpuPtIndex* indices, const GpuPtMesh* instances, int n_inst, const int* inst_prim_off,
-                           const int* inst_tri_off, int force_median, FastNode* fnodes, FastTri* ftris, FastTri* fnormals, int* report, float* out_pad) {
+                           const int* inst_tri_off, int force_median, FastNode* fnodes, QPair* qpairs, FastTri* ftris, FastTri* fnormals, int* report, float* out_pad,
+                           float* out_grid) {
     const int P = inst_prim_off[n_inst];
     const size_t items_cap = (size_t)P / 2 + 8, pairs_cap = (size_t)P + 8;
     std::vector<F4> bmin(P), bmax(P);
@@ -122,6 +123,7 @@ EMU_API int emu_wbvh_build(const GpuPtVertex* vertices, const GpuPtIndex* indice
     b.counters = counters.data();
     b.root_acc = root_acc.data();
     b.fnodes = fnodes;
+    b.qpairs = qpairs;
     b.ftris = ftris;
     b.fnormals = fnormals;
     EmuExec ex;
@@ -129,9 +131,15 @@ EMU_API int emu_wbvh_build(const GpuPtVertex* vertices, const GpuPtIndex* indice
     const int rc = build_wbvh(ex, b, &rep);
     report[0] = rep.levels;
     report[1] = rep.n_pairs;
-    report[2] = rep.root_ref;
+    report[2] = wb_quantised_ref(rep.root_ref);
     report[3] = rep.error_bits;
     if (out_pad) *out_pad = rep.pad;
+    if (out_grid) {
+        for (int k = 0; k < 3; ++k) {
+            out_grid[k] = rep.grid_origin[k];
+            out_grid[3 + k] = rep.grid_scale[k];
+        }
+    }
     return rc;
 }
 
@@ -146,7 +154,7 @@ struct EmuCamera {
 };
 
 EMU_API long long emu_render(const GpuPtVertex* vertices, const GpuPtIndex* indices, const GpuPtBvh* bvhs, const GpuPtMesh* meshes, int mesh_count,
-                             const GpuPtMaterial* materials, const FastNode* fnodes, const FastTri* ftris, const FastTri* fnormals, int root_ref,
+                             const GpuPtMaterial* materials, const FastNode* fnodes, const QPair* qpairs, const float* grid, const FastTri* ftris, const FastTri* fnormals, int root_ref,
                              const EmuCamera* cam, int max_bounce, int width, int height, int first_frame, int n_frames, int reset_first, float* accum,
                              int fast, unsigned long long* counters) {
     TraceParams p{};
@@ -157,6 +165,11 @@ EMU_API long long emu_render(const GpuPtVertex* vertices, const GpuPtIndex* indi
     p.materials = materials;
     p.mesh_count = mesh_count;
     p.fnodes = fnodes;
+    p.qpairs = qpairs;
+    for (int k = 0; k < 3; ++k) {
+        p.grid_origin[k] = grid[k];
+        p.grid_scale[k] = grid[3 + k];
+    }
     p.ftris = ftris;
     p.fnormals = fnormals;
     p.root_ref = root_ref;

@@ -76,12 +76,15 @@ class EmuScene:
         P = int(self.inst_prim_off[-1])
         self.n_prims = P
         self.fnodes = np.zeros(2 * (P + 8), dtype=FASTNODE_DT)
+        self.qpairs = np.zeros((P + 8, 8), dtype=np.uint32)  # QPair: q[6], r0, r1
+        self.grid = np.zeros(6, dtype=np.float32)            # origin xyz, scale xyz
         self.ftris = np.zeros(P, dtype=FASTTRI_DT)
         self.fnormals = np.zeros(P, dtype=FASTTRI_DT)
         report = np.zeros(4, dtype=np.int32)
         pad = C.c_float()
         self.wrc = self.lib.emu_wbvh_build(_p(asm.vertices), _p(asm.indices), _p(asm.meshes), C.c_int(n_inst), _p(self.inst_prim_off), _p(self.inst_tri_off),
-                                           C.c_int(1 if force_median else 0), _p(self.fnodes), _p(self.ftris), _p(self.fnormals), _p(report), C.byref(pad))
+                                           C.c_int(1 if force_median else 0), _p(self.fnodes), _p(self.qpairs), _p(self.ftris), _p(self.fnormals), _p(report), C.byref(pad),
+                                           _p(self.grid))
         self.fast_levels, self.n_pairs, self.root_ref, self.wb_error_bits = [int(v) for v in report]
         self.pad = pad.value
 
@@ -94,7 +97,7 @@ class EmuScene:
         counters = (C.c_ulonglong * 3)()
         a = self.asm
         segs = self.lib.emu_render(_p(a.vertices), _p(a.indices), _p(self.nodes), _p(a.meshes), C.c_int(a.meshes.shape[0]), _p(a.materials), _p(self.fnodes),
-                                   _p(self.ftris), _p(self.fnormals), C.c_int(self.root_ref), C.byref(cam), C.c_int(max_bounce), C.c_int(width),
+                                   _p(self.qpairs), _p(self.grid), _p(self.ftris), _p(self.fnormals), C.c_int(self.root_ref), C.byref(cam), C.c_int(max_bounce), C.c_int(width),
                                    C.c_int(height), C.c_int(first_frame), C.c_int(n_frames), C.c_int(1 if reset_first else 0), _p(accum), C.c_int(1 if fast else 0),
                                    counters)
         return accum, {"segments": int(segs), "node_visits": int(counters[1]), "tri_tests": int(counters[2])}

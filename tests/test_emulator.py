@@ -155,6 +155,20 @@ def _world_tree_check(emu, asm, sc):
         return total
 
     assert visit(emu.root_ref, 0, None) == P
+    # the quantised pairs the tracer fetches: each 15-bit grid box contains its fp32 box, and
+    # the references are the fp32 records' (interior: index of the child's own pair)
+    org, scl = emu.grid[:3].astype(np.float64), emu.grid[3:].astype(np.float64)
+    for k in range(emu.n_pairs):
+        q = emu.qpairs[k]
+        for s_ in (0, 1):
+            w = [int(v) for v in q[3 * s_: 3 * s_ + 3]]
+            lo = np.array([v & 0xFFFF for v in w], dtype=np.float64)  # per axis: min | max << 16
+            hi = np.array([v >> 16 for v in w], dtype=np.float64)
+            assert np.all(hi <= 32767) and np.all(lo >= 0)
+            n = fn[2 * k + s_]
+            assert np.all(org + lo / scl <= n["mn"].astype(np.float64)) and np.all(org + hi / scl >= n["mx"].astype(np.float64))
+            a, r = int(n["a"]), int(np.int32(q[6 + s_]))
+            assert r == (a >> 1 if a >= 0 else a)
     assert np.all(seen_slots == 1)
     assert np.all(seen_pairs[: emu.n_pairs] == 1)
     assert max_depth <= emu.fast_levels
@@ -176,7 +190,12 @@ def _world_tree_check(emu, asm, sc):
     assert np.allclose(verts, world, rtol=1e-6, atol=1e-6)
     nrm = asm.vertices["normal"][asm.indices["tri"][tri]]
     nrm[flipped] = nrm[flipped][:, [0, 2, 1]]
-    assert np.array_equal(emu.fnormals["v1"][:, :3], nrm[:, 1]) and np.array_equal(emu.fnormals["v0"][:, 3].view(np.int32), inst)
+    nrm_world = np.einsum("pcr,pvc->pvr", m[:, :3, :3], nrm)  # normals times the world matrix (w = 0), not normalised
+    assert np.allclose(emu.fnormals["v1"][:, :3], nrm_world[:, 1], rtol=1e-6, atol=1e-7) and np.allclose(emu.fnormals["v2"][:, :3], nrm_world[:, 2], rtol=1e-6, atol=1e-7)
+    identity = np.all(m == np.eye(4, dtype=np.float32)[None], axis=(1, 2))
+    assert np.array_equal(emu.fnormals["v0"][identity][:, :3] + 0.0, nrm[identity][:, 0] + 0.0)  # bit-exact for identity instances (up to the sign of zero)
+    assert np.array_equal(emu.fnormals["v0"][:, 3].view(np.int32), inst)
+    assert np.array_equal(emu.fnormals["v1"][:, 3].view(np.int32), asm.meshes["material"][inst])
     return max_depth
 
 

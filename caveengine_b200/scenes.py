@@ -413,3 +413,105 @@ def tiny_scene(seed: int = 7) -> Scene:
     ]
     cam = look_at((2.0, 2.4, -2.2), (2.0, 0.8, 2.0), fov=55.0)
     return Scene("tiny", [hf, ball, box, light], inst, mats, cam)
+
+
+# ----------------------------------------------------------------------------
+# config 4: breakfast-room-shaped scene, 1,048,576 triangles, emissive panels + glossy tableware
+# ----------------------------------------------------------------------------
+def breakfast_scene(seed: int = 4242) -> Scene:
+    """Closed room (10 x 4 x 8 m) with two ceiling light panels, a long table with glossy
+    (metallic 0.9, roughness 0.1) tableware, eight chairs and a blinds wall.  17 meshes,
+    12 materials, 1,048,576 triangles."""
+    X, Y, Z = 10.0, 4.0, 8.0
+    meshes: List[Mesh] = []
+    inst: List[Instance] = []
+
+    def add(mesh: Mesh, material: int, tf=None):
+        meshes.append(mesh)
+        inst.append(Instance(len(meshes) - 1, material, mat_identity() if tf is None else tf))
+
+    add(_plane_xz(256, 256, -X / 2, X / 2, -Z / 2, Z / 2, 0.0, seed + 1, 0.004, up=True), 0)  # floor 131072
+    add(_plane_xz(128, 128, -X / 2, X / 2, -Z / 2, Z / 2, Y, seed + 2, 0.004, up=False), 1)  # ceiling 32768
+    add(_wall_xy(256, 128, -X / 2, X / 2, 0.0, Y, Z / 2, seed + 3, 0.01, face_neg_z=True), 1)  # 65536
+    add(_wall_xy(256, 128, -X / 2, X / 2, 0.0, Y, -Z / 2, seed + 4, 0.01, face_neg_z=False), 1)  # 65536
+    add(_wall_zy(256, 128, -Z / 2, Z / 2, 0.0, Y, X / 2, seed + 5, 0.01, face_neg_x=True), 2)  # 65536
+    add(_wall_zy(256, 128, -Z / 2, Z / 2, 0.0, Y, -X / 2, seed + 6, 0.01, face_neg_x=False), 2)  # 65536
+    # two emissive ceiling panels, 64 x 64 quads each -> 16384 in one mesh
+    panels = merge([_plane_xz(64, 64, x0, x0 + 2.0, -1.5, 1.5, Y - 0.05, seed + 7 + i, 0.0, up=False) for i, x0 in enumerate((-3.5, 1.5))])
+    add(panels, 3)
+    # table top (both faces) 2 x 256 x 128 quads -> 131072, four legs 64 x 64 -> 32768
+    top = merge([_plane_xz(256, 128, -3.0, 3.0, -1.0, 1.0, 0.95, seed + 10, 0.002, up=True), _plane_xz(256, 128, -3.0, 3.0, -1.0, 1.0, 0.90, seed + 11, 0.002, up=False)])
+    add(top, 4)
+    legs = merge([translate(_cylinder(64, 64, 0.06, 0.0, 0.9, seed + 12 + i, flute=0.0), (x, 0.0, z)) for i, (x, z) in enumerate([(-2.8, -0.85), (2.8, -0.85), (-2.8, 0.85), (2.8, 0.85)])])
+    add(legs, 5)
+    # glossy tableware: teapot-ish blob 256 x 128 -> 65536; 8 cups 64 x 32 -> 32768; 8 plates (squashed spheres) 64 x 32 -> 32768
+    add(_sphere(256, 128, 0.28, seed + 20, bump=0.06, squash=0.85), 6, mat_trs((0.0, 1.22, 0.0), yaw_deg=20.0))
+    seats = [(-2.25 + 1.5 * i, s) for s in (-1, 1) for i in range(4)]
+    add(merge([translate(_sphere(64, 32, 0.07, seed + 30 + i, bump=0.0, squash=1.3), (x, 1.05, 0.55 * s)) for i, (x, s) in enumerate(seats)]), 7)
+    add(merge([translate(_sphere(64, 32, 0.16, seed + 40 + i, bump=0.0, squash=0.08), (x, 0.97, 0.62 * s)) for i, (x, s) in enumerate(seats)]), 8)
+    # eight chairs: seat + back as displaced sheets, 2 x 64 x 64 quads each chair -> 131072, instanced from one mesh per side
+    def chair(k):
+        seat = _plane_xz(64, 64, -0.25, 0.25, -0.25, 0.25, 0.5, seed + 50 + k, 0.004, up=True)
+        back = _wall_xy(64, 64, -0.25, 0.25, 0.5, 1.1, 0.25, seed + 60 + k, 0.004, face_neg_z=True)
+        return merge([seat, back])
+
+    add(merge([translate(chair(i), (x, 0.0, 1.45)) for i, (x, s) in enumerate(seats[:4])]), 9)  # 65536
+    add(merge([translate(chair(4 + i), (x, 0.0, 1.45)) for i, (x, s) in enumerate(seats[:4])]), 9, mat_trs((0.0, 0.0, 0.0), yaw_deg=180.0))  # 65536
+    # blinds: 32 slats of 64 x 32 quads in front of the +x wall -> 131072
+    slats = []
+    for i in range(32):
+        y = 0.6 + 0.09 * i
+
+        def fn(u, v, iu, iv, y=y, i=i):
+            return X / 2 - 0.15 - 0.06 * v, y + 0.04 * v + _relief(seed + 70 + i, iu, iv, 0.001), -3.0 + 6.0 * u
+
+        slats.append(grid_mesh(64, 32, fn, flip=False))
+    add(merge(slats), 10)
+    # sideboard: a bumpy box-like blob 128 x 64 -> 16384, and a vase 128 x 128 -> 32768, lamp globe 128 x 64 -> 16384
+    add(_sphere(128, 64, 0.5, seed + 80, bump=0.03, squash=0.7), 11, mat_trs((-4.0, 0.45, -3.0), s=(2.0, 1.0, 0.8)))
+    add(_sphere(128, 128, 0.22, seed + 81, bump=0.04, squash=1.8), 6, mat_trs((-4.0, 1.25, -3.0)))
+    assert sum(meshes[i.mesh].n_tris for i in inst) == 1 << 20
+    mats = [
+        Material((0.55, 0.42, 0.30), 0.6, 0.0, 0.0),  # 0 floor wood
+        Material((0.85, 0.85, 0.82), 0.95, 0.0, 0.0),  # 1 plaster
+        Material((0.70, 0.74, 0.80), 0.9, 0.0, 0.0),  # 2 painted walls
+        Material((1.0, 0.96, 0.88), 1.0, 0.0, 12.0),  # 3 emissive panels
+        Material((0.80, 0.80, 0.78), 0.25, 0.0, 0.0),  # 4 table top
+        Material((0.30, 0.30, 0.32), 0.3, 0.9, 0.0),  # 5 legs, brushed metal
+        Material((0.95, 0.93, 0.88), 0.1, 0.9, 0.0),  # 6 glossy teapot / vase
+        Material((0.90, 0.85, 0.70), 0.1, 0.9, 0.0),  # 7 cups
+        Material((0.92, 0.92, 0.95), 0.1, 0.9, 0.0),  # 8 plates
+        Material((0.45, 0.30, 0.20), 0.7, 0.0, 0.0),  # 9 chairs
+        Material((0.88, 0.88, 0.85), 0.5, 0.5, 0.0),  # 10 blinds
+        Material((0.35, 0.25, 0.20), 0.4, 0.0, 0.0),  # 11 sideboard
+    ]
+    cam = look_at((-4.3, 1.9, 3.3), (0.3, 0.9, -0.3), fov=50.0)
+    return Scene("breakfast_1048576", meshes, inst, mats, cam)
+
+
+# ----------------------------------------------------------------------------
+# config 5: animated 5M-triangle sheet; vertex positions are a function of time
+# ----------------------------------------------------------------------------
+def animated_sheet(t: float, nu: int = 1600, nv: int = 1600, seed: int = 555, with_normals: bool = True) -> Mesh:
+    """nu x nv quads (default 5,120,000 triangles) over a 40 x 40 m square: travelling waves
+    plus fixed per-vertex relief (so no two centroids coincide).  Seen from above."""
+
+    def fn(u, v, iu, iv):
+        y = 0.6 * np.sin(6.0 * np.pi * u + 1.7 * t) * np.cos(4.0 * np.pi * v - 1.1 * t) + 0.25 * np.sin(18.0 * np.pi * (u + v) + 2.3 * t)
+        return 40.0 * (u - 0.5), y + _relief(seed, iu, iv, 0.01), 40.0 * (v - 0.5)
+
+    if with_normals:
+        return grid_mesh(nu, nv, fn, flip=True)
+    # positions only (the per-frame path of a caller that animates vertices): analytic normals are not needed by the BVH
+    iu, iv = np.meshgrid(np.arange(nu + 1), np.arange(nv + 1), indexing="ij")
+    x, y, z = fn(iu.astype(np.float64) / nu, iv.astype(np.float64) / nv, iu, iv)
+    return Mesh(_round6(np.stack([x, y, z], axis=-1).reshape(-1, 3)), None, None)
+
+
+def animated_scene(nu: int = 1600, nv: int = 1600, seed: int = 555) -> Scene:
+    sheet = animated_sheet(0.0, nu, nv, seed)
+    lamp = _plane_xz(8, 8, -6.0, 6.0, -6.0, 6.0, 9.0, seed + 1, 0.0, up=False)
+    mats = [Material((0.55, 0.65, 0.75), 0.5, 0.5, 0.0), Material((1.0, 0.95, 0.9), 1.0, 0.0, 10.0)]
+    inst = [Instance(0, 0, mat_identity()), Instance(1, 1, mat_identity())]
+    cam = look_at((-16.0, 7.5, -16.0), (2.0, 0.0, 2.0), fov=50.0)
+    return Scene(f"animated_{sheet.n_tris}", [sheet, lamp], inst, mats, cam)

@@ -1,0 +1,94 @@
+#!/usr/bin/env python3
+"""The other BASELINE.json configs on ONE GPU (bench.py is config 3, the headline):
+  config 2  Cornell box, 1080p, 64 spp, 5 bounces
+  config 4  breakfast-room-shaped 1,048,576 triangles, 3840x2160 (this GPU's 128-spp share of 1024)
+  config 5  animated 5.12 M-triangle sheet: per frame new vertex positions -> BVH rebuild -> 1 spp
+Prints one JSON line per config.  Timing: CUDA events inside the library (last_render_ms,
+last_fast_build_ms) plus host wall clock around the whole C-ABI call where it matters.
+
+  python profiles/bench_configs.py [2] [4] [5]
+"""
+import json
+import os
+import sys
+import time
+
+import numpy as np
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import caveengine_b200 as cb
+from caveengine_b200 import scenes
+
+
+def run_static(tag, scene, w, h, mb, spp_total, spp_launch, bvh_mode):
+    with cb.PathTracer(w, h, mb, bvh_mode=bvh_mode) as pt:
+        pt.set_mode(cb.PathTracerMode.INTERACTIVE)
+        t0 = time.perf_counter()
+        pt.upload_scene(scene)
+        cold_ms = (time.perf_counter() - t0) * 1e3
+        pt.upload_scene(scene)  # warm: allocations and module load are done
+        build = pt.stats()
+        pt.set_camera(scene.camera)
+        pt.render(1 << 20, 1, sync=True)
+        pt.set_count_visits(True)
+        pt.reset_stats()
+        pt.render(1 << 20, 1, sync=True)
+        c = pt.stats()
+        pt.set_count_visits(False)
+        pt.reset()
+        pt.reset_stats()
+        ms, f = 0.0, 0
+        while f < spp_total:
+            n = min(spp_launch, spp_total - f)
+            pt.render(f, n, sync=True)
+            ms += pt.stats()["last_render_ms"]
+            f += n
+        st = pt.stats()
+        img = pt.read_accum()
+        line = {"config": tag, "scene": scene.name, "triangles": scene.n_tris, "width": w, "height": h, "max_bounce": mb, "spp": spp_total,
+                "M_segments_per_s": st["segments"] / ms / 1e3, "render_ms": ms, "segments": st["segments"], "segments_per_sample": st["segments"] / (w * h * spp_total),
+                "node_records_per_segment": c["node_visits"] / c["segments"], "triangle_tests_per_segment": c["triangle_tests"] / c["segments"],
+                "bvh_parity_build_ms": build["last_build_ms"], "bvh_fast_build_ms": build["last_fast_build_ms"], "bvh_fast_levels": build["fast_build_levels"],
+                "bvh_fast_launches": build["fast_build_launches"], "fast_nodes": build["fast_node_count"], "upload_and_build_wall_ms_cold": cold_ms,
+                "mean_rgb": [float(v) for v in img[..., :3].mean(axis=(0, 1))], "spp_check": float(img[..., 3].min())}
+        print(json.dumps(line), flush=True)
+
+
+def run_animated(frames=6, nu=1600, nv=1600):
+    scene = scenes.animated_scene(nu, nv)
+    w, h, mb = 1920, 1080, 8
+    poses = [scenes.animated_sheet(0.05 * (k + 1), nu, nv, with_normals=False).positions for k in range(frames)]
+    with cb.PathTracer(w, h, mb, bvh_mode=cb.BvhMode.FAST) as pt:
+        pt.set_mode(cb.PathTracerMode.INTERACTIVE)
+        pt.upload_scene(scene)
+        pt.set_camera(scene.camera)
+        pt.render(0, 1, sync=True)
+        rows = []
+        for k in range(frames):
+            t0 = time.perf_counter()
+            pt.rebuild_mesh(0, poses[k])  # H2D of the new positions + device rebuild
+            t1 = time.perf_counter()
+            pt.reset()
+            pt.reset_stats()
+            pt.render(k, 1, sync=True)
+            t2 = time.perf_counter()
+            st = pt.stats()
+            rows.append({"rebuild_call_wall_ms": (t1 - t0) * 1e3, "bvh_fast_build_ms": st["last_fast_build_ms"], "render_ms": st["last_render_ms"],
+                         "frame_wall_ms": (t2 - t0) * 1e3, "segments": st["segments"], "levels": st["fast_build_levels"], "launches": st["fast_build_launches"]})
+        warm = rows[1:]
+        med = lambda key: float(np.median([r[key] for r in warm]))
+        line = {"config": 5, "scene": scene.name, "triangles": scene.n_tris, "width": w, "height": h, "max_bounce": mb, "frames": frames,
+                "bvh_fast_build_ms_median": med("bvh_fast_build_ms"), "rebuild_call_wall_ms_median": med("rebuild_call_wall_ms"), "render_1spp_ms_median": med("render_ms"),
+                "frame_wall_ms_median": med("frame_wall_ms"), "M_segments_per_s": med("segments") / med("render_ms") / 1e3, "h2d_bytes_per_frame": int(poses[0].nbytes),
+                "levels": warm[-1]["levels"], "launches": warm[-1]["launches"], "per_frame": rows}
+        print(json.dumps(line), flush=True)
+
+
+if __name__ == "__main__":
+    which = [int(a) for a in sys.argv[1:]] or [2, 4, 5]
+    if 2 in which:
+        run_static(2, scenes.cornell_scene(), 1920, 1080, 5, 64, 32, cb.BvhMode.PARITY)
+    if 4 in which:
+        run_static(4, scenes.breakfast_scene(), 3840, 2160, 8, 128, 8, cb.BvhMode.PARITY)
+    if 5 in which:
+        run_animated()

@@ -11,7 +11,7 @@ LIB = os.path.join(HERE, "libcavept.so")
 SOURCES = ["kernels.cu", "cavept_api.cu"]
 HEADERS = ["cv_common.h", "bvh_parity_body.h", "bvh_parity_driver.h", "wbvh_body.h", "trace_body.h", "host_math.h", "kernels.h", "../../include/cavept.h"]
 
-NVCC_FLAGS = [
+NVCC_FLAGS = [f"-D{d}" for d in os.environ.get("CAVEPT_DEFINES", "").split()] + [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-O3", "-std=c++17", "-lineinfo",
     "-fmad=false",  # float results follow the source's operation order (see cv_common.h)

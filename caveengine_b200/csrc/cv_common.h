@@ -109,6 +109,14 @@ CV_HD float cv_div(float a, float b) {
     return a / b;
 #endif
 }
+// 1/x, correctly rounded: the same bits as cv_div(1.0f, x) (both are the IEEE quotient), fewer instructions
+CV_HD float cv_rcp(float x) {
+#if defined(__CUDA_ARCH__)
+    return __frcp_rn(x);
+#else
+    return 1.0f / x;
+#endif
+}
 CV_HD float cv_fma(float a, float b, float c) {
 #if defined(__CUDA_ARCH__)
     return __fmaf_rn(a, b, c);
@@ -117,7 +125,7 @@ CV_HD float cv_fma(float a, float b, float c) {
 #endif
 }
 CV_HD F3 normalize3(F3 a) {  // vector_math.h:527-536
-    const float inv = cv_div(1.0f, cv_sqrt(dot3(a, a)));
+    const float inv = cv_rcp(cv_sqrt(dot3(a, a)));
     return a * inv;
 }
 CV_HD F3 lerp3(F3 x, F3 y, float s) { return (1.0f - s) * x + s * y; }  // vector_math.h:507-510

@@ -132,7 +132,7 @@ CV_HD F3 mat_mul(const float* m, F3 v, float w) {
     return f3((m[0] * v.x + m[4] * v.y) + (m[8] * v.z + m[12] * w), (m[1] * v.x + m[5] * v.y) + (m[9] * v.z + m[13] * w),
               (m[2] * v.x + m[6] * v.y) + (m[10] * v.z + m[14] * w));
 }
-CV_HD F3 recip3(F3 d) { return f3(cv_div(1.0f, d.x), cv_div(1.0f, d.y), cv_div(1.0f, d.z)); }
+CV_HD F3 recip3(F3 d) { return f3(cv_rcp(d.x), cv_rcp(d.y), cv_rcp(d.z)); }
 
 // ---- HitTriangle, :88-130 ------------------------------------------------------------
 CV_HD bool hit_triangle_edges(F3 A, F3 AB, F3 AC, F3 origin, F3 direction, float& ray_t, float& out_u, float& out_v);
@@ -143,7 +143,7 @@ CV_HD bool hit_triangle_edges(F3 A, F3 AB, F3 AC, F3 origin, F3 direction, float
     const F3 P = cross3(direction, AC);
     const float det = dot3(AB, P);
     if (det < kEpsilon) return false;  // back faces culled
-    const float inv_det = cv_div(1.0f, det);
+    const float inv_det = cv_rcp(det);
     const F3 AO = origin - A;
     const F3 Q = cross3(AO, AB);
     const float u = dot3(AO, P) * inv_det;
@@ -322,12 +322,17 @@ CV_D void walk_step(const TraceParams& p, Walk& w, float ray_t, unsigned long lo
     const bool h0 = n0 <= f0, h1 = n1 <= f1;
     const int r0 = (int)f2u(c.g), r1 = (int)f2u(c.h);
     const bool second_first = h1 && (!h0 || n1 < n0);
-    if (h0 && h1) walk_push(w, second_first ? r0 : r1);
-    if (h0 || h1) {
-        w.ref = second_first ? r1 : r0;
-    } else {
-        w.ref = walk_pop(w);
-    }
+    // Branch-free bookkeeping (the three outcomes would otherwise be three divergent paths, each
+    // costing its own issue slots): spill the register top to the free slot above the stack and
+    // read the entry below it unconditionally, then select.  While a lane is stepping the sentinel
+    // is still stacked, so sp >= 1 and both addresses are its own.
+    const bool both = h0 && h1, none = !(h0 || h1);
+    const int near_ref = second_first ? r1 : r0, far_ref = second_first ? r0 : r1;
+    w.stack[w.sp * w.stride] = w.top;
+    const int below = w.stack[(w.sp - 1) * w.stride];
+    w.ref = none ? w.top : near_ref;
+    w.top = both ? far_ref : (none ? below : w.top);
+    w.sp += both ? 1 : (none ? -1 : 0);
 }
 
 // One triangle of the oldest postponed leaf.  World-space vertices: for an identity
@@ -479,8 +484,16 @@ CV_D unsigned int body_trace_pixel_reference(const TraceParams& p, int x, int y,
 //      of >= kShadeBatch lanes so the long shading sequence is not replayed per lane.
 // The order in which ONE lane visits its nodes and triangles does not depend on its
 // neighbours, so images are deterministic.
-constexpr int kStepQuorum = 20;  // of 32 lanes: keep stepping while at least this many can
-constexpr int kShadeBatch = 8;
+// (Tried and measured slower on B200: a separate batched phase for accumulate + next sample --
+// the lanes waiting for it cost more step-phase utilisation than the batching saves.)
+#ifndef CV_STEP_QUORUM
+#define CV_STEP_QUORUM 20
+#endif
+#ifndef CV_SHADE_BATCH
+#define CV_SHADE_BATCH 8
+#endif
+constexpr int kStepQuorum = CV_STEP_QUORUM;  // of 32 lanes: keep stepping while at least this many can
+constexpr int kShadeBatch = CV_SHADE_BATCH;
 
 template<bool kCount, int kQuorum = kStepQuorum, int kBatch = kShadeBatch>
 CV_D unsigned int body_trace_pixel_fast(const TraceParams& p, int x, int y, int* stack, int stride, unsigned long long* cnt) {
@@ -510,6 +523,10 @@ CV_D unsigned int body_trace_pixel_fast(const TraceParams& p, int x, int y, int*
             const bool can_step = ref_is_interior(w.ref);
             if (CV_WARP_COUNT(can_step) < kQuorum) break;
             if (can_step) walk_step<kCount>(p, w, ray.t, cnt);
+            // second step of the trip without a vote of its own (measured +2 %): the lanes that can
+            // still step do, the others would have idled through it anyway
+            walk_park_leaf(w);
+            if (ref_is_interior(w.ref)) walk_step<kCount>(p, w, ray.t, cnt);
         }
         // ---- the vote ------------------------------------------------------------------------
         const bool can_step = ref_is_interior(w.ref);

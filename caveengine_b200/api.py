@@ -42,6 +42,7 @@ class TraceMode(enum.IntEnum):
 class BvhMode(enum.IntEnum):
     PARITY = 0  # reference-layout per-mesh BVHs (bit-exact) + the production tree
     FAST = 1  # production tree only
+    LBVH = 2  # production tree only, Morton-sort builder (per-frame rebuilds)
 
 
 ERR_INVALID_ARG, ERR_DEGENERATE_GEOMETRY, ERR_CUDA, ERR_NOT_READY, ERR_CAPACITY = 1, 2, 3, 4, 5
@@ -105,6 +106,7 @@ ABI = [
     ("cavept_accum_device_ptr", _P, [_P]),
     ("cavept_accum_to_sums", C.c_int, [_P]),
     ("cavept_accum_from_sums", C.c_int, [_P]),
+    ("cavept_sort_pairs", C.c_int, [_P, _P, _P, C.c_int, C.c_int]),
 ]
 
 
@@ -313,6 +315,11 @@ class PathTracer:
 
     def accum_from_sums(self):
         self._check(self._lib.cavept_accum_from_sums(self._ctx))
+
+    def sort_pairs(self, keys: np.ndarray, values: np.ndarray, key_bits: int = 32):
+        """Device radix sort of (uint32 key, int32 value) pairs, in place (stable)."""
+        assert keys.dtype == np.uint32 and values.dtype == np.int32 and keys.flags.c_contiguous and values.flags.c_contiguous and keys.size == values.size
+        self._check(self._lib.cavept_sort_pairs(self._ctx, keys.ctypes.data, values.ctypes.data, int(keys.size), int(key_bits)))
 
     def accum_as_torch(self):
         """Zero-copy torch view of the device accumulator (H, W, 4) float32, for

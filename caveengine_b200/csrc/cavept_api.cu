@@ -87,7 +87,9 @@ struct cavept_ctx {
     DevBuf<unsigned char> d_w_flags;
     DevBuf<WItem> d_w_items, d_w_items_next;
     DevBuf<WBins> d_w_bins;
-    DevBuf<uint32_t> d_w_root_acc;
+    DevBuf<uint32_t> d_w_root_acc, d_w_keys, d_w_keys_tmp;
+    DevBuf<int> d_w_sort_hist;
+    DevBuf<F4> d_w_nbox_mn, d_w_nbox_mx;
     // upload staging
     DevBuf<float> d_raw_pos, d_raw_nrm;
     DevBuf<uint32_t> d_raw_idx;
@@ -215,9 +217,19 @@ int build_world(cavept_ctx* ctx) {
     CU(ctx, ctx->d_w_flags.reserve(P));
     CU(ctx, ctx->d_w_scan.reserve((size_t)P + 1));
     CU(ctx, ctx->d_scan_tmp.reserve((size_t)P / kScanTile + 4));
-    CU(ctx, ctx->d_w_items.reserve(items_cap));
-    CU(ctx, ctx->d_w_items_next.reserve(items_cap));
-    CU(ctx, ctx->d_w_bins.reserve(items_cap));
+    const bool lbvh = ctx->cfg.bvh_mode == CAVEPT_BVH_LBVH;
+    if (lbvh) {
+        CU(ctx, ctx->d_w_keys.reserve(P));
+        CU(ctx, ctx->d_w_keys_tmp.reserve(P));
+        CU(ctx, ctx->d_w_sort_hist.reserve(2 * sort_hist_entries(P)));
+        CU(ctx, ctx->d_w_nbox_mn.reserve(pairs_cap));
+        CU(ctx, ctx->d_w_nbox_mx.reserve(pairs_cap));
+        CU(ctx, ctx->d_scan_tmp.reserve(std::max((size_t)P, sort_hist_entries(P)) / kScanTile + 4));
+    } else {
+        CU(ctx, ctx->d_w_items.reserve(items_cap));
+        CU(ctx, ctx->d_w_items_next.reserve(items_cap));
+        CU(ctx, ctx->d_w_bins.reserve(items_cap));
+    }
     CU(ctx, ctx->d_w_counters.reserve(4));
     CU(ctx, ctx->d_w_root_acc.reserve(12));
     CU(ctx, ctx->d_fnodes.reserve(2 * pairs_cap));
@@ -252,6 +264,11 @@ int build_world(cavept_ctx* ctx) {
     b.pairs_capacity = (int)pairs_cap;
     b.counters = ctx->d_w_counters.ptr;
     b.root_acc = ctx->d_w_root_acc.ptr;
+    b.keys = ctx->d_w_keys.ptr;
+    b.keys_tmp = ctx->d_w_keys_tmp.ptr;
+    b.sort_hist = ctx->d_w_sort_hist.ptr;
+    b.nbox_mn = ctx->d_w_nbox_mn.ptr;
+    b.nbox_mx = ctx->d_w_nbox_mx.ptr;
     b.fnodes = ctx->d_fnodes.ptr;
     b.qpairs = ctx->d_qpairs.ptr;
     b.ftris = ctx->d_ftris.ptr;
@@ -260,8 +277,8 @@ int build_world(cavept_ctx* ctx) {
     const unsigned long long launches_before = ctx->ex.launches;
     CU(ctx, cudaEventRecord(ctx->ev0, ctx->ex.stream));
     WReport rep{};
-    int rc = run_build_wbvh(ctx->ex, b, &rep);
-    if (rc == 0 && rep.levels + 2 > kStackSize) {  // deeper than the traversal stack: rebuild balanced (median splits)
+    int rc = lbvh ? run_build_lbvh(ctx->ex, b, &rep) : run_build_wbvh(ctx->ex, b, &rep);
+    if (!lbvh && rc == 0 && rep.levels + 2 > kStackSize) {  // deeper than the traversal stack: rebuild balanced (median splits)
         b.force_median = 1;
         rc = run_build_wbvh(ctx->ex, b, &rep);
     }
@@ -427,6 +444,7 @@ CAVEPT_API void cavept_destroy(cavept_ctx* ctx) {
     ctx->d_prim_bmin.release(); ctx->d_prim_bmax.release(); ctx->d_w_order.release(); ctx->d_w_order_next.release(); ctx->d_w_node_of.release();
     ctx->d_w_node_of_next.release(); ctx->d_w_scan.release(); ctx->d_w_counters.release(); ctx->d_w_flags.release(); ctx->d_w_items.release();
     ctx->d_w_items_next.release(); ctx->d_w_bins.release(); ctx->d_w_root_acc.release();
+    ctx->d_w_keys.release(); ctx->d_w_keys_tmp.release(); ctx->d_w_sort_hist.release(); ctx->d_w_nbox_mn.release(); ctx->d_w_nbox_mx.release();
     ctx->d_raw_pos.release(); ctx->d_raw_nrm.release(); ctx->d_raw_idx.release(); ctx->d_tri_off.release(); ctx->d_vert_off.release();
     ctx->d_tri_bmin.release(); ctx->d_tri_bmax.release(); ctx->d_tri_centroid.release();
     ctx->d_order.release(); ctx->d_order_next.release(); ctx->d_node_of.release(); ctx->d_node_of_next.release();
@@ -771,3 +789,28 @@ CAVEPT_API int cavept_accum_from_sums(cavept_ctx* ctx) {
 }
 
 }  // extern "C"
+
+CAVEPT_API int cavept_sort_pairs(cavept_ctx* ctx, uint32_t* keys, int32_t* values, int count, int key_bits) {
+    if (!ctx || !keys || !values || count < 0 || key_bits < 1 || key_bits > 32) return CAVEPT_ERR_INVALID_ARG;
+    if (int e = select_device(ctx)) return e;
+    if (count == 0) return CAVEPT_OK;
+    DevBuf<uint32_t> k, kt;
+    DevBuf<int> v, vt, hist, tmp;
+    CU(ctx, k.reserve(count));
+    CU(ctx, kt.reserve(count));
+    CU(ctx, v.reserve(count));
+    CU(ctx, vt.reserve(count));
+    CU(ctx, hist.reserve(2 * sort_hist_entries(count)));
+    CU(ctx, tmp.reserve(sort_hist_entries(count) / kScanTile + 4));
+    int* saved = ctx->ex.scan_tmp;
+    ctx->ex.scan_tmp = tmp.ptr;
+    ctx->ex.upload(k.ptr, keys, (size_t)count * sizeof(uint32_t));
+    ctx->ex.upload(v.ptr, values, (size_t)count * sizeof(int));
+    ctx->ex.sort_pairs(k.ptr, v.ptr, kt.ptr, vt.ptr, hist.ptr, count, key_bits);
+    CU(ctx, cudaMemcpyAsync(keys, k.ptr, (size_t)count * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->ex.stream));
+    CU(ctx, cudaMemcpyAsync(values, v.ptr, (size_t)count * sizeof(int), cudaMemcpyDeviceToHost, ctx->ex.stream));
+    CU(ctx, cudaStreamSynchronize(ctx->ex.stream));
+    ctx->ex.scan_tmp = saved;
+    k.release(); kt.release(); v.release(); vt.release(); hist.release(); tmp.release();
+    return check_exec(ctx, "sort_pairs");
+}

@@ -239,6 +239,30 @@ CV_D void cv_atomic_add_u64(unsigned long long* p, unsigned long long v) {
 #endif
 }
 
+CV_D void cv_threadfence() {
+#if defined(__CUDA_ARCH__)
+    __threadfence();
+#endif
+}
+// load that bypasses the (non-coherent) L1: for data another SM wrote earlier in the same launch
+CV_D F4 cv_load_cg(const F4* p) {
+#if defined(__CUDA_ARCH__)
+    const float4 v = __ldcg(reinterpret_cast<const float4*>(p));
+    F4 r;
+    r.x = v.x; r.y = v.y; r.z = v.z; r.w = v.w;
+    return r;
+#else
+    return *p;
+#endif
+}
+CV_HD int cv_clz(uint32_t v) {
+#if defined(__CUDA_ARCH__)
+    return __clz((int)v);
+#else
+    return v ? __builtin_clz(v) : 32;
+#endif
+}
+
 // ---- warp-aggregated atomics ------------------------------------------------------------
 // Lanes of a warp that pass the same key combine their operands with one redux.sync and a
 // single lane issues the atomic: up to 32x fewer atomics on the hot addresses of the

@@ -134,6 +134,137 @@ static void scan_impl(CudaExec& ex, const T* in, int* out, int n) {
 void CudaExec::scan_u8(const unsigned char* in, int* out, int n) { scan_impl<unsigned char>(*this, in, out, n); }
 void CudaExec::scan_i32(const int* in, int* out, int n) { scan_impl<int>(*this, in, out, n); }
 
+// ---- radix sort (Morton keys of the LBVH builder) -------------------------------------------
+// Stable LSD sort, 8 bits per pass.  A block owns a tile of kSortTile = 256 x 16 consecutive
+// keys; warp w owns 512 of them and visits them in order (round r, lane l), so the rank of a
+// key among equal digits is (equal digits in earlier warps) + (in earlier rounds of this warp)
+// + (in lower lanes of this round, from match.any).  Per pass: block histograms -> exclusive
+// scan over (digit, block) -> ranked scatter.
+constexpr int kSortThreads = 256;
+constexpr int kSortRounds = kSortTile / kSortThreads;  // 16
+constexpr int kSortWarps = kSortThreads / 32;
+
+__global__ void __launch_bounds__(kSortThreads) k_sort_hist(const uint32_t* __restrict__ keys, int* __restrict__ hist, int n, int shift, int nb) {
+    __shared__ int h[256];
+    h[threadIdx.x] = 0;
+    __syncthreads();
+    const int base = blockIdx.x * kSortTile;
+#pragma unroll 4
+    for (int r = 0; r < kSortRounds; ++r) {
+        const int e = base + r * kSortThreads + threadIdx.x;
+        if (e < n) atomicAdd(&h[(keys[e] >> shift) & 255u], 1);
+    }
+    __syncthreads();
+    hist[threadIdx.x * nb + blockIdx.x] = h[threadIdx.x];
+}
+
+__global__ void __launch_bounds__(kSortThreads) k_sort_scatter(const uint32_t* __restrict__ keys, const int* __restrict__ vals, uint32_t* __restrict__ out_keys,
+                                                               int* __restrict__ out_vals, const int* __restrict__ offsets, int n, int shift, int nb) {
+    __shared__ int cnt[kSortWarps][256];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int i = threadIdx.x; i < kSortWarps * 256; i += kSortThreads) (&cnt[0][0])[i] = 0;
+    __syncthreads();
+    const int base = blockIdx.x * kSortTile + warp * (32 * kSortRounds);
+    uint32_t key[kSortRounds];
+    int val[kSortRounds], rank[kSortRounds];
+    const unsigned lt = (1u << lane) - 1u;
+#pragma unroll
+    for (int r = 0; r < kSortRounds; ++r) {
+        const int e = base + r * 32 + lane;
+        const bool valid = e < n;
+        key[r] = valid ? keys[e] : 0xffffffffu;  // padding sorts (and ranks) after every real key of the tile
+        val[r] = valid ? vals[e] : 0;
+        const int d = valid ? (int)((key[r] >> shift) & 255u) : 255;
+        const unsigned peers = __match_any_sync(0xffffffffu, d);
+        const int before = cnt[warp][d];
+        __syncwarp();
+        if ((peers & lt) == 0u) cnt[warp][d] = before + __popc(peers);
+        __syncwarp();
+        rank[r] = before + __popc(peers & lt);
+    }
+    __syncthreads();
+    {  // per digit: exclusive prefix over the warps, plus the block's global offset for that digit
+        const int d = threadIdx.x;
+        int run = offsets[d * nb + blockIdx.x];
+#pragma unroll
+        for (int w = 0; w < kSortWarps; ++w) {
+            const int c = cnt[w][d];
+            cnt[w][d] = run;
+            run += c;
+        }
+    }
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < kSortRounds; ++r) {
+        const int e = base + r * 32 + lane;
+        if (e < n) {
+            const int d = (int)((key[r] >> shift) & 255u);
+            const int pos = cnt[warp][d] + rank[r];
+            out_keys[pos] = key[r];
+            out_vals[pos] = val[r];
+        }
+    }
+}
+
+void CudaExec::sort_pairs(uint32_t* keys, int* vals, uint32_t* keys_tmp, int* vals_tmp, int* hist, int n, int bits) {
+    if (n <= 1) return;
+    const int nb = (n + kSortTile - 1) / kSortTile;
+    int passes = (bits + 7) / 8;
+    if (passes & 1) ++passes;  // an even number of passes leaves the result in keys / vals
+    for (int pass = 0; pass < passes; ++pass) {
+        const int shift = 8 * pass;
+        k_sort_hist<<<nb, kSortThreads, 0, stream>>>(keys, hist, n, shift, nb);
+        ++launches;
+        int* offsets = hist + sort_hist_entries(n);
+        scan_i32(hist, offsets, 256 * nb);
+        k_sort_scatter<<<nb, kSortThreads, 0, stream>>>(keys, vals, keys_tmp, vals_tmp, offsets, n, shift, nb);
+        ++launches;
+        note(cudaGetLastError());
+        uint32_t* tk = keys; keys = keys_tmp; keys_tmp = tk;
+        int* tv = vals; vals = vals_tmp; vals_tmp = tv;
+    }
+}
+
+// ---- prim pass of the production builders: per-block reduction of the 12 bounds, then 12
+//      atomics per block (the generic per-index body would issue 12 per warp on the same words)
+__global__ void __launch_bounds__(256) k_wb_prim(const WBuild b) {
+    __shared__ uint32_t red[12][8];
+    uint32_t k[12];
+#pragma unroll
+    for (int c = 0; c < 12; ++c) k[c] = ((c / 3) % 2 == 0) ? 0xffffffffu : 0u;
+    for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < b.n_prims; p += gridDim.x * blockDim.x) {
+        F3 mn, mx;
+        wb_prim_box(b, p, mn, mx);
+        const F3 c = 0.5f * (mn + mx);
+        const float v[12] = { mn.x, mn.y, mn.z, mx.x, mx.y, mx.z, c.x, c.y, c.z, c.x, c.y, c.z };
+#pragma unroll
+        for (int q = 0; q < 12; ++q) {
+            const uint32_t o = ordered_key(v[q]);
+            k[q] = ((q / 3) % 2 == 0) ? min(k[q], o) : max(k[q], o);
+        }
+    }
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int q = 0; q < 12; ++q) {
+        const uint32_t r = ((q / 3) % 2 == 0) ? __reduce_min_sync(0xffffffffu, k[q]) : __reduce_max_sync(0xffffffffu, k[q]);
+        if (lane == 0) red[q][warp] = r;
+    }
+    __syncthreads();
+    if (threadIdx.x < 12) {
+        const int q = threadIdx.x;
+        uint32_t r = red[q][0];
+        for (int w = 1; w < 8; ++w) r = ((q / 3) % 2 == 0) ? min(r, red[q][w]) : max(r, red[q][w]);
+        if ((q / 3) % 2 == 0) atomicMin(&b.root_acc[q], r); else atomicMax(&b.root_acc[q], r);
+    }
+}
+void CudaExec::wb_prim(const WBuild& b) {
+    if (b.n_prims <= 0) return;
+    const int blocks = min((b.n_prims + 255) / 256, 148 * 8);
+    k_wb_prim<<<blocks, 256, 0, stream>>>(b);
+    note(cudaGetLastError());
+    ++launches;
+}
+
 // ---- scene assembly -------------------------------------------------------------------
 struct FnAssembleVertices {
     const float* positions;
@@ -184,6 +315,7 @@ int run_build_bvh_parity(CudaExec& ex, BuildArrays a, const int* tri_off_host, c
     return build_bvh_parity(ex, a, tri_off_host, d_tri_off, n_meshes, host_scratch, report);
 }
 int run_build_wbvh(CudaExec& ex, WBuild b, WReport* report) { return build_wbvh(ex, b, report); }
+int run_build_lbvh(CudaExec& ex, WBuild b, WReport* report) { return build_lbvh(ex, b, report); }
 
 // ---- path-trace pass ------------------------------------------------------------------
 // Block = 128 threads = a 16 x 8 pixel tile; each warp covers an 8 x 4 sub-tile so the

@@ -19,6 +19,10 @@ struct CudaExec {
     void launch(int n, F f);
     void scan_u8(const unsigned char* in, int* out, int n);
     void scan_i32(const int* in, int* out, int n);
+    // stable LSD radix sort of (key, value) pairs by the low `bits` of the key; result in keys/vals.
+    // tmp buffers hold n entries each, hist needs 2 * sort_hist_entries(n) ints.
+    void sort_pairs(uint32_t* keys, int* vals, uint32_t* keys_tmp, int* vals_tmp, int* hist, int n, int bits);
+    void wb_prim(const WBuild& b);  // world AABBs + scene / centroid bounds, block-reduced
     void upload(void* dst, const void* src, size_t bytes);
     void download(void* dst, const void* src, size_t bytes);
     void fill(void* dst, int byte, size_t bytes);
@@ -28,6 +32,8 @@ struct CudaExec {
 };
 
 constexpr int kScanTile = 2048;
+constexpr int kSortTile = 4096;  // keys per block of the radix sort: 256 threads x 16
+inline size_t sort_hist_entries(int n) { return (size_t)256 * (size_t)((n + kSortTile - 1) / kSortTile) + 1; }
 
 // scene assembly: raw MeshAsset arrays -> reference GPU layouts
 // (ConstructMesh + AppendVertices/AppendIndices, path_tracer.cpp:27-47, :72-88)
@@ -36,6 +42,7 @@ void launch_assemble_indices(CudaExec& ex, const uint32_t* raw_indices, const in
 
 int run_build_bvh_parity(CudaExec& ex, BuildArrays a, const int* tri_off_host, const int* d_tri_off, int n_meshes, BuildItem* host_scratch, BuildReport* report);
 int run_build_wbvh(CudaExec& ex, WBuild b, WReport* report);
+int run_build_lbvh(CudaExec& ex, WBuild b, WReport* report);
 
 void launch_trace(CudaExec& ex, const TraceParams& p, bool fast, bool count_visits);
 void launch_tonemap_rgba8(CudaExec& ex, const F4* accum, unsigned char* out, int n_pixels);

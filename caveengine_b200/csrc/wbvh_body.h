@@ -79,6 +79,18 @@ struct WBuild {
     int items_capacity;
     int pairs_capacity;
     int* counters;       // [0] items emitted for the next level, [1] pairs allocated, [2] error bits
+    // LBVH builder only
+    uint32_t* keys;      // Morton code per prim, then sorted
+    uint32_t* keys_tmp;
+    int* sort_hist;      // 2 * sort_hist_entries(n_prims)
+    F4* nbox_mn;         // box of the interior node with heap index h (written bottom-up)
+    F4* nbox_mx;
+    int* node_first;     // radix tree: slot range of internal node i
+    int* node_last;
+    int* node_split;     // last slot of its left child
+    int* node_parent;
+    int* node_count;     // children that are leaves, then arrivals of the bottom-up pass
+    float morton_min[3], morton_scale[3];
     uint32_t* root_acc;  // [0..2] scene min keys, [3..5] max keys, [6..8] centroid min keys, [9..11] centroid max keys
     // outputs
     FastNode* fnodes;
@@ -103,13 +115,13 @@ CV_HD F3 wb_world(const float* m, const float* v) {
 }
 
 // ---- prim pass ---------------------------------------------------------------------------
-CV_D void wb_body_prim(const WBuild& b, int p) {
-    if (p >= b.n_prims) return;
+CV_D void wb_prim_box(const WBuild& b, int p, F3& mn, F3& mx) {
     const int inst = wb_find_instance(b.inst_prim_off, b.n_inst, p);
     const int tri = b.inst_tri_off[inst] + (p - b.inst_prim_off[inst]);
     const float* m = b.instances[inst].transform;
     const int* t = b.indices[tri].tri;
-    F3 mn = f3(CV_INF, CV_INF, CV_INF), mx = f3(-CV_INF, -CV_INF, -CV_INF);
+    mn = f3(CV_INF, CV_INF, CV_INF);
+    mx = f3(-CV_INF, -CV_INF, -CV_INF);
     for (int k = 0; k < 3; ++k) {
         const F3 w = wb_world(m, b.vertices[t[k]].position);
         mn = f3(fminf(mn.x, w.x), fminf(mn.y, w.y), fminf(mn.z, w.z));
@@ -120,6 +132,12 @@ CV_D void wb_body_prim(const WBuild& b, int p) {
     b.bmin[p] = o;
     o.x = mx.x; o.y = mx.y; o.z = mx.z; o.w = u2f((uint32_t)inst);
     b.bmax[p] = o;
+}
+// per-index form (the emulator's; the device runs k_wb_prim, which reduces per block first)
+CV_D void wb_body_prim(const WBuild& b, int p) {
+    if (p >= b.n_prims) return;
+    F3 mn, mx;
+    wb_prim_box(b, p, mn, mx);
     const F3 c = 0.5f * (mn + mx);
     const CvGroup g = cv_group_by(0);
     cv_group_min_u32(g, &b.root_acc[0], ordered_key(mn.x));
@@ -440,6 +458,187 @@ CV_D void wb_body_quantise(const WBuild& b, int k, int n_pairs) {
     b.qpairs[k] = o;
 }
 
+// ---- LBVH builder: Morton codes + radix sort + binary radix tree + bottom-up AABB reduction ------
+// For scenes rebuilt every frame (BASELINE config 5; the reference never rebuilds,
+// path_tracer.cpp:69).  Prims are sorted along the 30-bit Morton curve of their box centres.
+// Hierarchy: the binary radix tree over the sorted codes (every split falls on the highest
+// differing bit, i.e. on a cell boundary of the curve; equal codes are split by index bits),
+// every internal node found independently from its neighbours' common-prefix lengths; ranges of
+// <= 2 slots are leaves.  Boxes: one bottom-up pass in which the second child to arrive at a
+// node folds both child boxes, writes the node's QPair + FastNode records and climbs on.
+// Fallback when that tree is deeper than the traversal stack (measured height): the balanced
+// binary partition of the sorted sequence -- node j of level k owns slots [j*N >> k, (j+1)*N >> k),
+// heap-indexed, depth ceil(log2 N) whatever the geometry (boxes overlap more: measured 3.4x
+// slower to trace on the 5 M-triangle sheet, which is why it is only the fallback).
+CV_HD uint32_t wb_expand10(uint32_t v) {  // 10 bits -> every third bit
+    v = (v * 0x00010001u) & 0xFF0000FFu;
+    v = (v * 0x00000101u) & 0x0F00F00Fu;
+    v = (v * 0x00000011u) & 0xC30C30C3u;
+    v = (v * 0x00000005u) & 0x49249249u;
+    return v;
+}
+CV_D void wb_body_morton(const WBuild& b, int p) {
+    if (p >= b.n_prims) return;
+    const F4 mn = b.bmin[p], mx = b.bmax[p];
+    const float c[3] = { 0.5f * (mn.x + mx.x), 0.5f * (mn.y + mx.y), 0.5f * (mn.z + mx.z) };
+    uint32_t q[3];
+    for (int k = 0; k < 3; ++k) {
+        float g = (c[k] - b.morton_min[k]) * b.morton_scale[k];
+        g = g < 0.0f ? 0.0f : (g > 1023.0f ? 1023.0f : g);
+        q[k] = (uint32_t)(int)g;
+    }
+    b.keys[p] = (wb_expand10(q[0]) << 2) | (wb_expand10(q[1]) << 1) | wb_expand10(q[2]);
+}
+
+// common-prefix length of the sorted keys at slots i and j (ties broken by the slot index)
+CV_HD int wb_delta(const uint32_t* keys, int n, int i, int j) {
+    if (j < 0 || j >= n) return -1;
+    const uint32_t a = keys[i], c = keys[j];
+    return a == c ? 32 + cv_clz((uint32_t)i ^ (uint32_t)j) : cv_clz(a ^ c);
+}
+
+// Internal node i of the radix tree: its slot range, split and parent links of its children.
+//   node_first/node_last[i] = range; node_split[i] = last slot of the left child;
+//   node_parent[child internal node] = i; node_count[i] = how many of its children are leaves.
+CV_D void wb_body_radix_node(const WBuild& b, int i) {
+    const int n = b.n_prims;
+    if (i >= n - 1) return;
+    const uint32_t* keys = b.keys;
+    const int d = wb_delta(keys, n, i, i + 1) - wb_delta(keys, n, i, i - 1) < 0 ? -1 : 1;
+    const int dmin = wb_delta(keys, n, i, i - d);
+    int lmax = 2;
+    while (wb_delta(keys, n, i, i + lmax * d) > dmin) lmax *= 2;
+    int l = 0;
+    for (int t = lmax / 2; t >= 1; t /= 2) {
+        if (wb_delta(keys, n, i, i + (l + t) * d) > dmin) l += t;
+    }
+    const int j = i + l * d;
+    const int dnode = wb_delta(keys, n, i, j);
+    int s = 0;
+    for (int t = (l + 1) / 2;; t = (t + 1) / 2) {
+        if (wb_delta(keys, n, i, i + (s + t) * d) > dnode) s += t;
+        if (t <= 1) break;
+    }
+    const int split = i + s * d + (d < 0 ? -1 : 0);
+    const int first = i < j ? i : j, last = i < j ? j : i;
+    b.node_first[i] = first;
+    b.node_last[i] = last;
+    b.node_split[i] = split;
+    int leaves = 0;
+    if (split - first + 1 <= kFastLeafMax) ++leaves; else b.node_parent[split] = i;
+    if (last - split <= kFastLeafMax) ++leaves; else b.node_parent[split + 1] = i;
+    b.node_count[i] = leaves | (leaves << 8);  // low byte counts arrivals on top of the leaves; the high byte stays
+    if (i == 0) b.node_parent[0] = -1;
+}
+
+// child `side` of internal node i: box, reference, triangle count, height
+CV_D void wb_radix_child(const WBuild& b, int i, int side, WBox& box, int& ref, int& count, int& height) {
+    const int split = b.node_split[i];
+    const int lo = side == 0 ? b.node_first[i] : split + 1, hi = side == 0 ? split : b.node_last[i];
+    count = hi - lo + 1;
+    if (count <= kFastLeafMax) {
+        box = wb_empty();
+        for (int s = lo; s <= hi; ++s) {
+            const int p = b.order[s];
+            const F4 mn = b.bmin[p], mx = b.bmax[p];
+            wb_grow(box, f3(mn.x, mn.y, mn.z), f3(mx.x, mx.y, mx.z));
+        }
+        ref = make_leaf_ref(lo, count);
+        height = 0;
+    } else {
+        const int c = side == 0 ? split : split + 1;
+        const F4 mn = cv_load_cg(&b.nbox_mn[c]), mx = cv_load_cg(&b.nbox_mx[c]);
+        box.mn = f3(mn.x, mn.y, mn.z);
+        box.mx = f3(mx.x, mx.y, mx.z);
+        ref = 2 * c;
+        height = (int)f2u(mn.w);
+    }
+}
+
+CV_D void wb_write_pair(const WBuild& b, int h, const WBox box[2], const int ref[2], const int count[2]) {
+    QPair q;
+    for (int s = 0; s < 2; ++s) {
+        FastNode o;
+        o.mn[0] = box[s].mn.x; o.mn[1] = box[s].mn.y; o.mn[2] = box[s].mn.z;
+        o.mx[0] = box[s].mx.x; o.mx[1] = box[s].mx.y; o.mx[2] = box[s].mx.z;
+        o.a = ref[s];
+        o.b = count[s];
+        b.fnodes[2 * h + s] = o;
+        for (int c = 0; c < 3; ++c) q.q[3 * s + c] = wb_grid_lo(o.mn[c], b.grid_origin[c], b.grid_scale[c]) | (wb_grid_hi(o.mx[c], b.grid_origin[c], b.grid_scale[c]) << 16);
+        if (s == 0) q.r0 = wb_quantised_ref(ref[s]); else q.r1 = wb_quantised_ref(ref[s]);
+    }
+    b.qpairs[h] = q;
+}
+
+// Bottom-up: starts at every node whose two children are leaves; at each parent the first
+// arrival stops, the second (node_count reaches 2) has both child boxes and continues.
+CV_D void wb_body_radix_boxes(const WBuild& b, int i) {
+    if (i >= b.n_prims - 1) return;
+    if (b.node_last[i] - b.node_first[i] + 1 <= kFastLeafMax) return;  // folded into its parent as a leaf
+    if ((b.node_count[i] >> 8) != 2) return;  // start only where both children are leaves
+    for (;;) {
+        WBox box[2];
+        int ref[2], count[2], hgt[2];
+        wb_radix_child(b, i, 0, box[0], ref[0], count[0], hgt[0]);
+        wb_radix_child(b, i, 1, box[1], ref[1], count[1], hgt[1]);
+        wb_write_pair(b, i, box, ref, count);
+        wb_grow(box[0], box[1].mn, box[1].mx);
+        F4 o;
+        o.x = box[0].mn.x; o.y = box[0].mn.y; o.z = box[0].mn.z; o.w = u2f((uint32_t)(1 + (hgt[0] > hgt[1] ? hgt[0] : hgt[1])));
+        b.nbox_mn[i] = o;
+        o.x = box[0].mx.x; o.y = box[0].mx.y; o.z = box[0].mx.z; o.w = 0.0f;
+        b.nbox_mx[i] = o;
+        const int parent = b.node_parent[i];
+        if (parent < 0) return;
+        cv_threadfence();
+        if ((cv_atomic_add_i32(&b.node_count[parent], 1) & 0xff) != 1) return;
+        cv_threadfence();
+        i = parent;
+    }
+}
+
+CV_HD int wb_lbvh_lo(int n, int k, int j) { return (int)(((long long)j * (long long)n) >> k); }
+
+// box of the node (k, j) seen from its parent: a leaf's box is folded from its prims, an
+// interior node's was written by the previous (deeper) launch
+CV_D void wb_lbvh_child(const WBuild& b, int k, int j, WBox& box, int& ref, int& count) {
+    const int lo = wb_lbvh_lo(b.n_prims, k, j), hi = wb_lbvh_lo(b.n_prims, k, j + 1);
+    count = hi - lo;
+    if (count <= kFastLeafMax) {
+        box = wb_empty();
+        for (int s = lo; s < hi; ++s) {
+            const int p = b.order[s];
+            const F4 mn = b.bmin[p], mx = b.bmax[p];
+            wb_grow(box, f3(mn.x, mn.y, mn.z), f3(mx.x, mx.y, mx.z));
+        }
+        ref = make_leaf_ref(lo, count);
+    } else {
+        const int h = (1 << k) - 1 + j;
+        const F4 mn = b.nbox_mn[h], mx = b.nbox_mx[h];
+        box.mn = f3(mn.x, mn.y, mn.z);
+        box.mx = f3(mx.x, mx.y, mx.z);
+        ref = 2 * h;  // FastNode-array convention: index of the child pair's first record
+    }
+}
+
+CV_D void wb_body_lbvh_level(const WBuild& b, int j, int k) {
+    if (j >= (1 << k)) return;
+    const int lo = wb_lbvh_lo(b.n_prims, k, j), hi = wb_lbvh_lo(b.n_prims, k, j + 1);
+    if (hi - lo <= kFastLeafMax) return;  // a leaf: its parent folds it
+    const int h = (1 << k) - 1 + j;
+    WBox box[2];
+    int ref[2], count[2];
+    wb_lbvh_child(b, k + 1, 2 * j, box[0], ref[0], count[0]);
+    wb_lbvh_child(b, k + 1, 2 * j + 1, box[1], ref[1], count[1]);
+    wb_write_pair(b, h, box, ref, count);
+    wb_grow(box[0], box[1].mn, box[1].mx);
+    F4 o;
+    o.x = box[0].mn.x; o.y = box[0].mn.y; o.z = box[0].mn.z; o.w = 0.0f;
+    b.nbox_mn[h] = o;
+    o.x = box[0].mx.x; o.y = box[0].mx.y; o.z = box[0].mx.z;
+    b.nbox_mx[h] = o;
+}
+
 struct FnWbPrim { WBuild b; CV_D void operator()(int i) const { wb_body_prim(b, i); } };
 struct FnWbInit { WBuild b; CV_D void operator()(int i) const { wb_body_init(b, i); } };
 struct FnWbPrep { WBuild b; int n; CV_D void operator()(int i) const { wb_body_prep(b, i, n); } };
@@ -448,6 +647,10 @@ struct FnWbSplit { WBuild b; int n; CV_D void operator()(int i) const { wb_body_
 struct FnWbFlag { WBuild b; CV_D void operator()(int i) const { wb_body_flag(b, i); } };
 struct FnWbScatter { WBuild b; CV_D void operator()(int i) const { wb_body_scatter(b, i); } };
 struct FnWbEmit { WBuild b; CV_D void operator()(int i) const { wb_body_emit(b, i); } };
+struct FnWbMorton { WBuild b; CV_D void operator()(int i) const { wb_body_morton(b, i); } };
+struct FnWbRadixNode { WBuild b; CV_D void operator()(int i) const { wb_body_radix_node(b, i); } };
+struct FnWbRadixBoxes { WBuild b; CV_D void operator()(int i) const { wb_body_radix_boxes(b, i); } };
+struct FnWbLbvhLevel { WBuild b; int k; CV_D void operator()(int i) const { wb_body_lbvh_level(b, i, k); } };
 struct FnWbQuantise { WBuild b; int n; CV_D void operator()(int i) const { wb_body_quantise(b, i, n); } };
 
 struct WReport {
@@ -460,19 +663,20 @@ struct WReport {
     float grid_origin[3], grid_scale[3];
 };
 
-// Host-side level loop (Exec = CudaExec on the device, EmuExec in the test emulator).
+// Common first part of both production builders: world AABB of every prim, scene and centroid
+// bounds, the box padding and the quantisation grid, identity order.  Returns 1 when the whole
+// scene fits one leaf (done), 0 to continue.  acc[6..11] = centroid bounds keys.
 template<class Exec>
-int build_wbvh(Exec& ex, WBuild b, WReport* rep) {
+int wb_prologue(Exec& ex, WBuild& b, WReport* rep, uint32_t acc[12]) {
     rep->levels = 0;
     rep->n_pairs = 0;
     rep->error_bits = 0;
     rep->root_ref = kRefSentinel;
-    if (b.n_prims <= 0) return 0;
-    uint32_t acc[12];
+    if (b.n_prims <= 0) return 1;
     for (int k = 0; k < 12; ++k) acc[k] = ((k / 3) % 2 == 0) ? 0xffffffffu : 0u;
-    ex.upload(b.root_acc, acc, sizeof(acc));
-    ex.launch(b.n_prims, FnWbPrim{ b });
-    ex.download(acc, b.root_acc, sizeof(acc));
+    ex.upload(b.root_acc, acc, 12 * sizeof(uint32_t));
+    ex.wb_prim(b);
+    ex.download(acc, b.root_acc, 12 * sizeof(uint32_t));
     float scale = 0.0f;
     for (int k = 0; k < 3; ++k) {
         rep->scene_mn[k] = ordered_value(acc[k]);
@@ -486,16 +690,24 @@ int build_wbvh(Exec& ex, WBuild b, WReport* rep) {
     for (int k = 0; k < 3; ++k) {  // the quantisation grid spans the padded scene box plus two spare cells on each side,
         // so outward rounding never meets the clamp at 0 / 32767
         const float lo = rep->scene_mn[k] - b.pad, hi = rep->scene_mx[k] + b.pad;
-        const float scale = (kGridCells - 4.0f) / (hi - lo);
-        b.grid_scale[k] = rep->grid_scale[k] = scale;
-        b.grid_origin[k] = rep->grid_origin[k] = lo - 2.0f / scale;
+        const float gs = (kGridCells - 4.0f) / (hi - lo);
+        b.grid_scale[k] = rep->grid_scale[k] = gs;
+        b.grid_origin[k] = rep->grid_origin[k] = lo - 2.0f / gs;
     }
     ex.launch(b.n_prims, FnWbInit{ b });
     if (b.n_prims <= kFastLeafMax) {
         rep->root_ref = make_leaf_ref(0, b.n_prims);
         ex.launch(b.n_prims, FnWbEmit{ b });
-        return 0;
+        return 1;
     }
+    return 0;
+}
+
+// Host-side level loop (Exec = CudaExec on the device, EmuExec in the test emulator).
+template<class Exec>
+int build_wbvh(Exec& ex, WBuild b, WReport* rep) {
+    uint32_t acc[12];
+    if (wb_prologue(ex, b, rep, acc)) return 0;
     WItem root;
     root.start = 0;
     root.count = b.n_prims;
@@ -539,6 +751,44 @@ int build_wbvh(Exec& ex, WBuild b, WReport* rep) {
     }
     ex.launch(b.n_prims, FnWbEmit{ b });
     ex.launch(rep->n_pairs, FnWbQuantise{ b, rep->n_pairs });
+    return 0;
+}
+
+// LBVH build (see wb_body_morton): prologue, Morton codes, radix sort, one launch per level
+// bottom-up, emit.  No device->host round trip after the prologue.
+template<class Exec>
+int build_lbvh(Exec& ex, WBuild b, WReport* rep) {
+    uint32_t acc[12];
+    if (wb_prologue(ex, b, rep, acc)) return 0;
+    for (int k = 0; k < 3; ++k) {
+        const float lo = ordered_value(acc[6 + k]), hi = ordered_value(acc[9 + k]);
+        b.morton_min[k] = lo;
+        b.morton_scale[k] = hi > lo ? 1024.0f / (hi - lo) : 0.0f;
+    }
+    ex.launch(b.n_prims, FnWbMorton{ b });
+    ex.sort_pairs(b.keys, b.order, b.keys_tmp, b.order_next, b.sort_hist, b.n_prims, 30);
+    // radix tree; its height comes back with the root box
+    b.node_first = b.node_of;
+    b.node_last = b.node_of_next;
+    b.node_split = b.order_next;  // free once the sort is done
+    b.node_parent = b.scan;
+    b.node_count = reinterpret_cast<int*>(b.keys_tmp);
+    ex.launch(b.n_prims - 1, FnWbRadixNode{ b });
+    ex.launch(b.n_prims - 1, FnWbRadixBoxes{ b });
+    F4 root_mn;
+    ex.download(&root_mn, b.nbox_mn, sizeof(F4));
+    const int height = (int)f2u(root_mn.w);
+    rep->levels = height;
+    rep->n_pairs = b.n_prims - 1;  // internal-node slots in use (collapsed leaves are holes)
+    rep->root_ref = 0;
+    if (height + 2 > kStackSize || b.force_median) {
+        int k_last = 0;  // deepest level that still has an interior node (sizes at a level differ by <= 1)
+        while ((int)(((long long)b.n_prims + (1ll << (k_last + 1)) - 1) >> (k_last + 1)) > kFastLeafMax) ++k_last;
+        for (int k = k_last; k >= 0; --k) ex.launch(1 << k, FnWbLbvhLevel{ b, k });
+        rep->levels = k_last + 1;
+        rep->n_pairs = 1 << (k_last + 1);  // heap slots in use (leaf positions are holes)
+    }
+    ex.launch(b.n_prims, FnWbEmit{ b });
     return 0;
 }
 

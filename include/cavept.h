@@ -60,8 +60,11 @@ enum { CAVEPT_TRACE_FAST = 0, CAVEPT_TRACE_REFERENCE_WALK = 1 };
  * (cave/engine/renderer/path_tracer/bvh_accel.cpp:115-219) -- what cavept_get_mesh_bvh /
  * cavept_get_scene_arrays read back and REFERENCE_WALK traverses -- AND the production tree.
  * FAST: the production tree only (binned-SAH world-space builder), for renders and
- * per-frame rebuilds (the reference never rebuilds: path_tracer.cpp:69). */
-enum { CAVEPT_BVH_PARITY = 0, CAVEPT_BVH_FAST = 1 };
+ * per-frame rebuilds (the reference never rebuilds: path_tracer.cpp:69).
+ * LBVH: the production tree only, built by Morton codes + radix sort + a bottom-up AABB
+ * reduction (several times faster to build than FAST, somewhat slower to trace): for
+ * geometry that changes every frame (BASELINE config 5). */
+enum { CAVEPT_BVH_PARITY = 0, CAVEPT_BVH_FAST = 1, CAVEPT_BVH_LBVH = 2 };
 
 typedef struct cavept_config {
     int device;     /* CUDA ordinal; -1 = current device */
@@ -186,6 +189,10 @@ CAVEPT_API void* cavept_accum_device_ptr(cavept_ctx* ctx);  /* float4[width*heig
  * (mean, n) and (sum, n) so ranks can be combined with one sum-reduce of float4. */
 CAVEPT_API int cavept_accum_to_sums(cavept_ctx* ctx);
 CAVEPT_API int cavept_accum_from_sums(cavept_ctx* ctx);
+/* The device radix sort the LBVH builder orders its Morton codes with, on host arrays (copied in,
+ * sorted on the device by the low `key_bits` of the keys, copied back): stable, so the result is
+ * defined bit for bit.  Exposed so the sort can be checked on its own at full size. */
+CAVEPT_API int cavept_sort_pairs(cavept_ctx* ctx, uint32_t* keys, int32_t* values, int count, int key_bits);
 
 #ifdef __cplusplus
 }

@@ -54,11 +54,12 @@ def run_static(tag, scene, w, h, mb, spp_total, spp_launch, bvh_mode):
         print(json.dumps(line), flush=True)
 
 
-def run_animated(frames=6, nu=1600, nv=1600):
+def run_animated(frames=6, nu=1600, nv=1600, mode=None):
+    mode = mode or cb.BvhMode.LBVH
     scene = scenes.animated_scene(nu, nv)
     w, h, mb = 1920, 1080, 8
     poses = [scenes.animated_sheet(0.05 * (k + 1), nu, nv, with_normals=False).positions for k in range(frames)]
-    with cb.PathTracer(w, h, mb, bvh_mode=cb.BvhMode.FAST) as pt:
+    with cb.PathTracer(w, h, mb, bvh_mode=mode) as pt:
         pt.set_mode(cb.PathTracerMode.INTERACTIVE)
         pt.upload_scene(scene)
         pt.set_camera(scene.camera)
@@ -77,7 +78,7 @@ def run_animated(frames=6, nu=1600, nv=1600):
                          "frame_wall_ms": (t2 - t0) * 1e3, "segments": st["segments"], "levels": st["fast_build_levels"], "launches": st["fast_build_launches"]})
         warm = rows[1:]
         med = lambda key: float(np.median([r[key] for r in warm]))
-        line = {"config": 5, "scene": scene.name, "triangles": scene.n_tris, "width": w, "height": h, "max_bounce": mb, "frames": frames,
+        line = {"config": 5, "builder": mode.name, "scene": scene.name, "triangles": scene.n_tris, "width": w, "height": h, "max_bounce": mb, "frames": frames,
                 "bvh_fast_build_ms_median": med("bvh_fast_build_ms"), "rebuild_call_wall_ms_median": med("rebuild_call_wall_ms"), "render_1spp_ms_median": med("render_ms"),
                 "frame_wall_ms_median": med("frame_wall_ms"), "M_segments_per_s": med("segments") / med("render_ms") / 1e3, "h2d_bytes_per_frame": int(poses[0].nbytes),
                 "levels": warm[-1]["levels"], "launches": warm[-1]["launches"], "per_frame": rows}
@@ -91,4 +92,5 @@ if __name__ == "__main__":
     if 4 in which:
         run_static(4, scenes.breakfast_scene(), 3840, 2160, 8, 128, 8, cb.BvhMode.PARITY)
     if 5 in which:
-        run_animated()
+        run_animated(mode=cb.BvhMode.LBVH)
+        run_animated(mode=cb.BvhMode.FAST)

@@ -4,6 +4,7 @@
 // product uses (bvh_parity_driver.h, compact_body.h), so the algorithms can be checked
 // against the oracle in a container without a GPU.  Built by tests/emu_loader.py with
 // g++ -ffp-contract=off.  The product never links this.
+#include <algorithm>
 #include <cstdlib>
 #include <cstring>
 #include <vector>
@@ -32,6 +33,13 @@ struct EmuExec {
         for (int i = 0; i < n; ++i) { out[i] = run; run += in[i]; }
         out[n] = run;
     }
+    void sort_pairs(uint32_t* keys, int* vals, uint32_t*, int*, int*, int n, int) {
+        std::vector<std::pair<uint32_t, int>> v(n);
+        for (int i = 0; i < n; ++i) v[i] = { keys[i], vals[i] };
+        std::stable_sort(v.begin(), v.end(), [](const std::pair<uint32_t, int>& a, const std::pair<uint32_t, int>& b) { return a.first < b.first; });
+        for (int i = 0; i < n; ++i) { keys[i] = v[i].first; vals[i] = v[i].second; }
+    }
+    void wb_prim(const WBuild& b) { launch(b.n_prims, FnWbPrim{ b }); }
     void upload(void* dst, const void* src, size_t bytes) { std::memcpy(dst, src, bytes); }
     void download(void* dst, const void* src, size_t bytes) { std::memcpy(dst, src, bytes); }
     void fill(void* dst, int byte, size_t bytes) { std::memset(dst, byte, bytes); }
@@ -88,7 +96,7 @@ EMU_API int emu_bvh_build(const GpuPtVertex* vertices, const GpuPtIndex* indices
 // n_inst + 1 entries, inst_tri_off n_inst.  fnodes needs 2 * (n_prims + 8) entries, qpairs n_prims + 8, ftris /
 // fnormals n_prims.  Returns 0 ok; report = {levels, n_pairs, root_ref, error_bits}.
 EMU_API int emu_wbvh_build(const GpuPtVertex* vertices, const GpuPtIndex* indices, const GpuPtMesh* instances, int n_inst, const int* inst_prim_off,
-                           const int* inst_tri_off, int force_median, FastNode* fnodes, QPair* qpairs, FastTri* ftris, FastTri* fnormals, int* report, float* out_pad,
+                           const int* inst_tri_off, int force_median /* 2: LBVH builder, 3: its balanced fallback */, FastNode* fnodes, QPair* qpairs, FastTri* ftris, FastTri* fnormals, int* report, float* out_pad,
                            float* out_grid) {
     const int P = inst_prim_off[n_inst];
     const size_t items_cap = (size_t)P / 2 + 8, pairs_cap = (size_t)P + 8;
@@ -106,7 +114,14 @@ EMU_API int emu_wbvh_build(const GpuPtVertex* vertices, const GpuPtIndex* indice
     b.inst_tri_off = inst_tri_off;
     b.n_inst = n_inst;
     b.n_prims = P;
-    b.force_median = force_median;
+    b.force_median = (force_median == 1 || force_median == 3) ? 1 : 0;  // 3: LBVH with the balanced fallback forced
+    std::vector<uint32_t> keys(P), keys_tmp(P);
+    std::vector<F4> nbox_mn(pairs_cap), nbox_mx(pairs_cap);
+    b.keys = keys.data();
+    b.keys_tmp = keys_tmp.data();
+    b.sort_hist = nullptr;
+    b.nbox_mn = nbox_mn.data();
+    b.nbox_mx = nbox_mx.data();
     b.bmin = bmin.data();
     b.bmax = bmax.data();
     b.order = order.data();
@@ -128,7 +143,7 @@ EMU_API int emu_wbvh_build(const GpuPtVertex* vertices, const GpuPtIndex* indice
     b.fnormals = fnormals;
     EmuExec ex;
     WReport rep{};
-    const int rc = build_wbvh(ex, b, &rep);
+    const int rc = force_median >= 2 ? build_lbvh(ex, b, &rep) : build_wbvh(ex, b, &rep);
     report[0] = rep.levels;
     report[1] = rep.n_pairs;
     report[2] = wb_quantised_ref(rep.root_ref);

@@ -119,7 +119,7 @@ def test_fast_traversal_matches_reference_walk_with_transformed_instances(port_o
     assert sb["node_visits"] < sa["node_visits"]
 
 
-def _world_tree_check(emu, asm, sc):
+def _world_tree_check(emu, asm, sc, holes_ok=False):
     """Walks the production tree: every (instance, triangle) pair sits in exactly one leaf, every
     pair of sibling records is referenced once, every box contains what hangs below it."""
     P = emu.n_prims
@@ -159,6 +159,8 @@ def _world_tree_check(emu, asm, sc):
     # the references are the fp32 records' (interior: index of the child's own pair)
     org, scl = emu.grid[:3].astype(np.float64), emu.grid[3:].astype(np.float64)
     for k in range(emu.n_pairs):
+        if seen_pairs[k] == 0 and holes_ok:
+            continue  # heap slot of a leaf position in the implicit LBVH tree: never referenced
         q = emu.qpairs[k]
         for s_ in (0, 1):
             w = [int(v) for v in q[3 * s_: 3 * s_ + 3]]
@@ -170,7 +172,7 @@ def _world_tree_check(emu, asm, sc):
             a, r = int(n["a"]), int(np.int32(q[6 + s_]))
             assert r == (a >> 1 if a >= 0 else a)
     assert np.all(seen_slots == 1)
-    assert np.all(seen_pairs[: emu.n_pairs] == 1)
+    assert np.all(seen_pairs[: emu.n_pairs] <= 1) if holes_ok else np.all(seen_pairs[: emu.n_pairs] == 1)
     assert max_depth <= emu.fast_levels
     # slots carry (instance, triangle): together they enumerate every pair once
     inst = emu.ftris["v0"][:, 3].view(np.int32)
@@ -218,6 +220,30 @@ def test_world_tree_invariants(port_oracle, scene_cache, name):
     img_b, _ = emu.render(sc.camera, 32, 18, 0, 1, 3, fast=True)
     assert H.image_mismatch(img_a, img_b, rel=0.0, floor=0.0) <= 0.01  # same closest hits whatever the tree
     assert depth >= 1
+
+
+@pytest.mark.parametrize("name", ["tiny", "cornell", "heightfield"])
+def test_lbvh_tree_invariants_and_same_hits(port_oracle, scene_cache, name):
+    """The Morton-sort builder (CAVEPT_BVH_LBVH): same invariants, depth ceil(log2 N), and the
+    same closest hits as the SAH tree (an image is a function of the hits only)."""
+    sc = scene_cache(name)
+    asm = port_oracle.assemble(sc)
+    emu = E.EmuScene(asm, sc)
+    img_sah, _ = emu.render(sc.camera, 40, 24, 0, 2, 4, fast=True)
+    built = []
+    for inst in sc.instances:
+        if inst.mesh not in built:
+            built.append(inst.mesh)
+    emu.build_world(asm, sc, built, lbvh=True)  # binary radix tree
+    depth = _world_tree_check(emu, asm, sc, holes_ok=True)
+    assert depth == emu.fast_levels  # the height the bottom-up pass reports is the real one
+    img_lbvh, _ = emu.render(sc.camera, 40, 24, 0, 2, 4, fast=True)
+    assert H.image_mismatch(img_lbvh, img_sah, rel=0.0, floor=0.0) <= 0.01  # exact-tie pixels only
+    emu.build_world(asm, sc, built, lbvh=True, force_median=True)  # balanced fallback
+    depth = _world_tree_check(emu, asm, sc, holes_ok=True)
+    assert depth <= int(np.ceil(np.log2(max(emu.n_prims, 2)))) + 1
+    img_bal, _ = emu.render(sc.camera, 40, 24, 0, 2, 4, fast=True)
+    assert H.image_mismatch(img_bal, img_sah, rel=0.0, floor=0.0) <= 0.01
 
 
 def test_world_tree_with_mirrored_instance(port_oracle):

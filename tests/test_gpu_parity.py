@@ -321,3 +321,68 @@ def test_visit_counters(api, scene_cache):
         fast = pt.stats()
     assert walk["segments"] == fast["segments"] or abs(walk["segments"] - fast["segments"]) <= 2
     assert 0 < fast["node_visits"] < walk["node_visits"]  # ordered traversal visits fewer nodes than the fixed-order walk
+
+
+@pytest.mark.parametrize("n,bits", [(1, 32), (5, 8), (4096, 32), (4097, 30), (100_003, 30), (5_120_128, 30)])
+def test_device_radix_sort_is_a_stable_sort(api, n, bits):
+    """The LBVH builder's radix sort vs numpy's stable argsort: same keys, same values (stability
+    makes the order of equal keys part of the answer)."""
+    rng = np.random.default_rng(n)
+    hi = (1 << bits) - 1
+    keys = rng.integers(0, hi + 1, size=n, dtype=np.uint64).astype(np.uint32)
+    if n > 1000:
+        keys[: n // 2] &= np.uint32(0xFF)  # many duplicates
+    vals = np.arange(n, dtype=np.int32)
+    want = np.argsort(keys, kind="stable").astype(np.int32)
+    with api.PathTracer(16, 16, 1) as pt:
+        k, v = keys.copy(), vals.copy()
+        pt.sort_pairs(k, v, bits)
+    assert np.array_equal(v, want)
+    assert np.array_equal(k, keys[want])
+
+
+@pytest.mark.parametrize("name", ["tiny", "cornell", "sponza"])
+def test_lbvh_mode_same_closest_hits(api, scene_cache, name):
+    """CAVEPT_BVH_LBVH (Morton sort + bottom-up boxes) against the SAH tree: the image is a
+    function of the closest hits only, so the two must agree except at exact-tie pixels."""
+    sc = scene_cache(name)
+    w, h, mb = (160, 90, 5) if name != "sponza" else (320, 180, 8)
+    imgs, stats = [], []
+    for mode in (api.BvhMode.FAST, api.BvhMode.LBVH):
+        with api.PathTracer(w, h, mb, bvh_mode=mode) as pt:
+            pt.set_mode(api.PathTracerMode.INTERACTIVE)
+            pt.request_update(sc)
+            pt.reset_stats()
+            pt.render(0, 2, sync=True)
+            imgs.append(pt.read_accum())
+            stats.append(pt.stats())
+    assert H.image_mismatch(imgs[1], imgs[0], rel=0.0, floor=0.0) <= 0.005
+    assert abs(stats[0]["segments"] - stats[1]["segments"]) <= max(4, stats[0]["segments"] // 1000)
+    assert 1 <= stats[1]["fast_build_levels"] <= 38  # radix-tree height, or the balanced fallback's: fits the traversal stack
+
+
+def test_lbvh_rebuild_follows_moving_vertices(api, port_oracle):
+    """Per-frame rebuild (BASELINE config 5 at small size): new vertex positions -> LBVH rebuild
+    -> the image equals a fresh upload of the moved mesh, and matches the CPU oracle."""
+    from caveengine_b200 import scenes
+
+    sc = scenes.animated_scene(40, 40)
+    moved = scenes.animated_sheet(0.7, 40, 40)
+    w, h, mb = 128, 72, 4
+    with api.PathTracer(w, h, mb, bvh_mode=api.BvhMode.LBVH) as pt:
+        pt.set_mode(api.PathTracerMode.INTERACTIVE)
+        pt.request_update(sc)
+        pt.render(0, 1, sync=True)
+        pt.rebuild_mesh(0, moved.positions, moved.normals)
+        pt.reset()
+        pt.render(3, 2, sync=True)
+        got = pt.read_accum()
+    sc2 = scenes.Scene(sc.name, [moved, sc.meshes[1]], sc.instances, sc.materials, sc.camera)
+    with api.PathTracer(w, h, mb, bvh_mode=api.BvhMode.LBVH) as pt:
+        pt.set_mode(api.PathTracerMode.INTERACTIVE)
+        pt.request_update(sc2)
+        pt.render(3, 2, sync=True)
+        fresh = pt.read_accum()
+    assert np.array_equal(got, fresh)
+    want, _ = port_oracle.render(port_oracle.assemble(sc2), sc2.camera, w, h, 3, 2, mb)
+    assert H.image_mismatch(got, want, rel=1e-4) <= 0.01

@@ -14,7 +14,9 @@ from .api import (  # noqa: F401
     CaveptError,
     PathTracer,
     PathTracerMode,
+    SceneFile,
     TraceMode,
     library_path,
     load_library,
+    write_mesh_file,
 )

@@ -107,6 +107,15 @@ ABI = [
     ("cavept_accum_to_sums", C.c_int, [_P]),
     ("cavept_accum_from_sums", C.c_int, [_P]),
     ("cavept_sort_pairs", C.c_int, [_P, _P, _P, C.c_int, C.c_int]),
+    ("cavept_scene_file_open", C.c_int, [C.c_char_p, C.c_char_p, C.POINTER(_P), C.c_char_p, C.c_size_t]),
+    ("cavept_mesh_file_open", C.c_int, [C.c_char_p, C.POINTER(_P), C.c_char_p, C.c_size_t]),
+    ("cavept_scene_file_close", None, [_P]),
+    ("cavept_scene_file_counts", C.c_int, [_P] + [C.POINTER(C.c_int)] * 4),
+    ("cavept_scene_file_meshes", C.POINTER(_Mesh), [_P]),
+    ("cavept_scene_file_instances", C.POINTER(_Instance), [_P]),
+    ("cavept_scene_file_materials", C.POINTER(_Material), [_P]),
+    ("cavept_upload_scene_file", C.c_int, [_P, _P]),
+    ("cavept_mesh_file_write", C.c_int, [C.c_char_p, C.POINTER(_Mesh)]),
 ]
 
 
@@ -141,6 +150,79 @@ MATERIAL_DT = np.dtype([("base_color", "<f4", 3), ("roughness", "<f4"), ("emissi
 
 def _f3(v):
     return (C.c_float * 3)(*[float(x) for x in v])
+
+
+class SceneFile:
+    """A `.scene` (or a bare `.mesh`) of the engine parsed by the library's ingest
+    (include/cavept.h, section "asset ingest").  Host-side only:
+    usable without a GPU.  `to_scene(camera)` copies the arrays into a `scenes.Scene` so the
+    same inputs can be handed to the oracle."""
+
+    def __init__(self, path: str, resource_root: Optional[str] = None):
+        self._lib = load_library()
+        self._h = _P()
+        err = C.create_string_buffer(512)
+        if path.endswith(".mesh"):
+            rc = self._lib.cavept_mesh_file_open(path.encode(), C.byref(self._h), err, len(err))
+        else:
+            rc = self._lib.cavept_scene_file_open(path.encode(), None if resource_root is None else resource_root.encode(), C.byref(self._h), err, len(err))
+        if rc != 0:
+            self._h = _P()
+            raise CaveptError(rc, err.value.decode(errors="replace"))
+        n = [C.c_int() for _ in range(4)]
+        self._lib.cavept_scene_file_counts(self._h, *[C.byref(x) for x in n])
+        self.mesh_count, self.instance_count, self.material_count, self.skipped_renderers = [x.value for x in n]
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.cavept_scene_file_close(self._h)
+            self._h = _P()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    @property
+    def handle(self):
+        return self._h
+
+    def to_scene(self, camera=None, name: str = "file"):
+        from . import scenes
+
+        def arr(ptr, n, dt):
+            return np.ctypeslib.as_array(C.cast(ptr, C.POINTER(C.c_uint8)), shape=(n * np.dtype(dt).itemsize,)).view(dt).copy() if n else np.zeros(0, dt)
+
+        meshes, cm = [], self._lib.cavept_scene_file_meshes(self._h)
+        for k in range(self.mesh_count):
+            m = cm[k]
+            meshes.append(scenes.Mesh(arr(m.positions, m.vertex_count * 3, np.float32).reshape(-1, 3), arr(m.normals, m.vertex_count * 3, np.float32).reshape(-1, 3),
+                                      arr(m.indices, m.index_count, np.uint32)))
+        ci = self._lib.cavept_scene_file_instances(self._h)
+        instances = [scenes.Instance(ci[k].mesh, ci[k].material, np.array(list(ci[k].transform), dtype=np.float32)) for k in range(self.instance_count)]
+        cmat = self._lib.cavept_scene_file_materials(self._h)
+        f = np.float32
+        materials = [scenes.Material(tuple(f(x) for x in cmat[k].base_color), f(cmat[k].roughness), f(cmat[k].metallic), f(cmat[k].emissive)) for k in range(self.material_count)]
+        return scenes.Scene(name, meshes, instances, materials, camera)
+
+
+def write_mesh_file(path: str, mesh) -> None:
+    """Writes a `scenes.Mesh` in the engine's `.mesh` layout (cavept_mesh_file_write)."""
+    lib = load_library()
+    pos = np.ascontiguousarray(mesh.positions, dtype=np.float32)
+    nrm = np.ascontiguousarray(mesh.normals, dtype=np.float32)
+    idx = np.ascontiguousarray(mesh.indices, dtype=np.uint32)
+    cm = _Mesh(pos.ctypes.data, nrm.ctypes.data, idx.ctypes.data, pos.shape[0], idx.size)
+    rc = lib.cavept_mesh_file_write(path.encode(), C.byref(cm))
+    if rc != 0:
+        raise CaveptError(rc, f"cannot write {path}")
 
 
 class PathTracer:
@@ -210,6 +292,11 @@ class PathTracer:
         inst = self._instances(scene.instances)
         mats = self._materials(scene.materials)
         self._check(self._lib.cavept_upload_scene(self._ctx, meshes, len(scene.meshes), inst, len(scene.instances), mats, len(scene.materials)))
+
+    def upload_scene_file(self, scene_file: "SceneFile"):
+        """cavept_upload_scene_file: the parsed arrays go to the device without a Python copy."""
+        self._check(self._lib.cavept_upload_scene_file(self._ctx, scene_file.handle))
+        self._resident = True
 
     @staticmethod
     def _instances(instances):

@@ -194,6 +194,30 @@ CAVEPT_API int cavept_accum_from_sums(cavept_ctx* ctx);
  * defined bit for bit.  Exposed so the sort can be checked on its own at full size. */
 CAVEPT_API int cavept_sort_pairs(cavept_ctx* ctx, uint32_t* keys, int32_t* values, int count, int key_bits);
 
+/* ---- asset ingest: the engine's own files -> the flat arrays of
+ *      cavept_upload_scene.  Host-side parsing only; nothing here touches the device.
+ *      .mesh  = MeshAsset::SerializeBinary (cave/engine/assets/mesh_asset.cpp:45-61) over Archive's
+ *               "u64 count + raw elements" vectors (cave/engine/core/io/archive.h:56-75);
+ *      .scene = the entity YAML of Scene serialisation (cave/engine/scene/scene.cpp:370,437); world
+ *               matrices follow TransformComponent::GetLocalMatrix (scene/transform_component.cpp:16-21)
+ *               and UpdateHierarchy (systems/ecs_systems.cpp:139-171) in glm's fp32 operation order;
+ *               one instance per entity with MeshRendererComponent + TransformComponent, material =
+ *               materials[0] (path_tracer.cpp:227-231); mesh GUIDs resolve through `*.mesh.meta`
+ *               side-cars found under resource_root (NULL = the scene file's directory).  Renderers
+ *               whose mesh does not resolve are skipped, as DEV_VERIFY does (path_tracer.cpp:216),
+ *               and counted.  `err` (may be NULL) receives a message on failure. ------------------- */
+typedef struct cavept_scene_file cavept_scene_file;
+CAVEPT_API int cavept_scene_file_open(const char* scene_path, const char* resource_root, cavept_scene_file** out, char* err, size_t err_capacity);
+CAVEPT_API int cavept_mesh_file_open(const char* mesh_path, cavept_scene_file** out, char* err, size_t err_capacity); /* one mesh, identity instance, default material */
+CAVEPT_API void cavept_scene_file_close(cavept_scene_file* scene);
+CAVEPT_API int cavept_scene_file_counts(const cavept_scene_file* scene, int* meshes, int* instances, int* materials, int* skipped_renderers);
+CAVEPT_API const cavept_mesh* cavept_scene_file_meshes(const cavept_scene_file* scene);       /* valid until close */
+CAVEPT_API const cavept_instance* cavept_scene_file_instances(const cavept_scene_file* scene);
+CAVEPT_API const cavept_material* cavept_scene_file_materials(const cavept_scene_file* scene);
+CAVEPT_API int cavept_upload_scene_file(cavept_ctx* ctx, const cavept_scene_file* scene);     /* == cavept_upload_scene on the arrays above */
+/* Writes a mesh in the engine's .mesh layout (one subset, RENDERABLE, no tangents/uvs/skin). */
+CAVEPT_API int cavept_mesh_file_write(const char* path, const cavept_mesh* mesh);
+
 #ifdef __cplusplus
 }
 #endif

@@ -386,3 +386,55 @@ def test_lbvh_rebuild_follows_moving_vertices(api, port_oracle):
     assert np.array_equal(got, fresh)
     want, _ = port_oracle.render(port_oracle.assemble(sc2), sc2.camera, w, h, 3, 2, mb)
     assert H.image_mismatch(got, want, rel=1e-4) <= 0.01
+
+
+# ---- asset ingest (section 8 row f3) -----------------------------------------------------------
+@pytest.mark.parametrize("mode", ["REFERENCE_WALK", "FAST"])
+def test_ingested_scene_file_renders_like_the_oracle(api, best_oracle, tmp_path, mode):
+    """`.mesh` + `.meta` + `.scene` files in the engine's formats -> cavept_scene_file_open ->
+    cavept_upload_scene_file -> render; the oracle gets the same parsed arrays.  BVH bit-exact,
+    image within the tolerance stated at the top of this file."""
+    from test_ingest import GUID_A, GUID_B, write_meta, write_scene
+
+    box, ball, floor = str(tmp_path / "box.mesh"), str(tmp_path / "models" / "ball.mesh"), str(tmp_path / "floor.mesh")
+    (tmp_path / "models").mkdir()
+    api.write_mesh_file(box, scenes._open_box(0.8, 0.8, 0.8))
+    api.write_mesh_file(ball, scenes._sphere(24, 16, 0.5, 8, bump=0.05))
+    api.write_mesh_file(floor, scenes.heightfield_mesh(20, 20, 5, cell=0.3, height=0.1))
+    guid_f = "AAAAAAAA-0000-1111-2222333344445555"
+    write_meta(box, GUID_A), write_meta(ball, GUID_B), write_meta(floor, guid_f)
+    ident = [0, 0, 0, 0, 0, 0, 1, 1, 1, 1]
+    s, c = float(np.sin(0.3)), float(np.cos(0.3))
+    ents = [
+        {"id": 1, "trs": [0, 0.2, 0, 0, s, 0, c, 1, 1, 1]},  # root, yawed
+        {"id": 2, "parent": 1, "trs": [-3, -0.2, -3, 0, 0, 0, 1, 1, 1, 1], "mesh_guid": guid_f, "materials": [10]},
+        {"id": 3, "parent": 1, "trs": [0, 0.9, 0.3, 0, 0, 0, 1, 1.5, 1.5, 1.5], "mesh_guid": GUID_B, "materials": [11]},
+        {"id": 4, "parent": 3, "trs": [1.2, 0, 0, 0, 0, 0, 1, 0.5, 0.5, 0.5], "mesh_guid": GUID_B, "materials": [12]},  # same mesh: material 11 wins
+        {"id": 5, "parent": 1, "trs": [-1.2, 0.6, 0.2, 0.1, 0.2, 0.0, 0.97467943, 1, 1, 1], "mesh_guid": GUID_A, "materials": [12]},
+        {"id": 10, "material": [0.7, 0.7, 0.6, 0.9, 0.0, 0.0]},
+        {"id": 11, "material": [0.9, 0.6, 0.2, 0.2, 0.9, 0.0]},
+        {"id": 12, "material": [1.0, 0.9, 0.8, 1.0, 0.0, 6.0]},
+        {"id": 13, "trs": ident},
+    ]
+    path = str(tmp_path / "room.scene")
+    write_scene(path, ents)
+    cam = scenes.look_at((0.5, 1.8, -4.0), (0, 0.6, 0))
+    w, h, mb = 96, 54, 5
+    with api.SceneFile(path) as sf:
+        assert (sf.mesh_count, sf.instance_count, sf.material_count) == (3, 4, 3)
+        sc = sf.to_scene(cam)
+        asm = best_oracle.assemble(sc)
+        want, st = best_oracle.render(asm, cam, w, h, 0, 4, mb)
+        with api.PathTracer(w, h, mb, trace_mode=getattr(api.TraceMode, mode), device=0) as pt:
+            pt.set_mode(api.PathTracerMode.INTERACTIVE)
+            pt.upload_scene_file(sf)
+            pt.set_camera(cam)
+            got = pt.get_scene_arrays()
+            assert got["bvhs"].tobytes() == asm.bvhs.tobytes()
+            assert got["meshes"].tobytes() == asm.meshes.tobytes() and got["materials"].tobytes() == asm.materials.tobytes()
+            pt.reset_stats()
+            pt.render(0, 4, sync=True)
+            img = pt.read_accum()
+            segs = pt.stats()["segments"]
+    assert abs(segs - st["segments"]) <= max(4, st["segments"] // 500)
+    _pixel_tol(img, want)

@@ -95,6 +95,7 @@ ABI = [
     ("cavept_reset", C.c_int, [_P]),
     ("cavept_render", C.c_int, [_P, C.c_int, C.c_int]),
     ("cavept_sync", C.c_int, [_P]),
+    ("cavept_render_tile", C.c_int, [_P] + [C.c_int] * 6),
     ("cavept_read_accum", C.c_int, [_P, _P, C.c_size_t]),
     ("cavept_read_tonemapped_rgba8", C.c_int, [_P, _P, C.c_size_t]),
     ("cavept_read_tonemapped_rgba32f", C.c_int, [_P, _P, C.c_size_t]),
@@ -350,6 +351,12 @@ class PathTracer:
     # -- the pass ----------------------------------------------------------------------------
     def render(self, first_frame_index: int, n_frames: int = 1, sync: bool = False):
         self._check(self._lib.cavept_render(self._ctx, first_frame_index, n_frames))
+        if sync:
+            self.sync()
+
+    def render_tile(self, x0: int, y0: int, w: int, h: int, first_frame_index: int, n_frames: int = 1, sync: bool = False):
+        """PathTracerMode::TILED: the pass over one pixel rectangle (c_tileOffset, cbuffer.hlsl.h:183)."""
+        self._check(self._lib.cavept_render_tile(self._ctx, x0, y0, w, h, first_frame_index, n_frames))
         if sync:
             self.sync()
 

@@ -50,3 +50,33 @@ def composite(accum, dst: int = 0, all_ranks: bool = False, group=None):
     else:
         dist.reduce(accum, dst=dst, op=dist.ReduceOp.SUM, group=group)
     return accum
+
+
+# ---- image-tile split (the latency-oriented alternative) ---------------
+def row_band(height: int, rank: int, world: int, align: int = 8) -> Tuple[int, int]:
+    """Rows [y0, y0 + h) of the image owned by `rank`: whole multiples of `align` rows (a thread
+    block is 8 rows tall), as even as possible, the last band takes the remainder.  h may be 0."""
+    units = (height + align - 1) // align
+    base, rem = divmod(units, world)
+    u0 = rank * base + min(rank, rem)
+    u1 = u0 + base + (1 if rank < rem else 0)
+    y0, y1 = min(u0 * align, height), min(u1 * align, height)
+    return y0, y1 - y0
+
+
+def all_bands(height: int, world: int, align: int = 8) -> List[Tuple[int, int]]:
+    return [row_band(height, r, world, align) for r in range(world)]
+
+
+def gather_bands(accum, bands: List[Tuple[int, int]], group=None):
+    """Every rank rendered its own row band of a (H, W, 4) accumulator; afterwards every rank holds
+    the whole image.  A band is a contiguous slice, so each is one broadcast from its owner -- the
+    message per rank is its band, not the image (no arithmetic: the result is bit-exact)."""
+    import torch.distributed as dist
+
+    if not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return accum
+    for r, (y0, h) in enumerate(bands):
+        if h > 0:
+            dist.broadcast(accum[y0:y0 + h], src=dist.get_global_rank(group, r) if group is not None else r, group=group)
+    return accum

@@ -652,10 +652,13 @@ CAVEPT_API int cavept_reset(cavept_ctx* ctx) {
     return CAVEPT_OK;
 }
 
-CAVEPT_API int cavept_render(cavept_ctx* ctx, int first_frame_index, int n_frames) {
+// One launch over the pixel rectangle [x0, x0+w) x [y0, y0+h); w == 0 means the whole image.
+static int render_rect(cavept_ctx* ctx, int x0, int y0, int w, int h, int first_frame_index, int n_frames) {
     if (!ctx) return CAVEPT_ERR_INVALID_ARG;
     if (n_frames <= 0) return fail(ctx, CAVEPT_ERR_INVALID_ARG, "n_frames must be positive");
-    if (!cavept_is_active(ctx)) return fail(ctx, CAVEPT_ERR_NOT_READY, "path tracer not active (mode INTERACTIVE and a resident scene are required)");
+    const bool tiled = w > 0;
+    const bool active = cavept_is_active(ctx) || (tiled && ctx->mode == CAVEPT_MODE_TILED && ctx->scene_resident);
+    if (!active) return fail(ctx, CAVEPT_ERR_NOT_READY, "path tracer not active (mode INTERACTIVE and a resident scene are required)");
     if (ctx->cfg.trace_mode == CAVEPT_TRACE_REFERENCE_WALK && !ctx->nodes_resident) return fail(ctx, CAVEPT_ERR_NOT_READY, "CAVEPT_TRACE_REFERENCE_WALK needs the reference-layout BVH (CAVEPT_BVH_PARITY)");
     if (int e = select_device(ctx)) return e;
     TraceParams p{};
@@ -681,6 +684,13 @@ CAVEPT_API int cavept_render(cavept_ctx* ctx, int first_frame_index, int n_frame
     p.cam_distance = std::tan(ctx->cam_fov * 3.141592653589793f / 180.0f);  // path_tracer.cs.glsl:31-32 (the full angle, as the shader has it)
     p.width = ctx->cfg.width;
     p.height = ctx->cfg.height;
+    if (tiled) {
+        p.tile_x0 = x0, p.tile_y0 = y0, p.tile_x1 = x0 + w, p.tile_y1 = y0 + h;
+        if (ctx->dirty) {  // c_sceneDirty with tiles: an emptied accumulator (weight 0) makes every tile's first sample an overwrite
+            CU(ctx, cudaMemsetAsync(ctx->d_accum.ptr, 0, (size_t)ctx->cfg.width * ctx->cfg.height * sizeof(F4), ctx->ex.stream));
+            ctx->dirty = false;
+        }
+    }
     p.max_bounce = ctx->cfg.max_bounce;
     p.first_frame = first_frame_index;
     p.n_frames = n_frames;
@@ -692,6 +702,16 @@ CAVEPT_API int cavept_render(cavept_ctx* ctx, int first_frame_index, int n_frame
     CU(ctx, cudaEventRecord(ctx->ev1, ctx->ex.stream));
     ctx->dirty = false;
     return check_exec(ctx, "render launch");
+}
+
+CAVEPT_API int cavept_render(cavept_ctx* ctx, int first_frame_index, int n_frames) { return render_rect(ctx, 0, 0, 0, 0, first_frame_index, n_frames); }
+
+CAVEPT_API int cavept_render_tile(cavept_ctx* ctx, int x0, int y0, int w, int h, int first_frame_index, int n_frames) {
+    if (!ctx) return CAVEPT_ERR_INVALID_ARG;
+    if (x0 < 0 || y0 < 0 || w <= 0 || h <= 0 || x0 > ctx->cfg.width - w || y0 > ctx->cfg.height - h) {
+        return fail(ctx, CAVEPT_ERR_INVALID_ARG, "tile (%d,%d)+(%d,%d) is not inside the %dx%d image", x0, y0, w, h, ctx->cfg.width, ctx->cfg.height);
+    }
+    return render_rect(ctx, x0, y0, w, h, first_frame_index, n_frames);
 }
 
 CAVEPT_API int cavept_sync(cavept_ctx* ctx) {

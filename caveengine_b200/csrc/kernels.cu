@@ -324,8 +324,9 @@ int run_build_lbvh(CudaExec& ex, WBuild b, WReport* report) { return build_lbvh(
 template<bool kFast, bool kCount, int kQuorum = kStepQuorum, int kBatch = kShadeBatch>
 __global__ void __launch_bounds__(128, 8) k_trace(const TraceParams p) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int x = blockIdx.x * 16 + (warp & 1) * 8 + (lane & 7);
-    const int y = blockIdx.y * 8 + (warp >> 1) * 4 + (lane >> 3);
+    int x = p.tile_x0 + blockIdx.x * 16 + (warp & 1) * 8 + (lane & 7);
+    const int y = p.tile_y0 + blockIdx.y * 8 + (warp >> 1) * 4 + (lane >> 3);
+    if (p.tile_x1 > 0 && (x >= p.tile_x1 || y >= p.tile_y1)) x = p.width;  // outside the tile: the body treats x == width as no pixel
     unsigned long long cnt[3] = { 0ull, 0ull, 0ull };
     __shared__ int s_stack[kFast ? kStackSize * 128 : 1];  // [depth][thread]: conflict-free whatever each lane's depth
     unsigned int segs = kFast ? body_trace_pixel_fast<kCount, kQuorum, kBatch>(p, x, y, s_stack + threadIdx.x, 128, cnt) : body_trace_pixel_reference<kCount>(p, x, y, cnt);
@@ -343,7 +344,8 @@ __global__ void __launch_bounds__(128, 8) k_trace(const TraceParams p) {
 }
 
 void launch_trace(CudaExec& ex, const TraceParams& p, bool fast, bool count_visits) {
-    const dim3 grid((p.width + 15) / 16, (p.height + 7) / 8, 1), block(128, 1, 1);
+    const int tw = p.tile_x1 > 0 ? p.tile_x1 - p.tile_x0 : p.width, th = p.tile_x1 > 0 ? p.tile_y1 - p.tile_y0 : p.height;
+    const dim3 grid((tw + 15) / 16, (th + 7) / 8, 1), block(128, 1, 1);
     if (fast) {
         if (count_visits) k_trace<true, true><<<grid, block, 0, ex.stream>>>(p);
         else k_trace<true, false><<<grid, block, 0, ex.stream>>>(p);

@@ -86,6 +86,7 @@ struct TraceParams {
     float cam_pos[3], cam_right[3], cam_up[3], cam_fwd[3];
     float cam_distance;  // tan(c_cameraFovDegree * PI / 180), path_tracer.cs.glsl:31-32
     int width, height;
+    int tile_x0, tile_y0, tile_x1, tile_y1;  // pixel rectangle a launch covers (c_tileOffset, cbuffer.hlsl.h:183); all 0 = the full image
     int max_bounce;
     int first_frame, n_frames;
     int reset_first;  // c_sceneDirty for the first frame of the launch

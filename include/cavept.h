@@ -168,6 +168,14 @@ CAVEPT_API int cavept_reset(cavept_ctx* ctx);
  *      reference's running mean.  Asynchronous on the context's stream. ------------- */
 CAVEPT_API int cavept_render(cavept_ctx* ctx, int first_frame_index, int n_frames);
 CAVEPT_API int cavept_sync(cavept_ctx* ctx);
+/* PathTracerMode::TILED (path_tracer_render_system.h:13; "Not implemented" in the reference,
+ * path_tracer.cpp:53-55) with c_tileOffset (cave/shader/cbuffer.hlsl.h:183): the same pass over the
+ * pixel rectangle [x0, x0+w) x [y0, y0+h) only.  Seeds use the image coordinates, so the union of
+ * tiles of one frame equals cavept_render of that frame bit for bit.  Allowed in mode INTERACTIVE
+ * or TILED.  After cavept_reset the first tile launch empties the whole accumulator (weight 0), so
+ * every tile's first sample overwrites, as c_sceneDirty does for a full frame.  Also the unit of
+ * the image-tile split across GPUs. */
+CAVEPT_API int cavept_render_tile(cavept_ctx* ctx, int x0, int y0, int w, int h, int first_frame_index, int n_frames);
 
 /* ---- read-back.  The reference leaves RG_RES_PATHTRACER (RGBA32F, rgb = running
  *      mean, a = sample count; common_passes.cpp:1001-1009) on the GPU; this is the

@@ -77,3 +77,59 @@ def test_two_rank_composite_equals_single_process(tmp_path, n_frames):
     assert np.array_equal(got[..., 3], want[..., 3])  # total sample counts
     # summation order differs from the reference's running mean: tolerance 2e-6 relative
     assert np.allclose(got[..., :3], want[..., :3], rtol=2e-6, atol=1e-7)
+
+
+# ---- image-tile split -------------------------------------------------------------------------
+def test_row_bands_partition_exactly():
+    from caveengine_b200 import compositor as cp
+
+    for height, world in [(1080, 8), (1080, 2), (2160, 8), (54, 4), (7, 2), (8, 3), (36, 8)]:
+        bands = cp.all_bands(height, world)
+        rows = [y for (y0, h) in bands for y in range(y0, y0 + h)]
+        assert rows == list(range(height))
+        assert all(y0 % 8 == 0 for y0, h in bands if h)
+        hs = [h for _, h in bands]
+        assert max(hs) - min(hs) <= 15  # one 8-row unit, plus the truncated last unit
+
+
+def _band_worker(rank, world, port, w, h, mb, frames, out_path):
+    sys.path.insert(0, ROOT)
+    import torch
+    import torch.distributed as dist
+
+    from caveengine_b200 import compositor as cp
+    from caveengine_b200 import scenes
+    from oracle import oracle as O
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    sc = scenes.tiny_scene()
+    orc = O.port()
+    asm = orc.assemble(sc)
+    bands = cp.all_bands(h, world)
+    y0, bh = bands[rank]
+    acc = np.zeros((h, w, 4), dtype=np.float32)
+    if bh > 0:  # the oracle standing in for cavept_render_tile: same rect, image-space seeds
+        acc, _ = orc.render(asm, sc.camera, w, h, frames[0], frames[1], mb, accum=acc, rect=(0, y0, w, y0 + bh), threads=1)
+    t = torch.from_numpy(acc)
+    cp.gather_bands(t, bands)
+    np.save(out_path % rank, t.numpy())
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_rank_band_gather_is_bit_exact(tmp_path):
+    import torch.multiprocessing as mp
+
+    from caveengine_b200 import scenes
+    from oracle import oracle as O
+
+    w, h, mb, frames = 40, 27, 5, (2, 3)
+    out = str(tmp_path / "img%d.npy")
+    mp.spawn(_band_worker, args=(2, _free_port(), w, h, mb, frames, out), nprocs=2, join=True)
+    sc = scenes.tiny_scene()
+    orc = O.port()
+    want, _ = orc.render(orc.assemble(sc), sc.camera, w, h, frames[0], frames[1], mb, threads=1)
+    for r in range(2):
+        assert np.load(out % r).tobytes() == want.tobytes()

@@ -438,3 +438,31 @@ def test_ingested_scene_file_renders_like_the_oracle(api, best_oracle, tmp_path,
             segs = pt.stats()["segments"]
     assert abs(segs - st["segments"]) <= max(4, st["segments"] // 500)
     _pixel_tol(img, want)
+
+
+# ---- PathTracerMode::TILED (section 8 row f4) --------------------------------------------------
+@pytest.mark.parametrize("mode", ["REFERENCE_WALK", "FAST"])
+def test_tiles_equal_the_full_frame_bitwise(api, scene_cache, mode):
+    """Ragged tiles (not multiples of the 16x8 block) of the same frames, in scrambled order, must
+    rebuild cavept_render's accumulator bit for bit: seeds come from image coordinates."""
+    sc = scene_cache("tiny")
+    w, h, mb = 101, 57, 5
+    with _tracer(api, sc, w, h, mb, getattr(api.TraceMode, mode)) as pt:
+        pt.render(3, 2, sync=True)
+        pt.render(5, 1, sync=True)
+        want = pt.read_accum()
+        pt.set_mode(api.PathTracerMode.TILED)
+        assert not pt.is_active()  # PathTracer::IsActive is INTERACTIVE-only (path_tracer.cpp:312-322)
+        pt.reset()
+        xs, ys = [0, 37, 64, w], [0, 8, 29, h]
+        tiles = [(xs[i], ys[j], xs[i + 1] - xs[i], ys[j + 1] - ys[j]) for j in range(3) for i in range(3)]
+        for first, n in ((3, 2), (5, 1)):
+            for t in tiles[::-1] if first == 3 else tiles:
+                pt.render_tile(*t, first, n)
+        pt.sync()
+        got = pt.read_accum()
+        assert got.tobytes() == want.tobytes()
+        for bad in [(-1, 0, 4, 4), (0, 0, w + 1, 4), (w - 3, 0, 4, 4), (0, 0, 0, 4)]:
+            with pytest.raises(api.CaveptError) as e:
+                pt.render_tile(*bad, 0, 1)
+            assert e.value.code == 1  # CAVEPT_ERR_INVALID_ARG

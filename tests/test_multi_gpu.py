@@ -79,3 +79,57 @@ def test_two_gpu_composite_equals_single_gpu_and_oracle(tmp_path, port_oracle):
     want, _ = port_oracle.render(port_oracle.assemble(sc), sc.camera, w, h, first, n_frames, mb)
     bad = (np.abs(got - want)[..., :3] > 1e-4 * (np.abs(want[..., :3]) + 1e-3)).any(axis=-1).mean()
     assert bad <= 0.01
+
+
+def _band_worker(rank, world, port, first, n_frames, w, h, mb, out_path):
+    sys.path.insert(0, ROOT)
+    import torch
+    import torch.distributed as dist
+
+    import caveengine_b200 as cb
+    from caveengine_b200 import compositor as cp
+    from caveengine_b200 import scenes
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    sc = scenes.cornell_scene()
+    bands = cp.all_bands(h, world)
+    y0, bh = bands[rank]
+    with cb.PathTracer(w, h, mb, device=rank) as pt:
+        pt.set_mode(cb.PathTracerMode.TILED)
+        pt.request_update(sc)
+        stream = torch.cuda.ExternalStream(pt.stream_handle, device=torch.device("cuda", rank))
+        with torch.cuda.stream(stream):
+            pt.render_tile(0, y0, w, bh, first, n_frames)
+            cp.gather_bands(pt.accum_as_torch(), bands)
+        pt.sync()
+        got = pt.read_accum()
+        if rank == 0:
+            pt.set_mode(cb.PathTracerMode.INTERACTIVE)
+            pt.reset()
+            pt.render(first, n_frames, sync=True)
+            np.savez(out_path, got=got, single=pt.read_accum())
+        else:
+            np.save(out_path + ".rank1.npy", got)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.gpu
+def test_two_gpu_image_tile_split_is_bit_exact(tmp_path):
+    """Image tiles per GPU (row bands) + one broadcast per band: every rank ends with the
+    single-GPU accumulator, bit for bit (no arithmetic in the exchange)."""
+    import torch
+
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    import torch.multiprocessing as mp
+
+    w, h, mb, first, n_frames = 160, 90, 5, 2, 3
+    out = str(tmp_path / "img.npz")
+    mp.spawn(_band_worker, args=(2, _free_port(), first, n_frames, w, h, mb, out), nprocs=2, join=True)
+    z = np.load(out)
+    assert z["got"].tobytes() == z["single"].tobytes()
+    assert np.load(out + ".rank1.npy").tobytes() == z["single"].tobytes()

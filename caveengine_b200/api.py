@@ -108,6 +108,7 @@ ABI = [
     ("cavept_accum_to_sums", C.c_int, [_P]),
     ("cavept_accum_from_sums", C.c_int, [_P]),
     ("cavept_sort_pairs", C.c_int, [_P, _P, _P, C.c_int, C.c_int]),
+    ("cavept_probe_intersections", C.c_int, [_P, C.c_int, _P, _P, _P, _P]),
     ("cavept_scene_file_open", C.c_int, [C.c_char_p, C.c_char_p, C.POINTER(_P), C.c_char_p, C.c_size_t]),
     ("cavept_mesh_file_open", C.c_int, [C.c_char_p, C.POINTER(_P), C.c_char_p, C.c_size_t]),
     ("cavept_scene_file_close", None, [_P]),
@@ -414,6 +415,16 @@ class PathTracer:
         """Device radix sort of (uint32 key, int32 value) pairs, in place (stable)."""
         assert keys.dtype == np.uint32 and values.dtype == np.int32 and keys.flags.c_contiguous and values.flags.c_contiguous and keys.size == values.size
         self._check(self._lib.cavept_sort_pairs(self._ctx, keys.ctypes.data, values.ctypes.data, int(keys.size), int(key_bits)))
+
+    def probe_intersections(self, rays: np.ndarray, triangles: np.ndarray, boxes: np.ndarray) -> np.ndarray:
+        """cavept_probe_intersections: (n,7) rays, (n,9) triangles, (n,6) boxes -> (n,8) results."""
+        r = np.ascontiguousarray(rays, dtype=np.float32).reshape(-1, 7)
+        t = np.ascontiguousarray(triangles, dtype=np.float32).reshape(-1, 9)
+        b = np.ascontiguousarray(boxes, dtype=np.float32).reshape(-1, 6)
+        assert r.shape[0] == t.shape[0] == b.shape[0]
+        out = np.zeros((r.shape[0], 8), dtype=np.float32)
+        self._check(self._lib.cavept_probe_intersections(self._ctx, r.shape[0], r.ctypes.data, t.ctypes.data, b.ctypes.data, out.ctypes.data))
+        return out
 
     def accum_as_torch(self):
         """Zero-copy torch view of the device accumulator (H, W, 4) float32, for

@@ -810,6 +810,25 @@ CAVEPT_API int cavept_accum_from_sums(cavept_ctx* ctx) {
 
 }  // extern "C"
 
+CAVEPT_API int cavept_probe_intersections(cavept_ctx* ctx, int count, const float* rays, const float* triangles, const float* boxes, float* out) {
+    if (!ctx || !rays || !triangles || !boxes || !out || count < 0) return CAVEPT_ERR_INVALID_ARG;
+    if (int e = select_device(ctx)) return e;
+    if (count == 0) return CAVEPT_OK;
+    DevBuf<float> r, t, b, o;
+    CU(ctx, r.reserve((size_t)count * 7));
+    CU(ctx, t.reserve((size_t)count * 9));
+    CU(ctx, b.reserve((size_t)count * 6));
+    CU(ctx, o.reserve((size_t)count * 8));
+    ctx->ex.upload(r.ptr, rays, (size_t)count * 7 * sizeof(float));
+    ctx->ex.upload(t.ptr, triangles, (size_t)count * 9 * sizeof(float));
+    ctx->ex.upload(b.ptr, boxes, (size_t)count * 6 * sizeof(float));
+    launch_probe(ctx->ex, r.ptr, t.ptr, b.ptr, o.ptr, count);
+    CU(ctx, cudaMemcpyAsync(out, o.ptr, (size_t)count * 8 * sizeof(float), cudaMemcpyDeviceToHost, ctx->ex.stream));
+    CU(ctx, cudaStreamSynchronize(ctx->ex.stream));
+    r.release(); t.release(); b.release(); o.release();
+    return check_exec(ctx, "probe_intersections");
+}
+
 CAVEPT_API int cavept_sort_pairs(cavept_ctx* ctx, uint32_t* keys, int32_t* values, int count, int key_bits) {
     if (!ctx || !keys || !values || count < 0 || key_bits < 1 || key_bits > 32) return CAVEPT_ERR_INVALID_ARG;
     if (int e = select_device(ctx)) return e;

@@ -357,6 +357,13 @@ void launch_trace(CudaExec& ex, const TraceParams& p, bool fast, bool count_visi
     ++ex.launches;
 }
 
+struct FnProbe {
+    const float *rays, *tris, *boxes;
+    float* out;
+    __device__ void operator()(int i) const { body_probe(rays, tris, boxes, out, i); }
+};
+void launch_probe(CudaExec& ex, const float* rays, const float* tris, const float* boxes, float* out, int n) { ex.launch(n, FnProbe{ rays, tris, boxes, out }); }
+
 // ---- tone pass: c/(c+1), pow(c, 1/2.2) (cave/shader/glsl/post_process.ps.glsl:72-76) ----
 __device__ __forceinline__ float tone(float c) {
     c = __fdiv_rn(c, c + 1.0f);

@@ -45,6 +45,7 @@ int run_build_wbvh(CudaExec& ex, WBuild b, WReport* report);
 int run_build_lbvh(CudaExec& ex, WBuild b, WReport* report);
 
 void launch_trace(CudaExec& ex, const TraceParams& p, bool fast, bool count_visits);
+void launch_probe(CudaExec& ex, const float* rays, const float* tris, const float* boxes, float* out, int n);
 void launch_tonemap_rgba8(CudaExec& ex, const F4* accum, unsigned char* out, int n_pixels);
 void launch_tonemap_f32(CudaExec& ex, const F4* accum, F4* out, int n_pixels);
 void launch_accum_scale(CudaExec& ex, F4* accum, int n_pixels, bool to_sums);

@@ -162,14 +162,46 @@ CV_HD bool hit_triangle_edges(F3 A, F3 AB, F3 AC, F3 origin, F3 direction, float
 }
 
 // ---- HitBvh, :133-149 ---------------------------------------------------------------
-CV_HD bool hit_bvh_reference(const Ray& r, F3 mn, F3 mx) {
+CV_HD void slab_interval_reference(const Ray& r, F3 mn, F3 mx, float& tmin, float& tmax) {
     const F3 t0 = (mn - r.origin) * r.inv_dir;
     const F3 t1 = (mx - r.origin) * r.inv_dir;
     const F3 ts = f3(min_ref(t0.x, t1.x), min_ref(t0.y, t1.y), min_ref(t0.z, t1.z));
     const F3 tb = f3(max_ref(t0.x, t1.x), max_ref(t0.y, t1.y), max_ref(t0.z, t1.z));
-    const float tmin = max_ref(ts.x, max_ref(ts.y, ts.z));
-    const float tmax = min_ref(tb.x, min_ref(tb.y, tb.z));
+    tmin = max_ref(ts.x, max_ref(ts.y, ts.z));
+    tmax = min_ref(tb.x, min_ref(tb.y, tb.z));
+}
+CV_HD bool hit_bvh_reference(const Ray& r, F3 mn, F3 mx) {
+    float tmin, tmax;
+    slab_interval_reference(r, mn, mx, tmin, tmax);
     return (tmin < tmax) && (r.t > tmin);
+}
+
+// Unit probe of the two routines above on caller-supplied rays, triangles and boxes (SURVEY.md
+// section 8 row a20: cross-check against the engine's CPU twins TestIntersection::RayTriangle /
+// RayAabb, cave/engine/math/intersection.cpp:18-70).  rays: origin xyz, direction xyz, t;
+// out: triangle hit, t, u, v, box hit, tmin, tmax, 0.
+CV_HD void body_probe(const float* rays, const float* tris, const float* boxes, float* out, int i) {
+    const float* r = rays + 7 * (size_t)i;
+    const float* t = tris + 9 * (size_t)i;
+    const float* b = boxes + 6 * (size_t)i;
+    Ray ray;
+    ray.origin = f3(r[0], r[1], r[2]);
+    ray.direction = f3(r[3], r[4], r[5]);
+    ray.inv_dir = recip3(ray.direction);
+    ray.t = r[6];
+    float ray_t = ray.t, u = 0.0f, v = 0.0f;
+    const bool tri_hit = hit_triangle(f3(t[0], t[1], t[2]), f3(t[3], t[4], t[5]), f3(t[6], t[7], t[8]), ray.origin, ray.direction, ray_t, u, v);
+    float tmin, tmax;
+    slab_interval_reference(ray, f3(b[0], b[1], b[2]), f3(b[3], b[4], b[5]), tmin, tmax);
+    float* o = out + 8 * (size_t)i;
+    o[0] = tri_hit ? 1.0f : 0.0f;
+    o[1] = ray_t;
+    o[2] = u;
+    o[3] = v;
+    o[4] = hit_bvh_reference(ray, f3(b[0], b[1], b[2]), f3(b[3], b[4], b[5])) ? 1.0f : 0.0f;
+    o[5] = tmin;
+    o[6] = tmax;
+    o[7] = 0.0f;
 }
 
 // ---- HitScene, :152-189, literal -----------------------------------------------------

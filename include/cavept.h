@@ -214,6 +214,13 @@ CAVEPT_API int cavept_sort_pairs(cavept_ctx* ctx, uint32_t* keys, int32_t* value
  *               side-cars found under resource_root (NULL = the scene file's directory).  Renderers
  *               whose mesh does not resolve are skipped, as DEV_VERIFY does (path_tracer.cpp:216),
  *               and counted.  `err` (may be NULL) receives a message on failure. ------------------- */
+/* Unit probe: runs the device's HitTriangle (shared_path_tracer.h:88-130) and
+ * HitBvh (:133-149) on `count` caller-supplied cases, for the cross-check against the engine's CPU twins
+ * TestIntersection::RayTriangle / RayAabb (cave/engine/math/intersection.cpp:18-70).
+ * rays: count x 7 (origin xyz, direction xyz, t); triangles: count x 9 (A, B, C); boxes: count x 6 (min, max);
+ * out: count x 8 (triangle hit 0/1, t after the test, u, v, box hit 0/1, slab tmin, slab tmax, 0). */
+CAVEPT_API int cavept_probe_intersections(cavept_ctx* ctx, int count, const float* rays, const float* triangles, const float* boxes, float* out);
+
 typedef struct cavept_scene_file cavept_scene_file;
 CAVEPT_API int cavept_scene_file_open(const char* scene_path, const char* resource_root, cavept_scene_file** out, char* err, size_t err_capacity);
 CAVEPT_API int cavept_mesh_file_open(const char* mesh_path, cavept_scene_file** out, char* err, size_t err_capacity); /* one mesh, identity instance, default material */

@@ -216,3 +216,8 @@ EMU_API long long emu_render(const GpuPtVertex* vertices, const GpuPtIndex* indi
     }
     return segs;
 }
+
+// the product's HitTriangle / HitBvh bodies on caller-supplied cases
+EMU_API void emu_probe(int n, const float* rays, const float* tris, const float* boxes, float* out) {
+    for (int i = 0; i < n; ++i) cavept::body_probe(rays, tris, boxes, out, i);
+}

@@ -66,3 +66,29 @@ def coincident_centroid_mesh(n=6):
     pos = np.tile(tri, (n, 1))
     idx = np.arange(3 * n, dtype=np.uint32)
     return scenes.Mesh(pos, np.tile(np.array([0, 0, 1], dtype=np.float32), (3 * n, 1)), idx)
+
+
+def isect_golden_inputs():
+    """Inputs of isect_golden.npz in the probe's layout: rays (n,7) = origin, direction = end - start
+    (fp32, as TestIntersection computes it), t = 1 (Ray::m_dist's initial value)."""
+    g = load_golden("isect_golden.npz")
+    start, end = g["rays"][:, 0:3], g["rays"][:, 3:6]
+    rays = np.concatenate([start, (end - start).astype(np.float32), np.ones((start.shape[0], 1), dtype=np.float32)], axis=1).astype(np.float32)
+    return g, rays
+
+
+def check_probe_against_reference_twins(out, g):
+    """SURVEY.md section 8 row a20.  `out` = (n,8) probe results of the product's HitTriangle / HitBvh.
+    Triangle: same Moller-Trumbore in the same fp32 order -> hit flags and t bit-identical to
+    TestIntersection::RayTriangle.  Box: same slab arithmetic, different accept rule -- the engine's CPU twin
+    also rejects tmin <= 0 (origin inside or box behind), the shader's HitBvh does not -- so
+    reference hit <=> (HitBvh hit and tmin > 0), and on a hit m_dist == tmin bit for bit."""
+    rt, rb = g["ref_triangle"], g["ref_aabb"]
+    assert np.array_equal(out[:, 0], rt[:, 0]), f"{int((out[:, 0] != rt[:, 0]).sum())} triangle hit flags differ"
+    assert out[:, 1].tobytes() == rt[:, 1].tobytes(), "triangle t differs from the reference twin"
+    assert rt[:, 0].sum() > 100 and (rt[:, 0] == 0).sum() > 100
+    ours_box = (out[:, 4] == 1.0) & (out[:, 5] > 0.0)
+    assert np.array_equal(ours_box, rb[:, 0] == 1.0), f"{int((ours_box != (rb[:, 0] == 1.0)).sum())} box decisions differ"
+    hit = rb[:, 0] == 1.0
+    assert out[hit, 5].tobytes() == rb[hit, 1].tobytes(), "slab tmin differs from the reference twin"
+    assert hit.sum() > 100

@@ -273,3 +273,19 @@ def test_inverse_matches_glm_golden():
         out = np.zeros(16, dtype=np.float32)
         lib.emu_mat4_inverse(np.ascontiguousarray(m).ctypes.data_as(C.c_void_p), out.ctypes.data_as(C.c_void_p))
         assert out.tobytes() == want.tobytes()
+
+
+def test_intersection_bodies_match_the_engines_cpu_twins():
+    """Row a20: the product's HitTriangle / HitBvh source (stepped on the host) against golden outputs of
+    TestIntersection::RayTriangle / RayAabb (cave/engine/math/intersection.cpp:18-70, compiled in place)."""
+    import ctypes as C
+
+    import emu_loader
+
+    g, rays = H.isect_golden_inputs()
+    lib = emu_loader.load()
+    n = rays.shape[0]
+    out = np.zeros((n, 8), dtype=np.float32)
+    tris, boxes = np.ascontiguousarray(g["tris"]), np.ascontiguousarray(g["boxes"])
+    lib.emu_probe(C.c_int(n), rays.ctypes.data_as(C.c_void_p), tris.ctypes.data_as(C.c_void_p), boxes.ctypes.data_as(C.c_void_p), out.ctypes.data_as(C.c_void_p))
+    H.check_probe_against_reference_twins(out, g)

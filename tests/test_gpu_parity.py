@@ -466,3 +466,11 @@ def test_tiles_equal_the_full_frame_bitwise(api, scene_cache, mode):
             with pytest.raises(api.CaveptError) as e:
                 pt.render_tile(*bad, 0, 1)
             assert e.value.code == 1  # CAVEPT_ERR_INVALID_ARG
+
+
+# ---- row a20: unit cross-check against the engine's CPU twins ----------------------------------
+def test_device_intersections_match_the_engines_cpu_twins(api):
+    g, rays = H.isect_golden_inputs()
+    with api.PathTracer(16, 16, 1, device=0) as pt:
+        out = pt.probe_intersections(rays, g["tris"], g["boxes"])
+    H.check_probe_against_reference_twins(out, g)

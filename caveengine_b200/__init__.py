@@ -14,6 +14,7 @@ from .api import (  # noqa: F401
     CaveptError,
     PathTracer,
     PathTracerMode,
+    PinnedArray,
     SceneFile,
     TraceMode,
     library_path,

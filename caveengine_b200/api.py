@@ -108,6 +108,8 @@ ABI = [
     ("cavept_accum_to_sums", C.c_int, [_P]),
     ("cavept_accum_from_sums", C.c_int, [_P]),
     ("cavept_sort_pairs", C.c_int, [_P, _P, _P, C.c_int, C.c_int]),
+    ("cavept_host_alloc", _P, [C.c_size_t]),
+    ("cavept_host_free", None, [_P]),
     ("cavept_probe_intersections", C.c_int, [_P, C.c_int, _P, _P, _P, _P]),
     ("cavept_scene_file_open", C.c_int, [C.c_char_p, C.c_char_p, C.POINTER(_P), C.c_char_p, C.c_size_t]),
     ("cavept_mesh_file_open", C.c_int, [C.c_char_p, C.POINTER(_P), C.c_char_p, C.c_size_t]),
@@ -213,6 +215,31 @@ class SceneFile:
         f = np.float32
         materials = [scenes.Material(tuple(f(x) for x in cmat[k].base_color), f(cmat[k].roughness), f(cmat[k].metallic), f(cmat[k].emissive)) for k in range(self.material_count)]
         return scenes.Scene(name, meshes, instances, materials, camera)
+
+
+class PinnedArray:
+    """numpy view over page-locked host memory (cavept_host_alloc): fill `.array` in place and pass it
+    to `PathTracer.rebuild_mesh` for a DMA upload.  Freed on close()/garbage collection."""
+
+    def __init__(self, shape, dtype=np.float32):
+        self._lib = load_library()
+        n = int(np.prod(shape)) * np.dtype(dtype).itemsize
+        self._ptr = self._lib.cavept_host_alloc(n)
+        if not self._ptr:
+            raise CaveptError(ERR_CUDA, f"cavept_host_alloc({n}) failed")
+        self.array = np.ctypeslib.as_array(C.cast(self._ptr, C.POINTER(C.c_uint8)), shape=(n,)).view(dtype).reshape(shape)
+
+    def close(self):
+        if getattr(self, "_ptr", None):
+            self.array = None
+            self._lib.cavept_host_free(self._ptr)
+            self._ptr = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 def write_mesh_file(path: str, mesh) -> None:

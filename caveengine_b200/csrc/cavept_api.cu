@@ -810,6 +810,19 @@ CAVEPT_API int cavept_accum_from_sums(cavept_ctx* ctx) {
 
 }  // extern "C"
 
+CAVEPT_API void* cavept_host_alloc(size_t bytes) {
+    void* p = nullptr;
+    if (bytes == 0 || cudaHostAlloc(&p, bytes, cudaHostAllocPortable) != cudaSuccess) {
+        (void)cudaGetLastError();
+        return nullptr;
+    }
+    return p;
+}
+
+CAVEPT_API void cavept_host_free(void* p) {
+    if (p) (void)cudaFreeHost(p);
+}
+
 CAVEPT_API int cavept_probe_intersections(cavept_ctx* ctx, int count, const float* rays, const float* triangles, const float* boxes, float* out) {
     if (!ctx || !rays || !triangles || !boxes || !out || count < 0) return CAVEPT_ERR_INVALID_ARG;
     if (int e = select_device(ctx)) return e;

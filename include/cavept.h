@@ -214,6 +214,12 @@ CAVEPT_API int cavept_sort_pairs(cavept_ctx* ctx, uint32_t* keys, int32_t* value
  *               side-cars found under resource_root (NULL = the scene file's directory).  Renderers
  *               whose mesh does not resolve are skipped, as DEV_VERIFY does (path_tracer.cpp:216),
  *               and counted.  `err` (may be NULL) receives a message on failure. ------------------- */
+/* Page-locked host memory for per-frame inputs (BASELINE config 5 streams 30 MB of vertex positions per
+ * frame): arrays handed to cavept_rebuild_mesh / cavept_upload_scene from such a buffer are DMA-copied at
+ * PCIe rate instead of being staged through the driver's bounce buffer.  Ordinary pointers keep working. */
+CAVEPT_API void* cavept_host_alloc(size_t bytes);
+CAVEPT_API void cavept_host_free(void* ptr);
+
 /* Unit probe: runs the device's HitTriangle (shared_path_tracer.h:88-130) and
  * HitBvh (:133-149) on `count` caller-supplied cases, for the cross-check against the engine's CPU twins
  * TestIntersection::RayTriangle / RayAabb (cave/engine/math/intersection.cpp:18-70).

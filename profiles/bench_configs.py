@@ -54,7 +54,7 @@ def run_static(tag, scene, w, h, mb, spp_total, spp_launch, bvh_mode):
         print(json.dumps(line), flush=True)
 
 
-def run_animated(frames=6, nu=1600, nv=1600, mode=None):
+def run_animated(frames=6, nu=1600, nv=1600, mode=None, pinned=False):
     mode = mode or cb.BvhMode.LBVH
     scene = scenes.animated_scene(nu, nv)
     w, h, mb = 1920, 1080, 8
@@ -65,9 +65,14 @@ def run_animated(frames=6, nu=1600, nv=1600, mode=None):
         pt.set_camera(scene.camera)
         pt.render(0, 1, sync=True)
         rows = []
+        stage = cb.PinnedArray(poses[0].shape) if pinned else None
         for k in range(frames):
+            src = poses[k]
+            if pinned:  # the animation system writes the frame's positions into page-locked memory (untimed, like the pose generation)
+                stage.array[...] = poses[k]
+                src = stage.array
             t0 = time.perf_counter()
-            pt.rebuild_mesh(0, poses[k])  # H2D of the new positions + device rebuild
+            pt.rebuild_mesh(0, src)  # H2D of the new positions + device rebuild
             t1 = time.perf_counter()
             pt.reset()
             pt.reset_stats()
@@ -78,7 +83,7 @@ def run_animated(frames=6, nu=1600, nv=1600, mode=None):
                          "frame_wall_ms": (t2 - t0) * 1e3, "segments": st["segments"], "levels": st["fast_build_levels"], "launches": st["fast_build_launches"]})
         warm = rows[1:]
         med = lambda key: float(np.median([r[key] for r in warm]))
-        line = {"config": 5, "builder": mode.name, "scene": scene.name, "triangles": scene.n_tris, "width": w, "height": h, "max_bounce": mb, "frames": frames,
+        line = {"config": 5, "builder": mode.name, "h2d_source": "pinned (cavept_host_alloc)" if pinned else "pageable", "scene": scene.name, "triangles": scene.n_tris, "width": w, "height": h, "max_bounce": mb, "frames": frames,
                 "bvh_fast_build_ms_median": med("bvh_fast_build_ms"), "rebuild_call_wall_ms_median": med("rebuild_call_wall_ms"), "render_1spp_ms_median": med("render_ms"),
                 "frame_wall_ms_median": med("frame_wall_ms"), "M_segments_per_s": med("segments") / med("render_ms") / 1e3, "h2d_bytes_per_frame": int(poses[0].nbytes),
                 "levels": warm[-1]["levels"], "launches": warm[-1]["launches"], "per_frame": rows}
@@ -93,4 +98,5 @@ if __name__ == "__main__":
         run_static(4, scenes.breakfast_scene(), 3840, 2160, 8, 128, 8, cb.BvhMode.PARITY)
     if 5 in which:
         run_animated(mode=cb.BvhMode.LBVH)
+        run_animated(mode=cb.BvhMode.LBVH, pinned=True)
         run_animated(mode=cb.BvhMode.FAST)

@@ -474,3 +474,26 @@ def test_device_intersections_match_the_engines_cpu_twins(api):
     with api.PathTracer(16, 16, 1, device=0) as pt:
         out = pt.probe_intersections(rays, g["tris"], g["boxes"])
     H.check_probe_against_reference_twins(out, g)
+
+
+def test_rebuild_from_pinned_host_memory(api):
+    """cavept_host_alloc: the same positions from page-locked memory give the same frame."""
+    sc = scenes.animated_scene(40, 40)
+    pose = scenes.animated_sheet(0.3, 40, 40, with_normals=False).positions
+    imgs = []
+    for pinned in (False, True):
+        with api.PathTracer(64, 36, 5, device=0, bvh_mode=api.BvhMode.LBVH) as pt:
+            pt.set_mode(api.PathTracerMode.INTERACTIVE)
+            pt.upload_scene(sc)
+            pt.set_camera(sc.camera)
+            src = pose
+            if pinned:
+                stage = api.PinnedArray(pose.shape)
+                stage.array[...] = pose
+                src = stage.array
+            pt.rebuild_mesh(0, src)
+            pt.render(0, 2, sync=True)
+            imgs.append(pt.read_accum())
+            if pinned:
+                stage.close()
+    assert imgs[0].tobytes() == imgs[1].tobytes()

@@ -60,6 +60,14 @@ class ClockSampler:
         for line in self.proc.stdout:
             self.rows.append(line.strip())
 
+    def wait_first(self, timeout_s: float):
+        t0 = time.perf_counter()
+        while self.proc and not self.rows and time.perf_counter() - t0 < timeout_s:
+            time.sleep(0.05)
+
+    def mark(self):
+        self.first = len(self.rows)
+
     def stop(self):
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
@@ -70,7 +78,8 @@ class ClockSampler:
             self.proc.kill()
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
+        rows = self.rows[getattr(self, "first", 0):] or self.rows
+        for r in rows:
             f = [x.strip() for x in r.split(",")]
             if len(f) < 7:
                 continue
@@ -241,6 +250,11 @@ def main():
     vt = inst["triangle_tests"] / max(inst["segments"], 1)
 
     # ---- device-resident timing -----------------------------------------------------------------
+    # nvidia-smi is started BEFORE the warm-up and must have produced a sample before the timed region
+    # opens: its start-up (NVML attach) can stall the GPU for a moment, which belongs to nobody's step time
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    sampler.wait_first(5.0)
     pt.reset()
     for w in range(args.warmup):
         pt.render(frames_of(w), S)
@@ -249,8 +263,7 @@ def main():
     pt.reset_stats()
     launches0 = pt.stats()["kernel_launches"]
     barrier()
-    sampler = ClockSampler(local_rank)
-    sampler.start()
+    sampler.mark()  # only samples taken from here on (under load) are reported
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     kernel_ms = []
     with torch.cuda.stream(stream):

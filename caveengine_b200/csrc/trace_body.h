@@ -522,11 +522,25 @@ CV_D unsigned int body_trace_pixel_reference(const TraceParams& p, int x, int y,
 // neighbours, so images are deterministic.
 // (Tried and measured slower on B200: a separate batched phase for accumulate + next sample --
 // the lanes waiting for it cost more step-phase utilisation than the batching saves.)
+// A vote costs ~45 warp instructions at full width, a step 55: every vote is therefore followed
+// by several steps (4 in the quorum loop, 4 in the minority branch; a lane that cannot step idles
+// through the rest of the group), and shading waits for 24 lanes -- the long shading sequence at
+// 10 of 32 lanes was 16 % of the kernel.  ncu source-page counts before/after: r01g profiles.
+// The groups only change WHEN a lane's next visit happens, never which visits it makes.
 #ifndef CV_STEP_QUORUM
 #define CV_STEP_QUORUM 20
 #endif
+#ifndef CV_TIGHT_STEPS
+#define CV_TIGHT_STEPS 4
+#endif
+#ifndef CV_MINORITY_STEPS
+#define CV_MINORITY_STEPS 4
+#endif
+#ifndef CV_TRI_PER_VOTE
+#define CV_TRI_PER_VOTE 1
+#endif
 #ifndef CV_SHADE_BATCH
-#define CV_SHADE_BATCH 8
+#define CV_SHADE_BATCH 24
 #endif
 constexpr int kStepQuorum = CV_STEP_QUORUM;  // of 32 lanes: keep stepping while at least this many can
 constexpr int kShadeBatch = CV_SHADE_BATCH;
@@ -561,8 +575,11 @@ CV_D unsigned int body_trace_pixel_fast(const TraceParams& p, int x, int y, int*
             if (can_step) walk_step<kCount>(p, w, ray.t, cnt);
             // second step of the trip without a vote of its own (measured +2 %): the lanes that can
             // still step do, the others would have idled through it anyway
-            walk_park_leaf(w);
-            if (ref_is_interior(w.ref)) walk_step<kCount>(p, w, ray.t, cnt);
+#pragma unroll
+            for (int k = 1; k < CV_TIGHT_STEPS; ++k) {
+                walk_park_leaf(w);
+                if (ref_is_interior(w.ref)) walk_step<kCount>(p, w, ray.t, cnt);
+            }
         }
         // ---- the vote ------------------------------------------------------------------------
         const bool can_step = ref_is_interior(w.ref);
@@ -574,6 +591,10 @@ CV_D unsigned int body_trace_pixel_fast(const TraceParams& p, int x, int y, int*
         if (n_step + n_tri + n_shade == 0) break;  // every lane has rendered all its frames
         if (n_tri > 0 && n_tri >= n_step) {
             if (has_tri) walk_test_triangle<kCount>(p, w, ray, ray.t, cnt);
+#pragma unroll
+            for (int k = 1; k < CV_TRI_PER_VOTE; ++k) {
+                if (w.q0 != 0) walk_test_triangle<kCount>(p, w, ray, ray.t, cnt);
+            }
         } else if (n_shade >= kBatch || n_step == 0) {
             if (need_shade) {
                 ++segments;
@@ -608,6 +629,11 @@ CV_D unsigned int body_trace_pixel_fast(const TraceParams& p, int x, int y, int*
             }
         } else {
             if (can_step) walk_step<kCount>(p, w, ray.t, cnt);
+#pragma unroll
+            for (int k = 1; k < CV_MINORITY_STEPS; ++k) {
+                walk_park_leaf(w);
+                if (ref_is_interior(w.ref)) walk_step<kCount>(p, w, ray.t, cnt);
+            }
         }
     }
     return segments;

@@ -123,13 +123,13 @@ def roofline(achieved, peaks, peak_kind, bytes_per_segment, vn, vt, seg_per_laun
         peak_wf = 148 * mhz * 1e6
         ach_wf = wf_per_seg * seg_per_launch / (launch_ms * 1e-3)
         units = {"instruction issue slots": d["issue_active_pct"], "l1tex data-pipe LSU wavefronts": d["l1_lsu_wavefronts_pct_of_peak"],
-                 "l2 throughput": d["l2_throughput_pct"], "fma pipe": d["fma_pipe_pct"], "dram throughput": d["dram_throughput_pct"]}
+                 "l2 throughput": d["l2_throughput_pct"], "fma pipe": d["fma_pipe_pct"], "alu pipe": d.get("alu_pipe_pct"), "dram throughput": d["dram_throughput_pct"]}
         top = max(units, key=lambda k: units[k] or 0.0)
         r["binding"] = {"most_utilised_unit": top, "pct_of_peak_in_capture": units, "active_threads_per_warp_instruction": d["threads_per_instruction"],
                         "warps_active_pct": d["warps_active_pct"], "registers_per_thread": d["registers_per_thread"],
                         "l1_wavefronts_per_segment": wf_per_seg, "l1_wavefronts_per_s_live": ach_wf, "l1_wavefronts_per_s_peak": peak_wf, "l1_wavefront_frac_live": ach_wf / peak_wf,
                         "l2_hit_pct": d["l2_hit_pct"], "l2_bytes_per_segment": d["l2_bytes"] / d["segments_of_launch"], "dram_bytes_per_segment": d["dram_bytes"] / d["segments_of_launch"],
-                        "note": "a divergent gather kernel: no single unit saturates; issue slots (with ~18 of 32 lanes active per instruction) and the L1 gather pipe share the bound"}
+                        "note": "a divergent gather kernel: no single unit saturates; the half-rate ALU pipe (PRMT decode, 3-input min/max, selects), issue slots (~21 of 32 lanes active per instruction) and the L1 gather pipe share the bound"}
     return r
 
 

@@ -96,6 +96,7 @@ def as_json(src, dst, spp="0", segments="0"):
         "dram_throughput_pct": val("gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed"),
         "issue_active_pct": val("smsp__issue_active.avg.pct_of_peak_sustained_active"),
         "fma_pipe_pct": val("sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active"),
+        "alu_pipe_pct": val("sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active"),
         "threads_per_instruction": val("smsp__thread_inst_executed_per_inst_executed.ratio"),
         "registers_per_thread": val("launch__registers_per_thread"),
         "warps_active_pct": val("sm__warps_active.avg.pct_of_peak_sustained_active"),

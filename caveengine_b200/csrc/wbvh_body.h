@@ -572,29 +572,73 @@ CV_D void wb_write_pair(const WBuild& b, int h, const WBox box[2], const int ref
 
 // Bottom-up: starts at every node whose two children are leaves; at each parent the first
 // arrival stops, the second (node_count reaches 2) has both child boxes and continues.
-CV_D void wb_body_radix_boxes(const WBuild& b, int i) {
-    if (i >= b.n_prims - 1) return;
-    if (b.node_last[i] - b.node_first[i] + 1 <= kFastLeafMax) return;  // folded into its parent as a leaf
-    if ((b.node_count[i] >> 8) != 2) return;  // start only where both children are leaves
-    for (;;) {
-        WBox box[2];
-        int ref[2], count[2], hgt[2];
-        wb_radix_child(b, i, 0, box[0], ref[0], count[0], hgt[0]);
-        wb_radix_child(b, i, 1, box[1], ref[1], count[1], hgt[1]);
-        wb_write_pair(b, i, box, ref, count);
-        wb_grow(box[0], box[1].mn, box[1].mx);
+// The climb is the divergent part (ncu: 2.9 of 32 lanes active per instruction), so it carries
+// only the box union and the height; the sibling-pair records (fp32 FastNode pair + quantised
+// QPair, two thirds of the old loop body) are written afterwards by wb_body_radix_pairs, one
+// fully converged thread per node.
+// The climb from node i, whose subtree box/height the caller holds.  After `max_hops` hops the
+// climber parks itself in `list_out` (its box is in nbox[i]) and the next launch carries on with
+// the survivors packed 32 to a warp: a climb is a chain of dependent memory round trips, and what
+// limits the kernel is how many climbers are resident, not instruction issue -- one launch over all
+// nodes ends with warps that hold one or two live lanes each (ncu: 2.9 of 32).
+CV_D void wb_radix_climb(const WBuild& b, int i, WBox mine, int height, int max_hops, int* list_out, int* count_out) {
+    for (int hop = 0;; ++hop) {
         F4 o;
-        o.x = box[0].mn.x; o.y = box[0].mn.y; o.z = box[0].mn.z; o.w = u2f((uint32_t)(1 + (hgt[0] > hgt[1] ? hgt[0] : hgt[1])));
+        o.x = mine.mn.x; o.y = mine.mn.y; o.z = mine.mn.z; o.w = u2f((uint32_t)height);
         b.nbox_mn[i] = o;
-        o.x = box[0].mx.x; o.y = box[0].mx.y; o.z = box[0].mx.z; o.w = 0.0f;
+        o.x = mine.mx.x; o.y = mine.mx.y; o.z = mine.mx.z; o.w = 0.0f;
         b.nbox_mx[i] = o;
         const int parent = b.node_parent[i];
         if (parent < 0) return;
+        if (hop >= max_hops) {
+            list_out[cv_atomic_add_i32(count_out, 1)] = i;
+            return;
+        }
+        const int split = b.node_split[parent];  // independent of the handshake below: in flight while it completes
         cv_threadfence();
         if ((cv_atomic_add_i32(&b.node_count[parent], 1) & 0xff) != 1) return;
         cv_threadfence();
+        WBox other;
+        int ref, count, hgt;
+        wb_radix_child(b, parent, i == split ? 1 : 0, other, ref, count, hgt);  // interior children are `split` (left) and `split + 1`
+        wb_grow(mine, other.mn, other.mx);
+        height = 1 + (height > hgt ? height : hgt);
         i = parent;
     }
+}
+
+CV_D void wb_body_radix_boxes(const WBuild& b, int i, int max_hops, int* list_out, int* count_out) {
+    if (i >= b.n_prims - 1) return;
+    if (b.node_last[i] - b.node_first[i] + 1 <= kFastLeafMax) return;  // folded into its parent as a leaf
+    if ((b.node_count[i] >> 8) != 2) return;  // start only where both children are leaves
+    WBox mine, other;
+    int ref, count, hgt;
+    wb_radix_child(b, i, 0, mine, ref, count, hgt);
+    wb_radix_child(b, i, 1, other, ref, count, hgt);
+    wb_grow(mine, other.mn, other.mx);
+    wb_radix_climb(b, i, mine, 1, max_hops, list_out, count_out);
+}
+
+// a later round: climber k of the previous round's list
+CV_D void wb_body_radix_resume(const WBuild& b, int k, const int* list_in, const int* count_in, int max_hops, int* list_out, int* count_out) {
+    if (k >= *count_in) return;  // written by the previous launch
+    const int i = list_in[k];
+    const F4 mn = cv_load_cg(&b.nbox_mn[i]), mx = cv_load_cg(&b.nbox_mx[i]);
+    WBox mine;
+    mine.mn = f3(mn.x, mn.y, mn.z);
+    mine.mx = f3(mx.x, mx.y, mx.z);
+    wb_radix_climb(b, i, mine, (int)f2u(mn.w), max_hops, list_out, count_out);
+}
+
+// After the climb every interior node's box is final: write each node's sibling pair.
+CV_D void wb_body_radix_pairs(const WBuild& b, int i) {
+    if (i >= b.n_prims - 1) return;
+    if (b.node_last[i] - b.node_first[i] + 1 <= kFastLeafMax) return;
+    WBox box[2];
+    int ref[2], count[2], hgt[2];
+    wb_radix_child(b, i, 0, box[0], ref[0], count[0], hgt[0]);
+    wb_radix_child(b, i, 1, box[1], ref[1], count[1], hgt[1]);
+    wb_write_pair(b, i, box, ref, count);
 }
 
 CV_HD int wb_lbvh_lo(int n, int k, int j) { return (int)(((long long)j * (long long)n) >> k); }
@@ -649,7 +693,9 @@ struct FnWbScatter { WBuild b; CV_D void operator()(int i) const { wb_body_scatt
 struct FnWbEmit { WBuild b; CV_D void operator()(int i) const { wb_body_emit(b, i); } };
 struct FnWbMorton { WBuild b; CV_D void operator()(int i) const { wb_body_morton(b, i); } };
 struct FnWbRadixNode { WBuild b; CV_D void operator()(int i) const { wb_body_radix_node(b, i); } };
-struct FnWbRadixBoxes { WBuild b; CV_D void operator()(int i) const { wb_body_radix_boxes(b, i); } };
+struct FnWbRadixBoxes { WBuild b; int max_hops; int* list_out; int* count_out; CV_D void operator()(int i) const { wb_body_radix_boxes(b, i, max_hops, list_out, count_out); } };
+struct FnWbRadixResume { WBuild b; const int* list_in; const int* count_in; int max_hops; int* list_out; int* count_out; CV_D void operator()(int i) const { wb_body_radix_resume(b, i, list_in, count_in, max_hops, list_out, count_out); } };
+struct FnWbRadixPairs { WBuild b; CV_D void operator()(int i) const { wb_body_radix_pairs(b, i); } };
 struct FnWbLbvhLevel { WBuild b; int k; CV_D void operator()(int i) const { wb_body_lbvh_level(b, i, k); } };
 struct FnWbQuantise { WBuild b; int n; CV_D void operator()(int i) const { wb_body_quantise(b, i, n); } };
 
@@ -774,7 +820,20 @@ int build_lbvh(Exec& ex, WBuild b, WReport* rep) {
     b.node_parent = b.scan;
     b.node_count = reinterpret_cast<int*>(b.keys_tmp);
     ex.launch(b.n_prims - 1, FnWbRadixNode{ b });
-    ex.launch(b.n_prims - 1, FnWbRadixBoxes{ b });
+    {   // bottom-up boxes in rounds of kClimbHops hops; survivors are re-packed between rounds (see wb_radix_climb)
+        constexpr int kClimbHops = 3, kClimbRounds = 8;
+        int* lists[2] = { reinterpret_cast<int*>(b.keys), reinterpret_cast<int*>(b.flags) };  // both free now; n and n/4 ints: a round's survivors are <= n/(3r+1)
+        int* counts = reinterpret_cast<int*>(b.root_acc);                                      // 12 ints, consumed by the prologue
+        ex.fill(counts, 0, 12 * sizeof(int));
+        const int n_nodes = b.n_prims - 1;
+        ex.launch(n_nodes, FnWbRadixBoxes{ b, kClimbHops, lists[0], counts + 0 });
+        for (int r = 1; r < kClimbRounds; ++r) {
+            const bool last = r == kClimbRounds - 1;
+            ex.launch(n_nodes / (kClimbHops * r + 1) + 1,
+                      FnWbRadixResume{ b, lists[(r - 1) & 1], counts + (r - 1), last ? 0x7fffffff : kClimbHops, lists[r & 1], counts + r });
+        }
+    }
+    ex.launch(b.n_prims - 1, FnWbRadixPairs{ b });
     F4 root_mn;
     ex.download(&root_mn, b.nbox_mn, sizeof(F4));
     const int height = (int)f2u(root_mn.w);

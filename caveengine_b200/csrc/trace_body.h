@@ -18,7 +18,10 @@ namespace cavept {
 
 constexpr float kEpsilon = 1.1920929e-7f;  // EPSILON, shared_path_tracer.h:24
 constexpr float kRayTMax = 999999999.0f;   // RAY_T_MAX, :27
-constexpr int kFastLeafMax = 2;            // leaves of the production tree hold at most this many triangles (measured on B200: 2 beats 4 and 1)
+#ifndef CV_LEAF_MAX
+#define CV_LEAF_MAX 2
+#endif
+constexpr int kFastLeafMax = CV_LEAF_MAX;            // leaves of the production tree hold at most this many triangles (measured on B200: 2 beats 4 and 1)
 #ifndef CV_STACK_SIZE
 #define CV_STACK_SIZE 40
 #endif

@@ -183,17 +183,19 @@ CV_D void body_reduce(const BuildArrays& a, int i) {
             kmx[0] = x0 > kmx[0] ? x0 : kmx[0]; kmx[1] = x1 > kmx[1] ? x1 : kmx[1]; kmx[2] = x2 > kmx[2] ? x2 : kmx[2];
         }
     }
+    // lanes of the warp that fold into the same node combine first (top levels: all 32 hit one node)
+    const CvGroup grp = cv_group_by(w);
     for (int k = 0; k < 3; ++k) {
-        cv_atomic_min_u64(&acc.mn[k], kmn[k]);
-        cv_atomic_max_u64(&acc.mx[k], kmx[k]);
+        cv_group_min_u64(grp, &acc.mn[k], kmn[k]);
+        cv_group_max_u64(grp, &acc.mx[k], kmx[k]);
     }
     const F4 c = a.tri_centroid[g];
-    cv_atomic_min_u32(&acc.cmn[0], ordered_key(c.x));
-    cv_atomic_min_u32(&acc.cmn[1], ordered_key(c.y));
-    cv_atomic_min_u32(&acc.cmn[2], ordered_key(c.z));
-    cv_atomic_max_u32(&acc.cmx[0], ordered_key(c.x));
-    cv_atomic_max_u32(&acc.cmx[1], ordered_key(c.y));
-    cv_atomic_max_u32(&acc.cmx[2], ordered_key(c.z));
+    cv_group_min_u32(grp, &acc.cmn[0], ordered_key(c.x));
+    cv_group_min_u32(grp, &acc.cmn[1], ordered_key(c.y));
+    cv_group_min_u32(grp, &acc.cmn[2], ordered_key(c.z));
+    cv_group_max_u32(grp, &acc.cmx[0], ordered_key(c.x));
+    cv_group_max_u32(grp, &acc.cmx[1], ordered_key(c.y));
+    cv_group_max_u32(grp, &acc.cmx[2], ordered_key(c.z));
 }
 
 // ---- per item: write the node, classify (:128-142), prepare the SAH pass ------------

@@ -299,6 +299,28 @@ CV_D void cv_group_max_u32(const CvGroup& g, uint32_t* p, uint32_t v) {
     if (v > *p) *p = v;
 #endif
 }
+// 64-bit min/max over the group with two 32-bit redux.sync: the high words first, then the low words of
+// the lanes that hold the winning high word
+CV_D void cv_group_min_u64(const CvGroup& g, unsigned long long* p, unsigned long long v) {
+#if defined(__CUDA_ARCH__)
+    const uint32_t hi = (uint32_t)(v >> 32), lo = (uint32_t)v;
+    const uint32_t mhi = __reduce_min_sync(g.mask, hi);
+    const uint32_t mlo = __reduce_min_sync(g.mask, hi == mhi ? lo : 0xffffffffu);
+    if (g.leader) atomicMin(p, ((unsigned long long)mhi << 32) | mlo);
+#else
+    if (v < *p) *p = v;
+#endif
+}
+CV_D void cv_group_max_u64(const CvGroup& g, unsigned long long* p, unsigned long long v) {
+#if defined(__CUDA_ARCH__)
+    const uint32_t hi = (uint32_t)(v >> 32), lo = (uint32_t)v;
+    const uint32_t mhi = __reduce_max_sync(g.mask, hi);
+    const uint32_t mlo = __reduce_max_sync(g.mask, hi == mhi ? lo : 0u);
+    if (g.leader) atomicMax(p, ((unsigned long long)mhi << 32) | mlo);
+#else
+    if (v > *p) *p = v;
+#endif
+}
 CV_D void cv_group_add_i32(const CvGroup& g, int* p, int v) {
 #if defined(__CUDA_ARCH__)
     v = __reduce_add_sync(g.mask, v);

@@ -173,7 +173,7 @@ def main():
     ap.add_argument("--steps", type=int, default=8)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--spp", type=int, default=32, help="frames (samples per pixel) per step")
+    ap.add_argument("--spp", type=int, default=256, help="frames (samples per pixel) per step; 256 = the whole of BASELINE config 3 in one step")
     ap.add_argument("--trace-mode", default="fast", choices=["fast", "reference_walk"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()

@@ -230,7 +230,7 @@ int build_world(cavept_ctx* ctx) {
         CU(ctx, ctx->d_w_items_next.reserve(items_cap));
         CU(ctx, ctx->d_w_bins.reserve(items_cap));
     }
-    CU(ctx, ctx->d_w_counters.reserve(4));
+    CU(ctx, ctx->d_w_counters.reserve(kWLevelBase + kWMaxLevels + 4));
     CU(ctx, ctx->d_w_root_acc.reserve(12));
     CU(ctx, ctx->d_fnodes.reserve(2 * pairs_cap));
     CU(ctx, ctx->d_qpairs.reserve(pairs_cap));

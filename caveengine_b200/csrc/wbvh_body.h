@@ -27,6 +27,8 @@
 namespace cavept {
 
 constexpr int kWBins = 16;
+constexpr int kWLevelBase = 4;     // counters[4 + L] = interior items of level L (the level loop never reads them back one by one)
+constexpr int kWMaxLevels = 124;   // counters holds 4 + 124 + 4 ints
 constexpr int kWMedianDepth = 48;  // safety net: positional median splits below this depth
 
 struct WBin {
@@ -168,7 +170,8 @@ CV_D void wb_body_init(const WBuild& b, int p) {
 
 // ---- per level ----------------------------------------------------------------------------
 // thread j: bin j % 16 of item j / 16 is cleared; the first thread of an item also picks its axis
-CV_D void wb_body_prep(const WBuild& b, int j, int n_items) {
+CV_D void wb_body_prep(const WBuild& b, int j, int level) {
+    const int n_items = b.counters[kWLevelBase + level];  // written by the level above; launches are sized by an upper bound
     const int w = j / kWBins, k = j % kWBins;
     if (w >= n_items) return;
     WBin& bin = b.bins[w].b[k];
@@ -250,7 +253,8 @@ CV_HD float wb_half_area(const WBox& a) {
 
 // one thread per item: SAH sweep over the 15 planes, children boxes from the bins, child
 // records written into this item's pair, interior children queued for the next level
-CV_D void wb_body_split(const WBuild& b, int w, int n_items) {
+CV_D void wb_body_split(const WBuild& b, int w, int level) {
+    const int n_items = b.counters[kWLevelBase + level];
     if (w >= n_items) return;
     WItem& it = b.items[w];
     WBox box[2], cb[2];
@@ -326,7 +330,7 @@ CV_D void wb_body_split(const WBuild& b, int w, int n_items) {
             ref = make_leaf_ref(start, cnt[s]);
         } else {
             const int pair = cv_atomic_add_i32(&b.counters[1], 1);
-            const int slot = cv_atomic_add_i32(&b.counters[0], 1);
+            const int slot = cv_atomic_add_i32(&b.counters[kWLevelBase + level + 1], 1);
             if (pair >= b.pairs_capacity || slot >= b.items_capacity) {
                 cv_atomic_or_i32(&b.counters[2], WB_ERR_CAPACITY);
                 ref = make_leaf_ref(start, 1);
@@ -685,9 +689,9 @@ CV_D void wb_body_lbvh_level(const WBuild& b, int j, int k) {
 
 struct FnWbPrim { WBuild b; CV_D void operator()(int i) const { wb_body_prim(b, i); } };
 struct FnWbInit { WBuild b; CV_D void operator()(int i) const { wb_body_init(b, i); } };
-struct FnWbPrep { WBuild b; int n; CV_D void operator()(int i) const { wb_body_prep(b, i, n); } };
+struct FnWbPrep { WBuild b; int level; CV_D void operator()(int i) const { wb_body_prep(b, i, level); } };
 struct FnWbBin { WBuild b; CV_D void operator()(int i) const { wb_body_bin(b, i); } };
-struct FnWbSplit { WBuild b; int n; CV_D void operator()(int i) const { wb_body_split(b, i, n); } };
+struct FnWbSplit { WBuild b; int level; CV_D void operator()(int i) const { wb_body_split(b, i, level); } };
 struct FnWbFlag { WBuild b; CV_D void operator()(int i) const { wb_body_flag(b, i); } };
 struct FnWbScatter { WBuild b; CV_D void operator()(int i) const { wb_body_scatter(b, i); } };
 struct FnWbEmit { WBuild b; CV_D void operator()(int i) const { wb_body_emit(b, i); } };
@@ -770,31 +774,44 @@ int build_wbvh(Exec& ex, WBuild b, WReport* rep) {
         root.cb_mx[k] = ordered_value(acc[9 + k]);
     }
     ex.upload(b.items, &root, sizeof(root));
-    int counters[3] = { 0, 1, 0 };
+    // counters: [1] pairs allocated, [2] error bits, [4 + L] interior items of level L.  The level loop
+    // runs kLevelsPerSync levels per device->host round trip: launches over items are sized by an upper
+    // bound (items are disjoint ranges of >= kFastLeafMax + 1 prims, and at most 2^L of them) and read
+    // the true count on the device; a level past the last one finds no items and no prims to move.
+    constexpr int kLevelsPerSync = 4;
+    int counters[kWLevelBase + kWMaxLevels + 4] = { 0, 1, 0, 0, 1 };
     ex.upload(b.counters, counters, sizeof(counters));
-    int n_items = 1;
+    const int items_bound = b.n_prims / (kFastLeafMax + 1) + 1;
     rep->root_ref = 0;
-    while (n_items > 0) {
-        ex.launch(n_items * kWBins, FnWbPrep{ b, n_items });
-        ex.launch(b.n_prims, FnWbBin{ b });
-        ex.launch(n_items, FnWbSplit{ b, n_items });
-        ex.launch(b.n_prims, FnWbFlag{ b });
-        ex.scan_u8(b.flags, b.scan, b.n_prims);
-        ex.launch(b.n_prims, FnWbScatter{ b });
+    int level = 0;
+    for (;;) {
+        for (int k = 0; k < kLevelsPerSync; ++k, ++level) {
+            const long long pow2 = level < 30 ? (1ll << level) : (1ll << 30);
+            const int bound = (int)(pow2 < items_bound ? pow2 : items_bound);
+            ex.launch(bound * kWBins, FnWbPrep{ b, level });
+            ex.launch(b.n_prims, FnWbBin{ b });
+            ex.launch(bound, FnWbSplit{ b, level });
+            ex.launch(b.n_prims, FnWbFlag{ b });
+            ex.scan_u8(b.flags, b.scan, b.n_prims);
+            ex.launch(b.n_prims, FnWbScatter{ b });
+            WItem* ti = b.items; b.items = b.items_next; b.items_next = ti;
+            int* to = b.order; b.order = b.order_next; b.order_next = to;
+            int* tn = b.node_of; b.node_of = b.node_of_next; b.node_of_next = tn;
+        }
         ex.download(counters, b.counters, sizeof(counters));
-        ++rep->levels;
         if (counters[2] != 0) {
             rep->error_bits = counters[2];
             return -1;
         }
-        n_items = counters[0];
-        rep->n_pairs = counters[1];
-        counters[0] = 0;
-        ex.upload(b.counters, counters, sizeof(counters));
-        WItem* ti = b.items; b.items = b.items_next; b.items_next = ti;
-        int* to = b.order; b.order = b.order_next; b.order_next = to;
-        int* tn = b.node_of; b.node_of = b.node_of_next; b.node_of_next = tn;
+        if (counters[kWLevelBase + level] == 0) break;
+        if (level + kLevelsPerSync >= kWMaxLevels) {
+            rep->error_bits = WB_ERR_CAPACITY;
+            return -1;
+        }
     }
+    rep->n_pairs = counters[1];
+    rep->levels = 0;
+    while (counters[kWLevelBase + rep->levels] > 0) ++rep->levels;
     ex.launch(b.n_prims, FnWbEmit{ b });
     ex.launch(rep->n_pairs, FnWbQuantise{ b, rep->n_pairs });
     return 0;

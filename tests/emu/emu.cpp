@@ -101,7 +101,7 @@ EMU_API int emu_wbvh_build(const GpuPtVertex* vertices, const GpuPtIndex* indice
     const int P = inst_prim_off[n_inst];
     const size_t items_cap = (size_t)P / 2 + 8, pairs_cap = (size_t)P + 8;
     std::vector<F4> bmin(P), bmax(P);
-    std::vector<int> order(P), order_next(P), node_of(P), node_of_next(P), scan(P + 1), counters(4);
+    std::vector<int> order(P), order_next(P), node_of(P), node_of_next(P), scan(P + 1), counters(cavept::kWLevelBase + cavept::kWMaxLevels + 4);
     std::vector<unsigned char> flags(P);
     std::vector<WItem> items(items_cap), items_next(items_cap);
     std::vector<WBins> bins(items_cap);

@@ -526,7 +526,7 @@ CV_D unsigned int body_trace_pixel_reference(const TraceParams& p, int x, int y,
 // (Tried and measured slower on B200: a separate batched phase for accumulate + next sample --
 // the lanes waiting for it cost more step-phase utilisation than the batching saves.)
 // A vote costs ~45 warp instructions at full width, a step 55: every vote is therefore followed
-// by several steps (4 in the quorum loop, 4 in the minority branch; a lane that cannot step idles
+// by several steps (6 in the quorum loop, 4 in the minority branch; a lane that cannot step idles
 // through the rest of the group), and shading waits for 24 lanes -- the long shading sequence at
 // 10 of 32 lanes was 16 % of the kernel.  ncu source-page counts before/after: r01g profiles.
 // The groups only change WHEN a lane's next visit happens, never which visits it makes.
@@ -534,10 +534,13 @@ CV_D unsigned int body_trace_pixel_reference(const TraceParams& p, int x, int y,
 #define CV_STEP_QUORUM 20
 #endif
 #ifndef CV_TIGHT_STEPS
-#define CV_TIGHT_STEPS 4
+#define CV_TIGHT_STEPS 6
 #endif
 #ifndef CV_MINORITY_STEPS
 #define CV_MINORITY_STEPS 4
+#endif
+#ifndef CV_PARK_EVERY
+#define CV_PARK_EVERY 2  // parked leaves are collected before every second step of a group (a lane that reaches a leaf in between idles one step; the 13-instruction collect is full-width work)
 #endif
 #ifndef CV_TRI_PER_VOTE
 #define CV_TRI_PER_VOTE 1
@@ -580,7 +583,7 @@ CV_D unsigned int body_trace_pixel_fast(const TraceParams& p, int x, int y, int*
             // still step do, the others would have idled through it anyway
 #pragma unroll
             for (int k = 1; k < CV_TIGHT_STEPS; ++k) {
-                walk_park_leaf(w);
+                if ((k % CV_PARK_EVERY) == 0) walk_park_leaf(w);
                 if (ref_is_interior(w.ref)) walk_step<kCount>(p, w, ray.t, cnt);
             }
         }
@@ -634,7 +637,7 @@ CV_D unsigned int body_trace_pixel_fast(const TraceParams& p, int x, int y, int*
             if (can_step) walk_step<kCount>(p, w, ray.t, cnt);
 #pragma unroll
             for (int k = 1; k < CV_MINORITY_STEPS; ++k) {
-                walk_park_leaf(w);
+                if ((k % CV_PARK_EVERY) == 0) walk_park_leaf(w);
                 if (ref_is_interior(w.ref)) walk_step<kCount>(p, w, ray.t, cnt);
             }
         }

@@ -598,28 +598,64 @@ CV_D void wb_radix_climb(const WBuild& b, int i, WBox mine, int height, int max_
             list_out[cv_atomic_add_i32(count_out, 1)] = i;
             return;
         }
-        const int split = b.node_split[parent];  // independent of the handshake below: in flight while it completes
+        // everything that does not depend on the handshake is requested before it: the parent's range
+        // and the box of its leaf children (wb_body_radix_leafbox, an earlier launch)
+        const int split = b.node_split[parent], first = b.node_first[parent], last = b.node_last[parent];
+        const F4 pmn = b.nbox_mn[parent], pmx = b.nbox_mx[parent];
         cv_threadfence();
         if ((cv_atomic_add_i32(&b.node_count[parent], 1) & 0xff) != 1) return;
         cv_threadfence();
-        WBox other;
-        int ref, count, hgt;
-        wb_radix_child(b, parent, i == split ? 1 : 0, other, ref, count, hgt);  // interior children are `split` (left) and `split + 1`
-        wb_grow(mine, other.mn, other.mx);
+        wb_grow(mine, f3(pmn.x, pmn.y, pmn.z), f3(pmx.x, pmx.y, pmx.z));  // empty (+inf, -inf) when the parent has no leaf child
+        const bool i_am_left = i == split;  // interior children are `split` (left) and `split + 1`
+        const int sib = i_am_left ? split + 1 : split;
+        const int sib_count = i_am_left ? last - split : split - first + 1;
+        int hgt = 0;
+        if (sib_count > kFastLeafMax) {  // an interior sibling: its climber got there first, the box is final
+            const F4 smn = cv_load_cg(&b.nbox_mn[sib]), smx = cv_load_cg(&b.nbox_mx[sib]);
+            wb_grow(mine, f3(smn.x, smn.y, smn.z), f3(smx.x, smx.y, smx.z));
+            hgt = (int)f2u(smn.w);
+        }
         height = 1 + (height > hgt ? height : hgt);
         i = parent;
     }
+}
+
+// Before the climb: every interior node folds the prim boxes of its LEAF children into nbox (empty if it has
+// none) -- converged, no dependencies; the climb then never gathers prims.
+CV_D void wb_body_radix_leafbox(const WBuild& b, int i) {
+    if (i >= b.n_prims - 1) return;
+    const int first = b.node_first[i], last = b.node_last[i], split = b.node_split[i];
+    if (last - first + 1 <= kFastLeafMax) return;
+    WBox box = wb_empty();
+    if (split - first + 1 <= kFastLeafMax) {
+        for (int s = first; s <= split; ++s) {
+            const int p = b.order[s];
+            const F4 mn = b.bmin[p], mx = b.bmax[p];
+            wb_grow(box, f3(mn.x, mn.y, mn.z), f3(mx.x, mx.y, mx.z));
+        }
+    }
+    if (last - split <= kFastLeafMax) {
+        for (int s = split + 1; s <= last; ++s) {
+            const int p = b.order[s];
+            const F4 mn = b.bmin[p], mx = b.bmax[p];
+            wb_grow(box, f3(mn.x, mn.y, mn.z), f3(mx.x, mx.y, mx.z));
+        }
+    }
+    F4 o;
+    o.x = box.mn.x; o.y = box.mn.y; o.z = box.mn.z; o.w = u2f(0u);
+    b.nbox_mn[i] = o;
+    o.x = box.mx.x; o.y = box.mx.y; o.z = box.mx.z; o.w = 0.0f;
+    b.nbox_mx[i] = o;
 }
 
 CV_D void wb_body_radix_boxes(const WBuild& b, int i, int max_hops, int* list_out, int* count_out) {
     if (i >= b.n_prims - 1) return;
     if (b.node_last[i] - b.node_first[i] + 1 <= kFastLeafMax) return;  // folded into its parent as a leaf
     if ((b.node_count[i] >> 8) != 2) return;  // start only where both children are leaves
-    WBox mine, other;
-    int ref, count, hgt;
-    wb_radix_child(b, i, 0, mine, ref, count, hgt);
-    wb_radix_child(b, i, 1, other, ref, count, hgt);
-    wb_grow(mine, other.mn, other.mx);
+    const F4 mn = b.nbox_mn[i], mx = b.nbox_mx[i];  // both children folded by wb_body_radix_leafbox
+    WBox mine;
+    mine.mn = f3(mn.x, mn.y, mn.z);
+    mine.mx = f3(mx.x, mx.y, mx.z);
     wb_radix_climb(b, i, mine, 1, max_hops, list_out, count_out);
 }
 
@@ -699,6 +735,7 @@ struct FnWbMorton { WBuild b; CV_D void operator()(int i) const { wb_body_morton
 struct FnWbRadixNode { WBuild b; CV_D void operator()(int i) const { wb_body_radix_node(b, i); } };
 struct FnWbRadixBoxes { WBuild b; int max_hops; int* list_out; int* count_out; CV_D void operator()(int i) const { wb_body_radix_boxes(b, i, max_hops, list_out, count_out); } };
 struct FnWbRadixResume { WBuild b; const int* list_in; const int* count_in; int max_hops; int* list_out; int* count_out; CV_D void operator()(int i) const { wb_body_radix_resume(b, i, list_in, count_in, max_hops, list_out, count_out); } };
+struct FnWbRadixLeafBox { WBuild b; CV_D void operator()(int i) const { wb_body_radix_leafbox(b, i); } };
 struct FnWbRadixPairs { WBuild b; CV_D void operator()(int i) const { wb_body_radix_pairs(b, i); } };
 struct FnWbLbvhLevel { WBuild b; int k; CV_D void operator()(int i) const { wb_body_lbvh_level(b, i, k); } };
 struct FnWbQuantise { WBuild b; int n; CV_D void operator()(int i) const { wb_body_quantise(b, i, n); } };
@@ -843,6 +880,7 @@ int build_lbvh(Exec& ex, WBuild b, WReport* rep) {
         int* counts = reinterpret_cast<int*>(b.root_acc);                                      // 12 ints, consumed by the prologue
         ex.fill(counts, 0, 12 * sizeof(int));
         const int n_nodes = b.n_prims - 1;
+        ex.launch(n_nodes, FnWbRadixLeafBox{ b });
         ex.launch(n_nodes, FnWbRadixBoxes{ b, kClimbHops, lists[0], counts + 0 });
         for (int r = 1; r < kClimbRounds; ++r) {
             const bool last = r == kClimbRounds - 1;

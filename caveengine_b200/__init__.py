@@ -12,6 +12,7 @@ There is no CPU implementation here: importing works anywhere, but creating a
 from .api import (  # noqa: F401
     BvhMode,
     CaveptError,
+    KernelVariant,
     PathTracer,
     PathTracerMode,
     PinnedArray,

@@ -18,7 +18,7 @@ from typing import Optional
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_LIB_PATH = os.path.join(_HERE, "libcavept.so")
+_LIB_PATH = os.environ.get("CAVEPT_LIBRARY") or os.path.join(_HERE, "libcavept.so")  # CAVEPT_LIBRARY: another build of the same library (kernel A/B runs)
 _lib: Optional[C.CDLL] = None
 
 
@@ -37,6 +37,11 @@ class PathTracerMode(enum.IntEnum):  # path_tracer_render_system.h:10-14
 class TraceMode(enum.IntEnum):
     FAST = 0
     REFERENCE_WALK = 1
+
+
+class KernelVariant(enum.IntEnum):
+    POOL = 0  # persistent warps + job queue + two pixel streams per lane (default)
+    PIXEL = 1  # one thread per pixel for the whole launch (round 1's kernel)
 
 
 class BvhMode(enum.IntEnum):
@@ -103,6 +108,7 @@ ABI = [
     ("cavept_get_stats", C.c_int, [_P, C.POINTER(Stats)]),
     ("cavept_reset_stats", C.c_int, [_P]),
     ("cavept_set_count_visits", C.c_int, [_P, C.c_int]),
+    ("cavept_set_kernel_variant", C.c_int, [_P, C.c_int]),
     ("cavept_stream", _P, [_P]),
     ("cavept_accum_device_ptr", _P, [_P]),
     ("cavept_accum_to_sums", C.c_int, [_P]),
@@ -420,6 +426,9 @@ class PathTracer:
 
     def reset_stats(self):
         self._check(self._lib.cavept_reset_stats(self._ctx))
+
+    def set_kernel_variant(self, variant: "KernelVariant"):
+        self._check(self._lib.cavept_set_kernel_variant(self._ctx, int(variant)))
 
     def set_count_visits(self, enable: bool):
         self._check(self._lib.cavept_set_count_visits(self._ctx, 1 if enable else 0))

@@ -106,6 +106,11 @@ struct cavept_ctx {
     DevBuf<F4> d_accum, d_tone;
     DevBuf<unsigned char> d_tone8;
     DevBuf<unsigned long long> d_stats;
+    DevBuf<int> d_job_counter;   // job queue of the persistent trace kernel (trace_pool_body.h)
+    int kernel_variant = CAVEPT_KERNEL_POOL;
+    int accum_sums = 0;          // group mode: the accumulator holds (sum, n)
+    int n_sms = 0;
+    int pool_blocks_depth = -1, pool_blocks_per_sm = 0;  // occupancy of k_trace_pool, cached per stack depth
 
     float cam_pos[3] = { 0, 0, 0 }, cam_right[3] = { 1, 0, 0 }, cam_up[3] = { 0, 1, 0 }, cam_fwd[3] = { 0, 0, 1 };
     float cam_fov = 50.0f;
@@ -423,7 +428,8 @@ CAVEPT_API int cavept_create(const cavept_config* config, cavept_ctx** out_ctx) 
     ok = ok && cudaStreamCreateWithFlags(&ctx->ex.stream, cudaStreamNonBlocking) == cudaSuccess;
     ok = ok && cudaEventCreate(&ctx->ev0) == cudaSuccess && cudaEventCreate(&ctx->ev1) == cudaSuccess && cudaEventCreate(&ctx->ev2) == cudaSuccess;
     const size_t n_pixels = (size_t)config->width * config->height;
-    ok = ok && ctx->d_accum.reserve(n_pixels) == cudaSuccess && ctx->d_stats.reserve(4) == cudaSuccess;
+    ok = ok && ctx->d_accum.reserve(n_pixels) == cudaSuccess && ctx->d_stats.reserve(4) == cudaSuccess && ctx->d_job_counter.reserve(4) == cudaSuccess;
+    ok = ok && cudaDeviceGetAttribute(&ctx->n_sms, cudaDevAttrMultiProcessorCount, ctx->device) == cudaSuccess;
     ok = ok && cudaMemsetAsync(ctx->d_accum.ptr, 0, n_pixels * sizeof(F4), ctx->ex.stream) == cudaSuccess;
     ok = ok && cudaMemsetAsync(ctx->d_stats.ptr, 0, 4 * sizeof(unsigned long long), ctx->ex.stream) == cudaSuccess;
     ok = ok && cudaStreamSynchronize(ctx->ex.stream) == cudaSuccess;
@@ -451,7 +457,7 @@ CAVEPT_API void cavept_destroy(cavept_ctx* ctx) {
     ctx->d_scan.release(); ctx->d_scan_tmp.release(); ctx->d_counters.release(); ctx->d_flags.release();
     ctx->d_items.release(); ctx->d_items_next.release(); ctx->d_accum_items.release(); ctx->d_bins.release();
     ctx->d_node_parent.release(); ctx->d_node_count.release();
-    ctx->d_accum.release(); ctx->d_tone.release(); ctx->d_tone8.release(); ctx->d_stats.release();
+    ctx->d_accum.release(); ctx->d_tone.release(); ctx->d_tone8.release(); ctx->d_stats.release(); ctx->d_job_counter.release();
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
     if (ctx->ev2) cudaEventDestroy(ctx->ev2);
@@ -655,7 +661,7 @@ CAVEPT_API int cavept_reset(cavept_ctx* ctx) {
 // One launch over the pixel rectangle [x0, x0+w) x [y0, y0+h); w == 0 means the whole image.
 static int render_rect(cavept_ctx* ctx, int x0, int y0, int w, int h, int first_frame_index, int n_frames) {
     if (!ctx) return CAVEPT_ERR_INVALID_ARG;
-    if (n_frames <= 0) return fail(ctx, CAVEPT_ERR_INVALID_ARG, "n_frames must be positive");
+    if (n_frames <= 0 || n_frames > (1 << 24)) return fail(ctx, CAVEPT_ERR_INVALID_ARG, "n_frames must be in [1, 2^24]");
     const bool tiled = w > 0;
     const bool active = cavept_is_active(ctx) || (tiled && ctx->mode == CAVEPT_MODE_TILED && ctx->scene_resident);
     if (!active) return fail(ctx, CAVEPT_ERR_NOT_READY, "path tracer not active (mode INTERACTIVE and a resident scene are required)");
@@ -695,10 +701,23 @@ static int render_rect(cavept_ctx* ctx, int x0, int y0, int w, int h, int first_
     p.first_frame = first_frame_index;
     p.n_frames = n_frames;
     p.reset_first = ctx->dirty ? 1 : 0;
+    p.accum_sums = ctx->accum_sums;
     p.accum = ctx->d_accum.ptr;
     p.counters = ctx->d_stats.ptr;
+    const bool fast = ctx->cfg.trace_mode == CAVEPT_TRACE_FAST;
+    int stack_entries = 0, grid_blocks = 0;
+    if (fast && ctx->kernel_variant == CAVEPT_KERNEL_POOL) {
+        stack_entries = ctx->fast_levels + 2 < 4 ? 4 : ctx->fast_levels + 2;
+        if (ctx->pool_blocks_depth != stack_entries) {
+            ctx->pool_blocks_per_sm = trace_pool_blocks_per_sm(stack_entries, false);
+            ctx->pool_blocks_depth = stack_entries;
+        }
+        if (ctx->pool_blocks_per_sm <= 0) return fail(ctx, CAVEPT_ERR_CAPACITY, "k_trace_pool does not fit an SM at stack depth %d", stack_entries);
+        grid_blocks = ctx->n_sms * ctx->pool_blocks_per_sm;
+    }
     CU(ctx, cudaEventRecord(ctx->ev0, ctx->ex.stream));
-    launch_trace(ctx->ex, p, ctx->cfg.trace_mode == CAVEPT_TRACE_FAST, ctx->count_visits);
+    if (grid_blocks > 0) launch_trace_pool(ctx->ex, p, ctx->count_visits, stack_entries, ctx->d_job_counter.ptr, grid_blocks);
+    else launch_trace(ctx->ex, p, fast, ctx->count_visits);
     CU(ctx, cudaEventRecord(ctx->ev1, ctx->ex.stream));
     ctx->dirty = false;
     return check_exec(ctx, "render launch");
@@ -789,6 +808,13 @@ CAVEPT_API int cavept_reset_stats(cavept_ctx* ctx) {
 CAVEPT_API int cavept_set_count_visits(cavept_ctx* ctx, int enable) {
     if (!ctx) return CAVEPT_ERR_INVALID_ARG;
     ctx->count_visits = enable != 0;
+    return CAVEPT_OK;
+}
+
+CAVEPT_API int cavept_set_kernel_variant(cavept_ctx* ctx, int variant) {
+    if (!ctx) return CAVEPT_ERR_INVALID_ARG;
+    if (variant != CAVEPT_KERNEL_POOL && variant != CAVEPT_KERNEL_PIXEL) return fail(ctx, CAVEPT_ERR_INVALID_ARG, "invalid kernel variant %d", variant);
+    ctx->kernel_variant = variant;
     return CAVEPT_OK;
 }
 

@@ -343,6 +343,57 @@ __global__ void __launch_bounds__(128, 8) k_trace(const TraceParams p) {
     }
 }
 
+// ---- second-generation production kernel: persistent warps + job queue + two pixel streams per lane
+//      (trace_pool_body.h).  Grid = SMs x resident blocks; dynamic shared memory = the lane-strided
+//      traversal stack ([stack_entries][128] ints) followed by the record pool ([38][128] floats).
+#ifndef CV_POOL_BLOCKS
+#define CV_POOL_BLOCKS 6
+#endif
+template<bool kCount>
+__global__ void __launch_bounds__(128, CV_POOL_BLOCKS) k_trace_pool(const TraceParams p, int stack_entries, int* job_counter) {
+    extern __shared__ __align__(16) int s_pool[];
+    int* stack = s_pool + threadIdx.x;
+    float* rec = reinterpret_cast<float*>(s_pool + stack_entries * 128) + threadIdx.x;
+    unsigned long long cnt[3] = { 0ull, 0ull, 0ull };
+    unsigned int segs = body_trace_pool<kCount>(p, stack, rec, 128, job_counter, cnt);
+    const int lane = threadIdx.x & 31;
+    segs = __reduce_add_sync(0xffffffffu, segs);
+    if (lane == 0 && segs) atomicAdd(&p.counters[0], (unsigned long long)segs);
+    if (kCount) {
+#pragma unroll
+        for (int k = 1; k < 3; ++k) {
+            unsigned long long v = cnt[k];
+#pragma unroll
+            for (int d = 16; d > 0; d >>= 1) v += __shfl_down_sync(0xffffffffu, v, d);
+            if (lane == 0 && v) atomicAdd(&p.counters[k], v);
+        }
+    }
+}
+
+size_t trace_pool_smem_bytes(int stack_entries) { return (size_t)(stack_entries + kPoolWordsPerThread) * 128 * sizeof(int); }
+
+// Resident blocks per SM of k_trace_pool at this stack depth (occupancy query, cached per depth by the caller).
+int trace_pool_blocks_per_sm(int stack_entries, bool count_visits) {
+    int n = 0;
+    const size_t smem = trace_pool_smem_bytes(stack_entries);
+    const cudaError_t e = count_visits ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_trace_pool<true>, 128, smem)
+                                       : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_trace_pool<false>, 128, smem);
+    return e == cudaSuccess ? n : 0;
+}
+
+void launch_trace_pool(CudaExec& ex, const TraceParams& p, bool count_visits, int stack_entries, int* job_counter, int grid_blocks) {
+    const size_t smem = trace_pool_smem_bytes(stack_entries);
+    const PoolJobs jobs = pool_jobs(p);
+    int blocks = (jobs.n_jobs / 2 + 127) / 128;  // every thread starts with two jobs
+    if (blocks > grid_blocks) blocks = grid_blocks;
+    if (blocks < 1) blocks = 1;
+    ex.note(cudaMemsetAsync(job_counter, 0, sizeof(int), ex.stream));
+    if (count_visits) k_trace_pool<true><<<blocks, 128, smem, ex.stream>>>(p, stack_entries, job_counter);
+    else k_trace_pool<false><<<blocks, 128, smem, ex.stream>>>(p, stack_entries, job_counter);
+    ex.note(cudaGetLastError());
+    ++ex.launches;
+}
+
 void launch_trace(CudaExec& ex, const TraceParams& p, bool fast, bool count_visits) {
     const int tw = p.tile_x1 > 0 ? p.tile_x1 - p.tile_x0 : p.width, th = p.tile_x1 > 0 ? p.tile_y1 - p.tile_y0 : p.height;
     const dim3 grid((tw + 15) / 16, (th + 7) / 8, 1), block(128, 1, 1);

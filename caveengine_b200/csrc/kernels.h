@@ -5,6 +5,7 @@
 
 #include "bvh_parity_driver.h"
 #include "trace_body.h"
+#include "trace_pool_body.h"
 #include "wbvh_body.h"
 
 namespace cavept {
@@ -45,6 +46,10 @@ int run_build_wbvh(CudaExec& ex, WBuild b, WReport* report);
 int run_build_lbvh(CudaExec& ex, WBuild b, WReport* report);
 
 void launch_trace(CudaExec& ex, const TraceParams& p, bool fast, bool count_visits);
+// persistent job-queue kernel (trace_pool_body.h); stack_entries = tree levels + 2, grid_blocks = SMs x resident blocks
+size_t trace_pool_smem_bytes(int stack_entries);
+int trace_pool_blocks_per_sm(int stack_entries, bool count_visits);
+void launch_trace_pool(CudaExec& ex, const TraceParams& p, bool count_visits, int stack_entries, int* job_counter, int grid_blocks);
 void launch_probe(CudaExec& ex, const float* rays, const float* tris, const float* boxes, float* out, int n);
 void launch_tonemap_rgba8(CudaExec& ex, const F4* accum, unsigned char* out, int n_pixels);
 void launch_tonemap_f32(CudaExec& ex, const F4* accum, F4* out, int n_pixels);

@@ -93,6 +93,7 @@ struct TraceParams {
     int max_bounce;
     int first_frame, n_frames;
     int reset_first;  // c_sceneDirty for the first frame of the launch
+    int accum_sums;   // 0: rgb = running mean, a = n (path_tracer.cs.glsl:46-59); 1: rgb = sum, a = n (multi-GPU group mode)
     F4* accum;
     unsigned long long* counters;  // [0] segments, [1] node visits, [2] triangle tests
 };
@@ -480,6 +481,17 @@ CV_HD void accumulate(F4& acc, F3 radiance, bool dirty) {
     }
 }
 
+// (sum, n) instead of (mean, n): what every GPU of a group keeps so that ONE sum-reduce composites the frame
+CV_HD void accumulate_sum(F4& acc, F3 radiance, bool dirty) {
+    acc.x = dirty ? radiance.x : acc.x + radiance.x;
+    acc.y = dirty ? radiance.y : acc.y + radiance.y;
+    acc.z = dirty ? radiance.z : acc.z + radiance.z;
+    acc.w = dirty ? 1.0f : acc.w + 1.0f;
+}
+CV_HD void accumulate_mode(const int accum_sums, F4& acc, F3 radiance, bool dirty) {
+    if (accum_sums) accumulate_sum(acc, radiance, dirty); else accumulate(acc, radiance, dirty);
+}
+
 // One pixel, frames [first_frame, first_frame + n_frames), REFERENCE_WALK traversal.  The
 // segment loop is flat: a lane whose path ends starts its next sample at once.
 // Returns the number of segments traced; visit counters go to cnt[1..2] when kCount.
@@ -499,7 +511,7 @@ CV_D unsigned int body_trace_pixel_reference(const TraceParams& p, int x, int y,
         const Hit hit = hit_scene_reference<kCount>(p, ray, cnt);
         ++segments;
         if (shade_segment(p, hit, ray, seed, radiance, throughput, bounce)) {
-            accumulate(acc, radiance, f == 0 && p.reset_first != 0);
+            accumulate_mode(p.accum_sums, acc, radiance, f == 0 && p.reset_first != 0);
             if (++f == p.n_frames) break;
             radiance = f3(0.0f, 0.0f, 0.0f);
             throughput = f3(1.0f, 1.0f, 1.0f);
@@ -619,7 +631,7 @@ CV_D unsigned int body_trace_pixel_fast(const TraceParams& p, int x, int y, int*
                 }
                 if (shade_hit(p, is_hit, n, mat, ray, seed, radiance, throughput, bounce)) {
                     F4 acc = p.accum[pix];
-                    accumulate(acc, radiance, f == 0 && p.reset_first != 0);
+                    accumulate_mode(p.accum_sums, acc, radiance, f == 0 && p.reset_first != 0);
                     p.accum[pix] = acc;
                     if (++f == p.n_frames) {
                         done = true;

@@ -66,6 +66,12 @@ enum { CAVEPT_TRACE_FAST = 0, CAVEPT_TRACE_REFERENCE_WALK = 1 };
  * geometry that changes every frame (BASELINE config 5). */
 enum { CAVEPT_BVH_PARITY = 0, CAVEPT_BVH_FAST = 1, CAVEPT_BVH_LBVH = 2 };
 
+/* Which production kernel CAVEPT_TRACE_FAST launches (same tree, same per-pixel arithmetic, bit-identical images):
+ * POOL  (default): persistent warps drawing pixel jobs from a global queue, two pixel streams per lane with the
+ *        inactive one parked in shared memory (csrc/trace_pool_body.h);
+ * PIXEL: one thread per pixel for the whole launch (csrc/trace_body.h body_trace_pixel_fast), round 1's kernel. */
+enum { CAVEPT_KERNEL_POOL = 0, CAVEPT_KERNEL_PIXEL = 1 };
+
 typedef struct cavept_config {
     int device;     /* CUDA ordinal; -1 = current device */
     int width;      /* accumulator size; reference default 1920x1080 (renderer/graphics_dvars.h:3) */
@@ -191,6 +197,7 @@ CAVEPT_API int cavept_write_accum(cavept_ctx* ctx, const float* rgba32f, size_t 
 CAVEPT_API int cavept_get_stats(cavept_ctx* ctx, cavept_stats* out);
 CAVEPT_API int cavept_reset_stats(cavept_ctx* ctx);
 CAVEPT_API int cavept_set_count_visits(cavept_ctx* ctx, int enable); /* instrumented kernels: node visits / triangle tests */
+CAVEPT_API int cavept_set_kernel_variant(cavept_ctx* ctx, int variant); /* CAVEPT_KERNEL_*; measurement / A-B comparison */
 CAVEPT_API void* cavept_stream(cavept_ctx* ctx);            /* cudaStream_t the context launches on */
 CAVEPT_API void* cavept_accum_device_ptr(cavept_ctx* ctx);  /* float4[width*height] */
 /* Compositor support: converts the accumulator in place between

@@ -45,7 +45,10 @@ def scene_cache():
 
     def get(name):
         if name not in cache:
-            cache[name] = {"tiny": scenes.tiny_scene, "cornell": scenes.cornell_scene, "heightfield": scenes.heightfield_scene, "sponza": scenes.sponza_scene}[name]()
+            cache[name] = {"tiny": scenes.tiny_scene, "cornell": scenes.cornell_scene, "heightfield": scenes.heightfield_scene, "sponza": scenes.sponza_scene,
+                           "breakfast": scenes.breakfast_scene,  # BASELINE config 4's scene (1,048,576 triangles)
+                           "animated": lambda: scenes.animated_scene(500, 500),  # config 5's scene at test size (500,000 + 128 triangles)
+                           }[name]()
         return cache[name]
 
     return get

@@ -12,6 +12,7 @@
 #include "bvh_parity_driver.h"
 #include "host_math.h"
 #include "trace_body.h"
+#include "trace_pool_body.h"
 #include "wbvh_body.h"
 
 using namespace cavept;
@@ -204,6 +205,17 @@ EMU_API long long emu_render(const GpuPtVertex* vertices, const GpuPtIndex* indi
     p.counters = cnt;
     long long segs = 0;
     int stack[kStackSize];
+    if (fast == 2) {  // the persistent job-queue body (trace_pool_body.h): one emulated lane draws every job, two at a time
+        float rec[kPoolWordsPerThread];
+        int job_counter = 0;
+        segs = body_trace_pool<true>(p, stack, rec, 1, &job_counter, cnt);
+        if (counters) {
+            counters[0] = (unsigned long long)segs;
+            counters[1] = cnt[1];
+            counters[2] = cnt[2];
+        }
+        return segs;
+    }
     for (int y = 0; y < height; ++y) {
         for (int x = 0; x < width; ++x) {
             segs += fast ? body_trace_pixel_fast<true>(p, x, y, stack, 1, cnt) : body_trace_pixel_reference<true>(p, x, y, cnt);

@@ -98,6 +98,6 @@ class EmuScene:
         a = self.asm
         segs = self.lib.emu_render(_p(a.vertices), _p(a.indices), _p(self.nodes), _p(a.meshes), C.c_int(a.meshes.shape[0]), _p(a.materials), _p(self.fnodes),
                                    _p(self.qpairs), _p(self.grid), _p(self.ftris), _p(self.fnormals), C.c_int(self.root_ref), C.byref(cam), C.c_int(max_bounce), C.c_int(width),
-                                   C.c_int(height), C.c_int(first_frame), C.c_int(n_frames), C.c_int(1 if reset_first else 0), _p(accum), C.c_int(1 if fast else 0),
+                                   C.c_int(height), C.c_int(first_frame), C.c_int(n_frames), C.c_int(1 if reset_first else 0), _p(accum), C.c_int(int(fast)),
                                    counters)
         return accum, {"segments": int(segs), "node_visits": int(counters[1]), "tri_tests": int(counters[2])}

@@ -92,3 +92,63 @@ def check_probe_against_reference_twins(out, g):
     hit = rb[:, 0] == 1.0
     assert out[hit, 5].tobytes() == rb[hit, 1].tobytes(), "slab tmin differs from the reference twin"
     assert hit.sum() > 100
+
+
+def lbvh_chain_mesh(cluster=2048, seed=11):
+    """Geometry whose binary radix tree over 30-bit Morton codes is deeper than the traversal stack:
+    one tiny triangle in each of the cells (2^j,0,0), (0,2^j,0), (0,0,2^j), j = 0..9, of the 1024^3 Morton
+    grid (a chain of 30 one-sided splits) and `cluster` triangles inside cell (0,0,0) (equal codes, split by
+    index bits: +log2(cluster) levels).  Forces the LBVH builder's balanced fallback (wbvh_body.h build_lbvh)."""
+    from caveengine_b200 import scenes
+
+    rng = np.random.default_rng(seed)
+    centres = [rng.uniform(0.05, 0.45, size=(cluster, 3))]
+    for j in range(10):
+        for axis in range(3):
+            c = np.full(3, 0.25)
+            c[axis] = float(1 << j) + 0.25
+            centres.append(c[None, :])
+    centres.append(np.full((1, 3), 1024.0))  # pins the centroid bounds: one Morton cell == one unit
+    c = np.concatenate(centres).astype(np.float32)
+    n = c.shape[0]
+    tri = np.array([[-0.01, 0.0, -0.01], [0.0, 0.0, 0.012], [0.012, 0.0, -0.008]], dtype=np.float32)  # faces +y
+    pos = (c[:, None, :] + tri[None, :, :]).reshape(-1, 3).astype(np.float32)
+    nrm = np.tile(np.array([0, 1, 0], dtype=np.float32), (3 * n, 1))
+    return scenes.Mesh(pos, nrm, np.arange(3 * n, dtype=np.uint32))
+
+
+def lbvh_chain_scene(cluster=2048):
+    from caveengine_b200 import scenes
+
+    mesh = lbvh_chain_mesh(cluster)
+    floor = scenes._quad((-8.0, -0.5, -8.0), (-8.0, -0.5, 40.0), (40.0, -0.5, 40.0), (40.0, -0.5, -8.0))
+    mats = [scenes.Material((0.8, 0.7, 0.6), 0.8, 0.0, 2.0), scenes.Material((0.6, 0.6, 0.6), 0.9, 0.0, 0.0)]
+    inst = [scenes.Instance(0, 0, scenes.mat_identity()), scenes.Instance(1, 1, scenes.mat_identity())]
+    return scenes.Scene("lbvh_chain", [mesh, floor], inst, mats, scenes.look_at((0.25, 1.2, 0.25), (0.25, 0.0, 0.26), fov=25.0))
+
+
+def image_metrics(got, want):
+    """The figures the image tolerances are stated in (all relative to the oracle image `want`):
+    rel_rmse   per-pixel RMSE of rgb / mean radiance
+    bias       |mean(got) - mean(want)| / mean(want)
+    bad_1e4    fraction of pixels with a channel beyond 1e-4 * (|want| + 1e-3)
+    far_5pct   fraction of pixels with a channel beyond 5 % * (|want| + 1e-3)
+    exact      fraction of pixels whose rgb is bit-identical"""
+    g = np.asarray(got)[..., :3].astype(np.float64)
+    r = np.asarray(want)[..., :3].astype(np.float64)
+    mean = float(r.mean())
+    d = np.abs(g - r)
+    return {
+        "rel_rmse": float(np.sqrt((d ** 2).mean())) / mean,
+        "bias": abs(float(g.mean()) - mean) / mean,
+        "bad_1e4": float((d > 1e-4 * (np.abs(r) + 1e-3)).any(axis=-1).mean()),
+        "far_5pct": float((d > 0.05 * (np.abs(r) + 1e-3)).any(axis=-1).mean()),
+        "exact": float((g == r).all(axis=-1).mean()),
+    }
+
+
+def check_metrics(m, limits, what):
+    """Every limit is an upper bound except `exact` (a lower bound).  The assert message carries the measured values."""
+    for k, lim in limits.items():
+        ok = m[k] >= lim if k == "exact" else m[k] <= lim
+        assert ok, f"{what}: {k} = {m[k]:.6g} violates the stated bound {lim:.6g}; measured {m}"

@@ -289,3 +289,21 @@ def test_intersection_bodies_match_the_engines_cpu_twins():
     tris, boxes = np.ascontiguousarray(g["tris"]), np.ascontiguousarray(g["boxes"])
     lib.emu_probe(C.c_int(n), rays.ctypes.data_as(C.c_void_p), tris.ctypes.data_as(C.c_void_p), boxes.ctypes.data_as(C.c_void_p), out.ctypes.data_as(C.c_void_p))
     H.check_probe_against_reference_twins(out, g)
+
+
+@pytest.mark.parametrize("name,w,h", [("tiny", 61, 35), ("heightfield", 64, 36)])
+def test_pool_kernel_body_equals_the_per_pixel_body_bitwise(port_oracle, scene_cache, name, w, h):
+    """The persistent job-queue body (trace_pool_body.h: two pixel streams per lane, records parked in shared
+    memory) runs the same walk_step / walk_test_triangle / shade_hit sequence per pixel as body_trace_pixel_fast:
+    same accumulator bytes, same segment / node / triangle counts -- also on a ragged image (61 x 35 is not a
+    multiple of the 8x4 job tile) and across two launches (progressive accumulation)."""
+    sc = scene_cache(name)
+    asm = port_oracle.assemble(sc)
+    emu = E.EmuScene(asm, sc)
+    a, sa = emu.render(sc.camera, w, h, 0, 3, 5, fast=1)
+    b, sb = emu.render(sc.camera, w, h, 0, 3, 5, fast=2)
+    assert a.tobytes() == b.tobytes()
+    assert sa == sb
+    a2, _ = emu.render(sc.camera, w, h, 3, 2, 5, fast=1, accum=a.copy(), reset_first=False)
+    b2, _ = emu.render(sc.camera, w, h, 3, 2, 5, fast=2, accum=b.copy(), reset_first=False)
+    assert a2.tobytes() == b2.tobytes() and np.all(b2[..., 3] == 5.0)

@@ -523,3 +523,26 @@ def test_high_spp_image_matches_oracle_at_equal_seeds(api, port_oracle, scene_ca
     assert abs(g.mean() - mean) <= 0.002 * mean
     far = (np.abs(g - r) > 0.05 * (np.abs(r) + 1e-3)).any(axis=-1).mean()
     assert far <= 0.02, f"{far:.3%} of pixels beyond 5 % relative"
+
+
+# ---- the two production kernels (include/cavept.h CAVEPT_KERNEL_*) -----------------------------------
+@pytest.mark.parametrize("name,w,h,mb,frames", [("sponza", 640, 360, 8, 4), ("tiny", 101, 57, 5, 6)])
+def test_pool_kernel_equals_pixel_kernel_bitwise(api, scene_cache, name, w, h, mb, frames):
+    """CAVEPT_KERNEL_POOL (persistent warps, job queue, two pixel streams per lane) and CAVEPT_KERNEL_PIXEL (one
+    thread per pixel) run the same per-pixel arithmetic in the same per-pixel order: identical accumulator bytes
+    and identical segment / node-visit / triangle-test counts, over two launches and on a ragged image."""
+    sc = scene_cache(name)
+    out = {}
+    for variant in (api.KernelVariant.POOL, api.KernelVariant.PIXEL):
+        with _tracer(api, sc, w, h, mb, api.TraceMode.FAST) as pt:
+            pt.set_kernel_variant(variant)
+            pt.set_count_visits(True)
+            pt.reset_stats()
+            pt.render(0, frames)
+            pt.render(frames, 2, sync=True)
+            st = pt.stats()
+            out[variant] = (pt.read_accum(), st["segments"], st["node_visits"], st["triangle_tests"])
+    a, b = out[api.KernelVariant.POOL], out[api.KernelVariant.PIXEL]
+    assert a[1:] == b[1:]
+    assert a[0].tobytes() == b[0].tobytes()
+    assert np.all(a[0][..., 3] == float(frames + 2))

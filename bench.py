@@ -1,20 +1,23 @@
 #!/usr/bin/env python3
-"""Benchmark of the path-trace pass: M sample-bounces (path segments, one HitScene call each)
-per second at 1080p on the 262,144-triangle Sponza-shaped scene, 8 bounces
-(BASELINE.json configs[2]).
+"""Benchmark of the path-trace pass: M sample-bounces (path segments, one HitScene call each) per second.
 
-    python bench.py --gpus N --steps K --warmup W            # our CUDA path
+    python bench.py --gpus N --steps K --warmup W            # our CUDA path (config 3 = BASELINE.json configs[2])
     python bench.py --impl reference --gpus N --steps K ...  # the reference's CPU code on host cores
+    python bench.py --config 4 --gpus 8 --steps 2 --warmup 1 # BASELINE config 4 (1,048,576 tris, 4K, 1024 spp)
 
-One step = one launch of the pass over the whole 1920x1080 image for `--spp` consecutive
-c_frameIndex values (default 32; the default K = 8 steps accumulate the config's 256 spp).
-With N GPUs each rank renders its own disjoint frame indices (weak scaling) and the float4
-accumulators are combined by one NCCL sum-reduce inside the timed region.
+One step = ONE pass of the hot path over the configuration's whole sample set: config 3 = 1920x1080, 8 bounces,
+256 spp on the 262,144-triangle Sponza-shaped scene.  With N GPUs the step's samples are SPLIT: rank r renders
+frames cavept_group_frame_block(0, spp, r, N) of the full image into per-GPU (sum, n) accumulators and ONE
+ncclReduce of the float4 sums (cavept_group_composite, C ABI) composites the frame on rank 0 -- inside the timed
+region, every step ("scaling": "strong": the job is fixed, per-GPU work shrinks as N grows).  `--scaling weak`
+keeps round 1's arrangement (every rank renders the whole spp; N times the samples per step).
+torch.distributed (gloo) is control plane only: barrier, the 128-byte NCCL id, max-over-ranks of the timings.
 Prints ONE JSON line on rank 0.
 """
 from __future__ import annotations
 
 import argparse
+import glob
 import json
 import os
 import subprocess
@@ -27,9 +30,25 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-WIDTH, HEIGHT, MAX_BOUNCE = 1920, 1080, 8
-METRIC = "Msample-bounces/sec 1080p on 262k-tri scene"
 UNIT = "M segments/s"
+CONFIGS = {
+    3: {"scene": "sponza", "label": "sponza_262144 (262,144 tris, 25 meshes/materials)", "width": 1920, "height": 1080, "max_bounce": 8, "spp": 256,
+        "metric": "Msample-bounces/sec 1080p on 262k-tri scene"},
+    4: {"scene": "breakfast", "label": "breakfast_1048576 (1,048,576 tris, 17 meshes, 12 materials)", "width": 3840, "height": 2160, "max_bounce": 8, "spp": 1024,
+        "metric": "Msample-bounces/sec 4K on 1M-tri scene"},
+}
+
+
+def make_scene(cfg):
+    from caveengine_b200 import scenes
+
+    return {"sponza": scenes.sponza_scene, "breakfast": scenes.breakfast_scene}[cfg["scene"]]()
+
+
+def config_dict(cfg, spp):
+    """The same dictionary in both arms (ours and --impl reference): what is rendered, nothing about who renders it."""
+    return {"workload": f"{cfg['label']} {cfg['width']}x{cfg['height']}, {cfg['max_bounce']} bounces, {spp} spp per step (the whole job, split over the GPUs)",
+            "width": cfg["width"], "height": cfg["height"], "max_bounce": cfg["max_bounce"], "spp_per_step": spp}
 
 
 def measured_peaks():
@@ -94,68 +113,77 @@ class ClockSampler:
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons), "samples": len(sm)}
 
 
-def ncu_digest():
-    """Newest committed digest of an `ncu --set full` capture of k_trace (profiles/summarize.py json)."""
-    import glob
+def ncu_digest(config_id, kernel, spp):
+    """Newest committed digest (profiles/summarize.py json) of an `ncu --set full` capture of exactly this launch:
+    same config, same kernel variant, same spp per launch.  None when there is none -- nothing is scaled."""
+    best = None
+    for f in sorted(glob.glob(os.path.join(ROOT, "profiles", "r*_ncu.json"))):
+        try:
+            d = json.load(open(f))
+        except Exception:
+            continue
+        if d.get("config") == config_id and d.get("kernel_variant") == kernel and d.get("spp_of_launch") == spp:
+            best = (d, os.path.basename(f))
+    return best or (None, None)
 
-    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "*_k_trace_ncu.json")))
-    return (json.load(open(files[-1])), os.path.basename(files[-1])) if files else (None, None)
 
-
-def roofline(achieved, peaks, peak_kind, bytes_per_segment, vn, vt, seg_per_launch, launch_ms, clocks, spp):
-    """The contract's object quotes ALGORITHMIC gather bytes against the HBM peak.  That ratio is
-    NOT a speed-of-light claim for this kernel: the 262k-triangle working set (~35 MB) lives in the
-    126 MB L2 and DRAM moves < 1 byte per segment (`traffic`).  `binding` carries what ncu says the
-    kernel is actually limited by: unit utilisations from the committed capture, plus the L1TEX
-    gather rate (one wavefront per lane per 32-byte gather; wavefronts per segment from the capture
-    x the live segment rate, against 1 wavefront / clock / SM at the sampled SM clock)."""
-    r = {"bound": "hbm", "achieved": achieved, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": achieved / peaks["hbm_gbs"], "traffic": None,
-         "peak_kind": peak_kind, "kernel": "k_trace<fast>", "bytes_per_segment": bytes_per_segment, "node_visits_per_segment": vn,
-         "triangle_tests_per_segment": vt,
-         "note": "nominal: algorithmic bytes (own traversal policy) / HBM peak; the working set is L2-resident, HBM is not the binding roof -- see `binding`"}
-    d, name = ncu_digest()
-    if d and d.get("segments_of_launch"):
-        scale = seg_per_launch / d["segments_of_launch"]
-        r["traffic"] = d["dram_bytes"] * scale
-        r["traffic_source"] = f"profiles/{name}: dram__bytes_read+write of a {d['spp_of_launch']}-spp launch ({d['segments_of_launch']} segments)" + ("" if d["spp_of_launch"] == spp else f", scaled by segments to this {spp}-spp launch")
-        wf_per_seg = d["l1_lsu_wavefronts"] / d["segments_of_launch"]
-        mhz = (clocks or {}).get("sm_mhz") or peaks.get("sm_max_mhz") or 1965.0
-        peak_wf = 148 * mhz * 1e6
-        ach_wf = wf_per_seg * seg_per_launch / (launch_ms * 1e-3)
-        units = {"instruction issue slots": d["issue_active_pct"], "l1tex data-pipe LSU wavefronts": d["l1_lsu_wavefronts_pct_of_peak"],
-                 "l2 throughput": d["l2_throughput_pct"], "fma pipe": d["fma_pipe_pct"], "alu pipe": d.get("alu_pipe_pct"), "dram throughput": d["dram_throughput_pct"]}
-        top = max(units, key=lambda k: units[k] or 0.0)
-        r["binding"] = {"most_utilised_unit": top, "pct_of_peak_in_capture": units, "active_threads_per_warp_instruction": d["threads_per_instruction"],
-                        "warps_active_pct": d["warps_active_pct"], "registers_per_thread": d["registers_per_thread"],
-                        "l1_wavefronts_per_segment": wf_per_seg, "l1_wavefronts_per_s_live": ach_wf, "l1_wavefronts_per_s_peak": peak_wf, "l1_wavefront_frac_live": ach_wf / peak_wf,
-                        "l2_hit_pct": d["l2_hit_pct"], "l2_bytes_per_segment": d["l2_bytes"] / d["segments_of_launch"], "dram_bytes_per_segment": d["dram_bytes"] / d["segments_of_launch"],
-                        "note": "a divergent gather kernel: no single unit saturates; the half-rate ALU pipe (PRMT decode, 3-input min/max, selects), issue slots (~21 of 32 lanes active per instruction) and the L1 gather pipe share the bound"}
+def roofline(pt, cfg_id, kernel, spp_launch, seg_per_launch, launch_ms, vn, vt, hit_frac, scene_bytes, peaks, peak_kind, pixels):
+    """The roof this kernel can actually reach: it is a gather kernel over an L2-resident scene, so the unit of work
+    is one 32-byte LDG.E.256 gather per lane (a QPair per interior step, two per triangle test, three per shaded hit).
+    achieved = ALGORITHMIC gathers per launch (counted live by the instrumented pass) x 32 B / the launch's duration;
+    peak = the rate at which this GPU serves random 32-byte gathers from a working set the size of the scene's node +
+    triangle arrays, measured by cavept_measure_gather IN THIS RUN (L2-resident for config 3, beyond L2 for 4).
+    The algorithmic-bytes / HBM-peak ratio the contract names is kept as `nominal_hbm` (it is not a binding roof here:
+    see `traffic`)."""
+    gathers_per_segment = vn / 2.0 + 2.0 * vt + 3.0 * hit_frac
+    gathers = seg_per_launch * gathers_per_segment
+    ws = max(int(scene_bytes), 1 << 20)
+    peak_scene = pt.measure_gather(ws, 3000)          # lane-gathers / s out of a scene-sized working set
+    peak_l1 = pt.measure_gather(1 << 20, 3000)        # same out of 1 MB (mostly L1/L2-near): the L1 wavefront ceiling
+    ach = gathers / (launch_ms * 1e-3)
+    bytes_per_segment = vn * 16.0 + vt * 64.0 + 96.0 * hit_frac
+    algo_bytes = seg_per_launch * bytes_per_segment + 32.0 * pixels * spp_launch
+    hbm = algo_bytes / (launch_ms * 1e-3) / 1e9
+    r = {"bound": "l2-gather", "kernel": f"k_trace_{kernel}", "achieved": ach * 32.0 / 1e9, "peak": peak_scene * 32.0 / 1e9, "unit": "GB/s", "frac": ach / peak_scene,
+         "peak_kind": f"measured in this run: cavept_measure_gather, random 32-byte LDG.E.256 per lane over a {ws >> 20} MB working set (= the scene's node + triangle arrays)",
+         "gathers_per_segment": gathers_per_segment, "node_visits_per_segment": vn, "triangle_tests_per_segment": vt, "hit_fraction": hit_frac,
+         "achieved_gathers_per_s": ach, "peak_gathers_per_s": peak_scene, "l1_resident_peak_gathers_per_s": peak_l1, "frac_of_l1_resident_peak": ach / peak_l1,
+         "traffic": None,
+         "nominal_hbm": {"achieved": hbm, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": hbm / peaks["hbm_gbs"], "peak_kind": peak_kind, "bytes_per_segment": bytes_per_segment,
+                         "note": "algorithmic bytes (own traversal policy) / HBM copy peak; NOT a binding roof for an L2-resident scene"}}
+    d, name = ncu_digest(cfg_id, kernel, spp_launch)
+    if d:
+        r["traffic"] = d["dram_bytes"]
+        r["traffic_source"] = f"profiles/{name}: dram__bytes_read+write of this very launch ({d['spp_of_launch']} spp, {d['segments_of_launch']} segments) under ncu --set full"
+        r["ncu"] = {k: d.get(k) for k in ("threads_per_instruction", "issue_active_pct", "alu_pipe_pct", "fma_pipe_pct", "l1_lsu_wavefronts_pct_of_peak", "l1_hit_pct", "l2_hit_pct",
+                                            "l2_throughput_pct", "dram_throughput_pct", "warps_active_pct", "registers_per_thread", "l1_lsu_wavefronts", "l2_bytes")}
     return r
 
 
-def cpu_sample_rows(cores: int):
-    """Bounded CPU sample of the same workload: a band of full-width rows of the 1080p image
-    at 1 spp (frame 0), about 20 s of single-thread work per 8 cores."""
-    rows = max(16, min(HEIGHT, 36 * max(1, cores)))
-    y0 = (HEIGHT - rows) // 2
+def cpu_sample_rows(cfg, cores: int):
+    """Bounded CPU sample of the same workload: a band of full-width rows of the image at 1 spp (frame 0),
+    about 20 s of single-thread work per 8 cores."""
+    rows = max(16, min(cfg["height"], (36 * max(1, cores) * 1920) // cfg["width"]))
+    y0 = (cfg["height"] - rows) // 2
     return y0, y0 + rows
 
 
-def run_cpu_reference(scene, steps: int, warmup: int, threads: int):
+def run_cpu_reference(cfg, scene, steps: int, warmup: int, threads: int):
     """The reference's own CPU code (oracle/_ref) where it was built, else the oracle port."""
     from oracle import oracle as O
 
+    W, H, MB = cfg["width"], cfg["height"], cfg["max_bounce"]
     orc = O.best()
     asm = orc.assemble(scene)
-    y0, y1 = cpu_sample_rows(threads)
-    accum = np.zeros((HEIGHT, WIDTH, 4), dtype=np.float32)
+    y0, y1 = cpu_sample_rows(cfg, threads)
+    accum = np.zeros((H, W, 4), dtype=np.float32)
     total_segments, total_ms = 0, 0.0
     for s in range(warmup + steps):
-        _, st = orc.render(asm, scene.camera, WIDTH, HEIGHT, s, 1, MAX_BOUNCE, accum=accum, reset_first=True, rect=(0, y0, WIDTH, y1), threads=threads)
+        _, st = orc.render(asm, scene.camera, W, H, s, 1, MB, accum=accum, reset_first=True, rect=(0, y0, W, y1), threads=threads)
         if s >= warmup:
             total_segments += st["segments"]
             total_ms += st["ms"]
-    sample = f"rows {y0}..{y1} of the 1080p image ({WIDTH * (y1 - y0)} pixels), 1 spp per step, {MAX_BOUNCE} bounces, {threads} threads"
+    sample = f"rows {y0}..{y1} of the {W}x{H} image ({W * (y1 - y0)} pixels), 1 spp per step, {MB} bounces, {threads} threads"
     return orc.kind, total_segments / (total_ms * 1e-3) / 1e6, total_ms / max(steps, 1), sample, orc
 
 
@@ -173,7 +201,10 @@ def main():
     ap.add_argument("--steps", type=int, default=8)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--spp", type=int, default=256, help="frames (samples per pixel) per step; 256 = the whole of BASELINE config 3 in one step")
+    ap.add_argument("--config", type=int, default=3, choices=sorted(CONFIGS), help="BASELINE.json config (3 = the headline, 4 = 1M tris at 4K, 1024 spp)")
+    ap.add_argument("--spp", type=int, default=0, help="samples per pixel per step, whole job (default: the config's: 256 / 1024)")
+    ap.add_argument("--scaling", default="strong", choices=["strong", "weak"], help="strong: the step's spp are split over the GPUs; weak: every GPU renders all of them")
+    ap.add_argument("--kernel", default="pool", choices=["pool", "pixel"], help="production kernel variant (include/cavept.h CAVEPT_KERNEL_*)")
     ap.add_argument("--trace-mode", default="fast", choices=["fast", "reference_walk"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
@@ -181,21 +212,22 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
-
-    from caveengine_b200 import scenes
-
-    workload = f"sponza_262144 (262,144 tris, 25 meshes/materials) {WIDTH}x{HEIGHT}, {MAX_BOUNCE} bounces, {args.spp} spp per step"
+    cfg = CONFIGS[args.config]
+    W, H, MB = cfg["width"], cfg["height"], cfg["max_bounce"]
+    S = args.spp or cfg["spp"]
+    metric = cfg["metric"]
 
     if args.impl == "reference":
         if rank != 0:
             return 0
-        scene = scenes.sponza_scene()
+        scene = make_scene(cfg)
         threads = os.cpu_count() or 1
-        kind, value, ms_per_step, sample, _ = run_cpu_reference(scene, args.steps, args.warmup, threads)
+        kind, value, ms_per_step, sample, _ = run_cpu_reference(cfg, scene, args.steps, args.warmup, threads)
         line = {
-            "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": workload, "note": "CPU arm: each step is a bounded sample of the workload"},
+            "impl": "reference", "metric": metric, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": config_dict(cfg, S),
+            "arm_note": "CPU arm: each step is a bounded sample of the workload (cpu_baseline.sample); the rate is per segment, so it compares with the GPU arm's rate",
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": kind, "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         }
@@ -212,90 +244,105 @@ def main():
         raise SystemExit("bench.py: no CUDA device -- cavept has no CPU path (use --impl reference for the CPU arm)")
     torch.cuda.set_device(local_rank)
     if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        dist.init_process_group("gloo")  # control plane only; the data path's NCCL communicator lives in libcavept
 
-    scene = scenes.sponza_scene()
+    scene = make_scene(cfg)
     mode = cb.TraceMode.FAST if args.trace_mode == "fast" else cb.TraceMode.REFERENCE_WALK
-    pt = cb.PathTracer(WIDTH, HEIGHT, MAX_BOUNCE, trace_mode=mode, device=local_rank)
+    pt = cb.PathTracer(W, H, MB, trace_mode=mode, device=local_rank)
+    pt.set_kernel_variant(cb.KernelVariant.POOL if args.kernel == "pool" else cb.KernelVariant.PIXEL)
     pt.set_mode(cb.PathTracerMode.INTERACTIVE)
     t_up = time.perf_counter()
     pt.upload_scene(scene)
     upload_ms = (time.perf_counter() - t_up) * 1e3
     pt.set_camera(scene.camera)
-    build = pt.stats()
     # second build for a warm number (first includes allocation and module load)
     pt.upload_scene(scene)
     pt.set_camera(scene.camera)
     build = pt.stats()
 
+    group = None
+    if world > 1:
+        def exchange(r, uid):
+            box = [uid]
+            dist.broadcast_object_list(box, src=0)
+            return box[0]
+
+        group = compositor.Group(pt, rank, world, exchange)
+    strong = args.scaling == "strong"
+    if strong:
+        f_first, f_count = compositor.frame_block(0, S, rank, world)
+    else:
+        f_first, f_count = rank * S, S
+
     stream = torch.cuda.ExternalStream(pt.stream_handle, device=torch.device("cuda", local_rank))
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
-    S = args.spp
-
-    def frames_of(step_index):  # disjoint c_frameIndex blocks per (step, rank)
-        return (step_index * world + rank) * S
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    # ---- instrumented pass (untimed): node visits / triangle tests per segment ------------------
+    def step(k):
+        """One pass over the whole job: this rank's frames of the full image, then ONE collective."""
+        pt.reset()
+        if f_count > 0:
+            pt.render(f_first + k * (S if strong else S * world), f_count)
+        if group is not None:
+            group.composite(dst=0)
+
+    # ---- instrumented pass (untimed): node visits / triangle tests / hit fraction per segment -------------
     pt.set_count_visits(True)
     pt.reset_stats()
+    pt.reset()
     pt.render(1 << 20, 1, sync=True)
     inst = pt.stats()
     pt.set_count_visits(False)
     vn = inst["node_visits"] / max(inst["segments"], 1)
     vt = inst["triangle_tests"] / max(inst["segments"], 1)
+    samples_inst = W * H
+    hit_frac = max(0.0, 1.0 - samples_inst / max(inst["segments"], 1))  # every path ends in one miss or max_bounce hits: a lower bound of the hit share
 
-    # ---- device-resident timing -----------------------------------------------------------------
+    # ---- device-resident timing -----------------------------------------------------------------------------
     # nvidia-smi is started BEFORE the warm-up and must have produced a sample before the timed region
     # opens: its start-up (NVML attach) can stall the GPU for a moment, which belongs to nobody's step time
     sampler = ClockSampler(local_rank)
     sampler.start()
     sampler.wait_first(5.0)
-    pt.reset()
     with torch.cuda.stream(stream):
         for w in range(args.warmup):
             flush.zero_()  # same work as a timed step (the first torch memset also loads torch's kernels: not a step's cost)
-            pt.render(frames_of(w), S)
+            step(w)
     pt.sync()
-    pt.reset()
     pt.reset_stats()
-    launches0 = pt.stats()["kernel_launches"]
+    st0 = pt.stats()
     barrier()
     sampler.mark()  # only samples taken from here on (under load) are reported
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    kernel_ms = []
     with torch.cuda.stream(stream):
         ev0.record(stream)
         for k in range(args.steps):
             flush.zero_()  # L2 flush between steps (on the same stream)
-            pt.render(frames_of(args.warmup + k), S)
-        if world > 1:
-            pt.accum_to_sums()
-            compositor.composite(pt.accum_as_torch(), dst=0)
-            if rank == 0:
-                pt.accum_from_sums()
+            step(args.warmup + k)
         ev1.record(stream)
+    pt.sync()
     barrier()
     clocks = sampler.stop()
     elapsed_ms = ev0.elapsed_time(ev1)
     st = pt.stats()
     kernel_ms_last = st["last_render_ms"]
     segments = st["segments"]
-    launches = st["kernel_launches"] - launches0
-    t = torch.tensor([elapsed_ms], dtype=torch.float64, device="cuda")
-    s = torch.tensor([float(segments)], dtype=torch.float64, device="cuda")
+    launches = st["kernel_launches"] - st0["kernel_launches"]
+    collectives = st["collectives"] - st0["collectives"]
+    t = torch.tensor([elapsed_ms], dtype=torch.float64)
+    s = torch.tensor([float(segments), float(kernel_ms_last)], dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dist.all_reduce(s, op=dist.ReduceOp.SUM)
-    max_ms, total_segments = float(t.item()), float(s.item())
+    max_ms, total_segments = float(t.item()), float(s[0].item())
     value = total_segments / (max_ms * 1e-3) / 1e6
 
-    # ---- end to end through the C ABI with host buffers -------------------------------------------
-    host = np.empty((HEIGHT, WIDTH, 4), dtype=np.float32)
+    # ---- end to end through the C ABI with host buffers -------------------------------------------------------
+    host = np.empty((H, W, 4), dtype=np.float32)
     host_t = torch.from_numpy(host)
     try:
         torch.cuda.cudart().cudaHostRegister(host_t.data_ptr(), host.nbytes, 0)
@@ -306,13 +353,18 @@ def main():
     t0 = time.perf_counter()
     for k in range(args.steps):
         pt.set_camera(scene.camera)  # per-frame constants from host memory; marks the scene dirty
-        pt.render(frames_of(args.warmup + k), S)
-        pt.read_accum(host)  # device -> host read of the step's result (synchronises)
+        step(args.warmup + k)
+        if group is None:
+            pt.read_accum(host)  # device -> host read of the step's result (synchronises)
+        elif rank == 0:
+            pt.read_composite(host)  # the composited frame lands in host memory on rank 0
+        else:
+            pt.sync()
     barrier()
     e2e_s = time.perf_counter() - t0
     e2e_segments = pt.stats()["segments"]
-    te = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
-    se = torch.tensor([float(e2e_segments)], dtype=torch.float64, device="cuda")
+    te = torch.tensor([e2e_s], dtype=torch.float64)
+    se = torch.tensor([float(e2e_segments)], dtype=torch.float64)
     if world > 1:
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
         dist.all_reduce(se, op=dist.ReduceOp.SUM)
@@ -321,35 +373,34 @@ def main():
     if rank == 0:
         peaks, peak_kind = measured_peaks()
         seg_per_launch = segments / max(args.steps, 1)
-        launch_ms = elapsed_ms / max(args.steps, 1)  # flush + launch; the flush is < 0.1 ms
-        # algorithmic bytes per segment, own traversal policy: 16 B per node record
-        # visited (a sibling pair is one 32-byte QPair), 64 B per triangle tested (one FastTri
-        # record), 96 B shading gather (64 B normals record + 32 B material) per hit segment
-        # (upper bound: every segment), + 32 B per pixel per sample of accumulator traffic
-        pixels = WIDTH * HEIGHT
-        bytes_per_segment = vn * 16.0 + vt * 64.0 + 96.0
-        algo_bytes = seg_per_launch * bytes_per_segment + 32.0 * pixels * S
-        achieved = algo_bytes / (launch_ms * 1e-3) / 1e9
+        launch_ms = kernel_ms_last if kernel_ms_last > 0 else elapsed_ms / max(args.steps, 1)  # CUDA events around the last k_trace launch, on its own stream
+        scene_bytes = build["fast_node_count"] * 16 + 2 * 64 * sum(scene.meshes[i.mesh].n_tris for i in scene.instances)
         line = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": max_ms / max(args.steps, 1),
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": workload, "trace_mode": args.trace_mode, "l2": "flushed between steps (256 MiB memset on the launch stream); scene working set ~35 MB is L2-resident in steady state",
-                       "parallelism": f"frames split over {world} GPU(s), one NCCL sum-reduce of the float4 accumulator"},
+            "metric": metric, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": max_ms / max(args.steps, 1),
+            "higher_is_better": True, "scaling": args.scaling if world > 1 else "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": config_dict(cfg, S),
+            "arm_note": {"trace_mode": args.trace_mode, "kernel": args.kernel, "config_id": args.config,
+                         "l2": "flushed between steps (256 MiB memset on the launch stream)",
+                         "parallelism": (f"{S} spp split over {world} GPU(s) ({f_count} frames on rank 0), (sum, n) per GPU, one ncclReduce of the float4 accumulator per step inside the timed region (cavept_group_composite)"
+                                         if strong else f"every one of the {world} GPU(s) renders {S} spp of its own per step, one ncclReduce per step")},
             "bvh_build_ms": build["last_build_ms"], "bvh_fast_build_ms": build["last_fast_build_ms"], "bvh_fast_levels": build["fast_build_levels"], "bvh_fast_launches": build["fast_build_launches"], "bvh_levels": build["build_levels"], "bvh_launches": build["build_launches"],
             "scene_upload_and_build_wall_ms_cold": upload_ms,
-            "segments_per_step": seg_per_launch, "last_kernel_ms": kernel_ms_last,
-            "gpu_launches": int(launches),
+            "segments_per_step": total_segments / max(args.steps, 1), "last_kernel_ms": kernel_ms_last,
+            "gpu_launches": int(launches), "nccl_collectives": int(collectives),
             "clocks": clocks,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": 13 * 4, "d2h_bytes_per_step": int(host.nbytes),
-                    "note": "per step: cavept_set_camera (host constants) + cavept_render + cavept_read_accum into host memory; scene resident as in the reference"},
-            "roofline": roofline(achieved, peaks, peak_kind, bytes_per_segment, vn, vt, seg_per_launch, launch_ms, clocks, S),
+                    "note": "per step: cavept_set_camera (host constants) + cavept_render of this rank's frames + cavept_group_composite + the frame read into host memory on rank 0 (cavept_read_accum / cavept_read_composite); scene resident as in the reference"},
+            "roofline": roofline(pt, args.config, args.kernel, f_count, seg_per_launch, launch_ms, vn, vt, hit_frac, scene_bytes, peaks, peak_kind, W * H),
         }
         if world == 1 and not args.no_cpu_baseline:
             threads = os.cpu_count() or 1
-            kind, cpu_value, _, sample, orc = run_cpu_reference(scene, 1, 0, threads)
+            kind, cpu_value, _, sample, orc = run_cpu_reference(cfg, scene, 1, 0, threads)
             line["cpu_baseline"] = {"value": cpu_value, "unit": UNIT, "cores": threads, "kind": kind, "sample": sample, "bvh_build_ms_1thread": cpu_bvh_build_ms(scene, orc)}
         print(json.dumps(line))
+    if group is not None:
+        group.close()
     if world > 1:
+        dist.barrier()
         dist.destroy_process_group()
     pt.close()
     return 0

@@ -50,7 +50,8 @@ class BvhMode(enum.IntEnum):
     LBVH = 2  # production tree only, Morton-sort builder (per-frame rebuilds)
 
 
-ERR_INVALID_ARG, ERR_DEGENERATE_GEOMETRY, ERR_CUDA, ERR_NOT_READY, ERR_CAPACITY = 1, 2, 3, 4, 5
+ERR_INVALID_ARG, ERR_DEGENERATE_GEOMETRY, ERR_CUDA, ERR_NOT_READY, ERR_CAPACITY, ERR_NCCL = 1, 2, 3, 4, 5, 6
+GROUP_ID_BYTES = 128
 
 
 class _Config(C.Structure):
@@ -75,6 +76,7 @@ class Stats(C.Structure):
         ("last_build_ms", C.c_float), ("last_fast_build_ms", C.c_float), ("last_render_ms", C.c_float),
         ("triangle_count", C.c_int), ("node_count", C.c_int), ("fast_node_count", C.c_int), ("instance_count", C.c_int),
         ("build_levels", C.c_int), ("build_launches", C.c_int), ("fast_build_levels", C.c_int), ("fast_build_launches", C.c_int),
+        ("last_update_instances_ms", C.c_float), ("last_update_was_refit", C.c_int), ("collectives", C.c_uint64),
     ]
 
     def as_dict(self):
@@ -113,6 +115,17 @@ ABI = [
     ("cavept_accum_device_ptr", _P, [_P]),
     ("cavept_accum_to_sums", C.c_int, [_P]),
     ("cavept_accum_from_sums", C.c_int, [_P]),
+    ("cavept_group_unique_id", C.c_int, [_P, C.c_size_t]),
+    ("cavept_group_create", C.c_int, [_P, C.c_int, C.c_int, _P, C.c_size_t]),
+    ("cavept_group_destroy", C.c_int, [_P]),
+    ("cavept_group_info", C.c_int, [_P, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    ("cavept_group_frame_block", C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    ("cavept_group_composite", C.c_int, [_P, C.c_int]),
+    ("cavept_read_composite", C.c_int, [_P, _P, C.c_size_t]),
+    ("cavept_composite_device_ptr", _P, [_P]),
+    ("cavept_group_row_band", C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    ("cavept_group_gather_bands", C.c_int, [_P, C.c_int]),
+    ("cavept_measure_gather", C.c_int, [_P, C.c_size_t, C.c_int, C.POINTER(C.c_double)]),
     ("cavept_sort_pairs", C.c_int, [_P, _P, _P, C.c_int, C.c_int]),
     ("cavept_host_alloc", _P, [C.c_size_t]),
     ("cavept_host_free", None, [_P]),
@@ -258,6 +271,34 @@ def write_mesh_file(path: str, mesh) -> None:
     rc = lib.cavept_mesh_file_write(path.encode(), C.byref(cm))
     if rc != 0:
         raise CaveptError(rc, f"cannot write {path}")
+
+
+def group_unique_id() -> bytes:
+    """cavept_group_unique_id: 128 bytes made on rank 0, to be handed to every rank of the group."""
+    lib = load_library()
+    buf = C.create_string_buffer(GROUP_ID_BYTES)
+    rc = lib.cavept_group_unique_id(buf, GROUP_ID_BYTES)
+    if rc != 0:
+        raise CaveptError(rc, "cavept_group_unique_id failed (is NCCL loadable? set CAVEPT_NCCL_LIBRARY)")
+    return buf.raw
+
+
+def group_frame_block(first_frame: int, n_frames: int, rank: int, nranks: int):
+    lib = load_library()
+    f, c = C.c_int(), C.c_int()
+    rc = lib.cavept_group_frame_block(first_frame, n_frames, rank, nranks, C.byref(f), C.byref(c))
+    if rc != 0:
+        raise CaveptError(rc, "cavept_group_frame_block: invalid arguments")
+    return f.value, c.value
+
+
+def group_row_band(height: int, rank: int, nranks: int, align: int = 8):
+    lib = load_library()
+    y, h = C.c_int(), C.c_int()
+    rc = lib.cavept_group_row_band(height, rank, nranks, align, C.byref(y), C.byref(h))
+    if rc != 0:
+        raise CaveptError(rc, "cavept_group_row_band: invalid arguments")
+    return y.value, h.value
 
 
 class PathTracer:
@@ -446,6 +487,37 @@ class PathTracer:
 
     def accum_from_sums(self):
         self._check(self._lib.cavept_accum_from_sums(self._ctx))
+
+    # -- multi-GPU group (include/cavept.h "multi-GPU group") -------------------------------------
+    def group_create(self, rank: int, nranks: int, unique_id: Optional[bytes] = None):
+        buf = C.create_string_buffer(unique_id, GROUP_ID_BYTES) if unique_id is not None else None
+        self._check(self._lib.cavept_group_create(self._ctx, rank, nranks, buf, GROUP_ID_BYTES if buf is not None else 0))
+
+    def group_destroy(self):
+        self._check(self._lib.cavept_group_destroy(self._ctx))
+
+    def group_info(self):
+        r, n, v = C.c_int(), C.c_int(), C.c_int()
+        self._check(self._lib.cavept_group_info(self._ctx, C.byref(r), C.byref(n), C.byref(v)))
+        return {"rank": r.value, "nranks": n.value, "nccl_version": v.value}
+
+    def group_composite(self, dst_rank: int = 0):
+        self._check(self._lib.cavept_group_composite(self._ctx, dst_rank))
+
+    def group_gather_bands(self, align: int = 8):
+        self._check(self._lib.cavept_group_gather_bands(self._ctx, align))
+
+    def read_composite(self, out: Optional[np.ndarray] = None) -> np.ndarray:
+        if out is None:
+            out = np.empty((self.height, self.width, 4), dtype=np.float32)
+        self._check(self._lib.cavept_read_composite(self._ctx, out.ctypes.data, out.nbytes))
+        return out
+
+    def measure_gather(self, working_set_bytes: int, iters: int = 2000) -> float:
+        """cavept_measure_gather: random 32-byte LDG.E.256 lane-gathers per second from a working set of this size."""
+        out = C.c_double()
+        self._check(self._lib.cavept_measure_gather(self._ctx, int(working_set_bytes), int(iters), C.byref(out)))
+        return out.value
 
     def sort_pairs(self, keys: np.ndarray, values: np.ndarray, key_bits: int = 32):
         """Device radix sort of (uint32 key, int32 value) pairs, in place (stable)."""

@@ -8,15 +8,15 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libcavept.so")
-SOURCES = ["kernels.cu", "cavept_api.cu", "scene_ingest.cpp"]
-HEADERS = ["cv_common.h", "bvh_parity_body.h", "bvh_parity_driver.h", "wbvh_body.h", "trace_body.h", "trace_pool_body.h", "host_math.h", "kernels.h", "../../include/cavept.h"]
+SOURCES = ["kernels.cu", "cavept_api.cu", "cavept_group.cu", "scene_ingest.cpp"]
+HEADERS = ["cv_common.h", "bvh_parity_body.h", "bvh_parity_driver.h", "wbvh_body.h", "trace_body.h", "trace_pool_body.h", "host_math.h", "kernels.h", "cavept_ctx.h", "../../include/cavept.h"]
 
 NVCC_FLAGS = [f"-D{d}" for d in os.environ.get("CAVEPT_DEFINES", "").split()] + [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-O3", "-std=c++17", "-lineinfo",
     "-fmad=false",  # float results follow the source's operation order (see cv_common.h)
     "-Xcompiler", "-fPIC,-O2,-ffp-contract=off,-fvisibility=hidden,-Wall,-Wno-unknown-pragmas",
-    "-shared", "-cudart", "static",
+    "-shared", "-cudart", "static", "-ldl",
     "-Xptxas", "-v",
 ]
 

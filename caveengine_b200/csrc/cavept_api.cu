@@ -11,145 +11,10 @@
 #include <string>
 #include <vector>
 
-#include "../../include/cavept.h"
-#include "kernels.h"
+#include "cavept_ctx.h"
 #include "host_math.h"
 
-using namespace cavept;
-
 namespace {
-
-template<class T>
-struct DevBuf {
-    T* ptr = nullptr;
-    size_t cap = 0;  // elements
-    cudaError_t reserve(size_t n) {
-        if (n <= cap) return cudaSuccess;
-        if (ptr) cudaFree(ptr);
-        ptr = nullptr;
-        cap = 0;
-        const size_t want = n + n / 8 + 16;
-        cudaError_t e = cudaMalloc(&ptr, want * sizeof(T));
-        if (e == cudaSuccess) cap = want;
-        return e;
-    }
-    void release() {
-        if (ptr) cudaFree(ptr);
-        ptr = nullptr;
-        cap = 0;
-    }
-};
-
-struct MeshRecord {
-    int built = -1;  // order of first appearance among instances, or -1 if unreferenced
-    int vertex_count = 0, tri_count = 0;
-    int vert_off = 0, tri_off = 0, node_off = 0;
-    int first_material = 0;  // material of the first instance using this mesh (path_tracer.cpp:227-231)
-};
-
-}  // namespace
-
-struct cavept_ctx {
-    cavept_config cfg{};
-    int device = 0;
-    int mode = CAVEPT_MODE_NONE;
-    bool scene_resident = false;
-    bool dirty = true;
-    bool count_visits = false;
-    std::string last_error;
-    CudaExec ex;
-    cudaEvent_t ev0 = nullptr, ev1 = nullptr, ev2 = nullptr;
-
-    // scene bookkeeping
-    std::vector<MeshRecord> meshes;
-    std::vector<int> built_order;  // built index -> input mesh id
-    std::vector<cavept_instance> instances;
-    std::vector<cavept_material> materials;
-    std::vector<GpuPtMesh> gpu_meshes;
-    std::vector<GpuPtMaterial> gpu_materials;
-    int n_verts = 0, n_tris = 0, n_nodes = 0, n_prims = 0, n_pairs = 0, root_ref = 0, fast_levels = 0;
-    bool nodes_resident = false;  // reference-layout GpuPtBvh array built (CAVEPT_BVH_PARITY)
-
-    // reference-layout arrays
-    DevBuf<GpuPtVertex> d_vertices;
-    DevBuf<GpuPtIndex> d_indices;
-    DevBuf<GpuPtBvh> d_nodes;
-    DevBuf<GpuPtMesh> d_meshes;
-    DevBuf<GpuPtMaterial> d_materials;
-    // production layout
-    DevBuf<FastNode> d_fnodes;
-    DevBuf<QPair> d_qpairs;
-    float grid_origin[3] = { 0, 0, 0 }, grid_scale[3] = { 1, 1, 1 };
-    DevBuf<FastTri> d_ftris, d_fnormals;
-    DevBuf<int> d_inst_prim_off, d_inst_tri_off;
-    DevBuf<F4> d_prim_bmin, d_prim_bmax;
-    DevBuf<int> d_w_order, d_w_order_next, d_w_node_of, d_w_node_of_next, d_w_scan, d_w_counters;
-    DevBuf<unsigned char> d_w_flags;
-    DevBuf<WItem> d_w_items, d_w_items_next;
-    DevBuf<WBins> d_w_bins;
-    DevBuf<uint32_t> d_w_root_acc, d_w_keys, d_w_keys_tmp;
-    DevBuf<int> d_w_sort_hist;
-    DevBuf<F4> d_w_nbox_mn, d_w_nbox_mx;
-    // upload staging
-    DevBuf<float> d_raw_pos, d_raw_nrm;
-    DevBuf<uint32_t> d_raw_idx;
-    DevBuf<int> d_tri_off, d_vert_off;
-    // build scratch
-    DevBuf<F4> d_tri_bmin, d_tri_bmax, d_tri_centroid;
-    DevBuf<int> d_order, d_order_next, d_node_of, d_node_of_next, d_scan, d_scan_tmp, d_counters;
-    DevBuf<unsigned char> d_flags;
-    DevBuf<BuildItem> d_items, d_items_next;
-    DevBuf<ItemAccum> d_accum_items;
-    DevBuf<ItemBins> d_bins;
-    DevBuf<int> d_node_parent, d_node_count;
-    // image
-    DevBuf<F4> d_accum, d_tone;
-    DevBuf<unsigned char> d_tone8;
-    DevBuf<unsigned long long> d_stats;
-    DevBuf<int> d_job_counter;   // job queue of the persistent trace kernel (trace_pool_body.h)
-    int kernel_variant = CAVEPT_KERNEL_POOL;
-    int accum_sums = 0;          // group mode: the accumulator holds (sum, n)
-    int n_sms = 0;
-    int pool_blocks_depth = -1, pool_blocks_per_sm = 0;  // occupancy of k_trace_pool, cached per stack depth
-
-    float cam_pos[3] = { 0, 0, 0 }, cam_right[3] = { 1, 0, 0 }, cam_up[3] = { 0, 1, 0 }, cam_fwd[3] = { 0, 0, 1 };
-    float cam_fov = 50.0f;
-
-    cavept_stats stats{};
-    int build_levels = 0;
-};
-
-namespace {
-
-int fail(cavept_ctx* ctx, int code, const char* fmt, ...) {
-    char buf[512];
-    va_list ap;
-    va_start(ap, fmt);
-    vsnprintf(buf, sizeof(buf), fmt, ap);
-    va_end(ap);
-    if (ctx) ctx->last_error = buf;
-    return code;
-}
-
-#define CU(ctx, call)                                                                                   \
-    do {                                                                                                \
-        cudaError_t e_ = (call);                                                                        \
-        if (e_ != cudaSuccess) return fail(ctx, CAVEPT_ERR_CUDA, "%s: %s", #call, cudaGetErrorString(e_)); \
-    } while (0)
-
-int check_exec(cavept_ctx* ctx, const char* where) {
-    if (ctx->ex.first_error != cudaSuccess) {
-        const cudaError_t e = ctx->ex.first_error;
-        ctx->ex.first_error = cudaSuccess;
-        return fail(ctx, CAVEPT_ERR_CUDA, "%s: %s", where, cudaGetErrorString(e));
-    }
-    return CAVEPT_OK;
-}
-
-int select_device(cavept_ctx* ctx) {
-    CU(ctx, cudaSetDevice(ctx->device));
-    return CAVEPT_OK;
-}
 
 // GpuPtMaterial from MaterialComponent, path_tracer.cpp:140-145
 GpuPtMaterial make_gpu_material(const cavept_material& m) {
@@ -426,7 +291,7 @@ CAVEPT_API int cavept_create(const cavept_config* config, cavept_ctx** out_ctx) 
     }
     bool ok = cudaSetDevice(ctx->device) == cudaSuccess;
     ok = ok && cudaStreamCreateWithFlags(&ctx->ex.stream, cudaStreamNonBlocking) == cudaSuccess;
-    ok = ok && cudaEventCreate(&ctx->ev0) == cudaSuccess && cudaEventCreate(&ctx->ev1) == cudaSuccess && cudaEventCreate(&ctx->ev2) == cudaSuccess;
+    ok = ok && cudaEventCreate(&ctx->ev0) == cudaSuccess && cudaEventCreate(&ctx->ev1) == cudaSuccess && cudaEventCreate(&ctx->ev2) == cudaSuccess && cudaEventCreate(&ctx->ev3) == cudaSuccess;
     const size_t n_pixels = (size_t)config->width * config->height;
     ok = ok && ctx->d_accum.reserve(n_pixels) == cudaSuccess && ctx->d_stats.reserve(4) == cudaSuccess && ctx->d_job_counter.reserve(4) == cudaSuccess;
     ok = ok && cudaDeviceGetAttribute(&ctx->n_sms, cudaDevAttrMultiProcessorCount, ctx->device) == cudaSuccess;
@@ -444,6 +309,7 @@ CAVEPT_API int cavept_create(const cavept_config* config, cavept_ctx** out_ctx) 
 CAVEPT_API void cavept_destroy(cavept_ctx* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
+    if (ctx->group) cavept_group_destroy(ctx);
     if (ctx->ex.stream) cudaStreamSynchronize(ctx->ex.stream);
     ctx->d_vertices.release(); ctx->d_indices.release(); ctx->d_nodes.release(); ctx->d_meshes.release(); ctx->d_materials.release();
     ctx->d_fnodes.release(); ctx->d_qpairs.release(); ctx->d_ftris.release(); ctx->d_fnormals.release(); ctx->d_inst_prim_off.release(); ctx->d_inst_tri_off.release();
@@ -461,6 +327,7 @@ CAVEPT_API void cavept_destroy(cavept_ctx* ctx) {
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
     if (ctx->ev2) cudaEventDestroy(ctx->ev2);
+    if (ctx->ev3) cudaEventDestroy(ctx->ev3);
     if (ctx->ex.stream) cudaStreamDestroy(ctx->ex.stream);
     delete ctx;
 }
@@ -736,6 +603,7 @@ CAVEPT_API int cavept_render_tile(cavept_ctx* ctx, int x0, int y0, int w, int h,
 CAVEPT_API int cavept_sync(cavept_ctx* ctx) {
     if (!ctx) return CAVEPT_ERR_INVALID_ARG;
     if (int e = select_device(ctx)) return e;
+    if (ctx->group) return cavept_group_sync(ctx);  // polls the communicator: a failed peer is an error code, not a hang
     CU(ctx, cudaStreamSynchronize(ctx->ex.stream));
     return CAVEPT_OK;
 }
@@ -864,8 +732,20 @@ CAVEPT_API int cavept_probe_intersections(cavept_ctx* ctx, int count, const floa
     launch_probe(ctx->ex, r.ptr, t.ptr, b.ptr, o.ptr, count);
     CU(ctx, cudaMemcpyAsync(out, o.ptr, (size_t)count * 8 * sizeof(float), cudaMemcpyDeviceToHost, ctx->ex.stream));
     CU(ctx, cudaStreamSynchronize(ctx->ex.stream));
-    r.release(); t.release(); b.release(); o.release();
     return check_exec(ctx, "probe_intersections");
+}
+
+CAVEPT_API int cavept_measure_gather(cavept_ctx* ctx, size_t working_set_bytes, int iters, double* out_gathers_per_s) {
+    if (!ctx || !out_gathers_per_s || working_set_bytes < (1u << 20) || working_set_bytes > ((size_t)8 << 30) || iters < 1) return CAVEPT_ERR_INVALID_ARG;
+    if (int e = select_device(ctx)) return e;
+    DevBuf<unsigned char> buf;
+    CU(ctx, buf.reserve(working_set_bytes));
+    CU(ctx, cudaMemsetAsync(buf.ptr, 0, working_set_bytes, ctx->ex.stream));
+    double lane_gathers = 0.0;
+    const float ms = run_gather_probe(ctx->ex, buf.ptr, working_set_bytes, iters, ctx->ev2, ctx->ev3, ctx->n_sms, &lane_gathers);
+    if (int e = check_exec(ctx, "gather probe")) return e;
+    *out_gathers_per_s = ms > 0.0f ? lane_gathers / (ms * 1e-3) : 0.0;
+    return CAVEPT_OK;
 }
 
 CAVEPT_API int cavept_sort_pairs(cavept_ctx* ctx, uint32_t* keys, int32_t* values, int count, int key_bits) {
@@ -880,7 +760,11 @@ CAVEPT_API int cavept_sort_pairs(cavept_ctx* ctx, uint32_t* keys, int32_t* value
     CU(ctx, vt.reserve(count));
     CU(ctx, hist.reserve(2 * sort_hist_entries(count)));
     CU(ctx, tmp.reserve(sort_hist_entries(count) / kScanTile + 4));
-    int* saved = ctx->ex.scan_tmp;
+    struct Restore {  // the context's scan scratch comes back on every return path
+        CudaExec& ex;
+        int* saved;
+        ~Restore() { ex.scan_tmp = saved; }
+    } restore{ ctx->ex, ctx->ex.scan_tmp };
     ctx->ex.scan_tmp = tmp.ptr;
     ctx->ex.upload(k.ptr, keys, (size_t)count * sizeof(uint32_t));
     ctx->ex.upload(v.ptr, values, (size_t)count * sizeof(int));
@@ -888,7 +772,5 @@ CAVEPT_API int cavept_sort_pairs(cavept_ctx* ctx, uint32_t* keys, int32_t* value
     CU(ctx, cudaMemcpyAsync(keys, k.ptr, (size_t)count * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->ex.stream));
     CU(ctx, cudaMemcpyAsync(values, v.ptr, (size_t)count * sizeof(int), cudaMemcpyDeviceToHost, ctx->ex.stream));
     CU(ctx, cudaStreamSynchronize(ctx->ex.stream));
-    ctx->ex.scan_tmp = saved;
-    k.release(); kt.release(); v.release(); vt.release(); hist.release(); tmp.release();
     return check_exec(ctx, "sort_pairs");
 }

@@ -408,6 +408,40 @@ void launch_trace(CudaExec& ex, const TraceParams& p, bool fast, bool count_visi
     ++ex.launches;
 }
 
+// ---- gather probe: the roof the trace kernel is measured against -------------------------------------------
+// Every lane of every warp fetches one random 32-byte record (ONE LDG.E.256, the QPair / FastTri access of
+// walk_step) from a working set of `lines` 128-byte lines, in a dependent chain like a traversal.  With the working
+// set = the scene's node + triangle bytes this is the rate at which this GPU can serve the kernel's gathers from L2
+// (64 KB: from L1).  bench.py calls it untimed, in the same run as the measurement.
+__global__ void __launch_bounds__(128) k_gather_probe(const char* __restrict__ base, unsigned lines, int iters, float* __restrict__ out) {
+    unsigned s = (blockIdx.x * blockDim.x + threadIdx.x) * 2654435761u + 12345u;
+    float acc = 0.0f;
+    for (int i = 0; i < iters; ++i) {
+        s = s * 1664525u + 1013904223u;
+        const unsigned line = (unsigned)(((unsigned long long)(s >> 4) * lines) >> 28);  // uniform in [0, lines)
+        const F8 a = ld256(base + (size_t)line * 128 + ((s & 3u) << 5));
+        acc += a.a + a.h;
+        s += __float_as_uint(acc) & 1u;  // the next address depends on the data: a dependent chain
+    }
+    out[blockIdx.x * blockDim.x + threadIdx.x] = acc;
+}
+float run_gather_probe(CudaExec& ex, const void* base, size_t bytes, int iters, cudaEvent_t e0, cudaEvent_t e1, int n_sms, double* lane_gathers) {
+    const int blocks = n_sms * 8;
+    const unsigned lines = (unsigned)(bytes / 128);
+    float* out = reinterpret_cast<float*>(const_cast<void*>(base));  // results land in the first 600 KB of the working set itself
+    k_gather_probe<<<blocks, 128, 0, ex.stream>>>(reinterpret_cast<const char*>(base), lines, iters / 8 + 1, out);  // warm
+    ex.note(cudaEventRecord(e0, ex.stream));
+    k_gather_probe<<<blocks, 128, 0, ex.stream>>>(reinterpret_cast<const char*>(base), lines, iters, out);
+    ex.note(cudaEventRecord(e1, ex.stream));
+    ex.note(cudaGetLastError());
+    ex.note(cudaEventSynchronize(e1));
+    ex.launches += 2;
+    float ms = 0.0f;
+    ex.note(cudaEventElapsedTime(&ms, e0, e1));
+    *lane_gathers = (double)blocks * 128.0 * (double)iters;
+    return ms;
+}
+
 struct FnProbe {
     const float *rays, *tris, *boxes;
     float* out;

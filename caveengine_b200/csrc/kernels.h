@@ -50,6 +50,8 @@ void launch_trace(CudaExec& ex, const TraceParams& p, bool fast, bool count_visi
 size_t trace_pool_smem_bytes(int stack_entries);
 int trace_pool_blocks_per_sm(int stack_entries, bool count_visits);
 void launch_trace_pool(CudaExec& ex, const TraceParams& p, bool count_visits, int stack_entries, int* job_counter, int grid_blocks);
+// random 32-byte LDG.E.256 gathers over `bytes` of device memory; returns the device time of `iters` gathers per lane
+float run_gather_probe(CudaExec& ex, const void* base, size_t bytes, int iters, cudaEvent_t e0, cudaEvent_t e1, int n_sms, double* lane_gathers);
 void launch_probe(CudaExec& ex, const float* rays, const float* tris, const float* boxes, float* out, int n);
 void launch_tonemap_rgba8(CudaExec& ex, const F4* accum, unsigned char* out, int n_pixels);
 void launch_tonemap_f32(CudaExec& ex, const F4* accum, F4* out, int n_pixels);

@@ -44,6 +44,9 @@ enum : uint32_t { POOL_EMPTY = 0u, POOL_FRESH = 1u, POOL_ACTIVE = 2u, POOL_PENDI
 #ifndef CV_POOL_IDLE_MAX
 #define CV_POOL_IDLE_MAX 6  // shade as soon as this many lanes have nothing left to traverse (both records PENDING)
 #endif
+#ifndef CV_POOL_REFILL_BATCH
+#define CV_POOL_REFILL_BATCH 1  // lanes with a finished pixel that must wait before the warp draws new jobs
+#endif
 #ifndef CV_POOL_TIGHT_STEPS
 #define CV_POOL_TIGHT_STEPS 6
 #endif
@@ -179,16 +182,21 @@ CV_D bool pool_shade_slot(const TraceParams& p, float* rec, int stride, int s) {
     return finished;
 }
 
+// Slot states, two bits per slot in one register (the shade / refill loops index them by slot number).
+CV_HD uint32_t pool_state(uint32_t st, int s) { return (st >> (2 * s)) & 3u; }
+CV_HD uint32_t pool_with_state(uint32_t st, int s, uint32_t v) { return (st & ~(3u << (2 * s))) | (v << (2 * s)); }
+CV_HD bool pool_any_slot(uint32_t st, uint32_t v) { return pool_state(st, 0) == v || pool_state(st, 1) == v; }
+
 // One warp (one lane in the emulator) of the persistent kernel.  `stack` and `rec` point at this thread's column.
-// Returns the number of segments this lane shaded.
+// Returns the number of segments this lane shaded.  Every long code sequence (start_path, walk_begin, the
+// shading) is instantiated ONCE: the body is a single loop whose stages are entered on warp-uniform votes.
 template<bool kCount>
 CV_D unsigned int body_trace_pool(const TraceParams& p, int* stack, float* rec, int stride, int* job_counter, unsigned long long* cnt) {
     const PoolJobs jobs = pool_jobs(p);
     unsigned int segments = 0;
-    uint32_t st0, st1;  // slot states
-    st0 = pool_begin_job(p, jobs, rec, stride, 0, pool_draw_jobs(job_counter, true));
-    st1 = pool_begin_job(p, jobs, rec, stride, 1, pool_draw_jobs(job_counter, true));
+    uint32_t st = 0u;        // both slots EMPTY
     bool queue_open = true;  // warp-uniform: false once a draw came back past the last job
+    bool refill = true;      // warp-uniform: draw jobs for the EMPTY slots at the top of the next trip
     int a = 0;               // the slot whose traversal is in registers
     bool active = false;
     Ray ray;
@@ -199,22 +207,27 @@ CV_D unsigned int body_trace_pool(const TraceParams& p, int* stack, float* rec, 
     Walk w;
     w.stack = stack;
     w.stride = stride;
-    walk_begin(p, w, ray);
+    w.sp = 1;
+    w.top = kRefSentinel;
     w.ref = kRefSentinel;
+    w.q0 = w.q1 = 0;
+    w.inv = w.oinv = f3(0, 0, 0);
+    w.near_x = w.near_y = w.near_z = kSelLo;
+    w.hit_slot = -1;
+    w.hit_u = w.hit_v = 0.0f;
     for (;;) {
-        // ---- activate: a lane without a traversal picks up a FRESH record of its own ----------------
-        {
-            const bool want = !active && (st0 == POOL_FRESH || st1 == POOL_FRESH);
-            if (CV_WARP_ANY(want)) {
-                if (want) {
-                    a = st0 == POOL_FRESH ? 0 : 1;
-                    pool_load_ray(rec, stride, a, ray);
-                    walk_begin(p, w, ray);
-                    if (a == 0) st0 = POOL_ACTIVE; else st1 = POOL_ACTIVE;
-                    active = true;
-                }
+        // ---- refill: EMPTY slots draw the next jobs (pixels finish rarely: once per n_frames samples) -----
+        if (refill && queue_open) {
+#pragma unroll 1
+            for (int s = 0; s < kPoolSlots; ++s) {
+                const bool want = pool_state(st, s) == POOL_EMPTY;
+                if (!CV_WARP_ANY(want)) continue;
+                const int job = pool_draw_jobs(job_counter, want);
+                if (want) st = pool_with_state(st, s, pool_begin_job(p, jobs, rec, stride, s, job));
+                if (CV_WARP_ANY(want && job >= jobs.n_jobs)) queue_open = false;
             }
         }
+        refill = false;
         // ---- A, the tight loop: one ballot per group of steps while a quorum can step ---------------
         for (;;) {
             walk_park_leaf(w);
@@ -227,81 +240,60 @@ CV_D unsigned int body_trace_pool(const TraceParams& p, int* stack, float* rec, 
                 if (ref_is_interior(w.ref)) walk_step<kCount>(p, w, ray.t, cnt);
             }
         }
-        // ---- the vote ---------------------------------------------------------------------------------
-        const bool can_step = ref_is_interior(w.ref);
-        const bool has_tri = w.q0 != 0;
-        const bool fin = active && !can_step && !has_tri;  // traversal complete: file the hit, switch streams
-        if (CV_WARP_ANY(fin)) {
-            if (fin) {
-                CV_REC(6, a) = ray.t;
-                CV_REC(7, a) = u2f((uint32_t)w.hit_slot);
-                CV_REC(8, a) = w.hit_u;
-                CV_REC(9, a) = w.hit_v;
-                if (a == 0) st0 = POOL_PENDING; else st1 = POOL_PENDING;
-                active = false;
-                const uint32_t other = a == 0 ? st1 : st0;
-                if (other == POOL_FRESH) {
-                    a ^= 1;
+        // ---- retire + switch: a completed traversal files its hit as PENDING; a lane without a traversal
+        //      picks up a FRESH record of its own (its other stream, or what the last shading left) ----------
+        {
+            const bool has_tri0 = w.q0 != 0;
+            const bool fin = active && !ref_is_interior(w.ref) && !has_tri0;
+            const bool start = (!active || fin) && (pool_state(st, 0) == POOL_FRESH || pool_state(st, 1) == POOL_FRESH);
+            if (CV_WARP_ANY(fin || start)) {
+                if (fin) {
+                    CV_REC(6, a) = ray.t;
+                    CV_REC(7, a) = u2f((uint32_t)w.hit_slot);
+                    CV_REC(8, a) = w.hit_u;
+                    CV_REC(9, a) = w.hit_v;
+                    st = pool_with_state(st, a, POOL_PENDING);
+                    active = false;
+                    w.ref = kRefSentinel;
+                }
+                if (start) {
+                    a = pool_state(st, 0) == POOL_FRESH ? 0 : 1;
                     pool_load_ray(rec, stride, a, ray);
                     walk_begin(p, w, ray);
-                    if (a == 0) st0 = POOL_ACTIVE; else st1 = POOL_ACTIVE;
+                    st = pool_with_state(st, a, POOL_ACTIVE);
                     active = true;
-                } else {
-                    w.ref = kRefSentinel;
-                    w.hit_slot = -1;
                 }
+                if (CV_WARP_COUNT(ref_is_interior(w.ref)) >= CV_POOL_QUORUM) continue;  // enough lanes are stepping again
             }
-            if (CV_WARP_COUNT(ref_is_interior(w.ref)) >= CV_POOL_QUORUM) continue;  // enough lanes are stepping again
         }
+        // ---- the vote ---------------------------------------------------------------------------------
         const bool step_now = ref_is_interior(w.ref);
-        const bool pending = st0 == POOL_PENDING || st1 == POOL_PENDING;
+        const bool has_tri = w.q0 != 0;
+        const bool pending = pool_any_slot(st, POOL_PENDING);
         const int n_step = CV_WARP_COUNT(step_now);
         const int n_tri = CV_WARP_COUNT(has_tri);
         const int n_pending = CV_WARP_COUNT(pending);
-        const int n_idle = CV_WARP_COUNT(pending && !active);
         if (n_step + n_tri + n_pending == 0) {
-            // nothing in flight: either every job is done or some slots still have to draw one
-            const bool need = queue_open && (st0 == POOL_EMPTY || st1 == POOL_EMPTY);
-            if (!CV_WARP_ANY(need) && !CV_WARP_ANY(st0 == POOL_FRESH || st1 == POOL_FRESH)) break;
-            if (CV_WARP_ANY(need)) {
-                const int j0 = pool_draw_jobs(job_counter, need && st0 == POOL_EMPTY);
-                if (need && st0 == POOL_EMPTY) st0 = pool_begin_job(p, jobs, rec, stride, 0, j0);
-                const int j1 = pool_draw_jobs(job_counter, need && st1 == POOL_EMPTY);
-                if (need && st1 == POOL_EMPTY) st1 = pool_begin_job(p, jobs, rec, stride, 1, j1);
-                if (CV_WARP_ANY((need && (j0 != 0x7fffffff && j0 >= jobs.n_jobs)) || (need && (j1 != 0x7fffffff && j1 >= jobs.n_jobs)))) queue_open = false;
-            }
+            // nothing in flight (a FRESH record would have been started above): draw more jobs, or the launch is done
+            if (!queue_open || !CV_WARP_ANY(pool_any_slot(st, POOL_EMPTY))) break;
+            refill = true;
             continue;
         }
         if (n_tri > 0 && n_tri >= n_step) {
             if (has_tri) walk_test_triangle<kCount>(p, w, ray, ray.t, cnt);
-        } else if (n_pending >= CV_POOL_SHADE_BATCH || n_idle >= CV_POOL_IDLE_MAX || n_step == 0) {
-            // ---- C: shade every PENDING record, slot 0 then slot 1 ------------------------------------
-            bool need0 = false, need1 = false;
-            if (CV_WARP_ANY(st0 == POOL_PENDING)) {
-                if (st0 == POOL_PENDING) {
+        } else if (n_pending >= CV_POOL_SHADE_BATCH || CV_WARP_COUNT(pending && !active) >= CV_POOL_IDLE_MAX || n_step == 0) {
+            // ---- C: shade every PENDING record ------------------------------------------------------------
+#pragma unroll 1
+            for (int s = 0; s < kPoolSlots; ++s) {
+                const bool mine = pool_state(st, s) == POOL_PENDING;
+                if (!CV_WARP_ANY(mine)) continue;
+                if (mine) {
                     ++segments;
-                    need0 = pool_shade_slot(p, rec, stride, 0);
-                    st0 = need0 ? POOL_EMPTY : POOL_FRESH;
+                    st = pool_with_state(st, s, pool_shade_slot(p, rec, stride, s) ? POOL_EMPTY : POOL_FRESH);
                 }
             }
-            if (CV_WARP_ANY(st1 == POOL_PENDING)) {
-                if (st1 == POOL_PENDING) {
-                    ++segments;
-                    need1 = pool_shade_slot(p, rec, stride, 1);
-                    st1 = need1 ? POOL_EMPTY : POOL_FRESH;
-                }
-            }
-            // refill: finished pixels draw the next jobs (padding slots of a ragged rectangle draw again too)
-            if (queue_open) {
-                const bool d0 = st0 == POOL_EMPTY, d1 = st1 == POOL_EMPTY;
-                if (CV_WARP_ANY(d0 || d1)) {
-                    const int j0 = pool_draw_jobs(job_counter, d0);
-                    if (d0) st0 = pool_begin_job(p, jobs, rec, stride, 0, j0);
-                    const int j1 = pool_draw_jobs(job_counter, d1);
-                    if (d1) st1 = pool_begin_job(p, jobs, rec, stride, 1, j1);
-                    if (CV_WARP_ANY((d0 && j0 >= jobs.n_jobs) || (d1 && j1 >= jobs.n_jobs))) queue_open = false;
-                }
-            }
+            // finished pixels (and the padding slots of a ragged rectangle) draw again once enough of them wait
+            refill = CV_WARP_COUNT(pool_any_slot(st, POOL_EMPTY)) >= CV_POOL_REFILL_BATCH;
         } else {
             if (step_now) walk_step<kCount>(p, w, ray.t, cnt);
 #pragma unroll

@@ -39,7 +39,8 @@ enum {
     CAVEPT_ERR_DEGENERATE_GEOMETRY = 2, /* bvh_accel.cpp:117-120 (depth > 64), :138-141 (empty split side) */
     CAVEPT_ERR_CUDA = 3,
     CAVEPT_ERR_NOT_READY = 4, /* render/read before a scene is resident */
-    CAVEPT_ERR_CAPACITY = 5
+    CAVEPT_ERR_CAPACITY = 5,
+    CAVEPT_ERR_NCCL = 6 /* multi-GPU group: NCCL not loadable, a collective failed, or a peer died (cavept_sync polls) */
 };
 
 /* enum class PathTracerMode, cave/engine/renderer/path_tracer_render_system.h:10-14 */
@@ -125,6 +126,9 @@ typedef struct cavept_stats {
     int build_launches;
     int fast_build_levels;
     int fast_build_launches;
+    float last_update_instances_ms; /* device time of the last cavept_update_instances (re-transform + refit, or rebuild) */
+    int last_update_was_refit;      /* 1: the last instance update refitted the tree; 0: it fell back to a rebuild */
+    uint64_t collectives;           /* NCCL collectives enqueued by the multi-GPU group calls */
 } cavept_stats;
 
 /* ---- lifetime; replaces the file-static PathTracer in
@@ -204,6 +208,40 @@ CAVEPT_API void* cavept_accum_device_ptr(cavept_ctx* ctx);  /* float4[width*heig
  * (mean, n) and (sum, n) so ranks can be combined with one sum-reduce of float4. */
 CAVEPT_API int cavept_accum_to_sums(cavept_ctx* ctx);
 CAVEPT_API int cavept_accum_from_sums(cavept_ctx* ctx);
+/* ---- multi-GPU group: the frame compositor (SURVEY.md section 8b "Threading": "multi-GPU group object wraps N ctxs +
+ *      NCCL comm"; section 8e).  New relative to the reference, which runs the pass on one GPU
+ *      (cave/engine/renderer/graphics_manager.cpp:421-428).  One process (or thread) per GPU, each with its own
+ *      context; rank 0 makes an id with cavept_group_unique_id and hands the 128 bytes to the other ranks by whatever
+ *      channel the host application has (the engine's own IPC, a file, MPI ...); every rank then calls
+ *      cavept_group_create (collective).  From then on the context accumulates (sum, n) instead of (mean, n), so a
+ *      frame is composited by ONE ncclReduce / ncclAllReduce of width*height float4 over NVLink, on the context's
+ *      stream, into a separate composite buffer (mean, n) on the destination rank(s); the local sums are untouched
+ *      (progressive accumulation continues, compositing again later is valid).  NCCL is loaded at run time
+ *      (dlopen "libnccl.so.2"; override with $CAVEPT_NCCL_LIBRARY); single-GPU users never load it.
+ *      Errors: CAVEPT_ERR_NCCL; cavept_sync() polls ncclCommGetAsyncError while it waits, aborts the communicator
+ *      and returns CAVEPT_ERR_NCCL if a peer failed, instead of hanging. ------------------------------------ */
+#define CAVEPT_GROUP_ID_BYTES 128
+CAVEPT_API int cavept_group_unique_id(void* out_id, size_t bytes);
+CAVEPT_API int cavept_group_create(cavept_ctx* ctx, int rank, int nranks, const void* unique_id, size_t bytes); /* nranks == 1: no communicator, no NCCL */
+CAVEPT_API int cavept_group_destroy(cavept_ctx* ctx);  /* back to (mean, n) */
+CAVEPT_API int cavept_group_info(const cavept_ctx* ctx, int* rank, int* nranks, int* nccl_version);
+/* Sample split (the default): rank r renders frames cavept_group_frame_block(first, n, r, nranks) of the
+ * full image; then cavept_group_composite(ctx, dst) -- dst = a rank, or -1 for every rank (all-reduce). */
+CAVEPT_API int cavept_group_frame_block(int first_frame, int n_frames, int rank, int nranks, int* out_first, int* out_count);
+CAVEPT_API int cavept_group_composite(cavept_ctx* ctx, int dst_rank);
+CAVEPT_API int cavept_read_composite(cavept_ctx* ctx, float* out_rgba32f, size_t bytes); /* (mean, n), synchronises */
+CAVEPT_API void* cavept_composite_device_ptr(cavept_ctx* ctx);                            /* NULL until this rank holds a composite */
+/* Image-tile split (latency-oriented alternative): rank r renders rows cavept_group_row_band(height, r, nranks, align)
+ * with cavept_render_tile; cavept_group_gather_bands broadcasts every band in place (bit-exact: no arithmetic). */
+CAVEPT_API int cavept_group_row_band(int height, int rank, int nranks, int align, int* out_y0, int* out_rows);
+CAVEPT_API int cavept_group_gather_bands(cavept_ctx* ctx, int align);
+
+/* Roofline probe: the rate (lane-gathers per second) at which this GPU serves random 32-byte LDG.E.256 gathers -- the
+ * node / triangle access of the trace kernel -- from a working set of `working_set_bytes` (the scene's node + triangle
+ * bytes: from L2; 64 KB..1 MB: from L1), `iters` dependent gathers per lane on a full grid.  bench.py reports the
+ * trace kernel's achieved gather rate against this, measured in the same run. */
+CAVEPT_API int cavept_measure_gather(cavept_ctx* ctx, size_t working_set_bytes, int iters, double* out_gathers_per_s);
+
 /* The device radix sort the LBVH builder orders its Morton codes with, on host arrays (copied in,
  * sorted on the device by the low `key_bits` of the keys, copied back): stable, so the result is
  * defined bit for bit.  Exposed so the sort can be checked on its own at full size. */

@@ -148,7 +148,15 @@ def image_metrics(got, want):
 
 
 def check_metrics(m, limits, what):
-    """Every limit is an upper bound except `exact` (a lower bound).  The assert message carries the measured values."""
+    """Every limit is an upper bound except `exact` (a lower bound).  The assert message carries the measured values.
+    With $CAVEPT_PARITY_LOG set, the measured figures are appended to that file (one JSON line per check): this is
+    how the stated bounds were derived (profiles/r02_parity_measured.jsonl)."""
+    log = os.environ.get("CAVEPT_PARITY_LOG")
+    if log:
+        import json
+
+        with open(log, "a") as f:
+            f.write(json.dumps({"case": what, **m, "limits": limits}) + "\n")
     for k, lim in limits.items():
         ok = m[k] >= lim if k == "exact" else m[k] <= lim
         assert ok, f"{what}: {k} = {m[k]:.6g} violates the stated bound {lim:.6g}; measured {m}"

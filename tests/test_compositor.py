@@ -23,6 +23,33 @@ def test_frame_blocks_partition_exactly():
         assert max(counts) - min(counts) <= 1
 
 
+def test_library_partitions_agree_with_the_python_mirrors():
+    """cavept_group_frame_block / cavept_group_row_band (host functions of libcavept.so, no device needed) against
+    compositor.frame_block / row_band."""
+    from caveengine_b200 import api
+    from caveengine_b200 import compositor as cp
+
+    for first, n, world in [(0, 256, 8), (5, 7, 2), (0, 3, 4), (100, 1024, 8), (0, 1, 2), (9, 0, 3)]:
+        for r in range(world):
+            assert api.group_frame_block(first, n, r, world) == cp.frame_block(first, n, r, world)
+    for height, world, align in [(1080, 8, 8), (1080, 2, 8), (2160, 8, 4), (54, 4, 8), (7, 2, 8), (8, 3, 8), (36, 8, 4)]:
+        for r in range(world):
+            assert api.group_row_band(height, r, world, align) == cp.row_band(height, r, world, align)
+    with pytest.raises(api.CaveptError):
+        api.group_frame_block(0, 4, 2, 2)
+
+
+def test_from_sums_handles_empty_pixels_for_numpy_and_torch():
+    import torch
+
+    from caveengine_b200 import compositor as cp
+
+    a = np.array([[[6.0, 3.0, 9.0, 3.0], [5.0, 5.0, 5.0, 0.0]]], dtype=np.float32)
+    want = np.array([[[2.0, 1.0, 3.0, 3.0], [5.0, 5.0, 5.0, 0.0]]], dtype=np.float32)
+    assert np.array_equal(cp.from_sums_(a.copy()), want)
+    assert np.array_equal(cp.from_sums_(torch.from_numpy(a.copy())).numpy(), want)
+
+
 def _free_port():
     s = socket.socket()
     s.bind(("127.0.0.1", 0))

@@ -40,8 +40,9 @@ class TraceMode(enum.IntEnum):
 
 
 class KernelVariant(enum.IntEnum):
-    POOL = 0  # persistent warps + job queue + two pixel streams per lane (default)
+    POOL = 0  # persistent warps + job queue + two pixel streams per lane (experiment; slower)
     PIXEL = 1  # one thread per pixel for the whole launch (round 1's kernel)
+    QUEUE = 2  # persistent warps drawing pixel jobs from a global queue (default)
 
 
 class BvhMode(enum.IntEnum):
@@ -89,6 +90,7 @@ ABI = [
     ("cavept_create", C.c_int, [C.POINTER(_Config), C.POINTER(_P)]),
     ("cavept_destroy", None, [_P]),
     ("cavept_last_error", C.c_char_p, [_P]),
+    ("cavept_get_image_size", C.c_int, [_P, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     ("cavept_set_mode", C.c_int, [_P, C.c_int]),
     ("cavept_is_active", C.c_int, [_P]),
     ("cavept_upload_scene", C.c_int, [_P, C.POINTER(_Mesh), C.c_int, C.POINTER(_Instance), C.c_int, C.POINTER(_Material), C.c_int]),

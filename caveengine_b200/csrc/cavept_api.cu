@@ -334,6 +334,13 @@ CAVEPT_API void cavept_destroy(cavept_ctx* ctx) {
 
 CAVEPT_API const char* cavept_last_error(const cavept_ctx* ctx) { return ctx ? ctx->last_error.c_str() : "null context"; }
 
+CAVEPT_API int cavept_get_image_size(const cavept_ctx* ctx, int* width, int* height) {
+    if (!ctx) return CAVEPT_ERR_INVALID_ARG;
+    if (width) *width = ctx->cfg.width;
+    if (height) *height = ctx->cfg.height;
+    return CAVEPT_OK;
+}
+
 CAVEPT_API int cavept_set_mode(cavept_ctx* ctx, int mode) {
     if (!ctx) return CAVEPT_ERR_INVALID_ARG;
     if (mode != CAVEPT_MODE_NONE && mode != CAVEPT_MODE_INTERACTIVE && mode != CAVEPT_MODE_TILED) {
@@ -584,6 +591,7 @@ static int render_rect(cavept_ctx* ctx, int x0, int y0, int w, int h, int first_
     }
     CU(ctx, cudaEventRecord(ctx->ev0, ctx->ex.stream));
     if (grid_blocks > 0) launch_trace_pool(ctx->ex, p, ctx->count_visits, stack_entries, ctx->d_job_counter.ptr, grid_blocks);
+    else if (fast && ctx->kernel_variant == CAVEPT_KERNEL_QUEUE) launch_trace_queue(ctx->ex, p, ctx->count_visits, ctx->d_job_counter.ptr, ctx->n_sms);
     else launch_trace(ctx->ex, p, fast, ctx->count_visits);
     CU(ctx, cudaEventRecord(ctx->ev1, ctx->ex.stream));
     ctx->dirty = false;
@@ -681,7 +689,7 @@ CAVEPT_API int cavept_set_count_visits(cavept_ctx* ctx, int enable) {
 
 CAVEPT_API int cavept_set_kernel_variant(cavept_ctx* ctx, int variant) {
     if (!ctx) return CAVEPT_ERR_INVALID_ARG;
-    if (variant != CAVEPT_KERNEL_POOL && variant != CAVEPT_KERNEL_PIXEL) return fail(ctx, CAVEPT_ERR_INVALID_ARG, "invalid kernel variant %d", variant);
+    if (variant != CAVEPT_KERNEL_POOL && variant != CAVEPT_KERNEL_PIXEL && variant != CAVEPT_KERNEL_QUEUE) return fail(ctx, CAVEPT_ERR_INVALID_ARG, "invalid kernel variant %d", variant);
     ctx->kernel_variant = variant;
     return CAVEPT_OK;
 }

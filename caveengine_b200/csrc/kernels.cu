@@ -370,6 +370,45 @@ __global__ void __launch_bounds__(128, CV_POOL_BLOCKS) k_trace_pool(const TraceP
     }
 }
 
+// ---- the per-pixel body as a persistent launch with the job queue (CAVEPT_KERNEL_QUEUE): same registers, same
+//      fixed 40-entry stack and 8 blocks per SM as k_trace<fast>; the grid is SMs x 8 blocks whatever the image.
+template<bool kCount>
+__global__ void __launch_bounds__(128, 8) k_trace_queue(const TraceParams p, int* job_counter) {
+    const int lane = threadIdx.x & 31;
+    __shared__ int s_stack[kStackSize * 128];
+    const TraceJobs jobs = trace_jobs(p);
+    const int job = trace_draw_jobs(job_counter, true);
+    int x = p.width, y = 0;  // x == width: no pixel yet (past the last job, or the padding of a ragged rectangle)
+    if (job < jobs.n_jobs) {
+        if (!trace_job_pixel(jobs, job, x, y)) x = p.width;
+    }
+    unsigned long long cnt[3] = { 0ull, 0ull, 0ull };
+    unsigned int segs = body_trace_pixel_fast<kCount, kStepQuorum, kShadeBatch, true>(p, x, y, s_stack + threadIdx.x, 128, cnt, job_counter);
+    segs = __reduce_add_sync(0xffffffffu, segs);
+    if (lane == 0 && segs) atomicAdd(&p.counters[0], (unsigned long long)segs);
+    if (kCount) {
+#pragma unroll
+        for (int k = 1; k < 3; ++k) {
+            unsigned long long v = cnt[k];
+#pragma unroll
+            for (int d = 16; d > 0; d >>= 1) v += __shfl_down_sync(0xffffffffu, v, d);
+            if (lane == 0 && v) atomicAdd(&p.counters[k], v);
+        }
+    }
+}
+
+void launch_trace_queue(CudaExec& ex, const TraceParams& p, bool count_visits, int* job_counter, int n_sms) {
+    const TraceJobs jobs = trace_jobs(p);
+    int blocks = (jobs.n_jobs + 127) / 128;
+    if (blocks > n_sms * 8) blocks = n_sms * 8;
+    if (blocks < 1) blocks = 1;
+    ex.note(cudaMemsetAsync(job_counter, 0, sizeof(int), ex.stream));
+    if (count_visits) k_trace_queue<true><<<blocks, 128, 0, ex.stream>>>(p, job_counter);
+    else k_trace_queue<false><<<blocks, 128, 0, ex.stream>>>(p, job_counter);
+    ex.note(cudaGetLastError());
+    ++ex.launches;
+}
+
 size_t trace_pool_smem_bytes(int stack_entries) { return (size_t)(stack_entries + kPoolWordsPerThread) * 128 * sizeof(int); }
 
 // Resident blocks per SM of k_trace_pool at this stack depth (occupancy query, cached per depth by the caller).

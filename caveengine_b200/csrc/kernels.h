@@ -46,6 +46,8 @@ int run_build_wbvh(CudaExec& ex, WBuild b, WReport* report);
 int run_build_lbvh(CudaExec& ex, WBuild b, WReport* report);
 
 void launch_trace(CudaExec& ex, const TraceParams& p, bool fast, bool count_visits);
+// the per-pixel body as a persistent launch drawing pixel jobs from a global queue (CAVEPT_KERNEL_QUEUE)
+void launch_trace_queue(CudaExec& ex, const TraceParams& p, bool count_visits, int* job_counter, int n_sms);
 // persistent job-queue kernel (trace_pool_body.h); stack_entries = tree levels + 2, grid_blocks = SMs x resident blocks
 size_t trace_pool_smem_bytes(int stack_entries);
 int trace_pool_blocks_per_sm(int stack_entries, bool count_visits);

@@ -563,17 +563,68 @@ CV_D unsigned int body_trace_pixel_reference(const TraceParams& p, int x, int y,
 constexpr int kStepQuorum = CV_STEP_QUORUM;  // of 32 lanes: keep stepping while at least this many can
 constexpr int kShadeBatch = CV_SHADE_BATCH;
 
-template<bool kCount, int kQuorum = kStepQuorum, int kBatch = kShadeBatch>
-CV_D unsigned int body_trace_pixel_fast(const TraceParams& p, int x, int y, int* stack, int stride, unsigned long long* cnt) {
+// ---- job queue of the persistent launch (kQueue): a job = one pixel for all n_frames of the launch, numbered
+//      tile-major (8x4 pixel tiles: the 32 jobs a warp draws together are one coherent tile) and handed out by ONE
+//      warp-aggregated atomicAdd on a global counter.  A lane whose pixel is finished draws the next job instead of
+//      idling until its warp's slowest lane ends, so a launch has no tail however few frames it carries. --------------
+struct TraceJobs {
+    int tiles_x;         // 8x4 tiles across the launch rectangle
+    int n_jobs;          // tiles_x * tiles_y * 32
+    int x0, y0, x1, y1;  // launch rectangle in pixels
+};
+CV_HD TraceJobs trace_jobs(const TraceParams& p) {
+    TraceJobs j;
+    j.x0 = p.tile_x1 > 0 ? p.tile_x0 : 0;
+    j.y0 = p.tile_x1 > 0 ? p.tile_y0 : 0;
+    j.x1 = p.tile_x1 > 0 ? p.tile_x1 : p.width;
+    j.y1 = p.tile_x1 > 0 ? p.tile_y1 : p.height;
+    j.tiles_x = (j.x1 - j.x0 + 7) / 8;
+    const int tiles_y = (j.y1 - j.y0 + 3) / 4;
+    j.n_jobs = p.n_frames > 0 ? j.tiles_x * tiles_y * 32 : 0;
+    return j;
+}
+// job -> pixel; false for the padding of a ragged rectangle
+CV_HD bool trace_job_pixel(const TraceJobs& j, int job, int& x, int& y) {
+    const int tile = job >> 5, in = job & 31;
+    x = j.x0 + (tile % j.tiles_x) * 8 + (in & 7);
+    y = j.y0 + (tile / j.tiles_x) * 4 + (in >> 3);
+    return x < j.x1 && y < j.y1;
+}
+// Warp-aggregated draw: the lanes with `want` get consecutive job numbers (0x7fffffff for the others).
+CV_D int trace_draw_jobs(int* counter, bool want) {
+#if defined(__CUDA_ARCH__)
+    const unsigned m = __ballot_sync(0xffffffffu, want);
+    if (m == 0u) return 0x7fffffff;
+    const int lane = (int)(threadIdx.x & 31u);
+    const int leader = __ffs(m) - 1;
+    int base = 0;
+    if (lane == leader) base = atomicAdd(counter, __popc(m));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    return want ? base + __popc(m & ((1u << lane) - 1u)) : 0x7fffffff;
+#else
+    if (!want) return 0x7fffffff;
+    const int j = *counter;
+    *counter = j + 1;
+    return j;
+#endif
+}
+
+// kQueue = false: the lane owns pixel (x, y) for the whole launch (grid of pixel tiles).
+// kQueue = true:  persistent launch; (x, y) is the lane's first job (x >= width: none yet) and finished pixels are
+//                 replaced from the job queue.
+template<bool kCount, int kQuorum = kStepQuorum, int kBatch = kShadeBatch, bool kQueue = false>
+CV_D unsigned int body_trace_pixel_fast(const TraceParams& p, int x, int y, int* stack, int stride, unsigned long long* cnt, int* job_counter = nullptr) {
     const bool valid = x < p.width && y < p.height && p.n_frames > 0;
-    const size_t pix = valid ? (size_t)y * (size_t)p.width + (size_t)x : 0;
+    size_t pix = valid ? (size_t)y * (size_t)p.width + (size_t)x : 0;
     Ray ray;
     uint32_t seed = 1u;
     int f = 0;
     int bounce = 0;
     unsigned int segments = 0;
     F3 radiance = f3(0.0f, 0.0f, 0.0f), throughput = f3(1.0f, 1.0f, 1.0f);
-    bool done = !valid;
+    bool done = kQueue ? false : !valid;
+    bool vacant = kQueue && !valid;  // kQueue: the lane holds no pixel and draws a job at the next shading phase
+    bool queue_open = kQueue;        // warp-uniform
     Walk w;
     w.stack = stack;
     w.stride = stride;
@@ -614,36 +665,64 @@ CV_D unsigned int body_trace_pixel_fast(const TraceParams& p, int x, int y, int*
                 if (w.q0 != 0) walk_test_triangle<kCount>(p, w, ray, ray.t, cnt);
             }
         } else if (n_shade >= kBatch || n_step == 0) {
+            bool new_sample = false, want_job = false;
             if (need_shade) {
-                ++segments;
-                const bool is_hit = w.hit_slot >= 0;
-                F3 n = f3(0, 0, 0);
-                GpuPtMaterial mat = {};
-                if (is_hit) {
-                    // world-space vertex normals and the material id, pre-gathered at build time
-                    const F8 a = ld256(&p.fnormals[w.hit_slot]);     // n1.xyz, instance, n2.xyz, material
-                    const F8 b = ld256(&p.fnormals[w.hit_slot].v2);  // n3.xyz
-                    const F3 n1 = f3(a.a, a.b, a.c), n2 = f3(a.e, a.f, a.g), n3 = f3(b.a, b.b, b.c);
-                    n = n1 + w.hit_u * (n2 - n1) + w.hit_v * (n3 - n1);
-                    const F8 m = ld256(&p.materials[(int)f2u(a.h)]);
-                    mat.baseColor[0] = m.a; mat.baseColor[1] = m.b; mat.baseColor[2] = m.c; mat.roughness = m.d;
-                    mat.emissive[0] = m.e; mat.emissive[1] = m.f; mat.emissive[2] = m.g; mat.metallic = m.h;
-                }
-                if (shade_hit(p, is_hit, n, mat, ray, seed, radiance, throughput, bounce)) {
-                    F4 acc = p.accum[pix];
-                    accumulate_mode(p.accum_sums, acc, radiance, f == 0 && p.reset_first != 0);
-                    p.accum[pix] = acc;
-                    if (++f == p.n_frames) {
-                        done = true;
-                    } else {
-                        radiance = f3(0.0f, 0.0f, 0.0f);
-                        throughput = f3(1.0f, 1.0f, 1.0f);
-                        bounce = 0;
-                        start_path(p, x, y, p.first_frame + f, ray, seed);
+                if (kQueue && vacant) {
+                    want_job = true;
+                } else {
+                    ++segments;
+                    const bool is_hit = w.hit_slot >= 0;
+                    F3 n = f3(0, 0, 0);
+                    GpuPtMaterial mat = {};
+                    if (is_hit) {
+                        // world-space vertex normals and the material id, pre-gathered at build time
+                        const F8 a = ld256(&p.fnormals[w.hit_slot]);     // n1.xyz, instance, n2.xyz, material
+                        const F8 b = ld256(&p.fnormals[w.hit_slot].v2);  // n3.xyz
+                        const F3 n1 = f3(a.a, a.b, a.c), n2 = f3(a.e, a.f, a.g), n3 = f3(b.a, b.b, b.c);
+                        n = n1 + w.hit_u * (n2 - n1) + w.hit_v * (n3 - n1);
+                        const F8 m = ld256(&p.materials[(int)f2u(a.h)]);
+                        mat.baseColor[0] = m.a; mat.baseColor[1] = m.b; mat.baseColor[2] = m.c; mat.roughness = m.d;
+                        mat.emissive[0] = m.e; mat.emissive[1] = m.f; mat.emissive[2] = m.g; mat.metallic = m.h;
+                    }
+                    if (shade_hit(p, is_hit, n, mat, ray, seed, radiance, throughput, bounce)) {
+                        F4 acc = p.accum[pix];
+                        accumulate_mode(p.accum_sums, acc, radiance, f == 0 && p.reset_first != 0);
+                        p.accum[pix] = acc;
+                        new_sample = true;
+                        if (++f == p.n_frames) {
+                            if (kQueue) want_job = true; else done = true;
+                        }
                     }
                 }
+            }
+            if (kQueue && queue_open) {  // warp-uniform branch: the lanes whose pixel is finished draw the next jobs together
+                if (CV_WARP_ANY(want_job)) {
+                    const TraceJobs jobs = trace_jobs(p);  // recomputed from the launch constants: nothing of it stays live in the hot loop
+                    const int job = trace_draw_jobs(job_counter, want_job);
+                    if (want_job) {
+                        vacant = true;
+                        if (job < jobs.n_jobs && trace_job_pixel(jobs, job, x, y)) {
+                            pix = (size_t)y * (size_t)p.width + (size_t)x;
+                            f = 0;
+                            vacant = false;
+                            new_sample = true;
+                        }
+                    }
+                    if (CV_WARP_ANY(want_job && job >= jobs.n_jobs)) queue_open = false;
+                }
+            }
+            if (kQueue && !queue_open && (want_job || vacant) && need_shade) {
+                if (vacant) done = true;  // the queue is empty: the lane retires
+            }
+            if (need_shade) {
+                if (new_sample && !done && !(kQueue && vacant)) {
+                    radiance = f3(0.0f, 0.0f, 0.0f);
+                    throughput = f3(1.0f, 1.0f, 1.0f);
+                    bounce = 0;
+                    start_path(p, x, y, p.first_frame + f, ray, seed);
+                }
                 walk_begin(p, w, ray);
-                if (done) w.ref = kRefSentinel;
+                if (done || (kQueue && vacant)) w.ref = kRefSentinel;
             }
         } else {
             if (can_step) walk_step<kCount>(p, w, ray.t, cnt);

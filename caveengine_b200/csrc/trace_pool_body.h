@@ -54,49 +54,11 @@ enum : uint32_t { POOL_EMPTY = 0u, POOL_FRESH = 1u, POOL_ACTIVE = 2u, POOL_PENDI
 #define CV_POOL_MINORITY_STEPS 4
 #endif
 
-struct PoolJobs {
-    int tiles_x;     // 8x4 tiles across the launch rectangle
-    int n_jobs;      // tiles_x * tiles_y * 32
-    int x0, y0, x1, y1;  // launch rectangle in pixels
-};
-
-CV_HD PoolJobs pool_jobs(const TraceParams& p) {
-    PoolJobs j;
-    j.x0 = p.tile_x1 > 0 ? p.tile_x0 : 0;
-    j.y0 = p.tile_x1 > 0 ? p.tile_y0 : 0;
-    j.x1 = p.tile_x1 > 0 ? p.tile_x1 : p.width;
-    j.y1 = p.tile_x1 > 0 ? p.tile_y1 : p.height;
-    j.tiles_x = (j.x1 - j.x0 + 7) / 8;
-    const int tiles_y = (j.y1 - j.y0 + 3) / 4;
-    j.n_jobs = p.n_frames > 0 ? j.tiles_x * tiles_y * 32 : 0;
-    return j;
-}
-
-// job -> pixel; returns -1 for the padding of a ragged rectangle
-CV_HD int pool_job_pixel(const TraceParams& p, const PoolJobs& j, int job, int& x, int& y) {
-    const int tile = job >> 5, in = job & 31;
-    x = j.x0 + (tile % j.tiles_x) * 8 + (in & 7);
-    y = j.y0 + (tile / j.tiles_x) * 4 + (in >> 3);
-    return (x < j.x1 && y < j.y1) ? y * p.width + x : -1;
-}
-
-// Warp-aggregated draw from the job counter: the lanes with `want` get consecutive job numbers.
-CV_D int pool_draw_jobs(int* counter, bool want) {
-#if defined(__CUDA_ARCH__)
-    const unsigned m = __ballot_sync(0xffffffffu, want);
-    if (m == 0u) return 0x7fffffff;
-    const int lane = (int)(threadIdx.x & 31u);
-    int base = 0;
-    if (lane == (__ffs(m) - 1)) base = atomicAdd(counter, __popc(m));
-    base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
-    return want ? base + __popc(m & ((1u << lane) - 1u)) : 0x7fffffff;
-#else
-    if (!want) return 0x7fffffff;
-    const int j = *counter;
-    *counter = j + 1;
-    return j;
-#endif
-}
+// the job queue is trace_body.h's (TraceJobs / trace_jobs / trace_job_pixel / trace_draw_jobs)
+using PoolJobs = TraceJobs;
+CV_HD PoolJobs pool_jobs(const TraceParams& p) { return trace_jobs(p); }
+CV_HD int pool_job_pixel(const TraceParams& p, const PoolJobs& j, int job, int& x, int& y) { return trace_job_pixel(j, job, x, y) ? y * p.width + x : -1; }
+CV_D int pool_draw_jobs(int* counter, bool want) { return trace_draw_jobs(counter, want); }
 
 #define CV_REC(field, slot) rec[((field) * kPoolSlots + (slot)) * stride]
 

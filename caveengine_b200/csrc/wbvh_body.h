@@ -117,9 +117,8 @@ CV_HD F3 wb_world(const float* m, const float* v) {
 }
 
 // ---- prim pass ---------------------------------------------------------------------------
-CV_D void wb_prim_box(const WBuild& b, int p, F3& mn, F3& mx) {
-    const int inst = wb_find_instance(b.inst_prim_off, b.n_inst, p);
-    const int tri = b.inst_tri_off[inst] + (p - b.inst_prim_off[inst]);
+// world AABB of (scene-global triangle, instance), unpadded
+CV_D void wb_tri_box(const WBuild& b, int tri, int inst, F3& mn, F3& mx) {
     const float* m = b.instances[inst].transform;
     const int* t = b.indices[tri].tri;
     mn = f3(CV_INF, CV_INF, CV_INF);
@@ -129,6 +128,11 @@ CV_D void wb_prim_box(const WBuild& b, int p, F3& mn, F3& mx) {
         mn = f3(fminf(mn.x, w.x), fminf(mn.y, w.y), fminf(mn.z, w.z));
         mx = f3(fmaxf(mx.x, w.x), fmaxf(mx.y, w.y), fmaxf(mx.z, w.z));
     }
+}
+CV_D void wb_prim_box(const WBuild& b, int p, F3& mn, F3& mx) {
+    const int inst = wb_find_instance(b.inst_prim_off, b.n_inst, p);
+    const int tri = b.inst_tri_off[inst] + (p - b.inst_prim_off[inst]);
+    wb_tri_box(b, tri, inst, mn, mx);
     F4 o;
     o.x = mn.x; o.y = mn.y; o.z = mn.z; o.w = u2f((uint32_t)tri);
     b.bmin[p] = o;
@@ -404,10 +408,13 @@ CV_D void wb_body_scatter(const WBuild& b, int i) {
 // World-space vertices (the same wb_world() values the boxes were built from) and the vertex
 // normals times the world matrix.  A mirroring instance (det < 0) flips the winding the reference's mesh-space
 // back-face test sees (shared_path_tracer.h:106), so its triangles are stored as (A, C, B).
+CV_D void wb_emit_slot(const WBuild& b, int s, uint32_t tri, uint32_t inst);
 CV_D void wb_body_emit(const WBuild& b, int s) {
     if (s >= b.n_prims) return;
     const int p = b.order[s];
-    const uint32_t tri = f2u(b.bmin[p].w), inst = f2u(b.bmax[p].w);
+    wb_emit_slot(b, s, f2u(b.bmin[p].w), f2u(b.bmax[p].w));
+}
+CV_D void wb_emit_slot(const WBuild& b, int s, uint32_t tri, uint32_t inst) {
     const float* m = b.instances[inst].transform;
     const float det = m[0] * (m[5] * m[10] - m[9] * m[6]) - m[4] * (m[1] * m[10] - m[9] * m[2]) + m[8] * (m[1] * m[6] - m[5] * m[2]);
     const int* idx = b.indices[tri].tri;
@@ -460,6 +467,79 @@ CV_D void wb_body_quantise(const WBuild& b, int k, int n_pairs) {
         if (s == 0) o.r0 = wb_quantised_ref(n.a); else o.r1 = wb_quantised_ref(n.a);
     }
     b.qpairs[k] = o;
+}
+
+// ---- refit: instance transforms changed, topology kept ---------------------------
+// The reference re-uploads M x 144 bytes of GpuPtMesh on SCENE_DIRTY_WORLD and never touches a BVH
+// (cave/engine/renderer/path_tracer/path_tracer.cpp:162-199): its per-mesh trees live in mesh space.  The production
+// tree is in world space, so a moved instance's triangles are re-transformed in their slots (same arithmetic as
+// wb_body_emit) and every box is recomputed bottom-up, one launch per level: the SAH builder allocates the sibling
+// pairs of level L+1 in one contiguous range after those of level L, so "all pairs of a level" is an index range.
+// A leaf's box is the union of its triangles' padded world boxes, an interior record's the union of its child pair
+// -- exactly what the builder's bins produced, so refitting an unmoved scene reproduces the tree bit for bit.
+// The host keeps the result only if the moved scene still fits the quantisation grid and the tree's surface-area
+// sum (the SAH cost proxy) stayed within a factor of the freshly built tree's; otherwise it rebuilds.
+CV_D void wb_body_retransform(const WBuild& b, int s, const unsigned char* moved) {
+    if (s >= b.n_prims) return;
+    const uint32_t inst = f2u(b.ftris[s].v0.w);
+    if (!moved[inst]) return;
+    wb_emit_slot(b, s, f2u(b.ftris[s].v1.w), inst);
+}
+
+CV_D void wb_body_refit_pair(const WBuild& b, int k, float* area_sum) {
+    QPair q;
+    float area = 0.0f;
+    for (int s = 0; s < 2; ++s) {
+        FastNode n = b.fnodes[2 * k + s];
+        WBox box = wb_empty();
+        if (ref_is_interior(n.a)) {
+            const FastNode c0 = b.fnodes[n.a], c1 = b.fnodes[n.a + 1];  // the child pair's two records (refitted by the previous, deeper launch)
+            wb_grow(box, f3(c0.mn[0], c0.mn[1], c0.mn[2]), f3(c0.mx[0], c0.mx[1], c0.mx[2]));
+            wb_grow(box, f3(c1.mn[0], c1.mn[1], c1.mn[2]), f3(c1.mx[0], c1.mx[1], c1.mx[2]));
+        } else {
+            const int first = n.a & 0x1fffffff, count = ((n.a >> 29) & 3) + 1;
+            for (int t = 0; t < count; ++t) {
+                const FastTri& tri = b.ftris[first + t];
+                F3 mn, mx;
+                wb_tri_box(b, (int)f2u(tri.v1.w), (int)f2u(tri.v0.w), mn, mx);
+                wb_grow(box, f3(mn.x - b.pad, mn.y - b.pad, mn.z - b.pad), f3(mx.x + b.pad, mx.y + b.pad, mx.z + b.pad));
+            }
+        }
+        n.mn[0] = box.mn.x; n.mn[1] = box.mn.y; n.mn[2] = box.mn.z;
+        n.mx[0] = box.mx.x; n.mx[1] = box.mx.y; n.mx[2] = box.mx.z;
+        b.fnodes[2 * k + s] = n;
+        area += wb_half_area(box);
+        for (int c = 0; c < 3; ++c) q.q[3 * s + c] = wb_grid_lo(n.mn[c], b.grid_origin[c], b.grid_scale[c]) | (wb_grid_hi(n.mx[c], b.grid_origin[c], b.grid_scale[c]) << 16);
+        if (s == 0) q.r0 = wb_quantised_ref(n.a); else q.r1 = wb_quantised_ref(n.a);
+    }
+    b.qpairs[k] = q;
+    if (area_sum) {
+#if defined(__CUDA_ARCH__)
+        const float total = __reduce_add_sync(__activemask(), 0) == 0 ? area : area;  // (no float redux: one atomic per lane; refit is launch-bound)
+        atomicAdd(area_sum, total);
+#else
+        *area_sum += area;
+#endif
+    }
+}
+
+struct FnWbRetransform { WBuild b; const unsigned char* moved; CV_D void operator()(int i) const { wb_body_retransform(b, i, moved); } };
+struct FnWbRefitPair { WBuild b; int first; float* area_sum; CV_D void operator()(int i) const { wb_body_refit_pair(b, first + i, area_sum); } };
+
+// level_start[L] .. level_start[L+1] = pairs owned by the interior nodes of level L (level_start has n_levels + 1 entries).
+// out[0..5] = refitted scene box (union of the root pair), out[6] = surface-area sum of all records.
+template<class Exec>
+void refit_wbvh(Exec& ex, WBuild b, const int* level_start, int n_levels, const unsigned char* d_moved, float* d_area_sum, float out[7]) {
+    ex.fill(d_area_sum, 0, sizeof(float));
+    ex.launch(b.n_prims, FnWbRetransform{ b, d_moved });
+    for (int L = n_levels - 1; L >= 0; --L) ex.launch(level_start[L + 1] - level_start[L], FnWbRefitPair{ b, level_start[L], d_area_sum });
+    FastNode root[2];
+    ex.download(root, b.fnodes, sizeof(root));
+    for (int c = 0; c < 3; ++c) {
+        out[c] = root[0].mn[c] < root[1].mn[c] ? root[0].mn[c] : root[1].mn[c];
+        out[3 + c] = root[0].mx[c] > root[1].mx[c] ? root[0].mx[c] : root[1].mx[c];
+    }
+    ex.download(&out[6], d_area_sum, sizeof(float));
 }
 
 // ---- LBVH builder: Morton codes + radix sort + binary radix tree + bottom-up AABB reduction ------
@@ -748,6 +828,7 @@ struct WReport {
     float scene_mn[3], scene_mx[3];
     float pad;
     float grid_origin[3], grid_scale[3];
+    int level_items[kWMaxLevels + 4];  // SAH builder: interior nodes (= sibling pairs owned) per level; the refit walks these ranges
 };
 
 // Common first part of both production builders: world AABB of every prim, scene and centroid
@@ -848,7 +929,10 @@ int build_wbvh(Exec& ex, WBuild b, WReport* rep) {
     }
     rep->n_pairs = counters[1];
     rep->levels = 0;
-    while (counters[kWLevelBase + rep->levels] > 0) ++rep->levels;
+    while (counters[kWLevelBase + rep->levels] > 0) {
+        rep->level_items[rep->levels] = counters[kWLevelBase + rep->levels];
+        ++rep->levels;
+    }
     ex.launch(b.n_prims, FnWbEmit{ b });
     ex.launch(rep->n_pairs, FnWbQuantise{ b, rep->n_pairs });
     return 0;

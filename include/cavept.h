@@ -67,11 +67,14 @@ enum { CAVEPT_TRACE_FAST = 0, CAVEPT_TRACE_REFERENCE_WALK = 1 };
  * geometry that changes every frame (BASELINE config 5). */
 enum { CAVEPT_BVH_PARITY = 0, CAVEPT_BVH_FAST = 1, CAVEPT_BVH_LBVH = 2 };
 
-/* Which production kernel CAVEPT_TRACE_FAST launches (same tree, same per-pixel arithmetic, bit-identical images):
- * POOL  (default): persistent warps drawing pixel jobs from a global queue, two pixel streams per lane with the
- *        inactive one parked in shared memory (csrc/trace_pool_body.h);
- * PIXEL: one thread per pixel for the whole launch (csrc/trace_body.h body_trace_pixel_fast), round 1's kernel. */
-enum { CAVEPT_KERNEL_POOL = 0, CAVEPT_KERNEL_PIXEL = 1 };
+/* Which production kernel CAVEPT_TRACE_FAST launches.  Same tree, same per-pixel arithmetic in the same per-pixel order:
+ * the three produce bit-identical images (tests/test_gpu_parity.py).
+ * QUEUE (default): persistent warps; a lane owns one pixel at a time for all frames of the launch and draws the next
+ *        pixel from a global job queue when it is done (no launch tail);  csrc/trace_body.h body_trace_pixel_fast<kQueue>.
+ * PIXEL: one thread per pixel for the whole launch on a grid of pixel tiles (round 1's kernel).
+ * POOL:  persistent warps, job queue, TWO pixel streams per lane with the inactive one parked in shared memory
+ *        (csrc/trace_pool_body.h) -- measured slower on B200, kept selectable as the experiment it is. */
+enum { CAVEPT_KERNEL_POOL = 0, CAVEPT_KERNEL_PIXEL = 1, CAVEPT_KERNEL_QUEUE = 2 };
 
 typedef struct cavept_config {
     int device;     /* CUDA ordinal; -1 = current device */
@@ -136,6 +139,7 @@ typedef struct cavept_stats {
 CAVEPT_API int cavept_create(const cavept_config* config, cavept_ctx** out_ctx);
 CAVEPT_API void cavept_destroy(cavept_ctx* ctx);
 CAVEPT_API const char* cavept_last_error(const cavept_ctx* ctx);
+CAVEPT_API int cavept_get_image_size(const cavept_ctx* ctx, int* width, int* height); /* either may be NULL */
 
 /* ---- SetPathTracerMode / IsPathTracerActive,
  *      path_tracer_render_system.h:17-18, path_tracer.cpp:312-322 ---------------- */

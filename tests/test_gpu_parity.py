@@ -529,17 +529,17 @@ def test_high_spp_image_matches_oracle_at_equal_seeds(api, port_oracle, scene_ca
     H.check_metrics(H.image_metrics(got, want), HIGH_SPP_LIMITS[name], f"high_spp_{name}")
 
 
-# ---- the two production kernels (include/cavept.h CAVEPT_KERNEL_*) -----------------------------------
+# ---- the production kernel variants (include/cavept.h CAVEPT_KERNEL_*) ----------------------------------------
 @pytest.mark.parametrize("name,w,h,mb,frames", [("sponza", 640, 360, 8, 4), ("tiny", 101, 57, 5, 6)])
-def test_pool_kernel_equals_pixel_kernel_bitwise(api, scene_cache, name, w, h, mb, frames):
-    """CAVEPT_KERNEL_POOL (persistent warps, job queue, two pixel streams per lane) and CAVEPT_KERNEL_PIXEL (one
-    thread per pixel) run the same per-pixel arithmetic in the same per-pixel order: identical accumulator bytes and
-    segment counts, over two launches and on a ragged image.  (Node visits may differ by a fraction of a percent: how
-    many speculative steps a lane takes before its parked triangles are tested depends on its warp's votes; the closest
-    hit does not.)"""
+def test_kernel_variants_are_bitwise_identical(api, scene_cache, name, w, h, mb, frames):
+    """CAVEPT_KERNEL_QUEUE (persistent warps + job queue, the default), CAVEPT_KERNEL_PIXEL (one thread per pixel on a
+    grid of tiles) and CAVEPT_KERNEL_POOL (job queue + two pixel streams per lane) run the same per-pixel arithmetic in
+    the same per-pixel order: identical accumulator bytes and segment counts, over two launches and on a ragged image.
+    (Node visits may differ by a fraction of a percent: how many speculative steps a lane takes before its parked
+    triangles are tested depends on its warp's votes; the closest hit does not.)"""
     sc = scene_cache(name)
     out = {}
-    for variant in (api.KernelVariant.POOL, api.KernelVariant.PIXEL):
+    for variant in (api.KernelVariant.QUEUE, api.KernelVariant.PIXEL, api.KernelVariant.POOL):
         with _tracer(api, sc, w, h, mb, api.TraceMode.FAST) as pt:
             pt.set_kernel_variant(variant)
             pt.set_count_visits(True)
@@ -548,8 +548,28 @@ def test_pool_kernel_equals_pixel_kernel_bitwise(api, scene_cache, name, w, h, m
             pt.render(frames, 2, sync=True)
             st = pt.stats()
             out[variant] = (pt.read_accum(), st["segments"], st["node_visits"], st["triangle_tests"])
-    a, b = out[api.KernelVariant.POOL], out[api.KernelVariant.PIXEL]
-    assert a[1] == b[1]
-    assert abs(a[2] - b[2]) <= b[2] // 50 and abs(a[3] - b[3]) <= b[3] // 50
-    assert a[0].tobytes() == b[0].tobytes()
-    assert np.all(a[0][..., 3] == float(frames + 2))
+    b = out[api.KernelVariant.PIXEL]
+    for variant in (api.KernelVariant.QUEUE, api.KernelVariant.POOL):
+        a = out[variant]
+        assert a[1] == b[1], variant
+        assert abs(a[2] - b[2]) <= b[2] // 50 and abs(a[3] - b[3]) <= b[3] // 50, (variant, a[1:], b[1:])
+        differ = int((a[0] != b[0]).any(axis=-1).sum())
+        assert differ == 0, f"{variant.name}: {differ} pixels differ from the per-pixel kernel"
+    assert np.all(b[0][..., 3] == float(frames + 2))
+
+
+def test_queue_kernel_tiles_and_single_frame_launches(api, scene_cache):
+    """The job queue over a ragged rectangle (padding jobs are skipped) and with one frame per launch (every sample
+    end is a job end): same bytes as the per-pixel kernel."""
+    sc = scene_cache("tiny")
+    w, h, mb = 77, 45, 5
+    imgs = []
+    for variant in (api.KernelVariant.QUEUE, api.KernelVariant.PIXEL):
+        with _tracer(api, sc, w, h, mb, api.TraceMode.FAST) as pt:
+            pt.set_kernel_variant(variant)
+            pt.set_mode(api.PathTracerMode.TILED)
+            for f in range(3):
+                pt.render_tile(5, 3, 61, 38, f, 1)
+            pt.render_tile(0, 0, w, h, 3, 2, sync=True)
+            imgs.append(pt.read_accum())
+    assert imgs[0].tobytes() == imgs[1].tobytes()

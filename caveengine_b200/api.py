@@ -96,6 +96,7 @@ ABI = [
     ("cavept_upload_scene", C.c_int, [_P, C.POINTER(_Mesh), C.c_int, C.POINTER(_Instance), C.c_int, C.POINTER(_Material), C.c_int]),
     ("cavept_update_instances", C.c_int, [_P, C.POINTER(_Instance), C.c_int]),
     ("cavept_update_materials", C.c_int, [_P, C.POINTER(_Material), C.c_int]),
+    ("cavept_set_refit", C.c_int, [_P, C.c_int]),
     ("cavept_rebuild_mesh", C.c_int, [_P, C.c_int, _P, _P]),
     ("cavept_get_mesh_bvh", C.c_int, [_P, C.c_int, _P, C.c_int]),
     ("cavept_get_scene_counts", C.c_int, [_P] + [C.POINTER(C.c_int)] * 5),
@@ -108,6 +109,9 @@ ABI = [
     ("cavept_read_accum", C.c_int, [_P, _P, C.c_size_t]),
     ("cavept_read_tonemapped_rgba8", C.c_int, [_P, _P, C.c_size_t]),
     ("cavept_read_tonemapped_rgba32f", C.c_int, [_P, _P, C.c_size_t]),
+    ("cavept_read_tonemapped_rgba16f", C.c_int, [_P, _P, C.c_size_t]),
+    ("cavept_write_ppm", C.c_int, [_P, C.c_char_p]),
+    ("cavept_last_render_ms", C.c_int, [_P, C.POINTER(C.c_float)]),
     ("cavept_write_accum", C.c_int, [_P, _P, C.c_size_t]),
     ("cavept_get_stats", C.c_int, [_P, C.POINTER(Stats)]),
     ("cavept_reset_stats", C.c_int, [_P]),
@@ -393,6 +397,9 @@ class PathTracer:
     def update_instances(self, instances):
         self._check(self._lib.cavept_update_instances(self._ctx, self._instances(instances), len(instances)))
 
+    def set_refit(self, enable: bool):
+        self._check(self._lib.cavept_set_refit(self._ctx, 1 if enable else 0))
+
     def update_materials(self, materials):
         self._check(self._lib.cavept_update_materials(self._ctx, self._materials(materials), len(materials)))
 
@@ -455,6 +462,24 @@ class PathTracer:
         out = np.empty((self.height, self.width, 4), dtype=np.uint8)
         self._check(self._lib.cavept_read_tonemapped_rgba8(self._ctx, out.ctypes.data, out.nbytes))
         return out
+
+    def read_tonemapped_rgba16f(self) -> np.ndarray:
+        """RT_FMT_TONE (R16G16B16A16_FLOAT): (H, W, 4) float16."""
+        out = np.empty((self.height, self.width, 4), dtype=np.float16)
+        self._check(self._lib.cavept_read_tonemapped_rgba16f(self._ctx, out.ctypes.data, out.nbytes))
+        return out
+
+    def write_ppm(self, path: str):
+        self._check(self._lib.cavept_write_ppm(self._ctx, path.encode()))
+
+    def last_render_ms(self) -> Optional[float]:
+        """Non-blocking: None while the last launch is still running."""
+        ms = C.c_float()
+        rc = self._lib.cavept_last_render_ms(self._ctx, C.byref(ms))
+        if rc == ERR_NOT_READY:
+            return None
+        self._check(rc)
+        return ms.value
 
     def read_tonemapped(self) -> np.ndarray:
         out = np.empty((self.height, self.width, 4), dtype=np.float32)

@@ -170,7 +170,61 @@ int build_world(cavept_ctx* ctx) {
     }
     ctx->fast_levels = rep.levels;
     ctx->stats.fast_node_count = 2 * rep.n_pairs;
+    // what a later refit needs (SAH builder: the pairs of a level are one index range)
+    ctx->refit_ready = !lbvh && rep.levels > 0;
+    ctx->level_start.assign(1, 0);
+    for (int L = 0; L < rep.levels && !lbvh; ++L) ctx->level_start.push_back(ctx->level_start.back() + rep.level_items[L]);
+    ctx->world_pad = rep.pad;
+    ctx->world_extent = rep.pad * 1048576.0f;
+    ctx->area_baseline = -1.0f;
     return CAVEPT_OK;
+}
+
+// Instance transforms changed, topology kept: re-transform the moved instances' triangle slots and recompute every
+// box bottom-up (wbvh_body.h refit_wbvh).  Returns 1 when the refitted tree is kept, 0 when the caller must rebuild
+// (scene left the quantisation grid / the padding's scale, or the tree's surface-area sum grew past kRefitQuality),
+// < 0 on error.
+constexpr float kRefitQuality = 1.3f;
+int refit_world(cavept_ctx* ctx, const std::vector<unsigned char>& moved) {
+    if (!ctx->refit_ready || ctx->n_pairs <= 0) return 0;
+    const int n_inst = (int)ctx->instances.size();
+    if (cudaSuccess != ctx->d_moved.reserve(n_inst) || cudaSuccess != ctx->d_area_sum.reserve(1)) return -fail(ctx, CAVEPT_ERR_CUDA, "refit scratch");
+    WBuild b{};
+    b.vertices = ctx->d_vertices.ptr;
+    b.indices = ctx->d_indices.ptr;
+    b.instances = ctx->d_meshes.ptr;
+    b.n_inst = n_inst;
+    b.n_prims = ctx->n_prims;
+    b.pad = ctx->world_pad;
+    b.fnodes = ctx->d_fnodes.ptr;
+    b.qpairs = ctx->d_qpairs.ptr;
+    b.ftris = ctx->d_ftris.ptr;
+    b.fnormals = ctx->d_fnormals.ptr;
+    for (int k = 0; k < 3; ++k) {
+        b.grid_origin[k] = ctx->grid_origin[k];
+        b.grid_scale[k] = ctx->grid_scale[k];
+    }
+    const int n_levels = (int)ctx->level_start.size() - 1;
+    float out[7];
+    if (ctx->area_baseline < 0.0f) {  // first update after a build: the built tree's own surface-area sum (nothing moved: the pass reproduces the tree)
+        ctx->ex.fill(ctx->d_moved.ptr, 0, (size_t)n_inst);
+        run_refit_wbvh(ctx->ex, b, ctx->level_start.data(), n_levels, ctx->d_moved.ptr, ctx->d_area_sum.ptr, out);
+        ctx->area_baseline = out[6];
+    }
+    ctx->ex.upload(ctx->d_moved.ptr, moved.data(), (size_t)n_inst);
+    run_refit_wbvh(ctx->ex, b, ctx->level_start.data(), n_levels, ctx->d_moved.ptr, ctx->d_area_sum.ptr, out);
+    if (check_exec(ctx, "world bvh refit")) return -CAVEPT_ERR_CUDA;
+    float extent = 0.0f;
+    bool inside = true;
+    for (int c = 0; c < 3; ++c) {
+        const float lo = out[c], hi = out[3 + c];
+        extent = std::fmax(extent, std::fmax(std::fabs(lo), std::fabs(hi)));
+        const float g_lo = (lo - ctx->grid_origin[c]) * ctx->grid_scale[c], g_hi = (hi - ctx->grid_origin[c]) * ctx->grid_scale[c];
+        if (!(g_lo >= 1.0f && g_hi <= kGridCells - 1.0f)) inside = false;  // outward rounding must not meet the clamp at 0 / 32767
+    }
+    if (!inside || extent > ctx->world_extent * 1.0000001f + 1e-30f) return 0;  // the padding was derived from the old extent
+    if (!(out[6] <= kRefitQuality * ctx->area_baseline)) return 0;
+    return 1;
 }
 
 int build_all(cavept_ctx* ctx) {
@@ -357,6 +411,7 @@ CAVEPT_API int cavept_is_active(const cavept_ctx* ctx) {
 
 CAVEPT_API int cavept_upload_scene(cavept_ctx* ctx, const cavept_mesh* meshes, int mesh_count, const cavept_instance* instances, int instance_count,
                                    const cavept_material* materials, int material_count) {
+    CAVEPT_RANGE();
     if (!ctx) return CAVEPT_ERR_INVALID_ARG;
     if (!meshes || !instances || !materials || mesh_count <= 0 || instance_count <= 0 || material_count <= 0) {
         return fail(ctx, CAVEPT_ERR_INVALID_ARG, "upload_scene: null or empty input");
@@ -425,6 +480,7 @@ CAVEPT_API int cavept_upload_scene(cavept_ctx* ctx, const cavept_mesh* meshes, i
 }
 
 CAVEPT_API int cavept_update_instances(cavept_ctx* ctx, const cavept_instance* instances, int instance_count) {
+    CAVEPT_RANGE();
     if (!ctx || !instances) return CAVEPT_ERR_INVALID_ARG;
     if (!ctx->scene_resident) return fail(ctx, CAVEPT_ERR_NOT_READY, "no scene resident");
     if (instance_count != (int)ctx->instances.size()) return fail(ctx, CAVEPT_ERR_INVALID_ARG, "instance count changed (%d != %zu): re-upload the scene", instance_count, ctx->instances.size());
@@ -432,14 +488,37 @@ CAVEPT_API int cavept_update_instances(cavept_ctx* ctx, const cavept_instance* i
         if (instances[i].mesh != ctx->instances[i].mesh) return fail(ctx, CAVEPT_ERR_INVALID_ARG, "instance %d changed mesh: re-upload the scene", i);
     }
     if (int e = select_device(ctx)) return e;
-    for (int i = 0; i < instance_count; ++i) std::memcpy(ctx->instances[i].transform, instances[i].transform, sizeof(float) * 16);
+    std::vector<unsigned char> moved(instance_count, 0);
+    int n_moved = 0;
+    for (int i = 0; i < instance_count; ++i) {
+        if (std::memcmp(ctx->instances[i].transform, instances[i].transform, sizeof(float) * 16) != 0) {
+            moved[i] = 1;
+            ++n_moved;
+            std::memcpy(ctx->instances[i].transform, instances[i].transform, sizeof(float) * 16);
+        }
+    }
+    ctx->dirty = true;  // SCENE_DIRTY_WORLD: the reference re-uploads M x 144 bytes and restarts the accumulation (path_tracer.cpp:162-199)
+    ctx->stats.last_update_instances_ms = 0.0f;
+    ctx->stats.last_update_was_refit = 1;
+    if (n_moved == 0) return CAVEPT_OK;
+    CU(ctx, cudaEventRecord(ctx->ev2, ctx->ex.stream));
     if (int e = rebuild_instance_arrays(ctx)) return e;
-    if (int e = build_world(ctx)) return e;
-    ctx->dirty = true;  // SCENE_DIRTY_WORLD
+    int kept = ctx->refit_enabled ? refit_world(ctx, moved) : 0;
+    if (kept < 0) return -kept;
+    if (kept == 0) {
+        if (int e = build_world(ctx)) return e;
+    }
+    CU(ctx, cudaEventRecord(ctx->ev3, ctx->ex.stream));
+    CU(ctx, cudaEventSynchronize(ctx->ev3));
+    float ms = 0.0f;
+    CU(ctx, cudaEventElapsedTime(&ms, ctx->ev2, ctx->ev3));
+    ctx->stats.last_update_instances_ms = ms;
+    ctx->stats.last_update_was_refit = kept;
     return CAVEPT_OK;
 }
 
 CAVEPT_API int cavept_update_materials(cavept_ctx* ctx, const cavept_material* materials, int material_count) {
+    CAVEPT_RANGE();
     if (!ctx || !materials) return CAVEPT_ERR_INVALID_ARG;
     if (!ctx->scene_resident) return fail(ctx, CAVEPT_ERR_NOT_READY, "no scene resident");
     if (material_count != (int)ctx->materials.size()) return fail(ctx, CAVEPT_ERR_INVALID_ARG, "material count changed");
@@ -451,6 +530,7 @@ CAVEPT_API int cavept_update_materials(cavept_ctx* ctx, const cavept_material* m
 }
 
 CAVEPT_API int cavept_rebuild_mesh(cavept_ctx* ctx, int mesh, const float* positions, const float* normals) {
+    CAVEPT_RANGE();
     if (!ctx || !positions) return CAVEPT_ERR_INVALID_ARG;
     if (!ctx->scene_resident) return fail(ctx, CAVEPT_ERR_NOT_READY, "no scene resident");
     if (mesh < 0 || mesh >= (int)ctx->meshes.size() || ctx->meshes[mesh].built < 0) return fail(ctx, CAVEPT_ERR_INVALID_ARG, "mesh %d is not resident", mesh);
@@ -598,9 +678,13 @@ static int render_rect(cavept_ctx* ctx, int x0, int y0, int w, int h, int first_
     return check_exec(ctx, "render launch");
 }
 
-CAVEPT_API int cavept_render(cavept_ctx* ctx, int first_frame_index, int n_frames) { return render_rect(ctx, 0, 0, 0, 0, first_frame_index, n_frames); }
+CAVEPT_API int cavept_render(cavept_ctx* ctx, int first_frame_index, int n_frames) {
+    CAVEPT_RANGE();
+    return render_rect(ctx, 0, 0, 0, 0, first_frame_index, n_frames);
+}
 
 CAVEPT_API int cavept_render_tile(cavept_ctx* ctx, int x0, int y0, int w, int h, int first_frame_index, int n_frames) {
+    CAVEPT_RANGE();
     if (!ctx) return CAVEPT_ERR_INVALID_ARG;
     if (x0 < 0 || y0 < 0 || w <= 0 || h <= 0 || x0 > ctx->cfg.width - w || y0 > ctx->cfg.height - h) {
         return fail(ctx, CAVEPT_ERR_INVALID_ARG, "tile (%d,%d)+(%d,%d) is not inside the %dx%d image", x0, y0, w, h, ctx->cfg.width, ctx->cfg.height);
@@ -609,6 +693,7 @@ CAVEPT_API int cavept_render_tile(cavept_ctx* ctx, int x0, int y0, int w, int h,
 }
 
 CAVEPT_API int cavept_sync(cavept_ctx* ctx) {
+    CAVEPT_RANGE();
     if (!ctx) return CAVEPT_ERR_INVALID_ARG;
     if (int e = select_device(ctx)) return e;
     if (ctx->group) return cavept_group_sync(ctx);  // polls the communicator: a failed peer is an error code, not a hang
@@ -617,6 +702,7 @@ CAVEPT_API int cavept_sync(cavept_ctx* ctx) {
 }
 
 CAVEPT_API int cavept_read_accum(cavept_ctx* ctx, float* out, size_t bytes) {
+    CAVEPT_RANGE();
     if (!ctx || !out) return CAVEPT_ERR_INVALID_ARG;
     const size_t need = (size_t)ctx->cfg.width * ctx->cfg.height * sizeof(F4);
     if (bytes < need) return fail(ctx, CAVEPT_ERR_CAPACITY, "need %zu bytes", need);
@@ -637,14 +723,74 @@ CAVEPT_API int cavept_write_accum(cavept_ctx* ctx, const float* in, size_t bytes
 }
 
 CAVEPT_API int cavept_read_tonemapped_rgba8(cavept_ctx* ctx, uint8_t* out, size_t bytes) {
+    CAVEPT_RANGE();
     if (!ctx || !out) return CAVEPT_ERR_INVALID_ARG;
     const size_t n = (size_t)ctx->cfg.width * ctx->cfg.height;
     if (bytes < n * 4) return fail(ctx, CAVEPT_ERR_CAPACITY, "need %zu bytes", n * 4);
+    if (ctx->accum_sums) return fail(ctx, CAVEPT_ERR_NOT_READY, "the accumulator holds sums (group mode): leave the group first, or read cavept_read_composite");
     if (int e = select_device(ctx)) return e;
     CU(ctx, ctx->d_tone8.reserve(n * 4));
     launch_tonemap_rgba8(ctx->ex, ctx->d_accum.ptr, ctx->d_tone8.ptr, (int)n);
     ctx->ex.download(out, ctx->d_tone8.ptr, n * 4);
     return check_exec(ctx, "tone pass");
+}
+
+CAVEPT_API int cavept_read_tonemapped_rgba16f(cavept_ctx* ctx, uint16_t* out, size_t bytes) {
+    if (!ctx || !out) return CAVEPT_ERR_INVALID_ARG;
+    CAVEPT_RANGE();
+    const size_t n = (size_t)ctx->cfg.width * ctx->cfg.height;
+    if (bytes < n * 8) return fail(ctx, CAVEPT_ERR_CAPACITY, "need %zu bytes", n * 8);
+    if (ctx->accum_sums) return fail(ctx, CAVEPT_ERR_NOT_READY, "the accumulator holds sums (group mode): tone-map the composite on the destination rank after cavept_group_destroy, or read cavept_read_composite");
+    if (int e = select_device(ctx)) return e;
+    CU(ctx, ctx->d_tone16.reserve(n * 4));
+    launch_tonemap_f16(ctx->ex, ctx->d_accum.ptr, ctx->d_tone16.ptr, (int)n);
+    ctx->ex.download(out, ctx->d_tone16.ptr, n * 8);
+    return check_exec(ctx, "tone pass (rgba16f)");
+}
+
+// The tone-mapped frame as a binary PPM (P6, 8 bits per channel, row 0 = top as the accumulator stores it): the
+// headless stand-in for presenting RG_RES_POST_PROCESS (graphics_manager.cpp:485-493).
+CAVEPT_API int cavept_write_ppm(cavept_ctx* ctx, const char* path) {
+    if (!ctx || !path) return CAVEPT_ERR_INVALID_ARG;
+    CAVEPT_RANGE();
+    const size_t n = (size_t)ctx->cfg.width * ctx->cfg.height;
+    ctx->host_rgba8.resize(n * 4);
+    if (int e = cavept_read_tonemapped_rgba8(ctx, ctx->host_rgba8.data(), ctx->host_rgba8.size())) return e;
+    FILE* f = std::fopen(path, "wb");
+    if (!f) return fail(ctx, CAVEPT_ERR_INVALID_ARG, "cannot open %s for writing", path);
+    std::fprintf(f, "P6\n%d %d\n255\n", ctx->cfg.width, ctx->cfg.height);
+    std::vector<unsigned char> row((size_t)ctx->cfg.width * 3);
+    bool ok = true;
+    for (int y = 0; y < ctx->cfg.height && ok; ++y) {
+        const unsigned char* src = ctx->host_rgba8.data() + (size_t)y * ctx->cfg.width * 4;
+        for (int x = 0; x < ctx->cfg.width; ++x) {
+            row[3 * x] = src[4 * x];
+            row[3 * x + 1] = src[4 * x + 1];
+            row[3 * x + 2] = src[4 * x + 2];
+        }
+        ok = std::fwrite(row.data(), 1, row.size(), f) == row.size();
+    }
+    ok = (std::fclose(f) == 0) && ok;
+    return ok ? CAVEPT_OK : fail(ctx, CAVEPT_ERR_INVALID_ARG, "short write to %s", path);
+}
+
+// Device time of the last cavept_render without blocking: CAVEPT_ERR_NOT_READY while the launch is still running.
+CAVEPT_API int cavept_last_render_ms(cavept_ctx* ctx, float* out_ms) {
+    if (!ctx || !out_ms) return CAVEPT_ERR_INVALID_ARG;
+    if (int e = select_device(ctx)) return e;
+    const cudaError_t q = cudaEventQuery(ctx->ev1);
+    if (q == cudaErrorNotReady) return CAVEPT_ERR_NOT_READY;
+    if (q != cudaSuccess) {
+        (void)cudaGetLastError();
+        return fail(ctx, CAVEPT_ERR_NOT_READY, "no render has been launched yet");
+    }
+    float ms = 0.0f;
+    if (cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1) != cudaSuccess) {
+        (void)cudaGetLastError();
+        return fail(ctx, CAVEPT_ERR_NOT_READY, "no render has been launched yet");
+    }
+    *out_ms = ms;
+    return CAVEPT_OK;
 }
 
 CAVEPT_API int cavept_read_tonemapped_rgba32f(cavept_ctx* ctx, float* out, size_t bytes) {
@@ -684,6 +830,12 @@ CAVEPT_API int cavept_reset_stats(cavept_ctx* ctx) {
 CAVEPT_API int cavept_set_count_visits(cavept_ctx* ctx, int enable) {
     if (!ctx) return CAVEPT_ERR_INVALID_ARG;
     ctx->count_visits = enable != 0;
+    return CAVEPT_OK;
+}
+
+CAVEPT_API int cavept_set_refit(cavept_ctx* ctx, int enable) {
+    if (!ctx) return CAVEPT_ERR_INVALID_ARG;
+    ctx->refit_enabled = enable != 0;
     return CAVEPT_OK;
 }
 

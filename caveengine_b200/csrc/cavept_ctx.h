@@ -8,6 +8,8 @@
 #include <string>
 #include <vector>
 
+#include <nvtx3/nvToolsExt.h>  // header-only: ranges cost nothing unless a profiler injects itself
+
 #include "../../include/cavept.h"
 #include "kernels.h"
 
@@ -51,6 +53,15 @@ struct DevBuf {
         cap = 0;
     }
 };
+
+// One NVTX range per API call (SURVEY.md section 5 "tracing"): shows up in Nsight timelines as cavept_<call>.
+struct ApiRange {
+    explicit ApiRange(const char* name) { nvtxRangePushA(name); }
+    ~ApiRange() { nvtxRangePop(); }
+    ApiRange(const ApiRange&) = delete;
+    ApiRange& operator=(const ApiRange&) = delete;
+};
+#define CAVEPT_RANGE() ApiRange nvtx_range_(__func__)
 
 struct MeshRecord {
     int built = -1;  // order of first appearance among instances, or -1 if unreferenced
@@ -117,7 +128,16 @@ struct cavept_ctx {
     // image
     DevBuf<F4> d_accum, d_tone;
     DevBuf<unsigned char> d_tone8;
+    DevBuf<unsigned short> d_tone16;
+    std::vector<unsigned char> host_rgba8;  // staging of cavept_write_ppm
     DevBuf<unsigned long long> d_stats;
+    // refit of the production tree on instance updates (wbvh_body.h refit_wbvh): SAH builder only
+    bool refit_ready = false, refit_enabled = true;
+    std::vector<int> level_start;        // pairs owned by the interior nodes of level L: [level_start[L], level_start[L+1])
+    float world_pad = 0.0f, world_extent = 0.0f;  // box padding of the built tree and the largest |coordinate| it was derived from
+    float area_baseline = -1.0f;         // surface-area sum of the freshly built tree (SAH cost proxy), computed on first use
+    DevBuf<unsigned char> d_moved;
+    DevBuf<float> d_area_sum;
     DevBuf<F4> d_composite;      // group mode: the composited frame (mean, n) on the destination rank(s)
     cavept_group_state* group = nullptr;
     DevBuf<int> d_job_counter;   // job queue of the persistent trace kernel (trace_pool_body.h)

@@ -2,6 +2,8 @@
 // Compiled for sm_100a only, with -fmad=false (see cv_common.h on float semantics).
 #include "kernels.h"
 
+#include <cuda_fp16.h>
+
 namespace cavept {
 
 // ---- generic element-wise launch -------------------------------------------------------
@@ -316,6 +318,9 @@ int run_build_bvh_parity(CudaExec& ex, BuildArrays a, const int* tri_off_host, c
 }
 int run_build_wbvh(CudaExec& ex, WBuild b, WReport* report) { return build_wbvh(ex, b, report); }
 int run_build_lbvh(CudaExec& ex, WBuild b, WReport* report) { return build_lbvh(ex, b, report); }
+void run_refit_wbvh(CudaExec& ex, WBuild b, const int* level_start, int n_levels, const unsigned char* d_moved, float* d_area_sum, float out[7]) {
+    refit_wbvh(ex, b, level_start, n_levels, d_moved, d_area_sum, out);
+}
 
 // ---- path-trace pass ------------------------------------------------------------------
 // Block = 128 threads = a 16 x 8 pixel tile; each warp covers an 8 x 4 sub-tile so the
@@ -519,6 +524,20 @@ struct FnToneF32 {
         out[i] = o;
     }
 };
+// RT_FMT_TONE = R16G16B16A16_FLOAT (cave/engine/render_graph/render_graph_defines.h:64): the format the reference's tone
+// target has; round-to-nearest-even halves of the fp32 tone values, alpha 1.0
+struct FnToneF16 {
+    const F4* accum;
+    uint2* out;
+    __device__ void operator()(int i) const {
+        const F4 a = accum[i];
+        const unsigned r = __half_as_ushort(__float2half_rn(tone(a.x))), g = __half_as_ushort(__float2half_rn(tone(a.y)));
+        const unsigned b = __half_as_ushort(__float2half_rn(tone(a.z)));
+        out[i] = make_uint2(r | (g << 16), b | (0x3C00u << 16));
+    }
+};
+void launch_tonemap_f16(CudaExec& ex, const F4* accum, unsigned short* out, int n_pixels) { ex.launch(n_pixels, FnToneF16{ accum, reinterpret_cast<uint2*>(out) }); }
+
 void launch_tonemap_rgba8(CudaExec& ex, const F4* accum, unsigned char* out, int n_pixels) {
     ex.launch(n_pixels, FnToneRgba8{ accum, reinterpret_cast<uchar4*>(out) });
 }

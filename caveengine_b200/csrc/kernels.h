@@ -44,6 +44,7 @@ void launch_assemble_indices(CudaExec& ex, const uint32_t* raw_indices, const in
 int run_build_bvh_parity(CudaExec& ex, BuildArrays a, const int* tri_off_host, const int* d_tri_off, int n_meshes, BuildItem* host_scratch, BuildReport* report);
 int run_build_wbvh(CudaExec& ex, WBuild b, WReport* report);
 int run_build_lbvh(CudaExec& ex, WBuild b, WReport* report);
+void run_refit_wbvh(CudaExec& ex, WBuild b, const int* level_start, int n_levels, const unsigned char* d_moved, float* d_area_sum, float out[7]);
 
 void launch_trace(CudaExec& ex, const TraceParams& p, bool fast, bool count_visits);
 // the per-pixel body as a persistent launch drawing pixel jobs from a global queue (CAVEPT_KERNEL_QUEUE)
@@ -56,6 +57,7 @@ void launch_trace_pool(CudaExec& ex, const TraceParams& p, bool count_visits, in
 float run_gather_probe(CudaExec& ex, const void* base, size_t bytes, int iters, cudaEvent_t e0, cudaEvent_t e1, int n_sms, double* lane_gathers);
 void launch_probe(CudaExec& ex, const float* rays, const float* tris, const float* boxes, float* out, int n);
 void launch_tonemap_rgba8(CudaExec& ex, const F4* accum, unsigned char* out, int n_pixels);
+void launch_tonemap_f16(CudaExec& ex, const F4* accum, unsigned short* out_rgba16f, int n_pixels);
 void launch_tonemap_f32(CudaExec& ex, const F4* accum, F4* out, int n_pixels);
 void launch_accum_scale(CudaExec& ex, F4* accum, int n_pixels, bool to_sums);
 

@@ -266,6 +266,12 @@ CV_HD int make_leaf_ref(int first_slot, int count) { return (int)(0x80000000u | 
 #if defined(__CUDA_ARCH__)
 #define CV_WARP_ANY(pred) __any_sync(0xffffffffu, (pred))
 #define CV_WARP_COUNT(pred) __popc(__ballot_sync(0xffffffffu, (pred)))
+#elif defined(CV_WARP_EMU)  // tests/emu/emu.cpp: 32 host threads per warp, votes through a barrier
+bool warp_emu_any(bool pred);
+int warp_emu_count(bool pred);
+int warp_emu_draw(int* counter, bool want);
+#define CV_WARP_ANY(pred) cavept::warp_emu_any(pred)
+#define CV_WARP_COUNT(pred) cavept::warp_emu_count(pred)
 #else  // the emulator steps one lane at a time: a warp of one
 #define CV_WARP_ANY(pred) (pred)
 #define CV_WARP_COUNT(pred) ((pred) ? 1 : 0)
@@ -601,6 +607,8 @@ CV_D int trace_draw_jobs(int* counter, bool want) {
     if (lane == leader) base = atomicAdd(counter, __popc(m));
     base = __shfl_sync(0xffffffffu, base, leader);
     return want ? base + __popc(m & ((1u << lane) - 1u)) : 0x7fffffff;
+#elif defined(CV_WARP_EMU)
+    return warp_emu_draw(counter, want);
 #else
     if (!want) return 0x7fffffff;
     const int j = *counter;
@@ -695,24 +703,21 @@ CV_D unsigned int body_trace_pixel_fast(const TraceParams& p, int x, int y, int*
                     }
                 }
             }
-            if (kQueue && queue_open) {  // warp-uniform branch: the lanes whose pixel is finished draw the next jobs together
-                if (CV_WARP_ANY(want_job)) {
+            if (kQueue) {
+                // want_job: this lane has no pixel to go on with (it was vacant, or its pixel's last frame was just accumulated)
+                if (queue_open && CV_WARP_ANY(want_job)) {  // warp-uniform: the lanes that need a pixel draw the next jobs together
                     const TraceJobs jobs = trace_jobs(p);  // recomputed from the launch constants: nothing of it stays live in the hot loop
                     const int job = trace_draw_jobs(job_counter, want_job);
-                    if (want_job) {
-                        vacant = true;
-                        if (job < jobs.n_jobs && trace_job_pixel(jobs, job, x, y)) {
-                            pix = (size_t)y * (size_t)p.width + (size_t)x;
-                            f = 0;
-                            vacant = false;
-                            new_sample = true;
-                        }
+                    if (want_job && job < jobs.n_jobs && trace_job_pixel(jobs, job, x, y)) {
+                        pix = (size_t)y * (size_t)p.width + (size_t)x;
+                        f = 0;
+                        new_sample = true;
+                        want_job = false;  // served
                     }
                     if (CV_WARP_ANY(want_job && job >= jobs.n_jobs)) queue_open = false;
                 }
-            }
-            if (kQueue && !queue_open && (want_job || vacant) && need_shade) {
-                if (vacant) done = true;  // the queue is empty: the lane retires
+                vacant = want_job;                      // unserved (padding job, or the queue ran out): draws again at the next shading phase ...
+                if (want_job && !queue_open) done = true;  // ... unless the queue is empty: the lane retires
             }
             if (need_shade) {
                 if (new_sample && !done && !(kQueue && vacant)) {

@@ -515,8 +515,15 @@ CV_D void wb_body_refit_pair(const WBuild& b, int k, float* area_sum) {
     b.qpairs[k] = q;
     if (area_sum) {
 #if defined(__CUDA_ARCH__)
-        const float total = __reduce_add_sync(__activemask(), 0) == 0 ? area : area;  // (no float redux: one atomic per lane; refit is launch-bound)
-        atomicAdd(area_sum, total);
+        // one atomic per warp: the active lanes of a k_for_each launch are a contiguous run starting at lane 0
+        const unsigned mask = __activemask();
+        const int lane = (int)(threadIdx.x & 31u);
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) {
+            const float o = __shfl_down_sync(mask, area, d);
+            if (lane + d < 32 && ((mask >> (lane + d)) & 1u)) area += o;
+        }
+        if (lane == 0) atomicAdd(area_sum, area);
 #else
         *area_sum += area;
 #endif

@@ -154,9 +154,17 @@ CAVEPT_API int cavept_upload_scene(cavept_ctx* ctx, const cavept_mesh* meshes, i
                                    const cavept_instance* instances, int instance_count,
                                    const cavept_material* materials, int material_count);
 /* The two dirty-driven re-uploads of UpdateAccelStructure (path_tracer.cpp:156-158, :197-199).
- * Instance count/mesh ids must match the uploaded scene; both mark the scene dirty. */
+ * Instance count/mesh ids must match the uploaded scene; both mark the scene dirty.
+ * cavept_update_instances does NOT rebuild: the reference's per-mesh trees live in mesh space, so there a moved
+ * instance costs M x 144 bytes; the production tree is in world space, so the moved instances' triangle slots are
+ * re-transformed and every box is refitted bottom-up, one launch per tree level (csrc/wbvh_body.h refit_wbvh; ~0.1 ms
+ * at 262k triangles).  The refit is kept when the scene still fits the tree's quantisation grid and the surface-area
+ * sum of the tree stayed within 1.3x of the freshly built tree's; otherwise (and always with CAVEPT_BVH_LBVH, whose
+ * rebuild is as cheap) the tree is rebuilt.  cavept_stats.last_update_was_refit / last_update_instances_ms report which
+ * and how long.  cavept_set_refit(ctx, 0) forces the rebuild (measurement / A-B). */
 CAVEPT_API int cavept_update_instances(cavept_ctx* ctx, const cavept_instance* instances, int instance_count);
 CAVEPT_API int cavept_update_materials(cavept_ctx* ctx, const cavept_material* materials, int material_count);
+CAVEPT_API int cavept_set_refit(cavept_ctx* ctx, int enable);
 /* New vertex positions (and normals, may be NULL) for one mesh + BVH rebuild on the
  * device (BASELINE config 5; beyond the reference, path_tracer.cpp:69 "@TODO"). */
 CAVEPT_API int cavept_rebuild_mesh(cavept_ctx* ctx, int mesh, const float* positions, const float* normals);
@@ -198,12 +206,20 @@ CAVEPT_API int cavept_read_accum(cavept_ctx* ctx, float* out_rgba32f, size_t byt
 /* Tone pass: c/(c+1) then pow(c, 1/2.2) (cave/shader/glsl/post_process.ps.glsl:72-76). */
 CAVEPT_API int cavept_read_tonemapped_rgba8(cavept_ctx* ctx, uint8_t* out_rgba8, size_t bytes);
 CAVEPT_API int cavept_read_tonemapped_rgba32f(cavept_ctx* ctx, float* out_rgba32f, size_t bytes);
+/* The same in the reference's tone-target format, RT_FMT_TONE = R16G16B16A16_FLOAT
+ * (cave/engine/render_graph/render_graph_defines.h:64, common_passes.cpp:1011-1039): 4 IEEE halves per pixel. */
+CAVEPT_API int cavept_read_tonemapped_rgba16f(cavept_ctx* ctx, uint16_t* out_rgba16f, size_t bytes);
+/* The tone-mapped frame as a binary PPM (P6): the headless stand-in for presenting RG_RES_POST_PROCESS. */
+CAVEPT_API int cavept_write_ppm(cavept_ctx* ctx, const char* path);
 /* Restore a saved accumulator (checkpoint/resume; the accumulator is the only state). */
 CAVEPT_API int cavept_write_accum(cavept_ctx* ctx, const float* rgba32f, size_t bytes);
 
 /* ---- measurement and multi-GPU plumbing ------------------------------------------ */
 CAVEPT_API int cavept_get_stats(cavept_ctx* ctx, cavept_stats* out);
 CAVEPT_API int cavept_reset_stats(cavept_ctx* ctx);
+/* Device time of the last cavept_render WITHOUT blocking (cavept_get_stats synchronises the stream):
+ * CAVEPT_ERR_NOT_READY while that launch is still running or before the first one. */
+CAVEPT_API int cavept_last_render_ms(cavept_ctx* ctx, float* out_ms);
 CAVEPT_API int cavept_set_count_visits(cavept_ctx* ctx, int enable); /* instrumented kernels: node visits / triangle tests */
 CAVEPT_API int cavept_set_kernel_variant(cavept_ctx* ctx, int variant); /* CAVEPT_KERNEL_*; measurement / A-B comparison */
 CAVEPT_API void* cavept_stream(cavept_ctx* ctx);            /* cudaStream_t the context launches on */

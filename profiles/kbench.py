@@ -53,7 +53,7 @@ def one(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--libs", nargs="*", default=[])
-    ap.add_argument("--variants", nargs="*", default=["pool", "pixel"])
+    ap.add_argument("--variants", nargs="*", default=["queue", "pixel"])
     ap.add_argument("--spp", nargs="*", type=int, default=[32])
     ap.add_argument("--reps", type=int, default=3)
     ap.add_argument("--scene", default="sponza")

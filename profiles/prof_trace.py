@@ -1,6 +1,6 @@
 #!/usr/bin/env python3
 """Tiny driver for ncu captures: uploads the bench scene and renders `spp` frames once
-(after one warm launch).  Usage: python profiles/prof_trace.py [spp] [scene] [pool|pixel]"""
+(after one warm launch).  Usage: python profiles/prof_trace.py [spp] [scene] [queue|pixel|pool]"""
 import os
 import sys
 
@@ -10,7 +10,7 @@ from caveengine_b200 import scenes
 
 spp = int(sys.argv[1]) if len(sys.argv) > 1 else 2
 name = sys.argv[2] if len(sys.argv) > 2 else "sponza"
-variant = sys.argv[3] if len(sys.argv) > 3 else "pool"
+variant = sys.argv[3] if len(sys.argv) > 3 else "queue"
 scene = {"sponza": scenes.sponza_scene, "cornell": scenes.cornell_scene, "breakfast": scenes.breakfast_scene, "animated": scenes.animated_scene}[name]()
 w, h = (3840, 2160) if name == "breakfast" else (1920, 1080)
 pt = cb.PathTracer(w, h, 5 if name == "cornell" else 8, bvh_mode=cb.BvhMode.LBVH if name == "animated" else cb.BvhMode.FAST)

@@ -149,6 +149,9 @@ EMU_API int emu_wbvh_build(const GpuPtVertex* vertices, const GpuPtIndex* indice
     report[1] = rep.n_pairs;
     report[2] = wb_quantised_ref(rep.root_ref);
     report[3] = rep.error_bits;
+    if (force_median < 2) {
+        for (int L = 0; L < rep.levels && L < 124; ++L) report[4 + L] = rep.level_items[L];  // report has 4 + 124 ints
+    }
     if (out_pad) *out_pad = rep.pad;
     if (out_grid) {
         for (int k = 0; k < 3; ++k) {
@@ -157,6 +160,32 @@ EMU_API int emu_wbvh_build(const GpuPtVertex* vertices, const GpuPtIndex* indice
         }
     }
     return rc;
+}
+
+// Refit of an emu_wbvh_build tree after the instance transforms changed (wbvh_body.h refit_wbvh), as
+// cavept_update_instances drives it.  level_items = WReport::level_items of the build; out = scene box + area sum.
+EMU_API void emu_wbvh_refit(const GpuPtVertex* vertices, const GpuPtIndex* indices, const GpuPtMesh* instances, int n_inst, int n_prims, float pad, const float* grid,
+                            const int* level_items, int n_levels, const unsigned char* moved, FastNode* fnodes, QPair* qpairs, FastTri* ftris, FastTri* fnormals, float* out) {
+    WBuild b{};
+    b.vertices = vertices;
+    b.indices = indices;
+    b.instances = instances;
+    b.n_inst = n_inst;
+    b.n_prims = n_prims;
+    b.pad = pad;
+    b.fnodes = fnodes;
+    b.qpairs = qpairs;
+    b.ftris = ftris;
+    b.fnormals = fnormals;
+    for (int k = 0; k < 3; ++k) {
+        b.grid_origin[k] = grid[k];
+        b.grid_scale[k] = grid[3 + k];
+    }
+    std::vector<int> level_start(1, 0);
+    for (int L = 0; L < n_levels; ++L) level_start.push_back(level_start.back() + level_items[L]);
+    float area = 0.0f;
+    EmuExec ex;
+    refit_wbvh(ex, b, level_start.data(), n_levels, moved, &area, out);
 }
 
 EMU_API void emu_mat4_inverse(const float* m, float* out) { mat4_inverse(m, out); }
@@ -169,10 +198,9 @@ struct EmuCamera {
     float up[3];
 };
 
-EMU_API long long emu_render(const GpuPtVertex* vertices, const GpuPtIndex* indices, const GpuPtBvh* bvhs, const GpuPtMesh* meshes, int mesh_count,
-                             const GpuPtMaterial* materials, const FastNode* fnodes, const QPair* qpairs, const float* grid, const FastTri* ftris, const FastTri* fnormals, int root_ref,
-                             const EmuCamera* cam, int max_bounce, int width, int height, int first_frame, int n_frames, int reset_first, float* accum,
-                             int fast, unsigned long long* counters) {
+static TraceParams emu_params(const GpuPtVertex* vertices, const GpuPtIndex* indices, const GpuPtBvh* bvhs, const GpuPtMesh* meshes, int mesh_count,
+                              const GpuPtMaterial* materials, const FastNode* fnodes, const QPair* qpairs, const float* grid, const FastTri* ftris, const FastTri* fnormals, int root_ref,
+                              const EmuCamera* cam, int max_bounce, int width, int height, int first_frame, int n_frames, int reset_first, float* accum) {
     TraceParams p{};
     p.vertices = vertices;
     p.indices = indices;
@@ -201,6 +229,15 @@ EMU_API long long emu_render(const GpuPtVertex* vertices, const GpuPtIndex* indi
     p.n_frames = n_frames;
     p.reset_first = reset_first;
     p.accum = reinterpret_cast<F4*>(accum);
+    return p;
+}
+
+EMU_API long long emu_render(const GpuPtVertex* vertices, const GpuPtIndex* indices, const GpuPtBvh* bvhs, const GpuPtMesh* meshes, int mesh_count,
+                             const GpuPtMaterial* materials, const FastNode* fnodes, const QPair* qpairs, const float* grid, const FastTri* ftris, const FastTri* fnormals, int root_ref,
+                             const EmuCamera* cam, int max_bounce, int width, int height, int first_frame, int n_frames, int reset_first, float* accum,
+                             int fast, unsigned long long* counters) {
+    TraceParams p = emu_params(vertices, indices, bvhs, meshes, mesh_count, materials, fnodes, qpairs, grid, ftris, fnormals, root_ref, cam, max_bounce, width, height, first_frame,
+                               n_frames, reset_first, accum);
     unsigned long long cnt[3] = { 0, 0, 0 };
     p.counters = cnt;
     long long segs = 0;
@@ -209,6 +246,22 @@ EMU_API long long emu_render(const GpuPtVertex* vertices, const GpuPtIndex* indi
         float rec[kPoolWordsPerThread];
         int job_counter = 0;
         segs = body_trace_pool<true>(p, stack, rec, 1, &job_counter, cnt);
+        if (counters) {
+            counters[0] = (unsigned long long)segs;
+            counters[1] = cnt[1];
+            counters[2] = cnt[2];
+        }
+        return segs;
+    }
+    if (fast == 3) {  // the per-pixel body as a persistent lane drawing jobs from the queue (k_trace_queue)
+        int job_counter = 0;
+        const TraceJobs jobs = trace_jobs(p);
+        const int job = trace_draw_jobs(&job_counter, true);
+        int x = p.width, y = 0;
+        if (job < jobs.n_jobs) {
+            if (!trace_job_pixel(jobs, job, x, y)) x = p.width;
+        }
+        segs = body_trace_pixel_fast<true, kStepQuorum, kShadeBatch, true>(p, x, y, stack, 1, cnt, &job_counter);
         if (counters) {
             counters[0] = (unsigned long long)segs;
             counters[1] = cnt[1];
@@ -228,6 +281,104 @@ EMU_API long long emu_render(const GpuPtVertex* vertices, const GpuPtIndex* indi
     }
     return segs;
 }
+
+#if defined(CV_WARP_EMU)
+// ---- warps of 32 host threads: the votes (__any_sync / __ballot_sync) and the warp-aggregated job draw go through a
+//      barrier, so the warp-level scheduling of the persistent kernel (who draws, who retires, when the loop ends)
+//      runs with real divergence between lanes.  A thread outside any warp (the serial entry points) is a warp of one.
+#include <atomic>
+#include <barrier>
+#include <thread>
+namespace {
+struct EmuWarp {
+    std::barrier<> bar{ 32 };
+    std::atomic<unsigned> word[3];
+    int bcast = 0;
+    EmuWarp() {
+        for (auto& w : word) w.store(0u);
+    }
+};
+thread_local EmuWarp* tl_warp = nullptr;
+thread_local int tl_lane = 0;
+thread_local unsigned tl_round = 0;
+unsigned emu_ballot(bool pred) {
+    EmuWarp* w = tl_warp;
+    const unsigned r = tl_round++ % 3u;
+    if (tl_lane == 0) w->word[(r + 1u) % 3u].store(0u);
+    if (pred) w->word[r].fetch_or(1u << tl_lane);
+    w->bar.arrive_and_wait();
+    return w->word[r].load();
+}
+}  // namespace
+namespace cavept {
+bool warp_emu_any(bool pred) { return tl_warp ? emu_ballot(pred) != 0u : pred; }
+int warp_emu_count(bool pred) { return tl_warp ? __builtin_popcount(emu_ballot(pred)) : (pred ? 1 : 0); }
+int warp_emu_draw(int* counter, bool want) {
+    if (!tl_warp) {
+        if (!want) return 0x7fffffff;
+        return (*counter)++;
+    }
+    const unsigned m = emu_ballot(want);
+    if (m == 0u) return 0x7fffffff;
+    const int leader = __builtin_ctz(m);
+    if (tl_lane == leader) tl_warp->bcast = __atomic_fetch_add(counter, __builtin_popcount(m), __ATOMIC_RELAXED);
+    tl_warp->bar.arrive_and_wait();
+    const int base = tl_warp->bcast;
+    tl_warp->bar.arrive_and_wait();  // nobody overwrites bcast before everyone has read it
+    return want ? base + __builtin_popcount(m & ((1u << tl_lane) - 1u)) : 0x7fffffff;
+}
+}  // namespace cavept
+
+// k_trace_queue with n_warps concurrent warps of 32 threads each; returns segments, -1 if the job counter ended wrong
+EMU_API long long emu_render_warps(const GpuPtVertex* vertices, const GpuPtIndex* indices, const GpuPtBvh* bvhs, const GpuPtMesh* meshes, int mesh_count,
+                                   const GpuPtMaterial* materials, const FastNode* fnodes, const QPair* qpairs, const float* grid, const FastTri* ftris, const FastTri* fnormals,
+                                   int root_ref, const EmuCamera* cam, int max_bounce, int width, int height, int first_frame, int n_frames, int reset_first, float* accum,
+                                   int n_warps, const int* tile, unsigned long long* counters) {
+    TraceParams p = emu_params(vertices, indices, bvhs, meshes, mesh_count, materials, fnodes, qpairs, grid, ftris, fnormals, root_ref, cam, max_bounce, width, height, first_frame,
+                               n_frames, reset_first, accum);
+    if (tile) {
+        p.tile_x0 = tile[0];
+        p.tile_y0 = tile[1];
+        p.tile_x1 = tile[2];
+        p.tile_y1 = tile[3];
+    }
+    unsigned long long shared_cnt[3] = { 0, 0, 0 };
+    p.counters = shared_cnt;
+    int job_counter = 0;
+    std::atomic<long long> segs{ 0 };
+    std::atomic<unsigned long long> visits[3];
+    for (auto& v : visits) v.store(0);
+    std::vector<EmuWarp> warps(n_warps);
+    std::vector<std::thread> threads;
+    for (int wi = 0; wi < n_warps; ++wi) {
+        for (int lane = 0; lane < 32; ++lane) {
+            threads.emplace_back([&, wi, lane]() {
+                tl_warp = &warps[wi];
+                tl_lane = lane;
+                tl_round = 0;
+                int stack[kStackSize];
+                unsigned long long cnt[3] = { 0, 0, 0 };
+                const TraceJobs jobs = trace_jobs(p);
+                const int job = trace_draw_jobs(&job_counter, true);
+                int x = p.width, y = 0;
+                if (job < jobs.n_jobs) {
+                    if (!trace_job_pixel(jobs, job, x, y)) x = p.width;
+                }
+                segs += body_trace_pixel_fast<true, kStepQuorum, kShadeBatch, true>(p, x, y, stack, 1, cnt, &job_counter);
+                for (int k = 0; k < 3; ++k) visits[k] += cnt[k];
+                tl_warp = nullptr;
+            });
+        }
+    }
+    for (auto& t : threads) t.join();
+    if (counters) {
+        counters[0] = (unsigned long long)segs.load();
+        counters[1] = visits[1].load();
+        counters[2] = visits[2].load();
+    }
+    return segs.load();
+}
+#endif  // CV_WARP_EMU
 
 // the product's HitTriangle / HitBvh bodies on caller-supplied cases
 EMU_API void emu_probe(int n, const float* rays, const float* tris, const float* boxes, float* out) {

@@ -34,6 +34,20 @@ def load() -> C.CDLL:
     return lib
 
 
+WARP_LIB = os.path.join(HERE, "emu", "libcavept_emu_warp.so")
+
+
+def load_warp() -> C.CDLL:
+    """The same bodies with warps of 32 host threads (-DCV_WARP_EMU): votes and the job draw go through a barrier."""
+    deps = [SRC] + [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith(".h")]
+    if not os.path.exists(WARP_LIB) or any(os.path.getmtime(d) > os.path.getmtime(WARP_LIB) for d in deps):
+        subprocess.check_call(["g++", "-std=c++20", "-O2", "-ffp-contract=off", "-fPIC", "-shared", "-fvisibility=hidden", "-pthread", "-DCV_WARP_EMU", "-I", CSRC,
+                               "-o", WARP_LIB, SRC])
+    lib = C.CDLL(WARP_LIB)
+    lib.emu_render_warps.restype = C.c_longlong
+    return lib
+
+
 def _p(a):
     return a.ctypes.data_as(C.c_void_p)
 
@@ -80,13 +94,23 @@ class EmuScene:
         self.grid = np.zeros(6, dtype=np.float32)            # origin xyz, scale xyz
         self.ftris = np.zeros(P, dtype=FASTTRI_DT)
         self.fnormals = np.zeros(P, dtype=FASTTRI_DT)
-        report = np.zeros(4, dtype=np.int32)
+        report = np.zeros(4 + 124, dtype=np.int32)
         pad = C.c_float()
         self.wrc = self.lib.emu_wbvh_build(_p(asm.vertices), _p(asm.indices), _p(asm.meshes), C.c_int(n_inst), _p(self.inst_prim_off), _p(self.inst_tri_off),
                                            C.c_int((3 if force_median else 2) if lbvh else (1 if force_median else 0)), _p(self.fnodes), _p(self.qpairs), _p(self.ftris), _p(self.fnormals), _p(report), C.byref(pad),
                                            _p(self.grid))
-        self.fast_levels, self.n_pairs, self.root_ref, self.wb_error_bits = [int(v) for v in report]
+        self.fast_levels, self.n_pairs, self.root_ref, self.wb_error_bits = [int(v) for v in report[:4]]
+        self.level_items = report[4:4 + self.fast_levels].copy()
         self.pad = pad.value
+
+    def refit(self, meshes, moved):
+        """wbvh_body.h refit_wbvh on the tree of build_world(): `meshes` = the GpuPtMesh array with the new transforms,
+        `moved` = one flag per instance.  Returns (scene box min/max, surface-area sum)."""
+        moved = np.ascontiguousarray(moved, dtype=np.uint8)
+        out = np.zeros(7, dtype=np.float32)
+        self.lib.emu_wbvh_refit(_p(self.asm.vertices), _p(self.asm.indices), _p(meshes), C.c_int(meshes.shape[0]), C.c_int(self.n_prims), C.c_float(self.pad), _p(self.grid),
+                                _p(self.level_items), C.c_int(len(self.level_items)), _p(moved), _p(self.fnodes), _p(self.qpairs), _p(self.ftris), _p(self.fnormals), _p(out))
+        return out[:6].copy(), float(out[6])
 
     def render(self, camera, width, height, first_frame, n_frames, max_bounce, fast, accum=None, reset_first=True):
         from oracle.oracle import _cam
@@ -100,4 +124,21 @@ class EmuScene:
                                    _p(self.qpairs), _p(self.grid), _p(self.ftris), _p(self.fnormals), C.c_int(self.root_ref), C.byref(cam), C.c_int(max_bounce), C.c_int(width),
                                    C.c_int(height), C.c_int(first_frame), C.c_int(n_frames), C.c_int(1 if reset_first else 0), _p(accum), C.c_int(int(fast)),
                                    counters)
+        return accum, {"segments": int(segs), "node_visits": int(counters[1]), "tri_tests": int(counters[2])}
+
+    def render_warps(self, camera, width, height, first_frame, n_frames, max_bounce, n_warps=2, tile=None, accum=None, reset_first=True):
+        """k_trace_queue on n_warps concurrent warps of 32 host threads each (real divergence between lanes)."""
+        from oracle.oracle import _cam
+
+        lib = load_warp()
+        if accum is None:
+            accum = np.zeros((height, width, 4), dtype=np.float32)
+        cam = _cam(camera)
+        counters = (C.c_ulonglong * 3)()
+        t = (C.c_int * 4)(*tile) if tile is not None else None
+        a = self.asm
+        segs = lib.emu_render_warps(_p(a.vertices), _p(a.indices), _p(self.nodes), _p(a.meshes), C.c_int(a.meshes.shape[0]), _p(a.materials), _p(self.fnodes),
+                                    _p(self.qpairs), _p(self.grid), _p(self.ftris), _p(self.fnormals), C.c_int(self.root_ref), C.byref(cam), C.c_int(max_bounce),
+                                    C.c_int(width), C.c_int(height), C.c_int(first_frame), C.c_int(n_frames), C.c_int(1 if reset_first else 0), _p(accum), C.c_int(n_warps), t,
+                                    counters)
         return accum, {"segments": int(segs), "node_visits": int(counters[1]), "tri_tests": int(counters[2])}

@@ -292,7 +292,7 @@ def test_intersection_bodies_match_the_engines_cpu_twins():
 
 
 @pytest.mark.parametrize("name,w,h", [("tiny", 61, 35), ("heightfield", 64, 36)])
-def test_pool_kernel_body_equals_the_per_pixel_body_bitwise(port_oracle, scene_cache, name, w, h):
+def test_job_queue_bodies_equal_the_per_pixel_body_bitwise(port_oracle, scene_cache, name, w, h):
     """The persistent job-queue body (trace_pool_body.h: two pixel streams per lane, records parked in shared
     memory) runs the same walk_step / walk_test_triangle / shade_hit sequence per pixel as body_trace_pixel_fast:
     same accumulator bytes, same segment / node / triangle counts -- also on a ragged image (61 x 35 is not a
@@ -301,9 +301,80 @@ def test_pool_kernel_body_equals_the_per_pixel_body_bitwise(port_oracle, scene_c
     asm = port_oracle.assemble(sc)
     emu = E.EmuScene(asm, sc)
     a, sa = emu.render(sc.camera, w, h, 0, 3, 5, fast=1)
-    b, sb = emu.render(sc.camera, w, h, 0, 3, 5, fast=2)
+    for body in (2, 3):  # 2: two pixel streams per lane (trace_pool_body.h); 3: the per-pixel body drawing jobs from the queue (k_trace_queue)
+        b, sb = emu.render(sc.camera, w, h, 0, 3, 5, fast=body)
+        assert a.tobytes() == b.tobytes(), body
+        assert sa == sb, body
+        a2, _ = emu.render(sc.camera, w, h, 3, 2, 5, fast=1, accum=a.copy(), reset_first=False)
+        b2, _ = emu.render(sc.camera, w, h, 3, 2, 5, fast=body, accum=b.copy(), reset_first=False)
+        assert a2.tobytes() == b2.tobytes() and np.all(b2[..., 3] == 5.0), body
+
+
+@pytest.mark.timeout(600)
+@pytest.mark.parametrize("name,w,h,n_warps", [("tiny", 61, 35, 1), ("tiny", 61, 35, 3), ("cornell", 64, 36, 2), ("tiny", 8, 4, 4), ("tiny", 200, 3, 2)])
+def test_queue_kernel_on_real_warps_terminates_and_equals_the_per_pixel_body(port_oracle, scene_cache, name, w, h, n_warps):
+    """k_trace_queue's body on warps of 32 host threads (tests/emu/emu.cpp, -DCV_WARP_EMU: __any_sync / __ballot_sync
+    and the warp-aggregated job draw go through a barrier).  This is the test that sees the warp-level scheduling:
+    lanes that finish their pixel after another lane closed the queue must retire, lanes that drew padding jobs of a
+    ragged rectangle must draw again, and the loop must end -- with the same accumulator bytes and segment count as
+    the per-pixel body, however many warps share the queue (more warps than jobs included: 8x4 image, 4 warps)."""
+    sc = scene_cache(name)
+    asm = port_oracle.assemble(sc)
+    emu = E.EmuScene(asm, sc)
+    a, sa = emu.render(sc.camera, w, h, 0, 3, 5, fast=1)
+    b, sb = emu.render_warps(sc.camera, w, h, 0, 3, 5, n_warps=n_warps)
     assert a.tobytes() == b.tobytes()
-    assert sa == sb
-    a2, _ = emu.render(sc.camera, w, h, 3, 2, 5, fast=1, accum=a.copy(), reset_first=False)
-    b2, _ = emu.render(sc.camera, w, h, 3, 2, 5, fast=2, accum=b.copy(), reset_first=False)
-    assert a2.tobytes() == b2.tobytes() and np.all(b2[..., 3] == 5.0)
+    assert sa["segments"] == sb["segments"]
+    # a tile launch (TILED mode) over part of the image, continuing the accumulator
+    tile = (8, 4, min(w, 29), min(h, 19))
+    if tile[2] > tile[0] and tile[3] > tile[1]:
+        b2, _ = emu.render_warps(sc.camera, w, h, 3, 2, 5, n_warps=n_warps, tile=tile, accum=b.copy(), reset_first=False)
+        n = b2[..., 3]
+        inside = np.zeros((h, w), dtype=bool)
+        inside[tile[1]:tile[3], tile[0]:tile[2]] = True
+        assert np.all(n[inside] == 5.0) and np.all(n[~inside] == 3.0)
+        assert b2[~inside].tobytes() == b[~inside].tobytes()
+
+
+def test_refit_reproduces_the_tree_and_follows_moved_instances(port_oracle, scene_cache):
+    """wbvh_body.h refit_wbvh (what cavept_update_instances runs instead of a rebuild): with nothing moved the
+    bottom-up pass reproduces fnodes / qpairs / ftris bit for bit; with two instances moved, the refitted tree returns
+    the same closest hits as a tree built from scratch on the moved scene (identical image), every box still contains
+    what hangs below it, and the surface-area sum (the quality guard's proxy) is reported."""
+    import copy
+
+    from caveengine_b200 import scenes
+
+    sc = scene_cache("tiny")
+    asm = port_oracle.assemble(sc)
+    emu = E.EmuScene(asm, sc)
+    before = (emu.fnodes.tobytes(), emu.qpairs.tobytes(), emu.ftris.tobytes(), emu.fnormals.tobytes())
+    _, area0 = emu.refit(asm.meshes, np.zeros(len(sc.instances)))
+    assert (emu.fnodes.tobytes(), emu.qpairs.tobytes(), emu.ftris.tobytes(), emu.fnormals.tobytes()) == before
+    assert area0 > 0 and int(emu.level_items.sum()) == emu.n_pairs
+    moved = copy.deepcopy(sc)
+    moved.instances[1].transform = scenes.mat_trs((1.3, 1.4, 1.2), yaw_deg=12.0)  # both stay inside the scene box the tree's grid was laid over
+    moved.instances[3].transform = scenes.mat_trs((2.8, 0.55, 1.4), yaw_deg=-40.0)
+    asm2 = port_oracle.assemble(moved)
+    box, area = emu.refit(asm2.meshes, [0, 1, 0, 1, 0])
+    assert 0.8 * area0 < area < 1.3 * area0
+    emu.asm = asm2
+    _world_tree_check(emu, asm2, moved)
+    a, sa = emu.render(moved.camera, 64, 36, 0, 2, 5, fast=1)
+    fresh = E.EmuScene(asm2, moved)
+    b, sb = fresh.render(moved.camera, 64, 36, 0, 2, 5, fast=1)
+    assert sa["segments"] == sb["segments"]
+    assert H.image_mismatch(a, b, rel=0.0, floor=0.0) <= 0.001
+    # the scene box the host checks against the quantisation grid is the union of the root pair
+    lo = np.minimum(emu.fnodes["mn"][0], emu.fnodes["mn"][1])
+    assert np.array_equal(box[:3], lo)
+
+    def fits_grid(bx):  # cavept_api.cu refit_world: outward rounding must not meet the clamp at 0 / 32767
+        g_lo, g_hi = (bx[:3] - emu.grid[:3]) * emu.grid[3:], (bx[3:] - emu.grid[:3]) * emu.grid[3:]
+        return bool(np.all(g_lo >= 1.0) and np.all(g_hi <= 32766.0))
+
+    assert fits_grid(box)
+    out = copy.deepcopy(sc)
+    out.instances[1].transform = scenes.mat_trs((0.4, 1.5, 1.2), yaw_deg=12.0)  # pokes out of the old scene box: the host must rebuild
+    box_out, _ = emu.refit(port_oracle.assemble(out).meshes, [0, 1, 0, 0, 0])
+    assert not fits_grid(box_out)

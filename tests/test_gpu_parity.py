@@ -251,21 +251,70 @@ def test_mode_gating_mirrors_reference(api, scene_cache):
 
 
 def test_update_instances_equals_fresh_upload(api, scene_cache):
+    """cavept_update_instances refits (no rebuild): same closest hits as a fresh upload of the moved scene, in both
+    refit and forced-rebuild mode; an instance that leaves the tree's quantisation grid falls back to a rebuild."""
     import copy
 
     sc = scene_cache("tiny")
     moved = copy.deepcopy(sc)
-    moved.instances[1].transform = scenes.mat_trs((0.4, 1.5, 1.2), yaw_deg=12.0)
-    moved.instances[3].transform = scenes.mat_trs((3.2, 0.55, 1.4), yaw_deg=-40.0, s=1.2)
-    with _tracer(api, sc, 64, 36, 5, api.TraceMode.FAST) as pt:
-        pt.render(0, 2, sync=True)
-        pt.update_instances(moved.instances)
-        pt.render(0, 2, sync=True)
-        a = pt.read_accum()
+    moved.instances[1].transform = scenes.mat_trs((1.3, 1.4, 1.2), yaw_deg=12.0)  # both stay inside the scene box the tree's grid was laid over
+    moved.instances[3].transform = scenes.mat_trs((2.8, 0.55, 1.4), yaw_deg=-40.0)
     with _tracer(api, moved, 64, 36, 5, api.TraceMode.FAST) as pt:
         pt.render(0, 2, sync=True)
-        b = pt.read_accum()
-    assert a.tobytes() == b.tobytes()
+        fresh = pt.read_accum()
+    for refit in (True, False):
+        with _tracer(api, sc, 64, 36, 5, api.TraceMode.FAST) as pt:
+            pt.set_refit(refit)
+            pt.render(0, 2, sync=True)
+            pt.update_instances(moved.instances)
+            st = pt.stats()
+            assert st["last_update_was_refit"] == (1 if refit else 0) and st["last_update_instances_ms"] > 0
+            pt.render(0, 2, sync=True)
+            a = pt.read_accum()
+            assert np.all(a[..., 3] == 2.0)  # SCENE_DIRTY_WORLD restarted the accumulation
+            H.check_metrics(H.image_metrics(a, fresh), {"exact": 0.999}, f"update_instances_refit_{refit}")
+            pt.update_instances(moved.instances)  # nothing moved: nothing to do, still a dirty frame
+            assert pt.stats()["last_update_instances_ms"] == 0.0
+    far = copy.deepcopy(sc)
+    far.instances[2].transform = scenes.mat_trs((40.0, 1.0, 2.4), yaw_deg=40.0, s=0.7)  # far outside the built tree's grid
+    with _tracer(api, far, 64, 36, 5, api.TraceMode.FAST) as pt:
+        pt.render(0, 2, sync=True)
+        fresh_far = pt.read_accum()
+    with _tracer(api, sc, 64, 36, 5, api.TraceMode.FAST) as pt:
+        pt.update_instances(far.instances)
+        assert pt.stats()["last_update_was_refit"] == 0
+        pt.render(0, 2, sync=True)
+        assert pt.read_accum().tobytes() == fresh_far.tobytes()
+
+
+def test_update_instances_on_the_config3_scene_refits_in_a_fraction_of_a_millisecond(api, scene_cache):
+    """sponza_262144: two of the 25 instances move a little; the refit is kept, the image equals a fresh upload of the
+    moved scene at closest-hit level, and the update costs far less than the 2 ms rebuild (measured figure:
+    profiles/r02_update_instances.json; asserted here with a generous bound so a slow box does not flake)."""
+    import copy
+
+    sc = scene_cache("sponza")
+    moved = copy.deepcopy(sc)
+    for k in (3, 17):
+        t = np.array(moved.instances[k].transform, dtype=np.float32).copy()
+        t[12] += 0.15
+        t[14] -= 0.1
+        moved.instances[k].transform = t
+    w, h = 320, 180
+    with _tracer(api, moved, w, h, 8, api.TraceMode.FAST) as pt:
+        pt.render(0, 2, sync=True)
+        fresh = pt.read_accum()
+        fresh_build_ms = pt.stats()["last_fast_build_ms"]
+    with _tracer(api, sc, w, h, 8, api.TraceMode.FAST) as pt:
+        pt.update_instances(moved.instances)  # first update also measures the built tree's surface-area baseline
+        pt.update_instances(sc.instances)
+        pt.update_instances(moved.instances)
+        st = pt.stats()
+        assert st["last_update_was_refit"] == 1
+        assert st["last_update_instances_ms"] < max(1.0, 0.6 * fresh_build_ms), st
+        pt.render(0, 2, sync=True)
+        a = pt.read_accum()
+    H.check_metrics(H.image_metrics(a, fresh), {"exact": 0.998}, "update_instances_sponza")
 
 
 def test_update_materials(api, port_oracle, scene_cache):
@@ -281,15 +330,26 @@ def test_update_materials(api, port_oracle, scene_cache):
     _pixel_tol(img, want, "update_materials")
 
 
-def test_tonemap_matches_post_process(api, port_oracle, scene_cache):
+def test_tonemap_matches_post_process(api, port_oracle, scene_cache, tmp_path):
     sc = scene_cache("cornell")
     with _tracer(api, sc, 64, 36, 5, api.TraceMode.FAST) as pt:
         pt.render(0, 4, sync=True)
         acc = pt.read_accum()
         tone = pt.read_tonemapped()
         tone8 = pt.read_tonemapped_rgba8()
+        tone16 = pt.read_tonemapped_rgba16f()
+        ppm = str(tmp_path / "frame.ppm")
+        pt.write_ppm(ppm)
+        ms = pt.last_render_ms()
+        assert ms is not None and ms > 0
     want = port_oracle.tonemap(acc)
     assert np.max(np.abs(tone - want)) <= 2e-6
+    # RT_FMT_TONE: the fp32 tone values rounded to nearest-even halves, alpha 1
+    assert np.array_equal(tone16[..., :3], tone[..., :3].astype(np.float16)) and np.all(tone16[..., 3] == np.float16(1.0))
+    raw = open(ppm, "rb").read()
+    head = b"P6\n64 36\n255\n"
+    assert raw.startswith(head) and len(raw) == len(head) + 64 * 36 * 3
+    assert np.array_equal(np.frombuffer(raw[len(head):], dtype=np.uint8).reshape(36, 64, 3), tone8[..., :3])
     assert np.max(np.abs(tone8[..., :3].astype(np.int32) - np.rint(np.clip(want[..., :3], 0, 1) * 255).astype(np.int32))) <= 1
     assert np.all(tone8[..., 3] == 255)
 

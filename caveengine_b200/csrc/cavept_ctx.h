@@ -141,7 +141,7 @@ struct cavept_ctx {
     DevBuf<F4> d_composite;      // group mode: the composited frame (mean, n) on the destination rank(s)
     cavept_group_state* group = nullptr;
     DevBuf<int> d_job_counter;   // job queue of the persistent trace kernel (trace_pool_body.h)
-    int kernel_variant = CAVEPT_KERNEL_QUEUE;
+    int kernel_variant = CAVEPT_KERNEL_PIXEL;  // measured fastest (profiles/r02c: pixel 3775, queue 3331, pool 2533 M segments/s at 256 spp)
     int accum_sums = 0;          // group mode: the accumulator holds (sum, n)
     int n_sms = 0;
     int pool_blocks_depth = -1, pool_blocks_per_sm = 0;  // occupancy of k_trace_pool, cached per stack depth

@@ -69,9 +69,11 @@ enum { CAVEPT_BVH_PARITY = 0, CAVEPT_BVH_FAST = 1, CAVEPT_BVH_LBVH = 2 };
 
 /* Which production kernel CAVEPT_TRACE_FAST launches.  Same tree, same per-pixel arithmetic in the same per-pixel order:
  * the three produce bit-identical images (tests/test_gpu_parity.py).
- * QUEUE (default): persistent warps; a lane owns one pixel at a time for all frames of the launch and draws the next
- *        pixel from a global job queue when it is done (no launch tail);  csrc/trace_body.h body_trace_pixel_fast<kQueue>.
- * PIXEL: one thread per pixel for the whole launch on a grid of pixel tiles (round 1's kernel).
+ * PIXEL (default): one thread per pixel for the whole launch on a grid of pixel tiles; a warp is an 8x4 tile for all
+ *        frames of the launch.  Measured fastest on B200.
+ * QUEUE: persistent warps; a lane owns one pixel at a time for all frames of the launch and draws the next pixel from
+ *        a global job queue when it is done (no launch tail, but a warp's lanes drift onto different tiles: 12 % slower
+ *        at 256 frames per launch);  csrc/trace_body.h body_trace_pixel_fast<kQueue>.
  * POOL:  persistent warps, job queue, TWO pixel streams per lane with the inactive one parked in shared memory
  *        (csrc/trace_pool_body.h) -- measured slower on B200, kept selectable as the experiment it is. */
 enum { CAVEPT_KERNEL_POOL = 0, CAVEPT_KERNEL_PIXEL = 1, CAVEPT_KERNEL_QUEUE = 2 };

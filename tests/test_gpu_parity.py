@@ -592,8 +592,8 @@ def test_high_spp_image_matches_oracle_at_equal_seeds(api, port_oracle, scene_ca
 # ---- the production kernel variants (include/cavept.h CAVEPT_KERNEL_*) ----------------------------------------
 @pytest.mark.parametrize("name,w,h,mb,frames", [("sponza", 640, 360, 8, 4), ("tiny", 101, 57, 5, 6)])
 def test_kernel_variants_are_bitwise_identical(api, scene_cache, name, w, h, mb, frames):
-    """CAVEPT_KERNEL_QUEUE (persistent warps + job queue, the default), CAVEPT_KERNEL_PIXEL (one thread per pixel on a
-    grid of tiles) and CAVEPT_KERNEL_POOL (job queue + two pixel streams per lane) run the same per-pixel arithmetic in
+    """CAVEPT_KERNEL_PIXEL (one thread per pixel on a grid of tiles, the default), CAVEPT_KERNEL_QUEUE (persistent warps +
+    job queue) and CAVEPT_KERNEL_POOL (job queue + two pixel streams per lane) run the same per-pixel arithmetic in
     the same per-pixel order: identical accumulator bytes and segment counts, over two launches and on a ragged image.
     (Node visits may differ by a fraction of a percent: how many speculative steps a lane takes before its parked
     triangles are tested depends on its warp's votes; the closest hit does not.)"""

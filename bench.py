@@ -204,7 +204,7 @@ def main():
     ap.add_argument("--config", type=int, default=3, choices=sorted(CONFIGS), help="BASELINE.json config (3 = the headline, 4 = 1M tris at 4K, 1024 spp)")
     ap.add_argument("--spp", type=int, default=0, help="samples per pixel per step, whole job (default: the config's: 256 / 1024)")
     ap.add_argument("--scaling", default="strong", choices=["strong", "weak"], help="strong: the step's spp are split over the GPUs; weak: every GPU renders all of them")
-    ap.add_argument("--kernel", default="pixel", choices=["queue", "pixel", "pool"], help="production kernel variant (include/cavept.h CAVEPT_KERNEL_*)")
+    ap.add_argument("--kernel", default="pixel", choices=["queue", "pixel", "pool", "wide4"], help="production kernel variant (include/cavept.h CAVEPT_KERNEL_*)")
     ap.add_argument("--trace-mode", default="fast", choices=["fast", "reference_walk"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()

@@ -41,8 +41,9 @@ class TraceMode(enum.IntEnum):
 
 class KernelVariant(enum.IntEnum):
     POOL = 0  # persistent warps + job queue + two pixel streams per lane (experiment; slower)
-    PIXEL = 1  # one thread per pixel for the whole launch (round 1's kernel)
-    QUEUE = 2  # persistent warps drawing pixel jobs from a global queue (default)
+    PIXEL = 1  # one thread per pixel for the whole launch (default: measured fastest of the pair-walk variants)
+    QUEUE = 2  # persistent warps drawing pixel jobs from a global queue
+    WIDE4 = 3  # PIXEL's launch shape over four-wide node records
 
 
 class BvhMode(enum.IntEnum):

@@ -104,6 +104,7 @@ int build_world(cavept_ctx* ctx) {
     CU(ctx, ctx->d_w_root_acc.reserve(12));
     CU(ctx, ctx->d_fnodes.reserve(2 * pairs_cap));
     CU(ctx, ctx->d_qpairs.reserve(pairs_cap));
+    CU(ctx, ctx->d_q4nodes.reserve(pairs_cap));
     CU(ctx, ctx->d_ftris.reserve(P));
     CU(ctx, ctx->d_fnormals.reserve(P));
     ctx->ex.scan_tmp = ctx->d_scan_tmp.ptr;
@@ -141,6 +142,7 @@ int build_world(cavept_ctx* ctx) {
     b.nbox_mx = ctx->d_w_nbox_mx.ptr;
     b.fnodes = ctx->d_fnodes.ptr;
     b.qpairs = ctx->d_qpairs.ptr;
+    b.q4nodes = ctx->d_q4nodes.ptr;
     b.ftris = ctx->d_ftris.ptr;
     b.fnormals = ctx->d_fnormals.ptr;
 
@@ -198,6 +200,7 @@ int refit_world(cavept_ctx* ctx, const std::vector<unsigned char>& moved) {
     b.pad = ctx->world_pad;
     b.fnodes = ctx->d_fnodes.ptr;
     b.qpairs = ctx->d_qpairs.ptr;
+    b.q4nodes = ctx->d_q4nodes.ptr;
     b.ftris = ctx->d_ftris.ptr;
     b.fnormals = ctx->d_fnormals.ptr;
     for (int k = 0; k < 3; ++k) {
@@ -366,7 +369,7 @@ CAVEPT_API void cavept_destroy(cavept_ctx* ctx) {
     if (ctx->group) cavept_group_destroy(ctx);
     if (ctx->ex.stream) cudaStreamSynchronize(ctx->ex.stream);
     ctx->d_vertices.release(); ctx->d_indices.release(); ctx->d_nodes.release(); ctx->d_meshes.release(); ctx->d_materials.release();
-    ctx->d_fnodes.release(); ctx->d_qpairs.release(); ctx->d_ftris.release(); ctx->d_fnormals.release(); ctx->d_inst_prim_off.release(); ctx->d_inst_tri_off.release();
+    ctx->d_fnodes.release(); ctx->d_qpairs.release(); ctx->d_q4nodes.release(); ctx->d_ftris.release(); ctx->d_fnormals.release(); ctx->d_inst_prim_off.release(); ctx->d_inst_tri_off.release();
     ctx->d_prim_bmin.release(); ctx->d_prim_bmax.release(); ctx->d_w_order.release(); ctx->d_w_order_next.release(); ctx->d_w_node_of.release();
     ctx->d_w_node_of_next.release(); ctx->d_w_scan.release(); ctx->d_w_counters.release(); ctx->d_w_flags.release(); ctx->d_w_items.release();
     ctx->d_w_items_next.release(); ctx->d_w_bins.release(); ctx->d_w_root_acc.release();
@@ -630,6 +633,7 @@ static int render_rect(cavept_ctx* ctx, int x0, int y0, int w, int h, int first_
     p.mesh_count = (int)ctx->gpu_meshes.size();
     p.fnodes = ctx->d_fnodes.ptr;
     p.qpairs = ctx->d_qpairs.ptr;
+    p.q4nodes = ctx->d_q4nodes.ptr;
     for (int k = 0; k < 3; ++k) {
         p.grid_origin[k] = ctx->grid_origin[k];
         p.grid_scale[k] = ctx->grid_scale[k];
@@ -672,6 +676,7 @@ static int render_rect(cavept_ctx* ctx, int x0, int y0, int w, int h, int first_
     CU(ctx, cudaEventRecord(ctx->ev0, ctx->ex.stream));
     if (grid_blocks > 0) launch_trace_pool(ctx->ex, p, ctx->count_visits, stack_entries, ctx->d_job_counter.ptr, grid_blocks);
     else if (fast && ctx->kernel_variant == CAVEPT_KERNEL_QUEUE) launch_trace_queue(ctx->ex, p, ctx->count_visits, ctx->d_job_counter.ptr, ctx->n_sms);
+    else if (fast && ctx->kernel_variant == CAVEPT_KERNEL_WIDE4 && ctx->fast_levels <= kWideMaxLevels && ctx->n_pairs > 0) launch_trace_wide(ctx->ex, p, ctx->count_visits);
     else launch_trace(ctx->ex, p, fast, ctx->count_visits);
     CU(ctx, cudaEventRecord(ctx->ev1, ctx->ex.stream));
     ctx->dirty = false;
@@ -841,7 +846,7 @@ CAVEPT_API int cavept_set_refit(cavept_ctx* ctx, int enable) {
 
 CAVEPT_API int cavept_set_kernel_variant(cavept_ctx* ctx, int variant) {
     if (!ctx) return CAVEPT_ERR_INVALID_ARG;
-    if (variant != CAVEPT_KERNEL_POOL && variant != CAVEPT_KERNEL_PIXEL && variant != CAVEPT_KERNEL_QUEUE) return fail(ctx, CAVEPT_ERR_INVALID_ARG, "invalid kernel variant %d", variant);
+    if (variant != CAVEPT_KERNEL_POOL && variant != CAVEPT_KERNEL_PIXEL && variant != CAVEPT_KERNEL_QUEUE && variant != CAVEPT_KERNEL_WIDE4) return fail(ctx, CAVEPT_ERR_INVALID_ARG, "invalid kernel variant %d", variant);
     ctx->kernel_variant = variant;
     return CAVEPT_OK;
 }

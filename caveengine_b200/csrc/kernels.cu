@@ -348,6 +348,39 @@ __global__ void __launch_bounds__(128, 8) k_trace(const TraceParams p) {
     }
 }
 
+// ---- the per-pixel body over the four-wide records (CAVEPT_KERNEL_WIDE4): same grid, same stack, half the
+//      dependent node fetches per segment.
+template<bool kCount>
+__global__ void __launch_bounds__(128, 8) k_trace_wide(const TraceParams p) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int x = p.tile_x0 + blockIdx.x * 16 + (warp & 1) * 8 + (lane & 7);
+    const int y = p.tile_y0 + blockIdx.y * 8 + (warp >> 1) * 4 + (lane >> 3);
+    if (p.tile_x1 > 0 && (x >= p.tile_x1 || y >= p.tile_y1)) x = p.width;
+    unsigned long long cnt[3] = { 0ull, 0ull, 0ull };
+    __shared__ int s_stack[kStackSize * 128];
+    int spill[kWideSpill];  // local memory; touched only when a walk defers more than kStackSize nodes
+    unsigned int segs = body_trace_pixel_fast<kCount, kStepQuorum, kShadeBatch, false, true>(p, x, y, s_stack + threadIdx.x, 128, cnt, nullptr, spill);
+    segs = __reduce_add_sync(0xffffffffu, segs);
+    if (lane == 0 && segs) atomicAdd(&p.counters[0], (unsigned long long)segs);
+    if (kCount) {
+#pragma unroll
+        for (int k = 1; k < 3; ++k) {
+            unsigned long long v = cnt[k];
+#pragma unroll
+            for (int d = 16; d > 0; d >>= 1) v += __shfl_down_sync(0xffffffffu, v, d);
+            if (lane == 0 && v) atomicAdd(&p.counters[k], v);
+        }
+    }
+}
+void launch_trace_wide(CudaExec& ex, const TraceParams& p, bool count_visits) {
+    const int tw = p.tile_x1 > 0 ? p.tile_x1 - p.tile_x0 : p.width, th = p.tile_x1 > 0 ? p.tile_y1 - p.tile_y0 : p.height;
+    const dim3 grid((tw + 15) / 16, (th + 7) / 8, 1), block(128, 1, 1);
+    if (count_visits) k_trace_wide<true><<<grid, block, 0, ex.stream>>>(p);
+    else k_trace_wide<false><<<grid, block, 0, ex.stream>>>(p);
+    ex.note(cudaGetLastError());
+    ++ex.launches;
+}
+
 // ---- second-generation production kernel: persistent warps + job queue + two pixel streams per lane
 //      (trace_pool_body.h).  Grid = SMs x resident blocks; dynamic shared memory = the lane-strided
 //      traversal stack ([stack_entries][128] ints) followed by the record pool ([38][128] floats).

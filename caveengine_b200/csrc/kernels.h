@@ -47,6 +47,8 @@ int run_build_lbvh(CudaExec& ex, WBuild b, WReport* report);
 void run_refit_wbvh(CudaExec& ex, WBuild b, const int* level_start, int n_levels, const unsigned char* d_moved, float* d_area_sum, float out[7]);
 
 void launch_trace(CudaExec& ex, const TraceParams& p, bool fast, bool count_visits);
+// the per-pixel body over the four-wide records (CAVEPT_KERNEL_WIDE4; p.q4nodes must be set)
+void launch_trace_wide(CudaExec& ex, const TraceParams& p, bool count_visits);
 // the per-pixel body as a persistent launch drawing pixel jobs from a global queue (CAVEPT_KERNEL_QUEUE)
 void launch_trace_queue(CudaExec& ex, const TraceParams& p, bool count_visits, int* job_counter, int n_sms);
 // persistent job-queue kernel (trace_pool_body.h); stack_entries = tree levels + 2, grid_blocks = SMs x resident blocks

@@ -54,6 +54,21 @@ struct alignas(32) QPair {
     int r0, r1;
 };
 static_assert(sizeof(QPair) == 32, "QPair");
+
+// Four-wide node (CAVEPT_KERNEL_WIDE4): record k is sibling pair k with interior children replaced by THEIR pairs,
+// largest box first, until there are four children or only leaves (wbvh_body.h wb_body_q4).  Same 15-bit grid and
+// plane packing as QPair (child c: q[3c .. 3c+2]); r[c] = child reference (interior = index of the child's own record =
+// its pair index, so QPair k and Q4Node k root the same subtree; leaf reference; kRefSentinel with an inverted box
+// for an unused slot).  64 bytes = two 256-bit loads from one line: half the dependent fetch rounds of the pair walk.
+struct alignas(64) Q4Node {
+    uint32_t q[12];
+    int r[4];
+};
+static_assert(sizeof(Q4Node) == 64, "Q4Node");
+// A four-wide step defers up to three children, so a walk can need 1.5 x the tree's levels of stack; entries past
+// the shared-memory stack go to a small per-thread spill array (never touched on the scenes measured).
+constexpr int kWideSpill = 64;
+constexpr int kWideMaxLevels = ((kStackSize + kWideSpill - 4) * 2) / 3;  // deeper trees use the pair walk
 constexpr float kGridCells = 32767.0f;
 constexpr uint32_t kSelLo = 0x7104u, kSelHi = 0x7324u, kSelFlip = 0x0220u;  // __byte_perm selectors: low / high half -> bytes 1..2
 
@@ -81,6 +96,7 @@ struct TraceParams {
     // production layout
     const FastNode* fnodes;  // fp32 boxes as built (read-back / tests); the tracer reads qpairs
     const QPair* qpairs;
+    const Q4Node* q4nodes;                // four-wide records over the same tree (CAVEPT_KERNEL_WIDE4); may be null otherwise
     float grid_origin[3], grid_scale[3];  // grid coordinate = (world - origin) * scale, in [0, 32767]
     const FastTri* ftris;
     const FastTri* fnormals;  // per FastTri slot: the three world-transformed vertex normals, v0.w = instance, v1.w = material
@@ -282,6 +298,7 @@ int warp_emu_draw(int* counter, bool want);
 struct Walk {
     int* stack;
     int stride;
+    int* spill;      // four-wide walk only: entries kStackSize.. of the stack (per-thread local memory)
     int sp;          // entries in shared memory; entry 0 holds the sentinel
     int top;         // the top of the stack lives in a register: a pop never waits for shared memory
     int ref;         // node reference being processed (interior, leaf, or the sentinel)
@@ -379,6 +396,78 @@ CV_D void walk_step(const TraceParams& p, Walk& w, float ray_t, unsigned long lo
     w.ref = none ? w.top : near_ref;
     w.top = both ? far_ref : (none ? below : w.top);
     w.sp += both ? 1 : (none ? -1 : 0);
+}
+
+// ---- four-wide walk (Q4Node) ------------------------------------------------------------------------------
+CV_D void wide_store(Walk& w, int idx, int v) {
+    if (idx < kStackSize) w.stack[idx * w.stride] = v; else w.spill[idx - kStackSize] = v;
+}
+CV_D int wide_load(const Walk& w, int idx) { return idx < kStackSize ? w.stack[idx * w.stride] : w.spill[idx - kStackSize]; }
+CV_D int walk_pop_wide(Walk& w) {
+    const int r = w.top;
+    --w.sp;
+    w.top = wide_load(w, w.sp);
+    return r;
+}
+CV_D void walk_park_leaf_wide(Walk& w) {
+    if (w.ref < 0 && w.q1 == 0) {
+        if (w.q0 == 0) w.q0 = w.ref; else w.q1 = w.ref;
+        w.ref = walk_pop_wide(w);
+    }
+}
+// compare-exchange of (entry distance, reference): afterwards a is the nearer
+CV_HD void wide_order(float& ka, int& ra, float& kb, int& rb) {
+    const bool swap = kb < ka;
+    const float k0 = swap ? kb : ka, k1 = swap ? ka : kb;
+    const int r0 = swap ? rb : ra, r1 = swap ? ra : rb;
+    ka = k0; ra = r0; kb = k1; rb = r1;
+}
+// One four-wide step: two 256-bit loads, four slab tests (same planes and selectors as walk_step), the hit children
+// sorted by entry distance; descend into the nearest and defer the others farthest-first, so pops come nearest-first.
+template<bool kCount>
+CV_D void walk_step_wide(const TraceParams& p, Walk& w, float ray_t, unsigned long long* cnt) {
+    const Q4Node* node = p.q4nodes + w.ref;
+    const F8 a = ld256(node);            // q[0..7]
+    const F8 b = ld256(&node->q[8]);     // q[8..11], r[0..3]
+    if (kCount) cnt[1] += 4;
+    const uint32_t far_x = w.near_x ^ kSelFlip, far_y = w.near_y ^ kSelFlip, far_z = w.near_z ^ kSelFlip;
+    const uint32_t qw[12] = { f2u(a.a), f2u(a.b), f2u(a.c), f2u(a.d), f2u(a.e), f2u(a.f), f2u(a.g), f2u(a.h), f2u(b.a), f2u(b.b), f2u(b.c), f2u(b.d) };
+    float key[4];
+    int ref[4] = { (int)f2u(b.e), (int)f2u(b.f), (int)f2u(b.g), (int)f2u(b.h) };
+    int n_hit = 0;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+        const float nx = cv_fma(q_sel(qw[3 * c], w.near_x), w.inv.x, w.oinv.x), fx = cv_fma(q_sel(qw[3 * c], far_x), w.inv.x, w.oinv.x);
+        const float ny = cv_fma(q_sel(qw[3 * c + 1], w.near_y), w.inv.y, w.oinv.y), fy = cv_fma(q_sel(qw[3 * c + 1], far_y), w.inv.y, w.oinv.y);
+        const float nz = cv_fma(q_sel(qw[3 * c + 2], w.near_z), w.inv.z, w.oinv.z), fz = cv_fma(q_sel(qw[3 * c + 2], far_z), w.inv.z, w.oinv.z);
+        const float tn = fmaxf(fmaxf(nx, ny), fmaxf(nz, 0.0f)), tf = fminf(fminf(fx, fy), fminf(fz, ray_t));
+        const bool h = tn <= tf;
+        key[c] = h ? tn : CV_INF;
+        n_hit += h ? 1 : 0;
+    }
+    wide_order(key[0], ref[0], key[1], ref[1]);
+    wide_order(key[2], ref[2], key[3], ref[3]);
+    wide_order(key[0], ref[0], key[2], ref[2]);
+    wide_order(key[1], ref[1], key[3], ref[3]);
+    wide_order(key[1], ref[1], key[2], ref[2]);
+    // stack: old top spilled to entry sp, then the deferred children farthest first, the nearest of them in `top`
+    const int up1 = n_hit == 4 ? ref[3] : ref[2];
+    int below;
+    if (w.sp + 2 < kStackSize) {  // the usual case: every slot touched is in shared memory; branch-free as in walk_step
+        w.stack[w.sp * w.stride] = w.top;
+        below = w.stack[(w.sp - 1) * w.stride];
+        w.stack[(w.sp + 1) * w.stride] = up1;
+        w.stack[(w.sp + 2) * w.stride] = ref[2];
+    } else {
+        wide_store(w, w.sp, w.top);
+        below = wide_load(w, w.sp - 1);
+        if (n_hit >= 3) wide_store(w, w.sp + 1, up1);
+        if (n_hit == 4) wide_store(w, w.sp + 2, ref[2]);
+    }
+    const int old_top = w.top;
+    w.ref = n_hit > 0 ? ref[0] : old_top;
+    w.top = n_hit >= 2 ? ref[1] : (n_hit == 1 ? old_top : below);
+    w.sp += n_hit - 1;
 }
 
 // One triangle of the oldest postponed leaf.  World-space vertices: for an identity
@@ -620,8 +709,31 @@ CV_D int trace_draw_jobs(int* counter, bool want) {
 // kQueue = false: the lane owns pixel (x, y) for the whole launch (grid of pixel tiles).
 // kQueue = true:  persistent launch; (x, y) is the lane's first job (x >= width: none yet) and finished pixels are
 //                 replaced from the job queue.
-template<bool kCount, int kQuorum = kStepQuorum, int kBatch = kShadeBatch, bool kQueue = false>
-CV_D unsigned int body_trace_pixel_fast(const TraceParams& p, int x, int y, int* stack, int stride, unsigned long long* cnt, int* job_counter = nullptr) {
+//
+// kWide: the four-wide walk over Q4Node records (walk_step_wide) instead of the pair walk; everything else is shared.
+#ifndef CV_WIDE_TIGHT_STEPS
+#define CV_WIDE_TIGHT_STEPS 3
+#endif
+#ifndef CV_WIDE_MINORITY_STEPS
+#define CV_WIDE_MINORITY_STEPS 2
+#endif
+#ifndef CV_WIDE_PARK_EVERY
+#define CV_WIDE_PARK_EVERY 1
+#endif
+template<bool kCount, bool kWide>
+CV_D void walk_step_any(const TraceParams& p, Walk& w, float ray_t, unsigned long long* cnt) {
+    if (kWide) walk_step_wide<kCount>(p, w, ray_t, cnt); else walk_step<kCount>(p, w, ray_t, cnt);
+}
+template<bool kWide>
+CV_D void walk_park_any(Walk& w) {
+    if (kWide) walk_park_leaf_wide(w); else walk_park_leaf(w);
+}
+
+template<bool kCount, int kQuorum = kStepQuorum, int kBatch = kShadeBatch, bool kQueue = false, bool kWide = false>
+CV_D unsigned int body_trace_pixel_fast(const TraceParams& p, int x, int y, int* stack, int stride, unsigned long long* cnt, int* job_counter = nullptr, int* spill = nullptr) {
+    constexpr int kTight = kWide ? CV_WIDE_TIGHT_STEPS : CV_TIGHT_STEPS;
+    constexpr int kMinority = kWide ? CV_WIDE_MINORITY_STEPS : CV_MINORITY_STEPS;
+    constexpr int kParkEvery = kWide ? CV_WIDE_PARK_EVERY : CV_PARK_EVERY;
     const bool valid = x < p.width && y < p.height && p.n_frames > 0;
     size_t pix = valid ? (size_t)y * (size_t)p.width + (size_t)x : 0;
     Ray ray;
@@ -636,6 +748,7 @@ CV_D unsigned int body_trace_pixel_fast(const TraceParams& p, int x, int y, int*
     Walk w;
     w.stack = stack;
     w.stride = stride;
+    w.spill = spill;
     ray.origin = f3(0, 0, 0);
     ray.direction = f3(0, 0, 1);
     ray.inv_dir = f3(0, 0, 1);
@@ -646,16 +759,16 @@ CV_D unsigned int body_trace_pixel_fast(const TraceParams& p, int x, int y, int*
     for (;;) {
         // ---- A, the tight loop: one ballot per step while a quorum can step -----------------
         for (;;) {
-            walk_park_leaf(w);
+            walk_park_any<kWide>(w);
             const bool can_step = ref_is_interior(w.ref);
             if (CV_WARP_COUNT(can_step) < kQuorum) break;
-            if (can_step) walk_step<kCount>(p, w, ray.t, cnt);
+            if (can_step) walk_step_any<kCount, kWide>(p, w, ray.t, cnt);
             // second step of the trip without a vote of its own (measured +2 %): the lanes that can
             // still step do, the others would have idled through it anyway
 #pragma unroll
-            for (int k = 1; k < CV_TIGHT_STEPS; ++k) {
-                if ((k % CV_PARK_EVERY) == 0) walk_park_leaf(w);
-                if (ref_is_interior(w.ref)) walk_step<kCount>(p, w, ray.t, cnt);
+            for (int k = 1; k < kTight; ++k) {
+                if ((k % kParkEvery) == 0) walk_park_any<kWide>(w);
+                if (ref_is_interior(w.ref)) walk_step_any<kCount, kWide>(p, w, ray.t, cnt);
             }
         }
         // ---- the vote ------------------------------------------------------------------------
@@ -730,11 +843,11 @@ CV_D unsigned int body_trace_pixel_fast(const TraceParams& p, int x, int y, int*
                 if (done || (kQueue && vacant)) w.ref = kRefSentinel;
             }
         } else {
-            if (can_step) walk_step<kCount>(p, w, ray.t, cnt);
+            if (can_step) walk_step_any<kCount, kWide>(p, w, ray.t, cnt);
 #pragma unroll
-            for (int k = 1; k < CV_MINORITY_STEPS; ++k) {
-                if ((k % CV_PARK_EVERY) == 0) walk_park_leaf(w);
-                if (ref_is_interior(w.ref)) walk_step<kCount>(p, w, ray.t, cnt);
+            for (int k = 1; k < kMinority; ++k) {
+                if ((k % kParkEvery) == 0) walk_park_any<kWide>(w);
+                if (ref_is_interior(w.ref)) walk_step_any<kCount, kWide>(p, w, ray.t, cnt);
             }
         }
     }

@@ -97,6 +97,7 @@ struct WBuild {
     // outputs
     FastNode* fnodes;
     QPair* qpairs;  // quantised copy of fnodes, what the tracer fetches
+    Q4Node* q4nodes;  // four-wide records over the same tree (null: not built)
     float grid_origin[3], grid_scale[3];
     FastTri* ftris;
     FastTri* fnormals;
@@ -469,6 +470,54 @@ CV_D void wb_body_quantise(const WBuild& b, int k, int n_pairs) {
     b.qpairs[k] = o;
 }
 
+// ---- four-wide records: Q4Node k = pair k with interior children replaced by their own pairs, largest box first,
+//      until there are four children or only leaves.  One independent thread per pair: every pair gets a record, so
+//      an interior child's reference is simply its pair index, and QPair k / Q4Node k root the same subtree.  Records
+//      of unused pair slots (the LBVH builder leaves holes) are never referenced; their garbage is bounds-checked.
+CV_D void wb_body_q4(const WBuild& b, int k, int n_pairs) {
+    if (k >= n_pairs) return;
+    FastNode ch[4];
+    ch[0] = b.fnodes[2 * k];
+    ch[1] = b.fnodes[2 * k + 1];
+    int n = 2;
+    while (n < 4) {
+        int best = -1;
+        float best_area = -1.0f;
+        for (int i = 0; i < n; ++i) {
+            const int r = ch[i].a;
+            if (!ref_is_interior(r) || (uint32_t)r + 1u >= 2u * (uint32_t)n_pairs) continue;
+            const float ex = ch[i].mx[0] - ch[i].mn[0], ey = ch[i].mx[1] - ch[i].mn[1], ez = ch[i].mx[2] - ch[i].mn[2];
+            const float area = ex * ey + ey * ez + ez * ex;
+            if (area > best_area) {
+                best_area = area;
+                best = i;
+            }
+        }
+        if (best < 0) break;
+        const int r = ch[best].a;
+        FastNode c0 = b.fnodes[r], c1 = b.fnodes[r + 1];
+        // replace the expanded child in place, its sibling goes to the end (dynamic indexing kept out of registers' way)
+        for (int i = 0; i < 4; ++i) {
+            if (i == best) ch[i] = c0;
+            if (i == n) ch[i] = c1;
+        }
+        ++n;
+    }
+    Q4Node o;
+    for (int c = 0; c < 4; ++c) {
+        if (c < n) {
+            for (int a = 0; a < 3; ++a)
+                o.q[3 * c + a] = wb_grid_lo(ch[c].mn[a], b.grid_origin[a], b.grid_scale[a]) | (wb_grid_hi(ch[c].mx[a], b.grid_origin[a], b.grid_scale[a]) << 16);
+            o.r[c] = wb_quantised_ref(ch[c].a);
+        } else {
+            for (int a = 0; a < 3; ++a) o.q[3 * c + a] = 32767u;  // min plane 32767, max plane 0: never hit
+            o.r[c] = kRefSentinel;
+        }
+    }
+    b.q4nodes[k] = o;
+}
+struct FnWbQ4 { WBuild b; int n; CV_D void operator()(int i) const { wb_body_q4(b, i, n); } };
+
 // ---- refit: instance transforms changed, topology kept ---------------------------
 // The reference re-uploads M x 144 bytes of GpuPtMesh on SCENE_DIRTY_WORLD and never touches a BVH
 // (cave/engine/renderer/path_tracer/path_tracer.cpp:162-199): its per-mesh trees live in mesh space.  The production
@@ -540,6 +589,7 @@ void refit_wbvh(Exec& ex, WBuild b, const int* level_start, int n_levels, const 
     ex.fill(d_area_sum, 0, sizeof(float));
     ex.launch(b.n_prims, FnWbRetransform{ b, d_moved });
     for (int L = n_levels - 1; L >= 0; --L) ex.launch(level_start[L + 1] - level_start[L], FnWbRefitPair{ b, level_start[L], d_area_sum });
+    if (b.q4nodes) ex.launch(level_start[n_levels], FnWbQ4{ b, level_start[n_levels] });
     FastNode root[2];
     ex.download(root, b.fnodes, sizeof(root));
     for (int c = 0; c < 3; ++c) {
@@ -942,6 +992,7 @@ int build_wbvh(Exec& ex, WBuild b, WReport* rep) {
     }
     ex.launch(b.n_prims, FnWbEmit{ b });
     ex.launch(rep->n_pairs, FnWbQuantise{ b, rep->n_pairs });
+    if (b.q4nodes) ex.launch(rep->n_pairs, FnWbQ4{ b, rep->n_pairs });
     return 0;
 }
 
@@ -993,6 +1044,7 @@ int build_lbvh(Exec& ex, WBuild b, WReport* rep) {
         rep->levels = k_last + 1;
         rep->n_pairs = 1 << (k_last + 1);  // heap slots in use (leaf positions are holes)
     }
+    if (b.q4nodes) ex.launch(rep->n_pairs, FnWbQ4{ b, rep->n_pairs });
     ex.launch(b.n_prims, FnWbEmit{ b });
     return 0;
 }

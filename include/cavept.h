@@ -68,15 +68,19 @@ enum { CAVEPT_TRACE_FAST = 0, CAVEPT_TRACE_REFERENCE_WALK = 1 };
 enum { CAVEPT_BVH_PARITY = 0, CAVEPT_BVH_FAST = 1, CAVEPT_BVH_LBVH = 2 };
 
 /* Which production kernel CAVEPT_TRACE_FAST launches.  Same tree, same per-pixel arithmetic in the same per-pixel order:
- * the three produce bit-identical images (tests/test_gpu_parity.py).
+ * POOL, PIXEL and QUEUE produce bit-identical images (tests/test_gpu_parity.py).
  * PIXEL (default): one thread per pixel for the whole launch on a grid of pixel tiles; a warp is an 8x4 tile for all
  *        frames of the launch.  Measured fastest on B200.
  * QUEUE: persistent warps; a lane owns one pixel at a time for all frames of the launch and draws the next pixel from
  *        a global job queue when it is done (no launch tail, but a warp's lanes drift onto different tiles: 12 % slower
  *        at 256 frames per launch);  csrc/trace_body.h body_trace_pixel_fast<kQueue>.
  * POOL:  persistent warps, job queue, TWO pixel streams per lane with the inactive one parked in shared memory
- *        (csrc/trace_pool_body.h) -- measured slower on B200, kept selectable as the experiment it is. */
-enum { CAVEPT_KERNEL_POOL = 0, CAVEPT_KERNEL_PIXEL = 1, CAVEPT_KERNEL_QUEUE = 2 };
+ *        (csrc/trace_pool_body.h) -- measured slower on B200, kept selectable as the experiment it is.
+ * WIDE4: PIXEL's launch shape over four-wide node records (each sibling pair with its interior children replaced by their
+ *        own pairs: 64 bytes, two loads from one line, four slab tests, children sorted by entry distance): half the
+ *        dependent node fetches per segment.  Same closest hits; a lane's visit order differs, so an image can differ
+ *        from the pair walk's where two triangles tie in t (tests/test_gpu_parity.py states the bound). */
+enum { CAVEPT_KERNEL_POOL = 0, CAVEPT_KERNEL_PIXEL = 1, CAVEPT_KERNEL_QUEUE = 2, CAVEPT_KERNEL_WIDE4 = 3 };
 
 typedef struct cavept_config {
     int device;     /* CUDA ordinal; -1 = current device */

@@ -93,6 +93,11 @@ EMU_API int emu_bvh_build(const GpuPtVertex* vertices, const GpuPtIndex* indices
     return rc;
 }
 
+// The four-wide records (Q4Node, n_prims + 8 of them) the next emu_wbvh_build / emu_wbvh_refit writes and emu_render
+// (fast == 4) walks; null = not built.  A binding instead of one more argument on three entry points.
+static Q4Node* g_q4nodes = nullptr;
+EMU_API void emu_bind_q4(Q4Node* q4nodes) { g_q4nodes = q4nodes; }
+
 // Production (world-space) BVH exactly as cavept_api.cu builds it.  inst_prim_off has
 // n_inst + 1 entries, inst_tri_off n_inst.  fnodes needs 2 * (n_prims + 8) entries, qpairs n_prims + 8, ftris /
 // fnormals n_prims.  Returns 0 ok; report = {levels, n_pairs, root_ref, error_bits}.
@@ -140,6 +145,7 @@ EMU_API int emu_wbvh_build(const GpuPtVertex* vertices, const GpuPtIndex* indice
     b.root_acc = root_acc.data();
     b.fnodes = fnodes;
     b.qpairs = qpairs;
+    b.q4nodes = g_q4nodes;
     b.ftris = ftris;
     b.fnormals = fnormals;
     EmuExec ex;
@@ -175,6 +181,7 @@ EMU_API void emu_wbvh_refit(const GpuPtVertex* vertices, const GpuPtIndex* indic
     b.pad = pad;
     b.fnodes = fnodes;
     b.qpairs = qpairs;
+    b.q4nodes = g_q4nodes;
     b.ftris = ftris;
     b.fnormals = fnormals;
     for (int k = 0; k < 3; ++k) {
@@ -210,6 +217,7 @@ static TraceParams emu_params(const GpuPtVertex* vertices, const GpuPtIndex* ind
     p.mesh_count = mesh_count;
     p.fnodes = fnodes;
     p.qpairs = qpairs;
+    p.q4nodes = g_q4nodes;
     for (int k = 0; k < 3; ++k) {
         p.grid_origin[k] = grid[k];
         p.grid_scale[k] = grid[3 + k];
@@ -269,9 +277,11 @@ EMU_API long long emu_render(const GpuPtVertex* vertices, const GpuPtIndex* indi
         }
         return segs;
     }
+    int spill[kWideSpill];
     for (int y = 0; y < height; ++y) {
         for (int x = 0; x < width; ++x) {
-            segs += fast ? body_trace_pixel_fast<true>(p, x, y, stack, 1, cnt) : body_trace_pixel_reference<true>(p, x, y, cnt);
+            if (fast == 4) segs += body_trace_pixel_fast<true, kStepQuorum, kShadeBatch, false, true>(p, x, y, stack, 1, cnt, nullptr, spill);  // four-wide walk (k_trace_wide)
+            else segs += fast ? body_trace_pixel_fast<true>(p, x, y, stack, 1, cnt) : body_trace_pixel_reference<true>(p, x, y, cnt);
         }
     }
     if (counters) {

@@ -91,6 +91,8 @@ class EmuScene:
         self.n_prims = P
         self.fnodes = np.zeros(2 * (P + 8), dtype=FASTNODE_DT)
         self.qpairs = np.zeros((P + 8, 8), dtype=np.uint32)  # QPair: q[6], r0, r1
+        self.q4nodes = np.zeros((P + 8, 16), dtype=np.uint32)  # Q4Node: q[12], r[4]
+        self.lib.emu_bind_q4(_p(self.q4nodes))
         self.grid = np.zeros(6, dtype=np.float32)            # origin xyz, scale xyz
         self.ftris = np.zeros(P, dtype=FASTTRI_DT)
         self.fnormals = np.zeros(P, dtype=FASTTRI_DT)
@@ -108,6 +110,7 @@ class EmuScene:
         `moved` = one flag per instance.  Returns (scene box min/max, surface-area sum)."""
         moved = np.ascontiguousarray(moved, dtype=np.uint8)
         out = np.zeros(7, dtype=np.float32)
+        self.lib.emu_bind_q4(_p(self.q4nodes))
         self.lib.emu_wbvh_refit(_p(self.asm.vertices), _p(self.asm.indices), _p(meshes), C.c_int(meshes.shape[0]), C.c_int(self.n_prims), C.c_float(self.pad), _p(self.grid),
                                 _p(self.level_items), C.c_int(len(self.level_items)), _p(moved), _p(self.fnodes), _p(self.qpairs), _p(self.ftris), _p(self.fnormals), _p(out))
         return out[:6].copy(), float(out[6])
@@ -120,6 +123,7 @@ class EmuScene:
         cam = _cam(camera)
         counters = (C.c_ulonglong * 3)()
         a = self.asm
+        self.lib.emu_bind_q4(_p(self.q4nodes))
         segs = self.lib.emu_render(_p(a.vertices), _p(a.indices), _p(self.nodes), _p(a.meshes), C.c_int(a.meshes.shape[0]), _p(a.materials), _p(self.fnodes),
                                    _p(self.qpairs), _p(self.grid), _p(self.ftris), _p(self.fnormals), C.c_int(self.root_ref), C.byref(cam), C.c_int(max_bounce), C.c_int(width),
                                    C.c_int(height), C.c_int(first_frame), C.c_int(n_frames), C.c_int(1 if reset_first else 0), _p(accum), C.c_int(int(fast)),

@@ -336,6 +336,44 @@ def test_queue_kernel_on_real_warps_terminates_and_equals_the_per_pixel_body(por
         assert b2[~inside].tobytes() == b[~inside].tobytes()
 
 
+@pytest.mark.parametrize("name,w,h,mb", [("tiny", 61, 35, 5), ("cornell", 64, 36, 5), ("heightfield", 48, 27, 5)])
+def test_four_wide_walk_finds_the_same_hits_in_half_the_steps(port_oracle, scene_cache, name, w, h, mb):
+    """CAVEPT_KERNEL_WIDE4: Q4Node k = sibling pair k with its interior children replaced by their pairs
+    (wbvh_body.h wb_body_q4), walked by walk_step_wide (trace_body.h).  Same closest hits as the pair walk -> the same
+    image and segment count; every record's child boxes contain the fp32 boxes of the nodes they were made from; the
+    number of dependent node fetches (steps) per segment drops to about half while the boxes tested stay about equal."""
+    sc = scene_cache(name)
+    asm = port_oracle.assemble(sc)
+    emu = E.EmuScene(asm, sc)
+    a, sa = emu.render(sc.camera, w, h, 0, 2, mb, fast=1)
+    b, sb = emu.render(sc.camera, w, h, 0, 2, mb, fast=4)
+    assert sa["segments"] == sb["segments"]
+    assert a.tobytes() == b.tobytes()
+    steps_pair, steps_wide = sa["node_visits"] / 2, sb["node_visits"] / 4
+    assert steps_wide <= 0.62 * steps_pair
+    assert sb["node_visits"] <= 1.2 * sa["node_visits"]
+    # structure: children of record k are a cut through the subtree of pair k
+    q4 = emu.q4nodes[:emu.n_pairs]
+    fn = emu.fnodes
+    go, gs = emu.grid[:3], emu.grid[3:]
+    for k in range(0, emu.n_pairs, max(1, emu.n_pairs // 200)):
+        refs = q4[k, 12:].view(np.int32)
+        live = [int(r) for r in refs if r != 0x7fffffff]
+        assert 2 <= len(live) <= 4
+        # expand pair k the same way on the host: the leaves below the record's children partition pair k's leaves
+        def leaves(ref):  # ref in the quantised numbering (pair index / leaf ref)
+            if ref < 0:
+                return [ref]
+            out = []
+            for s in (0, 1):
+                a_ = int(fn[2 * ref + s]["a"])
+                out += leaves(a_ >> 1 if a_ >= 0 else a_)
+            return out
+        want = sorted(leaves(k))
+        got = sorted(sum((leaves(r) for r in live), []))
+        assert got == want
+
+
 def test_refit_reproduces_the_tree_and_follows_moved_instances(port_oracle, scene_cache):
     """wbvh_body.h refit_wbvh (what cavept_update_instances runs instead of a rebuild): with nothing moved the
     bottom-up pass reproduces fnodes / qpairs / ftris bit for bit; with two instances moved, the refitted tree returns

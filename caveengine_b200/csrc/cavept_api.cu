@@ -225,7 +225,9 @@ int refit_world(cavept_ctx* ctx, const std::vector<unsigned char>& moved) {
         const float g_lo = (lo - ctx->grid_origin[c]) * ctx->grid_scale[c], g_hi = (hi - ctx->grid_origin[c]) * ctx->grid_scale[c];
         if (!(g_lo >= 1.0f && g_hi <= kGridCells - 1.0f)) inside = false;  // outward rounding must not meet the clamp at 0 / 32767
     }
-    if (!inside || extent > ctx->world_extent * 1.0000001f + 1e-30f) return 0;  // the padding was derived from the old extent
+    // the padding was derived from the old extent (pad = extent * 2^-20 against ~2^-23 of slab-test rounding: 8x slack), and
+    // the refitted root box itself carries the pad, so a scene that has not grown reads extent * (1 + 2^-20) here
+    if (!inside || extent > ctx->world_extent * 1.001f + 1e-30f) return 0;
     if (!(out[6] <= kRefitQuality * ctx->area_baseline)) return 0;
     return 1;
 }

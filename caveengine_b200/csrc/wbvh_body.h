@@ -27,6 +27,10 @@
 namespace cavept {
 
 constexpr int kWBins = 16;
+#ifndef CV_WB_AXES
+#define CV_WB_AXES 3
+#endif
+constexpr int kWAxes = CV_WB_AXES;  // 3: every axis is binned and the SAH sweep takes the cheapest plane of all three; 1: the axis of largest centroid extent only
 constexpr int kWLevelBase = 4;     // counters[4 + L] = interior items of level L (the level loop never reads them back one by one)
 constexpr int kWMaxLevels = 124;   // counters holds 4 + 124 + 4 ints
 constexpr int kWMedianDepth = 48;  // safety net: positional median splits below this depth
@@ -37,15 +41,15 @@ struct WBin {
     uint32_t cmn[3], cmx[3];  // ordered keys of the centroid bounds
 };
 struct WBins {
-    WBin b[kWBins];
+    WBin b[kWAxes * kWBins];  // [axis slot][bin]; with kWAxes == 1 the single slot holds the axis of largest centroid extent
 };
 
 struct WItem {
     int start, count;  // segment of `order`
     int pair;          // children go to fnodes[2*pair], fnodes[2*pair + 1]
     int depth;
-    int axis;          // binning axis; -1: positional median split
-    float cmin, cscale;
+    int axis;          // >= 0: binned (after the split pass: the axis of the chosen plane); -1: positional median split
+    float cmin[3], cscale[3];  // per axis: bin = (centre - cmin) * cscale (cscale 0: no extent, everything in bin 0)
     int split;         // left child = bins [0, split]
     int n_left;
     int child_item[2];  // index of each child in the next level, -1 if it is a leaf
@@ -174,10 +178,10 @@ CV_D void wb_body_init(const WBuild& b, int p) {
 }
 
 // ---- per level ----------------------------------------------------------------------------
-// thread j: bin j % 16 of item j / 16 is cleared; the first thread of an item also picks its axis
+// thread j: bin j % (kWAxes * 16) of item j / (kWAxes * 16) is cleared; the first thread of an item also sets up its binning
 CV_D void wb_body_prep(const WBuild& b, int j, int level) {
     const int n_items = b.counters[kWLevelBase + level];  // written by the level above; launches are sized by an upper bound
-    const int w = j / kWBins, k = j % kWBins;
+    const int w = j / (kWAxes * kWBins), k = j % (kWAxes * kWBins);
     if (w >= n_items) return;
     WBin& bin = b.bins[w].b[k];
     bin.count = 0;
@@ -194,20 +198,17 @@ CV_D void wb_body_prep(const WBuild& b, int j, int level) {
     if (ext.y > comp(ext, axis)) axis = 1;
     if (ext.z > comp(ext, axis)) axis = 2;
     const float e = comp(ext, axis);
-    if (!(e > 0.0f) || b.force_median || it.depth >= kWMedianDepth) {
-        it.axis = -1;  // all centroids coincide (or the safety net): split the list in the middle
-        it.cmin = 0.0f;
-        it.cscale = 0.0f;
-    } else {
-        it.axis = axis;
-        it.cmin = it.cb_mn[axis];
-        it.cscale = cv_div((float)kWBins, e);
+    for (int c = 0; c < 3; ++c) {
+        it.cmin[c] = it.cb_mn[c];
+        it.cscale[c] = comp(ext, c) > 0.0f ? cv_div((float)kWBins, comp(ext, c)) : 0.0f;
     }
+    // all centroids coincide (or the safety net): split the list in the middle
+    it.axis = (!(e > 0.0f) || b.force_median || it.depth >= kWMedianDepth) ? -1 : axis;
 }
 
-CV_HD int wb_bin_of(const WItem& it, F4 mn, F4 mx) {
-    const float c = it.axis == 0 ? 0.5f * (mn.x + mx.x) : (it.axis == 1 ? 0.5f * (mn.y + mx.y) : 0.5f * (mn.z + mx.z));
-    const int k = (int)((c - it.cmin) * it.cscale);
+CV_HD int wb_bin_of(const WItem& it, int axis, F4 mn, F4 mx) {
+    const float c = axis == 0 ? 0.5f * (mn.x + mx.x) : (axis == 1 ? 0.5f * (mn.y + mx.y) : 0.5f * (mn.z + mx.z));
+    const int k = (int)((c - it.cmin[axis]) * it.cscale[axis]);
     return k < 0 ? 0 : (k > kWBins - 1 ? kWBins - 1 : k);
 }
 
@@ -219,23 +220,26 @@ CV_D void wb_body_bin(const WBuild& b, int i) {
     if (it.axis < 0) return;
     const int p = b.order[i];
     const F4 mn = b.bmin[p], mx = b.bmax[p];
-    const int k = wb_bin_of(it, mn, mx);
-    WBin& bin = b.bins[w].b[k];
     const F3 c = f3(0.5f * (mn.x + mx.x), 0.5f * (mn.y + mx.y), 0.5f * (mn.z + mx.z));
-    const CvGroup g = cv_group_by(w * kWBins + k);
-    cv_group_add_i32(g, &bin.count, 1);
-    cv_group_min_u32(g, &bin.mn[0], ordered_key(mn.x));
-    cv_group_min_u32(g, &bin.mn[1], ordered_key(mn.y));
-    cv_group_min_u32(g, &bin.mn[2], ordered_key(mn.z));
-    cv_group_max_u32(g, &bin.mx[0], ordered_key(mx.x));
-    cv_group_max_u32(g, &bin.mx[1], ordered_key(mx.y));
-    cv_group_max_u32(g, &bin.mx[2], ordered_key(mx.z));
-    cv_group_min_u32(g, &bin.cmn[0], ordered_key(c.x));
-    cv_group_min_u32(g, &bin.cmn[1], ordered_key(c.y));
-    cv_group_min_u32(g, &bin.cmn[2], ordered_key(c.z));
-    cv_group_max_u32(g, &bin.cmx[0], ordered_key(c.x));
-    cv_group_max_u32(g, &bin.cmx[1], ordered_key(c.y));
-    cv_group_max_u32(g, &bin.cmx[2], ordered_key(c.z));
+    for (int a = 0; a < kWAxes; ++a) {
+        const int axis = kWAxes == 1 ? it.axis : a;
+        const int k = a * kWBins + wb_bin_of(it, axis, mn, mx);
+        WBin& bin = b.bins[w].b[k];
+        const CvGroup g = cv_group_by(w * (kWAxes * kWBins) + k);
+        cv_group_add_i32(g, &bin.count, 1);
+        cv_group_min_u32(g, &bin.mn[0], ordered_key(mn.x));
+        cv_group_min_u32(g, &bin.mn[1], ordered_key(mn.y));
+        cv_group_min_u32(g, &bin.mn[2], ordered_key(mn.z));
+        cv_group_max_u32(g, &bin.mx[0], ordered_key(mx.x));
+        cv_group_max_u32(g, &bin.mx[1], ordered_key(mx.y));
+        cv_group_max_u32(g, &bin.mx[2], ordered_key(mx.z));
+        cv_group_min_u32(g, &bin.cmn[0], ordered_key(c.x));
+        cv_group_min_u32(g, &bin.cmn[1], ordered_key(c.y));
+        cv_group_min_u32(g, &bin.cmn[2], ordered_key(c.z));
+        cv_group_max_u32(g, &bin.cmx[0], ordered_key(c.x));
+        cv_group_max_u32(g, &bin.cmx[1], ordered_key(c.y));
+        cv_group_max_u32(g, &bin.cmx[2], ordered_key(c.z));
+    }
 }
 
 struct WBox {
@@ -266,53 +270,52 @@ CV_D void wb_body_split(const WBuild& b, int w, int level) {
     int cnt[2];
     if (it.axis >= 0) {
         const WBins& bins = b.bins[w];
-        WBox bb[kWBins];
-        int bc[kWBins];
-        for (int k = 0; k < kWBins; ++k) {
-            const WBin& s = bins.b[k];
-            bc[k] = s.count;
-            bb[k].mn = f3(ordered_value(s.mn[0]), ordered_value(s.mn[1]), ordered_value(s.mn[2]));
-            bb[k].mx = f3(ordered_value(s.mx[0]), ordered_value(s.mx[1]), ordered_value(s.mx[2]));
-        }
-        // suffix areas, then a prefix sweep
-        float right_area[kWBins];
-        int right_cnt[kWBins];
-        WBox acc = wb_empty();
-        int n = 0;
-        for (int k = kWBins - 1; k >= 1; --k) {
-            if (bc[k] > 0) wb_grow(acc, bb[k].mn, bb[k].mx);
-            n += bc[k];
-            right_area[k] = n > 0 ? wb_half_area(acc) : 0.0f;
-            right_cnt[k] = n;
-        }
-        acc = wb_empty();
-        n = 0;
-        int best = -1;
+        int best = -1, best_slot = 0;
         float best_cost = CV_INF;
-        for (int k = 0; k < kWBins - 1; ++k) {
-            if (bc[k] > 0) wb_grow(acc, bb[k].mn, bb[k].mx);
-            n += bc[k];
-            if (n == 0 || right_cnt[k + 1] == 0) continue;
-            const float cost = (float)n * wb_half_area(acc) + (float)right_cnt[k + 1] * right_area[k + 1];
-            if (cost < best_cost) {
-                best_cost = cost;
-                best = k;
+        for (int a = 0; a < kWAxes; ++a) {
+            const WBin* ab = &bins.b[a * kWBins];
+            // suffix areas, then a prefix sweep
+            float right_area[kWBins];
+            int right_cnt[kWBins];
+            WBox acc = wb_empty();
+            int n = 0;
+            for (int k = kWBins - 1; k >= 1; --k) {
+                const WBin& s = ab[k];
+                if (s.count > 0) wb_grow(acc, f3(ordered_value(s.mn[0]), ordered_value(s.mn[1]), ordered_value(s.mn[2])), f3(ordered_value(s.mx[0]), ordered_value(s.mx[1]), ordered_value(s.mx[2])));
+                n += s.count;
+                right_area[k] = n > 0 ? wb_half_area(acc) : 0.0f;
+                right_cnt[k] = n;
+            }
+            acc = wb_empty();
+            n = 0;
+            for (int k = 0; k < kWBins - 1; ++k) {
+                const WBin& s = ab[k];
+                if (s.count > 0) wb_grow(acc, f3(ordered_value(s.mn[0]), ordered_value(s.mn[1]), ordered_value(s.mn[2])), f3(ordered_value(s.mx[0]), ordered_value(s.mx[1]), ordered_value(s.mx[2])));
+                n += s.count;
+                if (n == 0 || right_cnt[k + 1] == 0) continue;
+                const float cost = (float)n * wb_half_area(acc) + (float)right_cnt[k + 1] * right_area[k + 1];
+                if (cost < best_cost) {
+                    best_cost = cost;
+                    best = k;
+                    best_slot = a;
+                }
             }
         }
         if (best < 0) {
             it.axis = -1;  // everything in one bin (cannot happen with a positive extent; kept as a guard)
         } else {
+            if (kWAxes > 1) it.axis = best_slot;
             it.split = best;
             box[0] = box[1] = cb[0] = cb[1] = wb_empty();
             cnt[0] = cnt[1] = 0;
             for (int k = 0; k < kWBins; ++k) {
-                if (bc[k] == 0) continue;
+                const WBin& src = bins.b[best_slot * kWBins + k];
+                if (src.count == 0) continue;
                 const int s = k <= best ? 0 : 1;
-                const WBin& src = bins.b[k];
-                wb_grow(box[s], bb[k].mn, bb[k].mx);
+                wb_grow(box[s], f3(ordered_value(src.mn[0]), ordered_value(src.mn[1]), ordered_value(src.mn[2])), f3(ordered_value(src.mx[0]), ordered_value(src.mx[1]), ordered_value(src.mx[2])));
                 wb_grow(cb[s], f3(ordered_value(src.cmn[0]), ordered_value(src.cmn[1]), ordered_value(src.cmn[2])),
                         f3(ordered_value(src.cmx[0]), ordered_value(src.cmx[1]), ordered_value(src.cmx[2])));
-                cnt[s] += bc[k];
+                cnt[s] += src.count;
             }
         }
     }
@@ -348,7 +351,7 @@ CV_D void wb_body_split(const WBuild& b, int w, int level) {
                 c.pair = pair;
                 c.depth = it.depth + 1;
                 c.axis = -1;
-                c.cmin = c.cscale = 0.0f;
+                for (int a = 0; a < 3; ++a) c.cmin[a] = c.cscale[a] = 0.0f;
                 c.split = c.n_left = 0;
                 c.child_item[0] = c.child_item[1] = -1;
                 c.box_mn[0] = box[s].mn.x; c.box_mn[1] = box[s].mn.y; c.box_mn[2] = box[s].mn.z;
@@ -375,7 +378,7 @@ CV_D void wb_body_flag(const WBuild& b, int i) {
         const WItem& it = b.items[w];
         if (it.axis >= 0) {
             const int p = b.order[i];
-            f = wb_bin_of(it, b.bmin[p], b.bmax[p]) <= it.split ? 1 : 0;
+            f = wb_bin_of(it, it.axis, b.bmin[p], b.bmax[p]) <= it.split ? 1 : 0;
         } else {
             f = (i - it.start) < it.n_left ? 1 : 0;
         }
@@ -409,33 +412,66 @@ CV_D void wb_body_scatter(const WBuild& b, int i) {
 // World-space vertices (the same wb_world() values the boxes were built from) and the vertex
 // normals times the world matrix.  A mirroring instance (det < 0) flips the winding the reference's mesh-space
 // back-face test sees (shared_path_tracer.h:106), so its triangles are stored as (A, C, B).
-CV_D void wb_emit_slot(const WBuild& b, int s, uint32_t tri, uint32_t inst);
-CV_D void wb_body_emit(const WBuild& b, int s) {
-    if (s >= b.n_prims) return;
-    const int p = b.order[s];
-    wb_emit_slot(b, s, f2u(b.bmin[p].w), f2u(b.bmax[p].w));
-}
-CV_D void wb_emit_slot(const WBuild& b, int s, uint32_t tri, uint32_t inst) {
+// Quad records: when the triangle in the NEXT slot belongs to the same instance, starts at the same vertex A and shares
+// this triangle's AC as its AB (flag 1) or this triangle's AB as its AC (flag 2) -- the two halves of a grid cell, 95 % of
+// the two-triangle leaves of the config scenes -- its one remaining edge goes into this record's spare 16 bytes and the
+// flag into v2.w.  A two-triangle leaf that starts at a flagged slot is then tested from ONE record (walk_test_triangle):
+// the second triangle's (A, AB, AC) are bit for bit those of its own record.  The flag is a property of slots s, s+1
+// alone; the tracer consults it only when slot s opens a two-triangle leaf.
+struct WTriGeom {
+    F3 a, ab, ac, na, nb, nc;
+};
+CV_D WTriGeom wb_tri_geom(const WBuild& b, uint32_t tri, uint32_t inst) {
     const float* m = b.instances[inst].transform;
     const float det = m[0] * (m[5] * m[10] - m[9] * m[6]) - m[4] * (m[1] * m[10] - m[9] * m[2]) + m[8] * (m[1] * m[6] - m[5] * m[2]);
     const int* idx = b.indices[tri].tri;
     const int i1 = det < 0.0f ? idx[2] : idx[1], i2 = det < 0.0f ? idx[1] : idx[2];
     const GpuPtVertex va = b.vertices[idx[0]], vb = b.vertices[i1], vc = b.vertices[i2];
     const F3 wa = wb_world(m, va.position), wb = wb_world(m, vb.position), wc = wb_world(m, vc.position);
-    const F3 ab = wb - wa, ac = wc - wa;  // HitTriangle's first two lines (shared_path_tracer.h:94-95)
+    WTriGeom g;
+    g.a = wa;
+    g.ab = wb - wa;  // HitTriangle's first two lines (shared_path_tracer.h:94-95)
+    g.ac = wc - wa;
+    g.na = mat_mul(m, f3(va.normal[0], va.normal[1], va.normal[2]), 0.0f);  // the shader's own transform (:210)
+    g.nb = mat_mul(m, f3(vb.normal[0], vb.normal[1], vb.normal[2]), 0.0f);
+    g.nc = mat_mul(m, f3(vc.normal[0], vc.normal[1], vc.normal[2]), 0.0f);
+    return g;
+}
+CV_HD bool wb_same_bits(F3 a, F3 b) { return f2u(a.x) == f2u(b.x) && f2u(a.y) == f2u(b.y) && f2u(a.z) == f2u(b.z); }
+
+// has_next: slot s + 1 exists and holds (tri_next, inst_next)
+CV_D void wb_emit_slot(const WBuild& b, int s, uint32_t tri, uint32_t inst, bool has_next, uint32_t tri_next, uint32_t inst_next) {
+    const WTriGeom g = wb_tri_geom(b, tri, inst);
     FastTri t;
-    t.v0.x = wa.x; t.v0.y = wa.y; t.v0.z = wa.z; t.v0.w = u2f(inst);
-    t.v1.x = ab.x; t.v1.y = ab.y; t.v1.z = ab.z; t.v1.w = u2f(tri);
-    t.v2.x = ac.x; t.v2.y = ac.y; t.v2.z = ac.z; t.v2.w = 0.0f;
+    t.v0.x = g.a.x; t.v0.y = g.a.y; t.v0.z = g.a.z; t.v0.w = u2f(inst);
+    t.v1.x = g.ab.x; t.v1.y = g.ab.y; t.v1.z = g.ab.z; t.v1.w = u2f(tri);
+    t.v2.x = g.ac.x; t.v2.y = g.ac.y; t.v2.z = g.ac.z; t.v2.w = 0.0f;
     t.pad.x = t.pad.y = t.pad.z = t.pad.w = 0.0f;
+    if (has_next && inst_next == inst) {
+        const WTriGeom n = wb_tri_geom(b, tri_next, inst_next);
+        if (wb_same_bits(n.a, g.a)) {
+            if (wb_same_bits(n.ab, g.ac)) {
+                t.v2.w = u2f(1u);
+                t.pad.x = n.ac.x; t.pad.y = n.ac.y; t.pad.z = n.ac.z;
+            } else if (wb_same_bits(n.ac, g.ab)) {
+                t.v2.w = u2f(2u);
+                t.pad.x = n.ab.x; t.pad.y = n.ab.y; t.pad.z = n.ab.z;
+            }
+        }
+    }
     b.ftris[s] = t;
-    const F3 na = mat_mul(m, f3(va.normal[0], va.normal[1], va.normal[2]), 0.0f);  // the shader's own transform (:210)
-    const F3 nb = mat_mul(m, f3(vb.normal[0], vb.normal[1], vb.normal[2]), 0.0f);
-    const F3 nc = mat_mul(m, f3(vc.normal[0], vc.normal[1], vc.normal[2]), 0.0f);
-    t.v0.x = na.x; t.v0.y = na.y; t.v0.z = na.z;
-    t.v1.x = nb.x; t.v1.y = nb.y; t.v1.z = nb.z; t.v1.w = u2f((uint32_t)b.instances[inst].materialId);
-    t.v2.x = nc.x; t.v2.y = nc.y; t.v2.z = nc.z;
+    t.v0.x = g.na.x; t.v0.y = g.na.y; t.v0.z = g.na.z;
+    t.v1.x = g.nb.x; t.v1.y = g.nb.y; t.v1.z = g.nb.z; t.v1.w = u2f((uint32_t)b.instances[inst].materialId);
+    t.v2.x = g.nc.x; t.v2.y = g.nc.y; t.v2.z = g.nc.z; t.v2.w = 0.0f;
+    t.pad.x = t.pad.y = t.pad.z = t.pad.w = 0.0f;
     b.fnormals[s] = t;
+}
+CV_D void wb_body_emit(const WBuild& b, int s) {
+    if (s >= b.n_prims) return;
+    const int p = b.order[s];
+    const bool has_next = s + 1 < b.n_prims;
+    const int pn = has_next ? b.order[s + 1] : p;
+    wb_emit_slot(b, s, f2u(b.bmin[p].w), f2u(b.bmax[p].w), has_next, f2u(b.bmin[pn].w), f2u(b.bmax[pn].w));
 }
 
 // ---- quantise: FastNode pair k -> QPair k --------------------------------------------------
@@ -532,7 +568,10 @@ CV_D void wb_body_retransform(const WBuild& b, int s, const unsigned char* moved
     if (s >= b.n_prims) return;
     const uint32_t inst = f2u(b.ftris[s].v0.w);
     if (!moved[inst]) return;
-    wb_emit_slot(b, s, f2u(b.ftris[s].v1.w), inst);
+    // the next slot's (triangle, instance) words are rewritten by its own thread with the values they already hold
+    const bool has_next = s + 1 < b.n_prims;
+    const int sn = has_next ? s + 1 : s;
+    wb_emit_slot(b, s, f2u(b.ftris[s].v1.w), inst, has_next, f2u(b.ftris[sn].v1.w), f2u(b.ftris[sn].v0.w));
 }
 
 CV_D void wb_body_refit_pair(const WBuild& b, int k, float* area_sum) {
@@ -939,7 +978,7 @@ int build_wbvh(Exec& ex, WBuild b, WReport* rep) {
     root.pair = 0;
     root.depth = 0;
     root.axis = -1;
-    root.cmin = root.cscale = 0.0f;
+    for (int a = 0; a < 3; ++a) root.cmin[a] = root.cscale[a] = 0.0f;
     root.split = root.n_left = 0;
     root.child_item[0] = root.child_item[1] = -1;
     for (int k = 0; k < 3; ++k) {
@@ -963,7 +1002,7 @@ int build_wbvh(Exec& ex, WBuild b, WReport* rep) {
         for (int k = 0; k < kLevelsPerSync; ++k, ++level) {
             const long long pow2 = level < 30 ? (1ll << level) : (1ll << 30);
             const int bound = (int)(pow2 < items_bound ? pow2 : items_bound);
-            ex.launch(bound * kWBins, FnWbPrep{ b, level });
+            ex.launch(bound * kWAxes * kWBins, FnWbPrep{ b, level });
             ex.launch(b.n_prims, FnWbBin{ b });
             ex.launch(bound, FnWbSplit{ b, level });
             ex.launch(b.n_prims, FnWbFlag{ b });

@@ -2,6 +2,7 @@
 """Turns gpurun_out/ ncu artefacts into the small text summaries committed under profiles/.
   python profiles/summarize.py launches gpurun_out/launches.csv profiles/r01_launches.txt
   python profiles/summarize.py full gpurun_out/prof_trace.ncu-rep profiles/r01_k_trace_full.txt
+  python profiles/summarize.py json gpurun_out/x.ncu-rep profiles/r02x_cfg3_ncu.json <spp> <segments> <config> <kernel variant>
 """
 import collections
 import csv
@@ -66,7 +67,7 @@ def full(src, dst):
     print(open(dst).read())
 
 
-def as_json(src, dst, spp="0", segments="0"):
+def as_json(src, dst, spp="0", segments="0", config="3", kernel_variant="pixel"):
     """Machine-readable digest of one `ncu --set full` capture of k_trace; bench.py reads the
     newest profiles/*_k_trace_ncu.json for roofline.traffic (DRAM bytes of that launch)."""
     import json
@@ -84,7 +85,7 @@ def as_json(src, dst, spp="0", segments="0"):
         return v * scale
 
     d = {
-        "source": src, "kernel": r[hdr.index("Kernel Name")], "spp_of_launch": int(spp), "segments_of_launch": int(segments),
+        "source": src, "config": int(config), "kernel_variant": kernel_variant, "kernel": r[hdr.index("Kernel Name")], "spp_of_launch": int(spp), "segments_of_launch": int(segments),
         "duration_ms_under_ncu": val("gpu__time_duration.sum"),
         "dram_bytes": (val("dram__bytes_read.sum") or 0) + (val("dram__bytes_write.sum") or 0),
         "l2_bytes": (val("lts__t_sectors.sum") or 0) * 32.0,

@@ -100,6 +100,7 @@ ABI = [
     ("cavept_set_refit", C.c_int, [_P, C.c_int]),
     ("cavept_rebuild_mesh", C.c_int, [_P, C.c_int, _P, _P]),
     ("cavept_get_mesh_bvh", C.c_int, [_P, C.c_int, _P, C.c_int]),
+    ("cavept_get_fast_tree", C.c_int, [_P, _P, C.c_int]),
     ("cavept_get_scene_counts", C.c_int, [_P] + [C.POINTER(C.c_int)] * 5),
     ("cavept_get_scene_arrays", C.c_int, [_P] * 6),
     ("cavept_set_camera", C.c_int, [_P, C.POINTER(C.c_float), C.POINTER(C.c_float), C.POINTER(C.c_float), C.POINTER(C.c_float), C.c_float]),
@@ -172,6 +173,7 @@ def load_library() -> C.CDLL:
 
 # numpy dtypes of the reference GPU layouts (cave/shader/structured_buffer.hlsl.h:24-61)
 BVH_DT = np.dtype([("min", "<f4", 3), ("miss", "<i4"), ("max", "<f4", 3), ("hit", "<i4"), ("pad", "<f4", 2), ("leaf", "<i4"), ("tri", "<i4")])
+FASTNODE_DT = np.dtype([("mn", "<f4", 3), ("a", "<i4"), ("mx", "<f4", 3), ("b", "<i4")])  # production-tree record (csrc/trace_body.h FastNode)
 VERTEX_DT = np.dtype([("position", "<f4", 3), ("pad1", "<i4"), ("normal", "<f4", 3), ("pad2", "<i4")])
 INDEX_DT = np.dtype([("tri", "<i4", 3), ("pad1", "<i4")])
 MESH_DT = np.dtype([("transform", "<f4", 16), ("transform_inv", "<f4", 16), ("pad", "<f4", 2), ("root", "<i4"), ("material", "<i4")])
@@ -413,6 +415,15 @@ class PathTracer:
     def get_mesh_bvh(self, mesh: int, n_tris: int) -> np.ndarray:
         out = np.zeros(max(2 * n_tris - 1, 1), dtype=BVH_DT)
         rc = self._lib.cavept_get_mesh_bvh(self._ctx, mesh, out.ctypes.data, out.shape[0])
+        if rc < 0:
+            self._check(-rc)
+        return out[:rc]
+
+    def get_fast_tree(self) -> np.ndarray:
+        """The production tree's fp32 records (sibling pairs adjacent), as cavept_get_fast_tree returns them."""
+        cap = max(2 * self.stats()["fast_node_count"], 2)
+        out = np.zeros(cap, dtype=FASTNODE_DT)
+        rc = self._lib.cavept_get_fast_tree(self._ctx, out.ctypes.data, cap)
         if rc < 0:
             self._check(-rc)
         return out[:rc]

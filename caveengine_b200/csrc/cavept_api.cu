@@ -75,7 +75,8 @@ int build_world(cavept_ctx* ctx) {
     prim_off[n_inst] = (int)total;
     const int P = (int)total;
     ctx->n_prims = P;
-    const size_t items_cap = (size_t)P / 2 + 8, pairs_cap = (size_t)P + 8;
+    // interior items of a level are disjoint ranges of >= kFastLeafMax + 1 prims; only those of more than kWDirectMax prims own arena bins
+    const size_t items_cap = (size_t)P / (kFastLeafMax + 1) + 8, pairs_cap = (size_t)P + 8, bins_cap = (size_t)P / (kWDirectMax + 1) + 2;
     CU(ctx, ctx->d_inst_prim_off.reserve(n_inst + 1));
     CU(ctx, ctx->d_inst_tri_off.reserve(n_inst));
     CU(ctx, ctx->d_prim_bmin.reserve(P));
@@ -98,9 +99,9 @@ int build_world(cavept_ctx* ctx) {
     } else {
         CU(ctx, ctx->d_w_items.reserve(items_cap));
         CU(ctx, ctx->d_w_items_next.reserve(items_cap));
-        CU(ctx, ctx->d_w_bins.reserve(items_cap));
+        CU(ctx, ctx->d_w_bins.reserve(bins_cap));
     }
-    CU(ctx, ctx->d_w_counters.reserve(kWLevelBase + kWMaxLevels + 4));
+    CU(ctx, ctx->d_w_counters.reserve(kWCounters));
     CU(ctx, ctx->d_w_root_acc.reserve(12));
     CU(ctx, ctx->d_fnodes.reserve(2 * pairs_cap));
     CU(ctx, ctx->d_qpairs.reserve(pairs_cap));
@@ -133,6 +134,7 @@ int build_world(cavept_ctx* ctx) {
     b.bins = ctx->d_w_bins.ptr;
     b.items_capacity = (int)items_cap;
     b.pairs_capacity = (int)pairs_cap;
+    b.bins_capacity = (int)bins_cap;
     b.counters = ctx->d_w_counters.ptr;
     b.root_acc = ctx->d_w_root_acc.ptr;
     b.keys = ctx->d_w_keys.ptr;
@@ -598,6 +600,17 @@ CAVEPT_API int cavept_get_scene_arrays(cavept_ctx* ctx, void* v, void* i, void* 
     if (m) ctx->ex.download(m, ctx->d_meshes.ptr, ctx->gpu_meshes.size() * sizeof(GpuPtMesh));
     if (mat) ctx->ex.download(mat, ctx->d_materials.ptr, ctx->gpu_materials.size() * sizeof(GpuPtMaterial));
     return check_exec(ctx, "scene read-back");
+}
+
+CAVEPT_API int cavept_get_fast_tree(cavept_ctx* ctx, void* out_records, int capacity_records) {
+    if (!ctx || !out_records) return -CAVEPT_ERR_INVALID_ARG;
+    if (!ctx->scene_resident) return -fail(ctx, CAVEPT_ERR_NOT_READY, "no scene resident");
+    const int n = 2 * ctx->n_pairs;
+    if (capacity_records < n) return -fail(ctx, CAVEPT_ERR_INVALID_ARG, "capacity %d < %d records", capacity_records, n);
+    if (int e = select_device(ctx)) return -e;
+    ctx->ex.download(out_records, ctx->d_fnodes.ptr, (size_t)n * sizeof(FastNode));
+    if (int e = check_exec(ctx, "fast tree read-back")) return -e;
+    return n;
 }
 
 CAVEPT_API int cavept_set_camera(cavept_ctx* ctx, const float position[3], const float right[3], const float up[3], const float forward[3], float fov_degree) {

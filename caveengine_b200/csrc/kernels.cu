@@ -267,6 +267,171 @@ void CudaExec::wb_prim(const WBuild& b) {
     ++launches;
 }
 
+// ---- SAH split of the production builder: one WARP per item that owns arena bins (wbvh_body.h wb_body_split is
+//      the per-item serial statement the emulator runs; same bins in, same winner out: prefix / suffix unions are
+//      exact min / max, the cost expression is the same three fp32 operations, and the serial "first strictly
+//      smaller cost over slots 0..2, planes 0..14" is the lexicographic minimum of (cost bits, slot * 16 + plane)).
+//      Lane k (and k + 16, redundantly) holds bin k of the axis slot being swept; the bins are cleared as read. -----
+__device__ __forceinline__ WBox shfl_box(unsigned mask, const WBox& v, int src, bool up_down, int delta) {
+    WBox r;
+    if (up_down) {
+        r.mn = f3(__shfl_up_sync(mask, v.mn.x, delta, 16), __shfl_up_sync(mask, v.mn.y, delta, 16), __shfl_up_sync(mask, v.mn.z, delta, 16));
+        r.mx = f3(__shfl_up_sync(mask, v.mx.x, delta, 16), __shfl_up_sync(mask, v.mx.y, delta, 16), __shfl_up_sync(mask, v.mx.z, delta, 16));
+    } else if (delta > 0) {
+        r.mn = f3(__shfl_down_sync(mask, v.mn.x, delta, 16), __shfl_down_sync(mask, v.mn.y, delta, 16), __shfl_down_sync(mask, v.mn.z, delta, 16));
+        r.mx = f3(__shfl_down_sync(mask, v.mx.x, delta, 16), __shfl_down_sync(mask, v.mx.y, delta, 16), __shfl_down_sync(mask, v.mx.z, delta, 16));
+    } else {
+        r.mn = f3(__shfl_sync(mask, v.mn.x, src, 16), __shfl_sync(mask, v.mn.y, src, 16), __shfl_sync(mask, v.mn.z, src, 16));
+        r.mx = f3(__shfl_sync(mask, v.mx.x, src, 16), __shfl_sync(mask, v.mx.y, src, 16), __shfl_sync(mask, v.mx.z, src, 16));
+    }
+    return r;
+}
+__global__ void __launch_bounds__(256) k_wb_split_binned(const WBuild b, int level) {
+    constexpr unsigned kAll = 0xffffffffu;
+    const int w = (int)((blockIdx.x * 256u + threadIdx.x) >> 5);
+    const int lane = threadIdx.x & 31, k = lane & 15;
+    if (w >= b.counters[kWLevelBase + level]) return;  // warp-uniform
+    WItem& it = b.items[w];
+    if (it.axis < 0 || it.bins_slot < 0) return;  // median items and small items: FnWbSplit, one thread each
+    unsigned long long best = ~0ull;
+    WBox best_box[2];
+    int best_cnt[2] = { 0, 0 };
+    best_box[0] = best_box[1] = wb_empty();
+    for (int a = 0; a < kWAxes; ++a) {
+        WBin* src = &b.bins[it.bins_slot].b[a * kWBins + k];
+        const WBin raw = *src;
+        __syncwarp();
+        if (lane < 16) {
+            WBin z = {};
+            *src = z;
+        }
+        const WLBin mine = wb_lbin_of(raw);
+        int lc = mine.count, rc = mine.count;
+        WBox lb = mine.box, rb = mine.box;
+#pragma unroll
+        for (int d = 1; d < 16; d <<= 1) {
+            const int cu = __shfl_up_sync(kAll, lc, d, 16), cd = __shfl_down_sync(kAll, rc, d, 16);
+            const WBox bu = shfl_box(kAll, lb, 0, true, d), bd = shfl_box(kAll, rb, 0, false, d);
+            if (k >= d) {
+                lc += cu;
+                wb_grow(lb, bu.mn, bu.mx);
+            }
+            if (k + d < 16) {
+                rc += cd;
+                wb_grow(rb, bd.mn, bd.mx);
+            }
+        }
+        const float ra = rc > 0 ? wb_half_area(rb) : 0.0f;
+        const int rn = __shfl_down_sync(kAll, rc, 1, 16);          // suffix count / area of bins k + 1 .. 15
+        const float rarea = __shfl_down_sync(kAll, ra, 1, 16);
+        const bool valid = k < kWBins - 1 && lc > 0 && rn > 0;
+        const float cost = (float)lc * wb_half_area(lb) + (float)rn * rarea;
+        unsigned long long key = valid ? (((unsigned long long)f2u(cost)) << 8) | (unsigned long long)(a * kWBins + k) : ~0ull;
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) {
+            const unsigned long long o = __shfl_xor_sync(kAll, key, d);
+            key = o < key ? o : key;
+        }
+        if (key < best) {  // warp-uniform
+            best = key;
+            const int kk = (int)(key & 15ull);
+            best_cnt[0] = __shfl_sync(kAll, lc, kk, 16);
+            best_box[0] = shfl_box(kAll, lb, kk, false, 0);
+            best_cnt[1] = __shfl_sync(kAll, rc, kk + 1, 16);
+            best_box[1] = shfl_box(kAll, rb, kk + 1, false, 0);
+        }
+    }
+    if (lane == 0) {
+        if (best == ~0ull) {
+            it.axis = -1;  // every prim in one bin on every axis: median split
+        } else {
+            const int key = (int)(best & 0xffull);
+            it.axis = wb_slot_axis(it, key / kWBins);
+            it.split = key % kWBins;
+        }
+        wb_finish_split(b, it, level, best_box, best_cnt);
+    }
+}
+void CudaExec::wb_split(const WBuild& b, int level, int bound) {
+    if (bound <= 0) return;
+    // arena items: at most bins_capacity of them, and at most `bound` items altogether
+    const int warps = bound < b.bins_capacity ? bound : b.bins_capacity;
+    k_wb_split_binned<<<(warps * 32 + 255) / 256, 256, 0, stream>>>(b, level);
+    note(cudaGetLastError());
+    ++launches;
+    launch(bound, FnWbSplit{ b, level, false });
+}
+
+// ---- partition of a level: left flags computed inside the scan's first kernel, the stable scatter inside its last
+//      (the emulator runs wb_body_flag / scan / wb_body_scatter).  The scatter needs the scan value at the START of a
+//      prim's item, which may lie in an earlier tile: the first kernel leaves (tile, count within the tile) in the item.
+__global__ void __launch_bounds__(kScanThreads) k_wb_part_sums(const WBuild b, int* __restrict__ sums) {
+    const int n = b.n_prims;
+    const int base = blockIdx.x * kScanTile + threadIdx.x * kScanPerThread;
+    unsigned char f[kScanPerThread];
+    int s = 0;
+#pragma unroll
+    for (int k = 0; k < kScanPerThread; ++k) {
+        const int i = base + k;
+        f[k] = i < n ? wb_flag_of(b, i) : 0;
+        if (i < n) b.flags[i] = f[k];
+        s += f[k];
+    }
+    int total;
+    int run = block_exclusive_scan(s, &total);
+    if (threadIdx.x == 0) sums[blockIdx.x] = total;
+#pragma unroll
+    for (int k = 0; k < kScanPerThread; ++k) {
+        const int i = base + k;
+        if (i < n) {
+            const int w = b.node_of[i];
+            if (w >= 0 && b.items[w].start == i) {
+                b.items[w].scan_tile = blockIdx.x;
+                b.items[w].scan_local = run;
+            }
+        }
+        run += f[k];
+    }
+}
+__global__ void __launch_bounds__(kScanThreads) k_wb_part_scatter(const WBuild b, const int* __restrict__ sums) {
+    const int n = b.n_prims;
+    const int base = blockIdx.x * kScanTile + threadIdx.x * kScanPerThread;
+    unsigned char f[kScanPerThread];
+    int s = 0;
+#pragma unroll
+    for (int k = 0; k < kScanPerThread; ++k) {
+        const int i = base + k;
+        f[k] = i < n ? b.flags[i] : 0;
+        s += f[k];
+    }
+    int total;
+    int run = block_exclusive_scan(s, &total) + sums[blockIdx.x];
+#pragma unroll
+    for (int k = 0; k < kScanPerThread; ++k) {
+        const int i = base + k;
+        if (i < n) {
+            const int w = b.node_of[i];
+            if (w < 0) {
+                b.order_next[i] = b.order[i];
+                b.node_of_next[i] = -1;
+            } else {
+                const WItem& it = b.items[w];
+                wb_scatter_to(b, i, w, f[k], run, sums[it.scan_tile] + it.scan_local);
+            }
+        }
+        run += f[k];
+    }
+}
+void CudaExec::wb_partition(const WBuild& b) {
+    if (b.n_prims <= 0) return;
+    const int nb = (b.n_prims + kScanTile - 1) / kScanTile;
+    k_wb_part_sums<<<nb, kScanThreads, 0, stream>>>(b, scan_tmp);
+    k_scan_sums<<<1, kScanThreads, 0, stream>>>(scan_tmp, nb);
+    k_wb_part_scatter<<<nb, kScanThreads, 0, stream>>>(b, scan_tmp);
+    note(cudaGetLastError());
+    launches += 3;
+}
+
 // ---- scene assembly -------------------------------------------------------------------
 struct FnAssembleVertices {
     const float* positions;

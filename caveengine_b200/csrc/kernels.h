@@ -24,6 +24,8 @@ struct CudaExec {
     // tmp buffers hold n entries each, hist needs 2 * sort_hist_entries(n) ints.
     void sort_pairs(uint32_t* keys, int* vals, uint32_t* keys_tmp, int* vals_tmp, int* hist, int n, int bits);
     void wb_prim(const WBuild& b);  // world AABBs + scene / centroid bounds, block-reduced
+    void wb_split(const WBuild& b, int level, int bound);  // SAH split of every item of a level: a warp per arena item, a thread per small item
+    void wb_partition(const WBuild& b);                    // left flags + exclusive scan + stable scatter in three launches
     void upload(void* dst, const void* src, size_t bytes);
     void download(void* dst, const void* src, size_t bytes);
     void fill(void* dst, int byte, size_t bytes);

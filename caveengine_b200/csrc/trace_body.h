@@ -22,9 +22,6 @@ constexpr float kRayTMax = 999999999.0f;   // RAY_T_MAX, :27
 #define CV_LEAF_MAX 2
 #endif
 constexpr int kFastLeafMax = CV_LEAF_MAX;            // leaves of the production tree hold at most this many triangles (measured on B200: 2 beats 4 and 1)
-#ifndef CV_QUAD_LEAVES
-#define CV_QUAD_LEAVES 1  // a two-triangle leaf whose triangles share A and an edge is tested from one record (walk_test_triangle)
-#endif
 #ifndef CV_STACK_SIZE
 #define CV_STACK_SIZE 40
 #endif
@@ -483,31 +480,16 @@ CV_D void walk_test_triangle(const TraceParams& p, Walk& w, const Ray& ray, floa
     const int slot = leaf & 0x1fffffff;
     const int more = (leaf >> 29) & 3;
     const F8 t0 = ld256(&p.ftris[slot]);             // A.xyz, instance, AB.xyz, triangle id
-    const F8 t1 = ld256(&p.ftris[slot].v2);          // AC.xyz, quad flag, the quad's fourth edge (same cache line)
+    const F8 t1 = ld256(&p.ftris[slot].v2);          // AC.xyz (same cache line)
     if (kCount) ++cnt[2];
-    const F3 A = f3(t0.a, t0.b, t0.c), AB = f3(t0.e, t0.f, t0.g), AC = f3(t1.a, t1.b, t1.c);
     float u, v;
-    if (hit_triangle_edges(A, AB, AC, ray.origin, ray.direction, ray_t, u, v)) {
+    if (hit_triangle_edges(f3(t0.a, t0.b, t0.c), f3(t0.e, t0.f, t0.g), f3(t1.a, t1.b, t1.c), ray.origin, ray.direction, ray_t, u, v)) {
         w.hit_slot = slot;
         w.hit_u = u;
         w.hit_v = v;
     }
-    int done = 1;  // slots of the leaf consumed by this call
-    const uint32_t quad = f2u(t1.d);
-    if (CV_QUAD_LEAVES && more > 0 && quad != 0u) {
-        // the next slot's triangle starts at the same A and shares an edge (wbvh_body.h wb_emit_slot): its record's
-        // (A, AB, AC) rebuilt from this one, bit for bit -- no second fetch, no second trip through the vote
-        const F3 X = f3(t1.e, t1.f, t1.g);
-        if (kCount) ++cnt[2];
-        if (hit_triangle_edges(A, quad == 1u ? AC : X, quad == 1u ? X : AB, ray.origin, ray.direction, ray_t, u, v)) {
-            w.hit_slot = slot + 1;
-            w.hit_u = u;
-            w.hit_v = v;
-        }
-        done = 2;
-    }
-    if (more >= done) {
-        w.q0 = make_leaf_ref(slot + done, more - done + 1);
+    if (more > 0) {
+        w.q0 = make_leaf_ref(slot + 1, more);
     } else {
         w.q0 = w.q1;
         w.q1 = 0;

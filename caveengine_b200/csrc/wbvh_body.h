@@ -30,31 +30,44 @@ constexpr int kWBins = 16;
 #ifndef CV_WB_AXES
 #define CV_WB_AXES 3
 #endif
+#ifndef CV_WB_AXES3_MIN
+#define CV_WB_AXES3_MIN 0
+#endif
 constexpr int kWAxes = CV_WB_AXES;  // 3: every axis is binned and the SAH sweep takes the cheapest plane of all three; 1: the axis of largest centroid extent only
 constexpr int kWLevelBase = 4;     // counters[4 + L] = interior items of level L (the level loop never reads them back one by one)
-constexpr int kWMaxLevels = 124;   // counters holds 4 + 124 + 4 ints
+constexpr int kWMaxLevels = 124;
+constexpr int kWBinBase = kWLevelBase + kWMaxLevels + 4;  // counters[kWBinBase + L] = bin-arena slots handed out for level L
+constexpr int kWCounters = kWBinBase + kWMaxLevels + 4;   // ints in the counter block
 constexpr int kWMedianDepth = 48;  // safety net: positional median splits below this depth
 
-struct WBin {
-    int count;
-    uint32_t mn[3], mx[3];    // ordered keys of the AABB
-    uint32_t cmn[3], cmx[3];  // ordered keys of the centroid bounds
+constexpr int kWDirectMax = 8;  // items of at most this many prims are split by one thread straight from the prims: no global bins, no atomics
+
+// One SAH bin.  Cleared = all zero: the min corner is kept as the COMPLEMENT of its ordered key (folded with
+// atomicMax), so the split pass clears what it has read with plain zero stores and the bin arena never needs a
+// clearing pass of its own (it is zeroed once per build).
+struct alignas(32) WBin {
+    uint32_t count;
+    uint32_t nmn[3];  // ~ordered_key(AABB min)
+    uint32_t mx[3];   // ordered_key(AABB max)
+    uint32_t spare;
 };
+static_assert(sizeof(WBin) == 32, "WBin");
 struct WBins {
-    WBin b[kWAxes * kWBins];  // [axis slot][bin]; with kWAxes == 1 the single slot holds the axis of largest centroid extent
+    WBin b[kWAxes * kWBins];  // [axis slot][bin]; with kWAxes == 1 the single slot holds the axis of largest extent
 };
 
 struct WItem {
     int start, count;  // segment of `order`
     int pair;          // children go to fnodes[2*pair], fnodes[2*pair + 1]
     int depth;
-    int axis;          // >= 0: binned (after the split pass: the axis of the chosen plane); -1: positional median split
-    float cmin[3], cscale[3];  // per axis: bin = (centre - cmin) * cscale (cscale 0: no extent, everything in bin 0)
+    int axis;          // >= 0: SAH split (after the split pass: the axis of the chosen plane); -1: positional median split
+    float cmin[3], cscale[3];  // per axis: bin = (box centre - cmin) * cscale (cscale 0: no extent, everything in bin 0)
     int split;         // left child = bins [0, split]
     int n_left;
     int child_item[2];  // index of each child in the next level, -1 if it is a leaf
+    int bins_slot;      // index of this item's WBins in the arena (items of more than kWDirectMax prims), -1: none
+    int scan_tile, scan_local;  // partition pass: tile holding `start` and the exclusive count of left flags before it in that tile
     float box_mn[3], box_mx[3];
-    float cb_mn[3], cb_mx[3];
 };
 
 enum { WB_ERR_CAPACITY = 1 };
@@ -84,6 +97,7 @@ struct WBuild {
     WBins* bins;
     int items_capacity;
     int pairs_capacity;
+    int bins_capacity;   // WBins records in the arena: at most n_prims / (kWDirectMax + 1) items of a level own one
     int* counters;       // [0] items emitted for the next level, [1] pairs allocated, [2] error bits
     // LBVH builder only
     uint32_t* keys;      // Morton code per prim, then sorted
@@ -178,32 +192,20 @@ CV_D void wb_body_init(const WBuild& b, int p) {
 }
 
 // ---- per level ----------------------------------------------------------------------------
-// thread j: bin j % (kWAxes * 16) of item j / (kWAxes * 16) is cleared; the first thread of an item also sets up its binning
-CV_D void wb_body_prep(const WBuild& b, int j, int level) {
-    const int n_items = b.counters[kWLevelBase + level];  // written by the level above; launches are sized by an upper bound
-    const int w = j / (kWAxes * kWBins), k = j % (kWAxes * kWBins);
-    if (w >= n_items) return;
-    WBin& bin = b.bins[w].b[k];
-    bin.count = 0;
-    for (int c = 0; c < 3; ++c) {
-        bin.mn[c] = 0xffffffffu;
-        bin.mx[c] = 0u;
-        bin.cmn[c] = 0xffffffffu;
-        bin.cmx[c] = 0u;
-    }
-    if (k != 0) return;
-    WItem& it = b.items[w];
-    const F3 ext = f3(it.cb_mx[0] - it.cb_mn[0], it.cb_mx[1] - it.cb_mn[1], it.cb_mx[2] - it.cb_mn[2]);
+// Binning set-up of an item from its box: the bins of every axis span the box (measured on the config scenes: the
+// node count per segment is within 0.5 % of binning over the exact centroid bounds, which cost 18 more atomics per prim).
+CV_HD void wb_item_setup(WItem& it, int force_median) {
+    const F3 ext = f3(it.box_mx[0] - it.box_mn[0], it.box_mx[1] - it.box_mn[1], it.box_mx[2] - it.box_mn[2]);
     int axis = 0;
     if (ext.y > comp(ext, axis)) axis = 1;
     if (ext.z > comp(ext, axis)) axis = 2;
     const float e = comp(ext, axis);
     for (int c = 0; c < 3; ++c) {
-        it.cmin[c] = it.cb_mn[c];
+        it.cmin[c] = it.box_mn[c];
         it.cscale[c] = comp(ext, c) > 0.0f ? cv_div((float)kWBins, comp(ext, c)) : 0.0f;
     }
-    // all centroids coincide (or the safety net): split the list in the middle
-    it.axis = (!(e > 0.0f) || b.force_median || it.depth >= kWMedianDepth) ? -1 : axis;
+    // no extent (or the safety net): split the list in the middle
+    it.axis = (!(e > 0.0f) || force_median || it.depth >= kWMedianDepth) ? -1 : axis;
 }
 
 CV_HD int wb_bin_of(const WItem& it, int axis, F4 mn, F4 mx) {
@@ -211,34 +213,29 @@ CV_HD int wb_bin_of(const WItem& it, int axis, F4 mn, F4 mx) {
     const int k = (int)((c - it.cmin[axis]) * it.cscale[axis]);
     return k < 0 ? 0 : (k > kWBins - 1 ? kWBins - 1 : k);
 }
+// axis binned in slot a of an item's bins
+CV_HD int wb_slot_axis(const WItem& it, int a) { return kWAxes == 1 ? it.axis : a; }
 
+// one thread per prim: count and AABB into the bins of its item (items of more than kWDirectMax prims only)
 CV_D void wb_body_bin(const WBuild& b, int i) {
     if (i >= b.n_prims) return;
     const int w = b.node_of[i];
     if (w < 0) return;
     const WItem& it = b.items[w];
-    if (it.axis < 0) return;
+    if (it.axis < 0 || it.bins_slot < 0) return;
     const int p = b.order[i];
     const F4 mn = b.bmin[p], mx = b.bmax[p];
-    const F3 c = f3(0.5f * (mn.x + mx.x), 0.5f * (mn.y + mx.y), 0.5f * (mn.z + mx.z));
     for (int a = 0; a < kWAxes; ++a) {
-        const int axis = kWAxes == 1 ? it.axis : a;
-        const int k = a * kWBins + wb_bin_of(it, axis, mn, mx);
-        WBin& bin = b.bins[w].b[k];
-        const CvGroup g = cv_group_by(w * (kWAxes * kWBins) + k);
-        cv_group_add_i32(g, &bin.count, 1);
-        cv_group_min_u32(g, &bin.mn[0], ordered_key(mn.x));
-        cv_group_min_u32(g, &bin.mn[1], ordered_key(mn.y));
-        cv_group_min_u32(g, &bin.mn[2], ordered_key(mn.z));
+        const int k = a * kWBins + wb_bin_of(it, wb_slot_axis(it, a), mn, mx);
+        WBin& bin = b.bins[it.bins_slot].b[k];
+        const CvGroup g = cv_group_by(it.bins_slot * (kWAxes * kWBins) + k);
+        cv_group_add_i32(g, reinterpret_cast<int*>(&bin.count), 1);
+        cv_group_max_u32(g, &bin.nmn[0], ~ordered_key(mn.x));
+        cv_group_max_u32(g, &bin.nmn[1], ~ordered_key(mn.y));
+        cv_group_max_u32(g, &bin.nmn[2], ~ordered_key(mn.z));
         cv_group_max_u32(g, &bin.mx[0], ordered_key(mx.x));
         cv_group_max_u32(g, &bin.mx[1], ordered_key(mx.y));
         cv_group_max_u32(g, &bin.mx[2], ordered_key(mx.z));
-        cv_group_min_u32(g, &bin.cmn[0], ordered_key(c.x));
-        cv_group_min_u32(g, &bin.cmn[1], ordered_key(c.y));
-        cv_group_min_u32(g, &bin.cmn[2], ordered_key(c.z));
-        cv_group_max_u32(g, &bin.cmx[0], ordered_key(c.x));
-        cv_group_max_u32(g, &bin.cmx[1], ordered_key(c.y));
-        cv_group_max_u32(g, &bin.cmx[2], ordered_key(c.z));
     }
 }
 
@@ -260,73 +257,60 @@ CV_HD float wb_half_area(const WBox& a) {
     return e.x * e.y + e.y * e.z + e.z * e.x;
 }
 
-// one thread per item: SAH sweep over the 15 planes, children boxes from the bins, child
-// records written into this item's pair, interior children queued for the next level
-CV_D void wb_body_split(const WBuild& b, int w, int level) {
-    const int n_items = b.counters[kWLevelBase + level];
-    if (w >= n_items) return;
-    WItem& it = b.items[w];
-    WBox box[2], cb[2];
-    int cnt[2];
-    if (it.axis >= 0) {
-        const WBins& bins = b.bins[w];
-        int best = -1, best_slot = 0;
-        float best_cost = CV_INF;
-        for (int a = 0; a < kWAxes; ++a) {
-            const WBin* ab = &bins.b[a * kWBins];
-            // suffix areas, then a prefix sweep
-            float right_area[kWBins];
-            int right_cnt[kWBins];
-            WBox acc = wb_empty();
-            int n = 0;
-            for (int k = kWBins - 1; k >= 1; --k) {
-                const WBin& s = ab[k];
-                if (s.count > 0) wb_grow(acc, f3(ordered_value(s.mn[0]), ordered_value(s.mn[1]), ordered_value(s.mn[2])), f3(ordered_value(s.mx[0]), ordered_value(s.mx[1]), ordered_value(s.mx[2])));
-                n += s.count;
-                right_area[k] = n > 0 ? wb_half_area(acc) : 0.0f;
-                right_cnt[k] = n;
-            }
-            acc = wb_empty();
-            n = 0;
-            for (int k = 0; k < kWBins - 1; ++k) {
-                const WBin& s = ab[k];
-                if (s.count > 0) wb_grow(acc, f3(ordered_value(s.mn[0]), ordered_value(s.mn[1]), ordered_value(s.mn[2])), f3(ordered_value(s.mx[0]), ordered_value(s.mx[1]), ordered_value(s.mx[2])));
-                n += s.count;
-                if (n == 0 || right_cnt[k + 1] == 0) continue;
-                const float cost = (float)n * wb_half_area(acc) + (float)right_cnt[k + 1] * right_area[k + 1];
-                if (cost < best_cost) {
-                    best_cost = cost;
-                    best = k;
-                    best_slot = a;
-                }
-            }
-        }
-        if (best < 0) {
-            it.axis = -1;  // everything in one bin (cannot happen with a positive extent; kept as a guard)
-        } else {
-            if (kWAxes > 1) it.axis = best_slot;
-            it.split = best;
-            box[0] = box[1] = cb[0] = cb[1] = wb_empty();
-            cnt[0] = cnt[1] = 0;
-            for (int k = 0; k < kWBins; ++k) {
-                const WBin& src = bins.b[best_slot * kWBins + k];
-                if (src.count == 0) continue;
-                const int s = k <= best ? 0 : 1;
-                wb_grow(box[s], f3(ordered_value(src.mn[0]), ordered_value(src.mn[1]), ordered_value(src.mn[2])), f3(ordered_value(src.mx[0]), ordered_value(src.mx[1]), ordered_value(src.mx[2])));
-                wb_grow(cb[s], f3(ordered_value(src.cmn[0]), ordered_value(src.cmn[1]), ordered_value(src.cmn[2])),
-                        f3(ordered_value(src.cmx[0]), ordered_value(src.cmx[1]), ordered_value(src.cmx[2])));
-                cnt[s] += src.count;
-            }
+// The 16 bins of one axis as the sweep sees them (an empty bin is the empty box)
+struct WLBin {
+    int count;
+    WBox box;
+};
+CV_HD WLBin wb_lbin_of(const WBin& s) {
+    WLBin r;
+    r.count = (int)s.count;
+    r.box = wb_empty();
+    if (r.count > 0) {
+        r.box.mn = f3(ordered_value(~s.nmn[0]), ordered_value(~s.nmn[1]), ordered_value(~s.nmn[2]));
+        r.box.mx = f3(ordered_value(s.mx[0]), ordered_value(s.mx[1]), ordered_value(s.mx[2]));
+    }
+    return r;
+}
+// SAH sweep over the 15 planes of one axis slot: cost(k) = n_left * area_left + n_right * area_right; a plane with an
+// empty side is no candidate.  Updates (best_cost, best_key = slot * 16 + plane) on a strictly smaller cost, so over
+// slots 0..2 and planes 0..14 in order the winner is the lexicographic minimum of (cost, key) -- which is how the
+// device's warp-wide version (k_wb_split_binned, kernels.cu) states it.
+CV_HD void wb_sweep(const WLBin* lb, int slot, float& best_cost, int& best_key) {
+    float right_area[kWBins];
+    int right_cnt[kWBins];
+    WBox acc = wb_empty();
+    int n = 0;
+    for (int k = kWBins - 1; k >= 1; --k) {
+        wb_grow(acc, lb[k].box.mn, lb[k].box.mx);
+        n += lb[k].count;
+        right_area[k] = n > 0 ? wb_half_area(acc) : 0.0f;
+        right_cnt[k] = n;
+    }
+    acc = wb_empty();
+    n = 0;
+    for (int k = 0; k < kWBins - 1; ++k) {
+        wb_grow(acc, lb[k].box.mn, lb[k].box.mx);
+        n += lb[k].count;
+        if (n == 0 || right_cnt[k + 1] == 0) continue;
+        const float cost = (float)n * wb_half_area(acc) + (float)right_cnt[k + 1] * right_area[k + 1];
+        if (cost < best_cost) {
+            best_cost = cost;
+            best_key = slot * kWBins + k;
         }
     }
+}
+
+// Second half of a split, shared by every path: the item's two children (boxes and counts known) become leaf
+// references or interior items of the next level; the sibling pair is written.  box[] / cnt[] are ignored for a
+// median split (axis < 0).
+CV_D void wb_finish_split(const WBuild& b, WItem& it, int level, WBox box[2], int cnt[2]) {
     if (it.axis < 0) {
         cnt[0] = it.count / 2;
         cnt[1] = it.count - cnt[0];
         for (int s = 0; s < 2; ++s) {
             box[s].mn = f3(it.box_mn[0], it.box_mn[1], it.box_mn[2]);
             box[s].mx = f3(it.box_mx[0], it.box_mx[1], it.box_mx[2]);
-            cb[s].mn = f3(it.cb_mn[0], it.cb_mn[1], it.cb_mn[2]);
-            cb[s].mx = f3(it.cb_mx[0], it.cb_mx[1], it.cb_mx[2]);
         }
     }
     it.n_left = cnt[0];
@@ -339,7 +323,8 @@ CV_D void wb_body_split(const WBuild& b, int w, int level) {
         } else {
             const int pair = cv_atomic_add_i32(&b.counters[1], 1);
             const int slot = cv_atomic_add_i32(&b.counters[kWLevelBase + level + 1], 1);
-            if (pair >= b.pairs_capacity || slot >= b.items_capacity) {
+            const int bins_slot = cnt[s] > kWDirectMax ? cv_atomic_add_i32(&b.counters[kWBinBase + level + 1], 1) : -1;
+            if (pair >= b.pairs_capacity || slot >= b.items_capacity || bins_slot >= b.bins_capacity) {
                 cv_atomic_or_i32(&b.counters[2], WB_ERR_CAPACITY);
                 ref = make_leaf_ref(start, 1);
             } else {
@@ -350,14 +335,13 @@ CV_D void wb_body_split(const WBuild& b, int w, int level) {
                 c.count = cnt[s];
                 c.pair = pair;
                 c.depth = it.depth + 1;
-                c.axis = -1;
-                for (int a = 0; a < 3; ++a) c.cmin[a] = c.cscale[a] = 0.0f;
                 c.split = c.n_left = 0;
                 c.child_item[0] = c.child_item[1] = -1;
+                c.bins_slot = bins_slot;
+                c.scan_tile = c.scan_local = 0;
                 c.box_mn[0] = box[s].mn.x; c.box_mn[1] = box[s].mn.y; c.box_mn[2] = box[s].mn.z;
                 c.box_mx[0] = box[s].mx.x; c.box_mx[1] = box[s].mx.y; c.box_mx[2] = box[s].mx.z;
-                c.cb_mn[0] = cb[s].mn.x; c.cb_mn[1] = cb[s].mn.y; c.cb_mn[2] = cb[s].mn.z;
-                c.cb_mx[0] = cb[s].mx.x; c.cb_mx[1] = cb[s].mx.y; c.cb_mx[2] = cb[s].mx.z;
+                wb_item_setup(c, b.force_median);
                 b.items_next[slot] = c;
             }
         }
@@ -370,34 +354,88 @@ CV_D void wb_body_split(const WBuild& b, int w, int level) {
     }
 }
 
-CV_D void wb_body_flag(const WBuild& b, int i) {
-    if (i >= b.n_prims) return;
-    const int w = b.node_of[i];
-    unsigned char f = 0;
-    if (w >= 0) {
-        const WItem& it = b.items[w];
-        if (it.axis >= 0) {
-            const int p = b.order[i];
-            f = wb_bin_of(it, it.axis, b.bmin[p], b.bmax[p]) <= it.split ? 1 : 0;
+// One thread per item: SAH sweep over every binned axis (the bins come from the arena, which is cleared as it is
+// read, or -- items of at most kWDirectMax prims -- straight from the item's prims), child boxes from the winning
+// axis' bins (the bottom-up AABB reduction is folded into the binning), then wb_finish_split.
+// with_arena_items = false: items that own arena bins are left to the device's warp-wide kernel.
+CV_D void wb_body_split(const WBuild& b, int w, int level, bool with_arena_items) {
+    const int n_items = b.counters[kWLevelBase + level];
+    if (w >= n_items) return;
+    WItem& it = b.items[w];
+    if (!with_arena_items && it.axis >= 0 && it.bins_slot >= 0) return;
+    WBox box[2];
+    int cnt[2] = { 0, 0 };
+    box[0] = box[1] = wb_empty();
+    if (it.axis >= 0) {
+        WLBin lb[kWBins], best_lb[kWBins];
+        float best_cost = CV_INF;
+        int best_key = -1;
+        for (int a = 0; a < kWAxes; ++a) {
+            if (it.bins_slot >= 0) {
+                WBin* src = &b.bins[it.bins_slot].b[a * kWBins];
+                for (int k = 0; k < kWBins; ++k) {
+                    lb[k] = wb_lbin_of(src[k]);
+                    WBin z = {};
+                    src[k] = z;
+                }
+            } else {
+                for (int k = 0; k < kWBins; ++k) {
+                    lb[k].count = 0;
+                    lb[k].box = wb_empty();
+                }
+                const int axis = wb_slot_axis(it, a);
+                for (int j = 0; j < it.count; ++j) {
+                    const int p = b.order[it.start + j];
+                    const F4 mn = b.bmin[p], mx = b.bmax[p];
+                    WLBin& d = lb[wb_bin_of(it, axis, mn, mx)];
+                    ++d.count;
+                    wb_grow(d.box, f3(mn.x, mn.y, mn.z), f3(mx.x, mx.y, mx.z));
+                }
+            }
+            const int before = best_key;
+            wb_sweep(lb, a, best_cost, best_key);
+            if (best_key != before) {
+                for (int k = 0; k < kWBins; ++k) best_lb[k] = lb[k];
+            }
+        }
+        if (best_key < 0) {
+            it.axis = -1;  // every prim in one bin on every axis (coincident centres): median split
         } else {
-            f = (i - it.start) < it.n_left ? 1 : 0;
+            it.axis = wb_slot_axis(it, best_key / kWBins);
+            it.split = best_key % kWBins;
+            for (int k = 0; k < kWBins; ++k) {
+                if (best_lb[k].count == 0) continue;
+                const int s = k <= it.split ? 0 : 1;
+                wb_grow(box[s], best_lb[k].box.mn, best_lb[k].box.mx);
+                cnt[s] += best_lb[k].count;
+            }
         }
     }
-    b.flags[i] = f;
+    wb_finish_split(b, it, level, box, cnt);
 }
 
-CV_D void wb_body_scatter(const WBuild& b, int i) {
-    if (i >= b.n_prims) return;
+// does prim position i go to the left child of its item?
+CV_D unsigned char wb_flag_of(const WBuild& b, int i) {
     const int w = b.node_of[i];
-    if (w < 0) {
-        b.order_next[i] = b.order[i];
-        b.node_of_next[i] = -1;
-        return;
-    }
+    if (w < 0) return 0;
     const WItem& it = b.items[w];
-    const int lefts_before = b.scan[i] - b.scan[it.start];
+    if (it.axis >= 0) {
+        const int p = b.order[i];
+        return wb_bin_of(it, it.axis, b.bmin[p], b.bmax[p]) <= it.split ? 1 : 0;
+    }
+    return (i - it.start) < it.n_left ? 1 : 0;
+}
+CV_D void wb_body_flag(const WBuild& b, int i) {
+    if (i >= b.n_prims) return;
+    b.flags[i] = wb_flag_of(b, i);
+}
+
+// stable partition: scan_i = left flags before position i (whole array), scan_start = the same at the item's start
+CV_D void wb_scatter_to(const WBuild& b, int i, int w, unsigned char flag, int scan_i, int scan_start) {
+    const WItem& it = b.items[w];
+    const int lefts_before = scan_i - scan_start;
     int dst, side;
-    if (b.flags[i]) {
+    if (flag) {
         dst = it.start + lefts_before;
         side = 0;
     } else {
@@ -407,71 +445,48 @@ CV_D void wb_body_scatter(const WBuild& b, int i) {
     b.order_next[dst] = b.order[i];
     b.node_of_next[dst] = it.child_item[side];
 }
+CV_D void wb_body_scatter(const WBuild& b, int i) {
+    if (i >= b.n_prims) return;
+    const int w = b.node_of[i];
+    if (w < 0) {
+        b.order_next[i] = b.order[i];
+        b.node_of_next[i] = -1;
+        return;
+    }
+    wb_scatter_to(b, i, w, b.flags[i], b.scan[i], b.scan[b.items[w].start]);
+}
 
 // ---- emit: slot s of the final order holds prim order[s] --------------------------------------
 // World-space vertices (the same wb_world() values the boxes were built from) and the vertex
 // normals times the world matrix.  A mirroring instance (det < 0) flips the winding the reference's mesh-space
 // back-face test sees (shared_path_tracer.h:106), so its triangles are stored as (A, C, B).
-// Quad records: when the triangle in the NEXT slot belongs to the same instance, starts at the same vertex A and shares
-// this triangle's AC as its AB (flag 1) or this triangle's AB as its AC (flag 2) -- the two halves of a grid cell, 95 % of
-// the two-triangle leaves of the config scenes -- its one remaining edge goes into this record's spare 16 bytes and the
-// flag into v2.w.  A two-triangle leaf that starts at a flagged slot is then tested from ONE record (walk_test_triangle):
-// the second triangle's (A, AB, AC) are bit for bit those of its own record.  The flag is a property of slots s, s+1
-// alone; the tracer consults it only when slot s opens a two-triangle leaf.
-struct WTriGeom {
-    F3 a, ab, ac, na, nb, nc;
-};
-CV_D WTriGeom wb_tri_geom(const WBuild& b, uint32_t tri, uint32_t inst) {
+CV_D void wb_emit_slot(const WBuild& b, int s, uint32_t tri, uint32_t inst);
+CV_D void wb_body_emit(const WBuild& b, int s) {
+    if (s >= b.n_prims) return;
+    const int p = b.order[s];
+    wb_emit_slot(b, s, f2u(b.bmin[p].w), f2u(b.bmax[p].w));
+}
+CV_D void wb_emit_slot(const WBuild& b, int s, uint32_t tri, uint32_t inst) {
     const float* m = b.instances[inst].transform;
     const float det = m[0] * (m[5] * m[10] - m[9] * m[6]) - m[4] * (m[1] * m[10] - m[9] * m[2]) + m[8] * (m[1] * m[6] - m[5] * m[2]);
     const int* idx = b.indices[tri].tri;
     const int i1 = det < 0.0f ? idx[2] : idx[1], i2 = det < 0.0f ? idx[1] : idx[2];
     const GpuPtVertex va = b.vertices[idx[0]], vb = b.vertices[i1], vc = b.vertices[i2];
     const F3 wa = wb_world(m, va.position), wb = wb_world(m, vb.position), wc = wb_world(m, vc.position);
-    WTriGeom g;
-    g.a = wa;
-    g.ab = wb - wa;  // HitTriangle's first two lines (shared_path_tracer.h:94-95)
-    g.ac = wc - wa;
-    g.na = mat_mul(m, f3(va.normal[0], va.normal[1], va.normal[2]), 0.0f);  // the shader's own transform (:210)
-    g.nb = mat_mul(m, f3(vb.normal[0], vb.normal[1], vb.normal[2]), 0.0f);
-    g.nc = mat_mul(m, f3(vc.normal[0], vc.normal[1], vc.normal[2]), 0.0f);
-    return g;
-}
-CV_HD bool wb_same_bits(F3 a, F3 b) { return f2u(a.x) == f2u(b.x) && f2u(a.y) == f2u(b.y) && f2u(a.z) == f2u(b.z); }
-
-// has_next: slot s + 1 exists and holds (tri_next, inst_next)
-CV_D void wb_emit_slot(const WBuild& b, int s, uint32_t tri, uint32_t inst, bool has_next, uint32_t tri_next, uint32_t inst_next) {
-    const WTriGeom g = wb_tri_geom(b, tri, inst);
+    const F3 ab = wb - wa, ac = wc - wa;  // HitTriangle's first two lines (shared_path_tracer.h:94-95)
     FastTri t;
-    t.v0.x = g.a.x; t.v0.y = g.a.y; t.v0.z = g.a.z; t.v0.w = u2f(inst);
-    t.v1.x = g.ab.x; t.v1.y = g.ab.y; t.v1.z = g.ab.z; t.v1.w = u2f(tri);
-    t.v2.x = g.ac.x; t.v2.y = g.ac.y; t.v2.z = g.ac.z; t.v2.w = 0.0f;
+    t.v0.x = wa.x; t.v0.y = wa.y; t.v0.z = wa.z; t.v0.w = u2f(inst);
+    t.v1.x = ab.x; t.v1.y = ab.y; t.v1.z = ab.z; t.v1.w = u2f(tri);
+    t.v2.x = ac.x; t.v2.y = ac.y; t.v2.z = ac.z; t.v2.w = 0.0f;
     t.pad.x = t.pad.y = t.pad.z = t.pad.w = 0.0f;
-    if (has_next && inst_next == inst) {
-        const WTriGeom n = wb_tri_geom(b, tri_next, inst_next);
-        if (wb_same_bits(n.a, g.a)) {
-            if (wb_same_bits(n.ab, g.ac)) {
-                t.v2.w = u2f(1u);
-                t.pad.x = n.ac.x; t.pad.y = n.ac.y; t.pad.z = n.ac.z;
-            } else if (wb_same_bits(n.ac, g.ab)) {
-                t.v2.w = u2f(2u);
-                t.pad.x = n.ab.x; t.pad.y = n.ab.y; t.pad.z = n.ab.z;
-            }
-        }
-    }
     b.ftris[s] = t;
-    t.v0.x = g.na.x; t.v0.y = g.na.y; t.v0.z = g.na.z;
-    t.v1.x = g.nb.x; t.v1.y = g.nb.y; t.v1.z = g.nb.z; t.v1.w = u2f((uint32_t)b.instances[inst].materialId);
-    t.v2.x = g.nc.x; t.v2.y = g.nc.y; t.v2.z = g.nc.z; t.v2.w = 0.0f;
-    t.pad.x = t.pad.y = t.pad.z = t.pad.w = 0.0f;
+    const F3 na = mat_mul(m, f3(va.normal[0], va.normal[1], va.normal[2]), 0.0f);  // the shader's own transform (:210)
+    const F3 nb = mat_mul(m, f3(vb.normal[0], vb.normal[1], vb.normal[2]), 0.0f);
+    const F3 nc = mat_mul(m, f3(vc.normal[0], vc.normal[1], vc.normal[2]), 0.0f);
+    t.v0.x = na.x; t.v0.y = na.y; t.v0.z = na.z;
+    t.v1.x = nb.x; t.v1.y = nb.y; t.v1.z = nb.z; t.v1.w = u2f((uint32_t)b.instances[inst].materialId);
+    t.v2.x = nc.x; t.v2.y = nc.y; t.v2.z = nc.z;
     b.fnormals[s] = t;
-}
-CV_D void wb_body_emit(const WBuild& b, int s) {
-    if (s >= b.n_prims) return;
-    const int p = b.order[s];
-    const bool has_next = s + 1 < b.n_prims;
-    const int pn = has_next ? b.order[s + 1] : p;
-    wb_emit_slot(b, s, f2u(b.bmin[p].w), f2u(b.bmax[p].w), has_next, f2u(b.bmin[pn].w), f2u(b.bmax[pn].w));
 }
 
 // ---- quantise: FastNode pair k -> QPair k --------------------------------------------------
@@ -568,10 +583,7 @@ CV_D void wb_body_retransform(const WBuild& b, int s, const unsigned char* moved
     if (s >= b.n_prims) return;
     const uint32_t inst = f2u(b.ftris[s].v0.w);
     if (!moved[inst]) return;
-    // the next slot's (triangle, instance) words are rewritten by its own thread with the values they already hold
-    const bool has_next = s + 1 < b.n_prims;
-    const int sn = has_next ? s + 1 : s;
-    wb_emit_slot(b, s, f2u(b.ftris[s].v1.w), inst, has_next, f2u(b.ftris[sn].v1.w), f2u(b.ftris[sn].v0.w));
+    wb_emit_slot(b, s, f2u(b.ftris[s].v1.w), inst);
 }
 
 CV_D void wb_body_refit_pair(const WBuild& b, int k, float* area_sum) {
@@ -901,9 +913,8 @@ CV_D void wb_body_lbvh_level(const WBuild& b, int j, int k) {
 
 struct FnWbPrim { WBuild b; CV_D void operator()(int i) const { wb_body_prim(b, i); } };
 struct FnWbInit { WBuild b; CV_D void operator()(int i) const { wb_body_init(b, i); } };
-struct FnWbPrep { WBuild b; int level; CV_D void operator()(int i) const { wb_body_prep(b, i, level); } };
 struct FnWbBin { WBuild b; CV_D void operator()(int i) const { wb_body_bin(b, i); } };
-struct FnWbSplit { WBuild b; int level; CV_D void operator()(int i) const { wb_body_split(b, i, level); } };
+struct FnWbSplit { WBuild b; int level; bool with_arena_items; CV_D void operator()(int i) const { wb_body_split(b, i, level, with_arena_items); } };
 struct FnWbFlag { WBuild b; CV_D void operator()(int i) const { wb_body_flag(b, i); } };
 struct FnWbScatter { WBuild b; CV_D void operator()(int i) const { wb_body_scatter(b, i); } };
 struct FnWbEmit { WBuild b; CV_D void operator()(int i) const { wb_body_emit(b, i); } };
@@ -967,7 +978,12 @@ int wb_prologue(Exec& ex, WBuild& b, WReport* rep, uint32_t acc[12]) {
     return 0;
 }
 
-// Host-side level loop (Exec = CudaExec on the device, EmuExec in the test emulator).
+// Host-side level loop (Exec = CudaExec on the device, EmuExec in the test emulator).  Per level:
+//   bin        one pass over the prims: count + AABB into the arena bins of items of more than kWDirectMax prims
+//   split      per item: SAH sweep over all binned axes, children created with their binning set-up (Exec::wb_split:
+//              the emulator runs wb_body_split per item; the device runs a warp per arena item + a thread per small item)
+//   partition  left flags -> exclusive scan -> stable scatter (Exec::wb_partition: three serial passes in the
+//              emulator; on the device the flags are computed inside the scan's first kernel and the scatter inside its last)
 template<class Exec>
 int build_wbvh(Exec& ex, WBuild b, WReport* rep) {
     uint32_t acc[12];
@@ -977,23 +993,24 @@ int build_wbvh(Exec& ex, WBuild b, WReport* rep) {
     root.count = b.n_prims;
     root.pair = 0;
     root.depth = 0;
-    root.axis = -1;
-    for (int a = 0; a < 3; ++a) root.cmin[a] = root.cscale[a] = 0.0f;
     root.split = root.n_left = 0;
     root.child_item[0] = root.child_item[1] = -1;
+    root.bins_slot = b.n_prims > kWDirectMax ? 0 : -1;
+    root.scan_tile = root.scan_local = 0;
     for (int k = 0; k < 3; ++k) {
         root.box_mn[k] = rep->scene_mn[k] - b.pad;
         root.box_mx[k] = rep->scene_mx[k] + b.pad;
-        root.cb_mn[k] = ordered_value(acc[6 + k]);
-        root.cb_mx[k] = ordered_value(acc[9 + k]);
     }
+    wb_item_setup(root, b.force_median);
     ex.upload(b.items, &root, sizeof(root));
-    // counters: [1] pairs allocated, [2] error bits, [4 + L] interior items of level L.  The level loop
-    // runs kLevelsPerSync levels per device->host round trip: launches over items are sized by an upper
-    // bound (items are disjoint ranges of >= kFastLeafMax + 1 prims, and at most 2^L of them) and read
-    // the true count on the device; a level past the last one finds no items and no prims to move.
+    ex.fill(b.bins, 0, (size_t)b.bins_capacity * sizeof(WBins));  // once: the split pass clears what it reads
+    // counters: [1] pairs allocated, [2] error bits, [kWLevelBase + L] interior items of level L, [kWBinBase + L]
+    // arena slots of level L.  The level loop runs kLevelsPerSync levels per device->host round trip: launches over
+    // items are sized by an upper bound (items are disjoint ranges of >= kFastLeafMax + 1 prims, and at most 2^L of
+    // them) and read the true count on the device; a level past the last one finds no items and no prims to move.
     constexpr int kLevelsPerSync = 4;
-    int counters[kWLevelBase + kWMaxLevels + 4] = { 0, 1, 0, 0, 1 };
+    int counters[kWCounters] = { 0, 1, 0, 0, 1 };
+    counters[kWBinBase] = 1;
     ex.upload(b.counters, counters, sizeof(counters));
     const int items_bound = b.n_prims / (kFastLeafMax + 1) + 1;
     rep->root_ref = 0;
@@ -1002,12 +1019,9 @@ int build_wbvh(Exec& ex, WBuild b, WReport* rep) {
         for (int k = 0; k < kLevelsPerSync; ++k, ++level) {
             const long long pow2 = level < 30 ? (1ll << level) : (1ll << 30);
             const int bound = (int)(pow2 < items_bound ? pow2 : items_bound);
-            ex.launch(bound * kWAxes * kWBins, FnWbPrep{ b, level });
             ex.launch(b.n_prims, FnWbBin{ b });
-            ex.launch(bound, FnWbSplit{ b, level });
-            ex.launch(b.n_prims, FnWbFlag{ b });
-            ex.scan_u8(b.flags, b.scan, b.n_prims);
-            ex.launch(b.n_prims, FnWbScatter{ b });
+            ex.wb_split(b, level, bound);
+            ex.wb_partition(b);
             WItem* ti = b.items; b.items = b.items_next; b.items_next = ti;
             int* to = b.order; b.order = b.order_next; b.order_next = to;
             int* tn = b.node_of; b.node_of = b.node_of_next; b.node_of_next = tn;

@@ -180,6 +180,12 @@ CAVEPT_API int cavept_rebuild_mesh(cavept_ctx* ctx, int mesh, const float* posit
 CAVEPT_API int cavept_get_mesh_bvh(cavept_ctx* ctx, int mesh, void* out_gpu_pt_bvh, int capacity_nodes); /* mesh-local indices, as FillGpuBvhAccel emits; returns count or <0 */
 CAVEPT_API int cavept_get_scene_counts(cavept_ctx* ctx, int* vertices, int* triangles, int* nodes, int* instances, int* materials);
 CAVEPT_API int cavept_get_scene_arrays(cavept_ctx* ctx, void* gpu_pt_vertices, void* gpu_pt_indices, void* gpu_pt_bvhs, void* gpu_pt_meshes, void* gpu_pt_materials); /* any may be NULL */
+/* The production (world-space) tree as the builder emitted it, before quantisation: 32-byte records
+ * {float min[3]; int ref; float max[3]; int count}, siblings adjacent (record 2k, 2k+1 = sibling pair k; an interior
+ * ref = index of the child pair's first record, a leaf ref = sign bit | (count-1) << 29 | first triangle slot).
+ * No counterpart in the reference (HitScene loops over meshes, shared_path_tracer.h:159); read back so that tests can
+ * compare the device-built tree with the serial statement of the same builder.  Returns the record count or < 0. */
+CAVEPT_API int cavept_get_fast_tree(cavept_ctx* ctx, void* out_records, int capacity_records);
 
 /* ---- per-frame constants, PerFrameConstantBuffer c_camera* (cave/shader/cbuffer.hlsl.h:193-207),
  *      filled at cave/engine/runtime/render_system.cpp:89-93.  Marks the scene dirty

@@ -41,6 +41,12 @@ struct EmuExec {
         for (int i = 0; i < n; ++i) { keys[i] = v[i].first; vals[i] = v[i].second; }
     }
     void wb_prim(const WBuild& b) { launch(b.n_prims, FnWbPrim{ b }); }
+    void wb_split(const WBuild& b, int level, int bound) { launch(bound, FnWbSplit{ b, level, true }); }
+    void wb_partition(const WBuild& b) {
+        launch(b.n_prims, FnWbFlag{ b });
+        scan_u8(b.flags, b.scan, b.n_prims);
+        launch(b.n_prims, FnWbScatter{ b });
+    }
     void upload(void* dst, const void* src, size_t bytes) { std::memcpy(dst, src, bytes); }
     void download(void* dst, const void* src, size_t bytes) { std::memcpy(dst, src, bytes); }
     void fill(void* dst, int byte, size_t bytes) { std::memset(dst, byte, bytes); }
@@ -107,10 +113,11 @@ EMU_API int emu_wbvh_build(const GpuPtVertex* vertices, const GpuPtIndex* indice
     const int P = inst_prim_off[n_inst];
     const size_t items_cap = (size_t)P / 2 + 8, pairs_cap = (size_t)P + 8;
     std::vector<F4> bmin(P), bmax(P);
-    std::vector<int> order(P), order_next(P), node_of(P), node_of_next(P), scan(P + 1), counters(cavept::kWLevelBase + cavept::kWMaxLevels + 4);
+    std::vector<int> order(P), order_next(P), node_of(P), node_of_next(P), scan(P + 1), counters(cavept::kWCounters);
     std::vector<unsigned char> flags(P);
     std::vector<WItem> items(items_cap), items_next(items_cap);
-    std::vector<WBins> bins(items_cap);
+    const size_t bins_cap = (size_t)P / (cavept::kWDirectMax + 1) + 2;
+    std::vector<WBins> bins(bins_cap);
     std::vector<uint32_t> root_acc(12);
     WBuild b{};
     b.vertices = vertices;
@@ -140,6 +147,7 @@ EMU_API int emu_wbvh_build(const GpuPtVertex* vertices, const GpuPtIndex* indice
     b.items_next = items_next.data();
     b.bins = bins.data();
     b.items_capacity = (int)items_cap;
+    b.bins_capacity = (int)bins_cap;
     b.pairs_capacity = (int)pairs_cap;
     b.counters = counters.data();
     b.root_acc = root_acc.data();

@@ -595,8 +595,9 @@ def test_kernel_variants_are_bitwise_identical(api, scene_cache, name, w, h, mb,
     """CAVEPT_KERNEL_PIXEL (one thread per pixel on a grid of tiles, the default), CAVEPT_KERNEL_QUEUE (persistent warps +
     job queue) and CAVEPT_KERNEL_POOL (job queue + two pixel streams per lane) run the same per-pixel arithmetic in
     the same per-pixel order: identical accumulator bytes and segment counts, over two launches and on a ragged image.
-    (Node visits may differ by a fraction of a percent: how many speculative steps a lane takes before its parked
-    triangles are tested depends on its warp's votes; the closest hit does not.)"""
+    (Node visits and triangle tests may differ by a few percent -- measured on the B200, sponza 640x360: POOL +2.0 % / +2.7 %
+    against PIXEL: how many speculative steps a lane takes before its parked triangles are tested depends on its warp's
+    votes; the closest hit does not.)"""
     sc = scene_cache(name)
     out = {}
     for variant in (api.KernelVariant.QUEUE, api.KernelVariant.PIXEL, api.KernelVariant.POOL):
@@ -612,7 +613,7 @@ def test_kernel_variants_are_bitwise_identical(api, scene_cache, name, w, h, mb,
     for variant in (api.KernelVariant.QUEUE, api.KernelVariant.POOL):
         a = out[variant]
         assert a[1] == b[1], variant
-        assert abs(a[2] - b[2]) <= b[2] // 50 and abs(a[3] - b[3]) <= b[3] // 50, (variant, a[1:], b[1:])
+        assert abs(a[2] - b[2]) <= b[2] // 25 and abs(a[3] - b[3]) <= b[3] // 20, (variant, a[1:], b[1:])
         differ = int((a[0] != b[0]).any(axis=-1).sum())
         assert differ == 0, f"{variant.name}: {differ} pixels differ from the per-pixel kernel"
     assert np.all(b[0][..., 3] == float(frames + 2))
@@ -680,3 +681,30 @@ def test_queue_kernel_tiles_and_single_frame_launches(api, scene_cache):
             pt.render_tile(0, 0, w, h, 3, 2, sync=True)
             imgs.append(pt.read_accum())
     assert imgs[0].tobytes() == imgs[1].tobytes()
+
+
+# ---- the device's SAH builder against the serial statement of the same builder ----------------------------
+def _canonical_tree(rec):
+    """Pair numbering depends on the order in which a level's items allocate their children (atomics on the device):
+    compare the multiset of (box, subtree triangle count, leaf reference) records -- leaf references are slot ranges
+    of the final prim order, which is deterministic (stable partition)."""
+    leaf = rec["a"] < 0
+    a = np.where(leaf, rec["a"], 0).astype(np.int64)
+    key = np.concatenate([rec["mn"].view(np.uint32).astype(np.int64), rec["mx"].view(np.uint32).astype(np.int64), rec["b"].astype(np.int64)[:, None], a[:, None]], axis=1)
+    return key[np.lexsort(key.T[::-1])]
+
+
+@pytest.mark.parametrize("name", ["tiny", "cornell", "sponza"])
+def test_device_sah_tree_equals_the_serial_builder(api, port_oracle, scene_cache, name):
+    """The device runs the SAH split as one warp per item (k_wb_split_binned) and the partition fused into the scan
+    kernels; tests/emu runs wbvh_body.h's per-item / per-prim bodies serially.  Same boxes, same counts, same leaves."""
+    import emu_loader
+
+    sc = scene_cache(name)
+    emu = emu_loader.EmuScene(port_oracle.assemble(sc), sc)
+    want = emu.fnodes[: 2 * emu.n_pairs]
+    with _tracer(api, sc, 64, 36, 5, api.TraceMode.FAST, api.BvhMode.FAST) as pt:
+        got = pt.get_fast_tree()
+        st = pt.stats()
+    assert st["fast_build_levels"] == emu.fast_levels and got.shape[0] == want.shape[0], (st["fast_build_levels"], emu.fast_levels, got.shape, want.shape)
+    assert np.array_equal(_canonical_tree(got), _canonical_tree(want))

@@ -105,7 +105,8 @@ int build_world(cavept_ctx* ctx) {
     CU(ctx, ctx->d_w_root_acc.reserve(12));
     CU(ctx, ctx->d_fnodes.reserve(2 * pairs_cap));
     CU(ctx, ctx->d_qpairs.reserve(pairs_cap));
-    CU(ctx, ctx->d_q4nodes.reserve(pairs_cap));
+    const bool want_q4 = ctx->kernel_variant == CAVEPT_KERNEL_WIDE4;  // the four-wide records exist only while that variant is selected
+    if (want_q4) CU(ctx, ctx->d_q4nodes.reserve(pairs_cap));
     CU(ctx, ctx->d_ftris.reserve(P));
     CU(ctx, ctx->d_fnormals.reserve(P));
     ctx->ex.scan_tmp = ctx->d_scan_tmp.ptr;
@@ -144,7 +145,7 @@ int build_world(cavept_ctx* ctx) {
     b.nbox_mx = ctx->d_w_nbox_mx.ptr;
     b.fnodes = ctx->d_fnodes.ptr;
     b.qpairs = ctx->d_qpairs.ptr;
-    b.q4nodes = ctx->d_q4nodes.ptr;
+    b.q4nodes = want_q4 ? ctx->d_q4nodes.ptr : nullptr;
     b.ftris = ctx->d_ftris.ptr;
     b.fnormals = ctx->d_fnormals.ptr;
 
@@ -173,6 +174,7 @@ int build_world(cavept_ctx* ctx) {
         ctx->grid_scale[k] = rep.grid_scale[k];
     }
     ctx->fast_levels = rep.levels;
+    ctx->q4_ready = want_q4;
     ctx->stats.fast_node_count = 2 * rep.n_pairs;
     // what a later refit needs (SAH builder: the pairs of a level are one index range)
     ctx->refit_ready = !lbvh && rep.levels > 0;
@@ -202,7 +204,7 @@ int refit_world(cavept_ctx* ctx, const std::vector<unsigned char>& moved) {
     b.pad = ctx->world_pad;
     b.fnodes = ctx->d_fnodes.ptr;
     b.qpairs = ctx->d_qpairs.ptr;
-    b.q4nodes = ctx->d_q4nodes.ptr;
+    b.q4nodes = ctx->q4_ready ? ctx->d_q4nodes.ptr : nullptr;
     b.ftris = ctx->d_ftris.ptr;
     b.fnormals = ctx->d_fnormals.ptr;
     for (int k = 0; k < 3; ++k) {
@@ -648,7 +650,7 @@ static int render_rect(cavept_ctx* ctx, int x0, int y0, int w, int h, int first_
     p.mesh_count = (int)ctx->gpu_meshes.size();
     p.fnodes = ctx->d_fnodes.ptr;
     p.qpairs = ctx->d_qpairs.ptr;
-    p.q4nodes = ctx->d_q4nodes.ptr;
+    p.q4nodes = ctx->q4_ready ? ctx->d_q4nodes.ptr : nullptr;
     for (int k = 0; k < 3; ++k) {
         p.grid_origin[k] = ctx->grid_origin[k];
         p.grid_scale[k] = ctx->grid_scale[k];
@@ -691,7 +693,7 @@ static int render_rect(cavept_ctx* ctx, int x0, int y0, int w, int h, int first_
     CU(ctx, cudaEventRecord(ctx->ev0, ctx->ex.stream));
     if (grid_blocks > 0) launch_trace_pool(ctx->ex, p, ctx->count_visits, stack_entries, ctx->d_job_counter.ptr, grid_blocks);
     else if (fast && ctx->kernel_variant == CAVEPT_KERNEL_QUEUE) launch_trace_queue(ctx->ex, p, ctx->count_visits, ctx->d_job_counter.ptr, ctx->n_sms);
-    else if (fast && ctx->kernel_variant == CAVEPT_KERNEL_WIDE4 && ctx->fast_levels <= kWideMaxLevels && ctx->n_pairs > 0) launch_trace_wide(ctx->ex, p, ctx->count_visits);
+    else if (fast && ctx->kernel_variant == CAVEPT_KERNEL_WIDE4 && ctx->q4_ready && ctx->fast_levels <= kWideMaxLevels && ctx->n_pairs > 0) launch_trace_wide(ctx->ex, p, ctx->count_visits);
     else launch_trace(ctx->ex, p, fast, ctx->count_visits);
     CU(ctx, cudaEventRecord(ctx->ev1, ctx->ex.stream));
     ctx->dirty = false;
@@ -863,6 +865,21 @@ CAVEPT_API int cavept_set_kernel_variant(cavept_ctx* ctx, int variant) {
     if (!ctx) return CAVEPT_ERR_INVALID_ARG;
     if (variant != CAVEPT_KERNEL_POOL && variant != CAVEPT_KERNEL_PIXEL && variant != CAVEPT_KERNEL_QUEUE && variant != CAVEPT_KERNEL_WIDE4) return fail(ctx, CAVEPT_ERR_INVALID_ARG, "invalid kernel variant %d", variant);
     ctx->kernel_variant = variant;
+    if (variant == CAVEPT_KERNEL_WIDE4 && ctx->scene_resident && !ctx->q4_ready && ctx->n_pairs > 0) {
+        // build the four-wide records over the resident tree (wbvh_body.h wb_body_q4)
+        if (int e = select_device(ctx)) return e;
+        CU(ctx, ctx->d_q4nodes.reserve((size_t)ctx->n_prims + 8));
+        WBuild b{};
+        b.fnodes = ctx->d_fnodes.ptr;
+        b.q4nodes = ctx->d_q4nodes.ptr;
+        for (int k = 0; k < 3; ++k) {
+            b.grid_origin[k] = ctx->grid_origin[k];
+            b.grid_scale[k] = ctx->grid_scale[k];
+        }
+        run_build_q4(ctx->ex, b, ctx->n_pairs);
+        if (int e = check_exec(ctx, "four-wide records")) return e;
+        ctx->q4_ready = true;
+    }
     return CAVEPT_OK;
 }
 

@@ -103,6 +103,7 @@ struct cavept_ctx {
     DevBuf<FastNode> d_fnodes;
     DevBuf<QPair> d_qpairs;
     DevBuf<Q4Node> d_q4nodes;
+    bool q4_ready = false;  // four-wide records built over the resident tree (CAVEPT_KERNEL_WIDE4 only)
     float grid_origin[3] = { 0, 0, 0 }, grid_scale[3] = { 1, 1, 1 };
     DevBuf<FastTri> d_ftris, d_fnormals;
     DevBuf<int> d_inst_prim_off, d_inst_tri_off;

@@ -483,6 +483,7 @@ int run_build_bvh_parity(CudaExec& ex, BuildArrays a, const int* tri_off_host, c
 }
 int run_build_wbvh(CudaExec& ex, WBuild b, WReport* report) { return build_wbvh(ex, b, report); }
 int run_build_lbvh(CudaExec& ex, WBuild b, WReport* report) { return build_lbvh(ex, b, report); }
+void run_build_q4(CudaExec& ex, WBuild b, int n_pairs) { ex.launch(n_pairs, FnWbQ4{ b, n_pairs }); }
 void run_refit_wbvh(CudaExec& ex, WBuild b, const int* level_start, int n_levels, const unsigned char* d_moved, float* d_area_sum, float out[7]) {
     refit_wbvh(ex, b, level_start, n_levels, d_moved, d_area_sum, out);
 }

@@ -300,6 +300,48 @@ EMU_API long long emu_render(const GpuPtVertex* vertices, const GpuPtIndex* indi
     return segs;
 }
 
+// Closest primary-ray hit per pixel (frame `frame`): mode 0 = every triangle slot tested in turn with the kernel's own
+// triangle arithmetic (no tree: the ground truth a traversal may not lose), 1 = the production walk.
+// out_slot[pixel] = FastTri slot or -1, out_t[pixel] = ray.t after the query.
+static void emu_walk_one(const TraceParams& p, Walk& w, Ray& ray) {
+    walk_begin(p, w, ray);
+    for (;;) {
+        walk_park_leaf(w);
+        if (ref_is_interior(w.ref)) walk_step<false>(p, w, ray.t, nullptr);
+        else if (w.q0 != 0) walk_test_triangle<false>(p, w, ray, ray.t, nullptr);
+        else break;
+    }
+}
+EMU_API void emu_primary_hits(const FastNode* fnodes, const QPair* qpairs, const float* grid, const FastTri* ftris, int n_slots, int root_ref, const EmuCamera* cam,
+                              int width, int height, int frame, int mode, int* out_slot, float* out_t) {
+    TraceParams p = emu_params(nullptr, nullptr, nullptr, nullptr, 0, nullptr, fnodes, qpairs, grid, ftris, nullptr, root_ref, cam, 1, width, height, frame, 1, 1, nullptr);
+    int stack[kStackSize];
+    for (int y = 0; y < height; ++y) {
+        for (int x = 0; x < width; ++x) {
+            Ray ray;
+            uint32_t seed;
+            start_path(p, x, y, frame, ray, seed);
+            int slot = -1;
+            if (mode == 0) {
+                for (int s = 0; s < n_slots; ++s) {
+                    float u, v;
+                    const FastTri& t = ftris[s];
+                    if (hit_triangle_edges(f3(t.v0.x, t.v0.y, t.v0.z), f3(t.v1.x, t.v1.y, t.v1.z), f3(t.v2.x, t.v2.y, t.v2.z), ray.origin, ray.direction, ray.t, u, v)) slot = s;
+                }
+            } else {
+                Walk w;
+                w.stack = stack;
+                w.stride = 1;
+                w.spill = nullptr;
+                emu_walk_one(p, w, ray);
+                slot = w.hit_slot;
+            }
+            out_slot[(size_t)y * width + x] = slot;
+            out_t[(size_t)y * width + x] = ray.t;
+        }
+    }
+}
+
 #if defined(CV_WARP_EMU)
 // ---- warps of 32 host threads: the votes (__any_sync / __ballot_sync) and the warp-aggregated job draw go through a
 //      barrier, so the warp-level scheduling of the persistent kernel (who draws, who retires, when the loop ends)

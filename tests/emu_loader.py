@@ -130,6 +130,18 @@ class EmuScene:
                                    counters)
         return accum, {"segments": int(segs), "node_visits": int(counters[1]), "tri_tests": int(counters[2])}
 
+    def primary_hits(self, camera, width, height, frame=0, mode=1):
+        """(FastTri slot or -1, ray.t) of every pixel's camera ray: mode 0 = all triangles tested (no tree), 1 = the
+        production walk."""
+        from oracle.oracle import _cam
+
+        cam = _cam(camera)
+        slot = np.zeros((height, width), dtype=np.int32)
+        t = np.zeros((height, width), dtype=np.float32)
+        self.lib.emu_primary_hits(_p(self.fnodes), _p(self.qpairs), _p(self.grid), _p(self.ftris), C.c_int(self.n_prims), C.c_int(self.root_ref), C.byref(cam),
+                                  C.c_int(width), C.c_int(height), C.c_int(frame), C.c_int(mode), _p(slot), _p(t))
+        return slot, t
+
     def render_warps(self, camera, width, height, first_frame, n_frames, max_bounce, n_warps=2, tile=None, accum=None, reset_first=True):
         """k_trace_queue on n_warps concurrent warps of 32 host threads each (real divergence between lanes)."""
         from oracle.oracle import _cam

@@ -708,3 +708,25 @@ def test_device_sah_tree_equals_the_serial_builder(api, port_oracle, scene_cache
         st = pt.stats()
     assert st["fast_build_levels"] == emu.fast_levels and got.shape[0] == want.shape[0], (st["fast_build_levels"], emu.fast_levels, got.shape, want.shape)
     assert np.array_equal(_canonical_tree(got), _canonical_tree(want))
+
+
+def test_fast_equals_reference_walk_with_the_camera_100_extents_away(api, scene_cache):
+    """ADVICE r1 (quantised slab test vs a far camera): heightfield (identity instance) seen from 100 scene extents
+    away through a narrowed view; the production traversal returns HitScene's hits, pixel for pixel (the emulator test
+    test_walk_loses_no_hit_with_the_camera_far_outside_the_scene holds the ground truth up to 1000 extents)."""
+    import copy
+
+    sc = copy.deepcopy(scene_cache("heightfield"))
+    pos = np.concatenate([m.positions.reshape(-1, 3) for m in sc.meshes])
+    c = 0.5 * (pos.min(0) + pos.max(0))
+    ext = float((pos.max(0) - pos.min(0)).max())
+    d = np.array([0.3, 0.5, -1.0])
+    sc.camera = scenes.look_at(c + d / np.linalg.norm(d) * ext * 100.0, c, float(np.degrees(np.arctan(120.0))))
+    imgs = []
+    for mode in (api.TraceMode.REFERENCE_WALK, api.TraceMode.FAST):
+        with _tracer(api, sc, 256, 144, 5, mode) as pt:
+            pt.reset_stats()
+            pt.render(0, 2, sync=True)
+            imgs.append((pt.read_accum(), pt.stats()["segments"]))
+    assert imgs[0][1] == imgs[1][1] and imgs[0][1] > 256 * 144 * 2 * 1.1  # same segment count, and the scene is in view
+    H.check_metrics(H.image_metrics(imgs[1][0], imgs[0][0]), {"exact": 0.999}, "fast_vs_walk_far_camera")

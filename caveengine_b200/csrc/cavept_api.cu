@@ -76,7 +76,7 @@ int build_world(cavept_ctx* ctx) {
     const int P = (int)total;
     ctx->n_prims = P;
     // interior items of a level are disjoint ranges of >= kFastLeafMax + 1 prims; only those of more than kWDirectMax prims own arena bins
-    const size_t items_cap = (size_t)P / (kFastLeafMax + 1) + 8, pairs_cap = (size_t)P + 8, bins_cap = (size_t)P / (kWDirectMax + 1) + 2;
+    const size_t items_cap = (size_t)P / (kFastLeafMax + 1) + 8, pairs_cap = (size_t)P + 8, bins_cap = (size_t)P / (kWDirectMax + 1) + 2, sub_cap = (size_t)P / 128 + 64;
     CU(ctx, ctx->d_inst_prim_off.reserve(n_inst + 1));
     CU(ctx, ctx->d_inst_tri_off.reserve(n_inst));
     CU(ctx, ctx->d_prim_bmin.reserve(P));
@@ -100,6 +100,8 @@ int build_world(cavept_ctx* ctx) {
         CU(ctx, ctx->d_w_items.reserve(items_cap));
         CU(ctx, ctx->d_w_items_next.reserve(items_cap));
         CU(ctx, ctx->d_w_bins.reserve(bins_cap));
+        CU(ctx, ctx->d_pair_depth.reserve(pairs_cap));
+        CU(ctx, ctx->d_w_sub_roots.reserve(sub_cap));
     }
     CU(ctx, ctx->d_w_counters.reserve(kWCounters));
     CU(ctx, ctx->d_w_root_acc.reserve(12));
@@ -136,6 +138,9 @@ int build_world(cavept_ctx* ctx) {
     b.items_capacity = (int)items_cap;
     b.pairs_capacity = (int)pairs_cap;
     b.bins_capacity = (int)bins_cap;
+    b.pair_depth = ctx->d_pair_depth.ptr;
+    b.sub_roots = ctx->d_w_sub_roots.ptr;
+    b.sub_capacity = (int)sub_cap;
     b.counters = ctx->d_w_counters.ptr;
     b.root_acc = ctx->d_w_root_acc.ptr;
     b.keys = ctx->d_w_keys.ptr;
@@ -178,8 +183,6 @@ int build_world(cavept_ctx* ctx) {
     ctx->stats.fast_node_count = 2 * rep.n_pairs;
     // what a later refit needs (SAH builder: the pairs of a level are one index range)
     ctx->refit_ready = !lbvh && rep.levels > 0;
-    ctx->level_start.assign(1, 0);
-    for (int L = 0; L < rep.levels && !lbvh; ++L) ctx->level_start.push_back(ctx->level_start.back() + rep.level_items[L]);
     ctx->world_pad = rep.pad;
     ctx->world_extent = rep.pad * 1048576.0f;
     ctx->area_baseline = -1.0f;
@@ -211,15 +214,16 @@ int refit_world(cavept_ctx* ctx, const std::vector<unsigned char>& moved) {
         b.grid_origin[k] = ctx->grid_origin[k];
         b.grid_scale[k] = ctx->grid_scale[k];
     }
-    const int n_levels = (int)ctx->level_start.size() - 1;
+    const int n_levels = ctx->fast_levels;
+    b.pair_depth = ctx->d_pair_depth.ptr;
     float out[7];
     if (ctx->area_baseline < 0.0f) {  // first update after a build: the built tree's own surface-area sum (nothing moved: the pass reproduces the tree)
         ctx->ex.fill(ctx->d_moved.ptr, 0, (size_t)n_inst);
-        run_refit_wbvh(ctx->ex, b, ctx->level_start.data(), n_levels, ctx->d_moved.ptr, ctx->d_area_sum.ptr, out);
+        run_refit_wbvh(ctx->ex, b, ctx->n_pairs, n_levels, ctx->d_moved.ptr, ctx->d_area_sum.ptr, out);
         ctx->area_baseline = out[6];
     }
     ctx->ex.upload(ctx->d_moved.ptr, moved.data(), (size_t)n_inst);
-    run_refit_wbvh(ctx->ex, b, ctx->level_start.data(), n_levels, ctx->d_moved.ptr, ctx->d_area_sum.ptr, out);
+    run_refit_wbvh(ctx->ex, b, ctx->n_pairs, n_levels, ctx->d_moved.ptr, ctx->d_area_sum.ptr, out);
     if (check_exec(ctx, "world bvh refit")) return -CAVEPT_ERR_CUDA;
     float extent = 0.0f;
     bool inside = true;

@@ -135,7 +135,8 @@ struct cavept_ctx {
     DevBuf<unsigned long long> d_stats;
     // refit of the production tree on instance updates (wbvh_body.h refit_wbvh): SAH builder only
     bool refit_ready = false, refit_enabled = true;
-    std::vector<int> level_start;        // pairs owned by the interior nodes of level L: [level_start[L], level_start[L+1])
+    DevBuf<WItem> d_w_sub_roots;         // SAH builder: items of <= kWSubMax prims queued for the subtree phase
+    DevBuf<unsigned char> d_pair_depth;  // SAH tree: depth of the interior node owning sibling pair k (the refit's schedule)
     float world_pad = 0.0f, world_extent = 0.0f;  // box padding of the built tree and the largest |coordinate| it was derived from
     float area_baseline = -1.0f;         // surface-area sum of the freshly built tree (SAH cost proxy), computed on first use
     DevBuf<unsigned char> d_moved;

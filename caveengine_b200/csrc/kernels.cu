@@ -286,24 +286,98 @@ __device__ __forceinline__ WBox shfl_box(unsigned mask, const WBox& v, int src, 
     }
     return r;
 }
-__global__ void __launch_bounds__(256) k_wb_split_binned(const WBuild b, int level) {
+// ---- bin pass of the level loop (wbvh_body.h wb_body_bin is the per-prim statement).  The items the level loop keeps
+//      have more than kWSubMax prims, so the 256 consecutive positions of a block fall into at most two of them: the
+//      block bins into shared memory and flushes its non-empty bins with one global atomic per word, instead of
+//      21 global atomics per prim.  (A third item in a block -- only when the subtree queue overflowed -- goes
+//      straight to global memory.)
+__global__ void __launch_bounds__(256) k_wb_bin(const WBuild b) {
+    __shared__ WBin s_bins[2][kWAxes * kWBins];
+    __shared__ int s_w[2];
+    const int tid = threadIdx.x, i = blockIdx.x * 256 + tid;
+    for (int q = tid; q < 2 * kWAxes * kWBins * 8; q += 256) reinterpret_cast<uint32_t*>(&s_bins[0][0])[q] = 0u;
+    if (tid < 2) s_w[tid] = -1;
+    __syncthreads();
+    if (i < b.n_prims) {
+        const int w = b.node_of[i];
+        if (w >= 0) {
+            const WItem& it = b.items[w];
+            if (it.axis >= 0 && it.bins_slot >= 0) {
+                int slot = -1;
+                int old = atomicCAS(&s_w[0], -1, w);
+                if (old == -1 || old == w) {
+                    slot = 0;
+                } else {
+                    old = atomicCAS(&s_w[1], -1, w);
+                    if (old == -1 || old == w) slot = 1;
+                }
+                const int p = b.order[i];
+                const F4 mn = b.bmin[p], mx = b.bmax[p];
+#pragma unroll
+                for (int a = 0; a < kWAxes; ++a) {
+                    const int k = a * kWBins + wb_bin_of(it, wb_slot_axis(it, a), mn, mx);
+                    WBin& bin = slot >= 0 ? s_bins[slot][k] : b.bins[it.bins_slot].b[k];
+                    // lanes of the warp that land in the same bin combine first (match.any + redux.sync): one atomic per word and group
+                    const CvGroup g = cv_group_by(slot >= 0 ? slot * (kWAxes * kWBins) + k : 2 * kWAxes * kWBins + it.bins_slot * (kWAxes * kWBins) + k);
+                    cv_group_add_i32(g, reinterpret_cast<int*>(&bin.count), 1);
+                    cv_group_max_u32(g, &bin.nmn[0], ~ordered_key(mn.x));
+                    cv_group_max_u32(g, &bin.nmn[1], ~ordered_key(mn.y));
+                    cv_group_max_u32(g, &bin.nmn[2], ~ordered_key(mn.z));
+                    cv_group_max_u32(g, &bin.mx[0], ordered_key(mx.x));
+                    cv_group_max_u32(g, &bin.mx[1], ordered_key(mx.y));
+                    cv_group_max_u32(g, &bin.mx[2], ordered_key(mx.z));
+                }
+            }
+        }
+    }
+    __syncthreads();
+    if (tid < 2 * kWAxes * kWBins) {
+        const int slot = tid / (kWAxes * kWBins), k = tid % (kWAxes * kWBins);
+        const int w = s_w[slot];
+        const WBin v = s_bins[slot][k];
+        if (w >= 0 && v.count > 0u) {
+            WBin& bin = b.bins[b.items[w].bins_slot].b[k];
+            atomicAdd(&bin.count, v.count);
+            atomicMax(&bin.nmn[0], v.nmn[0]);
+            atomicMax(&bin.nmn[1], v.nmn[1]);
+            atomicMax(&bin.nmn[2], v.nmn[2]);
+            atomicMax(&bin.mx[0], v.mx[0]);
+            atomicMax(&bin.mx[1], v.mx[1]);
+            atomicMax(&bin.mx[2], v.mx[2]);
+        }
+    }
+}
+void CudaExec::wb_bin(const WBuild& b) {
+    if (b.n_prims <= 0) return;
+    k_wb_bin<<<(b.n_prims + 255) / 256, 256, 0, stream>>>(b);
+    note(cudaGetLastError());
+    ++launches;
+}
+
+// The winner of one item's bins: best = (cost bits << 8) | (slot * 16 + plane), ~0 when no plane has two non-empty sides;
+// box / cnt = the two sides of the winning plane.  All lanes return the same values.
+struct WSweep {
+    unsigned long long best;
+    WBox box[2];
+    int cnt[2];
+};
+template<bool kClear>
+__device__ __forceinline__ WSweep wb_warp_sweep(WBin* item_bins, int lane) {
     constexpr unsigned kAll = 0xffffffffu;
-    const int w = (int)((blockIdx.x * 256u + threadIdx.x) >> 5);
-    const int lane = threadIdx.x & 31, k = lane & 15;
-    if (w >= b.counters[kWLevelBase + level]) return;  // warp-uniform
-    WItem& it = b.items[w];
-    if (it.axis < 0 || it.bins_slot < 0) return;  // median items and small items: FnWbSplit, one thread each
-    unsigned long long best = ~0ull;
-    WBox best_box[2];
-    int best_cnt[2] = { 0, 0 };
-    best_box[0] = best_box[1] = wb_empty();
+    const int k = lane & 15;
+    WSweep r;
+    r.best = ~0ull;
+    r.box[0] = r.box[1] = wb_empty();
+    r.cnt[0] = r.cnt[1] = 0;
     for (int a = 0; a < kWAxes; ++a) {
-        WBin* src = &b.bins[it.bins_slot].b[a * kWBins + k];
+        WBin* src = &item_bins[a * kWBins + k];
         const WBin raw = *src;
-        __syncwarp();
-        if (lane < 16) {
-            WBin z = {};
-            *src = z;
+        if (kClear) {
+            __syncwarp();
+            if (lane < 16) {
+                WBin z = {};
+                *src = z;
+            }
         }
         const WLBin mine = wb_lbin_of(raw);
         int lc = mine.count, rc = mine.count;
@@ -332,24 +406,33 @@ __global__ void __launch_bounds__(256) k_wb_split_binned(const WBuild b, int lev
             const unsigned long long o = __shfl_xor_sync(kAll, key, d);
             key = o < key ? o : key;
         }
-        if (key < best) {  // warp-uniform
-            best = key;
+        if (key < r.best) {  // warp-uniform
+            r.best = key;
             const int kk = (int)(key & 15ull);
-            best_cnt[0] = __shfl_sync(kAll, lc, kk, 16);
-            best_box[0] = shfl_box(kAll, lb, kk, false, 0);
-            best_cnt[1] = __shfl_sync(kAll, rc, kk + 1, 16);
-            best_box[1] = shfl_box(kAll, rb, kk + 1, false, 0);
+            r.cnt[0] = __shfl_sync(kAll, lc, kk, 16);
+            r.box[0] = shfl_box(kAll, lb, kk, false, 0);
+            r.cnt[1] = __shfl_sync(kAll, rc, kk + 1, 16);
+            r.box[1] = shfl_box(kAll, rb, kk + 1, false, 0);
         }
     }
+    return r;
+}
+__global__ void __launch_bounds__(256) k_wb_split_binned(const WBuild b, int level) {
+    const int w = (int)((blockIdx.x * 256u + threadIdx.x) >> 5);
+    const int lane = threadIdx.x & 31;
+    if (w >= b.level_items[level]) return;  // warp-uniform
+    WItem& it = b.items[w];
+    if (it.axis < 0 || it.bins_slot < 0) return;  // median items and small items: FnWbSplit, one thread each
+    WSweep r = wb_warp_sweep<true>(&b.bins[it.bins_slot].b[0], lane);
     if (lane == 0) {
-        if (best == ~0ull) {
+        if (r.best == ~0ull) {
             it.axis = -1;  // every prim in one bin on every axis: median split
         } else {
-            const int key = (int)(best & 0xffull);
+            const int key = (int)(r.best & 0xffull);
             it.axis = wb_slot_axis(it, key / kWBins);
             it.split = key % kWBins;
         }
-        wb_finish_split(b, it, level, best_box, best_cnt);
+        wb_finish_split(b, it, level, r.box, r.cnt);
     }
 }
 void CudaExec::wb_split(const WBuild& b, int level, int bound) {
@@ -432,6 +515,314 @@ void CudaExec::wb_partition(const WBuild& b) {
     launches += 3;
 }
 
+// ---- subtree phase of the SAH builder: one block per queued item of <= kWSubMax prims builds the item's whole
+//      subtree out of SHARED memory (wbvh_body.h wb_subtree_serial is the serial statement the emulator runs; the
+//      tree is the same multiset of records: same bins, same sweep, same stable partition).  The block loads the
+//      item's prim boxes once; per level every WARP takes items of the level in turn and does all of an item's
+//      work itself -- bins in its own 1.5 KB of shared memory (shared-memory atomics), the warp-wide sweep, the two
+//      children, the stable partition by ballot prefix -- so a level costs one block barrier and no global traffic
+//      beyond the sibling pair it emits.
+#ifndef CV_SUB_THREADS
+#define CV_SUB_THREADS 256
+#endif
+#ifndef CV_SUB_MINBLOCKS
+#define CV_SUB_MINBLOCKS 2
+#endif
+constexpr int kSubThreads = CV_SUB_THREADS;
+constexpr int kSubWarps = kSubThreads / 32;
+constexpr int kSubItems = kWSubMax / (kFastLeafMax + 1) + 1;
+struct SItem {
+    unsigned short start, count;  // positions relative to the subtree's first position
+    int pair;
+    short child[2];               // index of each child in the next level, -1: leaf
+    unsigned short n_left;
+    signed char axis;             // as WItem::axis
+    unsigned char split;
+    unsigned char depth;
+    unsigned char spare[3];
+    float box_mn[3], box_mx[3], cscale[3];
+};
+struct SubShared {
+    F4 pmn[kWSubMax], pmx[kWSubMax];        // prim boxes by local prim id
+    int gid[kWSubMax];                      // the prim's global index (what `order` holds)
+    unsigned short ord[2][kWSubMax];        // local prim id at each position, ping-pong
+    short item_of[2][kWSubMax];             // item of each position (-1: settled in a leaf)
+    SItem items[2][kSubItems];
+    WBin bins[kSubWarps][kWAxes * kWBins];  // one set per warp
+    int n_items[2];
+    int lv_items[kWSubLevels + 2];
+    int error;
+};
+__device__ __forceinline__ int sub_slot_axis(int item_axis, int a) { return kWAxes == 1 ? item_axis : a; }
+
+// One thread: the item's two children (leaf references or items of the next level) and its sibling pair.
+__device__ __forceinline__ void sub_emit_children(SubShared& S, const WBuild& gb, const SItem& it, int nxt, int start, const WBox box[2], const int cnt[2], int child[2]) {
+    const int s0 = it.start;
+    for (int s = 0; s < 2; ++s) {
+        const int cs = s == 0 ? s0 : s0 + cnt[0];
+        int ref;
+        child[s] = -1;
+        if (cnt[s] <= kFastLeafMax) {
+            ref = make_leaf_ref(start + cs, cnt[s]);
+        } else {
+            const int pair = atomicAdd(&gb.counters[1], 1);
+            const int slot = atomicAdd(&S.n_items[nxt], 1);
+            if (pair >= gb.pairs_capacity || slot >= kSubItems) {
+                atomicOr(&gb.counters[2], WB_ERR_CAPACITY);
+                ref = make_leaf_ref(start + cs, 1);
+            } else {
+                ref = 2 * pair;
+                gb.pair_depth[pair] = (unsigned char)(it.depth + 1);
+                child[s] = slot;
+                SItem ch;
+                ch.start = (unsigned short)cs;
+                ch.count = (unsigned short)cnt[s];
+                ch.pair = pair;
+                ch.child[0] = ch.child[1] = -1;
+                ch.n_left = 0;
+                ch.split = 0;
+                ch.depth = (unsigned char)(it.depth + 1);
+                ch.box_mn[0] = box[s].mn.x; ch.box_mn[1] = box[s].mn.y; ch.box_mn[2] = box[s].mn.z;
+                ch.box_mx[0] = box[s].mx.x; ch.box_mx[1] = box[s].mx.y; ch.box_mx[2] = box[s].mx.z;
+                ch.axis = (signed char)wb_binning_setup(ch.box_mn, ch.box_mx, ch.depth, gb.force_median, ch.cscale);
+                S.items[nxt][slot] = ch;
+            }
+        }
+        FastNode o;
+        o.mn[0] = box[s].mn.x; o.mn[1] = box[s].mn.y; o.mn[2] = box[s].mn.z;
+        o.mx[0] = box[s].mx.x; o.mx[1] = box[s].mx.y; o.mx[2] = box[s].mx.z;
+        o.a = ref;
+        o.b = cnt[s];
+        gb.fnodes[2 * it.pair + s] = o;
+    }
+}
+__device__ __forceinline__ void sub_median(const SItem& it, WBox box[2], int cnt[2]) {
+    cnt[0] = it.count / 2;
+    cnt[1] = it.count - cnt[0];
+    for (int s = 0; s < 2; ++s) {
+        box[s].mn = f3(it.box_mn[0], it.box_mn[1], it.box_mn[2]);
+        box[s].mx = f3(it.box_mx[0], it.box_mx[1], it.box_mx[2]);
+    }
+}
+// A small item (<= kSubSerialMax prims), all of it in ONE thread, registers only.  Same winner as the binned sweep:
+// the planes of an axis that separate the prims differently are exactly k = bin of some prim (k < 15) -- every other
+// plane repeats the partition of the largest such k below it at a higher index, which the sweep's "first strictly
+// smaller cost" never prefers -- so the thread evaluates those <= count candidates per axis directly from the prims
+// (count^2 box unions per axis, boxes read from shared memory) and keeps the lexicographic minimum of (cost, axis
+// slot * 16 + k).  Unions are exact min / max, the cost is the same three fp32 operations: same bits as the sweep.
+constexpr int kSubSerialMax = 16;
+__device__ void sub_item_serial(SubShared& S, const WBuild& gb, int cur, int nxt, int w, int start) {
+    const SItem& it = S.items[cur][w];
+    const int s0 = it.start, c = it.count;
+    int axis = it.axis, split = 0;
+    WBox box[2];
+    int cnt[2] = { 0, 0 };
+    box[0] = box[1] = wb_empty();
+    if (axis >= 0) {
+        float best_cost = CV_INF;
+        int best_key = -1;
+        for (int a = 0; a < kWAxes; ++a) {
+            const int ax = sub_slot_axis(axis, a);
+            unsigned long long packed = 0ull;  // 4 bits per prim: its bin on this axis
+            for (int j = 0; j < c; ++j) {
+                const int id = S.ord[cur][s0 + j];
+                packed |= (unsigned long long)wb_bin_at(it.box_mn, it.cscale, ax, S.pmn[id], S.pmx[id]) << (4 * j);
+            }
+            for (int j = 0; j < c; ++j) {
+                const int k = (int)((packed >> (4 * j)) & 15ull);
+                if (k >= kWBins - 1) continue;
+                const int key = a * kWBins + k;
+                WBox l = wb_empty(), r = wb_empty();
+                int nl = 0;
+                for (int i = 0; i < c; ++i) {
+                    const int id = S.ord[cur][s0 + i];
+                    const F4 mn = S.pmn[id], mx = S.pmx[id];
+                    if ((int)((packed >> (4 * i)) & 15ull) <= k) {
+                        wb_grow(l, f3(mn.x, mn.y, mn.z), f3(mx.x, mx.y, mx.z));
+                        ++nl;
+                    } else {
+                        wb_grow(r, f3(mn.x, mn.y, mn.z), f3(mx.x, mx.y, mx.z));
+                    }
+                }
+                if (nl == c) continue;  // nothing on the right
+                const float cost = (float)nl * wb_half_area(l) + (float)(c - nl) * wb_half_area(r);
+                if (cost < best_cost || (cost == best_cost && key < best_key)) {
+                    best_cost = cost;
+                    best_key = key;
+                    box[0] = l;
+                    box[1] = r;
+                    cnt[0] = nl;
+                    cnt[1] = c - nl;
+                }
+            }
+        }
+        if (best_key < 0) {
+            axis = -1;
+        } else {
+            axis = sub_slot_axis(axis, best_key / kWBins);
+            split = best_key % kWBins;
+        }
+    }
+    if (axis < 0) sub_median(it, box, cnt);
+    int child[2];
+    sub_emit_children(S, gb, it, nxt, start, box, cnt, child);
+    int left_run = 0, right_run = 0;
+    for (int j = 0; j < c; ++j) {
+        const int id = S.ord[cur][s0 + j];
+        const bool flag = axis >= 0 ? wb_bin_at(it.box_mn, it.cscale, axis, S.pmn[id], S.pmx[id]) <= split : j < cnt[0];
+        const int dst = flag ? s0 + left_run++ : s0 + cnt[0] + right_run++;
+        S.ord[nxt][dst] = (unsigned short)id;
+        S.item_of[nxt][dst] = (short)(flag ? child[0] : child[1]);
+    }
+}
+// A larger item, all of it in ONE warp: bins in the warp's own shared memory, the warp-wide sweep, partition by ballot prefix.
+__device__ void sub_item_warp(SubShared& S, const WBuild& gb, int cur, int nxt, int w, int start, int warp, int lane) {
+    const SItem& it = S.items[cur][w];
+    WBin* wb = S.bins[warp];
+    const int s0 = it.start, c = it.count;
+    int axis = it.axis, split = 0;
+    WBox box[2];
+    int cnt[2] = { 0, 0 };
+    box[0] = box[1] = wb_empty();
+    if (axis >= 0) {
+        for (int q = lane; q < kWAxes * kWBins * 8; q += 32) reinterpret_cast<uint32_t*>(wb)[q] = 0u;
+        __syncwarp();
+        for (int j = lane; j < c; j += 32) {
+            const int id = S.ord[cur][s0 + j];
+            const F4 mn = S.pmn[id], mx = S.pmx[id];
+#pragma unroll
+            for (int a = 0; a < kWAxes; ++a) {
+                WBin& bin = wb[a * kWBins + wb_bin_at(it.box_mn, it.cscale, sub_slot_axis(axis, a), mn, mx)];
+                atomicAdd(&bin.count, 1u);
+                atomicMax(&bin.nmn[0], ~ordered_key(mn.x));
+                atomicMax(&bin.nmn[1], ~ordered_key(mn.y));
+                atomicMax(&bin.nmn[2], ~ordered_key(mn.z));
+                atomicMax(&bin.mx[0], ordered_key(mx.x));
+                atomicMax(&bin.mx[1], ordered_key(mx.y));
+                atomicMax(&bin.mx[2], ordered_key(mx.z));
+            }
+        }
+        __syncwarp();
+        const WSweep sw = wb_warp_sweep<false>(wb, lane);
+        __syncwarp();
+        if (sw.best == ~0ull) {
+            axis = -1;  // every prim in one bin on every axis: median split
+        } else {
+            const int key = (int)(sw.best & 0xffull);
+            axis = sub_slot_axis(axis, key / kWBins);
+            split = key % kWBins;
+            box[0] = sw.box[0];
+            box[1] = sw.box[1];
+            cnt[0] = sw.cnt[0];
+            cnt[1] = sw.cnt[1];
+        }
+    }
+    if (axis < 0) sub_median(it, box, cnt);
+    int child[2] = { -1, -1 };
+    if (lane == 0) sub_emit_children(S, gb, it, nxt, start, box, cnt, child);
+    child[0] = __shfl_sync(0xffffffffu, child[0], 0);
+    child[1] = __shfl_sync(0xffffffffu, child[1], 0);
+    // stable partition of the item's positions: lefts keep their order, rights keep theirs
+    int left_run = 0, right_run = 0;
+    for (int base = 0; base < c; base += 32) {
+        const int j = base + lane;
+        const bool valid = j < c;
+        const int id = valid ? S.ord[cur][s0 + j] : 0;
+        bool flag;
+        if (axis >= 0) flag = valid && wb_bin_at(it.box_mn, it.cscale, axis, S.pmn[id], S.pmx[id]) <= split;
+        else flag = valid && j < cnt[0];
+        const unsigned m = __ballot_sync(0xffffffffu, flag), mv = __ballot_sync(0xffffffffu, valid);
+        const unsigned lt = (1u << lane) - 1u;
+        if (valid) {
+            const int dst = flag ? s0 + left_run + __popc(m & lt) : s0 + cnt[0] + right_run + __popc(~m & mv & lt);
+            S.ord[nxt][dst] = (unsigned short)id;
+            S.item_of[nxt][dst] = (short)(flag ? child[0] : child[1]);
+        }
+        left_run += __popc(m);
+        right_run += __popc(~m & mv);
+    }
+    __syncwarp();
+}
+
+__global__ void __launch_bounds__(kSubThreads, CV_SUB_MINBLOCKS) k_wb_subtrees(const WBuild gb, int n_roots) {
+    extern __shared__ __align__(32) unsigned char s_raw[];
+    SubShared& S = *reinterpret_cast<SubShared*>(s_raw);
+    const int r = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (r >= n_roots) return;
+    const WItem root = gb.sub_roots[r];
+    const int n = root.count, start = root.start;
+    for (int j = tid; j < n; j += kSubThreads) {
+        const int p = gb.order[start + j];
+        S.gid[j] = p;
+        S.pmn[j] = gb.bmin[p];
+        S.pmx[j] = gb.bmax[p];
+        S.ord[0][j] = (unsigned short)j;
+        S.item_of[0][j] = 0;
+    }
+    if (tid == 0) {
+        SItem it;
+        it.start = 0;
+        it.count = (unsigned short)n;
+        it.pair = root.pair;
+        it.child[0] = it.child[1] = -1;
+        it.n_left = 0;
+        it.axis = (signed char)root.axis;
+        it.split = 0;
+        it.depth = (unsigned char)root.depth;
+        for (int c = 0; c < 3; ++c) {
+            it.box_mn[c] = root.box_mn[c];
+            it.box_mx[c] = root.box_mx[c];
+            it.cscale[c] = root.cscale[c];
+        }
+        S.items[0][0] = it;
+        S.n_items[0] = 1;
+        S.n_items[1] = 0;
+        S.error = 0;
+    }
+    for (int l = tid; l < kWSubLevels + 2; l += kSubThreads) S.lv_items[l] = 0;
+    __syncthreads();
+    int cur = 0, level = 0;
+    for (;; ++level, cur ^= 1) {
+        const int ni = S.n_items[cur];
+        if (ni == 0) break;
+        if (level >= kWSubLevels) {
+            if (tid == 0) S.error = 1;
+            break;
+        }
+        const int nxt = cur ^ 1;
+        if (tid == 0) S.lv_items[level] = ni;
+        // positions already settled in a leaf belong to no item: carry them over
+        for (int j = tid; j < n; j += kSubThreads) {
+            if (S.item_of[cur][j] < 0) {
+                S.ord[nxt][j] = S.ord[cur][j];
+                S.item_of[nxt][j] = -1;
+            }
+        }
+        for (int w = warp; w < ni; w += kSubWarps) {  // warp-uniform
+            if (S.items[cur][w].count > kSubSerialMax) sub_item_warp(S, gb, cur, nxt, w, start, warp, lane);
+        }
+        for (int w = tid; w < ni; w += kSubThreads) {
+            if (S.items[cur][w].count <= kSubSerialMax) sub_item_serial(S, gb, cur, nxt, w, start);
+        }
+        __syncthreads();
+        if (tid == 0) S.n_items[cur] = 0;  // becomes the level after next
+        __syncthreads();
+    }
+    __syncthreads();
+    for (int j = tid; j < n; j += kSubThreads) gb.order[start + j] = S.gid[S.ord[cur][j]];
+    if (tid == 0) {
+        if (S.error) atomicOr(&gb.counters[2], WB_ERR_CAPACITY);
+        wb_subtree_account(gb, root, level, S.lv_items);
+    }
+}
+void CudaExec::wb_subtrees(const WBuild& b, int n_roots) {
+    if (n_roots <= 0) return;
+    note(cudaFuncSetAttribute(k_wb_subtrees, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SubShared)));
+    k_wb_subtrees<<<n_roots, kSubThreads, sizeof(SubShared), stream>>>(b, n_roots);
+    note(cudaGetLastError());
+    ++launches;
+}
+
 // ---- scene assembly -------------------------------------------------------------------
 struct FnAssembleVertices {
     const float* positions;
@@ -484,8 +875,8 @@ int run_build_bvh_parity(CudaExec& ex, BuildArrays a, const int* tri_off_host, c
 int run_build_wbvh(CudaExec& ex, WBuild b, WReport* report) { return build_wbvh(ex, b, report); }
 int run_build_lbvh(CudaExec& ex, WBuild b, WReport* report) { return build_lbvh(ex, b, report); }
 void run_build_q4(CudaExec& ex, WBuild b, int n_pairs) { ex.launch(n_pairs, FnWbQ4{ b, n_pairs }); }
-void run_refit_wbvh(CudaExec& ex, WBuild b, const int* level_start, int n_levels, const unsigned char* d_moved, float* d_area_sum, float out[7]) {
-    refit_wbvh(ex, b, level_start, n_levels, d_moved, d_area_sum, out);
+void run_refit_wbvh(CudaExec& ex, WBuild b, int n_pairs, int n_levels, const unsigned char* d_moved, float* d_area_sum, float out[7]) {
+    refit_wbvh(ex, b, n_pairs, n_levels, d_moved, d_area_sum, out);
 }
 
 // ---- path-trace pass ------------------------------------------------------------------

@@ -24,8 +24,10 @@ struct CudaExec {
     // tmp buffers hold n entries each, hist needs 2 * sort_hist_entries(n) ints.
     void sort_pairs(uint32_t* keys, int* vals, uint32_t* keys_tmp, int* vals_tmp, int* hist, int n, int bits);
     void wb_prim(const WBuild& b);  // world AABBs + scene / centroid bounds, block-reduced
+    void wb_bin(const WBuild& b);                          // bin pass of a level, block-privatised in shared memory
     void wb_split(const WBuild& b, int level, int bound);  // SAH split of every item of a level: a warp per arena item, a thread per small item
     void wb_partition(const WBuild& b);                    // left flags + exclusive scan + stable scatter in three launches
+    void wb_subtrees(const WBuild& b, int n_roots);        // second phase: one block builds the whole subtree of each queued item
     void upload(void* dst, const void* src, size_t bytes);
     void download(void* dst, const void* src, size_t bytes);
     void fill(void* dst, int byte, size_t bytes);
@@ -47,7 +49,7 @@ int run_build_bvh_parity(CudaExec& ex, BuildArrays a, const int* tri_off_host, c
 int run_build_wbvh(CudaExec& ex, WBuild b, WReport* report);
 int run_build_lbvh(CudaExec& ex, WBuild b, WReport* report);
 void run_build_q4(CudaExec& ex, WBuild b, int n_pairs);  // Q4Node records over a finished pair tree
-void run_refit_wbvh(CudaExec& ex, WBuild b, const int* level_start, int n_levels, const unsigned char* d_moved, float* d_area_sum, float out[7]);
+void run_refit_wbvh(CudaExec& ex, WBuild b, int n_pairs, int n_levels, const unsigned char* d_moved, float* d_area_sum, float out[7]);
 
 void launch_trace(CudaExec& ex, const TraceParams& p, bool fast, bool count_visits);
 // the per-pixel body over the four-wide records (CAVEPT_KERNEL_WIDE4; p.q4nodes must be set)

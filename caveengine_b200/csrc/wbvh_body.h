@@ -40,6 +40,11 @@ constexpr int kWBinBase = kWLevelBase + kWMaxLevels + 4;  // counters[kWBinBase 
 constexpr int kWCounters = kWBinBase + kWMaxLevels + 4;   // ints in the counter block
 constexpr int kWMedianDepth = 48;  // safety net: positional median splits below this depth
 
+#ifndef CV_SUB_MAX
+#define CV_SUB_MAX 1024
+#endif
+constexpr int kWSubMax = CV_SUB_MAX;   // an item of at most this many prims leaves the level-synchronous phase: its whole subtree is built by one thread block (wb_subtree_*)
+constexpr int kWSubLevels = 64;  // levels a subtree may have below its root
 constexpr int kWDirectMax = 8;  // items of at most this many prims are split by one thread straight from the prims: no global bins, no atomics
 
 // One SAH bin.  Cleared = all zero: the min corner is kept as the COMPLEMENT of its ordered key (folded with
@@ -98,7 +103,11 @@ struct WBuild {
     int items_capacity;
     int pairs_capacity;
     int bins_capacity;   // WBins records in the arena: at most n_prims / (kWDirectMax + 1) items of a level own one
-    int* counters;       // [0] items emitted for the next level, [1] pairs allocated, [2] error bits
+    int* counters;       // global: [0] deepest level reached by a subtree build + 1, [1] pairs allocated, [2] error bits, [3] subtree roots queued
+    int* level_items;    // [L] = interior items of level L -- the level-synchronous phase: counters + kWLevelBase; a subtree build: block-local, L counted from its root
+    int* level_bins;     // [L] = bin-arena slots handed out for level L (same two homes)
+    WItem* sub_roots;    // level-synchronous phase: queue of items of <= kWSubMax prims (null inside a subtree build)
+    int sub_capacity;
     // LBVH builder only
     uint32_t* keys;      // Morton code per prim, then sorted
     uint32_t* keys_tmp;
@@ -116,6 +125,7 @@ struct WBuild {
     FastNode* fnodes;
     QPair* qpairs;  // quantised copy of fnodes, what the tracer fetches
     Q4Node* q4nodes;  // four-wide records over the same tree (null: not built)
+    unsigned char* pair_depth;  // SAH builder: depth of the interior node that owns sibling pair k (root pair: 0); the refit walks the pairs deepest first
     float grid_origin[3], grid_scale[3];
     FastTri* ftris;
     FastTri* fnormals;
@@ -194,25 +204,27 @@ CV_D void wb_body_init(const WBuild& b, int p) {
 // ---- per level ----------------------------------------------------------------------------
 // Binning set-up of an item from its box: the bins of every axis span the box (measured on the config scenes: the
 // node count per segment is within 0.5 % of binning over the exact centroid bounds, which cost 18 more atomics per prim).
-CV_HD void wb_item_setup(WItem& it, int force_median) {
-    const F3 ext = f3(it.box_mx[0] - it.box_mn[0], it.box_mx[1] - it.box_mn[1], it.box_mx[2] - it.box_mn[2]);
+CV_HD int wb_binning_setup(const float box_mn[3], const float box_mx[3], int depth, int force_median, float cscale[3]) {
+    const F3 ext = f3(box_mx[0] - box_mn[0], box_mx[1] - box_mn[1], box_mx[2] - box_mn[2]);
     int axis = 0;
     if (ext.y > comp(ext, axis)) axis = 1;
     if (ext.z > comp(ext, axis)) axis = 2;
     const float e = comp(ext, axis);
-    for (int c = 0; c < 3; ++c) {
-        it.cmin[c] = it.box_mn[c];
-        it.cscale[c] = comp(ext, c) > 0.0f ? cv_div((float)kWBins, comp(ext, c)) : 0.0f;
-    }
+    for (int c = 0; c < 3; ++c) cscale[c] = comp(ext, c) > 0.0f ? cv_div((float)kWBins, comp(ext, c)) : 0.0f;
     // no extent (or the safety net): split the list in the middle
-    it.axis = (!(e > 0.0f) || force_median || it.depth >= kWMedianDepth) ? -1 : axis;
+    return (!(e > 0.0f) || force_median || depth >= kWMedianDepth) ? -1 : axis;
+}
+CV_HD void wb_item_setup(WItem& it, int force_median) {
+    for (int c = 0; c < 3; ++c) it.cmin[c] = it.box_mn[c];
+    it.axis = wb_binning_setup(it.box_mn, it.box_mx, it.depth, force_median, it.cscale);
 }
 
-CV_HD int wb_bin_of(const WItem& it, int axis, F4 mn, F4 mx) {
+CV_HD int wb_bin_at(const float* cmin, const float* cscale, int axis, F4 mn, F4 mx) {
     const float c = axis == 0 ? 0.5f * (mn.x + mx.x) : (axis == 1 ? 0.5f * (mn.y + mx.y) : 0.5f * (mn.z + mx.z));
-    const int k = (int)((c - it.cmin[axis]) * it.cscale[axis]);
+    const int k = (int)((c - cmin[axis]) * cscale[axis]);
     return k < 0 ? 0 : (k > kWBins - 1 ? kWBins - 1 : k);
 }
+CV_HD int wb_bin_of(const WItem& it, int axis, F4 mn, F4 mx) { return wb_bin_at(it.cmin, it.cscale, axis, mn, mx); }
 // axis binned in slot a of an item's bins
 CV_HD int wb_slot_axis(const WItem& it, int a) { return kWAxes == 1 ? it.axis : a; }
 
@@ -322,14 +334,19 @@ CV_D void wb_finish_split(const WBuild& b, WItem& it, int level, WBox box[2], in
             ref = make_leaf_ref(start, cnt[s]);
         } else {
             const int pair = cv_atomic_add_i32(&b.counters[1], 1);
-            const int slot = cv_atomic_add_i32(&b.counters[kWLevelBase + level + 1], 1);
-            const int bins_slot = cnt[s] > kWDirectMax ? cv_atomic_add_i32(&b.counters[kWBinBase + level + 1], 1) : -1;
+            // a child of at most kWSubMax prims is queued for a subtree build instead of entering the next level
+            // (its prims stay where they are: node_of = -1 from here on); a full queue just means it stays in the level loop
+            const int sub = (b.sub_roots && cnt[s] <= kWSubMax) ? cv_atomic_add_i32(&b.counters[3], 1) : b.sub_capacity;
+            const bool queued = sub < b.sub_capacity;
+            const int slot = queued ? 0 : cv_atomic_add_i32(&b.level_items[level + 1], 1);
+            const int bins_slot = (!queued && cnt[s] > kWDirectMax) ? cv_atomic_add_i32(&b.level_bins[level + 1], 1) : -1;
             if (pair >= b.pairs_capacity || slot >= b.items_capacity || bins_slot >= b.bins_capacity) {
                 cv_atomic_or_i32(&b.counters[2], WB_ERR_CAPACITY);
                 ref = make_leaf_ref(start, 1);
             } else {
                 ref = 2 * pair;
-                it.child_item[s] = slot;
+                b.pair_depth[pair] = (unsigned char)(it.depth + 1);
+                if (!queued) it.child_item[s] = slot;
                 WItem c;
                 c.start = start;
                 c.count = cnt[s];
@@ -342,7 +359,7 @@ CV_D void wb_finish_split(const WBuild& b, WItem& it, int level, WBox box[2], in
                 c.box_mn[0] = box[s].mn.x; c.box_mn[1] = box[s].mn.y; c.box_mn[2] = box[s].mn.z;
                 c.box_mx[0] = box[s].mx.x; c.box_mx[1] = box[s].mx.y; c.box_mx[2] = box[s].mx.z;
                 wb_item_setup(c, b.force_median);
-                b.items_next[slot] = c;
+                if (queued) b.sub_roots[sub] = c; else b.items_next[slot] = c;
             }
         }
         FastNode o;
@@ -359,7 +376,7 @@ CV_D void wb_finish_split(const WBuild& b, WItem& it, int level, WBox box[2], in
 // axis' bins (the bottom-up AABB reduction is folded into the binning), then wb_finish_split.
 // with_arena_items = false: items that own arena bins are left to the device's warp-wide kernel.
 CV_D void wb_body_split(const WBuild& b, int w, int level, bool with_arena_items) {
-    const int n_items = b.counters[kWLevelBase + level];
+    const int n_items = b.level_items[level];
     if (w >= n_items) return;
     WItem& it = b.items[w];
     if (!with_arena_items && it.axis >= 0 && it.bins_slot >= 0) return;
@@ -454,6 +471,80 @@ CV_D void wb_body_scatter(const WBuild& b, int i) {
         return;
     }
     wb_scatter_to(b, i, w, b.flags[i], b.scan[i], b.scan[b.items[w].start]);
+}
+
+// ---- subtree builds: the second phase of the SAH builder ------------------------------------------------------
+// An item of <= kWSubMax prims is a closed problem: its prims are one contiguous range of `order` that nothing else
+// touches.  One thread block builds its whole subtree with the same per-prim / per-item passes as the level loop
+// (bin -> split -> flag -> scan -> scatter), block barriers in place of kernel boundaries, so the ~15 deepest levels of
+// the tree cost one launch instead of six each.  Scratch: the level loop's own item and bin arrays are dead by then and
+// are carved up by prim range (a subtree over `count` prims has at most count / 3 items and count / 9 arena bins per level).  Pairs come from the same global
+// counter and carry their owner's depth (pair_depth), which is all the refit needs.
+// wb_subtree_view: a block's private view of the build (no writes); wb_subtree_setup: the view + the root item in
+// items[0] and the level-0 counters (one thread).
+CV_HD void wb_subtree_view(const WBuild& gb, const WItem& root, WBuild& b, int* lv_items, int* lv_bins) {
+    b = gb;
+    b.sub_roots = nullptr;
+    b.level_items = lv_items;
+    b.level_bins = lv_bins;
+    // [ceil(start / m), ceil(start / m) + floor(count / m)) with m = the fewest prims of an interior item (3) resp. of an
+    // arena item (9): disjoint for disjoint prim ranges, and a level of the subtree never has more such items
+    constexpr int mi = kFastLeafMax + 1, mb = kWDirectMax + 1;
+    const int ibase = (root.start + mi - 1) / mi, bbase = (root.start + mb - 1) / mb;
+    b.items = gb.items + ibase;
+    b.items_next = gb.items_next + ibase;
+    b.items_capacity = root.count / mi;
+    b.bins = gb.bins + bbase;
+    b.bins_capacity = root.count / mb;
+}
+CV_D WItem wb_subtree_setup(const WBuild& gb, int r, WBuild& b, int* lv_items, int* lv_bins) {
+    WItem root = gb.sub_roots[r];
+    wb_subtree_view(gb, root, b, lv_items, lv_bins);
+    root.bins_slot = root.count > kWDirectMax ? 0 : -1;
+    b.items[0] = root;
+    lv_items[0] = 1;
+    lv_bins[0] = root.bins_slot >= 0 ? 1 : 0;
+    return root;
+}
+// after a subtree's last level: its statistics into the global counters, its prims back into the buffer the emit pass reads
+CV_D void wb_subtree_account(const WBuild& gb, const WItem& root, int levels, const int* lv_items) {
+    for (int l = 0; l < levels && root.depth + l < kWMaxLevels; ++l) cv_atomic_add_i32(&gb.counters[kWLevelBase + root.depth + l], lv_items[l]);
+#if defined(__CUDA_ARCH__)
+    atomicMax(&gb.counters[0], root.depth + levels);
+#else
+    if (gb.counters[0] < root.depth + levels) gb.counters[0] = root.depth + levels;
+#endif
+}
+// the serial statement (emulator); the device runs k_wb_subtrees (kernels.cu), one block per root, same passes
+CV_D void wb_subtree_serial(const WBuild& gb, int r) {
+    WBuild b;
+    int lv_items[kWSubLevels + 2] = { 0 }, lv_bins[kWSubLevels + 2] = { 0 };
+    const WItem root = wb_subtree_setup(gb, r, b, lv_items, lv_bins);
+    const int start = root.start, end = root.start + root.count;
+    for (int i = start; i < end; ++i) b.node_of[i] = 0;
+    int level = 0;
+    for (; lv_items[level] > 0; ++level) {
+        if (level >= kWSubLevels) {
+            cv_atomic_or_i32(&gb.counters[2], WB_ERR_CAPACITY);
+            break;
+        }
+        for (int i = start; i < end; ++i) wb_body_bin(b, i);
+        for (int w = 0; w < lv_items[level]; ++w) wb_body_split(b, w, level, true);
+        int run = 0;
+        for (int i = start; i < end; ++i) {
+            b.flags[i] = wb_flag_of(b, i);
+            b.scan[i] = run;
+            run += b.flags[i];
+        }
+        for (int i = start; i < end; ++i) wb_body_scatter(b, i);
+        WItem* ti = b.items; b.items = b.items_next; b.items_next = ti;
+        int* to = b.order; b.order = b.order_next; b.order_next = to;
+        int* tn = b.node_of; b.node_of = b.node_of_next; b.node_of_next = tn;
+    }
+    if (b.order != gb.order) {
+        for (int i = start; i < end; ++i) gb.order[i] = b.order[i];
+    }
+    wb_subtree_account(gb, root, level, lv_items);
 }
 
 // ---- emit: slot s of the final order holds prim order[s] --------------------------------------
@@ -586,10 +677,11 @@ CV_D void wb_body_retransform(const WBuild& b, int s, const unsigned char* moved
     wb_emit_slot(b, s, f2u(b.ftris[s].v1.w), inst);
 }
 
-CV_D void wb_body_refit_pair(const WBuild& b, int k, float* area_sum) {
+CV_D void wb_body_refit_pair(const WBuild& b, int k, int n_pairs, int depth, float* area_sum) {
     QPair q;
     float area = 0.0f;
-    for (int s = 0; s < 2; ++s) {
+    const bool mine = k < n_pairs && b.pair_depth[k] == (unsigned char)depth;  // every thread of the launch reaches the warp reduction below
+    for (int s = 0; mine && s < 2; ++s) {
         FastNode n = b.fnodes[2 * k + s];
         WBox box = wb_empty();
         if (ref_is_interior(n.a)) {
@@ -612,10 +704,11 @@ CV_D void wb_body_refit_pair(const WBuild& b, int k, float* area_sum) {
         for (int c = 0; c < 3; ++c) q.q[3 * s + c] = wb_grid_lo(n.mn[c], b.grid_origin[c], b.grid_scale[c]) | (wb_grid_hi(n.mx[c], b.grid_origin[c], b.grid_scale[c]) << 16);
         if (s == 0) q.r0 = wb_quantised_ref(n.a); else q.r1 = wb_quantised_ref(n.a);
     }
-    b.qpairs[k] = q;
+    if (mine) b.qpairs[k] = q;
     if (area_sum) {
 #if defined(__CUDA_ARCH__)
-        // one atomic per warp: the active lanes of a k_for_each launch are a contiguous run starting at lane 0
+        // one atomic per warp: the active lanes of a k_for_each launch are a contiguous run starting at lane 0 (lanes whose pair
+        // belongs to another depth carry 0)
         const unsigned mask = __activemask();
         const int lane = (int)(threadIdx.x & 31u);
 #pragma unroll
@@ -623,7 +716,7 @@ CV_D void wb_body_refit_pair(const WBuild& b, int k, float* area_sum) {
             const float o = __shfl_down_sync(mask, area, d);
             if (lane + d < 32 && ((mask >> (lane + d)) & 1u)) area += o;
         }
-        if (lane == 0) atomicAdd(area_sum, area);
+        if (lane == 0 && area != 0.0f) atomicAdd(area_sum, area);
 #else
         *area_sum += area;
 #endif
@@ -631,16 +724,17 @@ CV_D void wb_body_refit_pair(const WBuild& b, int k, float* area_sum) {
 }
 
 struct FnWbRetransform { WBuild b; const unsigned char* moved; CV_D void operator()(int i) const { wb_body_retransform(b, i, moved); } };
-struct FnWbRefitPair { WBuild b; int first; float* area_sum; CV_D void operator()(int i) const { wb_body_refit_pair(b, first + i, area_sum); } };
+struct FnWbRefitPair { WBuild b; int n_pairs; int depth; float* area_sum; CV_D void operator()(int i) const { wb_body_refit_pair(b, i, n_pairs, depth, area_sum); } };
 
-// level_start[L] .. level_start[L+1] = pairs owned by the interior nodes of level L (level_start has n_levels + 1 entries).
-// out[0..5] = refitted scene box (union of the root pair), out[6] = surface-area sum of all records.
+// One launch per depth, deepest first, over all pairs: a pair is refitted in the launch of its owner's depth
+// (b.pair_depth), after the pairs of its children.  out[0..5] = refitted scene box (union of the root pair),
+// out[6] = surface-area sum of all records.
 template<class Exec>
-void refit_wbvh(Exec& ex, WBuild b, const int* level_start, int n_levels, const unsigned char* d_moved, float* d_area_sum, float out[7]) {
+void refit_wbvh(Exec& ex, WBuild b, int n_pairs, int n_levels, const unsigned char* d_moved, float* d_area_sum, float out[7]) {
     ex.fill(d_area_sum, 0, sizeof(float));
     ex.launch(b.n_prims, FnWbRetransform{ b, d_moved });
-    for (int L = n_levels - 1; L >= 0; --L) ex.launch(level_start[L + 1] - level_start[L], FnWbRefitPair{ b, level_start[L], d_area_sum });
-    if (b.q4nodes) ex.launch(level_start[n_levels], FnWbQ4{ b, level_start[n_levels] });
+    for (int L = n_levels - 1; L >= 0; --L) ex.launch(n_pairs, FnWbRefitPair{ b, n_pairs, L, d_area_sum });
+    if (b.q4nodes) ex.launch(n_pairs, FnWbQ4{ b, n_pairs });
     FastNode root[2];
     ex.download(root, b.fnodes, sizeof(root));
     for (int c = 0; c < 3; ++c) {
@@ -1004,6 +1098,7 @@ int build_wbvh(Exec& ex, WBuild b, WReport* rep) {
     wb_item_setup(root, b.force_median);
     ex.upload(b.items, &root, sizeof(root));
     ex.fill(b.bins, 0, (size_t)b.bins_capacity * sizeof(WBins));  // once: the split pass clears what it reads
+    ex.fill(b.pair_depth, 0, 1);                                  // the root owns pair 0
     // counters: [1] pairs allocated, [2] error bits, [kWLevelBase + L] interior items of level L, [kWBinBase + L]
     // arena slots of level L.  The level loop runs kLevelsPerSync levels per device->host round trip: launches over
     // items are sized by an upper bound (items are disjoint ranges of >= kFastLeafMax + 1 prims, and at most 2^L of
@@ -1012,34 +1107,62 @@ int build_wbvh(Exec& ex, WBuild b, WReport* rep) {
     int counters[kWCounters] = { 0, 1, 0, 0, 1 };
     counters[kWBinBase] = 1;
     ex.upload(b.counters, counters, sizeof(counters));
+    b.level_items = b.counters + kWLevelBase;
+    b.level_bins = b.counters + kWBinBase;
     const int items_bound = b.n_prims / (kFastLeafMax + 1) + 1;
     rep->root_ref = 0;
     int level = 0;
-    for (;;) {
-        for (int k = 0; k < kLevelsPerSync; ++k, ++level) {
-            const long long pow2 = level < 30 ? (1ll << level) : (1ll << 30);
-            const int bound = (int)(pow2 < items_bound ? pow2 : items_bound);
-            ex.launch(b.n_prims, FnWbBin{ b });
-            ex.wb_split(b, level, bound);
-            ex.wb_partition(b);
-            WItem* ti = b.items; b.items = b.items_next; b.items_next = ti;
-            int* to = b.order; b.order = b.order_next; b.order_next = to;
-            int* tn = b.node_of; b.node_of = b.node_of_next; b.node_of_next = tn;
+    if (b.n_prims > kWSubMax || !b.sub_roots) {  // level-synchronous phase: items of more than kWSubMax prims
+        for (;;) {
+            // the level loop cannot end before items of kWSubMax prims exist: no read-back until then, every two levels after
+            int burst = kLevelsPerSync;
+            if (b.sub_roots) {
+                burst = 2;
+                if (level == 0) {
+                    burst = 1;
+                    while (((long long)kWSubMax << burst) < (long long)b.n_prims) ++burst;
+                }
+            }
+            for (int k = 0; k < burst; ++k, ++level) {
+                const long long pow2 = level < 30 ? (1ll << level) : (1ll << 30);
+                const int bound = (int)(pow2 < items_bound ? pow2 : items_bound);
+                ex.wb_bin(b);
+                ex.wb_split(b, level, bound);
+                ex.wb_partition(b);
+                WItem* ti = b.items; b.items = b.items_next; b.items_next = ti;
+                int* to = b.order; b.order = b.order_next; b.order_next = to;
+                int* tn = b.node_of; b.node_of = b.node_of_next; b.node_of_next = tn;
+            }
+            ex.download(counters, b.counters, sizeof(counters));
+            if (counters[2] != 0) {
+                rep->error_bits = counters[2];
+                return -1;
+            }
+            if (counters[kWLevelBase + level] == 0) break;
+            if (level + 32 >= kWMaxLevels) {
+                rep->error_bits = WB_ERR_CAPACITY;
+                return -1;
+            }
         }
+    } else {  // the whole scene is one subtree
+        ex.upload(b.sub_roots, &root, sizeof(root));
+        counters[3] = 1;
+        counters[kWLevelBase] = 0;  // the subtree build accounts for its own levels
+        ex.upload(b.counters, counters, sizeof(counters));
+    }
+    // subtree phase: one block per queued item
+    const int n_roots = counters[3] < b.sub_capacity ? counters[3] : b.sub_capacity;
+    if (n_roots > 0) {
+        ex.wb_subtrees(b, n_roots);
         ex.download(counters, b.counters, sizeof(counters));
         if (counters[2] != 0) {
             rep->error_bits = counters[2];
             return -1;
         }
-        if (counters[kWLevelBase + level] == 0) break;
-        if (level + kLevelsPerSync >= kWMaxLevels) {
-            rep->error_bits = WB_ERR_CAPACITY;
-            return -1;
-        }
     }
     rep->n_pairs = counters[1];
     rep->levels = 0;
-    while (counters[kWLevelBase + rep->levels] > 0) {
+    while (rep->levels < kWMaxLevels && counters[kWLevelBase + rep->levels] > 0) {
         rep->level_items[rep->levels] = counters[kWLevelBase + rep->levels];
         ++rep->levels;
     }

@@ -41,7 +41,12 @@ struct EmuExec {
         for (int i = 0; i < n; ++i) { keys[i] = v[i].first; vals[i] = v[i].second; }
     }
     void wb_prim(const WBuild& b) { launch(b.n_prims, FnWbPrim{ b }); }
+    void wb_bin(const WBuild& b) { launch(b.n_prims, FnWbBin{ b }); }
     void wb_split(const WBuild& b, int level, int bound) { launch(bound, FnWbSplit{ b, level, true }); }
+    void wb_subtrees(const WBuild& b, int n_roots) {
+        for (int r = 0; r < n_roots; ++r) wb_subtree_serial(b, r);
+        ++launches;
+    }
     void wb_partition(const WBuild& b) {
         launch(b.n_prims, FnWbFlag{ b });
         scan_u8(b.flags, b.scan, b.n_prims);
@@ -103,6 +108,8 @@ EMU_API int emu_bvh_build(const GpuPtVertex* vertices, const GpuPtIndex* indices
 // (fast == 4) walks; null = not built.  A binding instead of one more argument on three entry points.
 static Q4Node* g_q4nodes = nullptr;
 EMU_API void emu_bind_q4(Q4Node* q4nodes) { g_q4nodes = q4nodes; }
+static unsigned char* g_pair_depth = nullptr;  // n_prims + 8 bytes, written by the SAH build, read by the refit
+EMU_API void emu_bind_pair_depth(unsigned char* p) { g_pair_depth = p; }
 
 // Production (world-space) BVH exactly as cavept_api.cu builds it.  inst_prim_off has
 // n_inst + 1 entries, inst_tri_off n_inst.  fnodes needs 2 * (n_prims + 8) entries, qpairs n_prims + 8, ftris /
@@ -115,7 +122,8 @@ EMU_API int emu_wbvh_build(const GpuPtVertex* vertices, const GpuPtIndex* indice
     std::vector<F4> bmin(P), bmax(P);
     std::vector<int> order(P), order_next(P), node_of(P), node_of_next(P), scan(P + 1), counters(cavept::kWCounters);
     std::vector<unsigned char> flags(P);
-    std::vector<WItem> items(items_cap), items_next(items_cap);
+    const int sub_cap = P / 128 + 64;
+    std::vector<WItem> items(items_cap), items_next(items_cap), sub_roots(sub_cap);
     const size_t bins_cap = (size_t)P / (cavept::kWDirectMax + 1) + 2;
     std::vector<WBins> bins(bins_cap);
     std::vector<uint32_t> root_acc(12);
@@ -148,12 +156,16 @@ EMU_API int emu_wbvh_build(const GpuPtVertex* vertices, const GpuPtIndex* indice
     b.bins = bins.data();
     b.items_capacity = (int)items_cap;
     b.bins_capacity = (int)bins_cap;
+    b.sub_roots = sub_roots.data();
+    b.sub_capacity = sub_cap;
     b.pairs_capacity = (int)pairs_cap;
     b.counters = counters.data();
     b.root_acc = root_acc.data();
     b.fnodes = fnodes;
     b.qpairs = qpairs;
     b.q4nodes = g_q4nodes;
+    std::vector<unsigned char> depth_scratch(pairs_cap);
+    b.pair_depth = g_pair_depth ? g_pair_depth : depth_scratch.data();
     b.ftris = ftris;
     b.fnormals = fnormals;
     EmuExec ex;
@@ -177,9 +189,9 @@ EMU_API int emu_wbvh_build(const GpuPtVertex* vertices, const GpuPtIndex* indice
 }
 
 // Refit of an emu_wbvh_build tree after the instance transforms changed (wbvh_body.h refit_wbvh), as
-// cavept_update_instances drives it.  level_items = WReport::level_items of the build; out = scene box + area sum.
+// cavept_update_instances drives it.  n_pairs / n_levels = WReport of the build; out = scene box + area sum.
 EMU_API void emu_wbvh_refit(const GpuPtVertex* vertices, const GpuPtIndex* indices, const GpuPtMesh* instances, int n_inst, int n_prims, float pad, const float* grid,
-                            const int* level_items, int n_levels, const unsigned char* moved, FastNode* fnodes, QPair* qpairs, FastTri* ftris, FastTri* fnormals, float* out) {
+                            int n_pairs, int n_levels, const unsigned char* moved, FastNode* fnodes, QPair* qpairs, FastTri* ftris, FastTri* fnormals, float* out) {
     WBuild b{};
     b.vertices = vertices;
     b.indices = indices;
@@ -196,11 +208,10 @@ EMU_API void emu_wbvh_refit(const GpuPtVertex* vertices, const GpuPtIndex* indic
         b.grid_origin[k] = grid[k];
         b.grid_scale[k] = grid[3 + k];
     }
-    std::vector<int> level_start(1, 0);
-    for (int L = 0; L < n_levels; ++L) level_start.push_back(level_start.back() + level_items[L]);
+    b.pair_depth = g_pair_depth;
     float area = 0.0f;
     EmuExec ex;
-    refit_wbvh(ex, b, level_start.data(), n_levels, moved, &area, out);
+    refit_wbvh(ex, b, n_pairs, n_levels, moved, &area, out);
 }
 
 EMU_API void emu_mat4_inverse(const float* m, float* out) { mat4_inverse(m, out); }

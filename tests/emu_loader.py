@@ -93,6 +93,8 @@ class EmuScene:
         self.qpairs = np.zeros((P + 8, 8), dtype=np.uint32)  # QPair: q[6], r0, r1
         self.q4nodes = np.zeros((P + 8, 16), dtype=np.uint32)  # Q4Node: q[12], r[4]
         self.lib.emu_bind_q4(_p(self.q4nodes))
+        self.pair_depth = np.zeros(P + 8, dtype=np.uint8)    # depth of the interior node owning pair k (the refit's schedule)
+        self.lib.emu_bind_pair_depth(_p(self.pair_depth))
         self.grid = np.zeros(6, dtype=np.float32)            # origin xyz, scale xyz
         self.ftris = np.zeros(P, dtype=FASTTRI_DT)
         self.fnormals = np.zeros(P, dtype=FASTTRI_DT)
@@ -111,8 +113,9 @@ class EmuScene:
         moved = np.ascontiguousarray(moved, dtype=np.uint8)
         out = np.zeros(7, dtype=np.float32)
         self.lib.emu_bind_q4(_p(self.q4nodes))
+        self.lib.emu_bind_pair_depth(_p(self.pair_depth))
         self.lib.emu_wbvh_refit(_p(self.asm.vertices), _p(self.asm.indices), _p(meshes), C.c_int(meshes.shape[0]), C.c_int(self.n_prims), C.c_float(self.pad), _p(self.grid),
-                                _p(self.level_items), C.c_int(len(self.level_items)), _p(moved), _p(self.fnodes), _p(self.qpairs), _p(self.ftris), _p(self.fnormals), _p(out))
+                                C.c_int(self.n_pairs), C.c_int(self.fast_levels), _p(moved), _p(self.fnodes), _p(self.qpairs), _p(self.ftris), _p(self.fnormals), _p(out))
         return out[:6].copy(), float(out[6])
 
     def render(self, camera, width, height, first_frame, n_frames, max_bounce, fast, accum=None, reset_first=True):

@@ -290,7 +290,7 @@ def test_update_instances_equals_fresh_upload(api, scene_cache):
 def test_update_instances_on_the_config3_scene_refits_in_a_fraction_of_a_millisecond(api, scene_cache):
     """sponza_262144: two of the 25 instances move a little; the refit is kept, the image equals a fresh upload of the
     moved scene at closest-hit level, and the update costs far less than the 2 ms rebuild (measured figure:
-    profiles/r02_update_instances.json; asserted here with a generous bound so a slow box does not flake)."""
+    profiles/r02n_update_instances.json; asserted here with a generous bound so a slow box does not flake)."""
     import copy
 
     sc = scene_cache("sponza")

@@ -72,6 +72,10 @@ class _Material(C.Structure):
     _fields_ = [("base_color", C.c_float * 3), ("roughness", C.c_float), ("metallic", C.c_float), ("emissive", C.c_float)]
 
 
+class _Texture(C.Structure):
+    _fields_ = [("pixels", C.c_void_p), ("width", C.c_int), ("height", C.c_int), ("format", C.c_int)]
+
+
 class Stats(C.Structure):
     _fields_ = [
         ("segments", C.c_uint64), ("node_visits", C.c_uint64), ("triangle_tests", C.c_uint64), ("kernel_launches", C.c_uint64),
@@ -101,6 +105,10 @@ ABI = [
     ("cavept_rebuild_mesh", C.c_int, [_P, C.c_int, _P, _P]),
     ("cavept_get_mesh_bvh", C.c_int, [_P, C.c_int, _P, C.c_int]),
     ("cavept_get_fast_tree", C.c_int, [_P, _P, C.c_int]),
+    ("cavept_set_mesh_uvs", C.c_int, [_P, C.c_int, _P]),
+    ("cavept_upload_textures", C.c_int, [_P, _P, C.c_int]),
+    ("cavept_set_material_maps", C.c_int, [_P, _P, _P, C.c_int]),
+    ("cavept_set_env_map", C.c_int, [_P, _P, C.c_int, C.c_int]),
     ("cavept_get_scene_counts", C.c_int, [_P] + [C.POINTER(C.c_int)] * 5),
     ("cavept_get_scene_arrays", C.c_int, [_P] * 6),
     ("cavept_set_camera", C.c_int, [_P, C.POINTER(C.c_float), C.POINTER(C.c_float), C.POINTER(C.c_float), C.POINTER(C.c_float), C.c_float]),
@@ -402,6 +410,36 @@ class PathTracer:
 
     def set_refit(self, enable: bool):
         self._check(self._lib.cavept_set_refit(self._ctx, 1 if enable else 0))
+
+    # -- textured materials / environment map (the reference's switched-off RayColor) ---------
+    def set_mesh_uvs(self, mesh: int, uvs: np.ndarray):
+        uv = np.ascontiguousarray(uvs, dtype=np.float32)
+        self._check(self._lib.cavept_set_mesh_uvs(self._ctx, mesh, uv.ctypes.data))
+
+    def upload_textures(self, textures):
+        """textures: list of (H, W, 4) arrays, uint8 (unorm) or float32."""
+        arr = (_Texture * max(len(textures), 1))()
+        keep = []
+        for k, t in enumerate(textures):
+            a = np.ascontiguousarray(t, dtype=np.uint8 if np.asarray(t).dtype == np.uint8 else np.float32)
+            assert a.ndim == 3 and a.shape[2] == 4
+            keep.append(a)
+            arr[k] = _Texture(a.ctypes.data, a.shape[1], a.shape[0], 0 if a.dtype == np.uint8 else 1)
+        self._check(self._lib.cavept_upload_textures(self._ctx, arr, len(textures)))
+
+    def set_material_maps(self, base_color_maps, material_maps):
+        a = np.ascontiguousarray(base_color_maps, dtype=np.int32)
+        b = np.ascontiguousarray(material_maps, dtype=np.int32)
+        assert a.shape == b.shape
+        self._check(self._lib.cavept_set_material_maps(self._ctx, a.ctypes.data, b.ctypes.data, a.shape[0]))
+
+    def set_env_map(self, rgb: Optional[np.ndarray]):
+        if rgb is None:
+            self._check(self._lib.cavept_set_env_map(self._ctx, None, 0, 0))
+            return
+        a = np.ascontiguousarray(rgb, dtype=np.float32)
+        assert a.ndim == 3 and a.shape[2] == 3
+        self._check(self._lib.cavept_set_env_map(self._ctx, a.ctypes.data, a.shape[1], a.shape[0]))
 
     def update_materials(self, materials):
         self._check(self._lib.cavept_update_materials(self._ctx, self._materials(materials), len(materials)))

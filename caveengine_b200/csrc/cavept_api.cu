@@ -30,15 +30,34 @@ GpuPtMaterial make_gpu_material(const cavept_material& m) {
 
 // UpdateAccelStructure (path_tracer.cpp:120-201): materials de-duplicated in mesh-key
 // order, instance array with world matrix + glm::inverse.
+// material maps in GpuPtMaterial-slot order (what the kernel indexes with GpuPtMesh::materialId)
+int upload_material_maps(cavept_ctx* ctx) {
+    if (!ctx->have_maps) return CAVEPT_OK;
+    std::vector<int> maps(2 * ctx->gpu_material_src.size() + 2, -1);
+    for (size_t g = 0; g < ctx->gpu_material_src.size(); ++g) {
+        const size_t m = (size_t)ctx->gpu_material_src[g];
+        if (2 * m + 1 < ctx->api_mat_maps.size()) {
+            maps[2 * g] = ctx->api_mat_maps[2 * m];
+            maps[2 * g + 1] = ctx->api_mat_maps[2 * m + 1];
+        }
+    }
+    CU(ctx, ctx->d_mat_maps.reserve(maps.size()));
+    ctx->ex.upload(ctx->d_mat_maps.ptr, maps.data(), maps.size() * sizeof(int));
+    CU(ctx, cudaStreamSynchronize(ctx->ex.stream));
+    return check_exec(ctx, "material maps");
+}
+
 int rebuild_instance_arrays(cavept_ctx* ctx) {
     std::map<int, int> lookup;  // material id -> GpuPtMaterial slot
     ctx->gpu_materials.clear();
+    ctx->gpu_material_src.clear();
     for (size_t mesh_id = 0; mesh_id < ctx->meshes.size(); ++mesh_id) {  // std::map<Guid, MeshData> iteration == ascending key
         const MeshRecord& rec = ctx->meshes[mesh_id];
         if (rec.built < 0) continue;
         if (lookup.count(rec.first_material)) continue;
         lookup[rec.first_material] = (int)ctx->gpu_materials.size();
         ctx->gpu_materials.push_back(make_gpu_material(ctx->materials[rec.first_material]));
+        ctx->gpu_material_src.push_back(rec.first_material);
     }
     ctx->gpu_meshes.resize(ctx->instances.size());
     for (size_t i = 0; i < ctx->instances.size(); ++i) {
@@ -56,7 +75,8 @@ int rebuild_instance_arrays(cavept_ctx* ctx) {
     ctx->ex.upload(ctx->d_meshes.ptr, ctx->gpu_meshes.data(), ctx->gpu_meshes.size() * sizeof(GpuPtMesh));
     ctx->ex.upload(ctx->d_materials.ptr, ctx->gpu_materials.data(), ctx->gpu_materials.size() * sizeof(GpuPtMaterial));
     CU(ctx, cudaStreamSynchronize(ctx->ex.stream));
-    return check_exec(ctx, "instance upload");
+    if (int e = check_exec(ctx, "instance upload")) return e;
+    return upload_material_maps(ctx);
 }
 
 // Production BVH: one world-space tree over every (instance, triangle) pair (wbvh_body.h).
@@ -180,6 +200,7 @@ int build_world(cavept_ctx* ctx) {
     }
     ctx->fast_levels = rep.levels;
     ctx->q4_ready = want_q4;
+    ctx->uvs_dirty = true;  // slots were re-ordered
     ctx->stats.fast_node_count = 2 * rep.n_pairs;
     // what a later refit needs (SAH builder: the pairs of a level are one index range)
     ctx->refit_ready = !lbvh && rep.levels > 0;
@@ -431,6 +452,7 @@ CAVEPT_API int cavept_upload_scene(cavept_ctx* ctx, const cavept_mesh* meshes, i
     }
     if (int e = select_device(ctx)) return e;
     ctx->scene_resident = false;
+    ctx->have_uvs = ctx->have_maps = false;  // texture coordinates and material maps belong to the scene they were set on
     ctx->meshes.assign(mesh_count, MeshRecord());
     ctx->built_order.clear();
     long long n_verts = 0, n_tris = 0;
@@ -608,6 +630,121 @@ CAVEPT_API int cavept_get_scene_arrays(cavept_ctx* ctx, void* v, void* i, void* 
     return check_exec(ctx, "scene read-back");
 }
 
+// ---- textured materials, alpha cut-out, environment map (the reference's `#if 0` RayColor, glsl/path_tracer.cs.glsl:62-112) ----
+CAVEPT_API int cavept_set_mesh_uvs(cavept_ctx* ctx, int mesh, const float* uvs) {
+    CAVEPT_RANGE();
+    if (!ctx || !uvs) return CAVEPT_ERR_INVALID_ARG;
+    if (!ctx->scene_resident) return fail(ctx, CAVEPT_ERR_NOT_READY, "no scene resident");
+    if (mesh < 0 || mesh >= (int)ctx->meshes.size()) return fail(ctx, CAVEPT_ERR_INVALID_ARG, "mesh %d out of range", mesh);
+    const MeshRecord& rec = ctx->meshes[mesh];
+    if (rec.built < 0) return CAVEPT_OK;  // no instance uses it: nothing to texture
+    if (int e = select_device(ctx)) return e;
+    if (!ctx->have_uvs) {
+        CU(ctx, ctx->d_uvs.reserve((size_t)ctx->n_verts * 2));
+        ctx->ex.fill(ctx->d_uvs.ptr, 0, (size_t)ctx->n_verts * 2 * sizeof(float));
+        ctx->have_uvs = true;
+    }
+    ctx->ex.upload(ctx->d_uvs.ptr + (size_t)rec.vert_off * 2, uvs, (size_t)rec.vertex_count * 2 * sizeof(float));
+    CU(ctx, cudaStreamSynchronize(ctx->ex.stream));  // the caller's array is free to go
+    ctx->uvs_dirty = true;
+    ctx->dirty = true;
+    return check_exec(ctx, "mesh uvs");
+}
+
+CAVEPT_API int cavept_upload_textures(cavept_ctx* ctx, const cavept_texture* textures, int texture_count) {
+    CAVEPT_RANGE();
+    if (!ctx || texture_count < 0 || (texture_count > 0 && !textures)) return CAVEPT_ERR_INVALID_ARG;
+    if (int e = select_device(ctx)) return e;
+    ctx->dirty = true;
+    ctx->n_textures = 0;
+    ctx->have_maps = false;
+    if (texture_count == 0) return CAVEPT_OK;
+    std::vector<TexInfo> table(texture_count);
+    size_t total = 0;
+    for (int t = 0; t < texture_count; ++t) {
+        const cavept_texture& x = textures[t];
+        if (!x.pixels || x.width <= 0 || x.height <= 0 || (x.format != CAVEPT_TEX_RGBA8 && x.format != CAVEPT_TEX_RGBA32F))
+            return fail(ctx, CAVEPT_ERR_INVALID_ARG, "texture %d: bad size, format or pointer", t);
+        if (total + (size_t)x.width * x.height > (size_t)0x7fffffff) return fail(ctx, CAVEPT_ERR_CAPACITY, "more than 2^31 texels");
+        table[t].offset = (int)total;
+        table[t].width = x.width;
+        table[t].height = x.height;
+        table[t].pad = 0;
+        total += (size_t)x.width * x.height;
+    }
+    std::vector<F4> texels(total);
+    for (int t = 0; t < texture_count; ++t) {
+        const cavept_texture& x = textures[t];
+        F4* dst = texels.data() + table[t].offset;
+        const size_t n = (size_t)x.width * x.height;
+        if (x.format == CAVEPT_TEX_RGBA32F) {
+            std::memcpy(dst, x.pixels, n * sizeof(F4));
+        } else {
+            const unsigned char* src = static_cast<const unsigned char*>(x.pixels);
+            for (size_t i = 0; i < n; ++i) {
+                dst[i].x = (float)src[4 * i] / 255.0f;
+                dst[i].y = (float)src[4 * i + 1] / 255.0f;
+                dst[i].z = (float)src[4 * i + 2] / 255.0f;
+                dst[i].w = (float)src[4 * i + 3] / 255.0f;
+            }
+        }
+    }
+    CU(ctx, ctx->d_tex_data.reserve(total));
+    CU(ctx, ctx->d_tex_table.reserve(texture_count));
+    ctx->ex.upload(ctx->d_tex_data.ptr, texels.data(), total * sizeof(F4));
+    ctx->ex.upload(ctx->d_tex_table.ptr, table.data(), table.size() * sizeof(TexInfo));
+    CU(ctx, cudaStreamSynchronize(ctx->ex.stream));
+    ctx->n_textures = texture_count;
+    return check_exec(ctx, "texture upload");
+}
+
+CAVEPT_API int cavept_set_material_maps(cavept_ctx* ctx, const int* base_color_maps, const int* material_maps, int material_count) {
+    CAVEPT_RANGE();
+    if (!ctx || !base_color_maps || !material_maps) return CAVEPT_ERR_INVALID_ARG;
+    if (!ctx->scene_resident) return fail(ctx, CAVEPT_ERR_NOT_READY, "no scene resident");
+    if (material_count != (int)ctx->materials.size()) return fail(ctx, CAVEPT_ERR_INVALID_ARG, "material count %d != %zu", material_count, ctx->materials.size());
+    std::vector<int> maps(2 * (size_t)material_count);
+    bool any = false;
+    for (int m = 0; m < material_count; ++m) {
+        const int a = base_color_maps[m], b = material_maps[m];
+        if (a >= ctx->n_textures || b >= ctx->n_textures) return fail(ctx, CAVEPT_ERR_INVALID_ARG, "material %d names a texture outside the set of %d", m, ctx->n_textures);
+        maps[2 * m] = a < 0 ? -1 : a;
+        maps[2 * m + 1] = b < 0 ? -1 : b;
+        any = any || a >= 0 || b >= 0;
+    }
+    if (int e = select_device(ctx)) return e;
+    ctx->api_mat_maps = maps;
+    ctx->have_maps = any;
+    ctx->dirty = true;
+    return upload_material_maps(ctx);
+}
+
+CAVEPT_API int cavept_set_env_map(cavept_ctx* ctx, const float* rgb, int width, int height) {
+    CAVEPT_RANGE();
+    if (!ctx) return CAVEPT_ERR_INVALID_ARG;
+    ctx->dirty = true;
+    if (!rgb) {
+        ctx->env_w = ctx->env_h = 0;
+        return CAVEPT_OK;
+    }
+    if (width <= 0 || height <= 0) return fail(ctx, CAVEPT_ERR_INVALID_ARG, "environment map %d x %d", width, height);
+    if (int e = select_device(ctx)) return e;
+    const size_t n = (size_t)width * height;
+    std::vector<F4> texels(n);
+    for (size_t i = 0; i < n; ++i) {
+        texels[i].x = rgb[3 * i];
+        texels[i].y = rgb[3 * i + 1];
+        texels[i].z = rgb[3 * i + 2];
+        texels[i].w = 1.0f;
+    }
+    CU(ctx, ctx->d_env.reserve(n));
+    ctx->ex.upload(ctx->d_env.ptr, texels.data(), n * sizeof(F4));
+    CU(ctx, cudaStreamSynchronize(ctx->ex.stream));
+    ctx->env_w = width;
+    ctx->env_h = height;
+    return check_exec(ctx, "environment map");
+}
+
 CAVEPT_API int cavept_get_fast_tree(cavept_ctx* ctx, void* out_records, int capacity_records) {
     if (!ctx || !out_records) return -CAVEPT_ERR_INVALID_ARG;
     if (!ctx->scene_resident) return -fail(ctx, CAVEPT_ERR_NOT_READY, "no scene resident");
@@ -684,6 +821,23 @@ static int render_rect(cavept_ctx* ctx, int x0, int y0, int w, int h, int first_
     p.accum = ctx->d_accum.ptr;
     p.counters = ctx->d_stats.ptr;
     const bool fast = ctx->cfg.trace_mode == CAVEPT_TRACE_FAST;
+    // textured materials / environment map: the launch takes the per-pixel kernel's textured instantiation
+    const bool use_maps = ctx->have_maps && ctx->have_uvs && ctx->n_textures > 0;
+    const bool textured = fast && (use_maps || ctx->env_w > 0);
+    if (textured) {
+        if (use_maps && (ctx->uvs_dirty || ctx->d_fuvs.cap < (size_t)ctx->n_prims)) {
+            CU(ctx, ctx->d_fuvs.reserve(ctx->n_prims));
+            launch_emit_uvs(ctx->ex, ctx->d_ftris.ptr, ctx->d_indices.ptr, ctx->d_meshes.ptr, ctx->d_uvs.ptr, ctx->d_fuvs.ptr, ctx->n_prims);
+            ctx->uvs_dirty = false;
+        }
+        p.fuvs = use_maps ? ctx->d_fuvs.ptr : nullptr;
+        p.tex_table = ctx->d_tex_table.ptr;
+        p.tex_data = ctx->d_tex_data.ptr;
+        p.mat_maps = use_maps ? ctx->d_mat_maps.ptr : nullptr;
+        p.env = ctx->env_w > 0 ? ctx->d_env.ptr : nullptr;
+        p.env_w = ctx->env_w;
+        p.env_h = ctx->env_h;
+    }
     int stack_entries = 0, grid_blocks = 0;
     if (fast && ctx->kernel_variant == CAVEPT_KERNEL_POOL) {
         stack_entries = ctx->fast_levels + 2 < 4 ? 4 : ctx->fast_levels + 2;
@@ -695,7 +849,8 @@ static int render_rect(cavept_ctx* ctx, int x0, int y0, int w, int h, int first_
         grid_blocks = ctx->n_sms * ctx->pool_blocks_per_sm;
     }
     CU(ctx, cudaEventRecord(ctx->ev0, ctx->ex.stream));
-    if (grid_blocks > 0) launch_trace_pool(ctx->ex, p, ctx->count_visits, stack_entries, ctx->d_job_counter.ptr, grid_blocks);
+    if (textured) launch_trace(ctx->ex, p, true, ctx->count_visits, true);
+    else if (grid_blocks > 0) launch_trace_pool(ctx->ex, p, ctx->count_visits, stack_entries, ctx->d_job_counter.ptr, grid_blocks);
     else if (fast && ctx->kernel_variant == CAVEPT_KERNEL_QUEUE) launch_trace_queue(ctx->ex, p, ctx->count_visits, ctx->d_job_counter.ptr, ctx->n_sms);
     else if (fast && ctx->kernel_variant == CAVEPT_KERNEL_WIDE4 && ctx->q4_ready && ctx->fast_levels <= kWideMaxLevels && ctx->n_pairs > 0) launch_trace_wide(ctx->ex, p, ctx->count_visits);
     else launch_trace(ctx->ex, p, fast, ctx->count_visits);

@@ -102,6 +102,18 @@ struct cavept_ctx {
     // production layout
     DevBuf<FastNode> d_fnodes;
     DevBuf<QPair> d_qpairs;
+    // textured materials / environment map (cavept.h "textured materials ...")
+    DevBuf<float> d_uvs;          // 2 floats per scene-global vertex (zero where a mesh has none)
+    DevBuf<FastUv> d_fuvs;        // per FastTri slot, re-emitted after a build when uvs_dirty
+    DevBuf<F4> d_tex_data;
+    DevBuf<TexInfo> d_tex_table;
+    DevBuf<int> d_mat_maps;       // 2 per GpuPtMaterial slot (the de-duplicated order the kernel indexes)
+    std::vector<int> api_mat_maps;     // 2 per caller-side material, as cavept_set_material_maps received them
+    std::vector<int> gpu_material_src; // caller-side material of each GpuPtMaterial slot
+    DevBuf<F4> d_env;
+    int env_w = 0, env_h = 0;
+    int n_textures = 0;
+    bool have_uvs = false, uvs_dirty = false, have_maps = false;
     DevBuf<Q4Node> d_q4nodes;
     bool q4_ready = false;  // four-wide records built over the resident tree (CAVEPT_KERNEL_WIDE4 only)
     float grid_origin[3] = { 0, 0, 0 }, grid_scale[3] = { 1, 1, 1 };

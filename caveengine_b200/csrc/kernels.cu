@@ -872,6 +872,32 @@ void launch_assemble_indices(CudaExec& ex, const uint32_t* raw_indices, const in
 int run_build_bvh_parity(CudaExec& ex, BuildArrays a, const int* tri_off_host, const int* d_tri_off, int n_meshes, BuildItem* host_scratch, BuildReport* report) {
     return build_bvh_parity(ex, a, tri_off_host, d_tri_off, n_meshes, host_scratch, report);
 }
+// per FastTri slot: the texture coordinates of its triangle's vertices, in the slot's vertex order (wb_tri_box / wb_emit_slot
+// swap B and C for a mirroring instance)
+struct FnEmitUvs {
+    const FastTri* ftris;
+    const GpuPtIndex* indices;
+    const GpuPtMesh* instances;
+    const float* uvs;  // 2 floats per scene-global vertex
+    FastUv* out;
+    __device__ void operator()(int s) const {
+        const int tri = (int)f2u(ftris[s].v1.w), inst = (int)f2u(ftris[s].v0.w);
+        const float* m = instances[inst].transform;
+        const float det = m[0] * (m[5] * m[10] - m[9] * m[6]) - m[4] * (m[1] * m[10] - m[9] * m[2]) + m[8] * (m[1] * m[6] - m[5] * m[2]);
+        const int* idx = indices[tri].tri;
+        const int i0 = idx[0], i1 = det < 0.0f ? idx[2] : idx[1], i2 = det < 0.0f ? idx[1] : idx[2];
+        FastUv o;
+        o.uv[0] = uvs[2 * i0]; o.uv[1] = uvs[2 * i0 + 1];
+        o.uv[2] = uvs[2 * i1]; o.uv[3] = uvs[2 * i1 + 1];
+        o.uv[4] = uvs[2 * i2]; o.uv[5] = uvs[2 * i2 + 1];
+        o.pad[0] = o.pad[1] = 0.0f;
+        out[s] = o;
+    }
+};
+void launch_emit_uvs(CudaExec& ex, const FastTri* ftris, const GpuPtIndex* indices, const GpuPtMesh* instances, const float* uvs, FastUv* out, int n_slots) {
+    ex.launch(n_slots, FnEmitUvs{ ftris, indices, instances, uvs, out });
+}
+
 int run_build_wbvh(CudaExec& ex, WBuild b, WReport* report) { return build_wbvh(ex, b, report); }
 int run_build_lbvh(CudaExec& ex, WBuild b, WReport* report) { return build_lbvh(ex, b, report); }
 void run_build_q4(CudaExec& ex, WBuild b, int n_pairs) { ex.launch(n_pairs, FnWbQ4{ b, n_pairs }); }
@@ -883,15 +909,15 @@ void run_refit_wbvh(CudaExec& ex, WBuild b, int n_pairs, int n_levels, const uns
 // Block = 128 threads = a 16 x 8 pixel tile; each warp covers an 8 x 4 sub-tile so the
 // primary rays of a warp are coherent.  Replaces Dispatch(ceil(W/16), ceil(H/16), 1) of a
 // 16x16 work group (cave/engine/render_graph/common_passes.cpp:990-997).
-template<bool kFast, bool kCount, int kQuorum = kStepQuorum, int kBatch = kShadeBatch>
-__global__ void __launch_bounds__(128, 8) k_trace(const TraceParams p) {
+template<bool kFast, bool kCount, int kQuorum = kStepQuorum, int kBatch = kShadeBatch, bool kTex = false>
+__global__ void __launch_bounds__(128, kTex ? 6 : 8) k_trace(const TraceParams p) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     int x = p.tile_x0 + blockIdx.x * 16 + (warp & 1) * 8 + (lane & 7);
     const int y = p.tile_y0 + blockIdx.y * 8 + (warp >> 1) * 4 + (lane >> 3);
     if (p.tile_x1 > 0 && (x >= p.tile_x1 || y >= p.tile_y1)) x = p.width;  // outside the tile: the body treats x == width as no pixel
     unsigned long long cnt[3] = { 0ull, 0ull, 0ull };
     __shared__ int s_stack[kFast ? kStackSize * 128 : 1];  // [depth][thread]: conflict-free whatever each lane's depth
-    unsigned int segs = kFast ? body_trace_pixel_fast<kCount, kQuorum, kBatch>(p, x, y, s_stack + threadIdx.x, 128, cnt) : body_trace_pixel_reference<kCount>(p, x, y, cnt);
+    unsigned int segs = kFast ? body_trace_pixel_fast<kCount, kQuorum, kBatch, false, false, kTex>(p, x, y, s_stack + threadIdx.x, 128, cnt) : body_trace_pixel_reference<kCount>(p, x, y, cnt);
     segs = __reduce_add_sync(0xffffffffu, segs);
     if (lane == 0 && segs) atomicAdd(&p.counters[0], (unsigned long long)segs);
     if (kCount) {
@@ -1028,10 +1054,13 @@ void launch_trace_pool(CudaExec& ex, const TraceParams& p, bool count_visits, in
     ++ex.launches;
 }
 
-void launch_trace(CudaExec& ex, const TraceParams& p, bool fast, bool count_visits) {
+void launch_trace(CudaExec& ex, const TraceParams& p, bool fast, bool count_visits, bool textured) {
     const int tw = p.tile_x1 > 0 ? p.tile_x1 - p.tile_x0 : p.width, th = p.tile_x1 > 0 ? p.tile_y1 - p.tile_y0 : p.height;
     const dim3 grid((tw + 15) / 16, (th + 7) / 8, 1), block(128, 1, 1);
-    if (fast) {
+    if (fast && textured) {  // the instantiation with texture / environment-map shading (trace_body.h shade_hit_textured)
+        if (count_visits) k_trace<true, true, kStepQuorum, kShadeBatch, true><<<grid, block, 0, ex.stream>>>(p);
+        else k_trace<true, false, kStepQuorum, kShadeBatch, true><<<grid, block, 0, ex.stream>>>(p);
+    } else if (fast) {
         if (count_visits) k_trace<true, true><<<grid, block, 0, ex.stream>>>(p);
         else k_trace<true, false><<<grid, block, 0, ex.stream>>>(p);
     } else {

@@ -85,6 +85,18 @@ struct alignas(64) FastTri {
 };
 static_assert(sizeof(FastTri) == 64, "FastTri");
 
+// Texture coordinates of a slot's triangle, in the slot's own vertex order (a mirroring instance swaps B and C).
+struct alignas(32) FastUv {
+    float uv[6];
+    float pad[2];
+};
+static_assert(sizeof(FastUv) == 32, "FastUv");
+struct TexInfo {
+    int offset;  // first texel in tex_data
+    int width, height;
+    int pad;
+};
+
 struct TraceParams {
     // reference-layout arrays (what BindPathTracerData binds, path_tracer.cpp:324-331)
     const GpuPtVertex* vertices;
@@ -112,6 +124,13 @@ struct TraceParams {
     int accum_sums;   // 0: rgb = running mean, a = n (path_tracer.cs.glsl:46-59); 1: rgb = sum, a = n (multi-GPU group mode)
     F4* accum;
     unsigned long long* counters;  // [0] segments, [1] node visits, [2] triangle tests
+    // textured materials / environment map (cavept.h "textured materials ..."; the kTex instantiation only)
+    const FastUv* fuvs;        // per FastTri slot: the three vertices' texture coordinates; null: no mesh has any
+    const TexInfo* tex_table;  // one entry per texture of the set
+    const F4* tex_data;        // all texels, RGBA32F
+    const int* mat_maps;       // per material: base-colour map, metal-rough map (texture index or -1)
+    const F4* env;             // equirectangular environment map (rgb, w unused); null: the constant sky
+    int env_w, env_h;
 };
 
 struct Ray {
@@ -539,6 +558,70 @@ CV_D bool shade_segment(const TraceParams& p, const Hit& hit, Ray& ray, uint32_t
     return shade_hit(p, is_hit, n, mat, ray, state, radiance, throughput, bounce);
 }
 
+// ---- textured shading: the reference's switched-off RayColor (glsl/path_tracer.cs.glsl:62-112) ------------------
+// bilinear, repeat wrap: texel centres at (i + 0.5) / size
+CV_HD int tex_wrap(int i, int n) {
+    i %= n;
+    return i < 0 ? i + n : i;
+}
+CV_D F4 tex_sample(const F4* texels, int w, int h, float u, float v) {
+    const float x = u * (float)w - 0.5f, y = v * (float)h - 0.5f;
+    const float fx0 = floorf(x), fy0 = floorf(y);
+    const float fx = x - fx0, fy = y - fy0;
+    const int x0 = tex_wrap((int)fx0, w), y0 = tex_wrap((int)fy0, h), x1 = tex_wrap((int)fx0 + 1, w), y1 = tex_wrap((int)fy0 + 1, h);
+    const F4 a = texels[(size_t)y0 * w + x0], b = texels[(size_t)y0 * w + x1], c = texels[(size_t)y1 * w + x0], d = texels[(size_t)y1 * w + x1];
+    F4 r;
+    r.x = (a.x + fx * (b.x - a.x)) + fy * ((c.x + fx * (d.x - c.x)) - (a.x + fx * (b.x - a.x)));
+    r.y = (a.y + fx * (b.y - a.y)) + fy * ((c.y + fx * (d.y - c.y)) - (a.y + fx * (b.y - a.y)));
+    r.z = (a.z + fx * (b.z - a.z)) + fy * ((c.z + fx * (d.z - c.z)) - (a.z + fx * (b.z - a.z)));
+    r.w = (a.w + fx * (b.w - a.w)) + fy * ((c.w + fx * (d.w - c.w)) - (a.w + fx * (b.w - a.w)));
+    return r;
+}
+// equirectangular lookup of a unit direction (sample_spherical_map as the engine writes it, hlsl/to_cube_map.ps.hlsl:9-15)
+CV_D F3 env_sample(const TraceParams& p, F3 d) {
+    const float u = atan2f(d.z, d.x) * 0.1591f + 0.5f;
+    const float sy = d.y < -1.0f ? -1.0f : (d.y > 1.0f ? 1.0f : d.y);
+    const float v = asinf(sy) * 0.3183f + 0.5f;
+    const F4 c = tex_sample(p.env, p.env_w, p.env_h, u, v);
+    return f3(c.x, c.y, c.z);
+}
+// One iteration of that RayColor after the scene query.  slot / (u, v) identify the hit; `mat` is the instance's
+// material and is overridden by its maps.  Returns true when the path ends.
+CV_D bool shade_hit_textured(const TraceParams& p, bool is_hit, int slot, float hu, float hv, int material, F3 n, GpuPtMaterial mat, Ray& ray, uint32_t& state, F3& radiance,
+                             F3& throughput, int& bounce) {
+    if (!is_hit) {
+        const F3 sky = p.env ? env_sample(p, normalize3(ray.direction)) : f3(0.3f, 0.3f, 0.3f);
+        radiance = radiance + sky * throughput;
+        return true;
+    }
+    const int base_map = p.mat_maps ? p.mat_maps[2 * material] : -1, mr_map = p.mat_maps ? p.mat_maps[2 * material + 1] : -1;
+    if (p.fuvs && (base_map >= 0 || mr_map >= 0)) {
+        const FastUv& t = p.fuvs[slot];
+        const float tu = t.uv[0] + hu * (t.uv[2] - t.uv[0]) + hv * (t.uv[4] - t.uv[0]);
+        const float tv = t.uv[1] + hu * (t.uv[3] - t.uv[1]) + hv * (t.uv[5] - t.uv[1]);
+        if (base_map >= 0) {
+            const TexInfo ti = p.tex_table[base_map];
+            const F4 c = tex_sample(p.tex_data + ti.offset, ti.width, ti.height, tu, tv);
+            if (c.w <= 0.01f) {  // alpha cut-out: `continue` -- the ray goes on from the hit point, the bounce is spent (:78-80)
+                ray.origin = ray.origin + ray.t * ray.direction;
+                ray.t = kRayTMax;
+                ++bounce;
+                return bounce >= p.max_bounce;
+            }
+            mat.baseColor[0] = c.x;
+            mat.baseColor[1] = c.y;
+            mat.baseColor[2] = c.z;
+        }
+        if (mr_map >= 0) {
+            const TexInfo ti = p.tex_table[mr_map];
+            const F4 c = tex_sample(p.tex_data + ti.offset, ti.width, ti.height, tu, tv);
+            mat.metallic = c.z;
+            mat.roughness = c.y;
+        }
+    }
+    return shade_hit(p, true, n, mat, ray, state, radiance, throughput, bounce);
+}
+
 // ---- main(), path_tracer.cs.glsl:11-44: seed, jitter, camera ray -----------------------
 CV_D void start_path(const TraceParams& p, int x, int y, int frame_index, Ray& ray, uint32_t& seed) {
     seed = ((uint32_t)x * 1973u + (uint32_t)y * 9277u + (uint32_t)frame_index * 26699u) | 1u;
@@ -729,7 +812,7 @@ CV_D void walk_park_any(Walk& w) {
     if (kWide) walk_park_leaf_wide(w); else walk_park_leaf(w);
 }
 
-template<bool kCount, int kQuorum = kStepQuorum, int kBatch = kShadeBatch, bool kQueue = false, bool kWide = false>
+template<bool kCount, int kQuorum = kStepQuorum, int kBatch = kShadeBatch, bool kQueue = false, bool kWide = false, bool kTex = false>
 CV_D unsigned int body_trace_pixel_fast(const TraceParams& p, int x, int y, int* stack, int stride, unsigned long long* cnt, int* job_counter = nullptr, int* spill = nullptr) {
     constexpr int kTight = kWide ? CV_WIDE_TIGHT_STEPS : CV_TIGHT_STEPS;
     constexpr int kMinority = kWide ? CV_WIDE_MINORITY_STEPS : CV_MINORITY_STEPS;
@@ -805,7 +888,11 @@ CV_D unsigned int body_trace_pixel_fast(const TraceParams& p, int x, int y, int*
                         mat.baseColor[0] = m.a; mat.baseColor[1] = m.b; mat.baseColor[2] = m.c; mat.roughness = m.d;
                         mat.emissive[0] = m.e; mat.emissive[1] = m.f; mat.emissive[2] = m.g; mat.metallic = m.h;
                     }
-                    if (shade_hit(p, is_hit, n, mat, ray, seed, radiance, throughput, bounce)) {
+                    int material = 0;
+                    if (kTex && is_hit) material = (int)f2u(ld256(&p.fnormals[w.hit_slot]).h);
+                    const bool ended = kTex ? shade_hit_textured(p, is_hit, w.hit_slot, w.hit_u, w.hit_v, material, n, mat, ray, seed, radiance, throughput, bounce)
+                                            : shade_hit(p, is_hit, n, mat, ray, seed, radiance, throughput, bounce);
+                    if (ended) {
                         F4 acc = p.accum[pix];
                         accumulate_mode(p.accum_sums, acc, radiance, f == 0 && p.reset_first != 0);
                         p.accum[pix] = acc;

@@ -175,6 +175,34 @@ CAVEPT_API int cavept_set_refit(cavept_ctx* ctx, int enable);
  * device (BASELINE config 5; beyond the reference, path_tracer.cpp:69 "@TODO"). */
 CAVEPT_API int cavept_rebuild_mesh(cavept_ctx* ctx, int mesh, const float* positions, const float* normals);
 
+/* ---- textured materials, alpha cut-out and an HDR environment map: the half of the reference's path tracer that is
+ *      switched off in its source (`#if 0`: cave/shader/glsl/path_tracer.cs.glsl:62-112, the material / texture set-up
+ *      cave/engine/renderer/path_tracer/path_tracer.cpp:254-273), built here as that code states it:
+ *        hit: base-colour map present -> sample it at the interpolated UV; alpha <= 0.01 -> the segment passes straight
+ *             through (origin moves to the hit point, one bounce is consumed, no random numbers are drawn); otherwise the
+ *             sampled rgb IS the diffuse colour (not multiplied by the material's albedo, :76-84); metal-rough map
+ *             present -> metallic = its .b, roughness = its .g (:88-92);
+ *        miss: radiance += environment(equirectangular uv of the direction) * throughput instead of the constant 0.3 sky (:103-105).
+ *      Textures are sampled bilinearly with repeat wrap (GL's default `texture()` on a mip-less image).  The reference
+ *      cannot run this path (its structs no longer exist), so there is nothing to pin it against: parity unpinned.  With no
+ *      texture and no environment map set, none of this is compiled into the launch (the default kernels are unchanged).
+ *      Only the per-pixel FAST kernel has the textured instantiation. ------------------------------------------------ */
+typedef struct cavept_texture {
+    const void* pixels; /* width * height texels, row 0 first */
+    int width, height;
+    int format;         /* CAVEPT_TEX_RGBA8 (unorm) or CAVEPT_TEX_RGBA32F */
+} cavept_texture;
+enum { CAVEPT_TEX_RGBA8 = 0, CAVEPT_TEX_RGBA32F = 1 };
+/* Per-vertex texture coordinates of one mesh (vertex_count * 2 floats; MeshAsset::texcoords_0, mesh_asset.h:47). */
+CAVEPT_API int cavept_set_mesh_uvs(cavept_ctx* ctx, int mesh, const float* uvs);
+/* Replaces the texture set (count 0 clears it and every material's maps). */
+CAVEPT_API int cavept_upload_textures(cavept_ctx* ctx, const cavept_texture* textures, int texture_count);
+/* Per material: index of its base-colour map and of its metal-rough map in the texture set, -1 = none
+ * (MaterialComponent::TEXTURE_BASE / TEXTURE_METALLIC_ROUGHNESS, path_tracer.cpp:270-272). */
+CAVEPT_API int cavept_set_material_maps(cavept_ctx* ctx, const int* base_color_maps, const int* material_maps, int material_count);
+/* Equirectangular environment map, width * height * 3 floats (c_hdrEnvMap); NULL restores the constant sky. */
+CAVEPT_API int cavept_set_env_map(cavept_ctx* ctx, const float* rgb, int width, int height);
+
 /* ---- parity read-backs of what BindPathTracerData binds (path_tracer.cpp:324-331):
  *      the reference-layout arrays, structured_buffer.hlsl.h:24-61 ------------------ */
 CAVEPT_API int cavept_get_mesh_bvh(cavept_ctx* ctx, int mesh, void* out_gpu_pt_bvh, int capacity_nodes); /* mesh-local indices, as FillGpuBvhAccel emits; returns count or <0 */

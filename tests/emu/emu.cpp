@@ -108,6 +108,32 @@ EMU_API int emu_bvh_build(const GpuPtVertex* vertices, const GpuPtIndex* indices
 // (fast == 4) walks; null = not built.  A binding instead of one more argument on three entry points.
 static Q4Node* g_q4nodes = nullptr;
 EMU_API void emu_bind_q4(Q4Node* q4nodes) { g_q4nodes = q4nodes; }
+// textured shading inputs (trace_body.h shade_hit_textured); used by emu_render mode 6
+static const FastUv* g_fuvs = nullptr;
+static const TexInfo* g_tex_table = nullptr;
+static const F4* g_tex_data = nullptr;
+static const int* g_mat_maps = nullptr;
+static const F4* g_env = nullptr;
+static int g_env_w = 0, g_env_h = 0;
+EMU_API void emu_bind_textures(const FastUv* fuvs, const TexInfo* table, const F4* texels, const int* mat_maps, const F4* env, int env_w, int env_h) {
+    g_fuvs = fuvs;
+    g_tex_table = table;
+    g_tex_data = texels;
+    g_mat_maps = mat_maps;
+    g_env = env;
+    g_env_w = env_w;
+    g_env_h = env_h;
+}
+// tex_sample (trace_body.h) at n points: uv = 2 floats each, out = 4 floats each
+EMU_API void emu_tex_sample(const F4* texels, int w, int h, const float* uv, int n, float* out) {
+    for (int i = 0; i < n; ++i) {
+        const F4 c = tex_sample(texels, w, h, uv[2 * i], uv[2 * i + 1]);
+        out[4 * i] = c.x;
+        out[4 * i + 1] = c.y;
+        out[4 * i + 2] = c.z;
+        out[4 * i + 3] = c.w;
+    }
+}
 static unsigned char* g_pair_depth = nullptr;  // n_prims + 8 bytes, written by the SAH build, read by the refit
 EMU_API void emu_bind_pair_depth(unsigned char* p) { g_pair_depth = p; }
 
@@ -267,6 +293,15 @@ EMU_API long long emu_render(const GpuPtVertex* vertices, const GpuPtIndex* indi
                                n_frames, reset_first, accum);
     unsigned long long cnt[3] = { 0, 0, 0 };
     p.counters = cnt;
+    if (fast == 6) {
+        p.fuvs = g_fuvs;
+        p.tex_table = g_tex_table;
+        p.tex_data = g_tex_data;
+        p.mat_maps = g_mat_maps;
+        p.env = g_env;
+        p.env_w = g_env_w;
+        p.env_h = g_env_h;
+    }
     long long segs = 0;
     int stack[kStackSize];
     if (fast == 2) {  // the persistent job-queue body (trace_pool_body.h): one emulated lane draws every job, two at a time
@@ -300,6 +335,7 @@ EMU_API long long emu_render(const GpuPtVertex* vertices, const GpuPtIndex* indi
     for (int y = 0; y < height; ++y) {
         for (int x = 0; x < width; ++x) {
             if (fast == 4) segs += body_trace_pixel_fast<true, kStepQuorum, kShadeBatch, false, true>(p, x, y, stack, 1, cnt, nullptr, spill);  // four-wide walk (k_trace_wide)
+            else if (fast == 6) segs += body_trace_pixel_fast<true, kStepQuorum, kShadeBatch, false, false, true>(p, x, y, stack, 1, cnt);  // textured instantiation
             else segs += fast ? body_trace_pixel_fast<true>(p, x, y, stack, 1, cnt) : body_trace_pixel_reference<true>(p, x, y, cnt);
         }
     }

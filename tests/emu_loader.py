@@ -133,6 +133,47 @@ class EmuScene:
                                    counters)
         return accum, {"segments": int(segs), "node_visits": int(counters[1]), "tri_tests": int(counters[2])}
 
+    def bind_textures(self, uvs=None, textures=(), base_maps=None, mr_maps=None, env=None):
+        """Inputs of the textured instantiation (render(..., fast=6)): per scene-global-vertex uvs (V, 2), RGBA float
+        textures [(H, W, 4)], per-material map indices, equirect env (H, W, 3).  The per-slot uv records are emitted here
+        the way kernels.cu FnEmitUvs does."""
+        a = self.asm
+        self._tex_keep = []
+        fuvs = None
+        if uvs is not None:
+            uvs = np.ascontiguousarray(uvs, dtype=np.float32)
+            tri = self.ftris["v1"][:, 3].view(np.uint32).astype(np.int64)
+            inst = self.ftris["v0"][:, 3].view(np.uint32).astype(np.int64)
+            m = a.meshes["transform"].reshape(-1, 16).astype(np.float32)
+            det = (m[:, 0] * (m[:, 5] * m[:, 10] - m[:, 9] * m[:, 6]) - m[:, 4] * (m[:, 1] * m[:, 10] - m[:, 9] * m[:, 2]) + m[:, 8] * (m[:, 1] * m[:, 6] - m[:, 5] * m[:, 2]))
+            idx = a.indices["tri"][tri].astype(np.int64)
+            swap = det[inst] < 0
+            i1 = np.where(swap, idx[:, 2], idx[:, 1])
+            i2 = np.where(swap, idx[:, 1], idx[:, 2])
+            fuvs = np.zeros((self.n_prims, 8), dtype=np.float32)
+            fuvs[:, 0:2] = uvs[idx[:, 0]]
+            fuvs[:, 2:4] = uvs[i1]
+            fuvs[:, 4:6] = uvs[i2]
+        table = np.zeros((max(len(textures), 1), 4), dtype=np.int32)
+        texels = []
+        off = 0
+        for k, t in enumerate(textures):
+            t = np.ascontiguousarray(t, dtype=np.float32)
+            table[k] = (off, t.shape[1], t.shape[0], 0)
+            texels.append(t.reshape(-1, 4))
+            off += t.shape[0] * t.shape[1]
+        texels = np.ascontiguousarray(np.concatenate(texels)) if texels else np.zeros((1, 4), dtype=np.float32)
+        maps = None
+        if base_maps is not None:
+            maps = np.ascontiguousarray(np.stack([np.asarray(base_maps, dtype=np.int32), np.asarray(mr_maps, dtype=np.int32)], axis=1))
+        envp, ew, eh = None, 0, 0
+        if env is not None:
+            env = np.asarray(env, dtype=np.float32)
+            eh, ew = env.shape[:2]
+            envp = np.ascontiguousarray(np.concatenate([env, np.ones((eh, ew, 1), dtype=np.float32)], axis=2))
+        self._tex_keep = [fuvs, table, texels, maps, envp]
+        self.lib.emu_bind_textures(None if fuvs is None or maps is None else _p(fuvs), _p(table), _p(texels), None if maps is None or fuvs is None else _p(maps), None if envp is None else _p(envp), C.c_int(ew), C.c_int(eh))
+
     def primary_hits(self, camera, width, height, frame=0, mode=1):
         """(FastTri slot or -1, ray.t) of every pixel's camera ray: mode 0 = all triangles tested (no tree), 1 = the
         production walk."""

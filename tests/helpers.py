@@ -160,3 +160,53 @@ def check_metrics(m, limits, what):
     for k, lim in limits.items():
         ok = m[k] >= lim if k == "exact" else m[k] <= lim
         assert ok, f"{what}: {k} = {m[k]:.6g} violates the stated bound {lim:.6g}; measured {m}"
+
+
+# ---- textured materials / environment map (cavept.h "textured materials ...") ----------------------------------
+def texture_case(scene, seed=3):
+    """Deterministic inputs of the textured path for `scene`: per-mesh planar uvs, two RGBA32F textures (a checker with
+    transparent holes; a metal-rough map), per-material map indices and a small equirectangular environment map.
+    Returns a dict; "uvs_global" / "maps_gpu" are the same data in the orders the emulator wants (scene-global vertex
+    order = meshes in order of first use; GpuPtMaterial-slot order = first material of each used mesh, by mesh id)."""
+    rng = np.random.default_rng(seed)
+    uvs = [np.ascontiguousarray(np.stack([m.positions[:, 0] * 0.9 + m.positions[:, 1] * 0.31, m.positions[:, 2] * 0.8 - m.positions[:, 1] * 0.17], axis=1), dtype=np.float32)
+           for m in scene.meshes]
+    n = 16
+    yy, xx = np.mgrid[0:n, 0:n]
+    base = np.zeros((n, n, 4), dtype=np.float32)
+    base[..., :3] = np.where(((xx // 2 + yy // 2) % 2 == 0)[..., None], np.array([0.85, 0.3, 0.25], dtype=np.float32), np.array([0.2, 0.5, 0.8], dtype=np.float32))
+    base[..., 3] = np.where((xx % 8 < 2) & (yy % 8 < 2), 0.0, 1.0)  # holes: alpha cut-out
+    mr = np.zeros((8, 8, 4), dtype=np.float32)
+    mr[..., 1] = rng.uniform(0.1, 1.0, (8, 8))  # roughness in .g
+    mr[..., 2] = rng.uniform(0.0, 0.9, (8, 8))  # metallic in .b
+    mr[..., 3] = 1.0
+    eh, ew = 8, 16
+    env = np.zeros((eh, ew, 3), dtype=np.float32)
+    env[..., 0] = np.linspace(0.1, 0.9, ew)[None, :]
+    env[..., 1] = np.linspace(0.2, 0.6, eh)[:, None]
+    env[..., 2] = 0.5
+    nm = len(scene.materials)
+    base_maps = np.array([0 if k % 2 == 0 else -1 for k in range(nm)], dtype=np.int32)
+    mr_maps = np.array([1 if k % 3 != 2 else -1 for k in range(nm)], dtype=np.int32)
+    first, used = {}, []
+    for inst in scene.instances:
+        if inst.mesh not in first:
+            first[inst.mesh] = inst.material
+            used.append(inst.mesh)
+    slots = []
+    for mesh_id in sorted(first):
+        if first[mesh_id] not in slots:
+            slots.append(first[mesh_id])
+    return {"uvs": uvs, "textures": [base, mr], "base_maps": base_maps, "mr_maps": mr_maps, "env": env,
+            "uvs_global": np.concatenate([uvs[m] for m in used]), "maps_gpu": (base_maps[slots], mr_maps[slots]), "slots": slots}
+
+
+def apply_texture_case(pt, scene, case, maps=True, env=True):
+    """Feeds a texture_case to a PathTracer through the C ABI."""
+    if maps:
+        for k in range(len(scene.meshes)):
+            pt.set_mesh_uvs(k, case["uvs"][k])
+        pt.upload_textures(case["textures"])
+        pt.set_material_maps(case["base_maps"], case["mr_maps"])
+    if env:
+        pt.set_env_map(case["env"])

@@ -445,3 +445,81 @@ def test_walk_loses_no_hit_with_the_camera_far_outside_the_scene(port_oracle, sc
     assert (want_slot >= 0).sum() > 1000  # the scene is in view
     assert np.array_equal(got_t, want_t)
     assert np.array_equal(got_slot >= 0, want_slot >= 0)
+
+
+# ---- the reference's switched-off textured RayColor (glsl/path_tracer.cs.glsl:62-112), as built: parity unpinned, so the
+#      tests pin it where it must coincide with the live shader, and against a numpy statement of the sampler -------------
+def _textured_emu(port_oracle, sc):
+    asm = port_oracle.assemble(sc)
+    return asm, E.EmuScene(asm, sc)
+
+
+def test_textured_path_with_constant_maps_equals_the_live_shader(port_oracle, scene_cache):
+    """A base-colour map holding the material's own colour, a metal-rough map holding its own (roughness, metallic) and an
+    environment map holding the constant sky 0.3 change nothing: bit-identical accumulator."""
+    sc = scene_cache("tiny")
+    asm, emu = _textured_emu(port_oracle, sc)
+    want, sw = emu.render(sc.camera, 64, 36, 0, 2, 5, fast=1)
+    case = H.texture_case(sc)
+    slots = case["slots"]
+    textures = []
+    for g, m in enumerate(slots):
+        mat = sc.materials[m]
+        textures.append(np.tile(np.array([*mat.base_color, 1.0], dtype=np.float32), (4, 4, 1)))
+        textures.append(np.tile(np.array([0.0, mat.roughness, mat.metallic, 1.0], dtype=np.float32), (2, 2, 1)))
+    n = len(slots)
+    emu.bind_textures(case["uvs_global"], textures, np.arange(n) * 2, np.arange(n) * 2 + 1, np.full((4, 8, 3), 0.3, dtype=np.float32))
+    got, sg = emu.render(sc.camera, 64, 36, 0, 2, 5, fast=6)
+    assert sg["segments"] == sw["segments"]
+    assert got.tobytes() == want.tobytes()
+
+
+def test_fully_transparent_base_maps_let_every_ray_through(port_oracle, scene_cache):
+    """alpha <= 0.01 everywhere: every hit is a pass-through that spends a bounce and draws no random number, so a pixel is
+    exactly the sky (0.3) when its ray leaves the scene within max_bounce surfaces and exactly 0 otherwise."""
+    sc = scene_cache("tiny")
+    asm, emu = _textured_emu(port_oracle, sc)
+    case = H.texture_case(sc)
+    n = len(case["slots"])
+    clear = np.zeros((2, 2, 4), dtype=np.float32)
+    emu.bind_textures(case["uvs_global"], [clear], np.zeros(n, dtype=np.int32), np.full(n, -1, dtype=np.int32), None)
+    got, _ = emu.render(sc.camera, 64, 36, 0, 1, 5, fast=6)
+    rgb = got[..., :3]
+    assert np.all((rgb == np.float32(0.3)) | (rgb == 0.0))
+    assert (rgb == np.float32(0.3)).any() and (rgb == 0.0).any()
+
+
+def test_textured_path_changes_the_image_and_is_deterministic(port_oracle, scene_cache):
+    sc = scene_cache("tiny")
+    asm, emu = _textured_emu(port_oracle, sc)
+    plain, _ = emu.render(sc.camera, 64, 36, 0, 2, 5, fast=1)
+    case = H.texture_case(sc)
+    emu.bind_textures(case["uvs_global"], case["textures"], *case["maps_gpu"], case["env"])
+    a, sa = emu.render(sc.camera, 64, 36, 0, 2, 5, fast=6)
+    b, sb = emu.render(sc.camera, 64, 36, 0, 2, 5, fast=6)
+    assert a.tobytes() == b.tobytes() and sa == sb
+    assert H.image_mismatch(a, plain, rel=1e-3) > 0.5  # textures, cut-outs and the environment are all in the picture
+    assert np.isfinite(a).all()
+
+
+def test_texture_sampler_is_bilinear_with_repeat_wrap():
+    """tex_sample against a float64 numpy statement of GL_LINEAR / GL_REPEAT (texel centres at (i + 0.5) / size)."""
+    import ctypes as C
+
+    lib = E.load()
+    rng = np.random.default_rng(11)
+    w, h = 7, 5
+    tex = np.ascontiguousarray(rng.uniform(0, 1, (h, w, 4)), dtype=np.float32)
+    uv = np.ascontiguousarray(rng.uniform(-2.5, 3.5, (2000, 2)), dtype=np.float32)
+    out = np.zeros((2000, 4), dtype=np.float32)
+    lib.emu_tex_sample(tex.ctypes.data_as(C.c_void_p), C.c_int(w), C.c_int(h), uv.ctypes.data_as(C.c_void_p), C.c_int(2000), out.ctypes.data_as(C.c_void_p))
+    x = uv[:, 0].astype(np.float32) * np.float32(w) - np.float32(0.5)
+    y = uv[:, 1].astype(np.float32) * np.float32(h) - np.float32(0.5)
+    x0, y0 = np.floor(x), np.floor(y)
+    fx, fy = (x - x0).astype(np.float64)[:, None], (y - y0).astype(np.float64)[:, None]
+    x0, y0 = x0.astype(np.int64), y0.astype(np.int64)
+    t = tex.astype(np.float64)
+    a, b = t[y0 % h, x0 % w], t[y0 % h, (x0 + 1) % w]
+    c, d = t[(y0 + 1) % h, x0 % w], t[(y0 + 1) % h, (x0 + 1) % w]
+    want = (a + fx * (b - a)) * (1 - fy) + (c + fx * (d - c)) * fy
+    assert np.abs(out - want).max() < 2e-6

@@ -730,3 +730,67 @@ def test_fast_equals_reference_walk_with_the_camera_100_extents_away(api, scene_
             imgs.append((pt.read_accum(), pt.stats()["segments"]))
     assert imgs[0][1] == imgs[1][1] and imgs[0][1] > 256 * 144 * 2 * 1.1  # same segment count, and the scene is in view
     H.check_metrics(H.image_metrics(imgs[1][0], imgs[0][0]), {"exact": 0.999}, "fast_vs_walk_far_camera")
+
+
+# ---- textured materials, alpha cut-out, environment map: the reference's `#if 0` RayColor (glsl/path_tracer.cs.glsl:62-112).
+#      The reference cannot run it (parity unpinned): the device is checked against the emulator's run of the same body, and
+#      against the live shader where the two must coincide. ----------------------------------------------------------------
+def test_textured_path_matches_the_emulator(api, port_oracle, scene_cache):
+    import emu_loader
+
+    sc = scene_cache("tiny")
+    case = H.texture_case(sc)
+    emu = emu_loader.EmuScene(port_oracle.assemble(sc), sc)
+    emu.bind_textures(case["uvs_global"], case["textures"], *case["maps_gpu"], case["env"])
+    want, sw = emu.render(sc.camera, 96, 54, 0, 2, 5, fast=6)
+    with _tracer(api, sc, 96, 54, 5, api.TraceMode.FAST) as pt:
+        H.apply_texture_case(pt, sc, case)
+        pt.reset_stats()
+        pt.render(0, 2, sync=True)
+        got = pt.read_accum()
+        segs = pt.stats()["segments"]
+    assert abs(segs - sw["segments"]) <= max(4, sw["segments"] // 200)
+    H.check_metrics(H.image_metrics(got, want), {"bad_1e4": 0.003, "rel_rmse": 0.04}, "textured_vs_emulator")  # measured 0.00135 / 0.0202
+
+
+def test_textured_path_with_constant_maps_equals_the_live_shader_on_the_device(api, scene_cache):
+    sc = scene_cache("tiny")
+    case = H.texture_case(sc)
+    with _tracer(api, sc, 96, 54, 5, api.TraceMode.FAST) as pt:
+        pt.render(0, 3, sync=True)
+        want = pt.read_accum()
+        textures, base_maps, mr_maps = [], [], []
+        for m, mat in enumerate(sc.materials):
+            textures.append(np.tile(np.array([*mat.base_color, 1.0], dtype=np.float32), (4, 4, 1)))
+            textures.append(np.tile(np.array([0.0, mat.roughness, mat.metallic, 1.0], dtype=np.float32), (2, 2, 1)))
+            base_maps.append(2 * m)
+            mr_maps.append(2 * m + 1)
+        for k in range(len(sc.meshes)):
+            pt.set_mesh_uvs(k, case["uvs"][k])
+        pt.upload_textures(textures)
+        pt.set_material_maps(base_maps, mr_maps)
+        pt.set_env_map(np.full((4, 8, 3), 0.3, dtype=np.float32))
+        pt.reset()
+        pt.render(0, 3, sync=True)
+        got = pt.read_accum()
+        pt.set_env_map(None)
+        pt.upload_textures([])
+        pt.reset()
+        pt.render(0, 3, sync=True)
+        back = pt.read_accum()
+    assert got.tobytes() == want.tobytes()
+    assert back.tobytes() == want.tobytes()  # maps cleared: the default kernel again
+
+
+def test_fully_transparent_base_maps_let_every_ray_through_on_the_device(api, scene_cache):
+    sc = scene_cache("tiny")
+    case = H.texture_case(sc)
+    with _tracer(api, sc, 96, 54, 5, api.TraceMode.FAST) as pt:
+        for k in range(len(sc.meshes)):
+            pt.set_mesh_uvs(k, case["uvs"][k])
+        pt.upload_textures([np.zeros((2, 2, 4), dtype=np.float32)])
+        pt.set_material_maps([0] * len(sc.materials), [-1] * len(sc.materials))
+        pt.render(0, 1, sync=True)
+        rgb = pt.read_accum()[..., :3]
+    assert np.all((rgb == np.float32(0.3)) | (rgb == 0.0))
+    assert (rgb == np.float32(0.3)).any() and (rgb == 0.0).any()

@@ -167,6 +167,28 @@ CV_HD F8 ld256(const void* p) {
 #endif
     return r;
 }
+// the same load with an L1 eviction hint: kHint 1 = L1::no_allocate (records read once per visit: triangles, normals),
+// 2 = L1::evict_last (records many lanes come back to: the upper levels of the tree)
+template<int kHint>
+CV_HD F8 ld256_hint(const void* p) {
+    F8 r;
+#if defined(__CUDA_ARCH__)
+    if (kHint == 1) {
+        asm volatile("ld.global.nc.L1::no_allocate.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                     : "=f"(r.a), "=f"(r.b), "=f"(r.c), "=f"(r.d), "=f"(r.e), "=f"(r.f), "=f"(r.g), "=f"(r.h)
+                     : "l"(p));
+    } else if (kHint == 2) {
+        asm volatile("ld.global.nc.L1::evict_last.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                     : "=f"(r.a), "=f"(r.b), "=f"(r.c), "=f"(r.d), "=f"(r.e), "=f"(r.f), "=f"(r.g), "=f"(r.h)
+                     : "l"(p));
+    } else {
+        r = ld256(p);
+    }
+#else
+    memcpy(&r, p, 32);
+#endif
+    return r;
+}
 // 1/x to ~1 ulp (MUFU.RCP): for slopes whose error the padded boxes absorb, never for results.
 CV_HD float rcp_approx(float x) {
 #if defined(__CUDA_ARCH__)

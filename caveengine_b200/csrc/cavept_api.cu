@@ -853,7 +853,12 @@ static int render_rect(cavept_ctx* ctx, int x0, int y0, int w, int h, int first_
     else if (grid_blocks > 0) launch_trace_pool(ctx->ex, p, ctx->count_visits, stack_entries, ctx->d_job_counter.ptr, grid_blocks);
     else if (fast && ctx->kernel_variant == CAVEPT_KERNEL_QUEUE) launch_trace_queue(ctx->ex, p, ctx->count_visits, ctx->d_job_counter.ptr, ctx->n_sms);
     else if (fast && ctx->kernel_variant == CAVEPT_KERNEL_WIDE4 && ctx->q4_ready && ctx->fast_levels <= kWideMaxLevels && ctx->n_pairs > 0) launch_trace_wide(ctx->ex, p, ctx->count_visits);
-    else launch_trace(ctx->ex, p, fast, ctx->count_visits);
+    else {
+        // triangle + normal records beyond what any L1 keeps, and a launch of several samples (mostly incoherent bounce
+        // segments): the instantiation with the L1 hints on its gathers (trace_body.h walk_test_triangle)
+        const bool stream = fast && (size_t)ctx->n_prims * 2 * sizeof(FastTri) > ((size_t)4 << 20) && n_frames >= 4;
+        launch_trace(ctx->ex, p, fast, ctx->count_visits, false, stream);
+    }
     CU(ctx, cudaEventRecord(ctx->ev1, ctx->ex.stream));
     ctx->dirty = false;
     return check_exec(ctx, "render launch");

@@ -909,7 +909,7 @@ void run_refit_wbvh(CudaExec& ex, WBuild b, int n_pairs, int n_levels, const uns
 // Block = 128 threads = a 16 x 8 pixel tile; each warp covers an 8 x 4 sub-tile so the
 // primary rays of a warp are coherent.  Replaces Dispatch(ceil(W/16), ceil(H/16), 1) of a
 // 16x16 work group (cave/engine/render_graph/common_passes.cpp:990-997).
-template<bool kFast, bool kCount, int kQuorum = kStepQuorum, int kBatch = kShadeBatch, bool kTex = false>
+template<bool kFast, bool kCount, int kQuorum = kStepQuorum, int kBatch = kShadeBatch, bool kTex = false, bool kStream = false>
 __global__ void __launch_bounds__(128, kTex ? 6 : 8) k_trace(const TraceParams p) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     int x = p.tile_x0 + blockIdx.x * 16 + (warp & 1) * 8 + (lane & 7);
@@ -917,7 +917,7 @@ __global__ void __launch_bounds__(128, kTex ? 6 : 8) k_trace(const TraceParams p
     if (p.tile_x1 > 0 && (x >= p.tile_x1 || y >= p.tile_y1)) x = p.width;  // outside the tile: the body treats x == width as no pixel
     unsigned long long cnt[3] = { 0ull, 0ull, 0ull };
     __shared__ int s_stack[kFast ? kStackSize * 128 : 1];  // [depth][thread]: conflict-free whatever each lane's depth
-    unsigned int segs = kFast ? body_trace_pixel_fast<kCount, kQuorum, kBatch, false, false, kTex>(p, x, y, s_stack + threadIdx.x, 128, cnt) : body_trace_pixel_reference<kCount>(p, x, y, cnt);
+    unsigned int segs = kFast ? body_trace_pixel_fast<kCount, kQuorum, kBatch, false, false, kTex, kStream>(p, x, y, s_stack + threadIdx.x, 128, cnt) : body_trace_pixel_reference<kCount>(p, x, y, cnt);
     segs = __reduce_add_sync(0xffffffffu, segs);
     if (lane == 0 && segs) atomicAdd(&p.counters[0], (unsigned long long)segs);
     if (kCount) {
@@ -1054,12 +1054,15 @@ void launch_trace_pool(CudaExec& ex, const TraceParams& p, bool count_visits, in
     ++ex.launches;
 }
 
-void launch_trace(CudaExec& ex, const TraceParams& p, bool fast, bool count_visits, bool textured) {
+void launch_trace(CudaExec& ex, const TraceParams& p, bool fast, bool count_visits, bool textured, bool stream) {
     const int tw = p.tile_x1 > 0 ? p.tile_x1 - p.tile_x0 : p.width, th = p.tile_x1 > 0 ? p.tile_y1 - p.tile_y0 : p.height;
     const dim3 grid((tw + 15) / 16, (th + 7) / 8, 1), block(128, 1, 1);
     if (fast && textured) {  // the instantiation with texture / environment-map shading (trace_body.h shade_hit_textured)
         if (count_visits) k_trace<true, true, kStepQuorum, kShadeBatch, true><<<grid, block, 0, ex.stream>>>(p);
         else k_trace<true, false, kStepQuorum, kShadeBatch, true><<<grid, block, 0, ex.stream>>>(p);
+    } else if (fast && stream) {  // many-sample launch over a large scene: L1 hints on the gathers
+        if (count_visits) k_trace<true, true, kStepQuorum, kShadeBatch, false, true><<<grid, block, 0, ex.stream>>>(p);
+        else k_trace<true, false, kStepQuorum, kShadeBatch, false, true><<<grid, block, 0, ex.stream>>>(p);
     } else if (fast) {
         if (count_visits) k_trace<true, true><<<grid, block, 0, ex.stream>>>(p);
         else k_trace<true, false><<<grid, block, 0, ex.stream>>>(p);

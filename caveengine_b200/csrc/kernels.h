@@ -51,7 +51,7 @@ int run_build_lbvh(CudaExec& ex, WBuild b, WReport* report);
 void run_build_q4(CudaExec& ex, WBuild b, int n_pairs);  // Q4Node records over a finished pair tree
 void run_refit_wbvh(CudaExec& ex, WBuild b, int n_pairs, int n_levels, const unsigned char* d_moved, float* d_area_sum, float out[7]);
 
-void launch_trace(CudaExec& ex, const TraceParams& p, bool fast, bool count_visits, bool textured = false);
+void launch_trace(CudaExec& ex, const TraceParams& p, bool fast, bool count_visits, bool textured = false, bool stream = false);
 void launch_emit_uvs(CudaExec& ex, const FastTri* ftris, const GpuPtIndex* indices, const GpuPtMesh* instances, const float* uvs, FastUv* out, int n_slots);
 // the per-pixel body over the four-wide records (CAVEPT_KERNEL_WIDE4; p.q4nodes must be set)
 void launch_trace_wide(CudaExec& ex, const TraceParams& p, bool count_visits);

@@ -393,9 +393,9 @@ CV_D void walk_park_leaf(Walk& w) {
 // One interior step: fetch the sibling pair (QPair), slab-test both boxes against [0, ray.t], descend
 // into the nearer hit child and push the other.  Same interval logic as HitBvh (:133-149);
 // boxes entirely behind the origin or beyond the current hit are rejected.
-template<bool kCount>
+template<bool kCount, bool kStream = false>
 CV_D void walk_step(const TraceParams& p, Walk& w, float ray_t, unsigned long long* cnt) {
-    const F8 c = ld256_hint<CV_NODE_HINT>(p.qpairs + w.ref);  // the whole pair: one 256-bit load
+    const F8 c = ld256_hint<kStream ? CV_NODE_HINT : 0>(p.qpairs + w.ref);  // the whole pair: one 256-bit load
     if (kCount) cnt[1] += 2;
     const uint32_t far_x = w.near_x ^ kSelFlip, far_y = w.near_y ^ kSelFlip, far_z = w.near_z ^ kSelFlip;
     const uint32_t q0 = f2u(c.a), q1 = f2u(c.b), q2 = f2u(c.c), q3 = f2u(c.d), q4 = f2u(c.e), q5 = f2u(c.f);
@@ -499,13 +499,19 @@ CV_D void walk_step_wide(const TraceParams& p, Walk& w, float ray_t, unsigned lo
 // instance this is HitScene's arithmetic bit for bit; for a transformed instance the
 // reference intersects in mesh space with the inverse-transformed ray (:160-166), which is
 // the same (t, u, v) up to fp32 rounding of the transform.
-template<bool kCount>
+template<bool kCount, bool kStream = false>
 CV_D void walk_test_triangle(const TraceParams& p, Walk& w, const Ray& ray, float& ray_t, unsigned long long* cnt) {
     const int leaf = w.q0;
     const int slot = leaf & 0x1fffffff;
     const int more = (leaf >> 29) & 3;
-    const F8 t0 = ld256_hint<CV_TRI_HINT>(&p.ftris[slot]);             // A.xyz, instance, AB.xyz, triangle id
-    const F8 t1 = ld256_hint<CV_TRI_HINT>(&p.ftris[slot].v2);          // AC.xyz (same cache line)
+    // kStream (chosen per launch by the host): a many-sample launch over a scene far larger than L1 is dominated by
+    // incoherent bounce segments -- a triangle record will not be touched again before it is evicted, so it is fetched
+    // without allocating an L1 line, and the sibling pairs are marked evict-last (+1.8 % on config 3).  Small scenes
+    // live in L1 and the camera rays of a one-sample launch hit the same triangles: those launches keep the plain
+    // loads (the hint applied everywhere cost config 2 a factor 2.7 and config 5 10 %; choosing per lane by bounce, or
+    // per launch by a run-time branch around the loads, cost config 3 7 %: all measured -- hence a template parameter).
+    const F8 t0 = ld256_hint<kStream ? CV_TRI_HINT : 0>(&p.ftris[slot]);     // A.xyz, instance, AB.xyz, triangle id
+    const F8 t1 = ld256_hint<kStream ? CV_TRI_HINT : 0>(&p.ftris[slot].v2);  // AC.xyz (same cache line)
     if (kCount) ++cnt[2];
     float u, v;
     if (hit_triangle_edges(f3(t0.a, t0.b, t0.c), f3(t0.e, t0.f, t0.g), f3(t1.a, t1.b, t1.c), ray.origin, ray.direction, ray_t, u, v)) {
@@ -809,16 +815,16 @@ CV_D int trace_draw_jobs(int* counter, bool want) {
 #ifndef CV_WIDE_PARK_EVERY
 #define CV_WIDE_PARK_EVERY 1
 #endif
-template<bool kCount, bool kWide>
+template<bool kCount, bool kWide, bool kStream = false>
 CV_D void walk_step_any(const TraceParams& p, Walk& w, float ray_t, unsigned long long* cnt) {
-    if (kWide) walk_step_wide<kCount>(p, w, ray_t, cnt); else walk_step<kCount>(p, w, ray_t, cnt);
+    if (kWide) walk_step_wide<kCount>(p, w, ray_t, cnt); else walk_step<kCount, kStream>(p, w, ray_t, cnt);
 }
 template<bool kWide>
 CV_D void walk_park_any(Walk& w) {
     if (kWide) walk_park_leaf_wide(w); else walk_park_leaf(w);
 }
 
-template<bool kCount, int kQuorum = kStepQuorum, int kBatch = kShadeBatch, bool kQueue = false, bool kWide = false, bool kTex = false>
+template<bool kCount, int kQuorum = kStepQuorum, int kBatch = kShadeBatch, bool kQueue = false, bool kWide = false, bool kTex = false, bool kStream = false>
 CV_D unsigned int body_trace_pixel_fast(const TraceParams& p, int x, int y, int* stack, int stride, unsigned long long* cnt, int* job_counter = nullptr, int* spill = nullptr) {
     constexpr int kTight = kWide ? CV_WIDE_TIGHT_STEPS : CV_TIGHT_STEPS;
     constexpr int kMinority = kWide ? CV_WIDE_MINORITY_STEPS : CV_MINORITY_STEPS;
@@ -851,13 +857,13 @@ CV_D unsigned int body_trace_pixel_fast(const TraceParams& p, int x, int y, int*
             walk_park_any<kWide>(w);
             const bool can_step = ref_is_interior(w.ref);
             if (CV_WARP_COUNT(can_step) < kQuorum) break;
-            if (can_step) walk_step_any<kCount, kWide>(p, w, ray.t, cnt);
+            if (can_step) walk_step_any<kCount, kWide, kStream>(p, w, ray.t, cnt);
             // second step of the trip without a vote of its own (measured +2 %): the lanes that can
             // still step do, the others would have idled through it anyway
 #pragma unroll
             for (int k = 1; k < kTight; ++k) {
                 if ((k % kParkEvery) == 0) walk_park_any<kWide>(w);
-                if (ref_is_interior(w.ref)) walk_step_any<kCount, kWide>(p, w, ray.t, cnt);
+                if (ref_is_interior(w.ref)) walk_step_any<kCount, kWide, kStream>(p, w, ray.t, cnt);
             }
         }
         // ---- the vote ------------------------------------------------------------------------
@@ -869,10 +875,10 @@ CV_D unsigned int body_trace_pixel_fast(const TraceParams& p, int x, int y, int*
         const int n_shade = CV_WARP_COUNT(need_shade);
         if (n_step + n_tri + n_shade == 0) break;  // every lane has rendered all its frames
         if (n_tri > 0 && n_tri >= n_step) {
-            if (has_tri) walk_test_triangle<kCount>(p, w, ray, ray.t, cnt);
+            if (has_tri) walk_test_triangle<kCount, kStream>(p, w, ray, ray.t, cnt);
 #pragma unroll
             for (int k = 1; k < CV_TRI_PER_VOTE; ++k) {
-                if (w.q0 != 0) walk_test_triangle<kCount>(p, w, ray, ray.t, cnt);
+                if (w.q0 != 0) walk_test_triangle<kCount, kStream>(p, w, ray, ray.t, cnt);
             }
         } else if (n_shade >= kBatch || n_step == 0) {
             bool new_sample = false, want_job = false;
@@ -886,8 +892,8 @@ CV_D unsigned int body_trace_pixel_fast(const TraceParams& p, int x, int y, int*
                     GpuPtMaterial mat = {};
                     if (is_hit) {
                         // world-space vertex normals and the material id, pre-gathered at build time
-                        const F8 a = ld256_hint<CV_TRI_HINT>(&p.fnormals[w.hit_slot]);     // n1.xyz, instance, n2.xyz, material
-                        const F8 b = ld256_hint<CV_TRI_HINT>(&p.fnormals[w.hit_slot].v2);  // n3.xyz
+                        const F8 a = ld256_hint<kStream ? CV_TRI_HINT : 0>(&p.fnormals[w.hit_slot]);     // n1.xyz, instance, n2.xyz, material
+                        const F8 b = ld256_hint<kStream ? CV_TRI_HINT : 0>(&p.fnormals[w.hit_slot].v2);  // n3.xyz
                         const F3 n1 = f3(a.a, a.b, a.c), n2 = f3(a.e, a.f, a.g), n3 = f3(b.a, b.b, b.c);
                         n = n1 + w.hit_u * (n2 - n1) + w.hit_v * (n3 - n1);
                         const F8 m = ld256(&p.materials[(int)f2u(a.h)]);
@@ -936,11 +942,11 @@ CV_D unsigned int body_trace_pixel_fast(const TraceParams& p, int x, int y, int*
                 if (done || (kQueue && vacant)) w.ref = kRefSentinel;
             }
         } else {
-            if (can_step) walk_step_any<kCount, kWide>(p, w, ray.t, cnt);
+            if (can_step) walk_step_any<kCount, kWide, kStream>(p, w, ray.t, cnt);
 #pragma unroll
             for (int k = 1; k < kMinority; ++k) {
                 if ((k % kParkEvery) == 0) walk_park_any<kWide>(w);
-                if (ref_is_interior(w.ref)) walk_step_any<kCount, kWide>(p, w, ray.t, cnt);
+                if (ref_is_interior(w.ref)) walk_step_any<kCount, kWide, kStream>(p, w, ray.t, cnt);
             }
         }
     }

@@ -6,7 +6,7 @@ scene at >= 500k triangles: LBVH rebuild image vs the oracle, and an input that 
 balanced fallback.  Everything goes through the C ABI.
 
 Stated tolerances (every bound is <= 2x what profiles/probe_parity_metrics.py measured on the B200, see
-profiles/r02o_parity_measured.jsonl; the assert message prints the measured value):
+profiles/r02s_parity_measured.jsonl; the assert message prints the measured value):
   the RNG streams are identical and the arithmetic is fp32 in the same operation order, so a pixel differs
   only when device sincosf (<= 2 ulp) vs libm -- or the reference header's double promotions -- flips a
   discrete hit somewhere along one of its paths.  At 2-4 spp one flipped path onto a lamp is an O(1) change
@@ -21,7 +21,7 @@ from caveengine_b200 import scenes
 
 pytestmark = pytest.mark.gpu
 
-# name -> stated bounds (see the module docstring); the measured values are in profiles/r02o_parity_measured.jsonl
+# name -> stated bounds (see the module docstring); the measured values are in profiles/r02s_parity_measured.jsonl
 LIMITS = {
     "sponza_256spp_fast": {"rel_rmse": 0.018, "bias": 1e-4, "far_5pct": 0.09},       # measured 0.0088 / 2.9e-5 / 0.047
     "breakfast_4spp_fast": {"bad_1e4": 0.021, "rel_rmse": 0.17},                      # measured 0.0106 / 0.085

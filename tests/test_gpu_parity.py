@@ -47,14 +47,28 @@ def _tracer(api, scene, w, h, mb, mode, bvh_mode=None):
 
 
 # Stated image bounds per case: `bad_1e4` = fraction of pixels with a channel beyond 1e-4 * (|ref| + 1e-3), `rel_rmse` =
-# image RMSE / mean radiance.  Each is <= 2x the value measured on the B200 (profiles/r02_parity_measured.jsonl), with a
-# floor of two pixels / 1e-3 where the measurement was exactly zero.
+# image RMSE / mean radiance.  Each is <= 2x the value measured on the B200 (profiles/r02s_parity_measured.jsonl), with a
+# floor of two pixels / 1e-3 where the measurement was exactly zero.  The per-case entries were generated from
+# profiles/r02s_parity_measured.jsonl (2 x measured, rounded up to two digits); "default" only serves a case not yet measured.
 LIMITS = {
     "default": {"bad_1e4": 0.01, "rel_rmse": 0.04},
+    "oracle_tiny_REFERENCE_WALK": {"bad_1e4": 0.0047, "rel_rmse": 0.0035},
+    "oracle_cornell_REFERENCE_WALK": {"bad_1e4": 0.001, "rel_rmse": 0.001},
+    "oracle_heightfield_REFERENCE_WALK": {"bad_1e4": 0.0039, "rel_rmse": 0.009},
+    "oracle_sponza_REFERENCE_WALK": {"bad_1e4": 0.001, "rel_rmse": 0.0021},
+    "oracle_tiny_FAST": {"bad_1e4": 0.0085, "rel_rmse": 0.045},
+    "oracle_cornell_FAST": {"bad_1e4": 0.001, "rel_rmse": 0.001},
+    "oracle_heightfield_FAST": {"bad_1e4": 0.0039, "rel_rmse": 0.009},
+    "oracle_sponza_FAST": {"bad_1e4": 0.0087, "rel_rmse": 0.0091},
+    "golden_tiny_mb5": {"bad_1e4": 0.0031, "rel_rmse": 0.0021},
+    "golden_cornell_mb5": {"bad_1e4": 0.001, "rel_rmse": 0.001},
+    "update_materials": {"bad_1e4": 0.001, "rel_rmse": 0.001},
+    "ingest_REFERENCE_WALK": {"bad_1e4": 0.001, "rel_rmse": 0.001},
+    "ingest_FAST": {"bad_1e4": 0.019, "rel_rmse": 0.06},
     "fast_vs_walk_1080p": {"bad_1e4": 0.005, "bias": 0.005},
     "fast_vs_walk_identity": {"exact": 0.999},
     "lbvh_vs_sah": {"exact": 0.995},
-    "lbvh_rebuild_vs_oracle": {"bad_1e4": 0.01},
+    "lbvh_rebuild_vs_oracle": {"bad_1e4": 0.001},  # measured 0.00033
 }
 
 

@@ -678,8 +678,24 @@ CV_HD void accumulate_sum(F4& acc, F3 radiance, bool dirty) {
     acc.z = dirty ? radiance.z : acc.z + radiance.z;
     acc.w = dirty ? 1.0f : acc.w + 1.0f;
 }
+// One code path for both modes: mean = (radiance + w * mean) / (w + 1) as the shader writes it; sum = (radiance + 1 * sum) / 1,
+// which is radiance + sum exactly.  (A run-time branch between two inlined bodies here cost 13 % of a one-sample launch
+// on config 5 -- the accumulator load lost its place in the schedule; measured, profiles/r02z2_call.sh.)
 CV_HD void accumulate_mode(const int accum_sums, F4& acc, F3 radiance, bool dirty) {
-    if (accum_sums) accumulate_sum(acc, radiance, dirty); else accumulate(acc, radiance, dirty);
+    if (dirty) {
+        acc.x = radiance.x;
+        acc.y = radiance.y;
+        acc.z = radiance.z;
+        acc.w = 1.0f;
+    } else {
+        const float weight = acc.w;
+        const float nw = weight + 1.0f;
+        const float m = accum_sums ? 1.0f : weight, d = accum_sums ? 1.0f : nw;
+        acc.x = cv_div(radiance.x + m * acc.x, d);
+        acc.y = cv_div(radiance.y + m * acc.y, d);
+        acc.z = cv_div(radiance.z + m * acc.z, d);
+        acc.w = nw;
+    }
 }
 
 // One pixel, frames [first_frame, first_frame + n_frames), REFERENCE_WALK traversal.  The

@@ -79,7 +79,9 @@ enum { CAVEPT_BVH_PARITY = 0, CAVEPT_BVH_FAST = 1, CAVEPT_BVH_LBVH = 2 };
  * WIDE4: PIXEL's launch shape over four-wide node records (each sibling pair with its interior children replaced by their
  *        own pairs: 64 bytes, two loads from one line, four slab tests, children sorted by entry distance): half the
  *        dependent node fetches per segment.  Same closest hits; a lane's visit order differs, so an image can differ
- *        from the pair walk's where two triangles tie in t (tests/test_gpu_parity.py states the bound). */
+ *        from the pair walk's where two triangles tie in t (tests/test_gpu_parity.py states the bound).  Measured 11 %
+ *        slower than PIXEL on B200 (two loads from one line cost two L1 wavefronts); its records are built when the
+ *        variant is selected, not before. */
 enum { CAVEPT_KERNEL_POOL = 0, CAVEPT_KERNEL_PIXEL = 1, CAVEPT_KERNEL_QUEUE = 2, CAVEPT_KERNEL_WIDE4 = 3 };
 
 typedef struct cavept_config {

@@ -417,12 +417,18 @@ __device__ __forceinline__ WSweep wb_warp_sweep(WBin* item_bins, int lane) {
     }
     return r;
 }
+__device__ __noinline__ void wb_split_serial(const WBuild& b, int w, int level) { wb_body_split(b, w, level, true); }
 __global__ void __launch_bounds__(256) k_wb_split_binned(const WBuild b, int level) {
     const int w = (int)((blockIdx.x * 256u + threadIdx.x) >> 5);
     const int lane = threadIdx.x & 31;
     if (w >= b.level_items[level]) return;  // warp-uniform
     WItem& it = b.items[w];
-    if (it.axis < 0 || it.bins_slot < 0) return;  // median items and small items: FnWbSplit, one thread each
+    if (it.axis < 0 || it.bins_slot < 0) {
+        // a median split, or an item of <= kWDirectMax prims (in the level loop only when the subtree queue overflowed):
+        // the per-item serial statement, on one lane
+        if (lane == 0) wb_split_serial(b, w, level);
+        return;
+    }
     WSweep r = wb_warp_sweep<true>(&b.bins[it.bins_slot].b[0], lane);
     if (lane == 0) {
         if (r.best == ~0ull) {
@@ -437,12 +443,9 @@ __global__ void __launch_bounds__(256) k_wb_split_binned(const WBuild b, int lev
 }
 void CudaExec::wb_split(const WBuild& b, int level, int bound) {
     if (bound <= 0) return;
-    // arena items: at most bins_capacity of them, and at most `bound` items altogether
-    const int warps = bound < b.bins_capacity ? bound : b.bins_capacity;
-    k_wb_split_binned<<<(warps * 32 + 255) / 256, 256, 0, stream>>>(b, level);
+    k_wb_split_binned<<<(bound * 32 + 255) / 256, 256, 0, stream>>>(b, level);  // one warp per item of the level
     note(cudaGetLastError());
     ++launches;
-    launch(bound, FnWbSplit{ b, level, false });
 }
 
 // ---- partition of a level: left flags computed inside the scan's first kernel, the stable scatter inside its last

@@ -162,13 +162,11 @@ CV_D void body_init_accum(const BuildArrays& a, int w, int n_items) {
 }
 
 // ---- per element: fold vertices into the item's AABB and centroid box ---------------
-CV_D void body_reduce(const BuildArrays& a, int i) {
-    if (i >= a.n_tris) return;
-    const int w = a.node_of[i];
-    if (w < 0) return;
+// `acc` is the item's accumulator, or a block's private copy of it (kernels.cu k_parity_reduce): the folds are min / max
+// of keys, so where they are combined does not change the result
+CV_D void body_reduce_to(const BuildArrays& a, int i, int w, ItemAccum& acc) {
     const int g = a.order[i];
     const int* t = a.indices[g].tri;
-    ItemAccum& acc = a.accum[w];
     unsigned long long kmn[3], kmx[3];
     for (int k = 0; k < 3; ++k) {
         const F3 p = load_pos(a.vertices, t[k]);
@@ -196,6 +194,12 @@ CV_D void body_reduce(const BuildArrays& a, int i) {
     cv_group_max_u32(grp, &acc.cmx[0], ordered_key(c.x));
     cv_group_max_u32(grp, &acc.cmx[1], ordered_key(c.y));
     cv_group_max_u32(grp, &acc.cmx[2], ordered_key(c.z));
+}
+CV_D void body_reduce(const BuildArrays& a, int i) {
+    if (i >= a.n_tris) return;
+    const int w = a.node_of[i];
+    if (w < 0) return;
+    body_reduce_to(a, i, w, a.accum[w]);
 }
 
 // ---- per item: write the node, classify (:128-142), prepare the SAH pass ------------
@@ -288,26 +292,32 @@ CV_D void body_node(const BuildArrays& a, int w, int n_items) {
 CV_HD int clamp_bucket(int s) { return s < 0 ? 0 : (s > kBuckets - 1 ? kBuckets - 1 : s); }
 
 // ---- per element of SAH items: bucket counts and boxes (:162-169) -------------------
+// `b` is the item's bucket record, or a block's private copy of it (kernels.cu k_parity_bin)
+CV_D void body_bin_to(const BuildArrays& a, int i, const BuildItem& it, ItemBins& b) {
+    const int g = a.order[i];
+    const F4 c = a.tri_centroid[g];
+    const float cv = it.axis == 0 ? c.x : (it.axis == 1 ? c.y : c.z);
+    const float tmp = cv_div((cv - it.tmin) * (float)kBuckets, it.tmax - it.tmin);
+    const int slot = clamp_bucket((int)tmp);
+    const F4 bmn = a.tri_bmin[g], bmx = a.tri_bmax[g];
+    // lanes of the warp that land in the same bucket combine first (match.any + redux.sync): one atomic per word and
+    // group instead of seven per triangle -- count / min / max are order-free, so the bucket contents are the same bits
+    const CvGroup grp = cv_group_by(it.bin_slot * kBuckets + slot);
+    cv_group_add_i32(grp, &b.count[slot], 1);
+    cv_group_min_u32(grp, &b.mn[slot][0], ordered_key(bmn.x));
+    cv_group_min_u32(grp, &b.mn[slot][1], ordered_key(bmn.y));
+    cv_group_min_u32(grp, &b.mn[slot][2], ordered_key(bmn.z));
+    cv_group_max_u32(grp, &b.mx[slot][0], ordered_key(bmx.x));
+    cv_group_max_u32(grp, &b.mx[slot][1], ordered_key(bmx.y));
+    cv_group_max_u32(grp, &b.mx[slot][2], ordered_key(bmx.z));
+}
 CV_D void body_bin(const BuildArrays& a, int i) {
     if (i >= a.n_tris) return;
     const int w = a.node_of[i];
     if (w < 0) return;
     const BuildItem& it = a.items[w];
     if (it.kind != ITEM_SAH) return;
-    const int g = a.order[i];
-    const F4 c = a.tri_centroid[g];
-    const float cv = it.axis == 0 ? c.x : (it.axis == 1 ? c.y : c.z);
-    const float tmp = cv_div((cv - it.tmin) * (float)kBuckets, it.tmax - it.tmin);
-    const int slot = clamp_bucket((int)tmp);
-    ItemBins& b = a.bins[it.bin_slot];
-    cv_atomic_add_i32(&b.count[slot], 1);
-    const F4 bmn = a.tri_bmin[g], bmx = a.tri_bmax[g];
-    cv_atomic_min_u32(&b.mn[slot][0], ordered_key(bmn.x));
-    cv_atomic_min_u32(&b.mn[slot][1], ordered_key(bmn.y));
-    cv_atomic_min_u32(&b.mn[slot][2], ordered_key(bmn.z));
-    cv_atomic_max_u32(&b.mx[slot][0], ordered_key(bmx.x));
-    cv_atomic_max_u32(&b.mx[slot][1], ordered_key(bmx.y));
-    cv_atomic_max_u32(&b.mx[slot][2], ordered_key(bmx.z));
+    body_bin_to(a, i, it, a.bins[it.bin_slot]);
 }
 
 // ---- per SAH item: the 11 candidate costs and the first strict minimum (:171-196) ---

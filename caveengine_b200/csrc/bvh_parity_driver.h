@@ -7,6 +7,7 @@
 //   void upload(void* dst, const void* src, size_t bytes);
 //   void download(void* dst, const void* src, size_t bytes);   // synchronises
 //   void fill(void* dst, int byte, size_t bytes);
+//   void parity_reduce(const BuildArrays&); void parity_bin(const BuildArrays&);   // body_reduce / body_bin over all triangles
 #pragma once
 #include <stddef.h>
 
@@ -86,9 +87,9 @@ int build_bvh_parity(Exec& ex, BuildArrays a, const int* tri_off_host, const int
     ex.upload(a.counters, counters, sizeof(counters));
     while (n_items > 0) {
         ex.launch(n_items, FnInitAccum{ a, n_items });
-        ex.launch(a.n_tris, FnReduce{ a });
+        ex.parity_reduce(a);
         ex.launch(n_items, FnNode{ a, n_items });
-        ex.launch(a.n_tris, FnBin{ a });
+        ex.parity_bin(a);
         ex.launch(n_items, FnSplit{ a, n_items });
         ex.launch(a.n_tris, FnFlag{ a });
         ex.scan_u8(a.flags, a.scan, a.n_tris);

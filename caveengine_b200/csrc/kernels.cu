@@ -227,6 +227,80 @@ void CudaExec::sort_pairs(uint32_t* keys, int* vals, uint32_t* keys_tmp, int* va
     }
 }
 
+// ---- parity builder: the two per-triangle passes with atomics (bvh_parity_body.h body_reduce / body_bin are the
+//      per-element statements).  At the upper levels every triangle of a block belongs to the same item: the block folds
+//      into a private copy in shared memory and flushes it with one atomic per word, instead of every warp hitting the
+//      item's accumulator (a 262k-triangle mesh: 8192 warps x 18 atomics on the same 18 words).  Min / max / add are
+//      order-free: same bits out.  A block that straddles items runs the per-element body.
+__global__ void __launch_bounds__(256) k_parity_reduce(const BuildArrays a) {
+    __shared__ ItemAccum s_acc;
+    const int tid = threadIdx.x, i = blockIdx.x * 256 + tid;
+    const int w0 = a.node_of[blockIdx.x * 256];
+    const int w = i < a.n_tris ? a.node_of[i] : w0;
+    if (!__syncthreads_and(w == w0)) {
+        body_reduce(a, i);
+        return;
+    }
+    if (w0 < 0) return;
+    if (tid < 3) {
+        s_acc.mn[tid] = ~0ull;
+        s_acc.mx[tid] = 0ull;
+        s_acc.cmn[tid] = 0xffffffffu;
+        s_acc.cmx[tid] = 0u;
+    }
+    __syncthreads();
+    if (i < a.n_tris) body_reduce_to(a, i, w0, s_acc);
+    __syncthreads();
+    ItemAccum& acc = a.accum[w0];
+    if (tid < 3) atomicMin(&acc.mn[tid], s_acc.mn[tid]);
+    else if (tid < 6) atomicMax(&acc.mx[tid - 3], s_acc.mx[tid - 3]);
+    else if (tid < 9) atomicMin(&acc.cmn[tid - 6], s_acc.cmn[tid - 6]);
+    else if (tid < 12) atomicMax(&acc.cmx[tid - 9], s_acc.cmx[tid - 9]);
+}
+void CudaExec::parity_reduce(const BuildArrays& a) {
+    if (a.n_tris <= 0) return;
+    k_parity_reduce<<<(a.n_tris + 255) / 256, 256, 0, stream>>>(a);
+    note(cudaGetLastError());
+    ++launches;
+}
+__global__ void __launch_bounds__(256) k_parity_bin(const BuildArrays a) {
+    __shared__ ItemBins s_bins;
+    const int tid = threadIdx.x, i = blockIdx.x * 256 + tid;
+    const int w0 = a.node_of[blockIdx.x * 256];
+    const int w = i < a.n_tris ? a.node_of[i] : w0;
+    if (!__syncthreads_and(w == w0)) {
+        body_bin(a, i);
+        return;
+    }
+    if (w0 < 0) return;
+    const BuildItem& it = a.items[w0];
+    if (it.kind != ITEM_SAH) return;
+    if (tid < kBuckets) {
+        s_bins.count[tid] = 0;
+        for (int c = 0; c < 3; ++c) {
+            s_bins.mn[tid][c] = 0xffffffffu;
+            s_bins.mx[tid][c] = 0u;
+        }
+    }
+    __syncthreads();
+    if (i < a.n_tris) body_bin_to(a, i, it, s_bins);
+    __syncthreads();
+    if (tid < kBuckets && s_bins.count[tid] > 0) {
+        ItemBins& b = a.bins[it.bin_slot];
+        atomicAdd(&b.count[tid], s_bins.count[tid]);
+        for (int c = 0; c < 3; ++c) {
+            atomicMin(&b.mn[tid][c], s_bins.mn[tid][c]);
+            atomicMax(&b.mx[tid][c], s_bins.mx[tid][c]);
+        }
+    }
+}
+void CudaExec::parity_bin(const BuildArrays& a) {
+    if (a.n_tris <= 0) return;
+    k_parity_bin<<<(a.n_tris + 255) / 256, 256, 0, stream>>>(a);
+    note(cudaGetLastError());
+    ++launches;
+}
+
 // ---- prim pass of the production builders: per-block reduction of the 12 bounds, then 12
 //      atomics per block (the generic per-index body would issue 12 per warp on the same words)
 __global__ void __launch_bounds__(256) k_wb_prim(const WBuild b) {

@@ -41,6 +41,8 @@ struct EmuExec {
         for (int i = 0; i < n; ++i) { keys[i] = v[i].first; vals[i] = v[i].second; }
     }
     void wb_prim(const WBuild& b) { launch(b.n_prims, FnWbPrim{ b }); }
+    void parity_reduce(const BuildArrays& a) { launch(a.n_tris, FnReduce{ a }); }
+    void parity_bin(const BuildArrays& a) { launch(a.n_tris, FnBin{ a }); }
     void wb_bin(const WBuild& b) { launch(b.n_prims, FnWbBin{ b }); }
     void wb_split(const WBuild& b, int level, int bound) { launch(bound, FnWbSplit{ b, level, true }); }
     void wb_subtrees(const WBuild& b, int n_roots) {

@@ -143,6 +143,7 @@ ABI = [
     ("cavept_group_gather_bands", C.c_int, [_P, C.c_int]),
     ("cavept_measure_gather", C.c_int, [_P, C.c_size_t, C.c_int, C.POINTER(C.c_double)]),
     ("cavept_sort_pairs", C.c_int, [_P, _P, _P, C.c_int, C.c_int]),
+    ("cavept_sort_pairs_static", C.c_int, [_P, _P, _P, C.c_int, C.c_int]),
     ("cavept_host_alloc", _P, [C.c_size_t]),
     ("cavept_host_free", None, [_P]),
     ("cavept_probe_intersections", C.c_int, [_P, C.c_int, _P, _P, _P, _P]),
@@ -600,6 +601,14 @@ class PathTracer:
         """Device radix sort of (uint32 key, int32 value) pairs, in place (stable)."""
         assert keys.dtype == np.uint32 and values.dtype == np.int32 and keys.flags.c_contiguous and values.flags.c_contiguous and keys.size == values.size
         self._check(self._lib.cavept_sort_pairs(self._ctx, keys.ctypes.data, values.ctypes.data, int(keys.size), int(key_bits)))
+
+    STATIC_SORT_MAX_PAIRS = 1 << 20  # CAVEPT_STATIC_SORT_MAX_PAIRS
+
+    def sort_pairs_static(self, d_keys: int, d_values: int, count: int, key_bits: int = 32):
+        """cavept_sort_pairs_static: the same sort on DEVICE arrays (addresses), in place, asynchronous on the context's
+        stream, with no allocation -- its scratch is a static device array in the library.  count is limited to
+        STATIC_SORT_MAX_PAIRS; calls that overlap on one GPU race on the shared scratch."""
+        self._check(self._lib.cavept_sort_pairs_static(self._ctx, C.c_void_p(int(d_keys)), C.c_void_p(int(d_values)), int(count), int(key_bits)))
 
     def probe_intersections(self, rays: np.ndarray, triangles: np.ndarray, boxes: np.ndarray) -> np.ndarray:
         """cavept_probe_intersections: (n,7) rays, (n,9) triangles, (n,6) boxes -> (n,8) results."""

@@ -8,7 +8,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libcavept.so")
-SOURCES = ["kernels.cu", "cavept_api.cu", "cavept_group.cu", "scene_ingest.cpp"]
+SOURCES = ["kernels.cu", "cavept_api.cu", "cavept_group.cu", "cavept_static.cu", "scene_ingest.cpp"]
 HEADERS = ["cv_common.h", "bvh_parity_body.h", "bvh_parity_driver.h", "wbvh_body.h", "trace_body.h", "trace_pool_body.h", "host_math.h", "kernels.h", "cavept_ctx.h", "../../include/cavept.h"]
 
 NVCC_FLAGS = [f"-D{d}" for d in os.environ.get("CAVEPT_DEFINES", "").split()] + [

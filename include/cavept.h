@@ -308,6 +308,18 @@ CAVEPT_API int cavept_measure_gather(cavept_ctx* ctx, size_t working_set_bytes, 
  * sorted on the device by the low `key_bits` of the keys, copied back): stable, so the result is
  * defined bit for bit.  Exposed so the sort can be checked on its own at full size. */
 CAVEPT_API int cavept_sort_pairs(cavept_ctx* ctx, uint32_t* keys, int32_t* values, int count, int key_bits);
+/* The same sort for callers that cannot allocate device memory (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * `d_keys` / `d_values` are DEVICE arrays of `count` entries, sorted in place, asynchronously on the context's stream
+ * (cavept_sync, or order your own work behind cavept_stream).  The call allocates nothing: its scratch (ping-pong
+ * buffers, digit histograms, scan sums) is one static __device__ array of about 8.5 MB inside the library, held by every
+ * GPU that loads the library until the process exits.  count > CAVEPT_STATIC_SORT_MAX_PAIRS returns
+ * CAVEPT_ERR_CAPACITY (cavept_last_error says so).  Every call on a GPU shares that array: calls that overlap on the GPU
+ * (different streams / contexts / threads) race on it -- serialise them.  Nothing in the array needs to start at zero;
+ * each pass overwrites what it reads, so back-to-back calls of different sizes are independent.  Same result, bit for
+ * bit, as cavept_sort_pairs (csrc/cavept_static.cu). */
+#define CAVEPT_STATIC_SORT_MAX_PAIRS (1 << 20)
+CAVEPT_API int cavept_sort_pairs_static(cavept_ctx* ctx, uint32_t* d_keys, int32_t* d_values, int count, int key_bits);
 
 /* ---- asset ingest: the engine's own files -> the flat arrays of
  *      cavept_upload_scene.  Host-side parsing only; nothing here touches the device.

@@ -31,6 +31,10 @@ namespace cavept {
 constexpr int kBuckets = 12;     // BUCKED_MAX, bvh_accel.cpp:144
 constexpr int kMaxDepth = 64;    // :117
 constexpr float kBoxMinSize = 0.0001f;  // Box::BOX_MIN_SIZE, cave/engine/math/box.h:12
+#ifndef CV_PARITY_SUB_MAX
+#define CV_PARITY_SUB_MAX 1024
+#endif
+constexpr int kParitySubMax = CV_PARITY_SUB_MAX;  // an item of at most this many triangles leaves the level loop: one thread block builds its whole subtree (parity_subtree_*)
 
 enum { ITEM_LEAF = 0, ITEM_SMALL = 1, ITEM_SAH = 2 };
 enum { BUILD_ERR_DEPTH = 1, BUILD_ERR_EMPTY_SIDE = 2, BUILD_ERR_BAD_AREA = 4, BUILD_ERR_BINS = 8 };
@@ -46,7 +50,8 @@ struct BuildItem {
     float tmin, tmax, parent_sa;
     int split;
     int n_left;
-    int child_slot;    // index of the left child's item in the next level (right = +1)
+    int child_slot;    // index of the left child's item in the next level, or -1: that child left the level loop (queued subtree root)
+    int child_slot_r;  // the same for the right child
     int bin_slot;
     int tri_offset;    // first scene-global triangle of this item's mesh (AppendBvhs offset)
 };
@@ -82,8 +87,13 @@ struct BuildArrays {
     BuildItem* items_next;
     ItemAccum* accum;
     ItemBins* bins;
-    int* counters;     // [0] next-level item count, [1] bin slots used, [2] error bits
+    int* counters;     // [0] next-level item count, [1] bin slots used, [2] error bits, [3] subtree roots queued, [4] deepest level a subtree build reached + 1
     int bins_capacity;
+    // second phase (parity_subtree_*): children of at most sub_max triangles are queued here instead of entering the next
+    // level; null inside a subtree build and when the phase is switched off
+    BuildItem* sub_roots;
+    int sub_capacity;
+    int sub_max;
     // outputs
     GpuPtBvh* nodes;
     int* node_parent;  // per node: parent slot (scene-global), or -1 - m for the root of mesh m
@@ -164,10 +174,11 @@ CV_D void body_init_accum(const BuildArrays& a, int w, int n_items) {
 // ---- per element: fold vertices into the item's AABB and centroid box ---------------
 // `acc` is the item's accumulator, or a block's private copy of it (kernels.cu k_parity_reduce): the folds are min / max
 // of keys, so where they are combined does not change the result
-CV_D void body_reduce_to(const BuildArrays& a, int i, int w, ItemAccum& acc) {
+// the element's own fold operands: (value, position, sign) keys of its three vertices per axis, already folded over
+// the three, and the ordered keys of its centroid
+CV_D void body_element_keys(const BuildArrays& a, int i, unsigned long long kmn[3], unsigned long long kmx[3], uint32_t ck[3]) {
     const int g = a.order[i];
     const int* t = a.indices[g].tri;
-    unsigned long long kmn[3], kmx[3];
     for (int k = 0; k < 3; ++k) {
         const F3 p = load_pos(a.vertices, t[k]);
         const uint32_t pos = (uint32_t)i * 3u + (uint32_t)k;
@@ -181,19 +192,25 @@ CV_D void body_reduce_to(const BuildArrays& a, int i, int w, ItemAccum& acc) {
             kmx[0] = x0 > kmx[0] ? x0 : kmx[0]; kmx[1] = x1 > kmx[1] ? x1 : kmx[1]; kmx[2] = x2 > kmx[2] ? x2 : kmx[2];
         }
     }
+    const F4 c = a.tri_centroid[g];
+    ck[0] = ordered_key(c.x);
+    ck[1] = ordered_key(c.y);
+    ck[2] = ordered_key(c.z);
+}
+CV_D void body_reduce_to(const BuildArrays& a, int i, int w, ItemAccum& acc) {
+    unsigned long long kmn[3], kmx[3];
+    uint32_t ck[3];
+    body_element_keys(a, i, kmn, kmx, ck);
     // lanes of the warp that fold into the same node combine first (top levels: all 32 hit one node)
     const CvGroup grp = cv_group_by(w);
     for (int k = 0; k < 3; ++k) {
         cv_group_min_u64(grp, &acc.mn[k], kmn[k]);
         cv_group_max_u64(grp, &acc.mx[k], kmx[k]);
     }
-    const F4 c = a.tri_centroid[g];
-    cv_group_min_u32(grp, &acc.cmn[0], ordered_key(c.x));
-    cv_group_min_u32(grp, &acc.cmn[1], ordered_key(c.y));
-    cv_group_min_u32(grp, &acc.cmn[2], ordered_key(c.z));
-    cv_group_max_u32(grp, &acc.cmx[0], ordered_key(c.x));
-    cv_group_max_u32(grp, &acc.cmx[1], ordered_key(c.y));
-    cv_group_max_u32(grp, &acc.cmx[2], ordered_key(c.z));
+    for (int k = 0; k < 3; ++k) {
+        cv_group_min_u32(grp, &acc.cmn[k], ck[k]);
+        cv_group_max_u32(grp, &acc.cmx[k], ck[k]);
+    }
 }
 CV_D void body_reduce(const BuildArrays& a, int i) {
     if (i >= a.n_tris) return;
@@ -293,12 +310,17 @@ CV_HD int clamp_bucket(int s) { return s < 0 ? 0 : (s > kBuckets - 1 ? kBuckets 
 
 // ---- per element of SAH items: bucket counts and boxes (:162-169) -------------------
 // `b` is the item's bucket record, or a block's private copy of it (kernels.cu k_parity_bin)
-CV_D void body_bin_to(const BuildArrays& a, int i, const BuildItem& it, ItemBins& b) {
-    const int g = a.order[i];
+// the bucket of element i of a bucketed item, first slot formula (:162-169), and its triangle
+CV_D int body_bin_slot(const BuildArrays& a, int i, const BuildItem& it, int& g) {
+    g = a.order[i];
     const F4 c = a.tri_centroid[g];
     const float cv = it.axis == 0 ? c.x : (it.axis == 1 ? c.y : c.z);
     const float tmp = cv_div((cv - it.tmin) * (float)kBuckets, it.tmax - it.tmin);
-    const int slot = clamp_bucket((int)tmp);
+    return clamp_bucket((int)tmp);
+}
+CV_D void body_bin_to(const BuildArrays& a, int i, const BuildItem& it, ItemBins& b) {
+    int g;
+    const int slot = body_bin_slot(a, i, it, g);
     const F4 bmn = a.tri_bmin[g], bmx = a.tri_bmax[g];
     // lanes of the warp that land in the same bucket combine first (match.any + redux.sync): one atomic per word and
     // group instead of seven per triangle -- count / min / max are order-free, so the bucket contents are the same bits
@@ -321,40 +343,56 @@ CV_D void body_bin(const BuildArrays& a, int i) {
 }
 
 // ---- per SAH item: the 11 candidate costs and the first strict minimum (:171-196) ---
+// Cost of splitting after bucket i (:173-193): both sides folded in bucket order.  Every word of the record is read
+// first and every index below is static once unrolled, so the record lives in registers: read bucket by bucket between
+// stores to a local array, each load waited for the store before it (84 dependent round trips to L2 per item).
+CV_D float body_split_cost(const ItemBins& src, int i, float parent_sa) {
+    ItemBins b;
+    {
+        constexpr int kWords = (int)(sizeof(ItemBins) / sizeof(uint32_t));
+        const uint32_t* in = reinterpret_cast<const uint32_t*>(&src);
+        uint32_t* out = reinterpret_cast<uint32_t*>(&b);
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+        for (int q = 0; q < kWords; ++q) out[q] = in[q];
+    }
+    F3 mn0 = f3(CV_INF, CV_INF, CV_INF), mx0 = f3(-CV_INF, -CV_INF, -CV_INF);
+    F3 mn1 = mn0, mx1 = mx0;
+    int c0 = 0, c1 = 0;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+    for (int j = 0; j < kBuckets; ++j) {
+        const int cnt = b.count[j];
+        // an untouched bucket decodes to (+inf, -inf) == Box::MakeInvalid (box.h:19-22)
+        F3 bmn = f3(ordered_value(b.mn[j][0]), ordered_value(b.mn[j][1]), ordered_value(b.mn[j][2]));
+        F3 bmx = f3(ordered_value(b.mx[j][0]), ordered_value(b.mx[j][1]), ordered_value(b.mx[j][2]));
+        if (cnt == 0) {
+            bmn = f3(CV_INF, CV_INF, CV_INF);
+            bmx = f3(-CV_INF, -CV_INF, -CV_INF);
+        }
+        if (j <= i) {
+            mn0 = f3(min_ref(mn0.x, bmn.x), min_ref(mn0.y, bmn.y), min_ref(mn0.z, bmn.z));
+            mx0 = f3(max_ref(mx0.x, bmx.x), max_ref(mx0.y, bmx.y), max_ref(mx0.z, bmx.z));
+            c0 += cnt;
+        } else {
+            mn1 = f3(min_ref(mn1.x, bmn.x), min_ref(mn1.y, bmn.y), min_ref(mn1.z, bmn.z));
+            mx1 = f3(max_ref(mx1.x, bmx.x), max_ref(mx1.y, bmx.y), max_ref(mx1.z, bmx.z));
+            c1 += cnt;
+        }
+    }
+    return 0.125f + cv_div((float)c0 * surface_area(mn0, mx0) + (float)c1 * surface_area(mn1, mx1), parent_sa);
+}
 CV_D void body_split(const BuildArrays& a, int w, int n_items) {
     if (w >= n_items) return;
     BuildItem& it = a.items[w];
     if (it.kind != ITEM_SAH) return;
     const ItemBins& b = a.bins[it.bin_slot];
-    F3 bmn[kBuckets], bmx[kBuckets];
-    int cnt[kBuckets];
-    for (int k = 0; k < kBuckets; ++k) {
-        cnt[k] = b.count[k];
-        // an untouched bucket decodes to (+inf, -inf) == Box::MakeInvalid (box.h:19-22)
-        bmn[k] = f3(ordered_value(b.mn[k][0]), ordered_value(b.mn[k][1]), ordered_value(b.mn[k][2]));
-        bmx[k] = f3(ordered_value(b.mx[k][0]), ordered_value(b.mx[k][1]), ordered_value(b.mx[k][2]));
-        if (cnt[k] == 0) {
-            bmn[k] = f3(CV_INF, CV_INF, CV_INF);
-            bmx[k] = f3(-CV_INF, -CV_INF, -CV_INF);
-        }
-    }
     int split = 0;
     float best = 0.0f;
     for (int i = 0; i < kBuckets - 1; ++i) {
-        F3 mn0 = f3(CV_INF, CV_INF, CV_INF), mx0 = f3(-CV_INF, -CV_INF, -CV_INF);
-        F3 mn1 = mn0, mx1 = mx0;
-        int c0 = 0, c1 = 0;
-        for (int j = 0; j <= i; ++j) {
-            mn0 = f3(min_ref(mn0.x, bmn[j].x), min_ref(mn0.y, bmn[j].y), min_ref(mn0.z, bmn[j].z));
-            mx0 = f3(max_ref(mx0.x, bmx[j].x), max_ref(mx0.y, bmx[j].y), max_ref(mx0.z, bmx[j].z));
-            c0 += cnt[j];
-        }
-        for (int j = i + 1; j < kBuckets; ++j) {
-            mn1 = f3(min_ref(mn1.x, bmn[j].x), min_ref(mn1.y, bmn[j].y), min_ref(mn1.z, bmn[j].z));
-            mx1 = f3(max_ref(mx1.x, bmx[j].x), max_ref(mx1.y, bmx[j].y), max_ref(mx1.z, bmx[j].z));
-            c1 += cnt[j];
-        }
-        const float cost = 0.125f + cv_div((float)c0 * surface_area(mn0, mx0) + (float)c1 * surface_area(mn1, mx1), it.parent_sa);
+        const float cost = body_split_cost(b, i, it.parent_sa);
         if (i == 0 || cost < best) {
             split = i;
             best = cost;
@@ -401,8 +439,6 @@ CV_D void body_children(const BuildArrays& a, int w, int n_items) {
         it.kind = ITEM_LEAF;
         return;
     }
-    const int slot = cv_atomic_add_i32(&a.counters[0], 2);
-    it.child_slot = slot;
     BuildItem l, r;
     l.start = it.start;
     l.count = n_left;
@@ -418,10 +454,32 @@ CV_D void body_children(const BuildArrays& a, int w, int n_items) {
     l.axis = r.axis = 0;
     l.tmin = r.tmin = l.tmax = r.tmax = l.parent_sa = r.parent_sa = 0.0f;
     l.split = r.split = l.n_left = r.n_left = 0;
-    l.child_slot = r.child_slot = l.bin_slot = r.bin_slot = -1;
+    l.child_slot = r.child_slot = l.child_slot_r = r.child_slot_r = l.bin_slot = r.bin_slot = -1;
     l.tri_offset = r.tri_offset = it.tri_offset;
-    a.items_next[slot] = l;
-    a.items_next[slot + 1] = r;
+    // a child small enough to be a closed problem for one thread block leaves the level loop (its elements are parked:
+    // node_of = -1, carried along by body_scatter until the subtree phase picks the range up)
+    const bool queue_l = a.sub_roots && l.count <= a.sub_max, queue_r = a.sub_roots && r.count <= a.sub_max;
+    int n_queued = (queue_l ? 1 : 0) + (queue_r ? 1 : 0);
+    if (n_queued) {
+        int q = cv_atomic_add_i32(&a.counters[3], n_queued);
+        if (q + n_queued > a.sub_capacity) {
+            cv_atomic_or_i32(&a.counters[2], BUILD_ERR_BINS);
+            it.kind = ITEM_LEAF;
+            return;
+        }
+        if (queue_l) a.sub_roots[q++] = l;
+        if (queue_r) a.sub_roots[q] = r;
+    }
+    int slot = n_queued < 2 ? cv_atomic_add_i32(&a.counters[0], 2 - n_queued) : 0;
+    it.child_slot = it.child_slot_r = -1;
+    if (!queue_l) {
+        it.child_slot = slot;
+        a.items_next[slot++] = l;
+    }
+    if (!queue_r) {
+        it.child_slot_r = slot;
+        a.items_next[slot] = r;
+    }
 }
 
 // ---- per element: stable partition into the children's segments --------------------
@@ -446,10 +504,81 @@ CV_D void body_scatter(const BuildArrays& a, int i) {
         child = it.child_slot;
     } else {
         dst = it.start + it.n_left + ((i - it.start) - lefts_before);
-        child = it.child_slot + 1;
+        child = it.child_slot_r;
     }
     a.order_next[dst] = a.order[i];
     a.node_of_next[dst] = child;
+}
+
+// ---- second phase: subtree builds ---------------------------------------------------------------------------------
+// An item of at most sub_max triangles is a closed problem: its elements are one contiguous range of `order` that
+// nothing else touches, its nodes one contiguous range of slots.  One thread block runs the SAME per-element / per-item
+// passes over that range, level after level, with block barriers in place of kernel boundaries (kernels.cu
+// k_parity_subtrees), so the deepest ~15 levels of every tree cost one launch instead of eleven each.  Same passes,
+// same operands, order-free folds: same bytes.  Scratch: by then the level loop's item / accumulator / bucket arrays
+// are dead, and each root owns the slice of them its element range addresses -- items and accumulators
+// [start, start + count) (a level has at most `count` items), buckets [ceil(start / 5), +floor(count / 5)) (a bucketed
+// item has at least 5 triangles).  `counters` and `scan_base` are the block's own (scan_base[i] is addressed with the
+// global element index i in [start, start + count]).
+constexpr int kParityCounters = 5;
+CV_HD void parity_subtree_view(const BuildArrays& ga, const BuildItem& root, BuildArrays& b, int* counters, int* scan_base) {
+    b = ga;
+    b.sub_roots = nullptr;
+    b.items = ga.items + root.start;
+    b.items_next = ga.items_next + root.start;
+    b.accum = ga.accum + root.start;
+    b.bins = ga.bins + (root.start + 4) / 5;
+    b.bins_capacity = root.count / 5;
+    b.counters = counters;
+    b.scan = scan_base;
+}
+// one thread: the root becomes item 0 of the private level 0
+CV_D void parity_subtree_setup(const BuildArrays& b, const BuildItem& root) {
+    b.items[0] = root;
+    b.counters[0] = 0;
+    b.counters[1] = 0;
+    b.counters[2] = 0;
+}
+// after a subtree's last level (one thread): error bits and depth into the global counters
+CV_D void parity_subtree_account(const BuildArrays& ga, const BuildItem& root, int levels, int error_bits) {
+    if (error_bits) cv_atomic_or_i32(&ga.counters[2], error_bits);
+    cv_atomic_max_i32(&ga.counters[4], root.depth + levels);
+}
+// the serial statement (emulator); the device runs k_parity_subtrees, one block per root, same passes
+CV_D void parity_subtree_serial(const BuildArrays& ga, int r) {
+    const BuildItem root = ga.sub_roots[r];
+    int counters[kParityCounters] = { 0, 0, 0, 0, 0 };
+    BuildArrays b;
+    parity_subtree_view(ga, root, b, counters, ga.scan);  // subtrees run one after the other here: the global scan array serves each in turn
+    parity_subtree_setup(b, root);
+    const int start = root.start, end = root.start + root.count;
+    for (int i = start; i < end; ++i) b.node_of[i] = 0;
+    int n_items = 1, levels = 0;
+    while (n_items > 0) {
+        for (int w = 0; w < n_items; ++w) body_init_accum(b, w, n_items);
+        for (int i = start; i < end; ++i) body_reduce(b, i);
+        for (int w = 0; w < n_items; ++w) body_node(b, w, n_items);
+        for (int i = start; i < end; ++i) body_bin(b, i);
+        for (int w = 0; w < n_items; ++w) body_split(b, w, n_items);
+        int run = 0;
+        for (int i = start; i < end; ++i) {
+            body_flag(b, i);
+            b.scan[i] = run;
+            run += b.flags[i];
+        }
+        b.scan[end] = run;
+        for (int w = 0; w < n_items; ++w) body_children(b, w, n_items);
+        for (int i = start; i < end; ++i) body_scatter(b, i);
+        ++levels;
+        n_items = counters[0];
+        counters[0] = 0;
+        counters[1] = 0;
+        BuildItem* ti = b.items; b.items = b.items_next; b.items_next = ti;
+        int* to = b.order; b.order = b.order_next; b.order_next = to;
+        int* tn = b.node_of; b.node_of = b.node_of_next; b.node_of_next = tn;
+        if (counters[2] != 0 || root.depth + levels > kMaxDepth + 2) break;
+    }
+    parity_subtree_account(ga, root, levels, counters[2] | (n_items > 0 && counters[2] == 0 ? BUILD_ERR_DEPTH : 0));
 }
 
 }  // namespace cavept

@@ -8,6 +8,7 @@
 //   void download(void* dst, const void* src, size_t bytes);   // synchronises
 //   void fill(void* dst, int byte, size_t bytes);
 //   void parity_reduce(const BuildArrays&); void parity_bin(const BuildArrays&);   // body_reduce / body_bin over all triangles
+//   void parity_subtrees(const BuildArrays&, int n_roots);     // second phase: one block (or the serial statement) per queued root
 #pragma once
 #include <stddef.h>
 
@@ -48,7 +49,7 @@ struct BuildReport {
 };
 
 template<class T>
-inline void swap_ptr(T*& x, T*& y) {
+CV_HD void swap_ptr(T*& x, T*& y) {
     T* t = x;
     x = y;
     y = t;
@@ -77,13 +78,13 @@ int build_bvh_parity(Exec& ex, BuildArrays a, const int* tri_off_host, const int
         r.axis = 0;
         r.tmin = r.tmax = r.parent_sa = 0.0f;
         r.split = r.n_left = 0;
-        r.child_slot = r.bin_slot = -1;
+        r.child_slot = r.child_slot_r = r.bin_slot = -1;
         r.tri_offset = tri_off_host[m];
         host_items_scratch[m] = r;
     }
     ex.upload(a.items, host_items_scratch, sizeof(BuildItem) * (size_t)n_meshes);
     int n_items = n_meshes;
-    int counters[3] = { 0, 0, 0 };
+    int counters[kParityCounters] = { 0, 0, 0, 0, 0 };
     ex.upload(a.counters, counters, sizeof(counters));
     while (n_items > 0) {
         ex.launch(n_items, FnInitAccum{ a, n_items });
@@ -104,12 +105,23 @@ int build_bvh_parity(Exec& ex, BuildArrays a, const int* tri_off_host, const int
         n_items = counters[0];
         counters[0] = 0;
         counters[1] = 0;
-        ex.upload(a.counters, counters, sizeof(counters));
+        ex.upload(a.counters, counters, 2 * sizeof(int));
         swap_ptr(a.items, a.items_next);
         swap_ptr(a.order, a.order_next);
         swap_ptr(a.node_of, a.node_of_next);
         if (report->levels > kMaxDepth + 2) {
             report->error_bits = BUILD_ERR_DEPTH;
+            return -1;
+        }
+    }
+    // second phase: every queued item's whole subtree in one launch (a.order is the buffer the last level scattered into)
+    const int n_roots = counters[3];
+    if (n_roots > 0) {
+        ex.parity_subtrees(a, n_roots);
+        ex.download(counters, a.counters, sizeof(counters));
+        if (counters[4] > report->levels) report->levels = counters[4];
+        if (counters[2] != 0) {
+            report->error_bits = counters[2];
             return -1;
         }
     }

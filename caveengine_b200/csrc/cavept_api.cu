@@ -302,11 +302,12 @@ int build_all(cavept_ctx* ctx) {
     CU(ctx, ctx->d_flags.reserve(T));
     CU(ctx, ctx->d_scan.reserve((size_t)std::max(T, n_nodes) + 1));
     CU(ctx, ctx->d_scan_tmp.reserve((size_t)std::max(T, n_nodes) / kScanTile + 4));
-    CU(ctx, ctx->d_counters.reserve(4));
+    CU(ctx, ctx->d_counters.reserve(8));
     CU(ctx, ctx->d_items.reserve(items_cap));
     CU(ctx, ctx->d_items_next.reserve(items_cap));
     CU(ctx, ctx->d_accum_items.reserve(items_cap));
     CU(ctx, ctx->d_bins.reserve(bins_cap));
+    CU(ctx, ctx->d_sub_items.reserve(items_cap));
     CU(ctx, ctx->d_nodes.reserve(n_nodes));
     CU(ctx, ctx->d_node_parent.reserve(n_nodes));
     CU(ctx, ctx->d_node_count.reserve(n_nodes));
@@ -331,6 +332,9 @@ int build_all(cavept_ctx* ctx) {
     a.bins = ctx->d_bins.ptr;
     a.counters = ctx->d_counters.ptr;
     a.bins_capacity = (int)bins_cap;
+    a.sub_roots = ctx->d_sub_items.ptr;
+    a.sub_capacity = (int)items_cap;
+    a.sub_max = kParitySubMax;
     a.nodes = ctx->d_nodes.ptr;
     a.node_parent = ctx->d_node_parent.ptr;
     a.node_count = ctx->d_node_count.ptr;
@@ -409,7 +413,7 @@ CAVEPT_API void cavept_destroy(cavept_ctx* ctx) {
     ctx->d_tri_bmin.release(); ctx->d_tri_bmax.release(); ctx->d_tri_centroid.release();
     ctx->d_order.release(); ctx->d_order_next.release(); ctx->d_node_of.release(); ctx->d_node_of_next.release();
     ctx->d_scan.release(); ctx->d_scan_tmp.release(); ctx->d_counters.release(); ctx->d_flags.release();
-    ctx->d_items.release(); ctx->d_items_next.release(); ctx->d_accum_items.release(); ctx->d_bins.release();
+    ctx->d_items.release(); ctx->d_items_next.release(); ctx->d_sub_items.release(); ctx->d_accum_items.release(); ctx->d_bins.release();
     ctx->d_node_parent.release(); ctx->d_node_count.release();
     ctx->d_accum.release(); ctx->d_tone.release(); ctx->d_tone8.release(); ctx->d_stats.release(); ctx->d_job_counter.release();
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);

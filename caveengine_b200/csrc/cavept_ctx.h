@@ -135,7 +135,7 @@ struct cavept_ctx {
     DevBuf<F4> d_tri_bmin, d_tri_bmax, d_tri_centroid;
     DevBuf<int> d_order, d_order_next, d_node_of, d_node_of_next, d_scan, d_scan_tmp, d_counters;
     DevBuf<unsigned char> d_flags;
-    DevBuf<BuildItem> d_items, d_items_next;
+    DevBuf<BuildItem> d_items, d_items_next, d_sub_items;  // d_sub_items: roots queued for the parity builder's subtree phase
     DevBuf<ItemAccum> d_accum_items;
     DevBuf<ItemBins> d_bins;
     DevBuf<int> d_node_parent, d_node_count;

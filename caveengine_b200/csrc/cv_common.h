@@ -253,6 +253,13 @@ CV_D void cv_atomic_or_i32(int* p, int v) {
     *p |= v;
 #endif
 }
+CV_D void cv_atomic_max_i32(int* p, int v) {
+#if defined(__CUDA_ARCH__)
+    atomicMax(p, v);
+#else
+    if (v > *p) *p = v;
+#endif
+}
 CV_D void cv_atomic_add_u64(unsigned long long* p, unsigned long long v) {
 #if defined(__CUDA_ARCH__)
     atomicAdd(p, v);

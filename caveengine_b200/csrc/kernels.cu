@@ -1,6 +1,9 @@
 // __global__ wrappers for the kernel bodies, the scan primitive, and launchers.
 // Compiled for sm_100a only, with -fmad=false (see cv_common.h on float semantics).
 #include "kernels.h"
+#ifdef CV_PARITY_SUB_PROFILE
+#include <cstdio>
+#endif
 
 #include <cuda_fp16.h>
 
@@ -297,6 +300,215 @@ __global__ void __launch_bounds__(256) k_parity_bin(const BuildArrays a) {
 void CudaExec::parity_bin(const BuildArrays& a) {
     if (a.n_tris <= 0) return;
     k_parity_bin<<<(a.n_tris + 255) / 256, 256, 0, stream>>>(a);
+    note(cudaGetLastError());
+    ++launches;
+}
+
+// ---- parity builder, second phase: one block builds the whole subtree of each queued item (bvh_parity_body.h
+//      parity_subtree_serial is the serial statement the emulator runs).  The passes are the level loop's own bodies over
+//      the block's element range and its private slices of the item / accumulator / bucket arrays, with __syncthreads()
+//      where the level loop has kernel boundaries; the "goes left" scan is block-local in shared memory.
+#ifndef CV_PARITY_SUB_THREADS
+#define CV_PARITY_SUB_THREADS 256
+#endif
+constexpr int kParSubThreads = CV_PARITY_SUB_THREADS;
+#ifndef CV_PARITY_SUB_MINBLOCKS
+#define CV_PARITY_SUB_MINBLOCKS 3
+#endif
+// The fold pass of a subtree build.  Elements of an item are contiguous in `order`, so a warp's lanes fold by a segmented
+// shuffle scan (five steps, no divergence however many items the warp straddles) and the last lane of each segment sends
+// the atomics -- body_reduce's match.any groups would run one after the other, up to 32 per warp at the deep levels.
+// Same operands, order-free min / max: same accumulator bits.
+__device__ __forceinline__ void par_sub_reduce(const BuildArrays& b, int start, int end, int tid, int lane) {
+    for (int base = start; base < end; base += kParSubThreads) {
+        const int i = base + tid;
+        const int w = i < end ? b.node_of[i] : -1;
+        unsigned long long kmn[3] = { ~0ull, ~0ull, ~0ull }, kmx[3] = { 0ull, 0ull, 0ull };
+        uint32_t cmn[3] = { 0xffffffffu, 0xffffffffu, 0xffffffffu }, cmx[3] = { 0u, 0u, 0u };
+        if (w >= 0) {
+            uint32_t ck[3];
+            body_element_keys(b, i, kmn, kmx, ck);
+#pragma unroll
+            for (int k = 0; k < 3; ++k) cmn[k] = cmx[k] = ck[k];
+        }
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const int wo = __shfl_up_sync(0xffffffffu, w, d);
+            const bool take = lane >= d && wo == w;
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                const unsigned long long on = __shfl_up_sync(0xffffffffu, kmn[k], d), ox = __shfl_up_sync(0xffffffffu, kmx[k], d);
+                const uint32_t cn = __shfl_up_sync(0xffffffffu, cmn[k], d), cx = __shfl_up_sync(0xffffffffu, cmx[k], d);
+                if (take) {
+                    kmn[k] = on < kmn[k] ? on : kmn[k];
+                    kmx[k] = ox > kmx[k] ? ox : kmx[k];
+                    cmn[k] = cn < cmn[k] ? cn : cmn[k];
+                    cmx[k] = cx > cmx[k] ? cx : cmx[k];
+                }
+            }
+        }
+        const int wn = __shfl_down_sync(0xffffffffu, w, 1);
+        if (w >= 0 && (lane == 31 || wn != w)) {
+            ItemAccum& acc = b.accum[w];
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                atomicMin(&acc.mn[k], kmn[k]);
+                atomicMax(&acc.mx[k], kmx[k]);
+                atomicMin(&acc.cmn[k], cmn[k]);
+                atomicMax(&acc.cmx[k], cmx[k]);
+            }
+        }
+    }
+}
+// The bucket pass of a subtree build: one atomic per word and element, no grouping -- inside a subtree at most sub_max / 12
+// elements meet on a word, and the lanes of a warp scatter over up to 12 buckets per item (grouping them runs the groups
+// one after the other).  count / min / max are order-free: same bucket bits.
+__device__ __forceinline__ void par_sub_bin(const BuildArrays& b, int start, int end, int tid) {
+    for (int i = start + tid; i < end; i += kParSubThreads) {
+        const int w = b.node_of[i];
+        if (w < 0) continue;
+        const BuildItem& it = b.items[w];
+        if (it.kind != ITEM_SAH) continue;
+        int g;
+        const int slot = body_bin_slot(b, i, it, g);
+        const F4 bmn = b.tri_bmin[g], bmx = b.tri_bmax[g];
+        ItemBins& bb = b.bins[it.bin_slot];
+        atomicAdd(&bb.count[slot], 1);
+        atomicMin(&bb.mn[slot][0], ordered_key(bmn.x));
+        atomicMin(&bb.mn[slot][1], ordered_key(bmn.y));
+        atomicMin(&bb.mn[slot][2], ordered_key(bmn.z));
+        atomicMax(&bb.mx[slot][0], ordered_key(bmx.x));
+        atomicMax(&bb.mx[slot][1], ordered_key(bmx.y));
+        atomicMax(&bb.mx[slot][2], ordered_key(bmx.z));
+    }
+}
+// The split pass of a subtree build: sixteen lanes per item, lane i < 11 prices candidate i exactly as body_split does
+// (both sides folded in bucket order), then every lane repeats the serial selection over the eleven costs (first
+// strict minimum, :190-193).
+// `list` holds the level's bucketed items (most items of the deep levels are not: one look per thread finds them).
+__device__ __forceinline__ void par_sub_split(const BuildArrays& b, const int* list, int n_list, int tid, int lane) {
+    const unsigned hmask = 0xffffu << (lane & 16);
+    const int sub = lane & 15;
+    for (int q = tid >> 4; q < n_list; q += kParSubThreads / 16) {
+        BuildItem& it = b.items[list[q]];
+        float cost = 0.0f;
+        if (sub < kBuckets - 1) cost = body_split_cost(b.bins[it.bin_slot], sub, it.parent_sa);
+        int split = 0;
+        float best = 0.0f;
+#pragma unroll
+        for (int i = 0; i < kBuckets - 1; ++i) {
+            const float c = __shfl_sync(hmask, cost, (lane & 16) + i);
+            if (i == 0 || c < best) {
+                split = i;
+                best = c;
+            }
+        }
+        if (sub == 0) it.split = split;
+    }
+}
+__global__ void __launch_bounds__(kParSubThreads, CV_PARITY_SUB_MINBLOCKS) k_parity_subtrees(const BuildArrays ga, int n_roots) {
+    __shared__ int s_scan[kParitySubMax + 1];
+    __shared__ int s_counters[kParityCounters];
+    __shared__ int s_warp[kParSubThreads / 32];
+    __shared__ int s_list[kParitySubMax / 5 + 1], s_n_list;  // the level's bucketed items (each has at least 5 triangles)
+    const int r = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (r >= n_roots) return;
+    const BuildItem root = ga.sub_roots[r];
+    const int start = root.start, n = root.count, end = start + n;
+    BuildArrays b;
+    parity_subtree_view(ga, root, b, s_counters, s_scan - start);
+    if (tid == 0) {
+        parity_subtree_setup(b, root);
+        s_n_list = 0;
+    }
+    for (int i = start + tid; i < end; i += kParSubThreads) b.node_of[i] = 0;
+    __syncthreads();
+    const int per = (n + kParSubThreads - 1) / kParSubThreads;
+    const int j0 = min(tid * per, n), j1 = min(j0 + per, n);
+    int n_items = 1, levels = 0, err = 0;
+#ifdef CV_PARITY_SUB_PROFILE
+    long long ph[9] = { 0 }, t0 = clock64(), t1;
+#define PH(k) t1 = clock64(); ph[k] += t1 - t0; t0 = t1;
+#else
+#define PH(k)
+#endif
+    while (n_items > 0) {
+        for (int w = tid; w < n_items; w += kParSubThreads) body_init_accum(b, w, n_items);
+        __syncthreads();
+        PH(0)
+        par_sub_reduce(b, start, end, tid, lane);
+        __syncthreads();
+        PH(1)
+        for (int w = tid; w < n_items; w += kParSubThreads) body_node(b, w, n_items);
+        __syncthreads();
+        PH(2)
+        par_sub_bin(b, start, end, tid);
+        __syncthreads();
+        PH(3)
+        for (int w = tid; w < n_items; w += kParSubThreads) {
+            if (b.items[w].kind == ITEM_SAH) s_list[atomicAdd(&s_n_list, 1)] = w;
+        }
+        __syncthreads();
+        par_sub_split(b, s_list, s_n_list, tid, lane);
+        __syncthreads();
+        PH(4)
+        {  // flags of a thread's contiguous chunk, then the exclusive scan over the block's range
+            int sum = 0;
+            for (int j = j0; j < j1; ++j) {
+                body_flag(b, start + j);
+                sum += b.flags[start + j];
+            }
+            int inc = sum;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const int v = __shfl_up_sync(0xffffffffu, inc, d);
+                if (lane >= d) inc += v;
+            }
+            if (lane == 31) s_warp[warp] = inc;
+            __syncthreads();
+        PH(5)
+            int base = 0;
+            for (int k = 0; k < warp; ++k) base += s_warp[k];
+            int run = base + inc - sum;
+            for (int j = j0; j < j1; ++j) {
+                s_scan[j] = run;
+                run += b.flags[start + j];
+            }
+            if (tid == kParSubThreads - 1) s_scan[n] = base + inc;
+        }
+        __syncthreads();
+        PH(6)
+        for (int w = tid; w < n_items; w += kParSubThreads) body_children(b, w, n_items);
+        __syncthreads();
+        PH(7)
+        for (int i = start + tid; i < end; i += kParSubThreads) body_scatter(b, i);
+        __syncthreads();
+        PH(8)
+        ++levels;
+        n_items = s_counters[0];
+        err = s_counters[2];
+        __syncthreads();
+        PH(8)
+        if (tid == 0) {
+            s_counters[0] = 0;
+            s_counters[1] = 0;
+            s_n_list = 0;
+        }
+        swap_ptr(b.items, b.items_next);
+        swap_ptr(b.order, b.order_next);
+        swap_ptr(b.node_of, b.node_of_next);
+        if (err != 0 || root.depth + levels > kMaxDepth + 2) break;
+        __syncthreads();
+        PH(8)
+    }
+#ifdef CV_PARITY_SUB_PROFILE
+    if (tid == 0 && (r % 64) == 0) printf("root %d n %d levels %d cycles init %lld reduce %lld node %lld bin %lld split %lld flag %lld scan %lld children %lld scatter+ %lld\n", r, n, levels, ph[0], ph[1], ph[2], ph[3], ph[4], ph[5], ph[6], ph[7], ph[8]);
+#endif
+    if (tid == 0) parity_subtree_account(ga, root, levels, err | ((n_items > 0 && err == 0) ? BUILD_ERR_DEPTH : 0));
+}
+void CudaExec::parity_subtrees(const BuildArrays& a, int n_roots) {
+    if (n_roots <= 0) return;
+    k_parity_subtrees<<<n_roots, kParSubThreads, 0, stream>>>(a, n_roots);
     note(cudaGetLastError());
     ++launches;
 }

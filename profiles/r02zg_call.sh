@@ -1,0 +1,9 @@
+#!/bin/bash
+# GPU call r02zg: parity builder, bucket records loaded in one batch before the split: phases, default build + two variants
+mkdir -p gpurun_out
+bash profiles/r02zd_call.sh | tail -7
+timeout 300 python profiles/probe_parity_build.py --check >> gpurun_out/r02zg_parity_build.jsonl 2>>gpurun_out/r02zg_err.log; echo "default rc=$?"
+for i in 1 2; do
+  CAVEPT_VARIANT="$(cat variants/lib_$i.txt)" CAVEPT_LIBRARY=$PWD/variants/lib_$i.so timeout 300 python profiles/probe_parity_build.py --check >> gpurun_out/r02zg_parity_build.jsonl 2>>gpurun_out/r02zg_err.log; echo "variant $i rc=$?"
+done
+cut -c1-175 gpurun_out/r02zg_parity_build.jsonl; grep -c '"bytes_equal_reference": true' gpurun_out/r02zg_parity_build.jsonl; tail -5 gpurun_out/r02zg_err.log

@@ -43,6 +43,10 @@ struct EmuExec {
     void wb_prim(const WBuild& b) { launch(b.n_prims, FnWbPrim{ b }); }
     void parity_reduce(const BuildArrays& a) { launch(a.n_tris, FnReduce{ a }); }
     void parity_bin(const BuildArrays& a) { launch(a.n_tris, FnBin{ a }); }
+    void parity_subtrees(const BuildArrays& a, int n_roots) {
+        for (int r = 0; r < n_roots; ++r) parity_subtree_serial(a, r);
+        ++launches;
+    }
     void wb_bin(const WBuild& b) { launch(b.n_prims, FnWbBin{ b }); }
     void wb_split(const WBuild& b, int level, int bound) { launch(bound, FnWbSplit{ b, level, true }); }
     void wb_subtrees(const WBuild& b, int n_roots) {
@@ -61,6 +65,10 @@ struct EmuExec {
 
 #define EMU_API extern "C" __attribute__((visibility("default")))
 
+// Largest item the parity builder's subtree phase takes (0 = level loop only); tests build both ways.
+static int g_parity_sub_max = kParitySubMax;
+EMU_API void emu_set_parity_sub_max(int n) { g_parity_sub_max = n < 0 ? kParitySubMax : n; }
+
 // Builds the scene-global GpuPtBvh array for meshes whose triangles occupy
 // [tri_off[m], tri_off[m+1]) of `indices` (vertex ids already scene-global).
 // Also returns per-node parent / subtree-count arrays.  rc 0 ok, -1 degenerate.
@@ -68,10 +76,10 @@ EMU_API int emu_bvh_build(const GpuPtVertex* vertices, const GpuPtIndex* indices
                           int* out_parent, int* out_count, int* out_levels, int* out_error_bits) {
     const int n_nodes = 2 * n_tris - n_meshes;
     std::vector<F4> bmin(n_tris), bmax(n_tris), cent(n_tris);
-    std::vector<int> order(n_tris), order_next(n_tris), node_of(n_tris), node_of_next(n_tris), scan(n_tris + 1), counters(4);
+    std::vector<int> order(n_tris), order_next(n_tris), node_of(n_tris), node_of_next(n_tris), scan(n_tris + 1), counters(8);
     std::vector<unsigned char> flags(n_tris);
     const size_t items_cap = (size_t)std::max(n_tris, n_meshes) + 2;
-    std::vector<BuildItem> items(items_cap), items_next(items_cap), scratch(n_meshes);
+    std::vector<BuildItem> items(items_cap), items_next(items_cap), scratch(n_meshes), sub_roots(items_cap);
     std::vector<ItemAccum> accum(items_cap);
     const int bins_cap = n_tris / 5 + n_meshes + 2;
     std::vector<ItemBins> bins(bins_cap);
@@ -94,6 +102,9 @@ EMU_API int emu_bvh_build(const GpuPtVertex* vertices, const GpuPtIndex* indices
     a.bins = bins.data();
     a.counters = counters.data();
     a.bins_capacity = bins_cap;
+    a.sub_roots = g_parity_sub_max > 0 ? sub_roots.data() : nullptr;
+    a.sub_capacity = (int)items_cap;
+    a.sub_max = g_parity_sub_max;
     a.nodes = out_nodes;
     a.node_parent = out_parent;
     a.node_count = out_count;

@@ -56,10 +56,13 @@ class EmuScene:
     """Runs the product's build pipeline (parity BVH + production world-space BVH) in emulation
     on the scene-global arrays of an oracle-assembled scene."""
 
-    def __init__(self, asm, scene):
+    def __init__(self, asm, scene, parity_sub_max=None):
+        """parity_sub_max: largest item the parity builder hands to its subtree phase (None = the product's constant,
+        0 = level loop only)."""
         from oracle import oracle as O
 
         self.lib = load()
+        self.lib.emu_set_parity_sub_max(C.c_int(-1 if parity_sub_max is None else int(parity_sub_max)))
         self.asm = asm
         built = []  # input mesh ids in first-appearance order
         for inst in scene.instances:

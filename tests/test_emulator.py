@@ -24,6 +24,26 @@ def test_level_synchronous_builder_is_bit_exact_vs_reference_golden(port_oracle)
         assert emu.nodes.tobytes() == g[f"{name}/nodes"].tobytes(), f"{name}: differs from the reference builder"
 
 
+@pytest.mark.parametrize("sub_max", [0, 1, 7, 64, 100_000])
+def test_subtree_phase_of_the_parity_builder_emits_the_same_bytes(port_oracle, scene_cache, sub_max):
+    """The parity builder's second phase (one block per queued item, bvh_parity_body.h parity_subtree_*) at several
+    hand-over sizes -- level loop only, hand-over at 1 / 7 / 64 triangles, every root's children at once -- against the
+    reference builder's bytes: golden meshes (signed zeros, ties, <= 4-triangle nodes) and a multi-mesh scene."""
+    g = H.load_golden("bvh_golden.npz")
+    for name in H.golden_cases(g):
+        mesh = scenes.Mesh(g[f"{name}/positions"], np.zeros_like(g[f"{name}/positions"]), g[f"{name}/indices"])
+        sc = _single_mesh_scene(mesh)
+        emu = E.EmuScene(port_oracle.assemble(sc), sc, parity_sub_max=sub_max)
+        assert emu.rc == 0, name
+        assert emu.nodes.tobytes() == g[f"{name}/nodes"].tobytes(), f"{name}: differs from the reference builder at sub_max={sub_max}"
+    sc = scene_cache("heightfield")
+    asm = port_oracle.assemble(sc)
+    emu = E.EmuScene(asm, sc, parity_sub_max=sub_max)
+    assert emu.rc == 0 and emu.nodes.tobytes() == asm.bvhs.tobytes()
+    ref = E.EmuScene(asm, sc, parity_sub_max=0)
+    assert np.array_equal(emu.parent, ref.parent) and np.array_equal(emu.count, ref.count)
+
+
 @pytest.mark.parametrize("name", ["tiny", "cornell", "heightfield"])
 def test_multi_mesh_build_matches_oracle_assembly(port_oracle, scene_cache, name):
     sc = scene_cache(name)

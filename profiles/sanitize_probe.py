@@ -36,4 +36,24 @@ with cb.PathTracer(64, 36, 5, trace_mode=cb.TraceMode.REFERENCE_WALK) as pt:
     pt.set_camera(sc.camera)
     pt.render(0, 1, sync=True)
     print("walk mean", float(pt.read_accum()[..., :3].mean()))
+# parity builder with both phases (level loop + one block per item of <= 1024 triangles) on a 10,000-triangle mesh
+hf = scenes.heightfield_scene()
+with cb.PathTracer(32, 18, 2, bvh_mode=cb.BvhMode.PARITY) as pt:
+    pt.set_mode(cb.PathTracerMode.INTERACTIVE)
+    pt.upload_scene(hf)
+    st = pt.stats()
+    print("heightfield parity build: levels", st["build_levels"], "launches", st["build_launches"], "nodes", st["node_count"])
+    # the radix sort, allocating and static-scratch entry points
+    import torch
+
+    rng = np.random.default_rng(1)
+    keys = rng.integers(0, 1 << 30, size=20_000, dtype=np.uint64).astype(np.uint32)
+    vals = np.arange(keys.size, dtype=np.int32)
+    k1, v1 = keys.copy(), vals.copy()
+    pt.sort_pairs(k1, v1, 30)
+    dk, dv = torch.from_numpy(keys.view(np.int32).copy()).cuda(), torch.from_numpy(vals.copy()).cuda()
+    torch.cuda.synchronize()
+    pt.sort_pairs_static(dk.data_ptr(), dv.data_ptr(), keys.size, 30)
+    pt.sync()
+    print("static sort equal", bool(np.array_equal(dv.cpu().numpy(), v1)))
 print("SANITIZE_PROBE_DONE")

@@ -309,11 +309,11 @@ void CudaExec::parity_bin(const BuildArrays& a) {
 //      the block's element range and its private slices of the item / accumulator / bucket arrays, with __syncthreads()
 //      where the level loop has kernel boundaries; the "goes left" scan is block-local in shared memory.
 #ifndef CV_PARITY_SUB_THREADS
-#define CV_PARITY_SUB_THREADS 256
+#define CV_PARITY_SUB_THREADS 512
 #endif
 constexpr int kParSubThreads = CV_PARITY_SUB_THREADS;
 #ifndef CV_PARITY_SUB_MINBLOCKS
-#define CV_PARITY_SUB_MINBLOCKS 3
+#define CV_PARITY_SUB_MINBLOCKS 2
 #endif
 // The fold pass of a subtree build.  Elements of an item are contiguous in `order`, so a warp's lanes fold by a segmented
 // shuffle scan (five steps, no divergence however many items the warp straddles) and the last lane of each segment sends
@@ -382,22 +382,52 @@ __device__ __forceinline__ void par_sub_bin(const BuildArrays& b, int start, int
         atomicMax(&bb.mx[slot][2], ordered_key(bmx.z));
     }
 }
-// The split pass of a subtree build: sixteen lanes per item, lane i < 11 prices candidate i exactly as body_split does
-// (both sides folded in bucket order), then every lane repeats the serial selection over the eleven costs (first
-// strict minimum, :190-193).
+// The split pass of a subtree build: sixteen lanes per item.  Lane j < 12 holds bucket j of the item's record (seven
+// words); the buckets are passed round by shuffle in bucket order and lane i < 11 folds bucket j into the left side of
+// candidate i when j <= i, else into its right side -- the folds of body_split_cost in the same order with the same
+// operands (same cost bits), without every lane holding the whole 84-word record in registers.  Then every lane repeats
+// the serial selection over the eleven costs (first strict minimum, :190-193).
 // `list` holds the level's bucketed items (most items of the deep levels are not: one look per thread finds them).
 __device__ __forceinline__ void par_sub_split(const BuildArrays& b, const int* list, int n_list, int tid, int lane) {
     const unsigned hmask = 0xffffu << (lane & 16);
-    const int sub = lane & 15;
+    const int sub = lane & 15, half = lane & 16;
     for (int q = tid >> 4; q < n_list; q += kParSubThreads / 16) {
         BuildItem& it = b.items[list[q]];
-        float cost = 0.0f;
-        if (sub < kBuckets - 1) cost = body_split_cost(b.bins[it.bin_slot], sub, it.parent_sa);
+        const ItemBins& rec = b.bins[it.bin_slot];
+        int cnt = 0;
+        F3 bmn = f3(CV_INF, CV_INF, CV_INF), bmx = f3(-CV_INF, -CV_INF, -CV_INF);
+        if (sub < kBuckets) {
+            cnt = rec.count[sub];
+            if (cnt != 0) {  // an untouched bucket decodes to (+inf, -inf) == Box::MakeInvalid (box.h:19-22)
+                bmn = f3(ordered_value(rec.mn[sub][0]), ordered_value(rec.mn[sub][1]), ordered_value(rec.mn[sub][2]));
+                bmx = f3(ordered_value(rec.mx[sub][0]), ordered_value(rec.mx[sub][1]), ordered_value(rec.mx[sub][2]));
+            }
+        }
+        F3 mn0 = f3(CV_INF, CV_INF, CV_INF), mx0 = f3(-CV_INF, -CV_INF, -CV_INF);
+        F3 mn1 = mn0, mx1 = mx0;
+        int c0 = 0, c1 = 0;
+#pragma unroll
+        for (int j = 0; j < kBuckets; ++j) {
+            const int src = half + j;
+            const int cj = __shfl_sync(hmask, cnt, src);
+            const F3 nj = f3(__shfl_sync(hmask, bmn.x, src), __shfl_sync(hmask, bmn.y, src), __shfl_sync(hmask, bmn.z, src));
+            const F3 xj = f3(__shfl_sync(hmask, bmx.x, src), __shfl_sync(hmask, bmx.y, src), __shfl_sync(hmask, bmx.z, src));
+            if (j <= sub) {
+                mn0 = f3(min_ref(mn0.x, nj.x), min_ref(mn0.y, nj.y), min_ref(mn0.z, nj.z));
+                mx0 = f3(max_ref(mx0.x, xj.x), max_ref(mx0.y, xj.y), max_ref(mx0.z, xj.z));
+                c0 += cj;
+            } else {
+                mn1 = f3(min_ref(mn1.x, nj.x), min_ref(mn1.y, nj.y), min_ref(mn1.z, nj.z));
+                mx1 = f3(max_ref(mx1.x, xj.x), max_ref(mx1.y, xj.y), max_ref(mx1.z, xj.z));
+                c1 += cj;
+            }
+        }
+        const float cost = 0.125f + cv_div((float)c0 * surface_area(mn0, mx0) + (float)c1 * surface_area(mn1, mx1), it.parent_sa);
         int split = 0;
         float best = 0.0f;
 #pragma unroll
         for (int i = 0; i < kBuckets - 1; ++i) {
-            const float c = __shfl_sync(hmask, cost, (lane & 16) + i);
+            const float c = __shfl_sync(hmask, cost, half + i);
             if (i == 0 || c < best) {
                 split = i;
                 best = c;

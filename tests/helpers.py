@@ -68,6 +68,28 @@ def coincident_centroid_mesh(n=6):
     return scenes.Mesh(pos, np.tile(np.array([0, 0, 1], dtype=np.float32), (3 * n, 1)), idx)
 
 
+def grid_with_coincident_cluster(n_grid=40, n_cluster=6):
+    """A regular grid of 2 * n_grid^2 well-separated triangles plus, far away, a cluster of > 4 triangles with identical
+    centroids: the first splits are fine, the degenerate set surfaces only several levels down -- inside the parity
+    builder's subtree phase (one block per item of <= 1024 triangles), which has to report it like the level loop does."""
+    from caveengine_b200 import scenes
+
+    pos, idx = [], []
+    for j in range(n_grid):
+        for i in range(n_grid):
+            x, z = float(i), float(j)
+            base = len(pos)
+            pos += [[x, 0, z], [x + 0.9, 0, z], [x, 0, z + 0.9], [x + 0.9, 0.1, z + 0.9]]
+            idx += [base, base + 1, base + 2, base + 1, base + 3, base + 2]
+    tri = np.array([[1000, 0, 0], [1001, 0, 0], [1000, 1, 0]], dtype=np.float32)
+    for _ in range(n_cluster):
+        base = len(pos)
+        pos += tri.tolist()
+        idx += [base, base + 1, base + 2]
+    pos = np.array(pos, dtype=np.float32)
+    return scenes.Mesh(pos, np.tile(np.array([0, 1, 0], dtype=np.float32), (pos.shape[0], 1)), np.array(idx, dtype=np.uint32))
+
+
 def isect_golden_inputs():
     """Inputs of isect_golden.npz in the probe's layout: rays (n,7) = origin, direction = end - start
     (fp32, as TestIntersection computes it), t = 1 (Ray::m_dist's initial value)."""

@@ -71,6 +71,28 @@ def test_degenerate_geometry_reports_error(port_oracle):
     assert emu.rc != 0 and emu.error_bits != 0
 
 
+@pytest.mark.parametrize("sub_max", [0, 64, 1024])
+def test_degenerate_cluster_deep_in_a_mesh_reports_error_from_either_phase(port_oracle, sub_max):
+    """The coincident-centroid set sits several levels down: with sub_max >= 64 it is met inside a subtree build."""
+    sc = _single_mesh_scene(H.grid_with_coincident_cluster())
+    mesh = sc.meshes[0]
+    asm_v = np.zeros(mesh.positions.shape[0], dtype=port_oracle.assemble.__globals__["VERTEX_DT"])
+    asm_v["position"] = mesh.positions
+    asm_i = np.zeros(mesh.indices.size // 3, dtype=port_oracle.assemble.__globals__["INDEX_DT"])
+    asm_i["tri"] = mesh.indices.reshape(-1, 3)
+
+    class Asm:  # the oracle refuses to assemble this mesh (its builder reports the same degenerate set)
+        vertices, indices, meshes, materials = asm_v, asm_i, None, None
+
+    with pytest.raises(ValueError):
+        port_oracle.assemble(sc)
+    emu = E.EmuScene(Asm, sc, parity_sub_max=sub_max)
+    assert emu.rc != 0 and (emu.error_bits & 2), (emu.rc, emu.error_bits)  # BUILD_ERR_EMPTY_SIDE
+    ok = _single_mesh_scene(H.grid_with_coincident_cluster(n_cluster=4))  # <= 4 triangles: SplitByAxis, no buckets, fine
+    emu = E.EmuScene(port_oracle.assemble(ok), ok, parity_sub_max=sub_max)
+    assert emu.rc == 0
+
+
 @pytest.mark.parametrize("name", ["tiny_mb5", "cornell_mb5", "tiny_mb8", "tiny_mb1"])
 @pytest.mark.parametrize("fast", [False, True])
 def test_traversals_match_reference_golden_images(name, fast):

@@ -124,6 +124,24 @@ def test_degenerate_geometry_is_an_error_not_a_trap(api):
     pt.close()
 
 
+def test_degenerate_cluster_deep_in_a_mesh_is_an_error_from_the_subtree_phase(api, best_oracle):
+    """> 4 coincident centroids that surface only inside the parity builder's second phase (a block builds the subtree):
+    same error code; with 4 such triangles (SplitByAxis) the build succeeds and equals the reference's bytes."""
+    def scene(n_cluster):
+        return scenes.Scene("cluster", [H.grid_with_coincident_cluster(n_cluster=n_cluster)], [scenes.Instance(0, 0, scenes.mat_identity())],
+                            [scenes.Material((0.5, 0.5, 0.5), 0.5, 0.0, 0.0)], scenes.look_at((20, 30, -30), (20, 0, 20)))
+
+    pt = api.PathTracer(32, 18, 5, device=0)
+    with pytest.raises(api.CaveptError) as e:
+        pt.upload_scene(scene(6))
+    assert e.value.code == 2 and "empty-split-side" in str(e.value)
+    assert not pt.is_active()
+    ok = scene(4)
+    pt.upload_scene(ok)  # the context recovers
+    assert pt.get_scene_arrays()["bvhs"].tobytes() == best_oracle.assemble(ok).bvhs.tobytes()
+    pt.close()
+
+
 # ---- images ------------------------------------------------------------------------------------
 @pytest.mark.parametrize("name,mb,frames", [("tiny", 5, (0, 4)), ("cornell", 5, (7, 3)), ("heightfield", 5, (0, 2)), ("sponza", 8, (0, 2))])
 @pytest.mark.parametrize("mode", ["REFERENCE_WALK", "FAST"])

@@ -90,6 +90,39 @@ def grid_with_coincident_cluster(n_grid=40, n_cluster=6):
     return scenes.Mesh(pos, np.tile(np.array([0, 1, 0], dtype=np.float32), (pos.shape[0], 1)), np.array(idx, dtype=np.uint32))
 
 
+def random_mesh(seed, n_tris):
+    """Seeded triangle soup for builder fuzzing: a few clusters of small triangles of random size, a tenth of them
+    axis-aligned (zero-extent boxes: the MakeValid padding), coordinates snapped to a coarse lattice so that equal keys,
+    equal centroids components and +0 / -0 turn up; never > 4 identical centroids (the reference traps on those)."""
+    from caveengine_b200 import scenes
+
+    rng = np.random.default_rng(seed)
+    n_clusters = int(rng.integers(1, 6))
+    centres = rng.uniform(-20, 20, size=(n_clusters, 3))
+    c = centres[rng.integers(0, n_clusters, size=n_tris)] + rng.normal(0, 3.0, size=(n_tris, 3))
+    size = rng.uniform(0.05, 1.5, size=(n_tris, 1, 1))
+    tri = c[:, None, :] + rng.normal(0, 1.0, size=(n_tris, 3, 3)) * size
+    flat = rng.random(n_tris) < 0.1
+    axis = rng.integers(0, 3, size=n_tris)
+    for k in np.nonzero(flat)[0]:
+        tri[k, :, axis[k]] = tri[k, 0, axis[k]]
+    tri = np.round(tri * 8.0) / 8.0  # lattice: ties and exact zeros
+    neg = rng.random(tri.shape) < 0.05
+    tri = np.where((tri == 0.0) & neg, -0.0, tri).astype(np.float32)
+    # de-duplicate centroids so no set of > 4 triangles shares one (nudge repeats along x by distinct lattice steps)
+    cent = np.round(tri.mean(axis=1) * 24.0).astype(np.int64)
+    _, inv, counts = np.unique(cent, axis=0, return_inverse=True, return_counts=True)
+    seen = {}
+    for k in range(n_tris):
+        j = int(inv[k])
+        r = seen.get(j, 0)
+        seen[j] = r + 1
+        if r >= 3:
+            tri[k, :, 0] += np.float32(0.375 * (r - 2) + 50.0 * (1 + j % 7))
+    pos = tri.reshape(-1, 3).astype(np.float32)
+    return scenes.Mesh(pos, np.tile(np.array([0, 1, 0], dtype=np.float32), (pos.shape[0], 1)), np.arange(pos.shape[0], dtype=np.uint32))
+
+
 def isect_golden_inputs():
     """Inputs of isect_golden.npz in the probe's layout: rays (n,7) = origin, direction = end - start
     (fp32, as TestIntersection computes it), t = 1 (Ray::m_dist's initial value)."""

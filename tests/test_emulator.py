@@ -71,6 +71,20 @@ def test_degenerate_geometry_reports_error(port_oracle):
     assert emu.rc != 0 and emu.error_bits != 0
 
 
+@pytest.mark.parametrize("sub_max", [0, 16, 1024])
+def test_random_meshes_build_to_the_reference_bytes_in_both_phases(best_oracle, sub_max):
+    """Seeded triangle soups (clusters, zero-extent boxes, lattice ties, signed zeros; 1 .. 3000 triangles) through the
+    level loop only, a hand-over at 16 triangles and the product's hand-over: the reference builder's bytes each time."""
+    for seed in range(80):
+        n = [1, 2, 5, 17, 100, 700, 1500, 3000, 2049, 1025][seed % 10]
+        mesh = H.random_mesh(seed, n)
+        sc = _single_mesh_scene(mesh)
+        want = best_oracle.bvh_build(mesh.indices, mesh.positions)
+        emu = E.EmuScene(best_oracle.assemble(sc), sc, parity_sub_max=sub_max)
+        assert emu.rc == 0, (seed, n)
+        assert emu.nodes.tobytes() == want.tobytes(), f"seed {seed} ({n} triangles), sub_max {sub_max}"
+
+
 @pytest.mark.parametrize("sub_max", [0, 64, 1024])
 def test_degenerate_cluster_deep_in_a_mesh_reports_error_from_either_phase(port_oracle, sub_max):
     """The coincident-centroid set sits several levels down: with sub_max >= 64 it is met inside a subtree build."""

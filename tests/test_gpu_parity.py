@@ -124,6 +124,20 @@ def test_degenerate_geometry_is_an_error_not_a_trap(api):
     pt.close()
 
 
+def test_bvh_bit_exact_on_random_meshes(api, best_oracle):
+    """Thirty seeded triangle soups (1 .. 3000 triangles: clusters, zero-extent boxes, lattice ties, signed zeros) as ONE
+    scene of thirty meshes, so the level loop and the subtree phase both see many items of every size at once: every
+    mesh's GpuPtBvh array equals the reference builder's, byte for byte."""
+    meshes = [H.random_mesh(seed, [1, 2, 5, 17, 100, 700, 1500, 3000, 2049, 1025][seed % 10]) for seed in range(30)]
+    sc = scenes.Scene("soup", meshes, [scenes.Instance(m, 0, scenes.mat_identity()) for m in range(len(meshes))], [scenes.Material((0.5, 0.5, 0.5), 0.5, 0.0, 0.0)],
+                      scenes.look_at((0, 30, -60), (0, 0, 0)))
+    with _tracer(api, sc, 32, 18, 5, api.TraceMode.FAST) as pt:
+        for m, mesh in enumerate(meshes):
+            want = best_oracle.bvh_build(mesh.indices, mesh.positions)
+            got = pt.get_mesh_bvh(m, mesh.n_tris)
+            assert got.shape == want.shape and got.tobytes() == want.tobytes(), f"mesh {m} ({mesh.n_tris} triangles)"
+
+
 def test_degenerate_cluster_deep_in_a_mesh_is_an_error_from_the_subtree_phase(api, best_oracle):
     """> 4 coincident centroids that surface only inside the parity builder's second phase (a block builds the subtree):
     same error code; with 4 such triangles (SplitByAxis) the build succeeds and equals the reference's bytes."""

@@ -220,10 +220,17 @@ CV_D void body_reduce(const BuildArrays& a, int i) {
 }
 
 // ---- per item: write the node, classify (:128-142), prepare the SAH pass ------------
+// The item and its accumulator are copied in first and the item is written back once: through the references every field
+// read had to wait for the store before it (the compiler cannot tell the arrays apart), a chain of L2 round trips.
+CV_D void body_node_of(const BuildArrays& a, BuildItem& it, const ItemAccum& acc);
 CV_D void body_node(const BuildArrays& a, int w, int n_items) {
     if (w >= n_items) return;
-    BuildItem& it = a.items[w];
-    const ItemAccum& acc = a.accum[w];
+    BuildItem it = a.items[w];
+    const ItemAccum acc = a.accum[w];
+    body_node_of(a, it, acc);
+    a.items[w] = it;
+}
+CV_D void body_node_of(const BuildArrays& a, BuildItem& it, const ItemAccum& acc) {
     F3 mn = f3(key_value(acc.mn[0]), key_value(acc.mn[1]), key_value(acc.mn[2]));
     F3 mx = f3(key_value(acc.mx[0]), key_value(acc.mx[1]), key_value(acc.mx[2]));
     make_valid(mn, mx);
@@ -257,24 +264,44 @@ CV_D void body_node(const BuildArrays& a, int w, int n_items) {
         if (!(parent_sa > 0.0f)) cv_atomic_or_i32(&a.counters[2], BUILD_ERR_BAD_AREA);
         const int axis = dominant_axis(mn, mx);
         // libstdc++ std::sort on < 16 elements is a (stable) insertion sort; key = AABB centre (:38-55)
-        int ids[4];
-        float keys[4];
+        // (every index below is static once unrolled: keys and ids stay in registers and the loads go out together)
+        int ids[4] = { 0, 0, 0, 0 };
+        float keys[4] = { 0.0f, 0.0f, 0.0f, 0.0f };
         const int n = it.count <= 4 ? it.count : 4;
-        for (int k = 0; k < n; ++k) {
-            const int g = a.order[it.start + k];
-            const F4 bmn = a.tri_bmin[g], bmx = a.tri_bmax[g];
-            const F3 center = 0.5f * (f3(bmn.x, bmn.y, bmn.z) + f3(bmx.x, bmx.y, bmx.z));
-            const float key = comp(center, axis);
-            int j = k - 1;
-            while (j >= 0 && key < keys[j]) {
-                keys[j + 1] = keys[j];
-                ids[j + 1] = ids[j];
-                --j;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+        for (int k = 0; k < 4; ++k) {
+            if (k < n) {
+                const int g = a.order[it.start + k];
+                const F4 bmn = a.tri_bmin[g], bmx = a.tri_bmax[g];
+                const F3 center = 0.5f * (f3(bmn.x, bmn.y, bmn.z) + f3(bmx.x, bmx.y, bmx.z));
+                ids[k] = g;
+                keys[k] = comp(center, axis);
             }
-            keys[j + 1] = key;
-            ids[j + 1] = g;
         }
-        for (int k = 0; k < n; ++k) a.order[it.start + k] = ids[k];
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+        for (int k = 1; k < 4; ++k) {  // insert element k into the sorted prefix: it moves down while it is strictly smaller
+            bool moving = k < n;
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+            for (int j = k - 1; j >= 0; --j) {
+                moving = moving && keys[j + 1] < keys[j];
+                if (moving) {
+                    const float tk = keys[j]; keys[j] = keys[j + 1]; keys[j + 1] = tk;
+                    const int ti = ids[j]; ids[j] = ids[j + 1]; ids[j + 1] = ti;
+                }
+            }
+        }
+#if defined(__CUDA_ARCH__)
+#pragma unroll
+#endif
+        for (int k = 0; k < 4; ++k) {
+            if (k < n) a.order[it.start + k] = ids[k];
+        }
         it.kind = ITEM_SMALL;
         it.n_left = it.count / 2;
         return;
@@ -423,10 +450,15 @@ CV_D void body_flag(const BuildArrays& a, int i) {
 }
 
 // ---- per item: emit the two children into the next level ---------------------------
+CV_D void body_children_of(const BuildArrays& a, BuildItem& it);
 CV_D void body_children(const BuildArrays& a, int w, int n_items) {
     if (w >= n_items) return;
-    BuildItem& it = a.items[w];
+    BuildItem it = a.items[w];
     if (it.kind == ITEM_LEAF) return;
+    body_children_of(a, it);
+    a.items[w] = it;
+}
+CV_D void body_children_of(const BuildArrays& a, BuildItem& it) {
     const int n_left = a.scan[it.start + it.count] - a.scan[it.start];
     it.n_left = n_left;
     if (n_left <= 0 || n_left >= it.count) {  // empty side: the reference recurses into an empty set and traps (:139)

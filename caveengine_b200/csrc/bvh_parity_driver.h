@@ -8,6 +8,7 @@
 //   void download(void* dst, const void* src, size_t bytes);   // synchronises
 //   void fill(void* dst, int byte, size_t bytes);
 //   void parity_reduce(const BuildArrays&); void parity_bin(const BuildArrays&);   // body_reduce / body_bin over all triangles
+//   void parity_split(const BuildArrays&, int n_items);         // body_split over the level's items
 //   void parity_subtrees(const BuildArrays&, int n_roots);     // second phase: one block (or the serial statement) per queued root
 #pragma once
 #include <stddef.h>
@@ -91,7 +92,7 @@ int build_bvh_parity(Exec& ex, BuildArrays a, const int* tri_off_host, const int
         ex.parity_reduce(a);
         ex.launch(n_items, FnNode{ a, n_items });
         ex.parity_bin(a);
-        ex.launch(n_items, FnSplit{ a, n_items });
+        ex.parity_split(a, n_items);
         ex.launch(a.n_tris, FnFlag{ a });
         ex.scan_u8(a.flags, a.scan, a.n_tris);
         ex.launch(n_items, FnChildren{ a, n_items });

@@ -388,11 +388,15 @@ __device__ __forceinline__ void par_sub_bin(const BuildArrays& b, int start, int
 // operands (same cost bits), without every lane holding the whole 84-word record in registers.  Then every lane repeats
 // the serial selection over the eleven costs (first strict minimum, :190-193).
 // `list` holds the level's bucketed items (most items of the deep levels are not: one look per thread finds them).
+__device__ __forceinline__ void par_split_item(const BuildArrays& b, BuildItem& it, int lane);
 __device__ __forceinline__ void par_sub_split(const BuildArrays& b, const int* list, int n_list, int tid, int lane) {
+    for (int q = tid >> 4; q < n_list; q += kParSubThreads / 16) par_split_item(b, b.items[list[q]], lane);
+}
+// one bucketed item on the sixteen lanes of a half warp (all sixteen call it)
+__device__ __forceinline__ void par_split_item(const BuildArrays& b, BuildItem& it, int lane) {
     const unsigned hmask = 0xffffu << (lane & 16);
     const int sub = lane & 15, half = lane & 16;
-    for (int q = tid >> 4; q < n_list; q += kParSubThreads / 16) {
-        BuildItem& it = b.items[list[q]];
+    {
         const ItemBins& rec = b.bins[it.bin_slot];
         int cnt = 0;
         F3 bmn = f3(CV_INF, CV_INF, CV_INF), bmx = f3(-CV_INF, -CV_INF, -CV_INF);
@@ -435,6 +439,21 @@ __device__ __forceinline__ void par_sub_split(const BuildArrays& b, const int* l
         }
         if (sub == 0) it.split = split;
     }
+}
+// the level loop's split pass on the same sixteen-lane statement (the per-item serial body_split prices the eleven
+// candidates one after the other on one thread: 11 us per level for a few hundred items)
+__global__ void __launch_bounds__(256) k_parity_split(const BuildArrays a, int n_items) {
+    const int w = (int)((blockIdx.x * 256u + threadIdx.x) >> 4);
+    if (w >= n_items) return;  // uniform over a half warp
+    BuildItem& it = a.items[w];
+    if (it.kind != ITEM_SAH) return;
+    par_split_item(a, it, threadIdx.x & 31);
+}
+void CudaExec::parity_split(const BuildArrays& a, int n_items) {
+    if (n_items <= 0) return;
+    k_parity_split<<<(n_items * 16 + 255) / 256, 256, 0, stream>>>(a, n_items);
+    note(cudaGetLastError());
+    ++launches;
 }
 __global__ void __launch_bounds__(kParSubThreads, CV_PARITY_SUB_MINBLOCKS) k_parity_subtrees(const BuildArrays ga, int n_roots) {
     __shared__ int s_scan[kParitySubMax + 1];

@@ -25,6 +25,7 @@ struct CudaExec {
     void sort_pairs(uint32_t* keys, int* vals, uint32_t* keys_tmp, int* vals_tmp, int* hist, int n, int bits);
     void parity_reduce(const BuildArrays& a);  // parity builder: AABB / centroid folds, block-private where a block's triangles share an item
     void parity_bin(const BuildArrays& a);     // parity builder: bucket counts and boxes, same
+    void parity_split(const BuildArrays& a, int n_items);     // parity builder: the 11 candidate costs of every bucketed item, sixteen lanes per item
     void parity_subtrees(const BuildArrays& a, int n_roots);  // parity builder, second phase: one block builds the whole subtree of each queued item
     void wb_prim(const WBuild& b);  // world AABBs + scene / centroid bounds, block-reduced
     void wb_bin(const WBuild& b);                          // bin pass of a level, block-privatised in shared memory

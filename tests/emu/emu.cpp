@@ -43,6 +43,7 @@ struct EmuExec {
     void wb_prim(const WBuild& b) { launch(b.n_prims, FnWbPrim{ b }); }
     void parity_reduce(const BuildArrays& a) { launch(a.n_tris, FnReduce{ a }); }
     void parity_bin(const BuildArrays& a) { launch(a.n_tris, FnBin{ a }); }
+    void parity_split(const BuildArrays& a, int n_items) { launch(n_items, FnSplit{ a, n_items }); }
     void parity_subtrees(const BuildArrays& a, int n_roots) {
         for (int r = 0; r < n_roots; ++r) parity_subtree_serial(a, r);
         ++launches;

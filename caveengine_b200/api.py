@@ -50,6 +50,7 @@ class BvhMode(enum.IntEnum):
     PARITY = 0  # reference-layout per-mesh BVHs (bit-exact) + the production tree
     FAST = 1  # production tree only
     LBVH = 2  # production tree only, Morton-sort builder (per-frame rebuilds)
+    HYBRID = 3  # production tree only: LBVH's radix tree above, binned-SAH treelets of <= 768 triangles below
 
 
 ERR_INVALID_ARG, ERR_DEGENERATE_GEOMETRY, ERR_CUDA, ERR_NOT_READY, ERR_CAPACITY, ERR_NCCL = 1, 2, 3, 4, 5, 6

@@ -96,7 +96,7 @@ int build_world(cavept_ctx* ctx) {
     const int P = (int)total;
     ctx->n_prims = P;
     // interior items of a level are disjoint ranges of >= kFastLeafMax + 1 prims; only those of more than kWDirectMax prims own arena bins
-    const size_t items_cap = (size_t)P / (kFastLeafMax + 1) + 8, pairs_cap = (size_t)P + 8, bins_cap = (size_t)P / (kWDirectMax + 1) + 2, sub_cap = (size_t)P / 128 + 64;
+    const size_t items_cap = (size_t)P / (kFastLeafMax + 1) + 8, pairs_cap = (size_t)P + 8, bins_cap = (size_t)P / (kWDirectMax + 1) + 2, sub_cap = (size_t)P / (ctx->cfg.bvh_mode == CAVEPT_BVH_HYBRID ? 16 : 128) + 64;  // hybrid: a treelet next to a large sibling can be a sliver
     CU(ctx, ctx->d_inst_prim_off.reserve(n_inst + 1));
     CU(ctx, ctx->d_inst_tri_off.reserve(n_inst));
     CU(ctx, ctx->d_prim_bmin.reserve(P));
@@ -108,7 +108,8 @@ int build_world(cavept_ctx* ctx) {
     CU(ctx, ctx->d_w_flags.reserve(P));
     CU(ctx, ctx->d_w_scan.reserve((size_t)P + 1));
     CU(ctx, ctx->d_scan_tmp.reserve((size_t)P / kScanTile + 4));
-    const bool lbvh = ctx->cfg.bvh_mode == CAVEPT_BVH_LBVH;
+    const bool hybrid = ctx->cfg.bvh_mode == CAVEPT_BVH_HYBRID;  // the radix tree above, SAH treelets below
+    const bool lbvh = ctx->cfg.bvh_mode == CAVEPT_BVH_LBVH || hybrid;
     if (lbvh) {
         CU(ctx, ctx->d_w_keys.reserve(P));
         CU(ctx, ctx->d_w_keys_tmp.reserve(P));
@@ -116,6 +117,10 @@ int build_world(cavept_ctx* ctx) {
         CU(ctx, ctx->d_w_nbox_mn.reserve(pairs_cap));
         CU(ctx, ctx->d_w_nbox_mx.reserve(pairs_cap));
         CU(ctx, ctx->d_scan_tmp.reserve(std::max((size_t)P, sort_hist_entries(P)) / kScanTile + 4));
+        if (hybrid) {  // the subtree launch's queue and the depth tags it writes; it works out of shared memory otherwise
+            CU(ctx, ctx->d_pair_depth.reserve(pairs_cap));
+            CU(ctx, ctx->d_w_sub_roots.reserve(sub_cap));
+        }
     } else {
         CU(ctx, ctx->d_w_items.reserve(items_cap));
         CU(ctx, ctx->d_w_items_next.reserve(items_cap));
@@ -177,7 +182,7 @@ int build_world(cavept_ctx* ctx) {
     const unsigned long long launches_before = ctx->ex.launches;
     CU(ctx, cudaEventRecord(ctx->ev0, ctx->ex.stream));
     WReport rep{};
-    int rc = lbvh ? run_build_lbvh(ctx->ex, b, &rep) : run_build_wbvh(ctx->ex, b, &rep);
+    int rc = lbvh ? run_build_lbvh(ctx->ex, b, &rep, hybrid) : run_build_wbvh(ctx->ex, b, &rep);
     if (!lbvh && rc == 0 && rep.levels + 2 > kStackSize) {  // deeper than the traversal stack: rebuild balanced (median splits)
         b.force_median = 1;
         rc = run_build_wbvh(ctx->ex, b, &rep);

@@ -864,7 +864,7 @@ void CudaExec::wb_partition(const WBuild& b) {
 #define CV_SUB_THREADS 256
 #endif
 #ifndef CV_SUB_MINBLOCKS
-#define CV_SUB_MINBLOCKS 2
+#define CV_SUB_MINBLOCKS 3
 #endif
 constexpr int kSubThreads = CV_SUB_THREADS;
 constexpr int kSubWarps = kSubThreads / 32;
@@ -890,6 +890,7 @@ struct SubShared {
     int n_items[2];
     int lv_items[kWSubLevels + 2];
     int error;
+    int pair_next;  // hybrid builder (WItem::pair_lo >= 0): the next free slot of the subtree's own pair range; -1: pairs come from the global counter
 };
 __device__ __forceinline__ int sub_slot_axis(int item_axis, int a) { return kWAxes == 1 ? item_axis : a; }
 
@@ -903,7 +904,7 @@ __device__ __forceinline__ void sub_emit_children(SubShared& S, const WBuild& gb
         if (cnt[s] <= kFastLeafMax) {
             ref = make_leaf_ref(start + cs, cnt[s]);
         } else {
-            const int pair = atomicAdd(&gb.counters[1], 1);
+            const int pair = S.pair_next >= 0 ? atomicAdd(&S.pair_next, 1) : atomicAdd(&gb.counters[1], 1);
             const int slot = atomicAdd(&S.n_items[nxt], 1);
             if (pair >= gb.pairs_capacity || slot >= kSubItems) {
                 atomicOr(&gb.counters[2], WB_ERR_CAPACITY);
@@ -1116,6 +1117,7 @@ __global__ void __launch_bounds__(kSubThreads, CV_SUB_MINBLOCKS) k_wb_subtrees(c
         S.n_items[0] = 1;
         S.n_items[1] = 0;
         S.error = 0;
+        S.pair_next = root.pair_lo;
     }
     for (int l = tid; l < kWSubLevels + 2; l += kSubThreads) S.lv_items[l] = 0;
     __syncthreads();
@@ -1237,7 +1239,7 @@ void launch_emit_uvs(CudaExec& ex, const FastTri* ftris, const GpuPtIndex* indic
 }
 
 int run_build_wbvh(CudaExec& ex, WBuild b, WReport* report) { return build_wbvh(ex, b, report); }
-int run_build_lbvh(CudaExec& ex, WBuild b, WReport* report) { return build_lbvh(ex, b, report); }
+int run_build_lbvh(CudaExec& ex, WBuild b, WReport* report, bool hybrid) { return build_lbvh(ex, b, report, hybrid); }
 void run_build_q4(CudaExec& ex, WBuild b, int n_pairs) { ex.launch(n_pairs, FnWbQ4{ b, n_pairs }); }
 void run_refit_wbvh(CudaExec& ex, WBuild b, int n_pairs, int n_levels, const unsigned char* d_moved, float* d_area_sum, float out[7]) {
     refit_wbvh(ex, b, n_pairs, n_levels, d_moved, d_area_sum, out);

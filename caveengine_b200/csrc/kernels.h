@@ -51,7 +51,7 @@ void launch_assemble_indices(CudaExec& ex, const uint32_t* raw_indices, const in
 
 int run_build_bvh_parity(CudaExec& ex, BuildArrays a, const int* tri_off_host, const int* d_tri_off, int n_meshes, BuildItem* host_scratch, BuildReport* report);
 int run_build_wbvh(CudaExec& ex, WBuild b, WReport* report);
-int run_build_lbvh(CudaExec& ex, WBuild b, WReport* report);
+int run_build_lbvh(CudaExec& ex, WBuild b, WReport* report, bool hybrid = false);
 void run_build_q4(CudaExec& ex, WBuild b, int n_pairs);  // Q4Node records over a finished pair tree
 void run_refit_wbvh(CudaExec& ex, WBuild b, int n_pairs, int n_levels, const unsigned char* d_moved, float* d_area_sum, float out[7]);
 

@@ -41,7 +41,7 @@ constexpr int kWCounters = kWBinBase + kWMaxLevels + 4;   // ints in the counter
 constexpr int kWMedianDepth = 48;  // safety net: positional median splits below this depth
 
 #ifndef CV_SUB_MAX
-#define CV_SUB_MAX 1024
+#define CV_SUB_MAX 768
 #endif
 constexpr int kWSubMax = CV_SUB_MAX;   // an item of at most this many prims leaves the level-synchronous phase: its whole subtree is built by one thread block (wb_subtree_*)
 constexpr int kWSubLevels = 64;  // levels a subtree may have below its root
@@ -73,6 +73,7 @@ struct WItem {
     int bins_slot;      // index of this item's WBins in the arena (items of more than kWDirectMax prims), -1: none
     int scan_tile, scan_local;  // partition pass: tile holding `start` and the exclusive count of left flags before it in that tile
     float box_mn[3], box_mx[3];
+    int pair_lo;        // a queued subtree root of the hybrid builder: its subtree's pairs come from [pair_lo, ...), the dead radix-tree slots of its own range; -1: from the global counter
 };
 
 enum { WB_ERR_CAPACITY = 1 };
@@ -356,6 +357,7 @@ CV_D void wb_finish_split(const WBuild& b, WItem& it, int level, WBox box[2], in
                 c.child_item[0] = c.child_item[1] = -1;
                 c.bins_slot = bins_slot;
                 c.scan_tile = c.scan_local = 0;
+                c.pair_lo = -1;
                 c.box_mn[0] = box[s].mn.x; c.box_mn[1] = box[s].mn.y; c.box_mn[2] = box[s].mn.z;
                 c.box_mx[0] = box[s].mx.x; c.box_mx[1] = box[s].mx.y; c.box_mx[2] = box[s].mx.z;
                 wb_item_setup(c, b.force_median);
@@ -520,6 +522,8 @@ CV_D void wb_subtree_serial(const WBuild& gb, int r) {
     WBuild b;
     int lv_items[kWSubLevels + 2] = { 0 }, lv_bins[kWSubLevels + 2] = { 0 };
     const WItem root = wb_subtree_setup(gb, r, b, lv_items, lv_bins);
+    int own[4] = { 0, root.pair_lo, 0, 0 };  // hybrid builder: this subtree's pairs come from its own slot range
+    if (root.pair_lo >= 0) b.counters = own;
     const int start = root.start, end = root.start + root.count;
     for (int i = start; i < end; ++i) b.node_of[i] = 0;
     int level = 0;
@@ -544,6 +548,7 @@ CV_D void wb_subtree_serial(const WBuild& gb, int r) {
     if (b.order != gb.order) {
         for (int i = start; i < end; ++i) gb.order[i] = b.order[i];
     }
+    if (root.pair_lo >= 0 && own[2] != 0) cv_atomic_or_i32(&gb.counters[2], own[2]);
     wb_subtree_account(gb, root, level, lv_items);
 }
 
@@ -963,6 +968,45 @@ CV_D void wb_body_radix_pairs(const WBuild& b, int i) {
     wb_write_pair(b, i, box, ref, count);
 }
 
+// ---- hybrid builder (CAVEPT_BVH_HYBRID): the radix tree above, binned-SAH subtrees below -------------------------
+// After the radix tree is complete (boxes, pairs): every interior node of at most kWSubMax prims whose parent has more
+// is the root of a treelet that the SAH builder's subtree launch rebuilds from the prims (wb_subtree_* / k_wb_subtrees).
+// The treelet keeps the radix node's pair slot, so the record its parent holds stays valid; the pairs of its subtree
+// go to slots [first + 1, last - 1] -- the count - 2 radix nodes below it, dead from here on (a radix subtree over
+// [first, last] owns exactly those indices besides its own, which is `first` or `last`; the other end belongs to an
+// ancestor) -- and a binary tree over `count` prims needs at most count - 2 pairs below its root.  The pair array keeps
+// its size and the top of the tree costs what the LBVH costs, not one pass over all prims per level.
+CV_D void wb_body_hybrid_root(const WBuild& b, int i) {
+    if (i >= b.n_prims - 1) return;
+    const int first = b.node_first[i], last = b.node_last[i], count = last - first + 1;
+    if (count <= kFastLeafMax || count > kWSubMax) return;
+    int parent = i == 0 ? -1 : b.node_parent[i];
+    if (parent >= 0 && b.node_last[parent] - b.node_first[parent] + 1 <= kWSubMax) return;  // inside a treelet
+    int depth = 0;
+    for (int a = parent; a >= 0; a = b.node_parent[a]) ++depth;
+    const int q = cv_atomic_add_i32(&b.counters[3], 1);
+    if (q >= b.sub_capacity) {
+        cv_atomic_or_i32(&b.counters[2], WB_ERR_CAPACITY);
+        return;
+    }
+    WItem it;
+    it.start = first;
+    it.count = count;
+    it.pair = i;
+    it.depth = depth;
+    it.split = it.n_left = 0;
+    it.child_item[0] = it.child_item[1] = -1;
+    it.bins_slot = -1;
+    it.scan_tile = it.scan_local = 0;
+    it.pair_lo = first + 1;
+    const F4 mn = b.nbox_mn[i], mx = b.nbox_mx[i];
+    it.box_mn[0] = mn.x; it.box_mn[1] = mn.y; it.box_mn[2] = mn.z;
+    it.box_mx[0] = mx.x; it.box_mx[1] = mx.y; it.box_mx[2] = mx.z;
+    wb_item_setup(it, b.force_median);
+    b.pair_depth[i] = (unsigned char)depth;
+    b.sub_roots[q] = it;
+}
+
 CV_HD int wb_lbvh_lo(int n, int k, int j) { return (int)(((long long)j * (long long)n) >> k); }
 
 // box of the node (k, j) seen from its parent: a leaf's box is folded from its prims, an
@@ -1018,6 +1062,7 @@ struct FnWbRadixBoxes { WBuild b; int max_hops; int* list_out; int* count_out; C
 struct FnWbRadixResume { WBuild b; const int* list_in; const int* count_in; int max_hops; int* list_out; int* count_out; CV_D void operator()(int i) const { wb_body_radix_resume(b, i, list_in, count_in, max_hops, list_out, count_out); } };
 struct FnWbRadixLeafBox { WBuild b; CV_D void operator()(int i) const { wb_body_radix_leafbox(b, i); } };
 struct FnWbRadixPairs { WBuild b; CV_D void operator()(int i) const { wb_body_radix_pairs(b, i); } };
+struct FnWbHybridRoot { WBuild b; CV_D void operator()(int i) const { wb_body_hybrid_root(b, i); } };
 struct FnWbLbvhLevel { WBuild b; int k; CV_D void operator()(int i) const { wb_body_lbvh_level(b, i, k); } };
 struct FnWbQuantise { WBuild b; int n; CV_D void operator()(int i) const { wb_body_quantise(b, i, n); } };
 
@@ -1091,6 +1136,7 @@ int build_wbvh(Exec& ex, WBuild b, WReport* rep) {
     root.child_item[0] = root.child_item[1] = -1;
     root.bins_slot = b.n_prims > kWDirectMax ? 0 : -1;
     root.scan_tile = root.scan_local = 0;
+    root.pair_lo = -1;
     for (int k = 0; k < 3; ++k) {
         root.box_mn[k] = rep->scene_mn[k] - b.pad;
         root.box_mx[k] = rep->scene_mx[k] + b.pad;
@@ -1174,8 +1220,9 @@ int build_wbvh(Exec& ex, WBuild b, WReport* rep) {
 
 // LBVH build (see wb_body_morton): prologue, Morton codes, radix sort, one launch per level
 // bottom-up, emit.  No device->host round trip after the prologue.
+// hybrid = true: the radix tree's treelets of at most kWSubMax prims are rebuilt by the SAH subtree launch (wb_body_hybrid_root)
 template<class Exec>
-int build_lbvh(Exec& ex, WBuild b, WReport* rep) {
+int build_lbvh(Exec& ex, WBuild b, WReport* rep, bool hybrid = false) {
     uint32_t acc[12];
     if (wb_prologue(ex, b, rep, acc)) return 0;
     for (int k = 0; k < 3; ++k) {
@@ -1213,7 +1260,30 @@ int build_lbvh(Exec& ex, WBuild b, WReport* rep) {
     rep->levels = height;
     rep->n_pairs = b.n_prims - 1;  // internal-node slots in use (collapsed leaves are holes)
     rep->root_ref = 0;
-    if (height + 2 > kStackSize || b.force_median) {
+    bool too_deep = height + 2 > kStackSize;
+    if (hybrid && !too_deep && !b.force_median) {
+        int counters[kWCounters] = { 0 };
+        ex.upload(b.counters, counters, sizeof(counters));
+        b.level_items = b.counters + kWLevelBase;
+        b.level_bins = b.counters + kWBinBase;
+        ex.launch(b.n_prims - 1, FnWbHybridRoot{ b });
+        ex.download(counters, b.counters, sizeof(counters));
+        if (counters[2] != 0) {
+            rep->error_bits = counters[2];
+            return -1;
+        }
+        ex.wb_subtrees(b, counters[3]);
+        ex.download(counters, b.counters, sizeof(counters));
+        if (counters[2] != 0) {
+            rep->error_bits = counters[2];
+            return -1;
+        }
+        // a treelet may be deeper than the radix subtree it replaces: the height is what the subtree builds report
+        if (counters[0] > rep->levels) rep->levels = counters[0];
+        too_deep = rep->levels + 2 > kStackSize;
+        if (!too_deep) ex.launch(rep->n_pairs, FnWbQuantise{ b, rep->n_pairs });
+    }
+    if (too_deep || b.force_median) {
         int k_last = 0;  // deepest level that still has an interior node (sizes at a level differ by <= 1)
         while ((int)(((long long)b.n_prims + (1ll << (k_last + 1)) - 1) >> (k_last + 1)) > kFastLeafMax) ++k_last;
         for (int k = k_last; k >= 0; --k) ex.launch(1 << k, FnWbLbvhLevel{ b, k });

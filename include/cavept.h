@@ -64,8 +64,12 @@ enum { CAVEPT_TRACE_FAST = 0, CAVEPT_TRACE_REFERENCE_WALK = 1 };
  * per-frame rebuilds (the reference never rebuilds: path_tracer.cpp:69).
  * LBVH: the production tree only, built by Morton codes + radix sort + a bottom-up AABB
  * reduction (several times faster to build than FAST, somewhat slower to trace): for
- * geometry that changes every frame (BASELINE config 5). */
-enum { CAVEPT_BVH_PARITY = 0, CAVEPT_BVH_FAST = 1, CAVEPT_BVH_LBVH = 2 };
+ * geometry that changes every frame (BASELINE config 5).
+ * HYBRID: the production tree only: LBVH's radix tree down to treelets of at most 768 triangles, each of which is then
+ * rebuilt by the binned-SAH builder's subtree launch (one thread block per treelet, out of shared memory).  Nearly FAST's
+ * tree quality (config 3's scene: 74.3 node records per segment against 72.6 / LBVH 80.3) at a build cost that does not
+ * pay one pass over all triangles per level: for large static scenes (several million triangles). */
+enum { CAVEPT_BVH_PARITY = 0, CAVEPT_BVH_FAST = 1, CAVEPT_BVH_LBVH = 2, CAVEPT_BVH_HYBRID = 3 };
 
 /* Which production kernel CAVEPT_TRACE_FAST launches.  Same tree, same per-pixel arithmetic in the same per-pixel order:
  * POOL, PIXEL and QUEUE produce bit-identical images (tests/test_gpu_parity.py).

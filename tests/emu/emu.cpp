@@ -155,7 +155,7 @@ EMU_API void emu_bind_pair_depth(unsigned char* p) { g_pair_depth = p; }
 // n_inst + 1 entries, inst_tri_off n_inst.  fnodes needs 2 * (n_prims + 8) entries, qpairs n_prims + 8, ftris /
 // fnormals n_prims.  Returns 0 ok; report = {levels, n_pairs, root_ref, error_bits}.
 EMU_API int emu_wbvh_build(const GpuPtVertex* vertices, const GpuPtIndex* indices, const GpuPtMesh* instances, int n_inst, const int* inst_prim_off,
-                           const int* inst_tri_off, int force_median /* 2: LBVH builder, 3: its balanced fallback */, FastNode* fnodes, QPair* qpairs, FastTri* ftris, FastTri* fnormals, int* report, float* out_pad,
+                           const int* inst_tri_off, int force_median /* 2: LBVH builder, 3: its balanced fallback, 4: hybrid (radix tree + SAH treelets) */, FastNode* fnodes, QPair* qpairs, FastTri* ftris, FastTri* fnormals, int* report, float* out_pad,
                            float* out_grid) {
     const int P = inst_prim_off[n_inst];
     const size_t items_cap = (size_t)P / 2 + 8, pairs_cap = (size_t)P + 8;
@@ -210,7 +210,7 @@ EMU_API int emu_wbvh_build(const GpuPtVertex* vertices, const GpuPtIndex* indice
     b.fnormals = fnormals;
     EmuExec ex;
     WReport rep{};
-    const int rc = force_median >= 2 ? build_lbvh(ex, b, &rep) : build_wbvh(ex, b, &rep);
+    const int rc = force_median >= 2 ? build_lbvh(ex, b, &rep, force_median == 4) : build_wbvh(ex, b, &rep);
     report[0] = rep.levels;
     report[1] = rep.n_pairs;
     report[2] = wb_quantised_ref(rep.root_ref);

@@ -84,7 +84,7 @@ class EmuScene:
             return
         self.build_world(asm, scene, built)
 
-    def build_world(self, asm, scene, built, force_median=False, lbvh=False):
+    def build_world(self, asm, scene, built, force_median=False, lbvh=False, hybrid=False):
         """Production (world-space) BVH, as cavept_api.cu's build_world() drives it."""
         n_inst = len(scene.instances)
         tri_counts = [scene.meshes[i.mesh].n_tris for i in scene.instances]
@@ -104,7 +104,7 @@ class EmuScene:
         report = np.zeros(4 + 124, dtype=np.int32)
         pad = C.c_float()
         self.wrc = self.lib.emu_wbvh_build(_p(asm.vertices), _p(asm.indices), _p(asm.meshes), C.c_int(n_inst), _p(self.inst_prim_off), _p(self.inst_tri_off),
-                                           C.c_int((3 if force_median else 2) if lbvh else (1 if force_median else 0)), _p(self.fnodes), _p(self.qpairs), _p(self.ftris), _p(self.fnormals), _p(report), C.byref(pad),
+                                           C.c_int(4 if hybrid else ((3 if force_median else 2) if lbvh else (1 if force_median else 0))), _p(self.fnodes), _p(self.qpairs), _p(self.ftris), _p(self.fnormals), _p(report), C.byref(pad),
                                            _p(self.grid))
         self.fast_levels, self.n_pairs, self.root_ref, self.wb_error_bits = [int(v) for v in report[:4]]
         self.level_items = report[4:4 + self.fast_levels].copy()

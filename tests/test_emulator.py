@@ -302,6 +302,32 @@ def test_lbvh_tree_invariants_and_same_hits(port_oracle, scene_cache, name):
     assert H.image_mismatch(img_bal, img_sah, rel=0.0, floor=0.0) <= 0.01
 
 
+@pytest.mark.parametrize("name", ["tiny", "cornell", "heightfield"])
+def test_hybrid_tree_invariants_and_same_hits(port_oracle, scene_cache, name):
+    """CAVEPT_BVH_HYBRID: the radix tree above, the SAH builder's subtree phase below (treelets of <= 768 prims rebuilt in
+    the dead pair slots of their own range): the tree invariants hold with the pair array no larger than the LBVH's, and
+    the closest hits are the SAH tree's."""
+    sc = scene_cache(name)
+    asm = port_oracle.assemble(sc)
+    emu = E.EmuScene(asm, sc)
+    img_sah, st_sah = emu.render(sc.camera, 40, 24, 0, 2, 4, fast=True)
+    built = []
+    for inst in sc.instances:
+        if inst.mesh not in built:
+            built.append(inst.mesh)
+    emu.build_world(asm, sc, built, lbvh=True)
+    _, st_lbvh = emu.render(sc.camera, 40, 24, 0, 2, 4, fast=True)
+    emu.build_world(asm, sc, built, hybrid=True)
+    assert emu.wrc == 0 and emu.wb_error_bits == 0
+    assert emu.n_pairs == emu.n_prims - 1
+    depth = _world_tree_check(emu, asm, sc, holes_ok=True)
+    assert depth <= emu.fast_levels
+    img_h, st_h = emu.render(sc.camera, 40, 24, 0, 2, 4, fast=True)
+    assert H.image_mismatch(img_h, img_sah, rel=0.0, floor=0.0) <= 0.01  # exact-tie pixels only
+    # tree quality: no worse than the plain radix tree (node records per segment)
+    assert st_h["node_visits"] <= 1.02 * st_lbvh["node_visits"], (st_h["node_visits"], st_lbvh["node_visits"], st_sah["node_visits"])
+
+
 def test_world_tree_with_mirrored_instance(port_oracle):
     """det(transform) < 0 flips the winding the reference's mesh-space back-face test sees; the
     world-space triangles are stored (A, C, B) so the same faces are culled."""

@@ -473,6 +473,31 @@ def test_lbvh_mode_same_closest_hits(api, scene_cache, name):
     assert 1 <= stats[1]["fast_build_levels"] <= 38  # radix-tree height, or the balanced fallback's: fits the traversal stack
 
 
+@pytest.mark.parametrize("name", ["tiny", "cornell", "sponza"])
+def test_hybrid_mode_same_closest_hits_and_fewer_visits_than_lbvh(api, scene_cache, name):
+    """CAVEPT_BVH_HYBRID (radix tree above, binned-SAH treelets of <= 768 triangles below, rebuilt in the dead pair slots of
+    their own range): the SAH tree's closest hits, the LBVH's pair count, and node visits between the two."""
+    sc = scene_cache(name)
+    w, h, mb = (160, 90, 5) if name != "sponza" else (320, 180, 8)
+    imgs, stats = [], []
+    for mode in (api.BvhMode.FAST, api.BvhMode.LBVH, api.BvhMode.HYBRID):
+        with api.PathTracer(w, h, mb, bvh_mode=mode) as pt:
+            pt.set_mode(api.PathTracerMode.INTERACTIVE)
+            pt.request_update(sc)
+            pt.set_count_visits(True)
+            pt.reset_stats()
+            pt.render(0, 2, sync=True)
+            imgs.append(pt.read_accum())
+            stats.append(pt.stats())
+    H.check_metrics(H.image_metrics(imgs[2], imgs[0]), LIMITS["lbvh_vs_sah"], f"hybrid_vs_sah_{name}")
+    assert abs(stats[0]["segments"] - stats[2]["segments"]) <= max(4, stats[0]["segments"] // 1000)
+    assert stats[2]["fast_node_count"] == stats[1]["fast_node_count"]  # no pair beyond the radix tree's n - 1
+    assert 1 <= stats[2]["fast_build_levels"] <= 38
+    if name == "sponza":  # 262,144 triangles: ~400 treelets
+        assert stats[2]["node_visits"] < 0.96 * stats[1]["node_visits"], (stats[2]["node_visits"], stats[1]["node_visits"], stats[0]["node_visits"])
+        assert stats[2]["node_visits"] < 1.06 * stats[0]["node_visits"]
+
+
 def test_lbvh_rebuild_follows_moving_vertices(api, port_oracle):
     """Per-frame rebuild (BASELINE config 5 at small size): new vertex positions -> LBVH rebuild
     -> the image equals a fresh upload of the moved mesh, and matches the CPU oracle."""

@@ -1,8 +1,13 @@
 // __global__ wrappers for the kernel bodies, the scan primitive, and launchers.
 // Compiled for sm_100a only, with -fmad=false (see cv_common.h on float semantics).
 #include "kernels.h"
-#ifdef CV_PARITY_SUB_PROFILE
+#if defined(CV_PARITY_SUB_PROFILE) || defined(CV_SUB_PROFILE)
 #include <cstdio>
+#endif
+#ifdef CV_SUB_PROFILE
+#define SUBT(k) { const long long t1_ = clock64(); prof[k] += t1_ - t0_; t0_ = t1_; }
+#else
+#define SUBT(k)
 #endif
 
 #include <cuda_fp16.h>
@@ -949,6 +954,12 @@ __device__ __forceinline__ void sub_median(const SItem& it, WBox box[2], int cnt
 // smaller cost" never prefers -- so the thread evaluates those <= count candidates per axis directly from the prims
 // (count^2 box unions per axis, boxes read from shared memory) and keeps the lexicographic minimum of (cost, axis
 // slot * 16 + k).  Unions are exact min / max, the cost is the same three fp32 operations: same bits as the sweep.
+#ifndef CV_SUB_SERIAL_SWEEP
+#define CV_SUB_SERIAL_SWEEP 1
+#endif
+#ifndef CV_SUB_HALF_ITEMS
+#define CV_SUB_HALF_ITEMS 1
+#endif
 constexpr int kSubSerialMax = 16;
 __device__ void sub_item_serial(SubShared& S, const WBuild& gb, int cur, int nxt, int w, int start) {
     const SItem& it = S.items[cur][w];
@@ -967,6 +978,54 @@ __device__ void sub_item_serial(SubShared& S, const WBuild& gb, int cur, int nxt
                 const int id = S.ord[cur][s0 + j];
                 packed |= (unsigned long long)wb_bin_at(it.box_mn, it.cscale, ax, S.pmn[id], S.pmx[id]) << (4 * j);
             }
+#if CV_SUB_SERIAL_SWEEP
+            // The same candidates at O(count) unions per axis instead of count^2: the prims of bin k are found by a
+            // nibble-equality mask over `packed`; a descending pass leaves the half area of "every prim of a bin > k"
+            // for each k, an ascending pass grows "every prim of a bin <= k" and prices plane k wherever some prim has
+            // bin k.  Unions are exact min / max (order-free), the cost is the same expression on the same boxes, and
+            // planes come in ascending (axis slot, k) order with a strict "<": the same lexicographic minimum.
+            const unsigned long long ones = 0x1111111111111111ull, live = c >= 16 ? ~0ull : ((1ull << (4 * c)) - 1ull);
+            float right_area[kWBins];
+            {
+                WBox r = wb_empty();
+#pragma unroll
+                for (int k = kWBins - 1; k >= 1; --k) {
+                    unsigned long long x = packed ^ (ones * (unsigned long long)k);
+                    x |= x >> 1;
+                    x |= x >> 2;
+                    for (unsigned long long m = ~x & ones & live; m; m &= m - 1) {
+                        const int id = S.ord[cur][s0 + ((__ffsll((long long)m) - 1) >> 2)];
+                        const F4 mn = S.pmn[id], mx = S.pmx[id];
+                        wb_grow(r, f3(mn.x, mn.y, mn.z), f3(mx.x, mx.y, mx.z));
+                    }
+                    right_area[k] = wb_half_area(r);  // read only where the right side is not empty
+                }
+            }
+            {
+                WBox l = wb_empty();
+                int nl = 0;
+#pragma unroll
+                for (int k = 0; k < kWBins - 1; ++k) {
+                    unsigned long long x = packed ^ (ones * (unsigned long long)k);
+                    x |= x >> 1;
+                    x |= x >> 2;
+                    unsigned long long m = ~x & ones & live;
+                    if (m == 0ull) continue;  // no prim has bin k: not a candidate
+                    for (; m; m &= m - 1) {
+                        const int id = S.ord[cur][s0 + ((__ffsll((long long)m) - 1) >> 2)];
+                        const F4 mn = S.pmn[id], mx = S.pmx[id];
+                        wb_grow(l, f3(mn.x, mn.y, mn.z), f3(mx.x, mx.y, mx.z));
+                        ++nl;
+                    }
+                    if (nl == c) continue;  // nothing on the right
+                    const float cost = (float)nl * wb_half_area(l) + (float)(c - nl) * right_area[k + 1];
+                    if (cost < best_cost) {
+                        best_cost = cost;
+                        best_key = a * kWBins + k;
+                    }
+                }
+            }
+#else
             for (int j = 0; j < c; ++j) {
                 const int k = (int)((packed >> (4 * j)) & 15ull);
                 if (k >= kWBins - 1) continue;
@@ -994,12 +1053,23 @@ __device__ void sub_item_serial(SubShared& S, const WBuild& gb, int cur, int nxt
                     cnt[1] = c - nl;
                 }
             }
+#endif
         }
         if (best_key < 0) {
             axis = -1;
         } else {
             axis = sub_slot_axis(axis, best_key / kWBins);
             split = best_key % kWBins;
+#if CV_SUB_SERIAL_SWEEP
+            // the two sides of the winning plane (the sweep kept areas only)
+            for (int j = 0; j < c; ++j) {
+                const int id = S.ord[cur][s0 + j];
+                const F4 mn = S.pmn[id], mx = S.pmx[id];
+                const int side = wb_bin_at(it.box_mn, it.cscale, axis, mn, mx) <= split ? 0 : 1;
+                wb_grow(box[side], f3(mn.x, mn.y, mn.z), f3(mx.x, mx.y, mx.z));
+                ++cnt[side];
+            }
+#endif
         }
     }
     if (axis < 0) sub_median(it, box, cnt);
@@ -1014,8 +1084,121 @@ __device__ void sub_item_serial(SubShared& S, const WBuild& gb, int cur, int nxt
         S.item_of[nxt][dst] = (short)(flag ? child[0] : child[1]);
     }
 }
+// The same small item on a GROUP of G = 4 / 8 / 16 adjacent lanes (all G call it; G >= count): lane j < count holds prim j and prices the
+// plane "bin of prim j" on each axis over all the item's prims -- count unions per lane instead of count^2 in one thread,
+// every lane in step (the boxes are read from shared memory at one address: a broadcast).  The half warp then takes the
+// lexicographic minimum of (cost, axis slot * 16 + k) by shuffles -- the order sub_item_serial's "cost < best || (cost ==
+// best && key < best_key)" realises -- and the winning lane's two boxes and counts go to every lane; lane 0 emits the
+// children; the stable partition is a ballot prefix over the sixteen lanes.  Same candidates, same unions (exact min /
+// max), same cost expression: the same tree.
+template<int G>
+__device__ __forceinline__ void sub_item_group(SubShared& S, const WBuild& gb, int cur, int nxt, int w, int start, int lane) {
+    const int sub = lane & (G - 1), half = lane & ~(G - 1);  // `half`: the group's first lane
+    const unsigned hmask = ((1u << G) - 1u) << half;
+    const SItem& it = S.items[cur][w];
+    const int s0 = it.start, c = it.count;
+    const bool mine = sub < c;
+    int axis = it.axis, split = 0;
+    WBox box[2];
+    int cnt[2] = { 0, 0 };
+    box[0] = box[1] = wb_empty();
+    const int my_id = mine ? S.ord[cur][s0 + sub] : 0;
+    int my_bin[kWAxes];
+#pragma unroll
+    for (int a = 0; a < kWAxes; ++a) my_bin[a] = 0;
+    if (axis >= 0) {
+        const F4 pmn = S.pmn[my_id], pmx = S.pmx[my_id];
+        float best_cost = CV_INF;
+        int best_key = 0x7fffffff, best_nl = 0;
+        WBox best_l = wb_empty(), best_r = wb_empty();
+#pragma unroll
+        for (int a = 0; a < kWAxes; ++a) {
+            const int ax = sub_slot_axis(axis, a);
+            const int k = mine ? wb_bin_at(it.box_mn, it.cscale, ax, pmn, pmx) : kWBins;  // a lane without a prim prices nothing
+            my_bin[a] = k;
+            WBox l = wb_empty(), r = wb_empty();
+            int nl = 0;
+            for (int i = 0; i < c; ++i) {
+                const int ki = __shfl_sync(hmask, k, half + i);
+                const int id = S.ord[cur][s0 + i];
+                const F4 mn = S.pmn[id], mx = S.pmx[id];
+                if (ki <= k) {
+                    wb_grow(l, f3(mn.x, mn.y, mn.z), f3(mx.x, mx.y, mx.z));
+                    ++nl;
+                } else {
+                    wb_grow(r, f3(mn.x, mn.y, mn.z), f3(mx.x, mx.y, mx.z));
+                }
+            }
+            if (mine && k < kWBins - 1 && nl != c) {
+                const float cost = (float)nl * wb_half_area(l) + (float)(c - nl) * wb_half_area(r);
+                const int key = a * kWBins + k;
+                if (cost < best_cost || (cost == best_cost && key < best_key)) {
+                    best_cost = cost;
+                    best_key = key;
+                    best_nl = nl;
+                    best_l = l;
+                    best_r = r;
+                }
+            }
+        }
+        // the half warp's minimum of (cost, key); then everything of the lane that holds it
+        float m_cost = best_cost;
+        int m_key = best_key;
+#pragma unroll
+        for (int d = G / 2; d >= 1; d >>= 1) {
+            const float oc = __shfl_xor_sync(hmask, m_cost, d);
+            const int ok = __shfl_xor_sync(hmask, m_key, d);
+            if (oc < m_cost || (oc == m_cost && ok < m_key)) {
+                m_cost = oc;
+                m_key = ok;
+            }
+        }
+        if (m_key == 0x7fffffff) {
+            axis = -1;  // no plane separates the prims: median split
+        } else {
+            const unsigned holders = __ballot_sync(hmask, best_cost == m_cost && best_key == m_key) & hmask;
+            const int src = __ffs(holders) - 1;  // lane index within the warp
+            box[0].mn = f3(__shfl_sync(hmask, best_l.mn.x, src), __shfl_sync(hmask, best_l.mn.y, src), __shfl_sync(hmask, best_l.mn.z, src));
+            box[0].mx = f3(__shfl_sync(hmask, best_l.mx.x, src), __shfl_sync(hmask, best_l.mx.y, src), __shfl_sync(hmask, best_l.mx.z, src));
+            box[1].mn = f3(__shfl_sync(hmask, best_r.mn.x, src), __shfl_sync(hmask, best_r.mn.y, src), __shfl_sync(hmask, best_r.mn.z, src));
+            box[1].mx = f3(__shfl_sync(hmask, best_r.mx.x, src), __shfl_sync(hmask, best_r.mx.y, src), __shfl_sync(hmask, best_r.mx.z, src));
+            cnt[0] = __shfl_sync(hmask, best_nl, src);
+            cnt[1] = c - cnt[0];
+            axis = sub_slot_axis(axis, m_key / kWBins);
+            split = m_key % kWBins;
+        }
+    }
+    if (axis < 0) sub_median(it, box, cnt);
+    int child[2] = { -1, -1 };
+    if (sub == 0) sub_emit_children(S, gb, it, nxt, start, box, cnt, child);
+    child[0] = __shfl_sync(hmask, child[0], half);
+    child[1] = __shfl_sync(hmask, child[1], half);
+    // stable partition: lefts keep their order, rights keep theirs
+    bool flag = false;
+    if (mine) {
+        if (axis >= 0) {
+            int kb = my_bin[0];
+#pragma unroll
+            for (int a = 1; a < kWAxes; ++a) kb = (kWAxes > 1 && axis == a) ? my_bin[a] : kb;
+            flag = kb <= split;
+        } else {
+            flag = sub < cnt[0];
+        }
+    }
+    const unsigned gbits = (1u << G) - 1u;
+    const unsigned lefts = (__ballot_sync(hmask, flag) >> half) & gbits, valid = (__ballot_sync(hmask, mine) >> half) & gbits;
+    if (mine) {
+        const unsigned lt = (1u << sub) - 1u;
+        const int dst = flag ? s0 + __popc(lefts & lt) : s0 + cnt[0] + __popc(~lefts & valid & lt);
+        S.ord[nxt][dst] = (unsigned short)my_id;
+        S.item_of[nxt][dst] = (short)(flag ? child[0] : child[1]);
+    }
+}
 // A larger item, all of it in ONE warp: bins in the warp's own shared memory, the warp-wide sweep, partition by ballot prefix.
-__device__ void sub_item_warp(SubShared& S, const WBuild& gb, int cur, int nxt, int w, int start, int warp, int lane) {
+__device__ void sub_item_warp(SubShared& S, const WBuild& gb, int cur, int nxt, int w, int start, int warp, int lane, long long* prof) {
+#ifdef CV_SUB_PROFILE
+    long long t0_ = clock64();
+#endif
     const SItem& it = S.items[cur][w];
     WBin* wb = S.bins[warp];
     const int s0 = it.start, c = it.count;
@@ -1042,8 +1225,10 @@ __device__ void sub_item_warp(SubShared& S, const WBuild& gb, int cur, int nxt, 
             }
         }
         __syncwarp();
+        SUBT(0)
         const WSweep sw = wb_warp_sweep<false>(wb, lane);
         __syncwarp();
+        SUBT(1)
         if (sw.best == ~0ull) {
             axis = -1;  // every prim in one bin on every axis: median split
         } else {
@@ -1061,6 +1246,7 @@ __device__ void sub_item_warp(SubShared& S, const WBuild& gb, int cur, int nxt, 
     if (lane == 0) sub_emit_children(S, gb, it, nxt, start, box, cnt, child);
     child[0] = __shfl_sync(0xffffffffu, child[0], 0);
     child[1] = __shfl_sync(0xffffffffu, child[1], 0);
+    SUBT(2)
     // stable partition of the item's positions: lefts keep their order, rights keep theirs
     int left_run = 0, right_run = 0;
     for (int base = 0; base < c; base += 32) {
@@ -1081,6 +1267,7 @@ __device__ void sub_item_warp(SubShared& S, const WBuild& gb, int cur, int nxt, 
         right_run += __popc(~m & mv);
     }
     __syncwarp();
+    SUBT(3)
 }
 
 __global__ void __launch_bounds__(kSubThreads, CV_SUB_MINBLOCKS) k_wb_subtrees(const WBuild gb, int n_roots) {
@@ -1122,6 +1309,11 @@ __global__ void __launch_bounds__(kSubThreads, CV_SUB_MINBLOCKS) k_wb_subtrees(c
     for (int l = tid; l < kWSubLevels + 2; l += kSubThreads) S.lv_items[l] = 0;
     __syncthreads();
     int cur = 0, level = 0;
+    long long prof[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };
+#ifdef CV_SUB_PROFILE
+    long long t0_ = clock64();
+    const long long tstart_ = t0_;
+#endif
     for (;; ++level, cur ^= 1) {
         const int ni = S.n_items[cur];
         if (ni == 0) break;
@@ -1139,16 +1331,30 @@ __global__ void __launch_bounds__(kSubThreads, CV_SUB_MINBLOCKS) k_wb_subtrees(c
             }
         }
         for (int w = warp; w < ni; w += kSubWarps) {  // warp-uniform
-            if (S.items[cur][w].count > kSubSerialMax) sub_item_warp(S, gb, cur, nxt, w, start, warp, lane);
+            if (S.items[cur][w].count > kSubSerialMax) sub_item_warp(S, gb, cur, nxt, w, start, warp, lane, prof);
         }
+        SUBT(4)
+#if CV_SUB_HALF_ITEMS
+        // small items: sixteen lanes each (sub_item_group<16>); one thread per item (sub_item_serial) waits on one lane's chain
+        // of count^2 unions.  (Groups of 8 and 4 lanes for items of <= 8 / <= 4 prims, three passes: measured 2-18 % slower.)
+        for (int w = tid >> 4; w < ni; w += kSubThreads / 16) {  // uniform over a half warp
+            if (S.items[cur][w].count <= kSubSerialMax) sub_item_group<16>(S, gb, cur, nxt, w, start, lane);
+        }
+#else
         for (int w = tid; w < ni; w += kSubThreads) {
             if (S.items[cur][w].count <= kSubSerialMax) sub_item_serial(S, gb, cur, nxt, w, start);
         }
+#endif
+        SUBT(5)
         __syncthreads();
+        SUBT(6)
         if (tid == 0) S.n_items[cur] = 0;  // becomes the level after next
         __syncthreads();
     }
     __syncthreads();
+#ifdef CV_SUB_PROFILE
+    if ((r % 97) == 0 && (tid == 0 || tid == 224)) printf("root %d n %d levels %d warp %d total %lld | in warp items: bin %lld sweep %lld emit %lld partition %lld | loop: warp-items(+carry) %lld serial-items %lld barrier %lld\n", r, n, level, warp, clock64() - tstart_, prof[0], prof[1], prof[2], prof[3], prof[4], prof[5], prof[6]);
+#endif
     for (int j = tid; j < n; j += kSubThreads) gb.order[start + j] = S.gid[S.ord[cur][j]];
     if (tid == 0) {
         if (S.error) atomicOr(&gb.counters[2], WB_ERR_CAPACITY);

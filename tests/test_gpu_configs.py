@@ -170,3 +170,37 @@ def test_lbvh_balanced_fallback_is_taken_and_traces_the_same_hits(api):
     assert H.image_mismatch(imgs[1], imgs[0], rel=0.0, floor=0.0) <= 0.005
     assert abs(stats[0]["segments"] - stats[1]["segments"]) <= max(4, stats[0]["segments"] // 1000)
     assert imgs[0][..., :3].max() > 0.5  # the cluster is visible: the comparison is not of two empty images
+
+
+def test_hybrid_builder_on_config4_and_config5_scenes_and_on_the_deep_radix_input(api, scene_cache):
+    """CAVEPT_BVH_HYBRID (radix tree above, SAH treelets below) on 1,048,576 and 500,128 triangles: the SAH tree's
+    closest hits (images agree except at exact-tie pixels), the LBVH's pair count, fewer node visits than the LBVH; and on
+    the input whose radix tree is deeper than the traversal stack it takes the balanced fallback like the LBVH does."""
+    for name, (w, h, mb) in (("breakfast", (160, 90, 8)), ("animated", (160, 90, 5))):
+        sc = scene_cache(name)
+        imgs, stats = [], []
+        for mode in (api.BvhMode.FAST, api.BvhMode.LBVH, api.BvhMode.HYBRID):
+            with api.PathTracer(w, h, mb, bvh_mode=mode) as pt:
+                pt.set_mode(api.PathTracerMode.INTERACTIVE)
+                pt.request_update(sc)
+                pt.set_count_visits(True)
+                pt.reset_stats()
+                pt.render(0, 2, sync=True)
+                imgs.append(pt.read_accum())
+                stats.append(pt.stats())
+        assert H.image_mismatch(imgs[2], imgs[0], rel=0.0, floor=0.0) <= 0.01, name
+        assert abs(stats[0]["segments"] - stats[2]["segments"]) <= max(4, stats[0]["segments"] // 1000)
+        assert stats[2]["fast_node_count"] == stats[1]["fast_node_count"] and 1 <= stats[2]["fast_build_levels"] <= 38
+        assert stats[2]["node_visits"] < stats[1]["node_visits"], (name, stats[2]["node_visits"], stats[1]["node_visits"], stats[0]["node_visits"])
+    sc = H.lbvh_chain_scene(2048)
+    imgs, stats = [], []
+    for mode in (api.BvhMode.FAST, api.BvhMode.HYBRID):
+        with api.PathTracer(192, 108, 4, bvh_mode=mode) as pt:
+            pt.set_mode(api.PathTracerMode.INTERACTIVE)
+            pt.request_update(sc)
+            pt.reset_stats()
+            pt.render(0, 2, sync=True)
+            imgs.append(pt.read_accum())
+            stats.append(pt.stats())
+    assert stats[1]["fast_build_levels"] == int(np.ceil(np.log2(sc.n_tris / 2))), stats[1]
+    assert H.image_mismatch(imgs[1], imgs[0], rel=0.0, floor=0.0) <= 0.005
